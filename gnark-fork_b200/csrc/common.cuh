@@ -1,0 +1,102 @@
+// Shared host-side plumbing of the C ABI: context, error reporting, device buffers.
+#pragma once
+#include <cuda_runtime.h>
+#include <cstdint>
+#include <cstdio>
+#include <string>
+#include <vector>
+#include "../../include/b200prover.h"
+#include "field.cuh"
+#include "ec.cuh"
+
+namespace b200 {
+struct NttDomain;
+}
+
+struct b200_ctx {
+    int device = 0;
+    int sm_count = 0;
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    std::string err;
+    std::vector<b200::NttDomain*> domains;  // cache keyed by (log_n, generator, coset_gen)
+    void* scratch = nullptr;                // grow-only workspace shared by MSM / prove calls
+    size_t scratch_bytes = 0;
+    int msm_c_override = 0;                 // B200_MSM_C env (tuning): window width
+
+    int fail(int status, const char* what, const char* detail = nullptr) {
+        err = what;
+        if (detail) { err += ": "; err += detail; }
+        return status;
+    }
+};
+
+#define B2_CUDA(ctx, call)                                                                     \
+    do {                                                                                       \
+        cudaError_t e_ = (call);                                                               \
+        if (e_ != cudaSuccess) {                                                               \
+            char buf_[256];                                                                    \
+            snprintf(buf_, sizeof buf_, "%s:%d %s -> %s", __FILE__, __LINE__, #call,           \
+                     cudaGetErrorString(e_));                                                  \
+            return (ctx)->fail(e_ == cudaErrorMemoryAllocation ? B200_ERR_NOMEM : B200_ERR_CUDA, \
+                               "CUDA error", buf_);                                            \
+        }                                                                                      \
+    } while (0)
+
+#define B2_TRY(expr)                    \
+    do {                                \
+        int st_ = (expr);               \
+        if (st_ != B200_OK) return st_; \
+    } while (0)
+
+namespace b200 {
+
+// RAII device allocation (freed on scope exit; all work is ordered on ctx->stream and the
+// owning entry point synchronises before returning).
+struct DevBuf {
+    void* p = nullptr;
+    size_t bytes = 0;
+    DevBuf() {}
+    DevBuf(const DevBuf&) = delete;
+    DevBuf& operator=(const DevBuf&) = delete;
+    ~DevBuf() { release(); }
+    cudaError_t alloc(size_t n) {
+        release();
+        if (n == 0) n = 16;
+        cudaError_t e = cudaMalloc(&p, n);
+        if (e == cudaSuccess) bytes = n; else p = nullptr;
+        return e;
+    }
+    void release() { if (p) cudaFree(p); p = nullptr; bytes = 0; }
+    template <class T> T* as() const { return reinterpret_cast<T*>(p); }
+};
+
+// Bump allocator over the ctx workspace (256-byte aligned slices).
+struct Arena {
+    char* base = nullptr;
+    size_t off = 0;
+    static size_t align(size_t x) { return (x + 255) & ~(size_t)255; }
+    void* take(size_t bytes) {
+        void* p = base ? base + off : nullptr;
+        off += align(bytes ? bytes : 1);
+        return p;
+    }
+};
+
+// Make the ctx workspace at least `bytes` large (synchronises and reallocates when it grows).
+static inline int ctx_reserve(b200_ctx* ctx, size_t bytes) {
+    if (bytes <= ctx->scratch_bytes) return B200_OK;
+    cudaError_t e = cudaStreamSynchronize(ctx->stream);
+    if (e != cudaSuccess) return ctx->fail(B200_ERR_CUDA, "sync before workspace growth", cudaGetErrorString(e));
+    if (ctx->scratch) cudaFree(ctx->scratch);
+    ctx->scratch = nullptr;
+    ctx->scratch_bytes = 0;
+    e = cudaMalloc(&ctx->scratch, bytes);
+    if (e != cudaSuccess) { ctx->scratch = nullptr; return ctx->fail(B200_ERR_NOMEM, "workspace", cudaGetErrorString(e)); }
+    ctx->scratch_bytes = bytes;
+    return B200_OK;
+}
+
+static inline unsigned ceil_log2(size_t x) { unsigned l = 0; while (((size_t)1 << l) < x) ++l; return l; }
+
+}  // namespace b200

@@ -1,0 +1,162 @@
+// BN254 G1 / G2 group arithmetic for the MSM kernels and the host-side fix-ups.
+//
+// Device-side mirror of gnark-crypto's G1Affine / G1Jac / G2Affine / G2Jac as they are used by
+// /root/reference/backend/groth16/bn254/prove.go:192-301 (MultiExp inputs are affine bases with
+// (0,0) = infinity; results are Jacobian X,Y,Z with Z = 0 = infinity).  Buckets are kept in
+// extended Jacobian "XYZZ" coordinates (x = X/ZZ, y = Y/ZZZ, ZZ^3 = ZZZ^2), whose mixed addition
+// costs 8M + 2S; formulas are the EFD ones (madd-2008-s, add-2008-s, dbl-2008-s-1, mdbl-2008-s-1)
+// for y^2 = x^3 + b with a = 0, with the P = +-Q and infinity cases handled explicitly because
+// gnark's DummySetup (setup.go:532-546) makes every base the same point.
+#pragma once
+#include "field.cuh"
+
+namespace b200 {
+
+// Fp2 = Fp[u]/(u^2 + 1)   (gnark-crypto E2{A0, A1}; memory order A0 then A1)
+struct Fp2 {
+    Fp a0, a1;
+    B2_HD static Fp2 zero() { return {Fp::zero(), Fp::zero()}; }
+    B2_HD static Fp2 one() { return {Fp::one(), Fp::zero()}; }
+    B2_HD bool is_zero() const { return a0.is_zero() && a1.is_zero(); }
+    B2_HD bool operator==(const Fp2& o) const { return a0 == o.a0 && a1 == o.a1; }
+    B2_HD bool operator!=(const Fp2& o) const { return !(*this == o); }
+    B2_HD Fp2 operator+(const Fp2& o) const { return {a0 + o.a0, a1 + o.a1}; }
+    B2_HD Fp2 operator-(const Fp2& o) const { return {a0 - o.a0, a1 - o.a1}; }
+    B2_HD Fp2 neg() const { return {a0.neg(), a1.neg()}; }
+    B2_HD Fp2 dbl() const { return {a0.dbl(), a1.dbl()}; }
+    B2_HD Fp2 operator*(const Fp2& o) const {  // Karatsuba, 3 Fp mul
+        const Fp t0 = a0 * o.a0, t1 = a1 * o.a1;
+        const Fp t2 = (a0 + a1) * (o.a0 + o.a1);
+        return {t0 - t1, t2 - t0 - t1};
+    }
+    B2_HD Fp2 sqr() const {  // complex squaring, 2 Fp mul
+        const Fp t = a0 * a1;
+        return {(a0 + a1) * (a0 - a1), t.dbl()};
+    }
+    B2_HD Fp2 inv() const {
+        const Fp d = (a0.sqr() + a1.sqr()).inv();
+        return {a0 * d, a1.neg() * d};
+    }
+};
+
+template <class F>
+struct Affine {
+    F x, y;
+    B2_HD bool is_inf() const { return x.is_zero() && y.is_zero(); }
+    B2_HD static Affine inf() { return {F::zero(), F::zero()}; }
+    B2_HD Affine neg() const { return {x, y.neg()}; }
+};
+
+template <class F>
+struct Jac {
+    F X, Y, Z;
+    B2_HD static Jac inf() { return {F::one(), F::one(), F::zero()}; }
+    B2_HD bool is_inf() const { return Z.is_zero(); }
+};
+
+template <class F>
+struct XYZZ {
+    F X, Y, ZZ, ZZZ;
+    B2_HD static XYZZ inf() { return {F::zero(), F::zero(), F::zero(), F::zero()}; }
+    B2_HD bool is_inf() const { return ZZ.is_zero(); }
+    B2_HD static XYZZ from_affine(const Affine<F>& p) {
+        if (p.is_inf()) return inf();
+        return {p.x, p.y, F::one(), F::one()};
+    }
+    B2_HD XYZZ neg() const { return {X, Y.neg(), ZZ, ZZZ}; }
+
+    // doubling of an affine point (mdbl-2008-s-1, a = 0)
+    B2_HD static XYZZ dbl_affine(const Affine<F>& p) {
+        if (p.is_inf() || p.y.is_zero()) return inf();
+        const F U = p.y.dbl(), V = U.sqr(), W = U * V, S = p.x * V;
+        const F x2 = p.x.sqr(), M = x2.dbl() + x2;
+        XYZZ r;
+        r.X = M.sqr() - S.dbl();
+        r.Y = M * (S - r.X) - W * p.y;
+        r.ZZ = V;
+        r.ZZZ = W;
+        return r;
+    }
+    // dbl-2008-s-1, a = 0
+    B2_HD XYZZ dbl() const {
+        if (is_inf()) return *this;
+        const F U = Y.dbl(), V = U.sqr(), W = U * V, S = X * V;
+        const F x2 = X.sqr(), M = x2.dbl() + x2;
+        XYZZ r;
+        r.X = M.sqr() - S.dbl();
+        r.Y = M * (S - r.X) - W * Y;
+        r.ZZ = V * ZZ;
+        r.ZZZ = W * ZZZ;
+        return r;
+    }
+    // this += q (affine), madd-2008-s
+    B2_HD void add_mixed(const Affine<F>& q) {
+        if (q.is_inf()) return;
+        if (is_inf()) { X = q.x; Y = q.y; ZZ = F::one(); ZZZ = F::one(); return; }
+        const F U2 = q.x * ZZ, S2 = q.y * ZZZ;
+        const F P = U2 - X, R = S2 - Y;
+        if (P.is_zero()) {
+            if (R.is_zero()) *this = dbl_affine(q);
+            else *this = inf();
+            return;
+        }
+        const F PP = P.sqr(), PPP = P * PP, Q = X * PP;
+        const F X3 = R.sqr() - PPP - Q.dbl();
+        Y = R * (Q - X3) - Y * PPP;
+        X = X3;
+        ZZ = ZZ * PP;
+        ZZZ = ZZZ * PPP;
+    }
+    // this += q, add-2008-s
+    B2_HD void add(const XYZZ& q) {
+        if (q.is_inf()) return;
+        if (is_inf()) { *this = q; return; }
+        const F U1 = X * q.ZZ, U2 = q.X * ZZ, S1 = Y * q.ZZZ, S2 = q.Y * ZZZ;
+        const F P = U2 - U1, R = S2 - S1;
+        if (P.is_zero()) {
+            if (R.is_zero()) *this = dbl();
+            else *this = inf();
+            return;
+        }
+        const F PP = P.sqr(), PPP = P * PP, Q = U1 * PP;
+        const F X3 = R.sqr() - PPP - Q.dbl();
+        Y = R * (Q - X3) - S1 * PPP;
+        X = X3;
+        ZZ = ZZ * q.ZZ * PP;
+        ZZZ = ZZZ * q.ZZZ * PPP;
+    }
+    // (X/ZZ, Y/ZZZ) == (X*ZZ / ZZ^2, Y*ZZZ / ZZ^3): a Jacobian representative with Z = ZZ
+    B2_HD Jac<F> to_jac() const {
+        if (is_inf()) return Jac<F>::inf();
+        return {X * ZZ, Y * ZZZ, ZZ};
+    }
+    B2_HD Affine<F> to_affine() const {
+        if (is_inf()) return Affine<F>::inf();
+        const F zi = ZZZ.inv();        // 1/ZZZ
+        const F zzi = (zi * ZZ).sqr(); // (ZZ/ZZZ)^2 = 1/ZZ  (ZZ^3 = ZZZ^2)
+        return {X * zzi, Y * zi};
+    }
+};
+
+// Jacobian helpers used on the host for the O(1) fix-ups (prove.go:206-207,219-221,248-271,294-299)
+template <class F>
+B2_HD XYZZ<F> xyzz_from_jac(const Jac<F>& j) {
+    if (j.is_inf()) return XYZZ<F>::inf();
+    const F zz = j.Z.sqr();
+    return {j.X, j.Y, zz, zz * j.Z};
+}
+template <class F>
+B2_HD Affine<F> jac_to_affine(const Jac<F>& j) {
+    if (j.is_inf()) return Affine<F>::inf();
+    const F zi = j.Z.inv(), zi2 = zi.sqr();
+    return {j.X * zi2, j.Y * zi2 * zi};
+}
+
+typedef Affine<Fp> G1Affine;
+typedef Affine<Fp2> G2Affine;
+typedef Jac<Fp> G1Jac;
+typedef Jac<Fp2> G2Jac;
+typedef XYZZ<Fp> G1XYZZ;
+typedef XYZZ<Fp2> G2XYZZ;
+
+}  // namespace b200

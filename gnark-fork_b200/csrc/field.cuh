@@ -1,0 +1,404 @@
+// Montgomery prime-field arithmetic on 8 x 32-bit limbs for sm_100a (BN254 Fp and Fr).
+//
+// Replaces, for the device path, gnark-crypto's fp.Element / fr.Element arithmetic that
+// /root/reference/backend/groth16/bn254/prove.go reaches through MultiExp and fft.Domain
+// (prove.go:201-290,369-393).  Storage is bit-compatible with the Go side: an element is
+// 4 little-endian u64 limbs in Montgomery form (R = 2^256), viewed here as 8 u32 limbs.
+//
+// Device multiplication: operand-scanning Montgomery (CIOS) with the running sum split into
+// an "even" and an "odd" accumulator so that every row is one uninterrupted
+// mad.lo.cc / madc.hi.cc carry chain (ptxas fuses each lo/hi pair into one IMAD.WIDE.U32.X).
+// Invariant: T = E + O*2^32 < 2p < 2^255 between rows (p has two spare top bits), so E needs
+// 9 limbs inside a row and O never overflows 8.  After the reduction row the low limb of E is
+// zero, T/2^32 = (E>>32) + O, and the two accumulators swap parity: O becomes the new even
+// accumulator (plus the stray limb e1), E>>64 the new odd one.
+//
+// Host builds of the same templates (used by the host-side fix-ups of prove.go:192-301 and by
+// CPU unit tests) take the portable u64 path.
+#pragma once
+#include <cstdint>
+#include <cstring>
+
+#if defined(__CUDACC__)
+#define B2_HD __host__ __device__ __forceinline__
+#define B2_D __device__ __forceinline__
+#else
+#define B2_HD inline
+#define B2_D inline
+#endif
+
+namespace b200 {
+
+// ---------------------------------------------------------------------------------------
+// Field parameter packs.  Constants are derived from the moduli pinned in the reference at
+// backend/groth16/bn254/solidity.go:41-42 (P, R);  INV = -p^-1 mod 2^32, ONE = 2^256 mod p,
+// R2 = 2^512 mod p.
+// ---------------------------------------------------------------------------------------
+struct FpParams {
+    static constexpr int N = 8;
+    B2_HD static constexpr uint32_t p(int i) {
+        constexpr uint32_t v[8] = {0xd87cfd47u, 0x3c208c16u, 0x6871ca8du, 0x97816a91u,
+                                   0x8181585du, 0xb85045b6u, 0xe131a029u, 0x30644e72u};
+        return v[i];
+    }
+    B2_HD static constexpr uint32_t one(int i) {
+        constexpr uint32_t v[8] = {0xc58f0d9du, 0xd35d438du, 0xf5c70b3du, 0x0a78eb28u,
+                                   0x7879462cu, 0x666ea36fu, 0x9a07df2fu, 0x0e0a77c1u};
+        return v[i];
+    }
+    B2_HD static constexpr uint32_t r2(int i) {
+        constexpr uint32_t v[8] = {0x538afa89u, 0xf32cfc5bu, 0xd44501fbu, 0xb5e71911u,
+                                   0x0a417ff6u, 0x47ab1effu, 0xcab8351fu, 0x06d89f71u};
+        return v[i];
+    }
+    static constexpr uint32_t INV = 0xe4866389u;
+};
+
+struct FrParams {
+    static constexpr int N = 8;
+    B2_HD static constexpr uint32_t p(int i) {
+        constexpr uint32_t v[8] = {0xf0000001u, 0x43e1f593u, 0x79b97091u, 0x2833e848u,
+                                   0x8181585du, 0xb85045b6u, 0xe131a029u, 0x30644e72u};
+        return v[i];
+    }
+    B2_HD static constexpr uint32_t one(int i) {
+        constexpr uint32_t v[8] = {0x4ffffffbu, 0xac96341cu, 0x9f60cd29u, 0x36fc7695u,
+                                   0x7879462eu, 0x666ea36fu, 0x9a07df2fu, 0x0e0a77c1u};
+        return v[i];
+    }
+    B2_HD static constexpr uint32_t r2(int i) {
+        constexpr uint32_t v[8] = {0xae216da7u, 0x1bb8e645u, 0xe35c59e3u, 0x53fe3ab1u,
+                                   0x53bb8085u, 0x8c49833du, 0x7f4e44a5u, 0x0216d0b1u};
+        return v[i];
+    }
+    static constexpr uint32_t INV = 0xefffffffu;
+};
+
+// ---------------------------------------------------------------------------------------
+// Device carry-chain helpers (8 limbs).  Every helper is one self-contained asm block: the
+// carry flag never has to survive between two asm statements.
+// ---------------------------------------------------------------------------------------
+#if defined(__CUDACC__)
+
+// acc[0..7] += {x0,x1,x2,x3} * y laid out as 64-bit products at limb pairs (0,1),(2,3),(4,5),(6,7).
+// No carry leaves the top (caller guarantees the bound).
+B2_D void mad_chain8(uint32_t* acc, uint32_t x0, uint32_t x1, uint32_t x2, uint32_t x3, uint32_t y) {
+    asm("mad.lo.cc.u32 %0, %8, %12, %0;\n\t"
+        "madc.hi.cc.u32 %1, %8, %12, %1;\n\t"
+        "madc.lo.cc.u32 %2, %9, %12, %2;\n\t"
+        "madc.hi.cc.u32 %3, %9, %12, %3;\n\t"
+        "madc.lo.cc.u32 %4, %10, %12, %4;\n\t"
+        "madc.hi.cc.u32 %5, %10, %12, %5;\n\t"
+        "madc.lo.cc.u32 %6, %11, %12, %6;\n\t"
+        "madc.hi.u32 %7, %11, %12, %7;\n\t"
+        : "+r"(acc[0]), "+r"(acc[1]), "+r"(acc[2]), "+r"(acc[3]), "+r"(acc[4]), "+r"(acc[5]),
+          "+r"(acc[6]), "+r"(acc[7])
+        : "r"(x0), "r"(x1), "r"(x2), "r"(x3), "r"(y));
+}
+
+// Same, and the carry out of limb 7 is written to (NEW=true) or added into (NEW=false) acc[8].
+template <bool NEW>
+B2_D void mad_chain8_top(uint32_t* acc, uint32_t x0, uint32_t x1, uint32_t x2, uint32_t x3, uint32_t y) {
+    if (NEW) {
+        asm("mad.lo.cc.u32 %0, %9, %13, %0;\n\t"
+            "madc.hi.cc.u32 %1, %9, %13, %1;\n\t"
+            "madc.lo.cc.u32 %2, %10, %13, %2;\n\t"
+            "madc.hi.cc.u32 %3, %10, %13, %3;\n\t"
+            "madc.lo.cc.u32 %4, %11, %13, %4;\n\t"
+            "madc.hi.cc.u32 %5, %11, %13, %5;\n\t"
+            "madc.lo.cc.u32 %6, %12, %13, %6;\n\t"
+            "madc.hi.cc.u32 %7, %12, %13, %7;\n\t"
+            "addc.u32 %8, 0, 0;\n\t"
+            : "+r"(acc[0]), "+r"(acc[1]), "+r"(acc[2]), "+r"(acc[3]), "+r"(acc[4]), "+r"(acc[5]),
+              "+r"(acc[6]), "+r"(acc[7]), "=r"(acc[8])
+            : "r"(x0), "r"(x1), "r"(x2), "r"(x3), "r"(y));
+    } else {
+        asm("mad.lo.cc.u32 %0, %9, %13, %0;\n\t"
+            "madc.hi.cc.u32 %1, %9, %13, %1;\n\t"
+            "madc.lo.cc.u32 %2, %10, %13, %2;\n\t"
+            "madc.hi.cc.u32 %3, %10, %13, %3;\n\t"
+            "madc.lo.cc.u32 %4, %11, %13, %4;\n\t"
+            "madc.hi.cc.u32 %5, %11, %13, %5;\n\t"
+            "madc.lo.cc.u32 %6, %12, %13, %6;\n\t"
+            "madc.hi.cc.u32 %7, %12, %13, %7;\n\t"
+            "addc.u32 %8, %8, 0;\n\t"
+            : "+r"(acc[0]), "+r"(acc[1]), "+r"(acc[2]), "+r"(acc[3]), "+r"(acc[4]), "+r"(acc[5]),
+              "+r"(acc[6]), "+r"(acc[7]), "+r"(acc[8])
+            : "r"(x0), "r"(x1), "r"(x2), "r"(x3), "r"(y));
+    }
+}
+
+// Parity swap + next odd row in one chain:
+//   ne0      = o0 + e[1]                       (stray limb folded into the new even accumulator)
+//   no[0..7] = (e[2..8], 0) + {x1,x3,x5,x7}*y  (+ the carry of the fold, same weight 2^32)
+B2_D void fold_mad_shift8(uint32_t& ne0, uint32_t* no, const uint32_t* e, uint32_t o0,
+                          uint32_t x1, uint32_t x3, uint32_t x5, uint32_t x7, uint32_t y) {
+    asm("add.cc.u32 %0, %9, %10;\n\t"
+        "madc.lo.cc.u32 %1, %18, %22, %11;\n\t"
+        "madc.hi.cc.u32 %2, %18, %22, %12;\n\t"
+        "madc.lo.cc.u32 %3, %19, %22, %13;\n\t"
+        "madc.hi.cc.u32 %4, %19, %22, %14;\n\t"
+        "madc.lo.cc.u32 %5, %20, %22, %15;\n\t"
+        "madc.hi.cc.u32 %6, %20, %22, %16;\n\t"
+        "madc.lo.cc.u32 %7, %21, %22, %17;\n\t"
+        "madc.hi.u32 %8, %21, %22, 0;\n\t"
+        : "=&r"(ne0), "=&r"(no[0]), "=&r"(no[1]), "=&r"(no[2]), "=&r"(no[3]), "=&r"(no[4]),
+          "=&r"(no[5]), "=&r"(no[6]), "=&r"(no[7])
+        : "r"(o0), "r"(e[1]), "r"(e[2]), "r"(e[3]), "r"(e[4]), "r"(e[5]), "r"(e[6]), "r"(e[7]),
+          "r"(e[8]), "r"(x1), "r"(x3), "r"(x5), "r"(x7), "r"(y));
+}
+
+template <class PRM>
+B2_D void mont_mul_dev(uint32_t* r, const uint32_t* a, const uint32_t* b) {
+    uint32_t e[9], o[8];
+    // row 0: plain products
+    {
+        const uint32_t y = b[0];
+#pragma unroll
+        for (int j = 0; j < 8; j += 2) {
+            asm("mul.lo.u32 %0, %2, %3;\n\tmul.hi.u32 %1, %2, %3;" : "=r"(e[j]), "=r"(e[j + 1]) : "r"(a[j]), "r"(y));
+            asm("mul.lo.u32 %0, %2, %3;\n\tmul.hi.u32 %1, %2, %3;" : "=r"(o[j]), "=r"(o[j + 1]) : "r"(a[j + 1]), "r"(y));
+        }
+        const uint32_t m = e[0] * PRM::INV;
+        mad_chain8(o, PRM::p(1), PRM::p(3), PRM::p(5), PRM::p(7), m);
+        mad_chain8_top<true>(e, PRM::p(0), PRM::p(2), PRM::p(4), PRM::p(6), m);
+    }
+#pragma unroll
+    for (int i = 1; i < 8; ++i) {
+        const uint32_t y = b[i];
+        uint32_t ne[9], no[8];
+        fold_mad_shift8(ne[0], no, e, o[0], a[1], a[3], a[5], a[7], y);
+#pragma unroll
+        for (int k = 1; k < 8; ++k) ne[k] = o[k];
+        mad_chain8_top<true>(ne, a[0], a[2], a[4], a[6], y);
+        const uint32_t m = ne[0] * PRM::INV;
+        mad_chain8(no, PRM::p(1), PRM::p(3), PRM::p(5), PRM::p(7), m);
+        mad_chain8_top<false>(ne, PRM::p(0), PRM::p(2), PRM::p(4), PRM::p(6), m);
+#pragma unroll
+        for (int k = 0; k < 9; ++k) e[k] = ne[k];
+#pragma unroll
+        for (int k = 0; k < 8; ++k) o[k] = no[k];
+    }
+    // T = (E >> 32) + O  (< 2p), then one conditional subtraction
+    uint32_t t[8];
+    asm("add.cc.u32 %0, %8, %16;\n\t"
+        "addc.cc.u32 %1, %9, %17;\n\t"
+        "addc.cc.u32 %2, %10, %18;\n\t"
+        "addc.cc.u32 %3, %11, %19;\n\t"
+        "addc.cc.u32 %4, %12, %20;\n\t"
+        "addc.cc.u32 %5, %13, %21;\n\t"
+        "addc.cc.u32 %6, %14, %22;\n\t"
+        "addc.u32 %7, %15, %23;\n\t"
+        : "=&r"(t[0]), "=&r"(t[1]), "=&r"(t[2]), "=&r"(t[3]), "=&r"(t[4]), "=&r"(t[5]), "=&r"(t[6]), "=&r"(t[7])
+        : "r"(o[0]), "r"(o[1]), "r"(o[2]), "r"(o[3]), "r"(o[4]), "r"(o[5]), "r"(o[6]), "r"(o[7]),
+          "r"(e[1]), "r"(e[2]), "r"(e[3]), "r"(e[4]), "r"(e[5]), "r"(e[6]), "r"(e[7]), "r"(e[8]));
+    uint32_t s[8], borrow;
+    asm("sub.cc.u32 %0, %9, %17;\n\t"
+        "subc.cc.u32 %1, %10, %18;\n\t"
+        "subc.cc.u32 %2, %11, %19;\n\t"
+        "subc.cc.u32 %3, %12, %20;\n\t"
+        "subc.cc.u32 %4, %13, %21;\n\t"
+        "subc.cc.u32 %5, %14, %22;\n\t"
+        "subc.cc.u32 %6, %15, %23;\n\t"
+        "subc.cc.u32 %7, %16, %24;\n\t"
+        "subc.u32 %8, 0, 0;\n\t"
+        : "=&r"(s[0]), "=&r"(s[1]), "=&r"(s[2]), "=&r"(s[3]), "=&r"(s[4]), "=&r"(s[5]), "=&r"(s[6]), "=&r"(s[7]), "=&r"(borrow)
+        : "r"(t[0]), "r"(t[1]), "r"(t[2]), "r"(t[3]), "r"(t[4]), "r"(t[5]), "r"(t[6]), "r"(t[7]),
+          "r"(PRM::p(0)), "r"(PRM::p(1)), "r"(PRM::p(2)), "r"(PRM::p(3)), "r"(PRM::p(4)), "r"(PRM::p(5)), "r"(PRM::p(6)), "r"(PRM::p(7)));
+#pragma unroll
+    for (int k = 0; k < 8; ++k) r[k] = borrow ? t[k] : s[k];
+}
+
+template <class PRM>
+B2_D void mod_add_dev(uint32_t* r, const uint32_t* a, const uint32_t* b) {
+    uint32_t t[8];
+    asm("add.cc.u32 %0, %8, %16;\n\t"
+        "addc.cc.u32 %1, %9, %17;\n\t"
+        "addc.cc.u32 %2, %10, %18;\n\t"
+        "addc.cc.u32 %3, %11, %19;\n\t"
+        "addc.cc.u32 %4, %12, %20;\n\t"
+        "addc.cc.u32 %5, %13, %21;\n\t"
+        "addc.cc.u32 %6, %14, %22;\n\t"
+        "addc.u32 %7, %15, %23;\n\t"
+        : "=&r"(t[0]), "=&r"(t[1]), "=&r"(t[2]), "=&r"(t[3]), "=&r"(t[4]), "=&r"(t[5]), "=&r"(t[6]), "=&r"(t[7])
+        : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(a[4]), "r"(a[5]), "r"(a[6]), "r"(a[7]),
+          "r"(b[0]), "r"(b[1]), "r"(b[2]), "r"(b[3]), "r"(b[4]), "r"(b[5]), "r"(b[6]), "r"(b[7]));
+    // a + b < 2p < 2^255: no carry out of limb 7
+    uint32_t s[8], borrow;
+    asm("sub.cc.u32 %0, %9, %17;\n\t"
+        "subc.cc.u32 %1, %10, %18;\n\t"
+        "subc.cc.u32 %2, %11, %19;\n\t"
+        "subc.cc.u32 %3, %12, %20;\n\t"
+        "subc.cc.u32 %4, %13, %21;\n\t"
+        "subc.cc.u32 %5, %14, %22;\n\t"
+        "subc.cc.u32 %6, %15, %23;\n\t"
+        "subc.cc.u32 %7, %16, %24;\n\t"
+        "subc.u32 %8, 0, 0;\n\t"
+        : "=&r"(s[0]), "=&r"(s[1]), "=&r"(s[2]), "=&r"(s[3]), "=&r"(s[4]), "=&r"(s[5]), "=&r"(s[6]), "=&r"(s[7]), "=&r"(borrow)
+        : "r"(t[0]), "r"(t[1]), "r"(t[2]), "r"(t[3]), "r"(t[4]), "r"(t[5]), "r"(t[6]), "r"(t[7]),
+          "r"(PRM::p(0)), "r"(PRM::p(1)), "r"(PRM::p(2)), "r"(PRM::p(3)), "r"(PRM::p(4)), "r"(PRM::p(5)), "r"(PRM::p(6)), "r"(PRM::p(7)));
+#pragma unroll
+    for (int k = 0; k < 8; ++k) r[k] = borrow ? t[k] : s[k];
+}
+
+template <class PRM>
+B2_D void mod_sub_dev(uint32_t* r, const uint32_t* a, const uint32_t* b) {
+    uint32_t t[8], borrow;
+    asm("sub.cc.u32 %0, %9, %17;\n\t"
+        "subc.cc.u32 %1, %10, %18;\n\t"
+        "subc.cc.u32 %2, %11, %19;\n\t"
+        "subc.cc.u32 %3, %12, %20;\n\t"
+        "subc.cc.u32 %4, %13, %21;\n\t"
+        "subc.cc.u32 %5, %14, %22;\n\t"
+        "subc.cc.u32 %6, %15, %23;\n\t"
+        "subc.cc.u32 %7, %16, %24;\n\t"
+        "subc.u32 %8, 0, 0;\n\t"
+        : "=&r"(t[0]), "=&r"(t[1]), "=&r"(t[2]), "=&r"(t[3]), "=&r"(t[4]), "=&r"(t[5]), "=&r"(t[6]), "=&r"(t[7]), "=&r"(borrow)
+        : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(a[4]), "r"(a[5]), "r"(a[6]), "r"(a[7]),
+          "r"(b[0]), "r"(b[1]), "r"(b[2]), "r"(b[3]), "r"(b[4]), "r"(b[5]), "r"(b[6]), "r"(b[7]));
+    // borrow is 0 or 0xffffffff: add (p & borrow)
+    asm("add.cc.u32 %0, %0, %8;\n\t"
+        "addc.cc.u32 %1, %1, %9;\n\t"
+        "addc.cc.u32 %2, %2, %10;\n\t"
+        "addc.cc.u32 %3, %3, %11;\n\t"
+        "addc.cc.u32 %4, %4, %12;\n\t"
+        "addc.cc.u32 %5, %5, %13;\n\t"
+        "addc.cc.u32 %6, %6, %14;\n\t"
+        "addc.u32 %7, %7, %15;\n\t"
+        : "+r"(t[0]), "+r"(t[1]), "+r"(t[2]), "+r"(t[3]), "+r"(t[4]), "+r"(t[5]), "+r"(t[6]), "+r"(t[7])
+        : "r"(PRM::p(0) & borrow), "r"(PRM::p(1) & borrow), "r"(PRM::p(2) & borrow), "r"(PRM::p(3) & borrow),
+          "r"(PRM::p(4) & borrow), "r"(PRM::p(5) & borrow), "r"(PRM::p(6) & borrow), "r"(PRM::p(7) & borrow));
+#pragma unroll
+    for (int k = 0; k < 8; ++k) r[k] = t[k];
+}
+#endif  // __CUDACC__
+
+// ---------------------------------------------------------------------------------------
+// Portable path (host): same results, u64 arithmetic.
+// ---------------------------------------------------------------------------------------
+template <class PRM>
+inline void mont_mul_host(uint32_t* r, const uint32_t* a, const uint32_t* b) {
+    constexpr int N = PRM::N;
+    uint32_t t[N + 2];
+    for (int i = 0; i < N + 2; ++i) t[i] = 0;
+    for (int i = 0; i < N; ++i) {
+        uint64_t c = 0;
+        for (int j = 0; j < N; ++j) {
+            c += (uint64_t)a[j] * b[i] + t[j];
+            t[j] = (uint32_t)c; c >>= 32;
+        }
+        c += t[N]; t[N] = (uint32_t)c; t[N + 1] = (uint32_t)(c >> 32);
+        const uint32_t m = t[0] * PRM::INV;
+        c = ((uint64_t)m * PRM::p(0) + t[0]) >> 32;
+        for (int j = 1; j < N; ++j) {
+            c += (uint64_t)m * PRM::p(j) + t[j];
+            t[j - 1] = (uint32_t)c; c >>= 32;
+        }
+        c += t[N]; t[N - 1] = (uint32_t)c; t[N] = t[N + 1] + (uint32_t)(c >> 32);
+    }
+    uint32_t s[N]; uint64_t br = 0;
+    for (int j = 0; j < N; ++j) {
+        uint64_t d = (uint64_t)t[j] - PRM::p(j) - br;
+        s[j] = (uint32_t)d; br = (d >> 32) & 1;
+    }
+    const bool ge = t[N] || !br;
+    for (int j = 0; j < N; ++j) r[j] = ge ? s[j] : t[j];
+}
+
+template <class PRM>
+inline void mod_add_host(uint32_t* r, const uint32_t* a, const uint32_t* b) {
+    constexpr int N = PRM::N;
+    uint32_t t[N], s[N]; uint64_t c = 0, br = 0;
+    for (int j = 0; j < N; ++j) { c += (uint64_t)a[j] + b[j]; t[j] = (uint32_t)c; c >>= 32; }
+    for (int j = 0; j < N; ++j) { uint64_t d = (uint64_t)t[j] - PRM::p(j) - br; s[j] = (uint32_t)d; br = (d >> 32) & 1; }
+    const bool ge = c || !br;
+    for (int j = 0; j < N; ++j) r[j] = ge ? s[j] : t[j];
+}
+
+template <class PRM>
+inline void mod_sub_host(uint32_t* r, const uint32_t* a, const uint32_t* b) {
+    constexpr int N = PRM::N;
+    uint32_t t[N]; uint64_t br = 0;
+    for (int j = 0; j < N; ++j) { uint64_t d = (uint64_t)a[j] - b[j] - br; t[j] = (uint32_t)d; br = (d >> 32) & 1; }
+    if (br) { uint64_t c = 0; for (int j = 0; j < N; ++j) { c += (uint64_t)t[j] + PRM::p(j); t[j] = (uint32_t)c; c >>= 32; } }
+    for (int j = 0; j < N; ++j) r[j] = t[j];
+}
+
+// ---------------------------------------------------------------------------------------
+// Field element
+// ---------------------------------------------------------------------------------------
+template <class PRM>
+struct alignas(16) Fe {
+    static constexpr int N = PRM::N;
+    typedef PRM Params;
+    uint32_t l[N];
+
+    B2_HD static Fe zero() { Fe r; for (int i = 0; i < N; ++i) r.l[i] = 0; return r; }
+    B2_HD static Fe one() { Fe r; for (int i = 0; i < N; ++i) r.l[i] = PRM::one(i); return r; }
+    B2_HD static Fe r2() { Fe r; for (int i = 0; i < N; ++i) r.l[i] = PRM::r2(i); return r; }
+    B2_HD static Fe modulus() { Fe r; for (int i = 0; i < N; ++i) r.l[i] = PRM::p(i); return r; }
+    B2_HD bool is_zero() const { uint32_t x = 0; for (int i = 0; i < N; ++i) x |= l[i]; return x == 0; }
+    B2_HD bool operator==(const Fe& o) const { uint32_t x = 0; for (int i = 0; i < N; ++i) x |= l[i] ^ o.l[i]; return x == 0; }
+    B2_HD bool operator!=(const Fe& o) const { return !(*this == o); }
+
+    B2_HD Fe operator*(const Fe& o) const {
+        Fe r;
+#if defined(__CUDA_ARCH__)
+        mont_mul_dev<PRM>(r.l, l, o.l);
+#else
+        mont_mul_host<PRM>(r.l, l, o.l);
+#endif
+        return r;
+    }
+    B2_HD Fe sqr() const { return *this * *this; }
+    B2_HD Fe operator+(const Fe& o) const {
+        Fe r;
+#if defined(__CUDA_ARCH__)
+        mod_add_dev<PRM>(r.l, l, o.l);
+#else
+        mod_add_host<PRM>(r.l, l, o.l);
+#endif
+        return r;
+    }
+    B2_HD Fe operator-(const Fe& o) const {
+        Fe r;
+#if defined(__CUDA_ARCH__)
+        mod_sub_dev<PRM>(r.l, l, o.l);
+#else
+        mod_sub_host<PRM>(r.l, l, o.l);
+#endif
+        return r;
+    }
+    B2_HD Fe dbl() const { return *this + *this; }
+    B2_HD Fe neg() const { return zero() - *this; }
+    // Montgomery form <-> canonical integer
+    B2_HD Fe to_mont() const { return *this * r2(); }
+    B2_HD Fe from_mont() const { Fe o = zero(); o.l[0] = 1; return *this * o; }
+    B2_HD static Fe from_u32(uint32_t x) { Fe r = zero(); r.l[0] = x; return r.to_mont(); }
+
+    // x^e for a little-endian u32 exponent (square-and-multiply, MSB first)
+    B2_HD Fe pow(const uint32_t* e, int nlimbs) const {
+        Fe acc = one();
+        for (int i = nlimbs * 32 - 1; i >= 0; --i) {
+            acc = acc.sqr();
+            if ((e[i >> 5] >> (i & 31)) & 1) acc = acc * *this;
+        }
+        return acc;
+    }
+    B2_HD Fe pow_u64(uint64_t e) const {
+        uint32_t w[2] = {(uint32_t)e, (uint32_t)(e >> 32)};
+        return pow(w, 2);
+    }
+    // Fermat inverse x^(p-2); 0 -> 0 (same convention as gnark-crypto's Inverse)
+    B2_HD Fe inv() const {
+        uint32_t e[N];
+        for (int i = 0; i < N; ++i) e[i] = PRM::p(i);
+        e[0] -= 2;  // p is odd and p(0) >= 2 for every modulus here
+        return pow(e, N);
+    }
+};
+
+typedef Fe<FpParams> Fp;
+typedef Fe<FrParams> Fr;
+
+}  // namespace b200

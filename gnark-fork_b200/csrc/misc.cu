@@ -1,0 +1,178 @@
+// Element-wise field kernels, the IMAD roofline microbenchmark and the fixed-base batch scalar
+// multiplication (curve.BatchScalarMultiplicationG1/G2, /root/reference/backend/groth16/bn254/
+// setup.go:251,308; prove.go:192) used to build synthetic proving keys on the device.
+#include "misc_host.cuh"
+
+namespace b200 {
+
+template <class F>
+__global__ void vec_mul_kernel(const F* __restrict__ a, const F* __restrict__ b, F* __restrict__ out, size_t n) {
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    st_vec(out + i, ld_vec(a + i) * ld_vec(b + i));
+}
+
+int vec_mul_fr(b200_ctx* ctx, const Fr* a, const Fr* b, Fr* out, size_t n) {
+    if (!n) return B200_OK;
+    vec_mul_kernel<Fr><<<(unsigned)((n + 255) / 256), 256, 0, ctx->stream>>>(a, b, out, n);
+    B2_CUDA(ctx, cudaGetLastError());
+    return B200_OK;
+}
+int vec_mul_fp(b200_ctx* ctx, const Fp* a, const Fp* b, Fp* out, size_t n) {
+    if (!n) return B200_OK;
+    vec_mul_kernel<Fp><<<(unsigned)((n + 255) / 256), 256, 0, ctx->stream>>>(a, b, out, n);
+    B2_CUDA(ctx, cudaGetLastError());
+    return B200_OK;
+}
+
+// ---------------------------------------------------------------------------------------
+// IMAD-pipe peak.  (a) the instruction pattern the field multiplication is made of: four
+// independent 8-limb mad.lo.cc/madc.hi.cc chains per thread (SASS: IMAD.WIDE.U32.X);
+// (b) independent plain 32-bit mad.lo chains (SASS: IMAD).
+// ---------------------------------------------------------------------------------------
+constexpr int PEAK_ITERS = 4096;
+
+__global__ void __launch_bounds__(256) peak_wide_kernel(const uint32_t* __restrict__ in, uint32_t* __restrict__ out, long long* cycles) {
+    uint32_t acc[4][8];
+    const uint32_t x0 = in[threadIdx.x & 31], x1 = in[32 + (threadIdx.x & 31)], x2 = x0 ^ 0x9e3779b9u, x3 = x1 + 0x7f4a7c15u;
+    uint32_t y = in[64 + (threadIdx.x & 31)];
+#pragma unroll
+    for (int k = 0; k < 4; ++k)
+#pragma unroll
+        for (int j = 0; j < 8; ++j) acc[k][j] = x0 + k * 8 + j;
+    const long long t0 = clock64();
+#pragma unroll 1
+    for (int it = 0; it < PEAK_ITERS; ++it) {
+#pragma unroll
+        for (int k = 0; k < 4; ++k) mad_chain8(acc[k], x0, x1, x2, x3, y);
+    }
+    const long long t1 = clock64();
+    uint32_t s = 0;
+#pragma unroll
+    for (int k = 0; k < 4; ++k)
+#pragma unroll
+        for (int j = 0; j < 8; ++j) s ^= acc[k][j];
+    if (s == 0x12345678u) out[0] = s;  // keep the chains live
+    if (blockIdx.x == 0 && threadIdx.x == 0) *cycles = t1 - t0;
+}
+
+__global__ void __launch_bounds__(256) peak_imad_kernel(const uint32_t* __restrict__ in, uint32_t* __restrict__ out) {
+    uint32_t a[16];
+    const uint32_t b = in[threadIdx.x & 31] | 1u, c = in[32 + (threadIdx.x & 31)];
+#pragma unroll
+    for (int j = 0; j < 16; ++j) a[j] = c + j;
+#pragma unroll 1
+    for (int it = 0; it < PEAK_ITERS; ++it) {
+#pragma unroll
+        for (int j = 0; j < 16; ++j) asm volatile("mad.lo.u32 %0, %0, %1, %2;" : "+r"(a[j]) : "r"(b), "r"(c));
+    }
+    uint32_t s = 0;
+#pragma unroll
+    for (int j = 0; j < 16; ++j) s ^= a[j];
+    if (s == 0x12345678u) out[0] = s;
+}
+
+int imad_peak(b200_ctx* ctx, double* mac32_per_s, double* imad32_per_s, double* sm_mhz) {
+    DevBuf in, out, cyc;
+    B2_CUDA(ctx, in.alloc(128 * 4));
+    B2_CUDA(ctx, out.alloc(16));
+    B2_CUDA(ctx, cyc.alloc(8));
+    uint32_t h[128];
+    for (int i = 0; i < 128; ++i) h[i] = 0x9e3779b9u * (i + 1) + 12345u;
+    B2_CUDA(ctx, cudaMemcpyAsync(in.p, h, sizeof h, cudaMemcpyHostToDevice, ctx->stream));
+    const int blocks = ctx->sm_count * 4, threads = 256;
+    float best_w = 1e30f, best_i = 1e30f;
+    long long cycles = 0;
+    for (int rep = 0; rep < 5; ++rep) {
+        B2_CUDA(ctx, cudaEventRecord(ctx->ev0, ctx->stream));
+        peak_wide_kernel<<<blocks, threads, 0, ctx->stream>>>(in.as<uint32_t>(), out.as<uint32_t>(), cyc.as<long long>());
+        B2_CUDA(ctx, cudaEventRecord(ctx->ev1, ctx->stream));
+        B2_CUDA(ctx, cudaEventSynchronize(ctx->ev1));
+        float ms;
+        B2_CUDA(ctx, cudaEventElapsedTime(&ms, ctx->ev0, ctx->ev1));
+        if (rep && ms < best_w) {
+            best_w = ms;
+            B2_CUDA(ctx, cudaMemcpy(&cycles, cyc.p, 8, cudaMemcpyDeviceToHost));
+        }
+        B2_CUDA(ctx, cudaEventRecord(ctx->ev0, ctx->stream));
+        peak_imad_kernel<<<blocks, threads, 0, ctx->stream>>>(in.as<uint32_t>(), out.as<uint32_t>());
+        B2_CUDA(ctx, cudaEventRecord(ctx->ev1, ctx->stream));
+        B2_CUDA(ctx, cudaEventSynchronize(ctx->ev1));
+        B2_CUDA(ctx, cudaEventElapsedTime(&ms, ctx->ev0, ctx->ev1));
+        if (rep && ms < best_i) best_i = ms;
+    }
+    const double lanes = (double)blocks * threads;
+    if (mac32_per_s) *mac32_per_s = lanes * PEAK_ITERS * 16.0 / (best_w * 1e-3);
+    if (imad32_per_s) *imad32_per_s = lanes * PEAK_ITERS * 16.0 / (best_i * 1e-3);
+    // one block's cycle count over the whole kernel's wall time: a lower bound of the SM clock
+    // when the grid is a single wave (4 blocks of 256 threads per SM fit at once).
+    if (sm_mhz) *sm_mhz = (double)cycles / (best_w * 1e-3) / 1e6;
+    return B200_OK;
+}
+
+// ---------------------------------------------------------------------------------------
+// fixed-base batch scalar multiplication: 32 windows of 8 bits, table T[w][d-1] = d * 2^(8w) * G
+// (affine, built on the host), one thread per scalar, per-thread Fermat inversion to normalise.
+// ---------------------------------------------------------------------------------------
+template <class F>
+__global__ void __launch_bounds__(128) batch_mul_kernel(const Affine<F>* __restrict__ table, const Fr* __restrict__ scalars, size_t n,
+                                 Affine<F>* __restrict__ out) {
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const Fr s = ld_vec(scalars + i).from_mont();
+    XYZZ<F> acc = XYZZ<F>::inf();
+    for (int w = 0; w < 32; ++w) {
+        const uint32_t d = (s.l[w >> 2] >> ((w & 3) * 8)) & 0xffu;
+        if (d) acc.add_mixed(ldg_vec(table + (size_t)w * 255 + d - 1));
+    }
+    st_vec(out + i, acc.to_affine());
+}
+
+template <class F>
+static int batch_mul_impl(b200_ctx* ctx, const Affine<F>& base, const Fr* d_scalars, size_t n, Affine<F>* d_out) {
+    if (!n) return B200_OK;
+    // host table: projective accumulation, then one batched inversion
+    const int TW = 32, TD = 255;
+    std::vector<XYZZ<F>> proj((size_t)TW * TD);
+    XYZZ<F> b = XYZZ<F>::from_affine(base);
+    for (int w = 0; w < TW; ++w) {
+        XYZZ<F> acc = b;
+        for (int d = 1; d <= TD; ++d) {
+            proj[(size_t)w * TD + d - 1] = acc;
+            acc.add(b);
+        }
+        b = acc;  // 256 * previous
+    }
+    // batch inversion of ZZZ (Montgomery trick); infinity entries (base = inf) stay (0,0)
+    std::vector<Affine<F>> table(proj.size());
+    std::vector<F> prefix(proj.size());
+    F run = F::one();
+    for (size_t k = 0; k < proj.size(); ++k) {
+        prefix[k] = run;
+        if (!proj[k].is_inf()) run = run * proj[k].ZZZ;
+    }
+    F inv = run.inv();
+    for (size_t k = proj.size(); k-- > 0;) {
+        if (proj[k].is_inf()) { table[k] = Affine<F>::inf(); continue; }
+        const F zi = inv * prefix[k];          // 1/ZZZ_k
+        inv = inv * proj[k].ZZZ;
+        const F zzi = (zi * proj[k].ZZ).sqr();  // 1/ZZ_k
+        table[k] = {proj[k].X * zzi, proj[k].Y * zi};
+    }
+    DevBuf dt;
+    B2_CUDA(ctx, dt.alloc(table.size() * sizeof(Affine<F>)));
+    B2_CUDA(ctx, cudaMemcpyAsync(dt.p, table.data(), table.size() * sizeof(Affine<F>), cudaMemcpyHostToDevice, ctx->stream));
+    batch_mul_kernel<F><<<(unsigned)((n + 127) / 128), 128, 0, ctx->stream>>>(dt.as<Affine<F>>(), d_scalars, n, d_out);
+    B2_CUDA(ctx, cudaGetLastError());
+    B2_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return B200_OK;
+}
+
+int batch_mul_g1(b200_ctx* ctx, const G1Affine& base, const Fr* d_scalars, size_t n, G1Affine* d_out) {
+    return batch_mul_impl<Fp>(ctx, base, d_scalars, n, d_out);
+}
+int batch_mul_g2(b200_ctx* ctx, const G2Affine& base, const Fr* d_scalars, size_t n, G2Affine* d_out) {
+    return batch_mul_impl<Fp2>(ctx, base, d_scalars, n, d_out);
+}
+
+}  // namespace b200

@@ -1,0 +1,9 @@
+#pragma once
+#include "msm.cuh"
+namespace b200 {
+int vec_mul_fr(b200_ctx* ctx, const Fr* a, const Fr* b, Fr* out, size_t n);
+int vec_mul_fp(b200_ctx* ctx, const Fp* a, const Fp* b, Fp* out, size_t n);
+int imad_peak(b200_ctx* ctx, double* mac32_per_s, double* imad32_per_s, double* sm_mhz);
+int batch_mul_g1(b200_ctx* ctx, const G1Affine& base, const Fr* d_scalars, size_t n, G1Affine* d_out);
+int batch_mul_g2(b200_ctx* ctx, const G2Affine& base, const Fr* d_scalars, size_t n, G2Affine* d_out);
+}  // namespace b200

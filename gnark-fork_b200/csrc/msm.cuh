@@ -1,0 +1,264 @@
+// Signed-digit Pippenger multi-scalar multiplication on the device (G1 and G2 share the code).
+//
+// Replaces gnark-crypto's G1Jac.MultiExp / G2Jac.MultiExp as called from
+// /root/reference/backend/groth16/bn254/prove.go:201,214,234,244,290 (and iciclegnark.MsmOnDevice /
+// MsmG2OnDevice, /root/reference/backend/groth16/bn254/icicle/icicle.go:302-382).
+//
+// Pipeline (all on one stream):
+//   1. digits   : scalar out of Montgomery form, c-bit signed-digit recoding, per-window
+//                 bucket histogram                                  (msm_digits_kernel)
+//   2. scan     : exclusive prefix sum of the W * 2^(c-1) bucket counts (msm_scan_*)
+//   3. scatter  : counting sort of (bucket -> point index | sign) per window
+//   4. accumulate: one thread per bucket, XYZZ += affine (8M + 2S), doubling / cancellation
+//                 handled (DummySetup keys make every base equal, setup.go:532-546)
+//   5. reduce   : sum_k k * B_k per window by a tree of running sums
+//   6. the W window sums go back to the host, which does the c-doubling Horner combine.
+#pragma once
+#include "common.cuh"
+
+namespace b200 {
+
+// Window count for c-bit signed digits over a 254-bit scalar: W*c >= 255 absorbs the last carry.
+B2_HD int msm_num_windows(int c) { return (255 + c - 1) / c; }
+
+// Signed-digit recoding of a canonical (non-Montgomery) scalar: digit d_w in [-2^(c-1)+1, 2^(c-1)],
+// sum_w d_w 2^(c w) = s.
+B2_HD void msm_signed_digits(const uint32_t* s, int c, int W, int32_t* out, size_t stride) {
+    int32_t carry = 0;
+    const uint32_t mask = (1u << c) - 1u;
+    for (int w = 0; w < W; ++w) {
+        const int off = w * c, limb = off >> 5, sh = off & 31;
+        const uint64_t lo = limb < 8 ? s[limb] : 0u, hi = limb + 1 < 8 ? s[limb + 1] : 0u;
+        const uint32_t raw = (uint32_t)(((hi << 32) | lo) >> sh) & mask;
+        int32_t d = (int32_t)raw + carry;
+        carry = 0;
+        if (d > (1 << (c - 1))) { d -= (1 << c); carry = 1; }
+        out[(size_t)w * stride] = d;
+    }
+}
+
+struct MsmPlan {
+    int c, W;
+    uint32_t nb;      // buckets per window = 2^(c-1)
+    uint32_t L0;      // leaves per level-0 reduce node
+    uint32_t L;       // fan-in of the upper reduce levels
+};
+
+inline MsmPlan msm_plan(size_t n, int c_override) {
+    int c;
+    if (c_override > 0) c = c_override;
+    else if (n <= ((size_t)1 << 10)) c = 8;
+    else if (n <= ((size_t)1 << 14)) c = 10;
+    else if (n <= ((size_t)1 << 17)) c = 12;
+    else if (n <= ((size_t)1 << 19)) c = 14;
+    else c = 16;
+    MsmPlan p;
+    p.c = c;
+    p.W = msm_num_windows(c);
+    p.nb = 1u << (c - 1);
+    p.L0 = 16;
+    p.L = 16;
+    return p;
+}
+
+#if defined(__CUDACC__)
+
+template <class T>
+__device__ __forceinline__ T ld_vec(const T* p) {
+    static_assert(sizeof(T) % 16 == 0, "16-byte multiples only");
+    T r;
+    const uint4* s = reinterpret_cast<const uint4*>(p);
+    uint4* d = reinterpret_cast<uint4*>(&r);
+#pragma unroll
+    for (int i = 0; i < (int)(sizeof(T) / 16); ++i) d[i] = s[i];
+    return r;
+}
+template <class T>
+__device__ __forceinline__ T ldg_vec(const T* p) {
+    static_assert(sizeof(T) % 16 == 0, "16-byte multiples only");
+    T r;
+    const uint4* s = reinterpret_cast<const uint4*>(p);
+    uint4* d = reinterpret_cast<uint4*>(&r);
+#pragma unroll
+    for (int i = 0; i < (int)(sizeof(T) / 16); ++i) d[i] = __ldg(s + i);
+    return r;
+}
+template <class T>
+__device__ __forceinline__ void st_vec(T* p, const T& v) {
+    static_assert(sizeof(T) % 16 == 0, "16-byte multiples only");
+    uint4* d = reinterpret_cast<uint4*>(p);
+    const uint4* s = reinterpret_cast<const uint4*>(&v);
+#pragma unroll
+    for (int i = 0; i < (int)(sizeof(T) / 16); ++i) d[i] = s[i];
+}
+
+// 1. digits + histogram.  idx_map (optional): scalar i is scalars[idx_map[i]] (wire filtering by
+// pk.InfinityA/B, prove.go:154-175, done as a gather instead of three host-side copies).
+static __global__ void msm_digits_kernel(const Fr* __restrict__ scalars, const uint32_t* __restrict__ idx_map, uint32_t n,
+                                  int c, int W, int32_t* __restrict__ digits, uint32_t* __restrict__ counts, uint32_t nb) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const uint32_t src = idx_map ? idx_map[i] : i;
+    const Fr s = ld_vec(scalars + src).from_mont();
+    int32_t carry = 0;
+    const uint32_t mask = (1u << c) - 1u;
+    for (int w = 0; w < W; ++w) {
+        const int off = w * c, limb = off >> 5, sh = off & 31;
+        const uint64_t lo = limb < 8 ? s.l[limb] : 0u, hi = limb + 1 < 8 ? s.l[limb + 1] : 0u;
+        const uint32_t raw = (uint32_t)(((hi << 32) | lo) >> sh) & mask;
+        int32_t d = (int32_t)raw + carry;
+        carry = 0;
+        if (d > (1 << (c - 1))) { d -= (1 << c); carry = 1; }
+        digits[(size_t)w * n + i] = d;
+        if (d != 0) atomicAdd(&counts[(size_t)w * nb + (uint32_t)((d < 0 ? -d : d) - 1)], 1u);
+    }
+}
+
+// 2. exclusive scan of `m` counters, three launches (block sums, scan of block sums, rescan).
+constexpr int SCAN_THREADS = 256;
+constexpr int SCAN_ITEMS = 16;
+constexpr int SCAN_CHUNK = SCAN_THREADS * SCAN_ITEMS;
+
+__device__ __forceinline__ uint32_t block_exclusive_scan(uint32_t v, uint32_t* total) {
+    __shared__ uint32_t warp_sums[32];
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    uint32_t x = v;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const uint32_t y = __shfl_up_sync(0xffffffffu, x, o);
+        if (lane >= o) x += y;
+    }
+    if (lane == 31) warp_sums[wid] = x;
+    __syncthreads();
+    if (wid == 0) {
+        const int nw = blockDim.x >> 5;
+        uint32_t s = lane < nw ? warp_sums[lane] : 0u;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const uint32_t y = __shfl_up_sync(0xffffffffu, s, o);
+            if (lane >= o) s += y;
+        }
+        warp_sums[lane] = s;  // inclusive
+    }
+    __syncthreads();
+    const uint32_t base = wid ? warp_sums[wid - 1] : 0u;
+    if (total) *total = warp_sums[(blockDim.x >> 5) - 1];
+    const uint32_t r = base + x - v;
+    __syncthreads();
+    return r;
+}
+
+static __global__ void msm_scan_sums_kernel(const uint32_t* __restrict__ in, uint32_t m, uint32_t* __restrict__ block_sums) {
+    const uint32_t base = blockIdx.x * SCAN_CHUNK + threadIdx.x * SCAN_ITEMS;
+    uint32_t s = 0;
+#pragma unroll
+    for (int j = 0; j < SCAN_ITEMS; ++j) if (base + j < m) s += in[base + j];
+    uint32_t total;
+    block_exclusive_scan(s, &total);
+    if (threadIdx.x == 0) block_sums[blockIdx.x] = total;
+}
+// single block: in-place exclusive scan of nblocks block sums
+static __global__ void msm_scan_top_kernel(uint32_t* block_sums, uint32_t nblocks) {
+    __shared__ uint32_t carry_s;
+    if (threadIdx.x == 0) carry_s = 0;
+    __syncthreads();
+    for (uint32_t base = 0; base < nblocks; base += blockDim.x) {
+        const uint32_t i = base + threadIdx.x;
+        const uint32_t v = i < nblocks ? block_sums[i] : 0u;
+        uint32_t total;
+        const uint32_t ex = block_exclusive_scan(v, &total);
+        const uint32_t carry = carry_s;
+        if (i < nblocks) block_sums[i] = carry + ex;
+        __syncthreads();
+        if (threadIdx.x == 0) carry_s = carry + total;
+        __syncthreads();
+    }
+}
+static __global__ void msm_scan_final_kernel(const uint32_t* __restrict__ in, uint32_t m, const uint32_t* __restrict__ block_sums,
+                                      uint32_t* __restrict__ out, uint32_t* __restrict__ out2) {
+    const uint32_t base = blockIdx.x * SCAN_CHUNK + threadIdx.x * SCAN_ITEMS;
+    uint32_t v[SCAN_ITEMS], s = 0;
+#pragma unroll
+    for (int j = 0; j < SCAN_ITEMS; ++j) { v[j] = base + j < m ? in[base + j] : 0u; s += v[j]; }
+    uint32_t ex = block_exclusive_scan(s, nullptr) + block_sums[blockIdx.x];
+#pragma unroll
+    for (int j = 0; j < SCAN_ITEMS; ++j) {
+        if (base + j < m) { out[base + j] = ex; out2[base + j] = ex; }
+        ex += v[j];
+    }
+}
+
+// 3. scatter (counting sort): cursor starts as a copy of the offsets.
+static __global__ void msm_scatter_kernel(const int32_t* __restrict__ digits, uint32_t n, int W, uint32_t nb,
+                                   uint32_t* __restrict__ cursor, uint32_t* __restrict__ sorted) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    for (int w = 0; w < W; ++w) {
+        const int32_t d = digits[(size_t)w * n + i];
+        if (d == 0) continue;
+        const uint32_t b = (uint32_t)((d < 0 ? -d : d) - 1);
+        const uint32_t pos = atomicAdd(&cursor[(size_t)w * nb + b], 1u);
+        sorted[pos] = i | (d < 0 ? 0x80000000u : 0u);
+    }
+}
+
+// 4. bucket accumulation: thread t owns bucket t (all windows concatenated).
+template <class F>
+__global__ void __launch_bounds__(128) msm_accumulate_kernel(const Affine<F>* __restrict__ bases, const uint32_t* __restrict__ sorted,
+                                      const uint32_t* __restrict__ offsets, const uint32_t* __restrict__ counts,
+                                      uint32_t n_buckets, XYZZ<F>* __restrict__ buckets) {
+    const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= n_buckets) return;
+    const uint32_t start = offsets[t], cnt = counts[t];
+    XYZZ<F> acc = XYZZ<F>::inf();
+    for (uint32_t j = 0; j < cnt; ++j) {
+        const uint32_t e = sorted[start + j];
+        Affine<F> p = ldg_vec(bases + (e & 0x7fffffffu));
+        if (e >> 31) p.y = p.y.neg();
+        acc.add_mixed(p);
+    }
+    st_vec(buckets + t, acc);
+}
+
+// 5. reduction tree.  A node over a range of `len` consecutive buckets carries
+//      S  = sum of the buckets,   Wt = sum of (position in range + first_weight) * bucket.
+// Level 0 builds nodes over L0 buckets with the running-sum trick (first_weight = 1: bucket k-1
+// of a window weighs k).  Upper levels merge L children of length `len`:
+//      S' = sum S_c,   Wt' = sum Wt_c + len * sum c * S_c.
+template <class F>
+__global__ void __launch_bounds__(64) msm_reduce_leaf_kernel(const XYZZ<F>* __restrict__ buckets, uint32_t n_nodes, uint32_t L0,
+                                       XYZZ<F>* __restrict__ outS, XYZZ<F>* __restrict__ outW) {
+    const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= n_nodes) return;
+    const XYZZ<F>* b = buckets + (size_t)t * L0;
+    XYZZ<F> run = XYZZ<F>::inf(), acc = XYZZ<F>::inf();
+    for (int j = (int)L0 - 1; j >= 0; --j) {
+        run.add(ld_vec(b + j));
+        acc.add(run);
+    }
+    st_vec(outS + t, run);
+    st_vec(outW + t, acc);
+}
+
+template <class F>
+__global__ void __launch_bounds__(64) msm_reduce_node_kernel(const XYZZ<F>* __restrict__ inS, const XYZZ<F>* __restrict__ inW, uint32_t n_nodes,
+                                       uint32_t L, uint32_t log_len, XYZZ<F>* __restrict__ outS, XYZZ<F>* __restrict__ outW) {
+    const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= n_nodes) return;
+    const XYZZ<F>* s = inS + (size_t)t * L;
+    const XYZZ<F>* w = inW + (size_t)t * L;
+    XYZZ<F> run = XYZZ<F>::inf(), acc = XYZZ<F>::inf(), wsum = XYZZ<F>::inf();
+    for (int j = (int)L - 1; j >= 0; --j) {
+        acc.add(run);              // child j weighs j
+        run.add(ld_vec(s + j));
+        wsum.add(ld_vec(w + j));
+    }
+    for (uint32_t k = 0; k < log_len; ++k) acc = acc.dbl();
+    wsum.add(acc);
+    st_vec(outS + t, run);
+    st_vec(outW + t, wsum);
+}
+
+#endif  // __CUDACC__
+
+}  // namespace b200

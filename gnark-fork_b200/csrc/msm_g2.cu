@@ -1,0 +1,8 @@
+// G2 instantiation of the MSM pipeline (G2Jac.MultiExp, prove.go:290).
+#include "msm_host.cuh"
+namespace b200 {
+int msm_g2_run(b200_ctx* ctx, const G2Affine* d_bases, const Fr* d_scalars, const uint32_t* d_idx_map, size_t n,
+               G2Jac* out_host, void* ws) {
+    return msm_run_impl<Fp2>(ctx, d_bases, d_scalars, d_idx_map, n, out_host, ws);
+}
+}  // namespace b200

@@ -1,0 +1,290 @@
+// Fr NTT kernels (sm_100a) and the device-side fft.Domain.
+// Reference semantics: gnark-crypto fft.Domain.FFT / FFTInverse as called from
+// /root/reference/backend/groth16/bn254/prove.go:369-375,393 (replaces iciclegnark.NttOnDevice /
+// INttOnDevice, /root/reference/backend/groth16/bn254/icicle/icicle.go:489-502).
+#include <cstdlib>
+#include "ntt_host.cuh"
+
+namespace b200 {
+
+// ---------------------------------------------------------------------------------------
+// shared-memory tile: element i is split into its low and high 16-byte halves, kept in two
+// planes so that a warp touching 32 consecutive elements issues conflict-free 128-bit accesses
+// (plane 1 is shifted by 64 B = 16 banks).
+// ---------------------------------------------------------------------------------------
+struct SmemTile {
+    uint4* lo;
+    uint4* hi;
+    __device__ __forceinline__ SmemTile(void* base, uint32_t tl) {
+        lo = reinterpret_cast<uint4*>(base);
+        hi = lo + ((size_t)1 << tl) + 4;
+    }
+    __device__ __forceinline__ Fr get(uint32_t i) const {
+        const uint4 a = lo[i], b = hi[i];
+        Fr f;
+        f.l[0] = a.x; f.l[1] = a.y; f.l[2] = a.z; f.l[3] = a.w;
+        f.l[4] = b.x; f.l[5] = b.y; f.l[6] = b.z; f.l[7] = b.w;
+        return f;
+    }
+    __device__ __forceinline__ void put(uint32_t i, const Fr& f) {
+        lo[i] = make_uint4(f.l[0], f.l[1], f.l[2], f.l[3]);
+        hi[i] = make_uint4(f.l[4], f.l[5], f.l[6], f.l[7]);
+    }
+};
+static inline size_t smem_tile_bytes(uint32_t tl) { return (((size_t)2 << tl) + 4) * sizeof(uint4); }
+
+__device__ __forceinline__ Fr ld_fr(const Fr* p) {
+    const uint4* q = reinterpret_cast<const uint4*>(p);
+    const uint4 a = q[0], b = q[1];
+    Fr f;
+    f.l[0] = a.x; f.l[1] = a.y; f.l[2] = a.z; f.l[3] = a.w;
+    f.l[4] = b.x; f.l[5] = b.y; f.l[6] = b.z; f.l[7] = b.w;
+    return f;
+}
+__device__ __forceinline__ Fr ldg_fr(const Fr* p) {  // read-only path (tables)
+    const uint4* q = reinterpret_cast<const uint4*>(p);
+    const uint4 a = __ldg(q), b = __ldg(q + 1);
+    Fr f;
+    f.l[0] = a.x; f.l[1] = a.y; f.l[2] = a.z; f.l[3] = a.w;
+    f.l[4] = b.x; f.l[5] = b.y; f.l[6] = b.z; f.l[7] = b.w;
+    return f;
+}
+__device__ __forceinline__ void st_fr(Fr* p, const Fr& f) {
+    uint4* q = reinterpret_cast<uint4*>(p);
+    q[0] = make_uint4(f.l[0], f.l[1], f.l[2], f.l[3]);
+    q[1] = make_uint4(f.l[4], f.l[5], f.l[6], f.l[7]);
+}
+
+struct NttPassArgs {
+    Fr* data;
+    const Fr* tw;    // w^j (or w^-j for an inverse transform), j < n/2
+    const Fr* pre;   // optional scale applied on load  (first pass)
+    const Fr* post;  // optional scale applied on store (last pass)
+    NttPassGeom g;
+    int has_post_scalar;
+    Fr post_scalar;
+};
+
+constexpr int NTT_THREADS = 1024;
+
+template <int DIT>
+__global__ void __launch_bounds__(NTT_THREADS) ntt_pass_kernel(const NttPassArgs a) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    SmemTile sm(smem_raw, a.g.TL);
+    const NttPassGeom g = a.g;
+    const uint32_t tile = blockIdx.x;
+    const uint32_t tile_n = 1u << g.TL;
+
+    for (uint32_t loc = threadIdx.x; loc < tile_n; loc += blockDim.x) {
+        const uint32_t gi = ntt_gidx(g, tile, loc);
+        Fr v = ld_fr(a.data + gi);
+        if (a.pre) v = v * ldg_fr(a.pre + gi);
+        sm.put(loc, v);
+    }
+    __syncthreads();
+
+    const uint32_t n_bf = tile_n >> 1;
+    for (uint32_t k = 0; k < g.S; ++k) {
+        const uint32_t bit = ntt_stage_bit(g, DIT, k);
+        const uint32_t s = g.s0 + k;
+        for (uint32_t bf = threadIdx.x; bf < n_bf; bf += blockDim.x) {
+            const uint32_t i0 = ntt_bf_lower(bf, bit), i1 = i0 | (1u << bit);
+            const uint32_t g0 = ntt_gidx(g, tile, i0);
+            const uint32_t e = ntt_twiddle_exp(g.log_n, DIT, s, g0);
+            const Fr u = sm.get(i0), v = sm.get(i1);
+            if (DIT) {
+                const Fr t = (e == 0) ? v : v * ldg_fr(a.tw + e);
+                sm.put(i0, u + t);
+                sm.put(i1, u - t);
+            } else {
+                const Fr d = u - v;
+                sm.put(i0, u + v);
+                sm.put(i1, (e == 0) ? d : d * ldg_fr(a.tw + e));
+            }
+        }
+        __syncthreads();
+    }
+
+    for (uint32_t loc = threadIdx.x; loc < tile_n; loc += blockDim.x) {
+        const uint32_t gi = ntt_gidx(g, tile, loc);
+        Fr v = sm.get(loc);
+        if (a.post) v = v * ldg_fr(a.post + gi);
+        if (a.has_post_scalar) v = v * a.post_scalar;
+        st_fr(a.data + gi, v);
+    }
+}
+
+// out[pos(k)] = mult * base^k for k < count; pos = k or bitrev_{log_n}(k).  Each thread owns a
+// run of 16 consecutive exponents: one square-and-multiply, then 15 products.
+constexpr int POW_RUN = 16;
+__global__ void powers_kernel(Fr* out, const Fr base, const Fr mult, uint32_t count, int bitrev_log_n) {
+    const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+    const uint64_t k0 = (uint64_t)t * POW_RUN;
+    if (k0 >= count) return;
+    Fr x = base.pow_u64(k0) * mult;
+    for (int j = 0; j < POW_RUN && k0 + j < count; ++j) {
+        const uint32_t k = (uint32_t)(k0 + j);
+        const uint32_t pos = bitrev_log_n ? (__brev(k) >> (32 - bitrev_log_n)) : k;
+        st_fr(out + pos, x);
+        x = x * base;
+    }
+}
+
+__global__ void mul_sub_kernel(Fr* a, const Fr* b, const Fr* c, size_t n) {
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    st_fr(a + i, ld_fr(a + i) * ld_fr(b + i) - ld_fr(c + i));
+}
+
+// ---------------------------------------------------------------------------------------
+// host side
+// ---------------------------------------------------------------------------------------
+static int gen_powers(b200_ctx* ctx, Fr* out, const Fr& base, const Fr& mult, size_t count, int bitrev_log_n) {
+    if (count == 0) return B200_OK;
+    const size_t threads = (count + POW_RUN - 1) / POW_RUN;
+    const int bs = 128;
+    powers_kernel<<<(unsigned)((threads + bs - 1) / bs), bs, 0, ctx->stream>>>(out, base, mult, (uint32_t)count, bitrev_log_n);
+    B2_CUDA(ctx, cudaGetLastError());
+    return B200_OK;
+}
+
+int ntt_domain_get(b200_ctx* ctx, unsigned log_n, const Fr& gen, const Fr& coset, NttDomain** out) {
+    if (log_n > 27) return ctx->fail(B200_ERR_UNSUPPORTED, "NTT size above 2^27");
+    for (NttDomain* d : ctx->domains)
+        if (d->log_n == log_n && d->gen == gen && d->coset == coset) { *out = d; return B200_OK; }
+    NttDomain* d = new NttDomain();
+    d->log_n = log_n;
+    d->gen = gen;
+    d->coset = coset;
+    d->gen_inv = gen.inv();
+    d->coset_inv = coset.inv();
+    d->ninv = Fr::from_u32(1).dbl().pow_u64(log_n).inv();  // (2^log_n)^-1
+    d->den = (coset.pow_u64((uint64_t)1 << log_n) - Fr::one()).inv();
+    const size_t half = log_n ? ((size_t)1 << (log_n - 1)) : 1;
+    cudaError_t e = d->tw_fwd.alloc(half * sizeof(Fr));
+    if (e == cudaSuccess) e = d->tw_inv.alloc(half * sizeof(Fr));
+    if (e != cudaSuccess) { delete d; return ctx->fail(B200_ERR_NOMEM, "twiddle tables", cudaGetErrorString(e)); }
+    int st = gen_powers(ctx, d->tw_fwd.as<Fr>(), d->gen, Fr::one(), half, 0);
+    if (st == B200_OK) st = gen_powers(ctx, d->tw_inv.as<Fr>(), d->gen_inv, Fr::one(), half, 0);
+    if (st != B200_OK) { delete d; return st; }
+    ctx->domains.push_back(d);
+    *out = d;
+    return B200_OK;
+}
+
+int ntt_domain_table(b200_ctx* ctx, NttDomain* d, NttDomain::Table t, const Fr** out) {
+    if (!d->tab[t].p) {
+        const size_t n = d->n();
+        cudaError_t e = d->tab[t].alloc(n * sizeof(Fr));
+        if (e != cudaSuccess) return ctx->fail(B200_ERR_NOMEM, "coset table", cudaGetErrorString(e));
+        Fr base, mult = Fr::one();
+        int br = 0;
+        switch (t) {
+            case NttDomain::COSET_NAT: base = d->coset; break;
+            case NttDomain::COSET_BR: base = d->coset; br = 1; break;
+            case NttDomain::COSETINV_NAT: base = d->coset_inv; mult = d->ninv; break;
+            case NttDomain::COSETINV_BR: base = d->coset_inv; mult = d->ninv; br = 1; break;
+            case NttDomain::H_BC: base = d->coset; mult = d->ninv; br = 1; break;
+            case NttDomain::H_A: base = d->coset; mult = d->ninv * d->den; br = 1; break;
+            default: return ctx->fail(B200_ERR_ARG, "bad table id");
+        }
+        int st = gen_powers(ctx, d->tab[t].as<Fr>(), base, mult, n, (br && d->log_n) ? (int)d->log_n : 0);
+        if (st != B200_OK) { d->tab[t].release(); return st; }
+    }
+    *out = d->tab[t].as<Fr>();
+    return B200_OK;
+}
+
+void ntt_domain_free_all(b200_ctx* ctx) {
+    for (NttDomain* d : ctx->domains) delete d;
+    ctx->domains.clear();
+}
+
+static uint32_t env_u32(const char* name, uint32_t dflt, uint32_t lo, uint32_t hi) {
+    const char* v = getenv(name);
+    if (!v || !*v) return dflt;
+    long x = strtol(v, nullptr, 10);
+    if (x < (long)lo || x > (long)hi) return dflt;
+    return (uint32_t)x;
+}
+
+int ntt_run(b200_ctx* ctx, NttDomain* d, Fr* data, int inverse, int dit, const Fr* pre, const Fr* post,
+            const Fr* post_scalar) {
+    static bool attr_set = false;
+    if (!attr_set) {
+        B2_CUDA(ctx, cudaFuncSetAttribute(ntt_pass_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_tile_bytes(12)));
+        B2_CUDA(ctx, cudaFuncSetAttribute(ntt_pass_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_tile_bytes(12)));
+        attr_set = true;
+    }
+    if (d->log_n == 0) {  // n = 1: every variant is the identity (1/n = 1, g^0 = 1)
+        return B200_OK;
+    }
+    const uint32_t tl_max = env_u32("B200_NTT_TILE_LOG", 12, 6, 12);
+    const uint32_t s_max = env_u32("B200_NTT_STRIDED_STAGES", 12, 1, tl_max);
+    NttPassGeom plan[8];
+    const int np = ntt_plan(d->log_n, dit, tl_max, s_max < tl_max ? s_max : tl_max, plan);
+    for (int i = 0; i < np; ++i) {
+        NttPassArgs a;
+        a.data = data;
+        a.tw = inverse ? d->tw_inv.as<Fr>() : d->tw_fwd.as<Fr>();
+        a.pre = (i == 0) ? pre : nullptr;
+        a.post = (i == np - 1) ? post : nullptr;
+        a.g = plan[i];
+        a.has_post_scalar = (i == np - 1 && post_scalar) ? 1 : 0;
+        a.post_scalar = post_scalar ? *post_scalar : Fr::one();
+        const uint32_t tiles = (uint32_t)(d->n() >> plan[i].TL);
+        uint32_t threads = 1u << (plan[i].TL > 1 ? plan[i].TL - 1 : 0);
+        if (threads > NTT_THREADS) threads = NTT_THREADS;
+        if (threads < 32) threads = 32;
+        const size_t smem = smem_tile_bytes(plan[i].TL);
+        if (dit) ntt_pass_kernel<1><<<tiles, threads, smem, ctx->stream>>>(a);
+        else ntt_pass_kernel<0><<<tiles, threads, smem, ctx->stream>>>(a);
+        B2_CUDA(ctx, cudaGetLastError());
+    }
+    return B200_OK;
+}
+
+int ntt_gnark(b200_ctx* ctx, NttDomain* d, Fr* data, int inverse, int dit, int on_coset) {
+    const Fr* pre = nullptr;
+    const Fr* post = nullptr;
+    const Fr* scalar = nullptr;
+    if (!inverse) {
+        if (on_coset) B2_TRY(ntt_domain_table(ctx, d, dit ? NttDomain::COSET_BR : NttDomain::COSET_NAT, &pre));
+    } else {
+        if (on_coset) B2_TRY(ntt_domain_table(ctx, d, dit ? NttDomain::COSETINV_NAT : NttDomain::COSETINV_BR, &post));
+        else scalar = &d->ninv;
+    }
+    return ntt_run(ctx, d, data, inverse, dit, pre, post, scalar);
+}
+
+int ntt_mul_sub(b200_ctx* ctx, Fr* a, const Fr* b, const Fr* c, size_t n) {
+    if (n == 0) return B200_OK;
+    const int bs = 256;
+    mul_sub_kernel<<<(unsigned)((n + bs - 1) / bs), bs, 0, ctx->stream>>>(a, b, c, n);
+    B2_CUDA(ctx, cudaGetLastError());
+    return B200_OK;
+}
+
+// computeH (prove.go:353-396) with the scalings folded:
+//   x <- FFTInverse(x, DIF)            (prove.go:369-371)  1/n   } one table product on the last
+//   x <- FFT(x, DIT, OnCoset)          (prove.go:373-375)  g^br(i)} store of the inverse transform
+//   a <- (a*b - c) * den               (prove.go:377-390)  den folded into a's table
+//   a <- FFTInverse(a, DIF, OnCoset)   (prove.go:393)      g^-br(i)/n on the last store
+// Field elements are canonical (fully reduced) so re-associating the products is bit-exact.
+int ntt_compute_h(b200_ctx* ctx, NttDomain* d, Fr* a, Fr* b, Fr* c) {
+    const Fr *ha, *hbc, *cinv;
+    B2_TRY(ntt_domain_table(ctx, d, NttDomain::H_A, &ha));
+    B2_TRY(ntt_domain_table(ctx, d, NttDomain::H_BC, &hbc));
+    B2_TRY(ntt_domain_table(ctx, d, NttDomain::COSETINV_BR, &cinv));
+    B2_TRY(ntt_run(ctx, d, a, 1, 0, nullptr, ha, nullptr));
+    B2_TRY(ntt_run(ctx, d, b, 1, 0, nullptr, hbc, nullptr));
+    B2_TRY(ntt_run(ctx, d, c, 1, 0, nullptr, hbc, nullptr));
+    B2_TRY(ntt_run(ctx, d, a, 0, 1, nullptr, nullptr, nullptr));
+    B2_TRY(ntt_run(ctx, d, b, 0, 1, nullptr, nullptr, nullptr));
+    B2_TRY(ntt_run(ctx, d, c, 0, 1, nullptr, nullptr, nullptr));
+    B2_TRY(ntt_mul_sub(ctx, a, b, c, d->n()));
+    B2_TRY(ntt_run(ctx, d, a, 1, 0, nullptr, cinv, nullptr));
+    return B200_OK;
+}
+
+}  // namespace b200

@@ -1,0 +1,210 @@
+/* b200prover.h -- C ABI of the B200-native (sm_100a) proving backend for gnark's Groth16 hot path.
+ *
+ * This is the boundary a cgo shim binds.  It replaces, call for call, the
+ * device-library surface the reference reaches through its `icicle` build tag
+ * (/root/reference/backend/groth16/bn254/icicle/icicle.go) and the gnark-crypto calls of the CPU
+ * prover (/root/reference/backend/groth16/bn254/prove.go).  Each entry point cites what it
+ * replaces.
+ *
+ * Conventions
+ *   - Every field element is 4 little-endian u64 limbs in MONTGOMERY form (R = 2^256), exactly as a
+ *     gnark-crypto fr.Element / fp.Element sits in Go memory, so the glue passes
+ *     unsafe.Pointer(&slice[0]) with no conversion.
+ *   - G1Affine = X,Y (8 u64; (0,0) = infinity); G1Jac = X,Y,Z (12 u64; Z = 0 = infinity);
+ *     G2Affine = X.A0,X.A1,Y.A0,Y.A1 (16 u64); G2Jac = 24 u64.
+ *   - Jacobian results are SOME representative of the point (not gnark-crypto's particular
+ *     one); equality with MultiExp is defined on the affine-normalised point (FromJacobian).
+ *   - Return value: 0 on success, a negative b200_status otherwise; b200_last_error(ctx) holds a
+ *     message.  No exception, abort or callback crosses the boundary.
+ *   - The caller owns host buffers for the duration of the call only.  Handles (ctx, domain,
+ *     bases, pk) own device memory and are freed explicitly.
+ *   - A ctx is bound to ONE device and is not re-entrant (serialise calls per ctx); distinct
+ *     ctx are independent.  Multi-GPU = one ctx per device/rank, shards selected with
+ *     (shard_index, shard_count); partial sums are combined by the host (b200_g1_jac_add ...).
+ *   - There is no CPU fallback: without a CUDA device b200_init fails with B200_ERR_CUDA.
+ *   - Zero-length MSM returns the point at infinity; infinity bases (0,0) and zero scalars are
+ *     legal inputs.
+ */
+#ifndef B200PROVER_H
+#define B200PROVER_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct b200_ctx b200_ctx;
+typedef struct b200_bases b200_bases;             /* resident MSM base set (G1 or G2)         */
+typedef struct b200_groth16_pk b200_groth16_pk;   /* resident Groth16 proving key (or shard)  */
+
+enum b200_status {
+    B200_OK = 0,
+    B200_ERR_CUDA = -1,        /* CUDA runtime error (message in b200_last_error)              */
+    B200_ERR_ARG = -2,         /* invalid argument                                             */
+    B200_ERR_NOMEM = -3,       /* device or pinned-host allocation failed                      */
+    B200_ERR_UNSUPPORTED = -4  /* curve / size not supported by this build                     */
+};
+
+enum b200_curve { B200_BN254 = 0, B200_BLS12_377 = 1 };
+
+#define B200_DIF 0 /* fft.DIF: natural order in, bit-reversed out */
+#define B200_DIT 1 /* fft.DIT: bit-reversed in, natural out       */
+
+/* ---- context ---------------------------------------------------------------------------------
+ * icicle has no context (implicit default device, icicle.go:31-130); cgo calls hop OS threads, so
+ * every entry point sets the device itself. */
+int b200_device_count(void);
+int b200_init(int device, b200_ctx **out);
+void b200_destroy(b200_ctx *ctx);
+const char *b200_last_error(const b200_ctx *ctx);
+/* Version string of the library build (arch, git describe when available). */
+const char *b200_version(void);
+
+/* Pinned host memory for the solver outputs (prove.go:119-125 W, A, B, C) so that the per-proof
+ * H2D copies run at PCIe speed; plain Go slices also work (pageable path). */
+void *b200_host_alloc(size_t bytes);
+void b200_host_free(void *p);
+
+/* Raw device buffers for the *_dev entry points (iciclegnark.CopyToDevice / FreeDevicePointer,
+ * icicle.go:44-65,231-278,416-418). */
+int b200_dev_alloc(b200_ctx *ctx, size_t bytes, void **dptr);
+int b200_dev_free(b200_ctx *ctx, void *dptr);
+int b200_h2d(b200_ctx *ctx, void *dst_dev, const void *src_host, size_t bytes);
+int b200_d2h(b200_ctx *ctx, void *dst_host, const void *src_dev, size_t bytes);
+int b200_sync(b200_ctx *ctx);
+
+/* ---- element-wise ----------------------------------------------------------------------------
+ * out[i] = a[i] * b[i] in Fr / Fp (gnark-crypto fr.Element.Mul / fp.Element.Mul); host buffers. */
+int b200_fr_vec_mul(b200_ctx *ctx, int curve, const uint64_t *a, const uint64_t *b, uint64_t *out, size_t n);
+int b200_fp_vec_mul(b200_ctx *ctx, int curve, const uint64_t *a, const uint64_t *b, uint64_t *out, size_t n);
+/* Roofline denominators measured on this device: register-resident mad.lo.cc/madc.hi.cc chains
+ * (32x32+64 multiply-accumulates per second, chip-wide) and the same for dependent-free plain
+ * 32-bit IMAD; sm_mhz = clock observed by the kernel (cycles / elapsed). */
+int b200_imad_peak(b200_ctx *ctx, double *mac32_per_s, double *imad32_per_s, double *sm_mhz);
+
+/* ---- NTT -------------------------------------------------------------------------------------
+ * fft.Domain.FFT / FFTInverse (prove.go:369-375,393); replaces iciclegnark.NttOnDevice /
+ * INttOnDevice (icicle.go:489,490,502) and GenerateTwiddleFactors (:68,:73).
+ *   inverse    0 = Domain.FFT, 1 = Domain.FFTInverse (scaled by 1/n)
+ *   decimation B200_DIF or B200_DIT (gnark-crypto semantics: no reordering pass is applied)
+ *   on_coset   fft.OnCoset(): evaluate on / interpolate from coset_gen * <generator>
+ *   generator  Domain.Generator (primitive 2^log_n-th root), coset_gen = Domain.FrMultiplicativeGen;
+ *              both are INPUTS taken from pk.Domain so the device never recomputes a convention.
+ * Twiddle and coset tables are built on the device once per (log_n, generator, coset_gen) and
+ * cached in the ctx. */
+int b200_ntt(b200_ctx *ctx, int curve, uint64_t *host_inout, unsigned log_n, int inverse, int decimation,
+             int on_coset, const uint64_t *generator, const uint64_t *coset_gen);
+/* Same on a device-resident vector; kernel_ms (optional) receives the CUDA-event time. */
+int b200_ntt_dev(b200_ctx *ctx, int curve, void *dev_inout, unsigned log_n, int inverse, int decimation,
+                 int on_coset, const uint64_t *generator, const uint64_t *coset_gen, float *kernel_ms);
+
+/* computeH (prove.go:353-396; icicle.go:453-513): a, b, c hold n_constraints elements (host),
+ * are zero-padded to n = 2^log_n on the device; h_out receives n elements in BIT-REVERSED order
+ * (prove.go:393 leaves them so; Setup bit-reverses pk.G1.Z to match, setup.go:265). */
+int b200_groth16_compute_h(b200_ctx *ctx, int curve, const uint64_t *a, const uint64_t *b, const uint64_t *c,
+                           size_t n_constraints, unsigned log_n, const uint64_t *generator,
+                           const uint64_t *coset_gen, uint64_t *h_out);
+
+/* ---- MSM -------------------------------------------------------------------------------------
+ * G1Jac.MultiExp / G2Jac.MultiExp (prove.go:201,214,234,244,290); replaces
+ * iciclegnark.MsmOnDevice / MsmG2OnDevice (icicle.go:302,315,332,355,382).  The MultiExpConfig
+ * (NbTasks) of the reference has no meaning on the device and is not part of the ABI. */
+int b200_msm_g1(b200_ctx *ctx, int curve, const uint64_t *scalars, const uint64_t *bases_affine, size_t n,
+                uint64_t *out_jac);
+int b200_msm_g2(b200_ctx *ctx, int curve, const uint64_t *scalars, const uint64_t *bases_affine, size_t n,
+                uint64_t *out_jac);
+/* Resident base sets (iciclegnark.CopyPointsToDevice / CopyG2PointsToDevice, icicle.go:88-126).
+ * group = 1 (G1) or 2 (G2). */
+int b200_bases_upload(b200_ctx *ctx, int curve, int group, const uint64_t *bases_affine, size_t n,
+                      b200_bases **out);
+int b200_bases_free(b200_ctx *ctx, b200_bases *bases);
+/* scalars on the host (copied in) ... */
+int b200_msm_resident(b200_ctx *ctx, const b200_bases *bases, const uint64_t *scalars, size_t n,
+                      uint64_t *out_jac);
+/* ... or already on the device; kernel_ms (optional) = CUDA-event time of the device work. */
+int b200_msm_dev(b200_ctx *ctx, const b200_bases *bases, const void *scalars_dev, size_t n, uint64_t *out_jac,
+                 float *kernel_ms);
+
+/* Host-side group helpers for combining per-GPU partial sums and for tests
+ * (G1Jac.AddAssign / FromJacobian semantics, prove.go:221,257-276,299). */
+int b200_g1_jac_add(const uint64_t *p_jac, const uint64_t *q_jac, uint64_t *out_jac);
+int b200_g2_jac_add(const uint64_t *p_jac, const uint64_t *q_jac, uint64_t *out_jac);
+int b200_g1_jac_to_affine(const uint64_t *p_jac, uint64_t *out_affine);
+int b200_g2_jac_to_affine(const uint64_t *p_jac, uint64_t *out_affine);
+
+/* Fixed-base batch scalar multiplication on the device: out[i] = scalars[i] * base (affine),
+ * curve.BatchScalarMultiplicationG1 / G2 (setup.go:251,308; prove.go:192).  group = 1 or 2.
+ * Used to build large synthetic proving keys without Go. */
+int b200_batch_scalar_mul(b200_ctx *ctx, int curve, int group, const uint64_t *base_affine,
+                          const uint64_t *scalars, size_t n, uint64_t *out_affine);
+
+/* ---- Groth16 ---------------------------------------------------------------------------------
+ * One-time residency of the proving key (setupDevicePointers, icicle.go:31-130).  All pointers are
+ * host pointers into the Go ProvingKey (setup.go:35-58); the descriptor is only read during the
+ * call.  With shard_count > 1 only the point range [i*len/shard_count, (i+1)*len/shard_count) of
+ * every base array is uploaded and proved on this ctx (MSM sharding by point range). */
+typedef struct b200_groth16_pk_desc {
+    unsigned log_n;               /* pk.Domain.Cardinality = 2^log_n                           */
+    const uint64_t *generator;    /* pk.Domain.Generator            (4 u64)                    */
+    const uint64_t *coset_gen;    /* pk.Domain.FrMultiplicativeGen  (4 u64)                    */
+    const uint64_t *g1_a; size_t n_a;    /* pk.G1.A (infinity points already stripped)        */
+    const uint64_t *g1_b; size_t n_b;    /* pk.G1.B                                            */
+    const uint64_t *g1_k; size_t n_k;    /* pk.G1.K (private wires)                            */
+    const uint64_t *g1_z; size_t n_z;    /* pk.G1.Z (bit-reversed, n-1 entries)                */
+    const uint64_t *g2_b; size_t n_g2b;  /* pk.G2.B                                            */
+    const uint8_t *infinity_a;    /* pk.InfinityA, one byte per wire (Go []bool)               */
+    const uint8_t *infinity_b;    /* pk.InfinityB                                              */
+    size_t n_wires;
+    size_t nb_public;             /* r1cs.GetNbPublicVariables() (K scalars = W[nb_public:])   */
+    int shard_index, shard_count; /* 0,1 for a single GPU                                      */
+} b200_groth16_pk_desc;
+
+int b200_groth16_pk_upload(b200_ctx *ctx, int curve, const b200_groth16_pk_desc *desc, b200_groth16_pk **out);
+int b200_groth16_pk_free(b200_ctx *ctx, b200_groth16_pk *pk);
+
+/* Per-stage device times in milliseconds (CUDA events on the ctx stream). */
+typedef struct b200_timings {
+    float h2d_ms, compute_h_ms, msm_a_ms, msm_b1_ms, msm_k_ms, msm_z_ms, msm_b2_ms, total_ms;
+} b200_timings;
+
+/* The five MultiExp results BEFORE the alpha/beta/delta/r/s fix-ups, which stay in Go
+ * (prove.go:206-207,219-221,248-271,294-299). */
+typedef struct b200_groth16_out {
+    uint64_t ar[12];    /* MSM(pk.G1.A, wireValuesA)       prove.go:214 */
+    uint64_t bs1[12];   /* MSM(pk.G1.B, wireValuesB)       prove.go:201 */
+    uint64_t krs[12];   /* MSM(pk.G1.K, W[nb_public:])     prove.go:244 */
+    uint64_t krs2[12];  /* MSM(pk.G1.Z, h[:n-1])           prove.go:234 */
+    uint64_t bs2[24];   /* MSM(pk.G2.B, wireValuesB)       prove.go:290 */
+} b200_groth16_out;
+
+/* computeH + wire filtering + the five MSMs on the device (prove.go:139-175,199-301;
+ * icicle.go:196-393).  a, b, c: solver outputs, n_constraints elements each (host); w: full wire
+ * vector, n_wires elements (host).  k_remove (optional, sorted ascending, indices relative to
+ * W[nb_public:]) lists committed wires to drop from the K scalars (prove.go:238-242).
+ * For a sharded pk the outputs are this shard's partial sums. */
+int b200_groth16_prove_core(b200_ctx *ctx, const b200_groth16_pk *pk, const uint64_t *a, const uint64_t *b,
+                            const uint64_t *c, size_t n_constraints, const uint64_t *w,
+                            const uint32_t *k_remove, size_t n_remove, b200_groth16_out *out,
+                            b200_timings *timings);
+
+/* Host mirror of groth16_bn254.Prove's tail (prove.go:178-321) for callers without Go: applies
+ * the fix-ups to the five MSM results with the given blinding scalars r, s (Montgomery Fr) and
+ * the key's alpha/beta/delta points, and returns the affine proof (Ar: 8 u64, Bs: 16 u64,
+ * Krs: 8 u64).  vk-side points are host pointers: g1_alpha, g1_beta, g1_delta (8 u64 each),
+ * g2_beta, g2_delta (16 u64 each). */
+int b200_groth16_finalize(const b200_groth16_out *msm, const uint64_t *r, const uint64_t *s,
+                          const uint64_t *g1_alpha, const uint64_t *g1_beta, const uint64_t *g1_delta,
+                          const uint64_t *g2_beta, const uint64_t *g2_delta, uint64_t *ar_affine,
+                          uint64_t *bs_affine, uint64_t *krs_affine);
+
+/* Proof.WriteTo without commitments (marshal.go:41-66): compressed Ar | Bs | Krs | u32 0 | Pok=inf.
+ * out must hold 164 bytes; returns the number of bytes written or a negative status. */
+int b200_groth16_proof_bytes(const uint64_t *ar_affine, const uint64_t *bs_affine, const uint64_t *krs_affine,
+                             uint8_t *out, size_t out_cap);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200PROVER_H */

@@ -1,0 +1,331 @@
+// extern "C" surface of libb200prover.so (declared in include/b200prover.h).  Thin: argument
+// checks, host<->device staging, and calls into ntt.cu / msm_g*.cu / groth16.cu / misc.cu.
+// No CPU fallback exists anywhere below this file: without a CUDA device b200_init fails.
+#include <cstdlib>
+#include "groth16_host.cuh"
+#include "misc_host.cuh"
+
+using namespace b200;
+
+struct b200_bases {
+    int group = 1;
+    size_t n = 0;
+    DevBuf pts;
+};
+
+namespace {
+thread_local std::string g_init_error;
+
+int set_device(b200_ctx* ctx) {
+    cudaError_t e = cudaSetDevice(ctx->device);
+    if (e != cudaSuccess) return ctx->fail(B200_ERR_CUDA, "cudaSetDevice", cudaGetErrorString(e));
+    return B200_OK;
+}
+int check_curve(b200_ctx* ctx, int curve) {
+    if (curve != B200_BN254) return ctx->fail(B200_ERR_UNSUPPORTED, "only BN254 is built into this library");
+    return B200_OK;
+}
+#define B2_ENTER(ctx, curve)                   \
+    if (!(ctx)) return B200_ERR_ARG;           \
+    B2_TRY(set_device(ctx));                   \
+    B2_TRY(check_curve(ctx, curve))
+}  // namespace
+
+extern "C" {
+
+const char* b200_version(void) { return "b200prover 0.1 (sm_100a, BN254)"; }
+
+int b200_device_count(void) {
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); return 0; }
+    return n;
+}
+
+int b200_init(int device, b200_ctx** out) {
+    if (!out) return B200_ERR_ARG;
+    *out = nullptr;
+    int n = 0;
+    cudaError_t e = cudaGetDeviceCount(&n);
+    if (e != cudaSuccess || n == 0 || device < 0 || device >= n) {
+        g_init_error = e != cudaSuccess ? cudaGetErrorString(e) : "no such CUDA device";
+        cudaGetLastError();
+        return B200_ERR_CUDA;
+    }
+    if (cudaSetDevice(device) != cudaSuccess) return B200_ERR_CUDA;
+    b200_ctx* ctx = new b200_ctx();
+    ctx->device = device;
+    cudaDeviceProp prop;
+    if (cudaGetDeviceProperties(&prop, device) != cudaSuccess) { delete ctx; return B200_ERR_CUDA; }
+    ctx->sm_count = prop.multiProcessorCount;
+    if (cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking) != cudaSuccess ||
+        cudaEventCreate(&ctx->ev0) != cudaSuccess || cudaEventCreate(&ctx->ev1) != cudaSuccess) {
+        delete ctx;
+        return B200_ERR_CUDA;
+    }
+    const char* c = getenv("B200_MSM_C");
+    if (c && *c) { int v = atoi(c); if (v >= 4 && v <= 24) ctx->msm_c_override = v; }
+    *out = ctx;
+    return B200_OK;
+}
+
+void b200_destroy(b200_ctx* ctx) {
+    if (!ctx) return;
+    cudaSetDevice(ctx->device);
+    cudaStreamSynchronize(ctx->stream);
+    ntt_domain_free_all(ctx);
+    if (ctx->scratch) cudaFree(ctx->scratch);
+    cudaEventDestroy(ctx->ev0);
+    cudaEventDestroy(ctx->ev1);
+    cudaStreamDestroy(ctx->stream);
+    delete ctx;
+}
+
+const char* b200_last_error(const b200_ctx* ctx) { return ctx ? ctx->err.c_str() : g_init_error.c_str(); }
+
+void* b200_host_alloc(size_t bytes) {
+    void* p = nullptr;
+    if (cudaMallocHost(&p, bytes ? bytes : 1) != cudaSuccess) { cudaGetLastError(); return nullptr; }
+    return p;
+}
+void b200_host_free(void* p) { if (p) cudaFreeHost(p); }
+
+int b200_dev_alloc(b200_ctx* ctx, size_t bytes, void** dptr) {
+    B2_ENTER(ctx, B200_BN254);
+    if (!dptr) return ctx->fail(B200_ERR_ARG, "null out pointer");
+    B2_CUDA(ctx, cudaMalloc(dptr, bytes ? bytes : 16));
+    return B200_OK;
+}
+int b200_dev_free(b200_ctx* ctx, void* dptr) {
+    B2_ENTER(ctx, B200_BN254);
+    B2_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    B2_CUDA(ctx, cudaFree(dptr));
+    return B200_OK;
+}
+int b200_h2d(b200_ctx* ctx, void* dst, const void* src, size_t bytes) {
+    B2_ENTER(ctx, B200_BN254);
+    B2_CUDA(ctx, cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, ctx->stream));
+    B2_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return B200_OK;
+}
+int b200_d2h(b200_ctx* ctx, void* dst, const void* src, size_t bytes) {
+    B2_ENTER(ctx, B200_BN254);
+    B2_CUDA(ctx, cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToHost, ctx->stream));
+    B2_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return B200_OK;
+}
+int b200_sync(b200_ctx* ctx) {
+    B2_ENTER(ctx, B200_BN254);
+    B2_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return B200_OK;
+}
+
+// ---- element-wise ------------------------------------------------------------------------
+static int vec_mul_host(b200_ctx* ctx, int fr, const uint64_t* a, const uint64_t* b, uint64_t* out, size_t n) {
+    if (n == 0) return B200_OK;
+    if (!a || !b || !out) return ctx->fail(B200_ERR_ARG, "null vector");
+    DevBuf da, db;
+    B2_CUDA(ctx, da.alloc(n * 32));
+    B2_CUDA(ctx, db.alloc(n * 32));
+    B2_CUDA(ctx, cudaMemcpyAsync(da.p, a, n * 32, cudaMemcpyHostToDevice, ctx->stream));
+    B2_CUDA(ctx, cudaMemcpyAsync(db.p, b, n * 32, cudaMemcpyHostToDevice, ctx->stream));
+    if (fr) B2_TRY(vec_mul_fr(ctx, da.as<Fr>(), db.as<Fr>(), da.as<Fr>(), n));
+    else B2_TRY(vec_mul_fp(ctx, da.as<Fp>(), db.as<Fp>(), da.as<Fp>(), n));
+    B2_CUDA(ctx, cudaMemcpyAsync(out, da.p, n * 32, cudaMemcpyDeviceToHost, ctx->stream));
+    B2_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return B200_OK;
+}
+int b200_fr_vec_mul(b200_ctx* ctx, int curve, const uint64_t* a, const uint64_t* b, uint64_t* out, size_t n) {
+    B2_ENTER(ctx, curve);
+    return vec_mul_host(ctx, 1, a, b, out, n);
+}
+int b200_fp_vec_mul(b200_ctx* ctx, int curve, const uint64_t* a, const uint64_t* b, uint64_t* out, size_t n) {
+    B2_ENTER(ctx, curve);
+    return vec_mul_host(ctx, 0, a, b, out, n);
+}
+int b200_imad_peak(b200_ctx* ctx, double* mac32_per_s, double* imad32_per_s, double* sm_mhz) {
+    B2_ENTER(ctx, B200_BN254);
+    return imad_peak(ctx, mac32_per_s, imad32_per_s, sm_mhz);
+}
+
+// ---- NTT ---------------------------------------------------------------------------------
+static int get_domain(b200_ctx* ctx, unsigned log_n, const uint64_t* generator, const uint64_t* coset_gen, NttDomain** d) {
+    if (!generator) return ctx->fail(B200_ERR_ARG, "generator is required");
+    Fr gen, coset;
+    memcpy(gen.l, generator, 32);
+    if (coset_gen) memcpy(coset.l, coset_gen, 32); else coset = Fr::one();
+    return ntt_domain_get(ctx, log_n, gen, coset, d);
+}
+
+int b200_ntt_dev(b200_ctx* ctx, int curve, void* dev_inout, unsigned log_n, int inverse, int decimation, int on_coset,
+                 const uint64_t* generator, const uint64_t* coset_gen, float* kernel_ms) {
+    B2_ENTER(ctx, curve);
+    if (!dev_inout) return ctx->fail(B200_ERR_ARG, "null vector");
+    if (decimation != B200_DIF && decimation != B200_DIT) return ctx->fail(B200_ERR_ARG, "bad decimation");
+    if (on_coset && !coset_gen) return ctx->fail(B200_ERR_ARG, "coset_gen is required with on_coset");
+    NttDomain* d;
+    B2_TRY(get_domain(ctx, log_n, generator, coset_gen, &d));
+    if (on_coset) {  // build the table outside the timed region
+        const Fr* t;
+        NttDomain::Table id = !inverse ? (decimation ? NttDomain::COSET_BR : NttDomain::COSET_NAT)
+                                       : (decimation ? NttDomain::COSETINV_NAT : NttDomain::COSETINV_BR);
+        B2_TRY(ntt_domain_table(ctx, d, id, &t));
+    }
+    B2_CUDA(ctx, cudaEventRecord(ctx->ev0, ctx->stream));
+    B2_TRY(ntt_gnark(ctx, d, (Fr*)dev_inout, inverse, decimation, on_coset));
+    B2_CUDA(ctx, cudaEventRecord(ctx->ev1, ctx->stream));
+    B2_CUDA(ctx, cudaEventSynchronize(ctx->ev1));
+    if (kernel_ms) B2_CUDA(ctx, cudaEventElapsedTime(kernel_ms, ctx->ev0, ctx->ev1));
+    return B200_OK;
+}
+
+int b200_ntt(b200_ctx* ctx, int curve, uint64_t* host_inout, unsigned log_n, int inverse, int decimation, int on_coset,
+             const uint64_t* generator, const uint64_t* coset_gen) {
+    B2_ENTER(ctx, curve);
+    if (!host_inout) return ctx->fail(B200_ERR_ARG, "null vector");
+    if (log_n > 27) return ctx->fail(B200_ERR_UNSUPPORTED, "NTT size above 2^27");
+    const size_t bytes = ((size_t)1 << log_n) * sizeof(Fr);
+    DevBuf d;
+    B2_CUDA(ctx, d.alloc(bytes));
+    B2_CUDA(ctx, cudaMemcpyAsync(d.p, host_inout, bytes, cudaMemcpyHostToDevice, ctx->stream));
+    B2_TRY(b200_ntt_dev(ctx, curve, d.p, log_n, inverse, decimation, on_coset, generator, coset_gen, nullptr));
+    B2_CUDA(ctx, cudaMemcpyAsync(host_inout, d.p, bytes, cudaMemcpyDeviceToHost, ctx->stream));
+    B2_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return B200_OK;
+}
+
+int b200_groth16_compute_h(b200_ctx* ctx, int curve, const uint64_t* a, const uint64_t* b, const uint64_t* c,
+                           size_t n_constraints, unsigned log_n, const uint64_t* generator, const uint64_t* coset_gen,
+                           uint64_t* h_out) {
+    B2_ENTER(ctx, curve);
+    if (!a || !b || !c || !h_out || !coset_gen) return ctx->fail(B200_ERR_ARG, "null argument");
+    if (log_n > 27) return ctx->fail(B200_ERR_UNSUPPORTED, "NTT size above 2^27");
+    const size_t n = (size_t)1 << log_n;
+    if (n_constraints > n) return ctx->fail(B200_ERR_ARG, "more constraints than the domain holds");
+    NttDomain* d;
+    B2_TRY(get_domain(ctx, log_n, generator, coset_gen, &d));
+    DevBuf buf[3];
+    const uint64_t* src[3] = {a, b, c};
+    for (int i = 0; i < 3; ++i) {
+        B2_CUDA(ctx, buf[i].alloc(n * sizeof(Fr)));
+        B2_CUDA(ctx, cudaMemcpyAsync(buf[i].p, src[i], n_constraints * sizeof(Fr), cudaMemcpyHostToDevice, ctx->stream));
+        if (n > n_constraints)
+            B2_CUDA(ctx, cudaMemsetAsync(buf[i].as<Fr>() + n_constraints, 0, (n - n_constraints) * sizeof(Fr), ctx->stream));
+    }
+    B2_TRY(ntt_compute_h(ctx, d, buf[0].as<Fr>(), buf[1].as<Fr>(), buf[2].as<Fr>()));
+    B2_CUDA(ctx, cudaMemcpyAsync(h_out, buf[0].p, n * sizeof(Fr), cudaMemcpyDeviceToHost, ctx->stream));
+    B2_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return B200_OK;
+}
+
+// ---- MSM ---------------------------------------------------------------------------------
+int b200_bases_upload(b200_ctx* ctx, int curve, int group, const uint64_t* bases_affine, size_t n, b200_bases** out) {
+    B2_ENTER(ctx, curve);
+    if (!out || (n && !bases_affine)) return ctx->fail(B200_ERR_ARG, "null argument");
+    if (group != 1 && group != 2) return ctx->fail(B200_ERR_ARG, "group must be 1 or 2");
+    b200_bases* b = new b200_bases();
+    b->group = group;
+    b->n = n;
+    const size_t bytes = n * (group == 1 ? sizeof(G1Affine) : sizeof(G2Affine));
+    cudaError_t e = b->pts.alloc(bytes);
+    if (e == cudaSuccess && bytes) e = cudaMemcpyAsync(b->pts.p, bases_affine, bytes, cudaMemcpyHostToDevice, ctx->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
+    if (e != cudaSuccess) { delete b; return ctx->fail(B200_ERR_CUDA, "bases upload", cudaGetErrorString(e)); }
+    *out = b;
+    return B200_OK;
+}
+int b200_bases_free(b200_ctx* ctx, b200_bases* bases) {
+    B2_ENTER(ctx, B200_BN254);
+    B2_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    delete bases;
+    return B200_OK;
+}
+
+int b200_msm_dev(b200_ctx* ctx, const b200_bases* bases, const void* scalars_dev, size_t n, uint64_t* out_jac, float* kernel_ms) {
+    B2_ENTER(ctx, B200_BN254);
+    if (!bases || !out_jac || (n && !scalars_dev)) return ctx->fail(B200_ERR_ARG, "null argument");
+    if (n > bases->n) return ctx->fail(B200_ERR_ARG, "more scalars than resident bases");
+    B2_CUDA(ctx, cudaEventRecord(ctx->ev0, ctx->stream));
+    if (bases->group == 1) {
+        G1Jac r;
+        B2_TRY(msm_g1_run(ctx, bases->pts.as<G1Affine>(), (const Fr*)scalars_dev, nullptr, n, &r, nullptr));
+        memcpy(out_jac, &r, sizeof r);
+    } else {
+        G2Jac r;
+        B2_TRY(msm_g2_run(ctx, bases->pts.as<G2Affine>(), (const Fr*)scalars_dev, nullptr, n, &r, nullptr));
+        memcpy(out_jac, &r, sizeof r);
+    }
+    B2_CUDA(ctx, cudaEventRecord(ctx->ev1, ctx->stream));
+    B2_CUDA(ctx, cudaEventSynchronize(ctx->ev1));
+    if (kernel_ms) B2_CUDA(ctx, cudaEventElapsedTime(kernel_ms, ctx->ev0, ctx->ev1));
+    return B200_OK;
+}
+
+int b200_msm_resident(b200_ctx* ctx, const b200_bases* bases, const uint64_t* scalars, size_t n, uint64_t* out_jac) {
+    B2_ENTER(ctx, B200_BN254);
+    if (n && !scalars) return ctx->fail(B200_ERR_ARG, "null scalars");
+    DevBuf ds;
+    B2_CUDA(ctx, ds.alloc(n * sizeof(Fr)));
+    if (n) B2_CUDA(ctx, cudaMemcpyAsync(ds.p, scalars, n * sizeof(Fr), cudaMemcpyHostToDevice, ctx->stream));
+    return b200_msm_dev(ctx, bases, ds.p, n, out_jac, nullptr);
+}
+
+static int msm_host(b200_ctx* ctx, int curve, int group, const uint64_t* scalars, const uint64_t* bases_affine, size_t n, uint64_t* out_jac) {
+    B2_ENTER(ctx, curve);
+    if (!out_jac) return ctx->fail(B200_ERR_ARG, "null output");
+    b200_bases* b = nullptr;
+    B2_TRY(b200_bases_upload(ctx, curve, group, bases_affine, n, &b));
+    const int st = b200_msm_resident(ctx, b, scalars, n, out_jac);
+    cudaStreamSynchronize(ctx->stream);
+    delete b;
+    return st;
+}
+int b200_msm_g1(b200_ctx* ctx, int curve, const uint64_t* scalars, const uint64_t* bases_affine, size_t n, uint64_t* out_jac) {
+    return msm_host(ctx, curve, 1, scalars, bases_affine, n, out_jac);
+}
+int b200_msm_g2(b200_ctx* ctx, int curve, const uint64_t* scalars, const uint64_t* bases_affine, size_t n, uint64_t* out_jac) {
+    return msm_host(ctx, curve, 2, scalars, bases_affine, n, out_jac);
+}
+
+int b200_batch_scalar_mul(b200_ctx* ctx, int curve, int group, const uint64_t* base_affine, const uint64_t* scalars,
+                          size_t n, uint64_t* out_affine) {
+    B2_ENTER(ctx, curve);
+    if (!base_affine || (n && (!scalars || !out_affine))) return ctx->fail(B200_ERR_ARG, "null argument");
+    if (group != 1 && group != 2) return ctx->fail(B200_ERR_ARG, "group must be 1 or 2");
+    const size_t psz = group == 1 ? sizeof(G1Affine) : sizeof(G2Affine);
+    DevBuf ds, dout;
+    B2_CUDA(ctx, ds.alloc(n * sizeof(Fr)));
+    B2_CUDA(ctx, dout.alloc(n * psz));
+    if (n) B2_CUDA(ctx, cudaMemcpyAsync(ds.p, scalars, n * sizeof(Fr), cudaMemcpyHostToDevice, ctx->stream));
+    if (group == 1) {
+        G1Affine b; memcpy(&b, base_affine, sizeof b);
+        B2_TRY(batch_mul_g1(ctx, b, ds.as<Fr>(), n, dout.as<G1Affine>()));
+    } else {
+        G2Affine b; memcpy(&b, base_affine, sizeof b);
+        B2_TRY(batch_mul_g2(ctx, b, ds.as<Fr>(), n, dout.as<G2Affine>()));
+    }
+    if (n) B2_CUDA(ctx, cudaMemcpyAsync(out_affine, dout.p, n * psz, cudaMemcpyDeviceToHost, ctx->stream));
+    B2_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return B200_OK;
+}
+
+// ---- Groth16 -----------------------------------------------------------------------------
+int b200_groth16_pk_upload(b200_ctx* ctx, int curve, const b200_groth16_pk_desc* desc, b200_groth16_pk** out) {
+    B2_ENTER(ctx, curve);
+    return groth16_pk_upload(ctx, desc, out);
+}
+int b200_groth16_pk_free(b200_ctx* ctx, b200_groth16_pk* pk) {
+    B2_ENTER(ctx, B200_BN254);
+    B2_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    delete pk;
+    return B200_OK;
+}
+int b200_groth16_prove_core(b200_ctx* ctx, const b200_groth16_pk* pk, const uint64_t* a, const uint64_t* b,
+                            const uint64_t* c, size_t n_constraints, const uint64_t* w, const uint32_t* k_remove,
+                            size_t n_remove, b200_groth16_out* out, b200_timings* timings) {
+    B2_ENTER(ctx, B200_BN254);
+    if (!pk || !out || !w || (n_constraints && (!a || !b || !c)) || (n_remove && !k_remove))
+        return ctx->fail(B200_ERR_ARG, "null argument");
+    return groth16_prove_core(ctx, pk, a, b, c, n_constraints, w, k_remove, n_remove, out, timings);
+}
+
+}  // extern "C"

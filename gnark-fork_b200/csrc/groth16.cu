@@ -1,0 +1,177 @@
+// Groth16 prover core on the device: resident proving key, computeH, wire filtering and the five
+// MultiExp of /root/reference/backend/groth16/bn254/prove.go:139-175,199-301 (device shape modelled
+// on /root/reference/backend/groth16/bn254/icicle/icicle.go:31-130,196-393), plus the host-side
+// fix-ups (prove.go:178-321) and Proof.WriteTo (marshal.go:41-66) for callers without Go.
+#include <algorithm>
+#include "groth16_host.cuh"
+
+namespace b200 {
+
+static void shard_range(size_t len, int idx, int cnt, size_t* lo, size_t* hi) {
+    *lo = len * (size_t)idx / (size_t)cnt;
+    *hi = len * (size_t)(idx + 1) / (size_t)cnt;
+}
+
+template <class T>
+static int upload_range(b200_ctx* ctx, DevBuf& dst, const uint64_t* host, size_t lo, size_t hi) {
+    const size_t cnt = hi - lo;
+    B2_CUDA(ctx, dst.alloc(cnt * sizeof(T)));
+    if (cnt)
+        B2_CUDA(ctx, cudaMemcpyAsync(dst.p, reinterpret_cast<const char*>(host) + lo * sizeof(T), cnt * sizeof(T),
+                                     cudaMemcpyHostToDevice, ctx->stream));
+    return B200_OK;
+}
+
+// wire indices whose base is not the point at infinity, positions [lo, hi) of that list
+static int upload_wire_map(b200_ctx* ctx, DevBuf& dst, const uint8_t* infinity, size_t n_wires, size_t expect,
+                           size_t lo, size_t hi) {
+    std::vector<uint32_t> map;
+    map.reserve(expect);
+    for (size_t i = 0; i < n_wires; ++i)
+        if (!infinity[i]) map.push_back((uint32_t)i);
+    if (map.size() != expect) return ctx->fail(B200_ERR_ARG, "infinity bitmap does not match the base count");
+    B2_CUDA(ctx, dst.alloc((hi - lo) * 4));
+    if (hi > lo) B2_CUDA(ctx, cudaMemcpy(dst.p, map.data() + lo, (hi - lo) * 4, cudaMemcpyHostToDevice));
+    return B200_OK;
+}
+
+int groth16_pk_upload(b200_ctx* ctx, const b200_groth16_pk_desc* d, b200_groth16_pk** out) {
+    if (!d || !out || !d->generator || !d->coset_gen) return ctx->fail(B200_ERR_ARG, "null descriptor field");
+    if (d->shard_count < 1 || d->shard_index < 0 || d->shard_index >= d->shard_count)
+        return ctx->fail(B200_ERR_ARG, "bad shard");
+    if (d->n_wires < d->nb_public || d->n_k > d->n_wires - d->nb_public)
+        return ctx->fail(B200_ERR_ARG, "K longer than the private wires");
+    if (d->n_z > ((size_t)1 << d->log_n)) return ctx->fail(B200_ERR_ARG, "Z longer than the domain");
+    if (d->n_g2b != d->n_b) return ctx->fail(B200_ERR_ARG, "G1.B and G2.B differ in length");
+    b200_groth16_pk* pk = new b200_groth16_pk();
+    pk->log_n = d->log_n;
+    pk->n_wires = d->n_wires;
+    pk->nb_public = d->nb_public;
+    pk->full_n_k = d->n_k;
+    Fr gen, coset;
+    memcpy(gen.l, d->generator, 32);
+    memcpy(coset.l, d->coset_gen, 32);
+    int st = ntt_domain_get(ctx, d->log_n, gen, coset, &pk->dom);
+    const int si = d->shard_index, sc = d->shard_count;
+    size_t lo, hi;
+    if (st == B200_OK) { shard_range(d->n_a, si, sc, &lo, &hi); pk->n_a = hi - lo;
+        st = upload_range<G1Affine>(ctx, pk->A, d->g1_a, lo, hi);
+        if (st == B200_OK) st = upload_wire_map(ctx, pk->mapA, d->infinity_a, d->n_wires, d->n_a, lo, hi); }
+    if (st == B200_OK) { shard_range(d->n_b, si, sc, &lo, &hi); pk->n_b = hi - lo;
+        st = upload_range<G1Affine>(ctx, pk->B, d->g1_b, lo, hi);
+        if (st == B200_OK) st = upload_range<G2Affine>(ctx, pk->G2B, d->g2_b, lo, hi);
+        if (st == B200_OK) st = upload_wire_map(ctx, pk->mapB, d->infinity_b, d->n_wires, d->n_b, lo, hi); }
+    if (st == B200_OK) { shard_range(d->n_k, si, sc, &lo, &hi); pk->n_k = hi - lo; pk->k_lo = lo;
+        st = upload_range<G1Affine>(ctx, pk->K, d->g1_k, lo, hi); }
+    if (st == B200_OK) { shard_range(d->n_z, si, sc, &lo, &hi); pk->n_z = hi - lo; pk->z_lo = lo;
+        st = upload_range<G1Affine>(ctx, pk->Z, d->g1_z, lo, hi); }
+    // build the computeH tables now so the first proof does not pay for them
+    const Fr* t;
+    if (st == B200_OK) st = ntt_domain_table(ctx, pk->dom, NttDomain::H_A, &t);
+    if (st == B200_OK) st = ntt_domain_table(ctx, pk->dom, NttDomain::H_BC, &t);
+    if (st == B200_OK) st = ntt_domain_table(ctx, pk->dom, NttDomain::COSETINV_BR, &t);
+    if (st == B200_OK && cudaStreamSynchronize(ctx->stream) != cudaSuccess)
+        st = ctx->fail(B200_ERR_CUDA, "pk upload", cudaGetErrorString(cudaGetLastError()));
+    if (st != B200_OK) { delete pk; return st; }
+    *out = pk;
+    return B200_OK;
+}
+
+static float ev_ms(cudaEvent_t a, cudaEvent_t b) {
+    float ms = 0.f;
+    cudaEventElapsedTime(&ms, a, b);
+    return ms;
+}
+
+int groth16_prove_core(b200_ctx* ctx, const b200_groth16_pk* pk, const uint64_t* a, const uint64_t* b,
+                       const uint64_t* c, size_t n_constraints, const uint64_t* w, const uint32_t* k_remove,
+                       size_t n_remove, b200_groth16_out* out, b200_timings* tm) {
+    const size_t n = (size_t)1 << pk->log_n;
+    if (n_constraints > n) return ctx->fail(B200_ERR_ARG, "more constraints than the domain holds");
+    if (n_remove && pk->full_n_k + n_remove != pk->n_wires - pk->nb_public)
+        return ctx->fail(B200_ERR_ARG, "k_remove does not match len(pk.G1.K)");
+    // workspace: a, b, c (n Fr each), W, optional K map, MSM scratch
+    size_t msm_ws = 0;
+    msm_ws = std::max(msm_ws, msm_workspace_bytes(pk->n_a, 1, ctx->msm_c_override));
+    msm_ws = std::max(msm_ws, msm_workspace_bytes(pk->n_b, 1, ctx->msm_c_override));
+    msm_ws = std::max(msm_ws, msm_workspace_bytes(pk->n_k, 1, ctx->msm_c_override));
+    msm_ws = std::max(msm_ws, msm_workspace_bytes(pk->n_z, 1, ctx->msm_c_override));
+    msm_ws = std::max(msm_ws, msm_workspace_bytes(pk->n_b, 2, ctx->msm_c_override));
+    Arena ar;
+    const size_t o_a = ar.off; ar.take(n * sizeof(Fr));
+    const size_t o_b = ar.off; ar.take(n * sizeof(Fr));
+    const size_t o_c = ar.off; ar.take(n * sizeof(Fr));
+    const size_t o_w = ar.off; ar.take(pk->n_wires * sizeof(Fr));
+    const size_t o_kmap = ar.off; ar.take(n_remove ? pk->n_k * 4 : 0);
+    const size_t o_msm = ar.off; ar.take(msm_ws);
+    B2_TRY(ctx_reserve(ctx, ar.off));
+    char* base = (char*)ctx->scratch;
+    Fr* d_a = (Fr*)(base + o_a); Fr* d_b = (Fr*)(base + o_b); Fr* d_c = (Fr*)(base + o_c);
+    Fr* d_w = (Fr*)(base + o_w);
+    uint32_t* d_kmap = n_remove ? (uint32_t*)(base + o_kmap) : nullptr;
+    void* ws = base + o_msm;
+    cudaStream_t st = ctx->stream;
+
+    cudaEvent_t ev[9];
+    for (auto& e : ev) B2_CUDA(ctx, cudaEventCreate(&e));
+    struct EvGuard { cudaEvent_t* e; ~EvGuard() { for (int i = 0; i < 9; ++i) cudaEventDestroy(e[i]); } } guard{ev};
+
+    B2_CUDA(ctx, cudaEventRecord(ev[0], st));
+    const uint64_t* src[3] = {a, b, c};
+    Fr* dst[3] = {d_a, d_b, d_c};
+    for (int i = 0; i < 3; ++i) {
+        if (n_constraints) B2_CUDA(ctx, cudaMemcpyAsync(dst[i], src[i], n_constraints * sizeof(Fr), cudaMemcpyHostToDevice, st));
+        if (n > n_constraints) B2_CUDA(ctx, cudaMemsetAsync(dst[i] + n_constraints, 0, (n - n_constraints) * sizeof(Fr), st));
+    }
+    B2_CUDA(ctx, cudaMemcpyAsync(d_w, w, pk->n_wires * sizeof(Fr), cudaMemcpyHostToDevice, st));
+    if (n_remove) {
+        // prove.go:238-242: K scalars are W[nb_public:] minus the committed wires
+        std::vector<uint32_t> map;
+        map.reserve(pk->full_n_k);
+        size_t r = 0;
+        for (size_t i = 0; i < pk->n_wires - pk->nb_public; ++i) {
+            if (r < n_remove && k_remove[r] == i) { ++r; continue; }
+            map.push_back((uint32_t)(pk->nb_public + i));
+        }
+        if (map.size() != pk->full_n_k) return ctx->fail(B200_ERR_ARG, "k_remove must be sorted and unique");
+        B2_CUDA(ctx, cudaMemcpyAsync(d_kmap, map.data() + pk->k_lo, pk->n_k * 4, cudaMemcpyHostToDevice, st));
+        B2_CUDA(ctx, cudaStreamSynchronize(st));  // `map` dies at scope exit
+    }
+    B2_CUDA(ctx, cudaEventRecord(ev[1], st));
+    B2_TRY(ntt_compute_h(ctx, pk->dom, d_a, d_b, d_c));
+    B2_CUDA(ctx, cudaEventRecord(ev[2], st));
+
+    G1Jac ja, jb1, jk, jz;
+    G2Jac jb2;
+    B2_TRY(msm_g1_run(ctx, pk->A.as<G1Affine>(), d_w, pk->mapA.as<uint32_t>(), pk->n_a, &ja, ws));
+    B2_CUDA(ctx, cudaEventRecord(ev[3], st));
+    B2_TRY(msm_g1_run(ctx, pk->B.as<G1Affine>(), d_w, pk->mapB.as<uint32_t>(), pk->n_b, &jb1, ws));
+    B2_CUDA(ctx, cudaEventRecord(ev[4], st));
+    if (d_kmap) B2_TRY(msm_g1_run(ctx, pk->K.as<G1Affine>(), d_w, d_kmap, pk->n_k, &jk, ws));
+    else B2_TRY(msm_g1_run(ctx, pk->K.as<G1Affine>(), d_w + pk->nb_public + pk->k_lo, nullptr, pk->n_k, &jk, ws));
+    B2_CUDA(ctx, cudaEventRecord(ev[5], st));
+    B2_TRY(msm_g1_run(ctx, pk->Z.as<G1Affine>(), d_a + pk->z_lo, nullptr, pk->n_z, &jz, ws));
+    B2_CUDA(ctx, cudaEventRecord(ev[6], st));
+    B2_TRY(msm_g2_run(ctx, pk->G2B.as<G2Affine>(), d_w, pk->mapB.as<uint32_t>(), pk->n_b, &jb2, ws));
+    B2_CUDA(ctx, cudaEventRecord(ev[7], st));
+    B2_CUDA(ctx, cudaStreamSynchronize(st));
+
+    memcpy(out->ar, &ja, sizeof ja);
+    memcpy(out->bs1, &jb1, sizeof jb1);
+    memcpy(out->krs, &jk, sizeof jk);
+    memcpy(out->krs2, &jz, sizeof jz);
+    memcpy(out->bs2, &jb2, sizeof jb2);
+    if (tm) {
+        tm->h2d_ms = ev_ms(ev[0], ev[1]);
+        tm->compute_h_ms = ev_ms(ev[1], ev[2]);
+        tm->msm_a_ms = ev_ms(ev[2], ev[3]);
+        tm->msm_b1_ms = ev_ms(ev[3], ev[4]);
+        tm->msm_k_ms = ev_ms(ev[4], ev[5]);
+        tm->msm_z_ms = ev_ms(ev[5], ev[6]);
+        tm->msm_b2_ms = ev_ms(ev[6], ev[7]);
+        tm->total_ms = ev_ms(ev[0], ev[7]);
+    }
+    return B200_OK;
+}
+
+}  // namespace b200

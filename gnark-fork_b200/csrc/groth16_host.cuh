@@ -1,0 +1,24 @@
+// Resident Groth16 proving key and the host entry points of groth16.cu / host_group.cu.
+#pragma once
+#include "ntt_host.cuh"
+#include "msm_host.cuh"
+
+// Device mirror of groth16_bn254.ProvingKey (setup.go:35-58) -- the analogue of the icicle
+// deviceInfo (icicle/provingkey.go:10-28).  With shard_count > 1 it holds one point range.
+struct b200_groth16_pk {
+    unsigned log_n = 0;
+    size_t n_wires = 0, nb_public = 0;
+    b200::NttDomain* dom = nullptr;  // owned by the ctx cache
+    b200::DevBuf A, B, K, Z, G2B;    // affine bases of this shard
+    b200::DevBuf mapA, mapB;         // wire index of each A / B base (prove.go:154-175 as a gather)
+    size_t n_a = 0, n_b = 0, n_k = 0, n_z = 0;  // shard-local counts
+    size_t k_lo = 0, z_lo = 0;       // first K / Z index of this shard
+    size_t full_n_k = 0;             // len(pk.G1.K)
+};
+
+namespace b200 {
+int groth16_pk_upload(b200_ctx* ctx, const b200_groth16_pk_desc* d, b200_groth16_pk** out);
+int groth16_prove_core(b200_ctx* ctx, const b200_groth16_pk* pk, const uint64_t* a, const uint64_t* b,
+                       const uint64_t* c, size_t n_constraints, const uint64_t* w, const uint32_t* k_remove,
+                       size_t n_remove, b200_groth16_out* out, b200_timings* tm);
+}  // namespace b200

@@ -1,0 +1,156 @@
+// Host-side group arithmetic of the C ABI: partial-sum combination, FromJacobian, the Groth16
+// fix-ups of /root/reference/backend/groth16/bn254/prove.go:178-321 and Proof.WriteTo
+// (/root/reference/backend/groth16/bn254/marshal.go:41-66).  Pure host code (the portable path of
+// field.cuh); O(1) work per proof, which the reference also keeps on the CPU (icicle.go:306-391).
+#include "common.cuh"
+
+using namespace b200;
+
+namespace {
+
+template <class F>
+XYZZ<F> scalar_mul(const XYZZ<F>& p, const Fr& k_mont) {
+    const Fr k = k_mont.from_mont();
+    XYZZ<F> acc = XYZZ<F>::inf();
+    for (int i = 255; i >= 0; --i) {
+        acc = acc.dbl();
+        if ((k.l[i >> 5] >> (i & 31)) & 1) acc.add(p);
+    }
+    return acc;
+}
+
+template <class F>
+int jac_add(const uint64_t* p, const uint64_t* q, uint64_t* out) {
+    if (!p || !q || !out) return B200_ERR_ARG;
+    Jac<F> a, b;
+    memcpy(&a, p, sizeof a);
+    memcpy(&b, q, sizeof b);
+    XYZZ<F> x = xyzz_from_jac(a);
+    x.add(xyzz_from_jac(b));
+    const Jac<F> r = x.to_jac();
+    memcpy(out, &r, sizeof r);
+    return B200_OK;
+}
+
+template <class F>
+int jac_aff(const uint64_t* p, uint64_t* out) {
+    if (!p || !out) return B200_ERR_ARG;
+    Jac<F> a;
+    memcpy(&a, p, sizeof a);
+    const Affine<F> r = jac_to_affine(a);
+    memcpy(out, &r, sizeof r);
+    return B200_OK;
+}
+
+template <class F>
+XYZZ<F> load_jac(const uint64_t* p) { Jac<F> a; memcpy(&a, p, sizeof a); return xyzz_from_jac(a); }
+template <class F>
+XYZZ<F> load_aff(const uint64_t* p) { Affine<F> a; memcpy(&a, p, sizeof a); return XYZZ<F>::from_affine(a); }
+
+// canonical big-endian bytes of an Fp element
+void fp_be(const Fp& x_mont, uint8_t* out32) {
+    const Fp x = x_mont.from_mont();
+    for (int i = 0; i < 8; ++i) {
+        const uint32_t v = x.l[7 - i];
+        out32[4 * i] = (uint8_t)(v >> 24); out32[4 * i + 1] = (uint8_t)(v >> 16);
+        out32[4 * i + 2] = (uint8_t)(v >> 8); out32[4 * i + 3] = (uint8_t)v;
+    }
+}
+// y > (p-1)/2  (gnark-crypto fp.Element.LexicographicallyLargest)
+bool lex_largest(const Fp& y_mont) {
+    const Fp y = y_mont.from_mont();
+    // (p-1)/2 limbs
+    uint32_t half[8];
+    uint32_t carry = 0;
+    for (int i = 7; i >= 0; --i) {
+        const uint32_t v = FpParams::p(i) - (i == 0 ? 1u : 0u);  // p is odd: p-1 only clears bit 0
+        half[i] = (v >> 1) | (carry << 31);
+        carry = v & 1u;
+    }
+    for (int i = 7; i >= 0; --i) {
+        if (y.l[i] != half[i]) return y.l[i] > half[i];
+    }
+    return false;
+}
+const uint8_t M_SMALLEST = 0x80, M_LARGEST = 0xC0, M_INFINITY = 0x40;
+
+void g1_compress(const G1Affine& p, uint8_t* out) {
+    if (p.is_inf()) { memset(out, 0, 32); out[0] = M_INFINITY; return; }
+    fp_be(p.x, out);
+    out[0] |= lex_largest(p.y) ? M_LARGEST : M_SMALLEST;
+}
+void g2_compress(const G2Affine& p, uint8_t* out) {
+    if (p.is_inf()) { memset(out, 0, 64); out[0] = M_INFINITY; return; }
+    fp_be(p.x.a1, out);
+    fp_be(p.x.a0, out + 32);
+    const bool largest = p.y.a1.is_zero() ? lex_largest(p.y.a0) : lex_largest(p.y.a1);
+    out[0] |= largest ? M_LARGEST : M_SMALLEST;
+}
+
+}  // namespace
+
+extern "C" {
+
+int b200_g1_jac_add(const uint64_t* p, const uint64_t* q, uint64_t* out) { return jac_add<Fp>(p, q, out); }
+int b200_g2_jac_add(const uint64_t* p, const uint64_t* q, uint64_t* out) { return jac_add<Fp2>(p, q, out); }
+int b200_g1_jac_to_affine(const uint64_t* p, uint64_t* out) { return jac_aff<Fp>(p, out); }
+int b200_g2_jac_to_affine(const uint64_t* p, uint64_t* out) { return jac_aff<Fp2>(p, out); }
+
+int b200_groth16_finalize(const b200_groth16_out* msm, const uint64_t* r, const uint64_t* s,
+                          const uint64_t* g1_alpha, const uint64_t* g1_beta, const uint64_t* g1_delta,
+                          const uint64_t* g2_beta, const uint64_t* g2_delta, uint64_t* ar_affine,
+                          uint64_t* bs_affine, uint64_t* krs_affine) {
+    if (!msm || !r || !s || !g1_alpha || !g1_beta || !g1_delta || !g2_beta || !g2_delta || !ar_affine ||
+        !bs_affine || !krs_affine)
+        return B200_ERR_ARG;
+    Fr fr_r, fr_s;
+    memcpy(fr_r.l, r, 32);
+    memcpy(fr_s.l, s, 32);
+    const Fr kr = (fr_r * fr_s).neg();  // _kr = -(r*s), prove.go:187-189
+    const G1XYZZ delta = load_aff<Fp>(g1_delta);
+    // deltas = BatchScalarMultiplicationG1(&pk.G1.Delta, {r, s, kr}), prove.go:192
+    const G1XYZZ d_r = scalar_mul(delta, fr_r), d_s = scalar_mul(delta, fr_s), d_kr = scalar_mul(delta, kr);
+    // ar = MSM_A + alpha + r*delta, prove.go:219-220
+    G1XYZZ ar = load_jac<Fp>(msm->ar);
+    ar.add(load_aff<Fp>(g1_alpha));
+    ar.add(d_r);
+    // bs1 = MSM_B + beta + s*delta, prove.go:206-207
+    G1XYZZ bs1 = load_jac<Fp>(msm->bs1);
+    bs1.add(load_aff<Fp>(g1_beta));
+    bs1.add(d_s);
+    // krs = MSM_K + kr*delta + MSM_Z + s*ar + r*bs1, prove.go:248-271
+    G1XYZZ krs = load_jac<Fp>(msm->krs);
+    krs.add(d_kr);
+    krs.add(load_jac<Fp>(msm->krs2));
+    krs.add(scalar_mul(ar, fr_s));
+    krs.add(scalar_mul(bs1, fr_r));
+    // Bs = MSM_B2 + s*delta2 + beta2, prove.go:294-297
+    G2XYZZ bs = load_jac<Fp2>(msm->bs2);
+    bs.add(scalar_mul(load_aff<Fp2>(g2_delta), fr_s));
+    bs.add(load_aff<Fp2>(g2_beta));
+    const G1Affine a_aff = ar.to_affine(), k_aff = krs.to_affine();
+    const G2Affine b_aff = bs.to_affine();
+    memcpy(ar_affine, &a_aff, sizeof a_aff);
+    memcpy(bs_affine, &b_aff, sizeof b_aff);
+    memcpy(krs_affine, &k_aff, sizeof k_aff);
+    return B200_OK;
+}
+
+int b200_groth16_proof_bytes(const uint64_t* ar_affine, const uint64_t* bs_affine, const uint64_t* krs_affine,
+                             uint8_t* out, size_t out_cap) {
+    if (!ar_affine || !bs_affine || !krs_affine || !out) return B200_ERR_ARG;
+    if (out_cap < 164) return B200_ERR_ARG;
+    G1Affine ar, krs;
+    G2Affine bs;
+    memcpy(&ar, ar_affine, sizeof ar);
+    memcpy(&bs, bs_affine, sizeof bs);
+    memcpy(&krs, krs_affine, sizeof krs);
+    g1_compress(ar, out);          // marshal.go:49
+    g2_compress(bs, out + 32);     // marshal.go:52
+    g1_compress(krs, out + 96);    // marshal.go:55
+    memset(out + 128, 0, 4);       // u32 len(Commitments) = 0, marshal.go:58
+    g1_compress(G1Affine::inf(), out + 132);  // CommitmentPok, marshal.go:61
+    return 164;
+}
+
+}  // extern "C"

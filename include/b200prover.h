@@ -35,6 +35,11 @@
 extern "C" {
 #endif
 
+/* Entry points are the only exported symbols of libb200prover.so. */
+#if defined(__GNUC__)
+#pragma GCC visibility push(default)
+#endif
+
 typedef struct b200_ctx b200_ctx;
 typedef struct b200_bases b200_bases;             /* resident MSM base set (G1 or G2)         */
 typedef struct b200_groth16_pk b200_groth16_pk;   /* resident Groth16 proving key (or shard)  */
@@ -204,6 +209,9 @@ int b200_groth16_finalize(const b200_groth16_out *msm, const uint64_t *r, const 
 int b200_groth16_proof_bytes(const uint64_t *ar_affine, const uint64_t *bs_affine, const uint64_t *krs_affine,
                              uint8_t *out, size_t out_cap);
 
+#if defined(__GNUC__)
+#pragma GCC visibility pop
+#endif
 #ifdef __cplusplus
 }
 #endif

@@ -135,3 +135,244 @@ def pinned_empty(shape, dtype=np.uint64) -> np.ndarray:
 
 
 _PINNED: dict = {}
+
+
+# ---- host-side group helpers (no ctx) -----------------------------------------------------
+def _host_call(name, *arrays, out_words):
+    lib = load_library()
+    out = np.zeros(out_words, dtype=np.uint64)
+    st = getattr(lib, name)(*[_ptr(_u64(a)) for a in arrays], _ptr(out))
+    if st != 0:
+        raise B200Error(f"{name} failed with status {st}")
+    return out
+
+
+def g1_jac_add(p, q):
+    return _host_call("b200_g1_jac_add", p, q, out_words=12)
+
+
+def g2_jac_add(p, q):
+    return _host_call("b200_g2_jac_add", p, q, out_words=24)
+
+
+def g1_jac_to_affine(p):
+    return _host_call("b200_g1_jac_to_affine", p, out_words=8)
+
+
+def g2_jac_to_affine(p):
+    return _host_call("b200_g2_jac_to_affine", p, out_words=16)
+
+
+def groth16_finalize(msm: Groth16MsmOut, r, s, g1_alpha, g1_beta, g1_delta, g2_beta, g2_delta):
+    """Fix-ups of prove.go:178-321 on the five MSM results -> affine (Ar, Bs, Krs)."""
+    lib = load_library()
+    ar, bs, krs = np.zeros(8, np.uint64), np.zeros(16, np.uint64), np.zeros(8, np.uint64)
+    ins = [_u64(x) for x in (r, s, g1_alpha, g1_beta, g1_delta, g2_beta, g2_delta)]
+    st = lib.b200_groth16_finalize(C.byref(msm), *[_ptr(x) for x in ins], _ptr(ar), _ptr(bs), _ptr(krs))
+    if st != 0:
+        raise B200Error(f"b200_groth16_finalize failed with status {st}")
+    return ar, bs, krs
+
+
+def groth16_proof_bytes(ar, bs, krs) -> bytes:
+    """Proof.WriteTo for a proof without commitments (marshal.go:41-66)."""
+    lib = load_library()
+    out = np.zeros(164, dtype=np.uint8)
+    n = lib.b200_groth16_proof_bytes(_ptr(_u64(ar)), _ptr(_u64(bs)), _ptr(_u64(krs)), _ptr(out), 164)
+    if n < 0:
+        raise B200Error(f"b200_groth16_proof_bytes failed with status {n}")
+    return out[:n].tobytes()
+
+
+# ---- handles ------------------------------------------------------------------------------
+class DeviceVector:
+    """A raw device buffer (iciclegnark.OnDeviceData analogue, icicle.go:228,248)."""
+
+    def __init__(self, ctx: "Context", nbytes: int):
+        self.ctx, self.nbytes = ctx, nbytes
+        p = C.c_void_p()
+        ctx._check(ctx.lib.b200_dev_alloc(ctx.h, nbytes, C.byref(p)))
+        self.ptr = p
+
+    def upload(self, host: np.ndarray):
+        host = np.ascontiguousarray(host)
+        assert host.nbytes <= self.nbytes
+        self.ctx._check(self.ctx.lib.b200_h2d(self.ctx.h, self.ptr, _ptr(host), host.nbytes))
+        return self
+
+    def download(self, shape, dtype=np.uint64) -> np.ndarray:
+        out = np.empty(shape, dtype=dtype)
+        assert out.nbytes <= self.nbytes
+        self.ctx._check(self.ctx.lib.b200_d2h(self.ctx.h, _ptr(out), self.ptr, out.nbytes))
+        return out
+
+    def free(self):
+        if self.ptr:
+            self.ctx.lib.b200_dev_free(self.ctx.h, self.ptr)
+            self.ptr = None
+
+
+class Bases:
+    """Resident MSM base set (CopyPointsToDevice, icicle.go:88-126)."""
+
+    def __init__(self, ctx, handle, n, group):
+        self.ctx, self.h, self.n, self.group = ctx, handle, n, group
+
+    def free(self):
+        if self.h:
+            self.ctx.lib.b200_bases_free(self.ctx.h, self.h)
+            self.h = None
+
+
+class Groth16ProvingKey:
+    """Device-resident groth16_bn254.ProvingKey (setup.go:35-58; icicle/provingkey.go:10-28)."""
+
+    def __init__(self, ctx, handle, keep):
+        self.ctx, self.h, self._keep = ctx, handle, keep
+
+    def free(self):
+        if self.h:
+            self.ctx.lib.b200_groth16_pk_free(self.ctx.h, self.h)
+            self.h = None
+
+
+class Context:
+    """One b200_ctx = one device. Not re-entrant."""
+
+    def __init__(self, device: int = 0):
+        self.lib = load_library()
+        h = C.c_void_p()
+        st = self.lib.b200_init(device, C.byref(h))
+        if st != 0:
+            msg = self.lib.b200_last_error(None)
+            raise B200Error(f"b200_init(device={device}) failed ({st}): {msg.decode() if msg else ''}; "
+                            "a CUDA device is required, there is no CPU fallback")
+        self.h = h
+        self.device = device
+
+    def close(self):
+        if self.h:
+            self.lib.b200_destroy(self.h)
+            self.h = None
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    def _check(self, st: int):
+        if st != 0:
+            msg = self.lib.b200_last_error(self.h)
+            raise B200Error(f"status {st}: {msg.decode() if msg else ''}")
+
+    def sync(self):
+        self._check(self.lib.b200_sync(self.h))
+
+    # -- element-wise / roofline
+    def fr_vec_mul(self, a, b):
+        a, b = _u64(a, (-1, 4)), _u64(b, (-1, 4))
+        out = np.empty_like(a)
+        self._check(self.lib.b200_fr_vec_mul(self.h, BN254, _ptr(a), _ptr(b), _ptr(out), a.shape[0]))
+        return out
+
+    def fp_vec_mul(self, a, b):
+        a, b = _u64(a, (-1, 4)), _u64(b, (-1, 4))
+        out = np.empty_like(a)
+        self._check(self.lib.b200_fp_vec_mul(self.h, BN254, _ptr(a), _ptr(b), _ptr(out), a.shape[0]))
+        return out
+
+    def imad_peak(self):
+        m, p, f = C.c_double(), C.c_double(), C.c_double()
+        self._check(self.lib.b200_imad_peak(self.h, C.byref(m), C.byref(p), C.byref(f)))
+        return {"mac32_per_s": m.value, "imad32_per_s": p.value, "sm_mhz": f.value}
+
+    # -- NTT (fft.Domain.FFT / FFTInverse)
+    def ntt(self, data, log_n, inverse, decimation, on_coset, generator, coset_gen):
+        out = _u64(data, (-1, 4)).copy()
+        assert out.shape[0] == 1 << log_n
+        self._check(self.lib.b200_ntt(self.h, BN254, _ptr(out), log_n, int(inverse), int(decimation),
+                                      int(on_coset), _ptr(_u64(generator)), _ptr(_u64(coset_gen))))
+        return out
+
+    def ntt_dev(self, vec: DeviceVector, log_n, inverse, decimation, on_coset, generator, coset_gen) -> float:
+        ms = C.c_float()
+        self._check(self.lib.b200_ntt_dev(self.h, BN254, vec.ptr, log_n, int(inverse), int(decimation),
+                                          int(on_coset), _ptr(_u64(generator)), _ptr(_u64(coset_gen)), C.byref(ms)))
+        return ms.value
+
+    def compute_h(self, a, b, c, log_n, generator, coset_gen):
+        a, b, c = (_u64(x, (-1, 4)) for x in (a, b, c))
+        out = np.empty((1 << log_n, 4), dtype=np.uint64)
+        self._check(self.lib.b200_groth16_compute_h(self.h, BN254, _ptr(a), _ptr(b), _ptr(c), a.shape[0], log_n,
+                                                    _ptr(_u64(generator)), _ptr(_u64(coset_gen)), _ptr(out)))
+        return out
+
+    # -- MSM (G1Jac.MultiExp / G2Jac.MultiExp)
+    def msm_g1(self, scalars, bases):
+        s, b = _u64(scalars, (-1, 4)), _u64(bases, (-1, 8))
+        out = np.zeros(12, dtype=np.uint64)
+        self._check(self.lib.b200_msm_g1(self.h, BN254, _ptr(s), _ptr(b), s.shape[0], _ptr(out)))
+        return out
+
+    def msm_g2(self, scalars, bases):
+        s, b = _u64(scalars, (-1, 4)), _u64(bases, (-1, 16))
+        out = np.zeros(24, dtype=np.uint64)
+        self._check(self.lib.b200_msm_g2(self.h, BN254, _ptr(s), _ptr(b), s.shape[0], _ptr(out)))
+        return out
+
+    def upload_bases(self, bases, group: int) -> Bases:
+        b = _u64(bases, (-1, 8 if group == 1 else 16))
+        h = C.c_void_p()
+        self._check(self.lib.b200_bases_upload(self.h, BN254, group, _ptr(b), b.shape[0], C.byref(h)))
+        return Bases(self, h, b.shape[0], group)
+
+    def msm_resident(self, bases: Bases, scalars):
+        s = _u64(scalars, (-1, 4))
+        out = np.zeros(12 if bases.group == 1 else 24, dtype=np.uint64)
+        self._check(self.lib.b200_msm_resident(self.h, bases.h, _ptr(s), s.shape[0], _ptr(out)))
+        return out
+
+    def msm_dev(self, bases: Bases, scalars: DeviceVector, n: int):
+        out = np.zeros(12 if bases.group == 1 else 24, dtype=np.uint64)
+        ms = C.c_float()
+        self._check(self.lib.b200_msm_dev(self.h, bases.h, scalars.ptr, n, _ptr(out), C.byref(ms)))
+        return out, ms.value
+
+    def batch_scalar_mul(self, base, scalars, group: int):
+        s = _u64(scalars, (-1, 4))
+        w = 8 if group == 1 else 16
+        out = np.zeros((s.shape[0], w), dtype=np.uint64)
+        self._check(self.lib.b200_batch_scalar_mul(self.h, BN254, group, _ptr(_u64(base)), _ptr(s), s.shape[0], _ptr(out)))
+        return out
+
+    # -- Groth16
+    def groth16_pk_upload(self, *, log_n, generator, coset_gen, g1_a, g1_b, g1_k, g1_z, g2_b, infinity_a,
+                          infinity_b, nb_public, shard_index=0, shard_count=1) -> Groth16ProvingKey:
+        keep = dict(gen=_u64(generator), cg=_u64(coset_gen), a=_u64(g1_a, (-1, 8)), b=_u64(g1_b, (-1, 8)),
+                    k=_u64(g1_k, (-1, 8)), z=_u64(g1_z, (-1, 8)), g2b=_u64(g2_b, (-1, 16)),
+                    ia=np.ascontiguousarray(infinity_a, dtype=np.uint8), ib=np.ascontiguousarray(infinity_b, dtype=np.uint8))
+        d = _PkDesc()
+        d.log_n = log_n
+        d.generator, d.coset_gen = _ptr(keep["gen"]), _ptr(keep["cg"])
+        d.g1_a, d.n_a = _ptr(keep["a"]), keep["a"].shape[0]
+        d.g1_b, d.n_b = _ptr(keep["b"]), keep["b"].shape[0]
+        d.g1_k, d.n_k = _ptr(keep["k"]), keep["k"].shape[0]
+        d.g1_z, d.n_z = _ptr(keep["z"]), keep["z"].shape[0]
+        d.g2_b, d.n_g2b = _ptr(keep["g2b"]), keep["g2b"].shape[0]
+        d.infinity_a, d.infinity_b = _ptr(keep["ia"]), _ptr(keep["ib"])
+        d.n_wires, d.nb_public = keep["ia"].shape[0], nb_public
+        d.shard_index, d.shard_count = shard_index, shard_count
+        h = C.c_void_p()
+        self._check(self.lib.b200_groth16_pk_upload(self.h, BN254, C.byref(d), C.byref(h)))
+        return Groth16ProvingKey(self, h, None)
+
+    def groth16_prove_core(self, pk: Groth16ProvingKey, a, b, c, w, k_remove=None):
+        """computeH + the five MSMs (prove.go:139-301). Returns (Groth16MsmOut, timings dict)."""
+        a, b, c, w = (_u64(x, (-1, 4)) for x in (a, b, c, w))
+        out, tm = Groth16MsmOut(), _Timings()
+        kr = None if k_remove is None or len(k_remove) == 0 else np.ascontiguousarray(k_remove, dtype=np.uint32)
+        self._check(self.lib.b200_groth16_prove_core(self.h, pk.h, _ptr(a), _ptr(b), _ptr(c), a.shape[0], _ptr(w),
+                                                     _ptr(kr), 0 if kr is None else kr.shape[0],
+                                                     C.byref(out), C.byref(tm)))
+        return out, {k: getattr(tm, k) for k, _ in _Timings._fields_}

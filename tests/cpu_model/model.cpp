@@ -1,0 +1,114 @@
+// CPU replay of the device algorithms' index logic (TEST INFRASTRUCTURE).
+// Compiled with g++ from the very headers the kernels use (ntt.cuh, msm.cuh, field.cuh, ec.cuh,
+// host path), so the tile geometry, twiddle exponents, signed-digit recoding, reduction tree and
+// group formulas are checked against oracle/ on a machine without a GPU.
+#include <vector>
+#include <cstring>
+#include "../../gnark-fork_b200/csrc/ntt.cuh"
+#include "../../gnark-fork_b200/csrc/msm.cuh"
+
+using namespace b200;
+
+extern "C" {
+
+// sequential replay of ntt_pass_kernel over the plan ntt_plan() produces
+void model_ntt(uint64_t* data, unsigned log_n, int inverse, int dit, unsigned tl_max, unsigned s_max,
+               const uint64_t* gen_mont) {
+    Fr* x = reinterpret_cast<Fr*>(data);
+    const size_t n = (size_t)1 << log_n;
+    Fr gen; memcpy(gen.l, gen_mont, 32);
+    if (inverse) gen = gen.inv();
+    std::vector<Fr> tw(n / 2 ? n / 2 : 1);
+    tw[0] = Fr::one();
+    for (size_t j = 1; j < tw.size(); ++j) tw[j] = tw[j - 1] * gen;
+    if (log_n == 0) return;
+    NttPassGeom plan[8];
+    const int np = ntt_plan(log_n, dit, tl_max, s_max < tl_max ? s_max : tl_max, plan);
+    for (int p = 0; p < np; ++p) {
+        const NttPassGeom g = plan[p];
+        const uint32_t tile_n = 1u << g.TL, tiles = (uint32_t)(n >> g.TL);
+        std::vector<Fr> sm(tile_n);
+        for (uint32_t tile = 0; tile < tiles; ++tile) {
+            for (uint32_t loc = 0; loc < tile_n; ++loc) sm[loc] = x[ntt_gidx(g, tile, loc)];
+            for (uint32_t k = 0; k < g.S; ++k) {
+                const uint32_t bit = ntt_stage_bit(g, dit, k), s = g.s0 + k;
+                for (uint32_t bf = 0; bf < tile_n / 2; ++bf) {
+                    const uint32_t i0 = ntt_bf_lower(bf, bit), i1 = i0 | (1u << bit);
+                    const uint32_t e = ntt_twiddle_exp(g.log_n, dit, s, ntt_gidx(g, tile, i0));
+                    const Fr u = sm[i0], v = sm[i1];
+                    if (dit) { const Fr t = v * tw[e]; sm[i0] = u + t; sm[i1] = u - t; }
+                    else { sm[i0] = u + v; sm[i1] = (u - v) * tw[e]; }
+                }
+            }
+            for (uint32_t loc = 0; loc < tile_n; ++loc) x[ntt_gidx(g, tile, loc)] = sm[loc];
+        }
+    }
+}
+
+}  // extern "C"
+
+// the whole MSM pipeline replayed on the host with the device formulas (XYZZ, reduction tree)
+template <class F>
+static void model_msm(const uint64_t* scalars, const uint64_t* bases, size_t n, int c_override, uint64_t* out_jac) {
+    const Fr* sc = reinterpret_cast<const Fr*>(scalars);
+    const Affine<F>* pts = reinterpret_cast<const Affine<F>*>(bases);
+    Jac<F> res = Jac<F>::inf();
+    if (n) {
+        const MsmPlan pl = msm_plan(n, c_override);
+        std::vector<int32_t> digits((size_t)pl.W * n);
+        for (size_t i = 0; i < n; ++i) {
+            const Fr s = sc[i].from_mont();
+            msm_signed_digits(s.l, pl.c, pl.W, &digits[i], n);
+        }
+        const size_t M = (size_t)pl.W * pl.nb;
+        std::vector<XYZZ<F>> buckets(M, XYZZ<F>::inf());
+        for (int w = 0; w < pl.W; ++w)
+            for (size_t i = 0; i < n; ++i) {
+                const int32_t d = digits[(size_t)w * n + i];
+                if (!d) continue;
+                Affine<F> p = pts[i];
+                if (d < 0) p.y = p.y.neg();
+                buckets[(size_t)w * pl.nb + (size_t)((d < 0 ? -d : d) - 1)].add_mixed(p);
+            }
+        uint32_t T = pl.nb / pl.L0, log_len = 0;
+        while ((1u << log_len) < pl.L0) ++log_len;
+        std::vector<XYZZ<F>> S((size_t)pl.W * T), Wt((size_t)pl.W * T);
+        for (size_t t = 0; t < S.size(); ++t) {
+            XYZZ<F> run = XYZZ<F>::inf(), acc = XYZZ<F>::inf();
+            for (int j = (int)pl.L0 - 1; j >= 0; --j) { run.add(buckets[t * pl.L0 + j]); acc.add(run); }
+            S[t] = run; Wt[t] = acc;
+        }
+        while (T > 1) {
+            const uint32_t L = T < pl.L ? T : pl.L;
+            uint32_t logL = 0; while ((1u << logL) < L) ++logL;
+            std::vector<XYZZ<F>> S2((size_t)pl.W * (T / L)), W2(S2.size());
+            for (size_t t = 0; t < S2.size(); ++t) {
+                XYZZ<F> run = XYZZ<F>::inf(), acc = XYZZ<F>::inf(), wsum = XYZZ<F>::inf();
+                for (int j = (int)L - 1; j >= 0; --j) { acc.add(run); run.add(S[t * L + j]); wsum.add(Wt[t * L + j]); }
+                for (uint32_t k = 0; k < log_len; ++k) acc = acc.dbl();
+                wsum.add(acc);
+                S2[t] = run; W2[t] = wsum;
+            }
+            S.swap(S2); Wt.swap(W2);
+            T /= L; log_len += logL;
+        }
+        XYZZ<F> acc = XYZZ<F>::inf();
+        for (int w = pl.W - 1; w >= 0; --w) {
+            for (int k = 0; k < pl.c; ++k) acc = acc.dbl();
+            acc.add(Wt[w]);
+        }
+        res = acc.to_jac();
+    }
+    memcpy(out_jac, &res, sizeof res);
+}
+extern "C" {
+void model_msm_g1(const uint64_t* s, const uint64_t* b, size_t n, int c, uint64_t* out) { model_msm<Fp>(s, b, n, c, out); }
+void model_msm_g2(const uint64_t* s, const uint64_t* b, size_t n, int c, uint64_t* out) { model_msm<Fp2>(s, b, n, c, out); }
+
+void model_fr_mul(const uint64_t* a, const uint64_t* b, uint64_t* o, size_t n) {
+    for (size_t i = 0; i < n; ++i) reinterpret_cast<Fr*>(o)[i] = reinterpret_cast<const Fr*>(a)[i] * reinterpret_cast<const Fr*>(b)[i];
+}
+void model_fp_mul(const uint64_t* a, const uint64_t* b, uint64_t* o, size_t n) {
+    for (size_t i = 0; i < n; ++i) reinterpret_cast<Fp*>(o)[i] = reinterpret_cast<const Fp*>(a)[i] * reinterpret_cast<const Fp*>(b)[i];
+}
+}

@@ -1,0 +1,163 @@
+"""Parity of the CUDA path (through the C ABI, host buffers) with the oracle.  Bit-exact for
+field elements; MSM results compared after affine normalisation (Jacobian representatives are
+not canonical)."""
+import numpy as np
+import pytest
+
+from oracle import bn254 as B
+from oracle import groth16 as G
+from oracle import ntt as N
+from tests import util
+from tests.conftest import rand_field
+
+pytestmark = pytest.mark.gpu
+
+
+def test_field_mul(ctx, cref):
+    rng = np.random.default_rng(1)
+    n = 1 << 18
+    a, b = rand_field(rng, n), rand_field(rng, n)
+    edge = cref.ints_to_mont([0, 1, B.R - 1, 2, B.R - 2, (1 << 256) % B.R], B.R)
+    a[:6], b[:6] = edge, edge[::-1]
+    assert np.array_equal(ctx.fr_vec_mul(a, b), cref.fr_mul(a, b))
+    edge = cref.ints_to_mont([0, 1, B.P - 1, 2, B.P - 2, (1 << 256) % B.P], B.P)
+    a[:6], b[:6] = edge, edge[::-1]
+    assert np.array_equal(ctx.fp_vec_mul(a, b), cref.fp_mul(a, b))
+    assert ctx.fr_vec_mul(a[:0], b[:0]).shape == (0, 4)
+
+
+def test_ntt_golden(ctx, cref):
+    g = util.golden()["ntt"]
+    x, gen, cg = util.fr_arr(g["input"]), cref.fr(g["generator"]), cref.fr(g["coset_gen"])
+    for case in g["cases"]:
+        got = ctx.ntt(x, g["log_n"], case["inverse"], case["decimation"], case["on_coset"], gen, cg)
+        assert util.fr_ints(got) == case["output"], case
+
+
+@pytest.mark.parametrize("log_n", [0, 1, 2, 5, 11, 12, 13, 16, 18, 20])
+def test_ntt_all_variants_vs_oracle(ctx, cref, log_n):
+    rng = np.random.default_rng(50 + log_n)
+    n = 1 << log_n
+    x = rand_field(rng, n)
+    d = N.Domain(n)
+    gen, cg = cref.fr(d.generator), cref.fr(d.coset_gen)
+    for inverse in (0, 1):
+        for dec in (0, 1):
+            for coset in (0, 1):
+                got = ctx.ntt(x, log_n, inverse, dec, coset, gen, cg)
+                want = cref.ntt(x, log_n, inverse, dec, coset, gen, cg)
+                assert np.array_equal(got, want), (log_n, inverse, dec, coset)
+
+
+def test_ntt_roundtrip_large(ctx, cref):
+    """size-independent property at a BASELINE size: FFTInverse(DIT) o FFT(DIF) = identity."""
+    log_n = 22
+    rng = np.random.default_rng(9)
+    x = rand_field(rng, 1 << log_n)
+    d = N.Domain(1 << log_n)
+    gen, cg = cref.fr(d.generator), cref.fr(d.coset_gen)
+    y = ctx.ntt(x, log_n, 0, 0, 1, gen, cg)
+    assert not np.array_equal(x, y)
+    z = ctx.ntt(y, log_n, 1, 1, 1, gen, cg)
+    assert np.array_equal(x, z)
+
+
+def test_compute_h_golden_and_oracle(ctx, cref):
+    g = util.golden()["compute_h"]
+    gen, cg = cref.fr(g["generator"]), cref.fr(g["coset_gen"])
+    got = ctx.compute_h(util.fr_arr(g["a"]), util.fr_arr(g["b"]), util.fr_arr(g["c"]), g["log_n"], gen, cg)
+    assert util.fr_ints(got) == g["h_bitreversed"]
+    for log_n, nc in ((10, 1000), (14, 1 << 14), (17, (1 << 17) - 5)):
+        rng = np.random.default_rng(log_n)
+        a, b, c = rand_field(rng, nc), rand_field(rng, nc), rand_field(rng, nc)
+        d = N.Domain(1 << log_n)
+        gen, cg = cref.fr(d.generator), cref.fr(d.coset_gen)
+        assert np.array_equal(ctx.compute_h(a, b, c, log_n, gen, cg), cref.compute_h(a, b, c, log_n, gen, cg))
+
+
+def test_msm_golden(ctx, cref):
+    g = util.golden()["msm"]
+    s = util.fr_arr(g["scalars"])
+    assert util.g1_aff_ints(cref.g1_jac_to_aff(ctx.msm_g1(s, util.g1_arr(g["g1_bases"])))) == g["g1_result"]
+    assert util.g2_aff_ints(cref.g2_jac_to_aff(ctx.msm_g2(s, util.g2_arr(g["g2_bases"])))) == g["g2_result"]
+
+
+@pytest.mark.parametrize("n", [0, 1, 2, 33, 1000, 5000, 1 << 15, (1 << 16) + 3])
+def test_msm_g1_vs_oracle(ctx, cref, n):
+    rng = np.random.default_rng(70 + n)
+    bases, _ = util.known_dlog_bases_g1(max(n, 1), seed=n)
+    bases = bases[:n]
+    scalars = rand_field(rng, n)
+    if n > 40:
+        scalars[0] = 0
+        scalars[1] = cref.fr(B.R - 1)
+        scalars[2] = cref.fr(1)
+        bases[7] = 0            # infinity base
+        bases[9] = bases[8]     # repeated base
+        scalars[9] = scalars[8]
+    got = ctx.msm_g1(scalars, bases)
+    want = cref.msm_g1(scalars, bases)
+    assert np.array_equal(cref.g1_jac_to_aff(got), cref.g1_jac_to_aff(want))
+
+
+def test_msm_g1_all_equal_bases(ctx, cref):
+    """DummySetup (setup.go:532-546): every base is the same point."""
+    rng = np.random.default_rng(4)
+    n = 3000
+    gen = cref.g1_points_to_array([B.G1_GEN])[0]
+    bases = np.tile(gen, (n, 1))
+    scalars = rand_field(rng, n)
+    scalars[:64] = cref.fr(12345)
+    want = B.g1_mul(B.G1_GEN, sum(util.fr_ints(scalars)) % B.R)
+    assert util.g1_aff_ints(cref.g1_jac_to_aff(ctx.msm_g1(scalars, bases))) == [want[0], want[1]]
+
+
+def test_msm_g1_witness_like_scalars(ctx, cref):
+    """Skewed digits: half the scalars in {0,1}, a quarter below 2^16."""
+    rng = np.random.default_rng(6)
+    n = 1 << 14
+    bases, ks = util.known_dlog_bases_g1(n, seed=3)
+    vals = [int(rng.integers(0, 2)) for _ in range(n // 2)] + [int(rng.integers(0, 1 << 16)) for _ in range(n // 4)]
+    vals += util.fr_ints(rand_field(rng, n - len(vals)))
+    scalars = util.fr_arr(vals)
+    want = B.g1_mul(B.G1_GEN, sum(k * s for k, s in zip(ks, vals)) % B.R)
+    assert util.g1_aff_ints(cref.g1_jac_to_aff(ctx.msm_g1(scalars, bases))) == [want[0], want[1]]
+
+
+@pytest.mark.parametrize("n", [1, 77, 3000, 1 << 14])
+def test_msm_g2_vs_oracle(ctx, cref, n):
+    rng = np.random.default_rng(90 + n)
+    bases, _ = util.known_dlog_bases_g2(n, seed=n)
+    scalars = rand_field(rng, n)
+    if n > 40:
+        scalars[0] = 0
+        bases[7] = 0
+        bases[9] = bases[8]
+        scalars[9] = scalars[8]
+    got = ctx.msm_g2(scalars, bases)
+    want = cref.msm_g2(scalars, bases)
+    assert np.array_equal(cref.g2_jac_to_aff(got), cref.g2_jac_to_aff(want))
+
+
+def test_msm_known_dlog_large(ctx, cref):
+    """2^20 points, exact at any size: bases [k_i]G from the device fixed-base kernel (itself
+    checked against the oracle on a slice), expected = [sum k_i s_i]G."""
+    rng = np.random.default_rng(12)
+    n = 1 << 20
+    ks = rand_field(rng, n)
+    gen = cref.g1_points_to_array([B.G1_GEN])[0]
+    bases = ctx.batch_scalar_mul(gen, ks, 1)
+    assert np.array_equal(bases[:512], cref.g1_batch_mul(gen, ks[:512]))
+    scalars = rand_field(rng, n)
+    prod = cref.fr_mul(ks, scalars)  # Montgomery form of k_i * s_i
+    total = sum(util.fr_ints(prod)) % B.R
+    want = B.g1_mul(B.G1_GEN, total)
+    assert util.g1_aff_ints(cref.g1_jac_to_aff(ctx.msm_g1(scalars, bases))) == [want[0], want[1]]
+
+
+def test_batch_scalar_mul_g2(ctx, cref):
+    rng = np.random.default_rng(13)
+    ks = rand_field(rng, 300)
+    ks[0] = 0
+    gen = cref.g2_points_to_array([B.G2_GEN])[0]
+    assert np.array_equal(ctx.batch_scalar_mul(gen, ks, 2), cref.g2_batch_mul(gen, ks))

@@ -1,0 +1,129 @@
+"""Pins the oracle: in-tree constants of the reference, the committed golden vectors (computed
+from the big-int definitions, tests/golden/make_golden.py), and C++ restatement == Python
+restatement at sizes Python can reach.  No GPU."""
+import numpy as np
+import pytest
+
+from oracle import bn254 as B
+from oracle import groth16 as G
+from oracle import ntt as N
+from tests import util
+from tests.conftest import rand_field
+
+
+def test_constants_pinned_in_reference_tree():
+    # backend/groth16/bn254/solidity.go:41-42
+    assert B.P == 0x30644e72e131a029b85045b68181585d97816a916871ca8d3c208c16d87cfd47
+    assert B.R == 0x30644e72e131a029b85045b68181585d2833e84879b9709143e1f593f0000001
+    # backend/plonk/bn254/solidity.go:25-27,56
+    assert B.R == 21888242871839275222246405745257275088548364400416034343698204186575808495617
+    assert B.P == 21888242871839275222246405745257275088696311157297823662689037894645226208583
+    assert B.FR_MULT_GEN == 5
+    # backend/groth16/bn254/solidity.go:52-54,57-58 (fractions in Fp pin the G2 twist 3/(9+u))
+    assert pow(2, -1, B.P) == 0x183227397098d014dc2822db40c0ac2ecbc0b548b438e5469e10460b6c3e7ea4
+    assert 27 * pow(82, -1, B.P) % B.P == 0x2b149d40ceb8aaae81be18991be06ac3b5b4c5e559dbefa33267e6dc24a138e5
+    assert 3 * pow(82, -1, B.P) % B.P == 0x2fcd3ac2a640a154eb23960892a85a68f031ca0c8344b23a577dcf1052b9e775
+    assert B.G2_B == (27 * pow(82, -1, B.P) % B.P, (-3 * pow(82, -1, B.P)) % B.P)
+    assert (B.P + 1) // 4 == 0xC19139CB84C680A6E14116DA060561765E05AA45A1C72A34F082305B61F3F52
+    # BN parameter t (solidity.go:36-40): p, r polynomials in t
+    t = 4965661367192848881
+    assert B.P == 36 * t**4 + 36 * t**3 + 24 * t**2 + 6 * t + 1
+    assert B.R == 36 * t**4 + 36 * t**3 + 18 * t**2 + 6 * t + 1
+
+
+def test_recalled_constants_self_check():
+    assert pow(B.FR_ROOT_2_28, 1 << 28, B.R) == 1 and pow(B.FR_ROOT_2_28, 1 << 27, B.R) == B.R - 1
+    assert (B.R - 1) % (1 << 28) == 0 and (B.R - 1) % (1 << 29) != 0
+    assert B.g1_on_curve(B.G1_GEN) and B.g2_on_curve(B.G2_GEN)
+    assert B.g1_mul(B.G1_GEN, B.R - 1) == B.g1_neg(B.G1_GEN)
+    assert B._aff_mul(B._Fp2, B.G2_GEN, B.R) is None  # G2 generator has order r
+
+
+def test_python_ntt_vs_naive_dft():
+    d = N.Domain(16)
+    x = [pow(7, i + 1, B.R) for i in range(16)]
+    y = list(x)
+    N.fft(y, d, N.DIF)
+    N.bit_reverse(y)
+    assert y == N.naive_dft(x, d.generator)
+    N.bit_reverse(y)
+    N.fft_inverse(y, d, N.DIT)
+    assert y == x
+
+
+def test_cref_ntt_golden(cref):
+    g = util.golden()["ntt"]
+    x, gen, cg = util.fr_arr(g["input"]), cref.fr(g["generator"]), cref.fr(g["coset_gen"])
+    for case in g["cases"]:
+        got = cref.ntt(x, g["log_n"], case["inverse"], case["decimation"], case["on_coset"], gen, cg)
+        assert util.fr_ints(got) == case["output"], case
+
+
+def test_python_ntt_golden():
+    g = util.golden()["ntt"]
+    d = N.Domain(1 << g["log_n"], g["generator"], g["coset_gen"])
+    for case in g["cases"]:
+        v = list(g["input"])
+        (N.fft_inverse if case["inverse"] else N.fft)(v, d, case["decimation"], bool(case["on_coset"]))
+        assert v == case["output"], case
+
+
+def test_compute_h_golden(cref):
+    g = util.golden()["compute_h"]
+    gen, cg = cref.fr(g["generator"]), cref.fr(g["coset_gen"])
+    got = cref.compute_h(util.fr_arr(g["a"]), util.fr_arr(g["b"]), util.fr_arr(g["c"]), g["log_n"], gen, cg)
+    assert util.fr_ints(got) == g["h_bitreversed"]
+    d = N.Domain(1 << g["log_n"], g["generator"], g["coset_gen"])
+    assert N.compute_h(g["a"], g["b"], g["c"], d) == g["h_bitreversed"]
+
+
+def test_msm_golden(cref):
+    g = util.golden()["msm"]
+    s = util.fr_arr(g["scalars"])
+    assert util.g1_aff_ints(cref.g1_jac_to_aff(cref.msm_g1(s, util.g1_arr(g["g1_bases"])))) == g["g1_result"]
+    assert util.g2_aff_ints(cref.g2_jac_to_aff(cref.msm_g2(s, util.g2_arr(g["g2_bases"])))) == g["g2_result"]
+
+
+@pytest.mark.parametrize("log_n", [6, 10])
+def test_cref_vs_python_ntt(cref, log_n):
+    rng = np.random.default_rng(log_n)
+    n = 1 << log_n
+    x = rand_field(rng, n)
+    xi = util.fr_ints(x)
+    d = N.Domain(n)
+    gen, cg = cref.fr(d.generator), cref.fr(d.coset_gen)
+    for inverse in (0, 1):
+        for dec in (0, 1):
+            for coset in (0, 1):
+                v = list(xi)
+                (N.fft_inverse if inverse else N.fft)(v, d, dec, bool(coset))
+                assert util.fr_ints(cref.ntt(x, log_n, inverse, dec, coset, gen, cg)) == v
+
+
+def test_cref_msm_vs_python_definition(cref):
+    rng = np.random.default_rng(5)
+    n = 40
+    bases, ks = util.known_dlog_bases_g1(n)
+    scalars = rand_field(rng, n)
+    si = util.fr_ints(scalars)
+    want = B.g1_mul(B.G1_GEN, sum(k * s for k, s in zip(ks, si)) % B.R)
+    assert util.g1_aff_ints(cref.g1_jac_to_aff(cref.msm_g1(scalars, bases))) == [want[0], want[1]]
+    bases2, ks2 = util.known_dlog_bases_g2(n)
+    want2 = B.g2_mul(B.G2_GEN, sum(k * s for k, s in zip(ks2, si)) % B.R)
+    assert util.g2_aff_ints(cref.g2_jac_to_aff(cref.msm_g2(scalars, bases2))) == [want2[0][0], want2[0][1], want2[1][0], want2[1][1]]
+
+
+def test_groth16_golden_trapdoor_and_bytes():
+    g = util.golden()["groth16"]
+    r1cs = G.mul_chain_circuit(g["nb_mul"])
+    w, a, b, c = G.mul_chain_witness(g["nb_mul"], g["x"])
+    assert G.solve(r1cs, w) == (a, b, c)
+    td = G.Trapdoor(*g["trapdoor"])
+    pk, vk = G.setup(r1cs, td, points=False)
+    dl = G.prove_dlog(pk, td, w, a, b, c, g["r"], g["s"], r1cs.nb_public)
+    assert G.trapdoor_check(vk, w[: r1cs.nb_public], dl["ar"], dl["bs"], dl["krs"])
+    assert not G.trapdoor_check(vk, w[: r1cs.nb_public], dl["ar"], dl["bs"], (dl["krs"] + 1) % B.R)
+    ar, krs = B.g1_mul(B.G1_GEN, dl["ar"]), B.g1_mul(B.G1_GEN, dl["krs"])
+    bs = B.g2_mul(B.G2_GEN, dl["bs"])
+    assert [ar[0], ar[1]] == g["ar"] and [krs[0], krs[1]] == g["krs"]
+    assert G.proof_bytes(ar, bs, krs).hex() == g["proof_hex"]

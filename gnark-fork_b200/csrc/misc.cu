@@ -26,34 +26,41 @@ int vec_mul_fp(b200_ctx* ctx, const Fp* a, const Fp* b, Fp* out, size_t n) {
 }
 
 // ---------------------------------------------------------------------------------------
-// IMAD-pipe peak.  (a) the instruction pattern the field multiplication is made of: four
-// independent 8-limb mad.lo.cc/madc.hi.cc chains per thread (SASS: IMAD.WIDE.U32.X);
+// IMAD-pipe peak.  (a) the instruction stream the field multiplication is made of, timed as
+// register-resident Montgomery products (SASS: IMAD.WIDE.U32.X chains);
 // (b) independent plain 32-bit mad.lo chains (SASS: IMAD).
 // ---------------------------------------------------------------------------------------
 constexpr int PEAK_ITERS = 4096;
 
+// (a) four independent chains of Montgomery products per thread, register resident: every
+// product is 128 IMAD.WIDE.U32(.X) + 8 IMAD (= 136 MAC32, the algorithmic count 2n^2 + n).
+constexpr int PEAK_MUL_ITERS = 512;
 __global__ void __launch_bounds__(256) peak_wide_kernel(const uint32_t* __restrict__ in, uint32_t* __restrict__ out, long long* cycles) {
-    uint32_t acc[4][8];
-    const uint32_t x0 = in[threadIdx.x & 31], x1 = in[32 + (threadIdx.x & 31)], x2 = x0 ^ 0x9e3779b9u, x3 = x1 + 0x7f4a7c15u;
-    uint32_t y = in[64 + (threadIdx.x & 31)];
+    Fr v[4], w[4];
 #pragma unroll
     for (int k = 0; k < 4; ++k)
 #pragma unroll
-        for (int j = 0; j < 8; ++j) acc[k][j] = x0 + k * 8 + j;
+        for (int j = 0; j < 8; ++j) {
+            v[k].l[j] = in[(threadIdx.x + 8 * k + j) & 127] >> 3;   // < 2^29: reduced
+            w[k].l[j] = in[(threadIdx.x + 40 * k + 5 * j) & 127] >> 3;
+        }
+    unsigned long long g0, g1;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(g0));
     const long long t0 = clock64();
 #pragma unroll 1
-    for (int it = 0; it < PEAK_ITERS; ++it) {
+    for (int it = 0; it < PEAK_MUL_ITERS; ++it) {
 #pragma unroll
-        for (int k = 0; k < 4; ++k) mad_chain8(acc[k], x0, x1, x2, x3, y);
+        for (int k = 0; k < 4; ++k) v[k] = v[k] * w[k];
     }
     const long long t1 = clock64();
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(g1));
     uint32_t s = 0;
 #pragma unroll
     for (int k = 0; k < 4; ++k)
 #pragma unroll
-        for (int j = 0; j < 8; ++j) s ^= acc[k][j];
+        for (int j = 0; j < 8; ++j) s ^= v[k].l[j];
     if (s == 0x12345678u) out[0] = s;  // keep the chains live
-    if (blockIdx.x == 0 && threadIdx.x == 0) *cycles = t1 - t0;
+    if (blockIdx.x == 0 && threadIdx.x == 0) { cycles[0] = t1 - t0; cycles[1] = (long long)(g1 - g0); }
 }
 
 __global__ void __launch_bounds__(256) peak_imad_kernel(const uint32_t* __restrict__ in, uint32_t* __restrict__ out) {
@@ -76,13 +83,13 @@ int imad_peak(b200_ctx* ctx, double* mac32_per_s, double* imad32_per_s, double* 
     DevBuf in, out, cyc;
     B2_CUDA(ctx, in.alloc(128 * 4));
     B2_CUDA(ctx, out.alloc(16));
-    B2_CUDA(ctx, cyc.alloc(8));
+    B2_CUDA(ctx, cyc.alloc(16));
     uint32_t h[128];
     for (int i = 0; i < 128; ++i) h[i] = 0x9e3779b9u * (i + 1) + 12345u;
     B2_CUDA(ctx, cudaMemcpyAsync(in.p, h, sizeof h, cudaMemcpyHostToDevice, ctx->stream));
     const int blocks = ctx->sm_count * 4, threads = 256;
     float best_w = 1e30f, best_i = 1e30f;
-    long long cycles = 0;
+    long long cycles[2] = {0, 1};
     for (int rep = 0; rep < 5; ++rep) {
         B2_CUDA(ctx, cudaEventRecord(ctx->ev0, ctx->stream));
         peak_wide_kernel<<<blocks, threads, 0, ctx->stream>>>(in.as<uint32_t>(), out.as<uint32_t>(), cyc.as<long long>());
@@ -92,7 +99,7 @@ int imad_peak(b200_ctx* ctx, double* mac32_per_s, double* imad32_per_s, double* 
         B2_CUDA(ctx, cudaEventElapsedTime(&ms, ctx->ev0, ctx->ev1));
         if (rep && ms < best_w) {
             best_w = ms;
-            B2_CUDA(ctx, cudaMemcpy(&cycles, cyc.p, 8, cudaMemcpyDeviceToHost));
+            B2_CUDA(ctx, cudaMemcpy(cycles, cyc.p, 16, cudaMemcpyDeviceToHost));
         }
         B2_CUDA(ctx, cudaEventRecord(ctx->ev0, ctx->stream));
         peak_imad_kernel<<<blocks, threads, 0, ctx->stream>>>(in.as<uint32_t>(), out.as<uint32_t>());
@@ -102,11 +109,10 @@ int imad_peak(b200_ctx* ctx, double* mac32_per_s, double* imad32_per_s, double* 
         if (rep && ms < best_i) best_i = ms;
     }
     const double lanes = (double)blocks * threads;
-    if (mac32_per_s) *mac32_per_s = lanes * PEAK_ITERS * 16.0 / (best_w * 1e-3);
+    if (mac32_per_s) *mac32_per_s = lanes * PEAK_MUL_ITERS * 4.0 * 136.0 / (best_w * 1e-3);
     if (imad32_per_s) *imad32_per_s = lanes * PEAK_ITERS * 16.0 / (best_i * 1e-3);
-    // one block's cycle count over the whole kernel's wall time: a lower bound of the SM clock
-    // when the grid is a single wave (4 blocks of 256 threads per SM fit at once).
-    if (sm_mhz) *sm_mhz = (double)cycles / (best_w * 1e-3) / 1e6;
+    // SM clock seen by the kernel: clock64 delta over the globaltimer delta (ns) of one thread
+    if (sm_mhz) *sm_mhz = (double)cycles[0] / (double)(cycles[1] ? cycles[1] : 1) * 1e3;
     return B200_OK;
 }
 

@@ -175,7 +175,7 @@ static __global__ void msm_scan_top_kernel(uint32_t* block_sums, uint32_t nblock
     }
 }
 static __global__ void msm_scan_final_kernel(const uint32_t* __restrict__ in, uint32_t m, const uint32_t* __restrict__ block_sums,
-                                      uint32_t* __restrict__ out, uint32_t* __restrict__ out2) {
+                                      uint32_t* out, uint32_t* out2) {
     const uint32_t base = blockIdx.x * SCAN_CHUNK + threadIdx.x * SCAN_ITEMS;
     uint32_t v[SCAN_ITEMS], s = 0;
 #pragma unroll
@@ -183,7 +183,7 @@ static __global__ void msm_scan_final_kernel(const uint32_t* __restrict__ in, ui
     uint32_t ex = block_exclusive_scan(s, nullptr) + block_sums[blockIdx.x];
 #pragma unroll
     for (int j = 0; j < SCAN_ITEMS; ++j) {
-        if (base + j < m) { out[base + j] = ex; out2[base + j] = ex; }
+        if (base + j < m) { out[base + j] = ex; if (out2) out2[base + j] = ex; }
         ex += v[j];
     }
 }
@@ -202,14 +202,41 @@ static __global__ void msm_scatter_kernel(const int32_t* __restrict__ digits, ui
     }
 }
 
-// 4. bucket accumulation: thread t owns bucket t (all windows concatenated).
+// 4. bucket accumulation.  Buckets are cut into tasks of at most `chunk` points so that one
+// oversized bucket (the top window only sees 254 - c*(W-1) scalar bits; real witnesses are full of
+// 0/1 values) cannot serialise the launch: ntasks[b] = max(1, ceil(count[b] / chunk)), an
+// exclusive scan gives task_off[b], msm_task_fill_kernel writes the owning bucket of every task.
+static __global__ void msm_task_count_kernel(const uint32_t* __restrict__ counts, uint32_t n_buckets, uint32_t chunk,
+                                             uint32_t* __restrict__ ntasks) {
+    const uint32_t b = blockIdx.x * blockDim.x + threadIdx.x;
+    if (b >= n_buckets) return;
+    const uint32_t c = counts[b];
+    ntasks[b] = c <= chunk ? 1u : (c + chunk - 1u) / chunk;
+}
+static __global__ void msm_task_fill_kernel(const uint32_t* __restrict__ ntasks, const uint32_t* __restrict__ task_off,
+                                            uint32_t n_buckets, uint32_t* __restrict__ task_bucket) {
+    const uint32_t b = blockIdx.x * blockDim.x + threadIdx.x;
+    if (b >= n_buckets) return;
+    const uint32_t nt = ntasks[b], o = task_off[b];
+    for (uint32_t j = 0; j < nt; ++j) task_bucket[o + j] = b;
+}
+
+// one thread per task; a single-task bucket is written straight to buckets[], the pieces of a
+// split bucket go to partials[task] and are merged by msm_combine_kernel.
 template <class F>
 __global__ void __launch_bounds__(128) msm_accumulate_kernel(const Affine<F>* __restrict__ bases, const uint32_t* __restrict__ sorted,
                                       const uint32_t* __restrict__ offsets, const uint32_t* __restrict__ counts,
-                                      uint32_t n_buckets, XYZZ<F>* __restrict__ buckets) {
+                                      const uint32_t* __restrict__ task_bucket, const uint32_t* __restrict__ task_off,
+                                      const uint32_t* __restrict__ ntasks, uint32_t max_tasks, uint32_t chunk,
+                                      XYZZ<F>* __restrict__ buckets, XYZZ<F>* __restrict__ partials) {
     const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
-    if (t >= n_buckets) return;
-    const uint32_t start = offsets[t], cnt = counts[t];
+    if (t >= max_tasks) return;
+    const uint32_t b = task_bucket[t];
+    if (b == 0xffffffffu) return;
+    const uint32_t nt = ntasks[b], j0 = (t - task_off[b]) * chunk;
+    const uint32_t cnt_b = counts[b];
+    uint32_t cnt = nt == 1 ? cnt_b : (cnt_b - j0 < chunk ? cnt_b - j0 : chunk);
+    const uint32_t start = offsets[b] + (nt == 1 ? 0u : j0);
     XYZZ<F> acc = XYZZ<F>::inf();
     for (uint32_t j = 0; j < cnt; ++j) {
         const uint32_t e = sorted[start + j];
@@ -217,7 +244,43 @@ __global__ void __launch_bounds__(128) msm_accumulate_kernel(const Affine<F>* __
         if (e >> 31) p.y = p.y.neg();
         acc.add_mixed(p);
     }
-    st_vec(buckets + t, acc);
+    st_vec(nt == 1 ? buckets + b : partials + t, acc);
+}
+
+template <class F>
+__device__ __forceinline__ XYZZ<F> shfl_down_point(const XYZZ<F>& p, int delta) {
+    XYZZ<F> r;
+    const uint32_t* s = reinterpret_cast<const uint32_t*>(&p);
+    uint32_t* d = reinterpret_cast<uint32_t*>(&r);
+#pragma unroll
+    for (int i = 0; i < (int)(sizeof(XYZZ<F>) / 4); ++i) d[i] = __shfl_down_sync(0xffffffffu, s[i], delta);
+    return r;
+}
+
+// a warp looks at 32 buckets; every split bucket among them is summed by the whole warp
+// (strided partial sums per lane, then a shuffle tree).
+template <class F>
+__global__ void __launch_bounds__(128) msm_combine_kernel(const uint32_t* __restrict__ task_off, const uint32_t* __restrict__ ntasks,
+                                   uint32_t n_buckets, const XYZZ<F>* __restrict__ partials, XYZZ<F>* __restrict__ buckets) {
+    const uint32_t b = blockIdx.x * blockDim.x + threadIdx.x;
+    const int lane = threadIdx.x & 31;
+    const uint32_t nt = b < n_buckets ? ntasks[b] : 1u;
+    uint32_t todo = __ballot_sync(0xffffffffu, nt > 1u);
+    while (todo) {
+        const int src = __ffs(todo) - 1;
+        todo &= todo - 1;
+        const uint32_t bb = __shfl_sync(0xffffffffu, b, src);
+        const uint32_t n = __shfl_sync(0xffffffffu, nt, src);
+        const uint32_t o = __shfl_sync(0xffffffffu, b < n_buckets ? task_off[b] : 0u, src);
+        XYZZ<F> acc = XYZZ<F>::inf();
+        for (uint32_t j = lane; j < n; j += 32) acc.add(ld_vec(partials + o + j));
+#pragma unroll 1
+        for (int d = 16; d >= 1; d >>= 1) {
+            const XYZZ<F> other = shfl_down_point(acc, d);
+            if (lane < d) acc.add(other);
+        }
+        if (lane == 0) st_vec(buckets + bb, acc);
+    }
 }
 
 // 5. reduction tree.  A node over a range of `len` consecutive buckets carries

@@ -21,7 +21,8 @@ struct MsmLayout {
     MsmPlan plan;
     size_t n, M;  // M = W * nb buckets
     size_t off_digits, off_sorted, off_counts, off_offsets, off_cursor, off_bsums, off_buckets, off_S[2], off_W[2], total;
-    uint32_t scan_blocks;
+    size_t off_ntasks, off_task_off, off_task_bucket, off_partials;
+    uint32_t scan_blocks, chunk, max_tasks;
     MsmLayout(size_t n_, int c_override) {
         n = n_;
         plan = msm_plan(n, c_override);
@@ -35,6 +36,14 @@ struct MsmLayout {
         scan_blocks = (uint32_t)((M + SCAN_CHUNK - 1) / SCAN_CHUNK);
         off_bsums = a.off; a.take((size_t)scan_blocks * 4);
         off_buckets = a.off; a.take(M * sizeof(XYZZ<F>));
+        // task splitting: chunk = twice the mean bucket load (at least 64 points)
+        const size_t mean = n / plan.nb;
+        chunk = (uint32_t)(2 * mean < 64 ? 64 : 2 * mean);
+        max_tasks = (uint32_t)(M + ((size_t)plan.W * n) / chunk + 1);
+        off_ntasks = a.off; a.take(M * 4);
+        off_task_off = a.off; a.take(M * 4);
+        off_task_bucket = a.off; a.take((size_t)max_tasks * 4);
+        off_partials = a.off; a.take((size_t)max_tasks * sizeof(XYZZ<F>));
         const size_t nodes0 = M / plan.L0;
         for (int i = 0; i < 2; ++i) {
             off_S[i] = a.off; a.take((i == 0 ? nodes0 : nodes0 / 2 + 1) * sizeof(XYZZ<F>));
@@ -61,6 +70,10 @@ int msm_run_impl(b200_ctx* ctx, const Affine<F>* d_bases, const Fr* d_scalars, c
     uint32_t* cursor = (uint32_t*)(base + lay.off_cursor);
     uint32_t* bsums = (uint32_t*)(base + lay.off_bsums);
     XYZZ<F>* buckets = (XYZZ<F>*)(base + lay.off_buckets);
+    uint32_t* ntasks = (uint32_t*)(base + lay.off_ntasks);
+    uint32_t* task_off = (uint32_t*)(base + lay.off_task_off);
+    uint32_t* task_bucket = (uint32_t*)(base + lay.off_task_bucket);
+    XYZZ<F>* partials = (XYZZ<F>*)(base + lay.off_partials);
     XYZZ<F>* S[2] = {(XYZZ<F>*)(base + lay.off_S[0]), (XYZZ<F>*)(base + lay.off_S[1])};
     XYZZ<F>* Wt[2] = {(XYZZ<F>*)(base + lay.off_W[0]), (XYZZ<F>*)(base + lay.off_W[1])};
     cudaStream_t st = ctx->stream;
@@ -84,8 +97,25 @@ int msm_run_impl(b200_ctx* ctx, const Affine<F>* d_bases, const Fr* d_scalars, c
         B2_CUDA(ctx, cudaGetLastError());
     }
     {
+        const int bs = 256;
+        msm_task_count_kernel<<<(M + bs - 1) / bs, bs, 0, st>>>(counts, M, lay.chunk, ntasks);
+        B2_CUDA(ctx, cudaGetLastError());
+        msm_scan_sums_kernel<<<lay.scan_blocks, SCAN_THREADS, 0, st>>>(ntasks, M, bsums);
+        B2_CUDA(ctx, cudaGetLastError());
+        msm_scan_top_kernel<<<1, 1024, 0, st>>>(bsums, lay.scan_blocks);
+        B2_CUDA(ctx, cudaGetLastError());
+        msm_scan_final_kernel<<<lay.scan_blocks, SCAN_THREADS, 0, st>>>(ntasks, M, bsums, task_off, nullptr);
+        B2_CUDA(ctx, cudaGetLastError());
+        B2_CUDA(ctx, cudaMemsetAsync(task_bucket, 0xff, (size_t)lay.max_tasks * 4, st));
+        msm_task_fill_kernel<<<(M + bs - 1) / bs, bs, 0, st>>>(ntasks, task_off, M, task_bucket);
+        B2_CUDA(ctx, cudaGetLastError());
+    }
+    {
         const int bs = 128;
-        msm_accumulate_kernel<F><<<(M + bs - 1) / bs, bs, 0, st>>>(d_bases, sorted, offsets, counts, M, buckets);
+        msm_accumulate_kernel<F><<<(lay.max_tasks + bs - 1) / bs, bs, 0, st>>>(d_bases, sorted, offsets, counts, task_bucket, task_off,
+                                                                            ntasks, lay.max_tasks, lay.chunk, buckets, partials);
+        B2_CUDA(ctx, cudaGetLastError());
+        msm_combine_kernel<F><<<(M + bs - 1) / bs, bs, 0, st>>>(task_off, ntasks, M, partials, buckets);
         B2_CUDA(ctx, cudaGetLastError());
     }
     // reduction tree

@@ -268,7 +268,7 @@ int ntt_mul_sub(b200_ctx* ctx, Fr* a, const Fr* b, const Fr* c, size_t n) {
 // computeH (prove.go:353-396) with the scalings folded:
 //   x <- FFTInverse(x, DIF)            (prove.go:369-371)  1/n   } one table product on the last
 //   x <- FFT(x, DIT, OnCoset)          (prove.go:373-375)  g^br(i)} store of the inverse transform
-//   a <- (a*b - c) * den               (prove.go:377-390)  den folded into a's table
+//   a <- (a*b - c) * den               (prove.go:377-390)  den folded into a's and c's table
 //   a <- FFTInverse(a, DIF, OnCoset)   (prove.go:393)      g^-br(i)/n on the last store
 // Field elements are canonical (fully reduced) so re-associating the products is bit-exact.
 int ntt_compute_h(b200_ctx* ctx, NttDomain* d, Fr* a, Fr* b, Fr* c) {
@@ -278,7 +278,7 @@ int ntt_compute_h(b200_ctx* ctx, NttDomain* d, Fr* a, Fr* b, Fr* c) {
     B2_TRY(ntt_domain_table(ctx, d, NttDomain::COSETINV_BR, &cinv));
     B2_TRY(ntt_run(ctx, d, a, 1, 0, nullptr, ha, nullptr));
     B2_TRY(ntt_run(ctx, d, b, 1, 0, nullptr, hbc, nullptr));
-    B2_TRY(ntt_run(ctx, d, c, 1, 0, nullptr, hbc, nullptr));
+    B2_TRY(ntt_run(ctx, d, c, 1, 0, nullptr, ha, nullptr));  // (a*b - c)*den = (a*den)*b - c*den
     B2_TRY(ntt_run(ctx, d, a, 0, 1, nullptr, nullptr, nullptr));
     B2_TRY(ntt_run(ctx, d, b, 0, 1, nullptr, nullptr, nullptr));
     B2_TRY(ntt_run(ctx, d, c, 0, 1, nullptr, nullptr, nullptr));

@@ -13,8 +13,8 @@ struct NttDomain {
         COSET_BR,          // g^bitrev(i)             pre-scale, FFT DIT OnCoset      (prove.go:373-375)
         COSETINV_NAT,      // g^-i / n                post-scale, FFTInverse DIT OnCoset
         COSETINV_BR,       // g^-bitrev(i) / n        post-scale, FFTInverse DIF OnCoset (prove.go:393)
-        H_BC,              // g^bitrev(i) / n         FFTInverse DIF fused with the following coset FFT DIT
-        H_A,               // g^bitrev(i) / n * den   same, with den = 1/(g^n - 1) folded in (prove.go:377-390)
+        H_BC,              // g^bitrev(i) / n         FFTInverse DIF fused with the following coset FFT DIT (vector b)
+        H_A,               // g^bitrev(i) / n * den   same for vectors a and c, den = 1/(g^n - 1) folded in (prove.go:377-390)
         NUM_TABLES
     };
     unsigned log_n = 0;

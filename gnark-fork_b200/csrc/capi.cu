@@ -74,6 +74,8 @@ void b200_destroy(b200_ctx* ctx) {
     cudaStreamSynchronize(ctx->stream);
     ntt_domain_free_all(ctx);
     if (ctx->scratch) cudaFree(ctx->scratch);
+    for (auto& sp : ctx->prof_spans) { cudaEventDestroy(sp.e0); cudaEventDestroy(sp.e1); }
+    for (auto e : ctx->prof_pool) cudaEventDestroy(e);
     cudaEventDestroy(ctx->ev0);
     cudaEventDestroy(ctx->ev1);
     cudaStreamDestroy(ctx->stream);
@@ -326,6 +328,46 @@ int b200_groth16_prove_core(b200_ctx* ctx, const b200_groth16_pk* pk, const uint
     if (!pk || !out || !w || (n_constraints && (!a || !b || !c)) || (n_remove && !k_remove))
         return ctx->fail(B200_ERR_ARG, "null argument");
     return groth16_prove_core(ctx, pk, a, b, c, n_constraints, w, k_remove, n_remove, out, timings);
+}
+
+int b200_groth16_prove_core_dev(b200_ctx* ctx, const b200_groth16_pk* pk, const void* a_dev, const void* b_dev,
+                                const void* c_dev, size_t n_constraints, const void* w_dev, b200_groth16_out* out,
+                                b200_timings* timings) {
+    B2_ENTER(ctx, B200_BN254);
+    if (!pk || !out || !w_dev || (n_constraints && (!a_dev || !b_dev || !c_dev)))
+        return ctx->fail(B200_ERR_ARG, "null argument");
+    return groth16_prove_core(ctx, pk, (const uint64_t*)a_dev, (const uint64_t*)b_dev, (const uint64_t*)c_dev,
+                              n_constraints, (const uint64_t*)w_dev, nullptr, 0, out, timings);
+}
+
+// ---- profiling ---------------------------------------------------------------------------
+int b200_profile_start(b200_ctx* ctx) {
+    B2_ENTER(ctx, B200_BN254);
+    B2_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    for (auto& sp : ctx->prof_spans) { ctx->prof_pool.push_back(sp.e0); ctx->prof_pool.push_back(sp.e1); }
+    ctx->prof_spans.clear();
+    ctx->prof_on = true;
+    return B200_OK;
+}
+int b200_profile_read(b200_ctx* ctx, b200_profile* out) {
+    B2_ENTER(ctx, B200_BN254);
+    if (!out) return ctx->fail(B200_ERR_ARG, "null output");
+    B2_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    memset(out, 0, sizeof *out);
+    for (auto& sp : ctx->prof_spans) {
+        float ms = 0.f;
+        if (cudaEventElapsedTime(&ms, sp.e0, sp.e1) == cudaSuccess && sp.slot >= 0 && sp.slot < B200_PROF_SLOTS) {
+            out->ms[sp.slot] += ms;
+            out->launches[sp.slot] += 1;
+            out->units[sp.slot] += sp.units;
+        }
+        ctx->prof_pool.push_back(sp.e0);
+        ctx->prof_pool.push_back(sp.e1);
+    }
+    cudaGetLastError();
+    ctx->prof_spans.clear();
+    ctx->prof_on = false;
+    return B200_OK;
 }
 
 }  // extern "C"

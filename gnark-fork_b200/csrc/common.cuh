@@ -24,6 +24,29 @@ struct b200_ctx {
     size_t scratch_bytes = 0;
     int msm_c_override = 0;                 // B200_MSM_C env (tuning): window width
 
+    // optional per-kernel-class timing (b200_profile_*): CUDA event pairs on `stream`
+    bool prof_on = false;
+    struct ProfSpan { int slot; double units; cudaEvent_t e0, e1; };
+    std::vector<ProfSpan> prof_spans;
+    std::vector<cudaEvent_t> prof_pool;
+    cudaEvent_t prof_event() {
+        cudaEvent_t e = nullptr;
+        if (!prof_pool.empty()) { e = prof_pool.back(); prof_pool.pop_back(); }
+        else cudaEventCreate(&e);
+        return e;
+    }
+    // returns an index to pass to prof_end (-1 when profiling is off)
+    int prof_begin(int slot, double units) {
+        if (!prof_on) return -1;
+        ProfSpan sp{slot, units, prof_event(), prof_event()};
+        cudaEventRecord(sp.e0, stream);
+        prof_spans.push_back(sp);
+        return (int)prof_spans.size() - 1;
+    }
+    void prof_end(int idx) {
+        if (idx >= 0) cudaEventRecord(prof_spans[idx].e1, stream);
+    }
+
     int fail(int status, const char* what, const char* detail = nullptr) {
         err = what;
         if (detail) { err += ": "; err += detail; }

@@ -13,11 +13,11 @@ static void shard_range(size_t len, int idx, int cnt, size_t* lo, size_t* hi) {
 }
 
 template <class T>
-static int upload_range(b200_ctx* ctx, DevBuf& dst, const uint64_t* host, size_t lo, size_t hi) {
+static int upload_range(b200_ctx* ctx, DevBuf& dst, const uint64_t* host, size_t lo, size_t hi, bool presliced) {
     const size_t cnt = hi - lo;
     B2_CUDA(ctx, dst.alloc(cnt * sizeof(T)));
     if (cnt)
-        B2_CUDA(ctx, cudaMemcpyAsync(dst.p, reinterpret_cast<const char*>(host) + lo * sizeof(T), cnt * sizeof(T),
+        B2_CUDA(ctx, cudaMemcpyAsync(dst.p, reinterpret_cast<const char*>(host) + (presliced ? 0 : lo) * sizeof(T), cnt * sizeof(T),
                                      cudaMemcpyHostToDevice, ctx->stream));
     return B200_OK;
 }
@@ -53,18 +53,19 @@ int groth16_pk_upload(b200_ctx* ctx, const b200_groth16_pk_desc* d, b200_groth16
     memcpy(coset.l, d->coset_gen, 32);
     int st = ntt_domain_get(ctx, d->log_n, gen, coset, &pk->dom);
     const int si = d->shard_index, sc = d->shard_count;
+    const bool ps = d->presliced != 0;
     size_t lo, hi;
     if (st == B200_OK) { shard_range(d->n_a, si, sc, &lo, &hi); pk->n_a = hi - lo;
-        st = upload_range<G1Affine>(ctx, pk->A, d->g1_a, lo, hi);
+        st = upload_range<G1Affine>(ctx, pk->A, d->g1_a, lo, hi, ps);
         if (st == B200_OK) st = upload_wire_map(ctx, pk->mapA, d->infinity_a, d->n_wires, d->n_a, lo, hi); }
     if (st == B200_OK) { shard_range(d->n_b, si, sc, &lo, &hi); pk->n_b = hi - lo;
-        st = upload_range<G1Affine>(ctx, pk->B, d->g1_b, lo, hi);
-        if (st == B200_OK) st = upload_range<G2Affine>(ctx, pk->G2B, d->g2_b, lo, hi);
+        st = upload_range<G1Affine>(ctx, pk->B, d->g1_b, lo, hi, ps);
+        if (st == B200_OK) st = upload_range<G2Affine>(ctx, pk->G2B, d->g2_b, lo, hi, ps);
         if (st == B200_OK) st = upload_wire_map(ctx, pk->mapB, d->infinity_b, d->n_wires, d->n_b, lo, hi); }
     if (st == B200_OK) { shard_range(d->n_k, si, sc, &lo, &hi); pk->n_k = hi - lo; pk->k_lo = lo;
-        st = upload_range<G1Affine>(ctx, pk->K, d->g1_k, lo, hi); }
+        st = upload_range<G1Affine>(ctx, pk->K, d->g1_k, lo, hi, ps); }
     if (st == B200_OK) { shard_range(d->n_z, si, sc, &lo, &hi); pk->n_z = hi - lo; pk->z_lo = lo;
-        st = upload_range<G1Affine>(ctx, pk->Z, d->g1_z, lo, hi); }
+        st = upload_range<G1Affine>(ctx, pk->Z, d->g1_z, lo, hi, ps); }
     // build the computeH tables now so the first proof does not pay for them
     const Fr* t;
     if (st == B200_OK) st = ntt_domain_table(ctx, pk->dom, NttDomain::H_A, &t);
@@ -117,13 +118,14 @@ int groth16_prove_core(b200_ctx* ctx, const b200_groth16_pk* pk, const uint64_t*
     struct EvGuard { cudaEvent_t* e; ~EvGuard() { for (int i = 0; i < 9; ++i) cudaEventDestroy(e[i]); } } guard{ev};
 
     B2_CUDA(ctx, cudaEventRecord(ev[0], st));
+    const int span = ctx->prof_begin(B200_PROF_COPY_IN, (double)(3 * n_constraints + pk->n_wires) * sizeof(Fr));
     const uint64_t* src[3] = {a, b, c};
     Fr* dst[3] = {d_a, d_b, d_c};
     for (int i = 0; i < 3; ++i) {
-        if (n_constraints) B2_CUDA(ctx, cudaMemcpyAsync(dst[i], src[i], n_constraints * sizeof(Fr), cudaMemcpyHostToDevice, st));
+        if (n_constraints) B2_CUDA(ctx, cudaMemcpyAsync(dst[i], src[i], n_constraints * sizeof(Fr), cudaMemcpyDefault, st));
         if (n > n_constraints) B2_CUDA(ctx, cudaMemsetAsync(dst[i] + n_constraints, 0, (n - n_constraints) * sizeof(Fr), st));
     }
-    B2_CUDA(ctx, cudaMemcpyAsync(d_w, w, pk->n_wires * sizeof(Fr), cudaMemcpyHostToDevice, st));
+    B2_CUDA(ctx, cudaMemcpyAsync(d_w, w, pk->n_wires * sizeof(Fr), cudaMemcpyDefault, st));
     if (n_remove) {
         // prove.go:238-242: K scalars are W[nb_public:] minus the committed wires
         std::vector<uint32_t> map;
@@ -137,6 +139,7 @@ int groth16_prove_core(b200_ctx* ctx, const b200_groth16_pk* pk, const uint64_t*
         B2_CUDA(ctx, cudaMemcpyAsync(d_kmap, map.data() + pk->k_lo, pk->n_k * 4, cudaMemcpyHostToDevice, st));
         B2_CUDA(ctx, cudaStreamSynchronize(st));  // `map` dies at scope exit
     }
+    ctx->prof_end(span);
     B2_CUDA(ctx, cudaEventRecord(ev[1], st));
     B2_TRY(ntt_compute_h(ctx, pk->dom, d_a, d_b, d_c));
     B2_CUDA(ctx, cudaEventRecord(ev[2], st));

@@ -79,6 +79,8 @@ int msm_run_impl(b200_ctx* ctx, const Affine<F>* d_bases, const Fr* d_scalars, c
     cudaStream_t st = ctx->stream;
     const uint32_t M = (uint32_t)lay.M;
 
+    constexpr int ACC_SLOT = sizeof(F) == sizeof(Fp) ? B200_PROF_MSM_ACC_G1 : B200_PROF_MSM_ACC_G2;
+    int span = ctx->prof_begin(B200_PROF_MSM_SORT, (double)n);
     B2_CUDA(ctx, cudaMemsetAsync(counts, 0, lay.M * 4, st));
     {
         const int bs = 256;
@@ -110,11 +112,15 @@ int msm_run_impl(b200_ctx* ctx, const Affine<F>* d_bases, const Fr* d_scalars, c
         msm_task_fill_kernel<<<(M + bs - 1) / bs, bs, 0, st>>>(ntasks, task_off, M, task_bucket);
         B2_CUDA(ctx, cudaGetLastError());
     }
+    ctx->prof_end(span);
     {
         const int bs = 128;
+        span = ctx->prof_begin(ACC_SLOT, (double)n);
         msm_accumulate_kernel<F><<<(lay.max_tasks + bs - 1) / bs, bs, 0, st>>>(d_bases, sorted, offsets, counts, task_bucket, task_off,
                                                                             ntasks, lay.max_tasks, lay.chunk, buckets, partials);
+        ctx->prof_end(span);
         B2_CUDA(ctx, cudaGetLastError());
+        span = ctx->prof_begin(B200_PROF_MSM_REDUCE, (double)n);
         msm_combine_kernel<F><<<(M + bs - 1) / bs, bs, 0, st>>>(task_off, ntasks, M, partials, buckets);
         B2_CUDA(ctx, cudaGetLastError());
     }
@@ -139,6 +145,7 @@ int msm_run_impl(b200_ctx* ctx, const Affine<F>* d_bases, const Fr* d_scalars, c
         log_len += logL;
         cur ^= 1;
     }
+    ctx->prof_end(span);
     // window sums -> host, Horner combine (c doublings per window)
     XYZZ<F> win[32];
     B2_CUDA(ctx, cudaMemcpyAsync(win, Wt[cur], (size_t)pl.W * sizeof(XYZZ<F>), cudaMemcpyDeviceToHost, st));

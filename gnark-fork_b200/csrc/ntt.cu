@@ -210,12 +210,8 @@ static uint32_t env_u32(const char* name, uint32_t dflt, uint32_t lo, uint32_t h
 
 int ntt_run(b200_ctx* ctx, NttDomain* d, Fr* data, int inverse, int dit, const Fr* pre, const Fr* post,
             const Fr* post_scalar) {
-    static bool attr_set = false;
-    if (!attr_set) {
-        B2_CUDA(ctx, cudaFuncSetAttribute(ntt_pass_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_tile_bytes(12)));
-        B2_CUDA(ctx, cudaFuncSetAttribute(ntt_pass_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_tile_bytes(12)));
-        attr_set = true;
-    }
+    B2_CUDA(ctx, cudaFuncSetAttribute(ntt_pass_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_tile_bytes(12)));
+    B2_CUDA(ctx, cudaFuncSetAttribute(ntt_pass_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_tile_bytes(12)));
     if (d->log_n == 0) {  // n = 1: every variant is the identity (1/n = 1, g^0 = 1)
         return B200_OK;
     }
@@ -237,8 +233,10 @@ int ntt_run(b200_ctx* ctx, NttDomain* d, Fr* data, int inverse, int dit, const F
         if (threads > NTT_THREADS) threads = NTT_THREADS;
         if (threads < 32) threads = 32;
         const size_t smem = smem_tile_bytes(plan[i].TL);
+        const int span = ctx->prof_begin(B200_PROF_NTT_PASS, (double)d->n() * plan[i].S * 0.5);
         if (dit) ntt_pass_kernel<1><<<tiles, threads, smem, ctx->stream>>>(a);
         else ntt_pass_kernel<0><<<tiles, threads, smem, ctx->stream>>>(a);
+        ctx->prof_end(span);
         B2_CUDA(ctx, cudaGetLastError());
     }
     return B200_OK;
@@ -260,7 +258,9 @@ int ntt_gnark(b200_ctx* ctx, NttDomain* d, Fr* data, int inverse, int dit, int o
 int ntt_mul_sub(b200_ctx* ctx, Fr* a, const Fr* b, const Fr* c, size_t n) {
     if (n == 0) return B200_OK;
     const int bs = 256;
+    const int span = ctx->prof_begin(B200_PROF_POINTWISE, (double)n);
     mul_sub_kernel<<<(unsigned)((n + bs - 1) / bs), bs, 0, ctx->stream>>>(a, b, c, n);
+    ctx->prof_end(span);
     B2_CUDA(ctx, cudaGetLastError());
     return B200_OK;
 }

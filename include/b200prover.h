@@ -89,6 +89,28 @@ int b200_fp_vec_mul(b200_ctx *ctx, int curve, const uint64_t *a, const uint64_t 
  * 32-bit IMAD; sm_mhz = clock observed by the kernel (cycles / elapsed). */
 int b200_imad_peak(b200_ctx *ctx, double *mac32_per_s, double *imad32_per_s, double *sm_mhz);
 
+/* Per-kernel-class device times, accumulated between b200_profile_start and b200_profile_read
+ * from CUDA event pairs recorded on the ctx stream around each launch (used by bench.py for the
+ * roofline of the dominant kernel; adds two event records per launch while enabled). */
+enum b200_prof_slot {
+    B200_PROF_MSM_SORT = 0,    /* digits + histogram + scan + scatter + task lists               */
+    B200_PROF_MSM_ACC_G1 = 1,  /* msm_accumulate_kernel<Fp>  (bucket accumulation, G1)           */
+    B200_PROF_MSM_ACC_G2 = 2,  /* msm_accumulate_kernel<Fp2> (bucket accumulation, G2)           */
+    B200_PROF_MSM_REDUCE = 3,  /* split-bucket combine + bucket reduction tree                   */
+    B200_PROF_NTT_PASS = 4,    /* ntt_pass_kernel launches                                       */
+    B200_PROF_POINTWISE = 5,   /* a*b - c                                                        */
+    B200_PROF_COPY_IN = 6,     /* H2D / D2D staging of a, b, c, W                                */
+    B200_PROF_SLOTS = 8
+};
+typedef struct b200_profile {
+    double ms[B200_PROF_SLOTS];       /* summed device time per slot                             */
+    uint64_t launches[B200_PROF_SLOTS]; /* spans per slot                                        */
+    double units[B200_PROF_SLOTS];    /* work units: points (MSM slots), elements*stages/2 =
+                                         butterflies (NTT), elements (pointwise), bytes (copy)   */
+} b200_profile;
+int b200_profile_start(b200_ctx *ctx);
+int b200_profile_read(b200_ctx *ctx, b200_profile *out); /* synchronises, returns and clears    */
+
 /* ---- NTT -------------------------------------------------------------------------------------
  * fft.Domain.FFT / FFTInverse (prove.go:369-375,393); replaces iciclegnark.NttOnDevice /
  * INttOnDevice (icicle.go:489,490,502) and GenerateTwiddleFactors (:68,:73).
@@ -164,6 +186,8 @@ typedef struct b200_groth16_pk_desc {
     size_t n_wires;
     size_t nb_public;             /* r1cs.GetNbPublicVariables() (K scalars = W[nb_public:])   */
     int shard_index, shard_count; /* 0,1 for a single GPU                                      */
+    int presliced;                /* non-zero: every base pointer already addresses the first
+                                     element of this shard's range (counts stay the full ones)  */
 } b200_groth16_pk_desc;
 
 int b200_groth16_pk_upload(b200_ctx *ctx, int curve, const b200_groth16_pk_desc *desc, b200_groth16_pk **out);
@@ -193,6 +217,12 @@ int b200_groth16_prove_core(b200_ctx *ctx, const b200_groth16_pk *pk, const uint
                             const uint64_t *c, size_t n_constraints, const uint64_t *w,
                             const uint32_t *k_remove, size_t n_remove, b200_groth16_out *out,
                             b200_timings *timings);
+
+/* Same with a, b, c (n_constraints elements each) and w (n_wires) already resident on the device
+ * (they are copied device-to-device into the workspace; the caller's buffers are not modified). */
+int b200_groth16_prove_core_dev(b200_ctx *ctx, const b200_groth16_pk *pk, const void *a_dev, const void *b_dev,
+                                const void *c_dev, size_t n_constraints, const void *w_dev,
+                                b200_groth16_out *out, b200_timings *timings);
 
 /* Host mirror of groth16_bn254.Prove's tail (prove.go:178-321) for callers without Go: applies
  * the fix-ups to the five MSM results with the given blinding scalars r, s (Montgomery Fr) and

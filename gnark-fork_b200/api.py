@@ -48,8 +48,16 @@ class _PkDesc(C.Structure):
         ("g2_b", C.c_void_p), ("n_g2b", C.c_size_t),
         ("infinity_a", C.c_void_p), ("infinity_b", C.c_void_p),
         ("n_wires", C.c_size_t), ("nb_public", C.c_size_t),
-        ("shard_index", C.c_int), ("shard_count", C.c_int),
+        ("shard_index", C.c_int), ("shard_count", C.c_int), ("presliced", C.c_int),
     ]
+
+
+PROF_SLOTS = ("msm_sort", "msm_acc_g1", "msm_acc_g2", "msm_reduce", "ntt_pass", "pointwise", "copy_in", "_7")
+
+
+class _Profile(C.Structure):
+    _fields_ = [("ms", C.c_double * 8), ("launches", C.c_uint64 * 8), ("units", C.c_double * 8),
+                ("kernel_launches", C.c_uint64)]
 
 
 def load_library():
@@ -96,6 +104,9 @@ def load_library():
         "b200_groth16_pk_upload": (i, [vp, i, C.POINTER(_PkDesc), C.POINTER(vp)]),
         "b200_groth16_pk_free": (i, [vp, vp]),
         "b200_groth16_prove_core": (i, [vp, vp, vp, vp, vp, sz, vp, vp, sz, C.POINTER(Groth16MsmOut), C.POINTER(_Timings)]),
+        "b200_groth16_prove_core_dev": (i, [vp, vp, vp, vp, vp, sz, vp, C.POINTER(Groth16MsmOut), C.POINTER(_Timings)]),
+        "b200_profile_start": (i, [vp]),
+        "b200_profile_read": (i, [vp, C.POINTER(_Profile)]),
         "b200_groth16_finalize": (i, [C.POINTER(Groth16MsmOut), vp, vp, vp, vp, vp, vp, vp, vp, vp, vp]),
         "b200_groth16_proof_bytes": (i, [vp, vp, vp, vp, sz]),
     }
@@ -348,7 +359,10 @@ class Context:
 
     # -- Groth16
     def groth16_pk_upload(self, *, log_n, generator, coset_gen, g1_a, g1_b, g1_k, g1_z, g2_b, infinity_a,
-                          infinity_b, nb_public, shard_index=0, shard_count=1) -> Groth16ProvingKey:
+                          infinity_b, nb_public, shard_index=0, shard_count=1, presliced=False,
+                          full_counts=None) -> Groth16ProvingKey:
+        """presliced=True: the base arrays hold only this shard's point range; full_counts =
+        dict(a=, b=, k=, z=) then gives the full lengths of pk.G1.A/B/K/Z."""
         keep = dict(gen=_u64(generator), cg=_u64(coset_gen), a=_u64(g1_a, (-1, 8)), b=_u64(g1_b, (-1, 8)),
                     k=_u64(g1_k, (-1, 8)), z=_u64(g1_z, (-1, 8)), g2b=_u64(g2_b, (-1, 16)),
                     ia=np.ascontiguousarray(infinity_a, dtype=np.uint8), ib=np.ascontiguousarray(infinity_b, dtype=np.uint8))
@@ -362,7 +376,10 @@ class Context:
         d.g2_b, d.n_g2b = _ptr(keep["g2b"]), keep["g2b"].shape[0]
         d.infinity_a, d.infinity_b = _ptr(keep["ia"]), _ptr(keep["ib"])
         d.n_wires, d.nb_public = keep["ia"].shape[0], nb_public
-        d.shard_index, d.shard_count = shard_index, shard_count
+        d.shard_index, d.shard_count, d.presliced = shard_index, shard_count, int(bool(presliced))
+        if presliced:
+            d.n_a, d.n_b, d.n_k, d.n_z = (full_counts[k] for k in ("a", "b", "k", "z"))
+            d.n_g2b = d.n_b
         h = C.c_void_p()
         self._check(self.lib.b200_groth16_pk_upload(self.h, BN254, C.byref(d), C.byref(h)))
         return Groth16ProvingKey(self, h, None)
@@ -376,3 +393,23 @@ class Context:
                                                      _ptr(kr), 0 if kr is None else kr.shape[0],
                                                      C.byref(out), C.byref(tm)))
         return out, {k: getattr(tm, k) for k, _ in _Timings._fields_}
+
+    def groth16_prove_core_dev(self, pk: Groth16ProvingKey, a: DeviceVector, b: DeviceVector, c: DeviceVector,
+                               n_constraints: int, w: DeviceVector):
+        """Same with a, b, c, W already resident on the device (copied D2D into the workspace)."""
+        out, tm = Groth16MsmOut(), _Timings()
+        self._check(self.lib.b200_groth16_prove_core_dev(self.h, pk.h, a.ptr, b.ptr, c.ptr, n_constraints, w.ptr,
+                                                         C.byref(out), C.byref(tm)))
+        return out, {k: getattr(tm, k) for k, _ in _Timings._fields_}
+
+    # -- per-kernel-class device times (CUDA events on the launching stream)
+    def profile_start(self):
+        self._check(self.lib.b200_profile_start(self.h))
+
+    def profile_read(self):
+        p = _Profile()
+        self._check(self.lib.b200_profile_read(self.h, C.byref(p)))
+        out = {name: {"ms": p.ms[i], "launches": int(p.launches[i]), "units": p.units[i]}
+               for i, name in enumerate(PROF_SLOTS) if not name.startswith("_")}
+        out["kernel_launches"] = int(p.kernel_launches)
+        return out

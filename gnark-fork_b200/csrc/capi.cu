@@ -347,6 +347,7 @@ int b200_profile_start(b200_ctx* ctx) {
     for (auto& sp : ctx->prof_spans) { ctx->prof_pool.push_back(sp.e0); ctx->prof_pool.push_back(sp.e1); }
     ctx->prof_spans.clear();
     ctx->prof_on = true;
+    ctx->n_launches = 0;
     return B200_OK;
 }
 int b200_profile_read(b200_ctx* ctx, b200_profile* out) {
@@ -365,6 +366,7 @@ int b200_profile_read(b200_ctx* ctx, b200_profile* out) {
         ctx->prof_pool.push_back(sp.e1);
     }
     cudaGetLastError();
+    out->kernel_launches = ctx->n_launches;
     ctx->prof_spans.clear();
     ctx->prof_on = false;
     return B200_OK;

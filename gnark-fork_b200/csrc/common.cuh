@@ -26,6 +26,7 @@ struct b200_ctx {
 
     // optional per-kernel-class timing (b200_profile_*): CUDA event pairs on `stream`
     bool prof_on = false;
+    uint64_t n_launches = 0;                // kernel launches since b200_profile_start
     struct ProfSpan { int slot; double units; cudaEvent_t e0, e1; };
     std::vector<ProfSpan> prof_spans;
     std::vector<cudaEvent_t> prof_pool;

@@ -134,7 +134,9 @@ int msm_run_impl(b200_ctx* ctx, const Affine<F>* d_bases, const Fr* d_scalars, c
         B2_CUDA(ctx, cudaGetLastError());
     }
     int cur = 0;
+    ctx->n_launches += 13;  // digits, 2 x 3 scan, scatter, task count/fill, accumulate, combine, leaf
     while (T > 1) {
+        ctx->n_launches += 1;
         const uint32_t L = T < pl.L ? T : pl.L;
         uint32_t logL = 0;
         while ((1u << logL) < L) ++logL;

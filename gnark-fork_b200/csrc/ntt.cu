@@ -237,6 +237,7 @@ int ntt_run(b200_ctx* ctx, NttDomain* d, Fr* data, int inverse, int dit, const F
         if (dit) ntt_pass_kernel<1><<<tiles, threads, smem, ctx->stream>>>(a);
         else ntt_pass_kernel<0><<<tiles, threads, smem, ctx->stream>>>(a);
         ctx->prof_end(span);
+        ctx->n_launches += 1;
         B2_CUDA(ctx, cudaGetLastError());
     }
     return B200_OK;
@@ -261,6 +262,7 @@ int ntt_mul_sub(b200_ctx* ctx, Fr* a, const Fr* b, const Fr* c, size_t n) {
     const int span = ctx->prof_begin(B200_PROF_POINTWISE, (double)n);
     mul_sub_kernel<<<(unsigned)((n + bs - 1) / bs), bs, 0, ctx->stream>>>(a, b, c, n);
     ctx->prof_end(span);
+    ctx->n_launches += 1;
     B2_CUDA(ctx, cudaGetLastError());
     return B200_OK;
 }

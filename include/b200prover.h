@@ -107,6 +107,7 @@ typedef struct b200_profile {
     uint64_t launches[B200_PROF_SLOTS]; /* spans per slot                                        */
     double units[B200_PROF_SLOTS];    /* work units: points (MSM slots), elements*stages/2 =
                                          butterflies (NTT), elements (pointwise), bytes (copy)   */
+    uint64_t kernel_launches;         /* every kernel of this library launched since start       */
 } b200_profile;
 int b200_profile_start(b200_ctx *ctx);
 int b200_profile_read(b200_ctx *ctx, b200_profile *out); /* synchronises, returns and clears    */

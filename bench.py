@@ -329,18 +329,8 @@ def gpu_arm(args):
     e2e_s = max_over_ranks((time.perf_counter() - t0) / args.steps)
     if dist is not None:
         # strong scaling: partial sums (576 B per rank) gathered and added on the host of rank 0
-        import torch
-        od = o.as_dict()
-        flat = torch.from_numpy(np.concatenate([od[k] for k in ("ar", "bs1", "krs", "krs2", "bs2")]).view(np.int64)).cuda(local)
-        gathered = [torch.empty_like(flat) for _ in range(world)]
         t1 = time.perf_counter()
-        dist.all_gather(gathered, flat)
-        if rank == 0:
-            parts = [g.cpu().numpy().view(np.uint64) for g in gathered]
-            acc = parts[0]
-            for p in parts[1:]:
-                acc = np.concatenate([pkg.g1_jac_add(acc[12 * i:12 * i + 12], p[12 * i:12 * i + 12]) for i in range(4)] +
-                                     [pkg.g2_jac_add(acc[48:72], p[48:72])])
+        combined = pkg.sharding.gather_combine(dist, o.as_dict(), device=f"cuda:{local}")
         e2e_s += max_over_ranks(time.perf_counter() - t1)
 
     if rank != 0:

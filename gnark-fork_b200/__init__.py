@@ -11,3 +11,4 @@ from .api import (  # noqa: F401
     g1_jac_add, g2_jac_add, g1_jac_to_affine, g2_jac_to_affine, groth16_finalize, groth16_proof_bytes,
     pinned_empty, library_path, load_library, DIF, DIT, BN254,
 )
+from . import sharding  # noqa: F401,E402

@@ -77,6 +77,7 @@ def load_library():
         "b200_destroy": (None, [vp]),
         "b200_last_error": (C.c_char_p, [vp]),
         "b200_version": (C.c_char_p, []),
+        "b200_set_option": (i, [vp, C.c_char_p, C.c_long]),
         "b200_host_alloc": (vp, [sz]),
         "b200_host_free": (None, [vp]),
         "b200_dev_alloc": (i, [vp, sz, C.POINTER(vp)]),
@@ -279,6 +280,9 @@ class Context:
 
     def sync(self):
         self._check(self.lib.b200_sync(self.h))
+
+    def set_option(self, key: str, value: int):
+        self._check(self.lib.b200_set_option(self.h, key.encode(), int(value)))
 
     # -- element-wise / roofline
     def fr_vec_mul(self, a, b):

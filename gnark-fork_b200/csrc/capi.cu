@@ -340,6 +340,17 @@ int b200_groth16_prove_core_dev(b200_ctx* ctx, const b200_groth16_pk* pk, const 
                               n_constraints, (const uint64_t*)w_dev, nullptr, 0, out, timings);
 }
 
+// ---- tuning knobs -------------------------------------------------------------------------
+int b200_set_option(b200_ctx* ctx, const char* key, long value) {
+    if (!ctx || !key) return B200_ERR_ARG;
+    const std::string k(key);
+    if (k == "msm_c") { if (value != 0 && (value < 4 || value > 24)) return ctx->fail(B200_ERR_ARG, "msm_c out of range"); ctx->msm_c_override = (int)value; }
+    else if (k == "ntt_tile_log") { if (value < 6 || value > 12) return ctx->fail(B200_ERR_ARG, "ntt_tile_log out of range"); ctx->ntt_tile_log = (int)value; }
+    else if (k == "ntt_strided_stages") { if (value < 1 || value > 12) return ctx->fail(B200_ERR_ARG, "ntt_strided_stages out of range"); ctx->ntt_strided_stages = (int)value; }
+    else return ctx->fail(B200_ERR_ARG, "unknown option", key);
+    return B200_OK;
+}
+
 // ---- profiling ---------------------------------------------------------------------------
 int b200_profile_start(b200_ctx* ctx) {
     B2_ENTER(ctx, B200_BN254);

@@ -22,7 +22,8 @@ struct b200_ctx {
     std::vector<b200::NttDomain*> domains;  // cache keyed by (log_n, generator, coset_gen)
     void* scratch = nullptr;                // grow-only workspace shared by MSM / prove calls
     size_t scratch_bytes = 0;
-    int msm_c_override = 0;                 // B200_MSM_C env (tuning): window width
+    int msm_c_override = 0;                 // tuning knobs (b200_set_option / B200_MSM_C env)
+    int ntt_tile_log = 10, ntt_strided_stages = 8;   // measured best: 2 CTAs of 512 threads per SM
 
     // optional per-kernel-class timing (b200_profile_*): CUDA event pairs on `stream`
     bool prof_on = false;

@@ -51,7 +51,8 @@ inline MsmPlan msm_plan(size_t n, int c_override) {
     else if (n <= ((size_t)1 << 14)) c = 10;
     else if (n <= ((size_t)1 << 17)) c = 12;
     else if (n <= ((size_t)1 << 19)) c = 14;
-    else c = 16;
+    else if (n <= ((size_t)1 << 21)) c = 15;
+    else c = 17;   // 15 x 17 = 255: full top window; measured best at 2^22..2^24 (scripts/tune_sweep.py)
     MsmPlan p;
     p.c = c;
     p.W = msm_num_windows(c);
@@ -94,12 +95,16 @@ __device__ __forceinline__ void st_vec(T* p, const T& v) {
 
 // 1. digits + histogram.  idx_map (optional): scalar i is scalars[idx_map[i]] (wire filtering by
 // pk.InfinityA/B, prove.go:154-175, done as a gather instead of three host-side copies).
+// Same-bucket lanes of a warp are merged with match.any before touching the counter: skewed
+// digits (the top window only holds 254 - c(W-1) bits; real witnesses are full of 0/1) would
+// otherwise serialise millions of atomics on one L2 address.
 static __global__ void msm_digits_kernel(const Fr* __restrict__ scalars, const uint32_t* __restrict__ idx_map, uint32_t n,
                                   int c, int W, int32_t* __restrict__ digits, uint32_t* __restrict__ counts, uint32_t nb) {
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n) return;
-    const uint32_t src = idx_map ? idx_map[i] : i;
-    const Fr s = ld_vec(scalars + src).from_mont();
+    const bool valid = i < n;
+    const int lane = threadIdx.x & 31;
+    Fr s = Fr::zero();
+    if (valid) s = ld_vec(scalars + (idx_map ? idx_map[i] : i)).from_mont();
     int32_t carry = 0;
     const uint32_t mask = (1u << c) - 1u;
     for (int w = 0; w < W; ++w) {
@@ -109,8 +114,10 @@ static __global__ void msm_digits_kernel(const Fr* __restrict__ scalars, const u
         int32_t d = (int32_t)raw + carry;
         carry = 0;
         if (d > (1 << (c - 1))) { d -= (1 << c); carry = 1; }
-        digits[(size_t)w * n + i] = d;
-        if (d != 0) atomicAdd(&counts[(size_t)w * nb + (uint32_t)((d < 0 ? -d : d) - 1)], 1u);
+        if (valid) digits[(size_t)w * n + i] = d;
+        const uint32_t key = (valid && d != 0) ? (uint32_t)((d < 0 ? -d : d) - 1) : 0xffffffffu;
+        const uint32_t peers = __match_any_sync(0xffffffffu, key);
+        if (key != 0xffffffffu && lane == __ffs(peers) - 1) atomicAdd(&counts[(size_t)w * nb + key], (uint32_t)__popc(peers));
     }
 }
 
@@ -192,13 +199,17 @@ static __global__ void msm_scan_final_kernel(const uint32_t* __restrict__ in, ui
 static __global__ void msm_scatter_kernel(const int32_t* __restrict__ digits, uint32_t n, int W, uint32_t nb,
                                    uint32_t* __restrict__ cursor, uint32_t* __restrict__ sorted) {
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n) return;
+    const bool valid = i < n;
+    const int lane = threadIdx.x & 31;
     for (int w = 0; w < W; ++w) {
-        const int32_t d = digits[(size_t)w * n + i];
-        if (d == 0) continue;
-        const uint32_t b = (uint32_t)((d < 0 ? -d : d) - 1);
-        const uint32_t pos = atomicAdd(&cursor[(size_t)w * nb + b], 1u);
-        sorted[pos] = i | (d < 0 ? 0x80000000u : 0u);
+        const int32_t d = valid ? digits[(size_t)w * n + i] : 0;
+        const uint32_t key = d != 0 ? (uint32_t)((d < 0 ? -d : d) - 1) : 0xffffffffu;
+        const uint32_t peers = __match_any_sync(0xffffffffu, key);
+        const int leader = __ffs(peers) - 1;
+        uint32_t base = 0;
+        if (key != 0xffffffffu && lane == leader) base = atomicAdd(&cursor[(size_t)w * nb + key], (uint32_t)__popc(peers));
+        base = __shfl_sync(0xffffffffu, base, leader);
+        if (key != 0xffffffffu) sorted[base + __popc(peers & ((1u << lane) - 1u))] = i | (d < 0 ? 0x80000000u : 0u);
     }
 }
 
@@ -206,12 +217,23 @@ static __global__ void msm_scatter_kernel(const int32_t* __restrict__ digits, ui
 // oversized bucket (the top window only sees 254 - c*(W-1) scalar bits; real witnesses are full of
 // 0/1 values) cannot serialise the launch: ntasks[b] = max(1, ceil(count[b] / chunk)), an
 // exclusive scan gives task_off[b], msm_task_fill_kernel writes the owning bucket of every task.
+// A bucket is cut into at most MSM_MAX_TASKS_PER_BUCKET equal pieces (so the warp-cooperative merge
+// stays short); oversized pieces are scheduled first by the size ordering below.
+constexpr uint32_t MSM_MAX_TASKS_PER_BUCKET = 4096;
+// piece j of a bucket with cnt points cut into nt pieces: [j*cb, min(cnt, (j+1)*cb)), cb = ceil(cnt/nt)
+__device__ __forceinline__ void msm_task_range(uint32_t cnt, uint32_t nt, uint32_t j, uint32_t* first, uint32_t* size) {
+    const uint32_t cb = (cnt + nt - 1u) / nt;
+    const uint32_t j0 = j * cb;
+    *first = j0;
+    *size = j0 >= cnt ? 0u : (cnt - j0 < cb ? cnt - j0 : cb);
+}
 static __global__ void msm_task_count_kernel(const uint32_t* __restrict__ counts, uint32_t n_buckets, uint32_t chunk,
                                              uint32_t* __restrict__ ntasks) {
     const uint32_t b = blockIdx.x * blockDim.x + threadIdx.x;
     if (b >= n_buckets) return;
     const uint32_t c = counts[b];
-    ntasks[b] = c <= chunk ? 1u : (c + chunk - 1u) / chunk;
+    uint32_t nt = c <= chunk ? 1u : (c + chunk - 1u) / chunk;
+    ntasks[b] = nt > MSM_MAX_TASKS_PER_BUCKET ? MSM_MAX_TASKS_PER_BUCKET : nt;
 }
 static __global__ void msm_task_fill_kernel(const uint32_t* __restrict__ ntasks, const uint32_t* __restrict__ task_off,
                                             uint32_t n_buckets, uint32_t* __restrict__ task_bucket) {
@@ -221,22 +243,99 @@ static __global__ void msm_task_fill_kernel(const uint32_t* __restrict__ ntasks,
     for (uint32_t j = 0; j < nt; ++j) task_bucket[o + j] = b;
 }
 
-// one thread per task; a single-task bucket is written straight to buckets[], the pieces of a
-// split bucket go to partials[task] and are merged by msm_combine_kernel.
+// Task order: tasks sorted by decreasing size (counting sort over size bins) so that the 32 lanes
+// of a warp run the same trip count -- with a mean load of 32 points the Poisson spread alone
+// costs a quarter of the lanes otherwise -- and the longest tasks start first.
+constexpr int ORDER_BINS = 2048;
+constexpr int ORDER_THREADS = 256;
+__device__ __forceinline__ uint32_t msm_task_size(uint32_t t, const uint32_t* task_bucket, const uint32_t* task_off,
+                                                  const uint32_t* ntasks, const uint32_t* counts, uint32_t chunk, uint32_t* b_out) {
+    const uint32_t b = task_bucket[t];
+    *b_out = b;
+    if (b == 0xffffffffu) return 0;
+    const uint32_t nt = ntasks[b], cnt_b = counts[b];
+    if (nt == 1) return cnt_b;
+    uint32_t first, size;
+    msm_task_range(cnt_b, nt, t - task_off[b], &first, &size);
+    return size;
+}
+// bin 0 holds the largest sizes; unused task slots go to the last bin
+__device__ __forceinline__ uint32_t msm_size_bin(uint32_t size, bool used, uint32_t chunk, uint32_t shift) {
+    if (!used) return ORDER_BINS - 1;
+    const uint32_t q = (size > chunk ? chunk : size) >> shift;   // 0 .. chunk >> shift  (<= ORDER_BINS - 2)
+    return (chunk >> shift) - q;
+}
+static __global__ void msm_order_hist_kernel(const uint32_t* __restrict__ task_bucket, const uint32_t* __restrict__ task_off,
+                                             const uint32_t* __restrict__ ntasks, const uint32_t* __restrict__ counts,
+                                             uint32_t max_tasks, uint32_t chunk, uint32_t shift, uint32_t* __restrict__ hist) {
+    __shared__ uint32_t lh[ORDER_BINS];
+    for (int k = threadIdx.x; k < ORDER_BINS; k += blockDim.x) lh[k] = 0;
+    __syncthreads();
+    const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t < max_tasks) {
+        uint32_t b;
+        const uint32_t sz = msm_task_size(t, task_bucket, task_off, ntasks, counts, chunk, &b);
+        atomicAdd(&lh[msm_size_bin(sz, b != 0xffffffffu, chunk, shift)], 1u);
+    }
+    __syncthreads();
+    for (int k = threadIdx.x; k < ORDER_BINS; k += blockDim.x) if (lh[k]) atomicAdd(&hist[k], lh[k]);
+}
+// single block: exclusive scan of the ORDER_BINS bins, in place
+static __global__ void msm_order_scan_kernel(uint32_t* hist) {
+    __shared__ uint32_t carry_s;
+    if (threadIdx.x == 0) carry_s = 0;
+    __syncthreads();
+    for (int base = 0; base < ORDER_BINS; base += blockDim.x) {
+        const int k = base + threadIdx.x;
+        const uint32_t v = hist[k];
+        uint32_t total;
+        const uint32_t ex = block_exclusive_scan(v, &total);
+        const uint32_t carry = carry_s;
+        hist[k] = carry + ex;
+        __syncthreads();
+        if (threadIdx.x == 0) carry_s = carry + total;
+        __syncthreads();
+    }
+}
+static __global__ void msm_order_fill_kernel(const uint32_t* __restrict__ task_bucket, const uint32_t* __restrict__ task_off,
+                                             const uint32_t* __restrict__ ntasks, const uint32_t* __restrict__ counts,
+                                             uint32_t max_tasks, uint32_t chunk, uint32_t shift, uint32_t* __restrict__ cursor,
+                                             uint32_t* __restrict__ order) {
+    __shared__ uint32_t lh[ORDER_BINS];
+    __shared__ uint32_t lbase[ORDER_BINS];
+    for (int k = threadIdx.x; k < ORDER_BINS; k += blockDim.x) lh[k] = 0;
+    __syncthreads();
+    const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+    uint32_t bin = 0, rank = 0;
+    if (t < max_tasks) {
+        uint32_t b;
+        const uint32_t sz = msm_task_size(t, task_bucket, task_off, ntasks, counts, chunk, &b);
+        bin = msm_size_bin(sz, b != 0xffffffffu, chunk, shift);
+        rank = atomicAdd(&lh[bin], 1u);
+    }
+    __syncthreads();
+    for (int k = threadIdx.x; k < ORDER_BINS; k += blockDim.x) if (lh[k]) lbase[k] = atomicAdd(&cursor[k], lh[k]);
+    __syncthreads();
+    if (t < max_tasks) order[lbase[bin] + rank] = t;
+}
+
+// one thread per task (taken in size order); a single-task bucket is written straight to
+// buckets[], the pieces of a split bucket go to partials[task] and are merged by msm_combine_kernel.
 template <class F>
 __global__ void __launch_bounds__(128) msm_accumulate_kernel(const Affine<F>* __restrict__ bases, const uint32_t* __restrict__ sorted,
                                       const uint32_t* __restrict__ offsets, const uint32_t* __restrict__ counts,
                                       const uint32_t* __restrict__ task_bucket, const uint32_t* __restrict__ task_off,
-                                      const uint32_t* __restrict__ ntasks, uint32_t max_tasks, uint32_t chunk,
-                                      XYZZ<F>* __restrict__ buckets, XYZZ<F>* __restrict__ partials) {
-    const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
-    if (t >= max_tasks) return;
+                                      const uint32_t* __restrict__ ntasks, const uint32_t* __restrict__ order, uint32_t max_tasks,
+                                      uint32_t chunk, XYZZ<F>* __restrict__ buckets, XYZZ<F>* __restrict__ partials) {
+    const uint32_t slot = blockIdx.x * blockDim.x + threadIdx.x;
+    if (slot >= max_tasks) return;
+    const uint32_t t = order[slot];
     const uint32_t b = task_bucket[t];
     if (b == 0xffffffffu) return;
-    const uint32_t nt = ntasks[b], j0 = (t - task_off[b]) * chunk;
-    const uint32_t cnt_b = counts[b];
-    uint32_t cnt = nt == 1 ? cnt_b : (cnt_b - j0 < chunk ? cnt_b - j0 : chunk);
-    const uint32_t start = offsets[b] + (nt == 1 ? 0u : j0);
+    const uint32_t nt = ntasks[b];
+    uint32_t first, cnt;
+    msm_task_range(counts[b], nt, t - task_off[b], &first, &cnt);
+    const uint32_t start = offsets[b] + first;
     XYZZ<F> acc = XYZZ<F>::inf();
     for (uint32_t j = 0; j < cnt; ++j) {
         const uint32_t e = sorted[start + j];

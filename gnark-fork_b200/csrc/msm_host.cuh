@@ -21,8 +21,8 @@ struct MsmLayout {
     MsmPlan plan;
     size_t n, M;  // M = W * nb buckets
     size_t off_digits, off_sorted, off_counts, off_offsets, off_cursor, off_bsums, off_buckets, off_S[2], off_W[2], total;
-    size_t off_ntasks, off_task_off, off_task_bucket, off_partials;
-    uint32_t scan_blocks, chunk, max_tasks;
+    size_t off_ntasks, off_task_off, off_task_bucket, off_partials, off_order, off_order_hist;
+    uint32_t scan_blocks, chunk, max_tasks, order_shift;
     MsmLayout(size_t n_, int c_override) {
         n = n_;
         plan = msm_plan(n, c_override);
@@ -44,6 +44,10 @@ struct MsmLayout {
         off_task_off = a.off; a.take(M * 4);
         off_task_bucket = a.off; a.take((size_t)max_tasks * 4);
         off_partials = a.off; a.take((size_t)max_tasks * sizeof(XYZZ<F>));
+        off_order = a.off; a.take((size_t)max_tasks * 4);
+        off_order_hist = a.off; a.take((size_t)ORDER_BINS * 4 * 2);
+        order_shift = 0;
+        while ((chunk >> order_shift) > (uint32_t)ORDER_BINS - 2) ++order_shift;
         const size_t nodes0 = M / plan.L0;
         for (int i = 0; i < 2; ++i) {
             off_S[i] = a.off; a.take((i == 0 ? nodes0 : nodes0 / 2 + 1) * sizeof(XYZZ<F>));
@@ -74,6 +78,8 @@ int msm_run_impl(b200_ctx* ctx, const Affine<F>* d_bases, const Fr* d_scalars, c
     uint32_t* task_off = (uint32_t*)(base + lay.off_task_off);
     uint32_t* task_bucket = (uint32_t*)(base + lay.off_task_bucket);
     XYZZ<F>* partials = (XYZZ<F>*)(base + lay.off_partials);
+    uint32_t* order = (uint32_t*)(base + lay.off_order);
+    uint32_t* order_hist = (uint32_t*)(base + lay.off_order_hist);
     XYZZ<F>* S[2] = {(XYZZ<F>*)(base + lay.off_S[0]), (XYZZ<F>*)(base + lay.off_S[1])};
     XYZZ<F>* Wt[2] = {(XYZZ<F>*)(base + lay.off_W[0]), (XYZZ<F>*)(base + lay.off_W[1])};
     cudaStream_t st = ctx->stream;
@@ -111,13 +117,22 @@ int msm_run_impl(b200_ctx* ctx, const Affine<F>* d_bases, const Fr* d_scalars, c
         B2_CUDA(ctx, cudaMemsetAsync(task_bucket, 0xff, (size_t)lay.max_tasks * 4, st));
         msm_task_fill_kernel<<<(M + bs - 1) / bs, bs, 0, st>>>(ntasks, task_off, M, task_bucket);
         B2_CUDA(ctx, cudaGetLastError());
+        // size-ordered task list
+        const uint32_t ob = (lay.max_tasks + ORDER_THREADS - 1) / ORDER_THREADS;
+        B2_CUDA(ctx, cudaMemsetAsync(order_hist, 0, (size_t)ORDER_BINS * 4, st));
+        msm_order_hist_kernel<<<ob, ORDER_THREADS, 0, st>>>(task_bucket, task_off, ntasks, counts, lay.max_tasks, lay.chunk, lay.order_shift, order_hist);
+        B2_CUDA(ctx, cudaGetLastError());
+        msm_order_scan_kernel<<<1, 1024, 0, st>>>(order_hist);
+        B2_CUDA(ctx, cudaGetLastError());
+        msm_order_fill_kernel<<<ob, ORDER_THREADS, 0, st>>>(task_bucket, task_off, ntasks, counts, lay.max_tasks, lay.chunk, lay.order_shift, order_hist, order);
+        B2_CUDA(ctx, cudaGetLastError());
     }
     ctx->prof_end(span);
     {
         const int bs = 128;
         span = ctx->prof_begin(ACC_SLOT, (double)n);
         msm_accumulate_kernel<F><<<(lay.max_tasks + bs - 1) / bs, bs, 0, st>>>(d_bases, sorted, offsets, counts, task_bucket, task_off,
-                                                                            ntasks, lay.max_tasks, lay.chunk, buckets, partials);
+                                                                            ntasks, order, lay.max_tasks, lay.chunk, buckets, partials);
         ctx->prof_end(span);
         B2_CUDA(ctx, cudaGetLastError());
         span = ctx->prof_begin(B200_PROF_MSM_REDUCE, (double)n);
@@ -134,7 +149,7 @@ int msm_run_impl(b200_ctx* ctx, const Affine<F>* d_bases, const Fr* d_scalars, c
         B2_CUDA(ctx, cudaGetLastError());
     }
     int cur = 0;
-    ctx->n_launches += 13;  // digits, 2 x 3 scan, scatter, task count/fill, accumulate, combine, leaf
+    ctx->n_launches += 16;  // digits, 2 x 3 scan, scatter, task count/fill, 3 x order, accumulate, combine, leaf
     while (T > 1) {
         ctx->n_launches += 1;
         const uint32_t L = T < pl.L ? T : pl.L;

@@ -200,14 +200,6 @@ void ntt_domain_free_all(b200_ctx* ctx) {
     ctx->domains.clear();
 }
 
-static uint32_t env_u32(const char* name, uint32_t dflt, uint32_t lo, uint32_t hi) {
-    const char* v = getenv(name);
-    if (!v || !*v) return dflt;
-    long x = strtol(v, nullptr, 10);
-    if (x < (long)lo || x > (long)hi) return dflt;
-    return (uint32_t)x;
-}
-
 int ntt_run(b200_ctx* ctx, NttDomain* d, Fr* data, int inverse, int dit, const Fr* pre, const Fr* post,
             const Fr* post_scalar) {
     B2_CUDA(ctx, cudaFuncSetAttribute(ntt_pass_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_tile_bytes(12)));
@@ -215,8 +207,8 @@ int ntt_run(b200_ctx* ctx, NttDomain* d, Fr* data, int inverse, int dit, const F
     if (d->log_n == 0) {  // n = 1: every variant is the identity (1/n = 1, g^0 = 1)
         return B200_OK;
     }
-    const uint32_t tl_max = env_u32("B200_NTT_TILE_LOG", 12, 6, 12);
-    const uint32_t s_max = env_u32("B200_NTT_STRIDED_STAGES", 12, 1, tl_max);
+    const uint32_t tl_max = (uint32_t)ctx->ntt_tile_log;
+    const uint32_t s_max = (uint32_t)ctx->ntt_strided_stages;
     NttPassGeom plan[8];
     const int np = ntt_plan(d->log_n, dit, tl_max, s_max < tl_max ? s_max : tl_max, plan);
     for (int i = 0; i < np; ++i) {

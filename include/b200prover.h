@@ -67,6 +67,11 @@ const char *b200_last_error(const b200_ctx *ctx);
 /* Version string of the library build (arch, git describe when available). */
 const char *b200_version(void);
 
+/* Tuning knobs (defaults are the measured best): "msm_c" (window width, 0 = automatic),
+ * "ntt_tile_log" (log2 of the shared-memory tile, 6..12), "ntt_strided_stages" (max stages of a
+ * strided NTT pass, 1..12). */
+int b200_set_option(b200_ctx *ctx, const char *key, long value);
+
 /* Pinned host memory for the solver outputs (prove.go:119-125 W, A, B, C) so that the per-proof
  * H2D copies run at PCIe speed; plain Go slices also work (pageable path). */
 void *b200_host_alloc(size_t bytes);

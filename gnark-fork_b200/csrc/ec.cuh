@@ -12,6 +12,16 @@
 
 namespace b200 {
 
+struct Fp2;
+#if defined(__CUDACC__)
+// Out-of-line Fp2 product / square: the three (two) Fp products inside are independent, so ptxas
+// interleaves six (four) carry chains -- enough ILP to keep the IMAD.WIDE pipe busy at the two
+// warps per scheduler that a 228-register G2 accumulator allows -- while the hot loop stays
+// inside the instruction cache.
+template <int TAG = 0> __device__ __noinline__ Fp2 fp2_mul_call(Fp2 a, Fp2 b);
+template <int TAG = 0> __device__ __noinline__ Fp2 fp2_sqr_call(Fp2 a);
+#endif
+
 // Fp2 = Fp[u]/(u^2 + 1)   (gnark-crypto E2{A0, A1}; memory order A0 then A1)
 struct Fp2 {
     Fp a0, a1;
@@ -24,20 +34,40 @@ struct Fp2 {
     B2_HD Fp2 operator-(const Fp2& o) const { return {a0 - o.a0, a1 - o.a1}; }
     B2_HD Fp2 neg() const { return {a0.neg(), a1.neg()}; }
     B2_HD Fp2 dbl() const { return {a0.dbl(), a1.dbl()}; }
-    B2_HD Fp2 operator*(const Fp2& o) const {  // Karatsuba, 3 Fp mul
+    B2_HD Fp2 mul_inline(const Fp2& o) const {  // Karatsuba, 3 Fp mul
         const Fp t0 = a0 * o.a0, t1 = a1 * o.a1;
         const Fp t2 = (a0 + a1) * (o.a0 + o.a1);
         return {t0 - t1, t2 - t0 - t1};
     }
-    B2_HD Fp2 sqr() const {  // complex squaring, 2 Fp mul
+    B2_HD Fp2 sqr_inline() const {  // complex squaring, 2 Fp mul
         const Fp t = a0 * a1;
         return {(a0 + a1) * (a0 - a1), t.dbl()};
+    }
+    B2_HD Fp2 operator*(const Fp2& o) const {
+#if defined(__CUDA_ARCH__)
+        return fp2_mul_call<0>(*this, o);
+#else
+        return mul_inline(o);
+#endif
+    }
+    B2_HD Fp2 sqr() const {
+#if defined(__CUDA_ARCH__)
+        return fp2_sqr_call<0>(*this);
+#else
+        return sqr_inline();
+#endif
     }
     B2_HD Fp2 inv() const {
         const Fp d = (a0.sqr() + a1.sqr()).inv();
         return {a0 * d, a1.neg() * d};
     }
 };
+
+#if defined(__CUDACC__)
+// templates only to get vague linkage (one copy per translation unit that uses them)
+template <int TAG> __device__ __noinline__ Fp2 fp2_mul_call(Fp2 a, Fp2 b) { return a.mul_inline(b); }
+template <int TAG> __device__ __noinline__ Fp2 fp2_sqr_call(Fp2 a) { return a.sqr_inline(); }
+#endif
 
 template <class F>
 struct Affine {

@@ -401,4 +401,24 @@ struct alignas(16) Fe {
 typedef Fe<FpParams> Fp;
 typedef Fe<FrParams> Fr;
 
+// Out-of-line product (operands and result travel in registers).  Used by the Fp2 tower: a fully
+// inlined G2 mixed addition is 28 Fp products = ~90 KB of SASS, far beyond the instruction cache
+// (ncu: "no instruction" was the top stall of msm_accumulate_kernel<Fp2>), and 250 registers.
+#if defined(__CUDACC__)
+template <class PRM>
+__device__ __noinline__ Fe<PRM> mont_mul_call(Fe<PRM> a, Fe<PRM> b) {
+    Fe<PRM> r;
+    mont_mul_dev<PRM>(r.l, a.l, b.l);
+    return r;
+}
+#endif
+template <class PRM>
+B2_HD Fe<PRM> mul_outlined(const Fe<PRM>& a, const Fe<PRM>& b) {
+#if defined(__CUDA_ARCH__)
+    return mont_mul_call<PRM>(a, b);
+#else
+    return a * b;
+#endif
+}
+
 }  // namespace b200

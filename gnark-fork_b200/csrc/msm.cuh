@@ -322,7 +322,7 @@ static __global__ void msm_order_fill_kernel(const uint32_t* __restrict__ task_b
 // one thread per task (taken in size order); a single-task bucket is written straight to
 // buckets[], the pieces of a split bucket go to partials[task] and are merged by msm_combine_kernel.
 template <class F>
-__global__ void __launch_bounds__(128) msm_accumulate_kernel(const Affine<F>* __restrict__ bases, const uint32_t* __restrict__ sorted,
+__global__ void __launch_bounds__(128, (sizeof(F) > 32 ? 2 : 1)) msm_accumulate_kernel(const Affine<F>* __restrict__ bases, const uint32_t* __restrict__ sorted,
                                       const uint32_t* __restrict__ offsets, const uint32_t* __restrict__ counts,
                                       const uint32_t* __restrict__ task_bucket, const uint32_t* __restrict__ task_off,
                                       const uint32_t* __restrict__ ntasks, const uint32_t* __restrict__ order, uint32_t max_tasks,

@@ -347,6 +347,7 @@ int b200_set_option(b200_ctx* ctx, const char* key, long value) {
     if (k == "msm_c") { if (value != 0 && (value < 4 || value > 24)) return ctx->fail(B200_ERR_ARG, "msm_c out of range"); ctx->msm_c_override = (int)value; }
     else if (k == "ntt_tile_log") { if (value < 6 || value > 12) return ctx->fail(B200_ERR_ARG, "ntt_tile_log out of range"); ctx->ntt_tile_log = (int)value; }
     else if (k == "ntt_strided_stages") { if (value < 1 || value > 12) return ctx->fail(B200_ERR_ARG, "ntt_strided_stages out of range"); ctx->ntt_strided_stages = (int)value; }
+    else if (k == "ntt_threads") { if (value < 32 || value > 1024 || (value & (value - 1))) return ctx->fail(B200_ERR_ARG, "ntt_threads must be a power of two in 32..1024"); ctx->ntt_threads = (int)value; }
     else return ctx->fail(B200_ERR_ARG, "unknown option", key);
     return B200_OK;
 }

@@ -95,9 +95,15 @@ __device__ __forceinline__ void st_vec(T* p, const T& v) {
 
 // 1. digits + histogram.  idx_map (optional): scalar i is scalars[idx_map[i]] (wire filtering by
 // pk.InfinityA/B, prove.go:154-175, done as a gather instead of three host-side copies).
-// Same-bucket lanes of a warp are merged with match.any before touching the counter: skewed
-// digits (the top window only holds 254 - c(W-1) bits; real witnesses are full of 0/1) would
-// otherwise serialise millions of atomics on one L2 address.
+// Windows whose digits are expected to pile up on a few buckets: window 0 (real witnesses are
+// full of 0/1/small values -- every higher digit of those is 0 and skipped) and a top window that
+// holds only a few of the 254 scalar bits.  There, same-bucket lanes of a warp are merged with
+// match.any before touching the counter, otherwise millions of atomics serialise on one L2
+// address (measured: ~0.8 ns each); match.any itself costs a few hundred cycles per warp, so the
+// other windows use plain atomics.
+__device__ __forceinline__ bool msm_window_is_skewed(int w, int W, int c) {
+    return w == 0 || (w == W - 1 && 254 - c * (W - 1) < c - 2);
+}
 static __global__ void msm_digits_kernel(const Fr* __restrict__ scalars, const uint32_t* __restrict__ idx_map, uint32_t n,
                                   int c, int W, int32_t* __restrict__ digits, uint32_t* __restrict__ counts, uint32_t nb) {
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -116,8 +122,12 @@ static __global__ void msm_digits_kernel(const Fr* __restrict__ scalars, const u
         if (d > (1 << (c - 1))) { d -= (1 << c); carry = 1; }
         if (valid) digits[(size_t)w * n + i] = d;
         const uint32_t key = (valid && d != 0) ? (uint32_t)((d < 0 ? -d : d) - 1) : 0xffffffffu;
-        const uint32_t peers = __match_any_sync(0xffffffffu, key);
-        if (key != 0xffffffffu && lane == __ffs(peers) - 1) atomicAdd(&counts[(size_t)w * nb + key], (uint32_t)__popc(peers));
+        if (msm_window_is_skewed(w, W, c)) {   // warp-uniform
+            const uint32_t peers = __match_any_sync(0xffffffffu, key);
+            if (key != 0xffffffffu && lane == __ffs(peers) - 1) atomicAdd(&counts[(size_t)w * nb + key], (uint32_t)__popc(peers));
+        } else if (key != 0xffffffffu) {
+            atomicAdd(&counts[(size_t)w * nb + key], 1u);
+        }
     }
 }
 
@@ -196,7 +206,7 @@ static __global__ void msm_scan_final_kernel(const uint32_t* __restrict__ in, ui
 }
 
 // 3. scatter (counting sort): cursor starts as a copy of the offsets.
-static __global__ void msm_scatter_kernel(const int32_t* __restrict__ digits, uint32_t n, int W, uint32_t nb,
+static __global__ void msm_scatter_kernel(const int32_t* __restrict__ digits, uint32_t n, int c, int W, uint32_t nb,
                                    uint32_t* __restrict__ cursor, uint32_t* __restrict__ sorted) {
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     const bool valid = i < n;
@@ -204,12 +214,16 @@ static __global__ void msm_scatter_kernel(const int32_t* __restrict__ digits, ui
     for (int w = 0; w < W; ++w) {
         const int32_t d = valid ? digits[(size_t)w * n + i] : 0;
         const uint32_t key = d != 0 ? (uint32_t)((d < 0 ? -d : d) - 1) : 0xffffffffu;
-        const uint32_t peers = __match_any_sync(0xffffffffu, key);
-        const int leader = __ffs(peers) - 1;
-        uint32_t base = 0;
-        if (key != 0xffffffffu && lane == leader) base = atomicAdd(&cursor[(size_t)w * nb + key], (uint32_t)__popc(peers));
-        base = __shfl_sync(0xffffffffu, base, leader);
-        if (key != 0xffffffffu) sorted[base + __popc(peers & ((1u << lane) - 1u))] = i | (d < 0 ? 0x80000000u : 0u);
+        if (msm_window_is_skewed(w, W, c)) {   // warp-uniform
+            const uint32_t peers = __match_any_sync(0xffffffffu, key);
+            const int leader = __ffs(peers) - 1;
+            uint32_t base = 0;
+            if (key != 0xffffffffu && lane == leader) base = atomicAdd(&cursor[(size_t)w * nb + key], (uint32_t)__popc(peers));
+            base = __shfl_sync(0xffffffffu, base, leader);
+            if (key != 0xffffffffu) sorted[base + __popc(peers & ((1u << lane) - 1u))] = i | (d < 0 ? 0x80000000u : 0u);
+        } else if (key != 0xffffffffu) {
+            sorted[atomicAdd(&cursor[(size_t)w * nb + key], 1u)] = i | (d < 0 ? 0x80000000u : 0u);
+        }
     }
 }
 

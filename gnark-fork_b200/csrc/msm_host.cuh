@@ -101,7 +101,7 @@ int msm_run_impl(b200_ctx* ctx, const Affine<F>* d_bases, const Fr* d_scalars, c
     B2_CUDA(ctx, cudaGetLastError());
     {
         const int bs = 256;
-        msm_scatter_kernel<<<(unsigned)((n + bs - 1) / bs), bs, 0, st>>>(digits, (uint32_t)n, pl.W, pl.nb, cursor, sorted);
+        msm_scatter_kernel<<<(unsigned)((n + bs - 1) / bs), bs, 0, st>>>(digits, (uint32_t)n, pl.c, pl.W, pl.nb, cursor, sorted);
         B2_CUDA(ctx, cudaGetLastError());
     }
     {

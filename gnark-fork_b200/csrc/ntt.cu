@@ -222,6 +222,7 @@ int ntt_run(b200_ctx* ctx, NttDomain* d, Fr* data, int inverse, int dit, const F
         a.post_scalar = post_scalar ? *post_scalar : Fr::one();
         const uint32_t tiles = (uint32_t)(d->n() >> plan[i].TL);
         uint32_t threads = 1u << (plan[i].TL > 1 ? plan[i].TL - 1 : 0);
+        if (threads > (uint32_t)ctx->ntt_threads) threads = (uint32_t)ctx->ntt_threads;
         if (threads > NTT_THREADS) threads = NTT_THREADS;
         if (threads < 32) threads = 32;
         const size_t smem = smem_tile_bytes(plan[i].TL);

@@ -10,7 +10,8 @@ using namespace b200;
 struct b200_bases {
     int group = 1;
     size_t n = 0;
-    DevBuf pts;
+    DevBuf pts;       // the bases, or their folded-window table
+    MsmFold fold;     // c == 0: plain
 };
 
 namespace {
@@ -232,6 +233,19 @@ int b200_bases_upload(b200_ctx* ctx, int curve, int group, const uint64_t* bases
     if (e == cudaSuccess && bytes) e = cudaMemcpyAsync(b->pts.p, bases_affine, bytes, cudaMemcpyHostToDevice, ctx->stream);
     if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
     if (e != cudaSuccess) { delete b; return ctx->fail(B200_ERR_CUDA, "bases upload", cudaGetErrorString(e)); }
+    if (ctx->msm_precompute && n >= 4096) {
+        const int c = ctx->msm_fold_c ? ctx->msm_fold_c : msm_fold_window(n);
+        DevBuf table;
+        const int st = group == 1 ? msm_fold_build_g1(ctx, b->pts.as<G1Affine>(), n, c, table)
+                                  : msm_fold_build_g2(ctx, b->pts.as<G2Affine>(), n, c, table);
+        if (st == B200_OK) {
+            b->pts.release();
+            b->pts.p = table.p; b->pts.bytes = table.bytes;
+            table.p = nullptr; table.bytes = 0;
+            b->fold.c = c;
+            b->fold.stride = n;
+        } else if (st != B200_ERR_NOMEM) { delete b; return st; }
+    }
     *out = b;
     return B200_OK;
 }
@@ -249,11 +263,11 @@ int b200_msm_dev(b200_ctx* ctx, const b200_bases* bases, const void* scalars_dev
     B2_CUDA(ctx, cudaEventRecord(ctx->ev0, ctx->stream));
     if (bases->group == 1) {
         G1Jac r;
-        B2_TRY(msm_g1_run(ctx, bases->pts.as<G1Affine>(), (const Fr*)scalars_dev, nullptr, n, &r, nullptr));
+        B2_TRY(msm_g1_run(ctx, bases->pts.as<G1Affine>(), (const Fr*)scalars_dev, nullptr, n, &r, nullptr, &bases->fold));
         memcpy(out_jac, &r, sizeof r);
     } else {
         G2Jac r;
-        B2_TRY(msm_g2_run(ctx, bases->pts.as<G2Affine>(), (const Fr*)scalars_dev, nullptr, n, &r, nullptr));
+        B2_TRY(msm_g2_run(ctx, bases->pts.as<G2Affine>(), (const Fr*)scalars_dev, nullptr, n, &r, nullptr, &bases->fold));
         memcpy(out_jac, &r, sizeof r);
     }
     B2_CUDA(ctx, cudaEventRecord(ctx->ev1, ctx->stream));
@@ -275,7 +289,11 @@ static int msm_host(b200_ctx* ctx, int curve, int group, const uint64_t* scalars
     B2_ENTER(ctx, curve);
     if (!out_jac) return ctx->fail(B200_ERR_ARG, "null output");
     b200_bases* b = nullptr;
-    B2_TRY(b200_bases_upload(ctx, curve, group, bases_affine, n, &b));
+    const int saved = ctx->msm_precompute;
+    ctx->msm_precompute = 0;   // a one-shot MSM cannot amortise the table
+    const int up = b200_bases_upload(ctx, curve, group, bases_affine, n, &b);
+    ctx->msm_precompute = saved;
+    B2_TRY(up);
     const int st = b200_msm_resident(ctx, b, scalars, n, out_jac);
     cudaStreamSynchronize(ctx->stream);
     delete b;
@@ -347,6 +365,8 @@ int b200_set_option(b200_ctx* ctx, const char* key, long value) {
     if (k == "msm_c") { if (value != 0 && (value < 4 || value > 24)) return ctx->fail(B200_ERR_ARG, "msm_c out of range"); ctx->msm_c_override = (int)value; }
     else if (k == "ntt_tile_log") { if (value < 6 || value > 12) return ctx->fail(B200_ERR_ARG, "ntt_tile_log out of range"); ctx->ntt_tile_log = (int)value; }
     else if (k == "ntt_strided_stages") { if (value < 1 || value > 12) return ctx->fail(B200_ERR_ARG, "ntt_strided_stages out of range"); ctx->ntt_strided_stages = (int)value; }
+    else if (k == "msm_precompute") { ctx->msm_precompute = value ? 1 : 0; }
+    else if (k == "msm_fold_c") { if (value != 0 && (value < 8 || value > 24)) return ctx->fail(B200_ERR_ARG, "msm_fold_c out of range"); ctx->msm_fold_c = (int)value; }
     else if (k == "ntt_threads") { if (value < 32 || value > 1024 || (value & (value - 1))) return ctx->fail(B200_ERR_ARG, "ntt_threads must be a power of two in 32..1024"); ctx->ntt_threads = (int)value; }
     else return ctx->fail(B200_ERR_ARG, "unknown option", key);
     return B200_OK;

@@ -23,6 +23,8 @@ struct b200_ctx {
     void* scratch = nullptr;                // grow-only workspace shared by MSM / prove calls
     size_t scratch_bytes = 0;
     int msm_c_override = 0;                 // tuning knobs (b200_set_option / B200_MSM_C env)
+    int msm_precompute = 1;                 // build folded-window tables for resident base sets
+    int msm_fold_c = 0;                     // 0 = automatic (msm_fold_window)
     int ntt_tile_log = 9, ntt_strided_stages = 8, ntt_threads = 128;   // measured best (scripts/ntt_sweep.py): many small CTAs overlap load, butterflies and store
 
     // optional per-kernel-class timing (b200_profile_*): CUDA event pairs on `stream`

@@ -22,6 +22,25 @@ static int upload_range(b200_ctx* ctx, DevBuf& dst, const uint64_t* host, size_t
     return B200_OK;
 }
 
+// Replace a resident base array by its folded-window table when enabled and it fits in memory.
+template <class F>
+static int maybe_fold(b200_ctx* ctx, DevBuf& bases, size_t n, MsmFold& fold, int group) {
+    fold = MsmFold();
+    if (!ctx->msm_precompute || n < 4096) return B200_OK;
+    const int c = ctx->msm_fold_c ? ctx->msm_fold_c : msm_fold_window(n);
+    DevBuf table;
+    int st = group == 1 ? msm_fold_build_g1(ctx, bases.as<G1Affine>(), n, c, table)
+                        : msm_fold_build_g2(ctx, bases.as<G2Affine>(), n, c, table);
+    if (st == B200_ERR_NOMEM) return B200_OK;   // keep the plain bases
+    if (st != B200_OK) return st;
+    bases.release();
+    bases.p = table.p; bases.bytes = table.bytes;
+    table.p = nullptr; table.bytes = 0;
+    fold.c = c;
+    fold.stride = n;
+    return B200_OK;
+}
+
 // wire indices whose base is not the point at infinity, positions [lo, hi) of that list
 static int upload_wire_map(b200_ctx* ctx, DevBuf& dst, const uint8_t* infinity, size_t n_wires, size_t expect,
                            size_t lo, size_t hi) {
@@ -66,6 +85,12 @@ int groth16_pk_upload(b200_ctx* ctx, const b200_groth16_pk_desc* d, b200_groth16
         st = upload_range<G1Affine>(ctx, pk->K, d->g1_k, lo, hi, ps); }
     if (st == B200_OK) { shard_range(d->n_z, si, sc, &lo, &hi); pk->n_z = hi - lo; pk->z_lo = lo;
         st = upload_range<G1Affine>(ctx, pk->Z, d->g1_z, lo, hi, ps); }
+    if (st == B200_OK && cudaStreamSynchronize(ctx->stream) != cudaSuccess) st = ctx->fail(B200_ERR_CUDA, "pk upload");
+    if (st == B200_OK) st = maybe_fold<Fp>(ctx, pk->A, pk->n_a, pk->fA, 1);
+    if (st == B200_OK) st = maybe_fold<Fp>(ctx, pk->B, pk->n_b, pk->fB, 1);
+    if (st == B200_OK) st = maybe_fold<Fp>(ctx, pk->K, pk->n_k, pk->fK, 1);
+    if (st == B200_OK) st = maybe_fold<Fp>(ctx, pk->Z, pk->n_z, pk->fZ, 1);
+    if (st == B200_OK) st = maybe_fold<Fp2>(ctx, pk->G2B, pk->n_b, pk->fG2B, 2);
     // build the computeH tables now so the first proof does not pay for them
     const Fr* t;
     if (st == B200_OK) st = ntt_domain_table(ctx, pk->dom, NttDomain::H_A, &t);
@@ -93,11 +118,11 @@ int groth16_prove_core(b200_ctx* ctx, const b200_groth16_pk* pk, const uint64_t*
         return ctx->fail(B200_ERR_ARG, "k_remove does not match len(pk.G1.K)");
     // workspace: a, b, c (n Fr each), W, optional K map, MSM scratch
     size_t msm_ws = 0;
-    msm_ws = std::max(msm_ws, msm_workspace_bytes(pk->n_a, 1, ctx->msm_c_override));
-    msm_ws = std::max(msm_ws, msm_workspace_bytes(pk->n_b, 1, ctx->msm_c_override));
-    msm_ws = std::max(msm_ws, msm_workspace_bytes(pk->n_k, 1, ctx->msm_c_override));
-    msm_ws = std::max(msm_ws, msm_workspace_bytes(pk->n_z, 1, ctx->msm_c_override));
-    msm_ws = std::max(msm_ws, msm_workspace_bytes(pk->n_b, 2, ctx->msm_c_override));
+    msm_ws = std::max(msm_ws, msm_workspace_bytes(pk->n_a, 1, ctx->msm_c_override, pk->fA.c));
+    msm_ws = std::max(msm_ws, msm_workspace_bytes(pk->n_b, 1, ctx->msm_c_override, pk->fB.c));
+    msm_ws = std::max(msm_ws, msm_workspace_bytes(pk->n_k, 1, ctx->msm_c_override, pk->fK.c));
+    msm_ws = std::max(msm_ws, msm_workspace_bytes(pk->n_z, 1, ctx->msm_c_override, pk->fZ.c));
+    msm_ws = std::max(msm_ws, msm_workspace_bytes(pk->n_b, 2, ctx->msm_c_override, pk->fG2B.c));
     Arena ar;
     const size_t o_a = ar.off; ar.take(n * sizeof(Fr));
     const size_t o_b = ar.off; ar.take(n * sizeof(Fr));
@@ -146,16 +171,16 @@ int groth16_prove_core(b200_ctx* ctx, const b200_groth16_pk* pk, const uint64_t*
 
     G1Jac ja, jb1, jk, jz;
     G2Jac jb2;
-    B2_TRY(msm_g1_run(ctx, pk->A.as<G1Affine>(), d_w, pk->mapA.as<uint32_t>(), pk->n_a, &ja, ws));
+    B2_TRY(msm_g1_run(ctx, pk->A.as<G1Affine>(), d_w, pk->mapA.as<uint32_t>(), pk->n_a, &ja, ws, &pk->fA));
     B2_CUDA(ctx, cudaEventRecord(ev[3], st));
-    B2_TRY(msm_g1_run(ctx, pk->B.as<G1Affine>(), d_w, pk->mapB.as<uint32_t>(), pk->n_b, &jb1, ws));
+    B2_TRY(msm_g1_run(ctx, pk->B.as<G1Affine>(), d_w, pk->mapB.as<uint32_t>(), pk->n_b, &jb1, ws, &pk->fB));
     B2_CUDA(ctx, cudaEventRecord(ev[4], st));
-    if (d_kmap) B2_TRY(msm_g1_run(ctx, pk->K.as<G1Affine>(), d_w, d_kmap, pk->n_k, &jk, ws));
-    else B2_TRY(msm_g1_run(ctx, pk->K.as<G1Affine>(), d_w + pk->nb_public + pk->k_lo, nullptr, pk->n_k, &jk, ws));
+    if (d_kmap) B2_TRY(msm_g1_run(ctx, pk->K.as<G1Affine>(), d_w, d_kmap, pk->n_k, &jk, ws, &pk->fK));
+    else B2_TRY(msm_g1_run(ctx, pk->K.as<G1Affine>(), d_w + pk->nb_public + pk->k_lo, nullptr, pk->n_k, &jk, ws, &pk->fK));
     B2_CUDA(ctx, cudaEventRecord(ev[5], st));
-    B2_TRY(msm_g1_run(ctx, pk->Z.as<G1Affine>(), d_a + pk->z_lo, nullptr, pk->n_z, &jz, ws));
+    B2_TRY(msm_g1_run(ctx, pk->Z.as<G1Affine>(), d_a + pk->z_lo, nullptr, pk->n_z, &jz, ws, &pk->fZ));
     B2_CUDA(ctx, cudaEventRecord(ev[6], st));
-    B2_TRY(msm_g2_run(ctx, pk->G2B.as<G2Affine>(), d_w, pk->mapB.as<uint32_t>(), pk->n_b, &jb2, ws));
+    B2_TRY(msm_g2_run(ctx, pk->G2B.as<G2Affine>(), d_w, pk->mapB.as<uint32_t>(), pk->n_b, &jb2, ws, &pk->fG2B));
     B2_CUDA(ctx, cudaEventRecord(ev[7], st));
     B2_CUDA(ctx, cudaStreamSynchronize(st));
 

@@ -9,7 +9,8 @@ struct b200_groth16_pk {
     unsigned log_n = 0;
     size_t n_wires = 0, nb_public = 0;
     b200::NttDomain* dom = nullptr;  // owned by the ctx cache
-    b200::DevBuf A, B, K, Z, G2B;    // affine bases of this shard
+    b200::DevBuf A, B, K, Z, G2B;    // affine bases of this shard (or their folded-window tables)
+    b200::MsmFold fA, fB, fK, fZ, fG2B;  // c == 0: plain bases
     b200::DevBuf mapA, mapB;         // wire index of each A / B base (prove.go:154-175 as a gather)
     size_t n_a = 0, n_b = 0, n_k = 0, n_z = 0;  // shard-local counts
     size_t k_lo = 0, z_lo = 0;       // first K / Z index of this shard

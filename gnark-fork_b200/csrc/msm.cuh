@@ -42,7 +42,26 @@ struct MsmPlan {
     uint32_t nb;      // buckets per window = 2^(c-1)
     uint32_t L0;      // leaves per level-0 reduce node
     uint32_t L;       // fan-in of the upper reduce levels
+    int fold;         // 1: all windows share ONE bucket set (bases precomputed as 2^(c w) P)
+    int WB;           // bucket sets: W, or 1 when folded
 };
+
+// Folded windows (resident base sets only): with T[w][i] = 2^(c w) P_i stored next to the bases,
+// digit d_w of scalar i adds sign(d_w) T[w][i] to bucket |d_w| of ONE shared bucket set, so the
+// bucket reduction is paid once instead of W times and c can grow: 2^24 points run 12 windows of
+// 22 bits (12 n additions) instead of 15 windows of 17 bits.  Costs W x the base memory -- the
+// reason this design wants a 180 GB part.  c minimises additions + reduction work.
+inline int msm_fold_window(size_t n) {
+    int best = 8;
+    double best_cost = 1e300;
+    for (int c = 8; c <= 24; ++c) {
+        const int W = msm_num_windows(c);
+        if ((double)n * W >= 2147483648.0) continue;       // sorted entries carry (w n + i) in 31 bits
+        const double cost = (double)n * W * 10.0 + (double)((size_t)1 << (c - 1)) * 2.0 * 14.0 * 1.5;
+        if (cost < best_cost) { best_cost = cost; best = c; }
+    }
+    return best;
+}
 
 inline MsmPlan msm_plan(size_t n, int c_override) {
     int c;
@@ -59,6 +78,19 @@ inline MsmPlan msm_plan(size_t n, int c_override) {
     p.nb = 1u << (c - 1);
     p.L0 = 16;
     p.L = 16;
+    p.fold = 0;
+    p.WB = p.W;
+    return p;
+}
+inline MsmPlan msm_plan_folded(int c) {
+    MsmPlan p;
+    p.c = c;
+    p.W = msm_num_windows(c);
+    p.nb = 1u << (c - 1);
+    p.L0 = 16;
+    p.L = 16;
+    p.fold = 1;
+    p.WB = 1;
     return p;
 }
 
@@ -105,7 +137,7 @@ __device__ __forceinline__ bool msm_window_is_skewed(int w, int W, int c) {
     return w == 0 || (w == W - 1 && 254 - c * (W - 1) < c - 2);
 }
 static __global__ void msm_digits_kernel(const Fr* __restrict__ scalars, const uint32_t* __restrict__ idx_map, uint32_t n,
-                                  int c, int W, int32_t* __restrict__ digits, uint32_t* __restrict__ counts, uint32_t nb) {
+                                  int c, int W, int fold, int32_t* __restrict__ digits, uint32_t* __restrict__ counts, uint32_t nb) {
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     const bool valid = i < n;
     const int lane = threadIdx.x & 31;
@@ -124,9 +156,9 @@ static __global__ void msm_digits_kernel(const Fr* __restrict__ scalars, const u
         const uint32_t key = (valid && d != 0) ? (uint32_t)((d < 0 ? -d : d) - 1) : 0xffffffffu;
         if (msm_window_is_skewed(w, W, c)) {   // warp-uniform
             const uint32_t peers = __match_any_sync(0xffffffffu, key);
-            if (key != 0xffffffffu && lane == __ffs(peers) - 1) atomicAdd(&counts[(size_t)w * nb + key], (uint32_t)__popc(peers));
+            if (key != 0xffffffffu && lane == __ffs(peers) - 1) atomicAdd(&counts[(fold ? 0 : (size_t)w * nb) + key], (uint32_t)__popc(peers));
         } else if (key != 0xffffffffu) {
-            atomicAdd(&counts[(size_t)w * nb + key], 1u);
+            atomicAdd(&counts[(fold ? 0 : (size_t)w * nb) + key], 1u);
         }
     }
 }
@@ -206,7 +238,7 @@ static __global__ void msm_scan_final_kernel(const uint32_t* __restrict__ in, ui
 }
 
 // 3. scatter (counting sort): cursor starts as a copy of the offsets.
-static __global__ void msm_scatter_kernel(const int32_t* __restrict__ digits, uint32_t n, int c, int W, uint32_t nb,
+static __global__ void msm_scatter_kernel(const int32_t* __restrict__ digits, uint32_t n, int c, int W, int fold, uint32_t stride, uint32_t nb,
                                    uint32_t* __restrict__ cursor, uint32_t* __restrict__ sorted) {
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     const bool valid = i < n;
@@ -218,11 +250,11 @@ static __global__ void msm_scatter_kernel(const int32_t* __restrict__ digits, ui
             const uint32_t peers = __match_any_sync(0xffffffffu, key);
             const int leader = __ffs(peers) - 1;
             uint32_t base = 0;
-            if (key != 0xffffffffu && lane == leader) base = atomicAdd(&cursor[(size_t)w * nb + key], (uint32_t)__popc(peers));
+            if (key != 0xffffffffu && lane == leader) base = atomicAdd(&cursor[(fold ? 0 : (size_t)w * nb) + key], (uint32_t)__popc(peers));
             base = __shfl_sync(0xffffffffu, base, leader);
-            if (key != 0xffffffffu) sorted[base + __popc(peers & ((1u << lane) - 1u))] = i | (d < 0 ? 0x80000000u : 0u);
+            if (key != 0xffffffffu) sorted[base + __popc(peers & ((1u << lane) - 1u))] = (fold ? (uint32_t)w * stride + i : i) | (d < 0 ? 0x80000000u : 0u);
         } else if (key != 0xffffffffu) {
-            sorted[atomicAdd(&cursor[(size_t)w * nb + key], 1u)] = i | (d < 0 ? 0x80000000u : 0u);
+            sorted[atomicAdd(&cursor[(fold ? 0 : (size_t)w * nb) + key], 1u)] = (fold ? (uint32_t)w * stride + i : i) | (d < 0 ? 0x80000000u : 0u);
         }
     }
 }
@@ -241,13 +273,19 @@ __device__ __forceinline__ void msm_task_range(uint32_t cnt, uint32_t nt, uint32
     *first = j0;
     *size = j0 >= cnt ? 0u : (cnt - j0 < cb ? cnt - j0 : cb);
 }
+// buckets cut into more than MSM_SMALL_SPLIT pieces are listed in big_list (big_count[0] entries)
+// and merged by one CTA each (msm_combine_big_kernel).
+constexpr uint32_t MSM_SMALL_SPLIT = 8;
 static __global__ void msm_task_count_kernel(const uint32_t* __restrict__ counts, uint32_t n_buckets, uint32_t chunk,
-                                             uint32_t* __restrict__ ntasks) {
+                                             uint32_t* __restrict__ ntasks, uint32_t* __restrict__ big_count,
+                                             uint32_t* __restrict__ big_list) {
     const uint32_t b = blockIdx.x * blockDim.x + threadIdx.x;
     if (b >= n_buckets) return;
     const uint32_t c = counts[b];
     uint32_t nt = c <= chunk ? 1u : (c + chunk - 1u) / chunk;
-    ntasks[b] = nt > MSM_MAX_TASKS_PER_BUCKET ? MSM_MAX_TASKS_PER_BUCKET : nt;
+    if (nt > MSM_MAX_TASKS_PER_BUCKET) nt = MSM_MAX_TASKS_PER_BUCKET;
+    ntasks[b] = nt;
+    if (nt > MSM_SMALL_SPLIT) big_list[atomicAdd(big_count, 1u)] = b;
 }
 static __global__ void msm_task_fill_kernel(const uint32_t* __restrict__ ntasks, const uint32_t* __restrict__ task_off,
                                             uint32_t n_buckets, uint32_t* __restrict__ task_bucket) {
@@ -370,29 +408,47 @@ __device__ __forceinline__ XYZZ<F> shfl_down_point(const XYZZ<F>& p, int delta) 
     return r;
 }
 
-// a warp looks at 32 buckets; every split bucket among them is summed by the whole warp
-// (strided partial sums per lane, then a shuffle tree).
+// buckets cut into 2..MSM_SMALL_SPLIT pieces: the owning thread adds them itself
 template <class F>
 __global__ void __launch_bounds__(128) msm_combine_kernel(const uint32_t* __restrict__ task_off, const uint32_t* __restrict__ ntasks,
                                    uint32_t n_buckets, const XYZZ<F>* __restrict__ partials, XYZZ<F>* __restrict__ buckets) {
     const uint32_t b = blockIdx.x * blockDim.x + threadIdx.x;
-    const int lane = threadIdx.x & 31;
-    const uint32_t nt = b < n_buckets ? ntasks[b] : 1u;
-    uint32_t todo = __ballot_sync(0xffffffffu, nt > 1u);
-    while (todo) {
-        const int src = __ffs(todo) - 1;
-        todo &= todo - 1;
-        const uint32_t bb = __shfl_sync(0xffffffffu, b, src);
-        const uint32_t n = __shfl_sync(0xffffffffu, nt, src);
-        const uint32_t o = __shfl_sync(0xffffffffu, b < n_buckets ? task_off[b] : 0u, src);
+    if (b >= n_buckets) return;
+    const uint32_t nt = ntasks[b];
+    if (nt <= 1u || nt > MSM_SMALL_SPLIT) return;
+    const uint32_t o = task_off[b];
+    XYZZ<F> acc = ld_vec(partials + o);
+    for (uint32_t j = 1; j < nt; ++j) acc.add(ld_vec(partials + o + j));
+    st_vec(buckets + b, acc);
+}
+
+// heavily split buckets (skewed digits): one CTA per bucket -- strided partial sums per thread, a
+// shuffle tree per warp, the warp results through shared memory.
+constexpr int COMBINE_BIG_THREADS = 256;
+template <class F>
+__global__ void __launch_bounds__(COMBINE_BIG_THREADS) msm_combine_big_kernel(const uint32_t* __restrict__ big_count, const uint32_t* __restrict__ big_list,
+                                       const uint32_t* __restrict__ task_off, const uint32_t* __restrict__ ntasks,
+                                       const XYZZ<F>* __restrict__ partials, XYZZ<F>* __restrict__ buckets) {
+    __shared__ XYZZ<F> warp_sum[COMBINE_BIG_THREADS / 32];
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    const uint32_t n_big = big_count[0];
+    for (uint32_t k = blockIdx.x; k < n_big; k += gridDim.x) {
+        const uint32_t b = big_list[k], nt = ntasks[b], o = task_off[b];
         XYZZ<F> acc = XYZZ<F>::inf();
-        for (uint32_t j = lane; j < n; j += 32) acc.add(ld_vec(partials + o + j));
+        for (uint32_t j = threadIdx.x; j < nt; j += blockDim.x) acc.add(ld_vec(partials + o + j));
 #pragma unroll 1
         for (int d = 16; d >= 1; d >>= 1) {
             const XYZZ<F> other = shfl_down_point(acc, d);
             if (lane < d) acc.add(other);
         }
-        if (lane == 0) st_vec(buckets + bb, acc);
+        if (lane == 0) warp_sum[wid] = acc;
+        __syncthreads();
+        if (threadIdx.x == 0) {
+#pragma unroll 1
+            for (int w2 = 1; w2 < COMBINE_BIG_THREADS / 32; ++w2) acc.add(warp_sum[w2]);
+            st_vec(buckets + b, acc);
+        }
+        __syncthreads();
     }
 }
 
@@ -416,23 +472,84 @@ __global__ void __launch_bounds__(64) msm_reduce_leaf_kernel(const XYZZ<F>* __re
     st_vec(outW + t, acc);
 }
 
+// Upper part of the reduction, latency-optimised: with T leaf nodes (S_t, Wt_t) per bucket set,
+//   sum_k k B_k = sum_t Wt_t + L0 * sum_t t * S_t = V_0 + L0 * sum_b 2^b V_{1+b},
+//   V_{1+b} = sum over the nodes t whose index has bit b set of S_t.
+// The Q = 1 + log2 T plain sums V_q are binary trees (log2 T launches of independent additions,
+// depth one addition each) instead of a chain of ~50 dependent additions per level; the last
+// Q values per set go to the host, which does the Horner step.
 template <class F>
-__global__ void __launch_bounds__(64) msm_reduce_node_kernel(const XYZZ<F>* __restrict__ inS, const XYZZ<F>* __restrict__ inW, uint32_t n_nodes,
-                                       uint32_t L, uint32_t log_len, XYZZ<F>* __restrict__ outS, XYZZ<F>* __restrict__ outW) {
-    const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
-    if (t >= n_nodes) return;
-    const XYZZ<F>* s = inS + (size_t)t * L;
-    const XYZZ<F>* w = inW + (size_t)t * L;
-    XYZZ<F> run = XYZZ<F>::inf(), acc = XYZZ<F>::inf(), wsum = XYZZ<F>::inf();
-    for (int j = (int)L - 1; j >= 0; --j) {
-        acc.add(run);              // child j weighs j
-        run.add(ld_vec(s + j));
-        wsum.add(ld_vec(w + j));
+__global__ void __launch_bounds__(128) msm_tree_first_kernel(const XYZZ<F>* __restrict__ S, const XYZZ<F>* __restrict__ Wt, uint32_t T,
+                                                            uint32_t Q, uint32_t total, XYZZ<F>* __restrict__ out) {
+    const uint32_t idx = blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= total) return;
+    const uint32_t half = T >> 1;
+    const uint32_t tp = idx % half, q = (idx / half) % Q, set = idx / half / Q;
+    const uint32_t t0 = 2u * tp, a = set * T + t0;
+    XYZZ<F> r;
+    if (q == 0) {
+        r = ld_vec(Wt + a);
+        r.add(ld_vec(Wt + a + 1));
+    } else {
+        const uint32_t bit = q - 1u;
+        r = XYZZ<F>::inf();
+        if ((t0 >> bit) & 1u) r = ld_vec(S + a);
+        if (((t0 + 1u) >> bit) & 1u) r.add(ld_vec(S + a + 1));
     }
-    for (uint32_t k = 0; k < log_len; ++k) acc = acc.dbl();
-    wsum.add(acc);
-    st_vec(outS + t, run);
-    st_vec(outW + t, wsum);
+    st_vec(out + idx, r);
+}
+// out[g * (m/2) + t] = in[g * m + 2t] + in[g * m + 2t + 1]
+template <class F>
+__global__ void __launch_bounds__(128) msm_tree_pass_kernel(const XYZZ<F>* __restrict__ in, uint32_t m, uint32_t total,
+                                                           XYZZ<F>* __restrict__ out) {
+    const uint32_t idx = blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= total) return;
+    const uint32_t half = m >> 1;
+    const uint32_t g = idx / half, t = idx % half;
+    XYZZ<F> r = ld_vec(in + (size_t)g * m + 2u * t);
+    r.add(ld_vec(in + (size_t)g * m + 2u * t + 1u));
+    st_vec(out + idx, r);
+}
+
+// Folded-window tables.  Pass 1: thread i walks 2^c P_i, 2^(2c) P_i, ... by repeated doubling and
+// parks the XYZZ results; pass 2 normalises the W-1 results of a point with ONE inversion
+// (Montgomery's trick over their ZZZ) and writes T[w][i] affine.  One-time cost at upload.
+template <class F>
+__global__ void __launch_bounds__(128) msm_fold_double_kernel(const Affine<F>* __restrict__ bases, uint32_t n0, uint32_t cnt, int c, int W,
+                                                             XYZZ<F>* __restrict__ tmp) {
+    const uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= cnt) return;
+    XYZZ<F> p = XYZZ<F>::from_affine(ld_vec(bases + n0 + j));
+    for (int w = 1; w < W; ++w) {
+        for (int k = 0; k < c; ++k) p = p.dbl();
+        st_vec(tmp + (size_t)(w - 1) * cnt + j, p);
+    }
+}
+template <class F>
+__global__ void __launch_bounds__(128) msm_fold_normalize_kernel(const XYZZ<F>* __restrict__ tmp, uint32_t n0, uint32_t cnt, int W,
+                                                                uint32_t stride, Affine<F>* __restrict__ table) {
+    const uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= cnt) return;
+    F pre[31];
+    F run = F::one();
+    for (int w = 1; w < W; ++w) {
+        pre[w - 1] = run;
+        const F zzz = ld_vec(&tmp[(size_t)(w - 1) * cnt + j].ZZZ);
+        if (!zzz.is_zero()) run = run * zzz;
+    }
+    F inv = run.inv();
+    for (int w = W - 1; w >= 1; --w) {
+        const XYZZ<F> p = ld_vec(tmp + (size_t)(w - 1) * cnt + j);
+        Affine<F> a = Affine<F>::inf();
+        if (!p.ZZZ.is_zero()) {
+            const F zi = inv * pre[w - 1];       // 1 / ZZZ_w
+            inv = inv * p.ZZZ;
+            const F zzi = (zi * p.ZZ).sqr();     // 1 / ZZ_w
+            a.x = p.X * zzi;
+            a.y = p.Y * zi;
+        }
+        st_vec(table + (size_t)w * stride + n0 + j, a);
+    }
 }
 
 #endif  // __CUDACC__

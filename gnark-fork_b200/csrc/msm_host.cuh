@@ -1,5 +1,6 @@
 // Host driver of the MSM pipeline (template over the coordinate field: Fp for G1, Fp2 for G2).
 #pragma once
+#include <vector>
 #include "msm.cuh"
 
 namespace b200 {
@@ -8,11 +9,21 @@ namespace b200 {
 // d_bases: n affine points on the device; d_scalars: Montgomery Fr on the device, read through
 // d_idx_map when it is not null (scalar i = d_scalars[d_idx_map[i]]).  The workspace is carved
 // from `ws` when ws != nullptr (the caller reserved msm_workspace_bytes), else from the ctx.
-size_t msm_workspace_bytes(size_t n, int group, int c_override);
+// Folded-window table of a resident base set (c == 0: none).  d_bases then points at the table
+// T[w][i] = 2^(c w) P_i, w-major with `stride` points per window (T[0] = the bases themselves).
+struct MsmFold {
+    int c = 0;
+    size_t stride = 0;
+};
+size_t msm_workspace_bytes(size_t n, int group, int c_override, int fold_c);
 int msm_g1_run(b200_ctx* ctx, const G1Affine* d_bases, const Fr* d_scalars, const uint32_t* d_idx_map, size_t n,
-               G1Jac* out_host, void* ws);
+               G1Jac* out_host, void* ws, const MsmFold* fold);
 int msm_g2_run(b200_ctx* ctx, const G2Affine* d_bases, const Fr* d_scalars, const uint32_t* d_idx_map, size_t n,
-               G2Jac* out_host, void* ws);
+               G2Jac* out_host, void* ws, const MsmFold* fold);
+// builds the table for n resident points (device) into `table` ((W x n) affine points); returns
+// B200_ERR_NOMEM without side effects when the table does not fit.
+int msm_fold_build_g1(b200_ctx* ctx, const G1Affine* d_bases, size_t n, int c, DevBuf& table);
+int msm_fold_build_g2(b200_ctx* ctx, const G2Affine* d_bases, size_t n, int c, DevBuf& table);
 
 #if defined(__CUDACC__)
 
@@ -21,12 +32,12 @@ struct MsmLayout {
     MsmPlan plan;
     size_t n, M;  // M = W * nb buckets
     size_t off_digits, off_sorted, off_counts, off_offsets, off_cursor, off_bsums, off_buckets, off_S[2], off_W[2], total;
-    size_t off_ntasks, off_task_off, off_task_bucket, off_partials, off_order, off_order_hist;
-    uint32_t scan_blocks, chunk, max_tasks, order_shift;
-    MsmLayout(size_t n_, int c_override) {
+    size_t off_ntasks, off_task_off, off_task_bucket, off_partials, off_order, off_order_hist, off_big;
+    uint32_t scan_blocks, chunk, max_tasks, order_shift, T, logT, Q;
+    MsmLayout(size_t n_, int c_override, int fold_c) {
         n = n_;
-        plan = msm_plan(n, c_override);
-        M = (size_t)plan.W * plan.nb;
+        plan = fold_c ? msm_plan_folded(fold_c) : msm_plan(n, c_override);
+        M = (size_t)plan.WB * plan.nb;
         Arena a;
         off_digits = a.off; a.take((size_t)plan.W * n * 4);
         off_sorted = a.off; a.take((size_t)plan.W * n * 4);
@@ -36,33 +47,46 @@ struct MsmLayout {
         scan_blocks = (uint32_t)((M + SCAN_CHUNK - 1) / SCAN_CHUNK);
         off_bsums = a.off; a.take((size_t)scan_blocks * 4);
         off_buckets = a.off; a.take(M * sizeof(XYZZ<F>));
-        // task splitting: chunk = twice the mean bucket load (at least 64 points)
-        const size_t mean = n / plan.nb;
-        chunk = (uint32_t)(2 * mean < 64 ? 64 : 2 * mean);
-        max_tasks = (uint32_t)(M + ((size_t)plan.W * n) / chunk + 1);
+        // task splitting: pieces of at most twice the mean bucket load, but small enough that the
+        // launch has ~400 K tasks (148 SMs x 20 warps x 32 lanes x 4 waves) even when few buckets exist
+        const size_t entries = (size_t)plan.W * n, mean = entries / M;
+        size_t ch = entries / 400000;
+        const size_t hi = 2 * mean < 64 ? 64 : 2 * mean;
+        if (ch > hi) ch = hi;
+        if (ch < 32) ch = 32;
+        chunk = (uint32_t)ch;
+        max_tasks = (uint32_t)(M + entries / chunk + 1);
         off_ntasks = a.off; a.take(M * 4);
         off_task_off = a.off; a.take(M * 4);
         off_task_bucket = a.off; a.take((size_t)max_tasks * 4);
         off_partials = a.off; a.take((size_t)max_tasks * sizeof(XYZZ<F>));
+        off_big = a.off; a.take((M + 1) * 4);   // [0] = count, then the list
         off_order = a.off; a.take((size_t)max_tasks * 4);
         off_order_hist = a.off; a.take((size_t)ORDER_BINS * 4 * 2);
         order_shift = 0;
         while ((chunk >> order_shift) > (uint32_t)ORDER_BINS - 2) ++order_shift;
         const size_t nodes0 = M / plan.L0;
-        for (int i = 0; i < 2; ++i) {
-            off_S[i] = a.off; a.take((i == 0 ? nodes0 : nodes0 / 2 + 1) * sizeof(XYZZ<F>));
-            off_W[i] = a.off; a.take((i == 0 ? nodes0 : nodes0 / 2 + 1) * sizeof(XYZZ<F>));
-        }
+        T = plan.nb / plan.L0;
+        logT = 0;
+        while ((1u << logT) < T) ++logT;
+        Q = 1 + logT;
+        off_S[0] = a.off; a.take(nodes0 * sizeof(XYZZ<F>));
+        off_W[0] = a.off; a.take(nodes0 * sizeof(XYZZ<F>));
+        // tree ping-pong buffers: WB * Q arrays of T/2 and T/4 points
+        off_S[1] = a.off; a.take((size_t)plan.WB * Q * (T / 2 + 1) * sizeof(XYZZ<F>));
+        off_W[1] = a.off; a.take((size_t)plan.WB * Q * (T / 4 + 1) * sizeof(XYZZ<F>));
         total = a.off;
     }
 };
 
 template <class F>
 int msm_run_impl(b200_ctx* ctx, const Affine<F>* d_bases, const Fr* d_scalars, const uint32_t* d_idx_map, size_t n,
-                 Jac<F>* out_host, void* ws) {
+                 Jac<F>* out_host, void* ws, const MsmFold* fold) {
     if (n == 0) { *out_host = Jac<F>::inf(); return B200_OK; }
     if (n >= ((size_t)1 << 31)) return ctx->fail(B200_ERR_UNSUPPORTED, "MSM above 2^31 points");
-    MsmLayout<F> lay(n, ctx->msm_c_override);
+    const int fold_c = fold ? fold->c : 0;
+    MsmLayout<F> lay(n, ctx->msm_c_override, fold_c);
+    const uint32_t stride = fold_c ? (uint32_t)fold->stride : 0u;
     const MsmPlan& pl = lay.plan;
     char* base;
     if (ws) base = (char*)ws;
@@ -78,6 +102,7 @@ int msm_run_impl(b200_ctx* ctx, const Affine<F>* d_bases, const Fr* d_scalars, c
     uint32_t* task_off = (uint32_t*)(base + lay.off_task_off);
     uint32_t* task_bucket = (uint32_t*)(base + lay.off_task_bucket);
     XYZZ<F>* partials = (XYZZ<F>*)(base + lay.off_partials);
+    uint32_t* big = (uint32_t*)(base + lay.off_big);
     uint32_t* order = (uint32_t*)(base + lay.off_order);
     uint32_t* order_hist = (uint32_t*)(base + lay.off_order_hist);
     XYZZ<F>* S[2] = {(XYZZ<F>*)(base + lay.off_S[0]), (XYZZ<F>*)(base + lay.off_S[1])};
@@ -90,7 +115,7 @@ int msm_run_impl(b200_ctx* ctx, const Affine<F>* d_bases, const Fr* d_scalars, c
     B2_CUDA(ctx, cudaMemsetAsync(counts, 0, lay.M * 4, st));
     {
         const int bs = 256;
-        msm_digits_kernel<<<(unsigned)((n + bs - 1) / bs), bs, 0, st>>>(d_scalars, d_idx_map, (uint32_t)n, pl.c, pl.W, digits, counts, pl.nb);
+        msm_digits_kernel<<<(unsigned)((n + bs - 1) / bs), bs, 0, st>>>(d_scalars, d_idx_map, (uint32_t)n, pl.c, pl.W, pl.fold, digits, counts, pl.nb);
         B2_CUDA(ctx, cudaGetLastError());
     }
     msm_scan_sums_kernel<<<lay.scan_blocks, SCAN_THREADS, 0, st>>>(counts, M, bsums);
@@ -101,12 +126,13 @@ int msm_run_impl(b200_ctx* ctx, const Affine<F>* d_bases, const Fr* d_scalars, c
     B2_CUDA(ctx, cudaGetLastError());
     {
         const int bs = 256;
-        msm_scatter_kernel<<<(unsigned)((n + bs - 1) / bs), bs, 0, st>>>(digits, (uint32_t)n, pl.c, pl.W, pl.nb, cursor, sorted);
+        msm_scatter_kernel<<<(unsigned)((n + bs - 1) / bs), bs, 0, st>>>(digits, (uint32_t)n, pl.c, pl.W, pl.fold, stride, pl.nb, cursor, sorted);
         B2_CUDA(ctx, cudaGetLastError());
     }
     {
         const int bs = 256;
-        msm_task_count_kernel<<<(M + bs - 1) / bs, bs, 0, st>>>(counts, M, lay.chunk, ntasks);
+        B2_CUDA(ctx, cudaMemsetAsync(big, 0, 4, st));
+        msm_task_count_kernel<<<(M + bs - 1) / bs, bs, 0, st>>>(counts, M, lay.chunk, ntasks, big, big + 1);
         B2_CUDA(ctx, cudaGetLastError());
         msm_scan_sums_kernel<<<lay.scan_blocks, SCAN_THREADS, 0, st>>>(ntasks, M, bsums);
         B2_CUDA(ctx, cudaGetLastError());
@@ -138,41 +164,85 @@ int msm_run_impl(b200_ctx* ctx, const Affine<F>* d_bases, const Fr* d_scalars, c
         span = ctx->prof_begin(B200_PROF_MSM_REDUCE, (double)n);
         msm_combine_kernel<F><<<(M + bs - 1) / bs, bs, 0, st>>>(task_off, ntasks, M, partials, buckets);
         B2_CUDA(ctx, cudaGetLastError());
+        msm_combine_big_kernel<F><<<ctx->sm_count * 2, COMBINE_BIG_THREADS, 0, st>>>(big, big + 1, task_off, ntasks, partials, buckets);
+        B2_CUDA(ctx, cudaGetLastError());
     }
-    // reduction tree
-    uint32_t T = pl.nb / pl.L0;  // nodes per window
-    uint32_t log_len = 0;
-    while ((1u << log_len) < pl.L0) ++log_len;
+    // reduction: leaf running sums, then binary trees for the Q plain sums of every bucket set
+    const uint32_t T = lay.T, Q = lay.Q;
     {
-        const uint32_t nodes = (uint32_t)pl.W * T;
+        const uint32_t nodes = (uint32_t)pl.WB * T;
         msm_reduce_leaf_kernel<F><<<(nodes + 63) / 64, 64, 0, st>>>(buckets, nodes, pl.L0, S[0], Wt[0]);
         B2_CUDA(ctx, cudaGetLastError());
     }
-    int cur = 0;
-    ctx->n_launches += 16;  // digits, 2 x 3 scan, scatter, task count/fill, 3 x order, accumulate, combine, leaf
-    while (T > 1) {
-        ctx->n_launches += 1;
-        const uint32_t L = T < pl.L ? T : pl.L;
-        uint32_t logL = 0;
-        while ((1u << logL) < L) ++logL;
-        const uint32_t nodes = (uint32_t)pl.W * (T / L);
-        msm_reduce_node_kernel<F><<<(nodes + 63) / 64, 64, 0, st>>>(S[cur], Wt[cur], nodes, L, log_len, S[cur ^ 1], Wt[cur ^ 1]);
-        B2_CUDA(ctx, cudaGetLastError());
-        T /= L;
-        log_len += logL;
-        cur ^= 1;
+    ctx->n_launches += 17;  // digits, 2 x 3 scan, scatter, task count/fill, 3 x order, accumulate, 2 x combine, leaf
+    std::vector<XYZZ<F>> fin((size_t)pl.WB * Q);
+    if (T >= 2) {
+        XYZZ<F>* buf[2] = {S[1], Wt[1]};
+        const uint32_t groups = (uint32_t)pl.WB * Q;
+        uint32_t m = T >> 1;  // length of every array after the first pass
+        {
+            const uint32_t total = groups * m;
+            msm_tree_first_kernel<F><<<(total + 127) / 128, 128, 0, st>>>(S[0], Wt[0], T, Q, total, buf[0]);
+            B2_CUDA(ctx, cudaGetLastError());
+            ctx->n_launches += 1;
+        }
+        int cur = 0;
+        while (m > 1) {
+            const uint32_t total = groups * (m >> 1);
+            msm_tree_pass_kernel<F><<<(total + 127) / 128, 128, 0, st>>>(buf[cur], m, total, buf[cur ^ 1]);
+            B2_CUDA(ctx, cudaGetLastError());
+            ctx->n_launches += 1;
+            m >>= 1;
+            cur ^= 1;
+        }
+        ctx->prof_end(span);
+        B2_CUDA(ctx, cudaMemcpyAsync(fin.data(), buf[cur], fin.size() * sizeof(XYZZ<F>), cudaMemcpyDeviceToHost, st));
+    } else {
+        ctx->prof_end(span);
+        B2_CUDA(ctx, cudaMemcpyAsync(fin.data(), Wt[0], fin.size() * sizeof(XYZZ<F>), cudaMemcpyDeviceToHost, st));
     }
-    ctx->prof_end(span);
-    // window sums -> host, Horner combine (c doublings per window)
-    XYZZ<F> win[32];
-    B2_CUDA(ctx, cudaMemcpyAsync(win, Wt[cur], (size_t)pl.W * sizeof(XYZZ<F>), cudaMemcpyDeviceToHost, st));
     B2_CUDA(ctx, cudaStreamSynchronize(st));
+    // host: per set V_0 + L0 * sum_b 2^b V_{1+b}; then the c-doubling Horner over the sets
+    uint32_t logL0 = 0;
+    while ((1u << logL0) < pl.L0) ++logL0;
     XYZZ<F> acc = XYZZ<F>::inf();
-    for (int w = pl.W - 1; w >= 0; --w) {
+    for (int w = pl.WB - 1; w >= 0; --w) {
         for (int k = 0; k < pl.c; ++k) acc = acc.dbl();
-        acc.add(win[w]);
+        const XYZZ<F>* v = &fin[(size_t)w * Q];
+        XYZZ<F> hi = XYZZ<F>::inf();
+        for (int bit = (int)Q - 2; bit >= 0; --bit) {
+            hi = hi.dbl();
+            hi.add(v[1 + bit]);
+        }
+        for (uint32_t k = 0; k < logL0; ++k) hi = hi.dbl();
+        hi.add(v[0]);
+        acc.add(hi);
     }
     *out_host = acc.to_jac();
+    return B200_OK;
+}
+
+template <class F>
+int msm_fold_build_impl(b200_ctx* ctx, const Affine<F>* d_bases, size_t n, int c, DevBuf& table) {
+    const int W = msm_num_windows(c);
+    if (n == 0 || W > 32 || (double)n * W >= 2147483648.0) return ctx->fail(B200_ERR_ARG, "folded table: bad size");
+    const size_t chunk = n < ((size_t)1 << 20) ? n : ((size_t)1 << 20);
+    DevBuf tmp;
+    if (table.alloc((size_t)W * n * sizeof(Affine<F>)) != cudaSuccess || tmp.alloc((size_t)(W - 1) * chunk * sizeof(XYZZ<F>)) != cudaSuccess) {
+        cudaGetLastError();
+        table.release();
+        return B200_ERR_NOMEM;
+    }
+    cudaStream_t st = ctx->stream;
+    B2_CUDA(ctx, cudaMemcpyAsync(table.p, d_bases, n * sizeof(Affine<F>), cudaMemcpyDeviceToDevice, st));
+    for (size_t n0 = 0; n0 < n; n0 += chunk) {
+        const uint32_t cnt = (uint32_t)(n - n0 < chunk ? n - n0 : chunk);
+        msm_fold_double_kernel<F><<<(cnt + 127) / 128, 128, 0, st>>>(d_bases, (uint32_t)n0, cnt, c, W, tmp.as<XYZZ<F>>());
+        B2_CUDA(ctx, cudaGetLastError());
+        msm_fold_normalize_kernel<F><<<(cnt + 127) / 128, 128, 0, st>>>(tmp.as<XYZZ<F>>(), (uint32_t)n0, cnt, W, (uint32_t)n, table.as<Affine<F>>());
+        B2_CUDA(ctx, cudaGetLastError());
+    }
+    B2_CUDA(ctx, cudaStreamSynchronize(st));
     return B200_OK;
 }
 

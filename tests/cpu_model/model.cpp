@@ -70,32 +70,31 @@ static void model_msm(const uint64_t* scalars, const uint64_t* bases, size_t n, 
                 if (d < 0) p.y = p.y.neg();
                 buckets[(size_t)w * pl.nb + (size_t)((d < 0 ? -d : d) - 1)].add_mixed(p);
             }
-        uint32_t T = pl.nb / pl.L0, log_len = 0;
-        while ((1u << log_len) < pl.L0) ++log_len;
+        const uint32_t T = pl.nb / pl.L0;
         std::vector<XYZZ<F>> S((size_t)pl.W * T), Wt((size_t)pl.W * T);
         for (size_t t = 0; t < S.size(); ++t) {
             XYZZ<F> run = XYZZ<F>::inf(), acc = XYZZ<F>::inf();
             for (int j = (int)pl.L0 - 1; j >= 0; --j) { run.add(buckets[t * pl.L0 + j]); acc.add(run); }
             S[t] = run; Wt[t] = acc;
         }
-        while (T > 1) {
-            const uint32_t L = T < pl.L ? T : pl.L;
-            uint32_t logL = 0; while ((1u << logL) < L) ++logL;
-            std::vector<XYZZ<F>> S2((size_t)pl.W * (T / L)), W2(S2.size());
-            for (size_t t = 0; t < S2.size(); ++t) {
-                XYZZ<F> run = XYZZ<F>::inf(), acc = XYZZ<F>::inf(), wsum = XYZZ<F>::inf();
-                for (int j = (int)L - 1; j >= 0; --j) { acc.add(run); run.add(S[t * L + j]); wsum.add(Wt[t * L + j]); }
-                for (uint32_t k = 0; k < log_len; ++k) acc = acc.dbl();
-                wsum.add(acc);
-                S2[t] = run; W2[t] = wsum;
-            }
-            S.swap(S2); Wt.swap(W2);
-            T /= L; log_len += logL;
-        }
+        // upper part exactly as msm_tree_* + the host Horner of msm_run_impl:
+        //   sum_k k B_k = V_0 + L0 * sum_b 2^b V_{1+b}
+        uint32_t logT = 0; while ((1u << logT) < T) ++logT;
+        const uint32_t Q = 1 + logT;
+        uint32_t logL0 = 0; while ((1u << logL0) < pl.L0) ++logL0;
         XYZZ<F> acc = XYZZ<F>::inf();
-        for (int w = pl.W - 1; w >= 0; --w) {
+        for (int w = pl.WB - 1; w >= 0; --w) {
             for (int k = 0; k < pl.c; ++k) acc = acc.dbl();
-            acc.add(Wt[w]);
+            std::vector<XYZZ<F>> v(Q, XYZZ<F>::inf());
+            for (uint32_t t = 0; t < T; ++t) {
+                v[0].add(Wt[(size_t)w * T + t]);
+                for (uint32_t bit = 0; bit < logT; ++bit) if ((t >> bit) & 1u) v[1 + bit].add(S[(size_t)w * T + t]);
+            }
+            XYZZ<F> hi = XYZZ<F>::inf();
+            for (int bit = (int)Q - 2; bit >= 0; --bit) { hi = hi.dbl(); hi.add(v[1 + bit]); }
+            for (uint32_t k = 0; k < logL0; ++k) hi = hi.dbl();
+            hi.add(v[0]);
+            acc.add(hi);
         }
         res = acc.to_jac();
     }

@@ -161,3 +161,40 @@ def test_batch_scalar_mul_g2(ctx, cref):
     ks[0] = 0
     gen = cref.g2_points_to_array([B.G2_GEN])[0]
     assert np.array_equal(ctx.batch_scalar_mul(gen, ks, 2), cref.g2_batch_mul(gen, ks))
+
+
+@pytest.mark.parametrize("group,n,fold_c", [(1, 5000, 0), (1, 5000, 9), (1, 1 << 15, 13), (1, (1 << 16) + 7, 0),
+                                            (2, 4500, 0), (2, 1 << 13, 11)])
+def test_msm_resident_folded_windows(ctx, cref, group, n, fold_c):
+    """Resident base sets run the folded-window path (tables T[w][i] = 2^(c w) P_i, one shared
+    bucket set); result must equal the oracle's MultiExp, also with fewer scalars than bases."""
+    rng = np.random.default_rng(300 + n + fold_c)
+    bases, _ = (util.known_dlog_bases_g1 if group == 1 else util.known_dlog_bases_g2)(n, seed=n)
+    bases[7] = 0                # infinity base: every multiple stays infinity
+    bases[9] = bases[8]         # repeated base
+    scalars = rand_field(rng, n)
+    scalars[0] = 0
+    scalars[1] = cref.fr(B.R - 1)
+    scalars[2] = cref.fr(1)
+    scalars[9] = scalars[8]
+    ctx.set_option("msm_fold_c", fold_c)
+    ctx.set_option("msm_precompute", 1)
+    try:
+        h = ctx.upload_bases(bases, group)
+    finally:
+        ctx.set_option("msm_fold_c", 0)
+    oracle_msm = cref.msm_g1 if group == 1 else cref.msm_g2
+    to_aff = cref.g1_jac_to_aff if group == 1 else cref.g2_jac_to_aff
+    for m in (n, n - 1234):
+        got = ctx.msm_resident(h, scalars[:m])
+        assert np.array_equal(to_aff(got), to_aff(oracle_msm(scalars[:m], bases[:m]))), (group, n, fold_c, m)
+    h.free()
+    # and the plain path on the same inputs
+    ctx.set_option("msm_precompute", 0)
+    try:
+        h = ctx.upload_bases(bases, group)
+        got = ctx.msm_resident(h, scalars)
+        h.free()
+    finally:
+        ctx.set_option("msm_precompute", 1)
+    assert np.array_equal(to_aff(got), to_aff(oracle_msm(scalars, bases)))

@@ -336,10 +336,10 @@ def gpu_arm(args):
     if rank != 0:
         ctx.close()
         return 0
-    return report(args, world, peak, prof, stage, step_ms, e2e_s, clk, verified, inst, t_setup, wall_dev)
+    return report(args, world, peak, prof, stage, step_ms, e2e_s, clk, verified, inst, t_setup, wall_dev, pk.info())
 
 
-def report(args, world, peak, prof, stage, step_ms, e2e_s, clk, verified, inst, t_setup, wall_dev):
+def report(args, world, peak, prof, stage, step_ms, e2e_s, clk, verified, inst, t_setup, wall_dev, pk_info):
     n = inst.n
     peaks_path = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(peaks_path):
@@ -356,6 +356,12 @@ def report(args, world, peak, prof, stage, step_ms, e2e_s, clk, verified, inst, 
                 "achieved": g1_mac_s / 1e12, "peak": mac_peak / 1e12, "unit": "TMAC32/s", "frac": g1_mac_s / mac_peak,
                 "traffic": None, "launch_ms": g1_launch_ms, "points_per_launch": g1_pts,
                 "algorithmic_mac32_per_point": MAC32_PER_G1_POINT,
+                "algorithmic_model": "SURVEY 8(d): 16 windows x 11 Fp-mul x 136 MAC32 per point, whatever the kernel executes",
+                "executed_mac32_per_point": pk_info["a"]["windows"] * 10 * 136,
+                "executed_frac": g1_pts * pk_info["a"]["windows"] * 10 * 136 / (g1_launch_ms * 1e-3) / mac_peak,
+                "executed_model": f"{pk_info['a']['windows']} windows of c={pk_info['a']['c']} "
+                                  f"({'folded table' if pk_info['a']['folded'] else 'plain bases'}) x XYZZ mixed add 8M+2S x 136; "
+                                  "frac > 1 means fewer field multiplications than the survey's model, not a faster pipe",
                 "peak_source": "measured in this run: register-resident Montgomery-product chains (b200_imad_peak)"}
     # NTT: north_star's HBM view (64 B per element per pass, 2 passes at <= 2^24) and the IMAD view
     passes_model = 1 if inst.log_n <= 12 else (2 if inst.log_n <= 24 else 3)
@@ -391,7 +397,7 @@ def report(args, world, peak, prof, stage, step_ms, e2e_s, clk, verified, inst, 
             "ntt_hbm_gbs": ntt_gbs, "stage_ms": stage,
             "kernel_ms_per_step": {k: v["ms"] / args.steps for k, v in prof.items() if isinstance(v, dict)},
             "g2_acc_frac_of_imad_peak": (g2["units"] * MAC32_PER_G2_POINT / (g2["ms"] * 1e-3) / mac_peak) if g2["ms"] else None,
-            "imad_peak": peak, "verified_known_dlog": verified, "setup_s": t_setup, "wall_s_timed_region": wall_dev,
+            "pk_sets": pk_info, "imad_peak": peak, "verified_known_dlog": verified, "setup_s": t_setup, "wall_s_timed_region": wall_dev,
         },
     }
     if world == 1 and not args.no_cpu:

@@ -31,6 +31,16 @@ class _Timings(C.Structure):
                 ("h2d_ms", "compute_h_ms", "msm_a_ms", "msm_b1_ms", "msm_k_ms", "msm_z_ms", "msm_b2_ms", "total_ms")]
 
 
+class _MsmSetInfo(C.Structure):
+    """b200_msm_set_info."""
+    _fields_ = [("n", C.c_uint64), ("device_bytes", C.c_uint64), ("c", C.c_int32), ("windows", C.c_int32),
+                ("folded", C.c_int32), ("reserved", C.c_int32)]
+
+    def as_dict(self):
+        return {"n": int(self.n), "device_bytes": int(self.device_bytes), "c": int(self.c),
+                "windows": int(self.windows), "folded": int(self.folded)}
+
+
 class Groth16MsmOut(C.Structure):
     """b200_groth16_out: the five MultiExp results before the fix-ups (prove.go:201-290)."""
     _fields_ = [("ar", C.c_uint64 * 12), ("bs1", C.c_uint64 * 12), ("krs", C.c_uint64 * 12),
@@ -95,6 +105,7 @@ def load_library():
         "b200_msm_g2": (i, [vp, i, vp, vp, sz, vp]),
         "b200_bases_upload": (i, [vp, i, i, vp, sz, C.POINTER(vp)]),
         "b200_bases_free": (i, [vp, vp]),
+        "b200_bases_info": (i, [vp, vp, C.POINTER(_MsmSetInfo)]),
         "b200_msm_resident": (i, [vp, vp, vp, sz, vp]),
         "b200_msm_dev": (i, [vp, vp, vp, sz, vp, C.POINTER(C.c_float)]),
         "b200_g1_jac_add": (i, [vp, vp, vp]),
@@ -104,6 +115,7 @@ def load_library():
         "b200_batch_scalar_mul": (i, [vp, i, i, vp, vp, sz, vp]),
         "b200_groth16_pk_upload": (i, [vp, i, C.POINTER(_PkDesc), C.POINTER(vp)]),
         "b200_groth16_pk_free": (i, [vp, vp]),
+        "b200_groth16_pk_info": (i, [vp, vp, C.POINTER(_MsmSetInfo)]),
         "b200_groth16_prove_core": (i, [vp, vp, vp, vp, vp, sz, vp, vp, sz, C.POINTER(Groth16MsmOut), C.POINTER(_Timings)]),
         "b200_groth16_prove_core_dev": (i, [vp, vp, vp, vp, vp, sz, vp, C.POINTER(Groth16MsmOut), C.POINTER(_Timings)]),
         "b200_profile_start": (i, [vp]),
@@ -230,6 +242,11 @@ class Bases:
     def __init__(self, ctx, handle, n, group):
         self.ctx, self.h, self.n, self.group = ctx, handle, n, group
 
+    def info(self):
+        o = _MsmSetInfo()
+        self.ctx._check(self.ctx.lib.b200_bases_info(self.ctx.h, self.h, C.byref(o)))
+        return o.as_dict()
+
     def free(self):
         if self.h:
             self.ctx.lib.b200_bases_free(self.ctx.h, self.h)
@@ -241,6 +258,12 @@ class Groth16ProvingKey:
 
     def __init__(self, ctx, handle, keep):
         self.ctx, self.h, self._keep = ctx, handle, keep
+
+    def info(self):
+        """{'a','b','k','z','g2b'} -> layout and Pippenger plan of each resident base set."""
+        arr = (_MsmSetInfo * 5)()
+        self.ctx._check(self.ctx.lib.b200_groth16_pk_info(self.ctx.h, self.h, arr))
+        return {k: arr[j].as_dict() for j, k in enumerate(("a", "b", "k", "z", "g2b"))}
 
     def free(self):
         if self.h:

@@ -233,11 +233,12 @@ int b200_bases_upload(b200_ctx* ctx, int curve, int group, const uint64_t* bases
     if (e == cudaSuccess && bytes) e = cudaMemcpyAsync(b->pts.p, bases_affine, bytes, cudaMemcpyHostToDevice, ctx->stream);
     if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
     if (e != cudaSuccess) { delete b; return ctx->fail(B200_ERR_CUDA, "bases upload", cudaGetErrorString(e)); }
-    if (ctx->msm_precompute && n >= 4096) {
-        const int c = ctx->msm_fold_c ? ctx->msm_fold_c : msm_fold_window(n);
+    const int c = ctx->msm_fold_c ? ctx->msm_fold_c : msm_fold_window(n);
+    if (ctx->msm_precompute && n >= 4096 && c != 0) {
         DevBuf table;
-        const int st = group == 1 ? msm_fold_build_g1(ctx, b->pts.as<G1Affine>(), n, c, table)
-                                  : msm_fold_build_g2(ctx, b->pts.as<G2Affine>(), n, c, table);
+        const size_t reserve = msm_workspace_bytes(n, group, ctx->msm_c_override, c) + n * sizeof(Fr) + ((size_t)1 << 30);
+        const int st = group == 1 ? msm_fold_build_g1(ctx, b->pts.as<G1Affine>(), n, c, reserve, table)
+                                  : msm_fold_build_g2(ctx, b->pts.as<G2Affine>(), n, c, reserve, table);
         if (st == B200_OK) {
             b->pts.release();
             b->pts.p = table.p; b->pts.bytes = table.bytes;
@@ -253,6 +254,17 @@ int b200_bases_free(b200_ctx* ctx, b200_bases* bases) {
     B2_ENTER(ctx, B200_BN254);
     B2_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     delete bases;
+    return B200_OK;
+}
+
+static void fill_set_info(b200_ctx* ctx, size_t n, size_t bytes, const MsmFold& f, b200_msm_set_info* o) {
+    const MsmPlan p = f.c ? msm_plan_folded(f.c) : msm_plan(n, ctx->msm_c_override);
+    o->n = n; o->device_bytes = bytes; o->c = p.c; o->windows = p.W; o->folded = p.fold; o->reserved = 0;
+}
+int b200_bases_info(b200_ctx* ctx, const b200_bases* bases, b200_msm_set_info* out) {
+    if (!ctx) return B200_ERR_ARG;
+    if (!bases || !out) return ctx->fail(B200_ERR_ARG, "null argument");
+    fill_set_info(ctx, bases->n, bases->pts.bytes, bases->fold, out);
     return B200_OK;
 }
 
@@ -337,6 +349,16 @@ int b200_groth16_pk_free(b200_ctx* ctx, b200_groth16_pk* pk) {
     B2_ENTER(ctx, B200_BN254);
     B2_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     delete pk;
+    return B200_OK;
+}
+int b200_groth16_pk_info(b200_ctx* ctx, const b200_groth16_pk* pk, b200_msm_set_info out[5]) {
+    if (!ctx) return B200_ERR_ARG;
+    if (!pk || !out) return ctx->fail(B200_ERR_ARG, "null argument");
+    fill_set_info(ctx, pk->n_a, pk->A.bytes, pk->fA, out + 0);
+    fill_set_info(ctx, pk->n_b, pk->B.bytes, pk->fB, out + 1);
+    fill_set_info(ctx, pk->n_k, pk->K.bytes, pk->fK, out + 2);
+    fill_set_info(ctx, pk->n_z, pk->Z.bytes, pk->fZ, out + 3);
+    fill_set_info(ctx, pk->n_b, pk->G2B.bytes, pk->fG2B, out + 4);
     return B200_OK;
 }
 int b200_groth16_prove_core(b200_ctx* ctx, const b200_groth16_pk* pk, const uint64_t* a, const uint64_t* b,

@@ -24,13 +24,14 @@ static int upload_range(b200_ctx* ctx, DevBuf& dst, const uint64_t* host, size_t
 
 // Replace a resident base array by its folded-window table when enabled and it fits in memory.
 template <class F>
-static int maybe_fold(b200_ctx* ctx, DevBuf& bases, size_t n, MsmFold& fold, int group) {
+static int maybe_fold(b200_ctx* ctx, DevBuf& bases, size_t n, MsmFold& fold, int group, size_t reserve_bytes) {
     fold = MsmFold();
     if (!ctx->msm_precompute || n < 4096) return B200_OK;
     const int c = ctx->msm_fold_c ? ctx->msm_fold_c : msm_fold_window(n);
+    if (c == 0) return B200_OK;
     DevBuf table;
-    int st = group == 1 ? msm_fold_build_g1(ctx, bases.as<G1Affine>(), n, c, table)
-                        : msm_fold_build_g2(ctx, bases.as<G2Affine>(), n, c, table);
+    int st = group == 1 ? msm_fold_build_g1(ctx, bases.as<G1Affine>(), n, c, reserve_bytes, table)
+                        : msm_fold_build_g2(ctx, bases.as<G2Affine>(), n, c, reserve_bytes, table);
     if (st == B200_ERR_NOMEM) return B200_OK;   // keep the plain bases
     if (st != B200_OK) return st;
     bases.release();
@@ -86,11 +87,18 @@ int groth16_pk_upload(b200_ctx* ctx, const b200_groth16_pk_desc* d, b200_groth16
     if (st == B200_OK) { shard_range(d->n_z, si, sc, &lo, &hi); pk->n_z = hi - lo; pk->z_lo = lo;
         st = upload_range<G1Affine>(ctx, pk->Z, d->g1_z, lo, hi, ps); }
     if (st == B200_OK && cudaStreamSynchronize(ctx->stream) != cudaSuccess) st = ctx->fail(B200_ERR_CUDA, "pk upload");
-    if (st == B200_OK) st = maybe_fold<Fp>(ctx, pk->A, pk->n_a, pk->fA, 1);
-    if (st == B200_OK) st = maybe_fold<Fp>(ctx, pk->B, pk->n_b, pk->fB, 1);
-    if (st == B200_OK) st = maybe_fold<Fp>(ctx, pk->K, pk->n_k, pk->fK, 1);
-    if (st == B200_OK) st = maybe_fold<Fp>(ctx, pk->Z, pk->n_z, pk->fZ, 1);
-    if (st == B200_OK) st = maybe_fold<Fp2>(ctx, pk->G2B, pk->n_b, pk->fG2B, 2);
+    // Folded tables take what is left after the prover's own working set: the domain tables (built
+    // below), a/b/c/W, and the largest MSM scratch.  G2 first: it gains the most per byte.
+    const size_t n_dom = (size_t)1 << d->log_n;
+    const size_t n_max = std::max(std::max(pk->n_a, pk->n_b), std::max(pk->n_k, pk->n_z));
+    const int fc = ctx->msm_fold_c ? ctx->msm_fold_c : msm_fold_window(n_max);
+    const size_t reserve = 9 * n_dom * sizeof(Fr) + d->n_wires * sizeof(Fr) + d->n_wires * 4
+                         + msm_workspace_bytes(n_max, 2, ctx->msm_c_override, fc) + ((size_t)1 << 30);
+    if (st == B200_OK) st = maybe_fold<Fp2>(ctx, pk->G2B, pk->n_b, pk->fG2B, 2, reserve);
+    if (st == B200_OK) st = maybe_fold<Fp>(ctx, pk->A, pk->n_a, pk->fA, 1, reserve);
+    if (st == B200_OK) st = maybe_fold<Fp>(ctx, pk->B, pk->n_b, pk->fB, 1, reserve);
+    if (st == B200_OK) st = maybe_fold<Fp>(ctx, pk->K, pk->n_k, pk->fK, 1, reserve);
+    if (st == B200_OK) st = maybe_fold<Fp>(ctx, pk->Z, pk->n_z, pk->fZ, 1, reserve);
     // build the computeH tables now so the first proof does not pay for them
     const Fr* t;
     if (st == B200_OK) st = ntt_domain_table(ctx, pk->dom, NttDomain::H_A, &t);

@@ -48,19 +48,22 @@ struct MsmPlan {
 
 // Folded windows (resident base sets only): with T[w][i] = 2^(c w) P_i stored next to the bases,
 // digit d_w of scalar i adds sign(d_w) T[w][i] to bucket |d_w| of ONE shared bucket set, so the
-// bucket reduction is paid once instead of W times and c can grow: 2^24 points run 12 windows of
-// 22 bits (12 n additions) instead of 15 windows of 17 bits.  Costs W x the base memory -- the
-// reason this design wants a 180 GB part.  c minimises additions + reduction work.
+// bucket reduction is paid once instead of W times and c can grow: 2^24 points run 13 windows of
+// 20 bits (13 n additions) instead of 15 windows of 17 bits.  Costs W x the base memory -- the
+// reason this design wants a 180 GB part.  The widths are the measured optimum of
+// scripts/fold_sweep.py on a B200 (16, 17 and 20 leave a full or nearly full top window; 18, 19,
+// 21 pile the top digits into a few buckets).  Returns 0 when the sorted-entry index (w n + i) does
+// not fit 31 bits.
 inline int msm_fold_window(size_t n) {
-    int best = 8;
-    double best_cost = 1e300;
-    for (int c = 8; c <= 24; ++c) {
-        const int W = msm_num_windows(c);
-        if ((double)n * W >= 2147483648.0) continue;       // sorted entries carry (w n + i) in 31 bits
-        const double cost = (double)n * W * 10.0 + (double)((size_t)1 << (c - 1)) * 2.0 * 14.0 * 1.5;
-        if (cost < best_cost) { best_cost = cost; best = c; }
-    }
-    return best;
+    int log_n = 0;
+    while (((size_t)1 << log_n) < n) ++log_n;
+    int c;
+    if (log_n >= 19) c = 20;
+    else if (log_n >= 17) c = 17;
+    else if (log_n >= 15) c = log_n;
+    else c = 13;
+    if ((double)n * msm_num_windows(c) >= 2147483648.0) return 0;
+    return c;
 }
 
 inline MsmPlan msm_plan(size_t n, int c_override) {
@@ -273,9 +276,11 @@ __device__ __forceinline__ void msm_task_range(uint32_t cnt, uint32_t nt, uint32
     *first = j0;
     *size = j0 >= cnt ? 0u : (cnt - j0 < cb ? cnt - j0 : cb);
 }
-// buckets cut into more than MSM_SMALL_SPLIT pieces are listed in big_list (big_count[0] entries)
-// and merged by one CTA each (msm_combine_big_kernel).
+// buckets cut into more than MSM_SMALL_SPLIT pieces are listed in big_list: up to MSM_WARP_SPLIT
+// pieces from the front (big_count[0] entries, merged by one warp each), more from the back
+// (big_count[1] entries, merged by one CTA each).
 constexpr uint32_t MSM_SMALL_SPLIT = 8;
+constexpr uint32_t MSM_WARP_SPLIT = 256;
 static __global__ void msm_task_count_kernel(const uint32_t* __restrict__ counts, uint32_t n_buckets, uint32_t chunk,
                                              uint32_t* __restrict__ ntasks, uint32_t* __restrict__ big_count,
                                              uint32_t* __restrict__ big_list) {
@@ -285,7 +290,8 @@ static __global__ void msm_task_count_kernel(const uint32_t* __restrict__ counts
     uint32_t nt = c <= chunk ? 1u : (c + chunk - 1u) / chunk;
     if (nt > MSM_MAX_TASKS_PER_BUCKET) nt = MSM_MAX_TASKS_PER_BUCKET;
     ntasks[b] = nt;
-    if (nt > MSM_SMALL_SPLIT) big_list[atomicAdd(big_count, 1u)] = b;
+    if (nt > MSM_WARP_SPLIT) big_list[n_buckets - 1u - atomicAdd(big_count + 1, 1u)] = b;
+    else if (nt > MSM_SMALL_SPLIT) big_list[atomicAdd(big_count, 1u)] = b;
 }
 static __global__ void msm_task_fill_kernel(const uint32_t* __restrict__ ntasks, const uint32_t* __restrict__ task_off,
                                             uint32_t n_buckets, uint32_t* __restrict__ task_bucket) {
@@ -422,6 +428,27 @@ __global__ void __launch_bounds__(128) msm_combine_kernel(const uint32_t* __rest
     st_vec(buckets + b, acc);
 }
 
+// buckets cut into MSM_SMALL_SPLIT+1..MSM_WARP_SPLIT pieces: one warp per bucket
+template <class F>
+__global__ void __launch_bounds__(128) msm_combine_warp_kernel(const uint32_t* __restrict__ big_count, const uint32_t* __restrict__ big_list,
+                                        const uint32_t* __restrict__ task_off, const uint32_t* __restrict__ ntasks,
+                                        const XYZZ<F>* __restrict__ partials, XYZZ<F>* __restrict__ buckets) {
+    const uint32_t lane = threadIdx.x & 31u;
+    const uint32_t warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, n_warps = (gridDim.x * blockDim.x) >> 5;
+    const uint32_t n_mid = big_count[0];
+    for (uint32_t k = warp; k < n_mid; k += n_warps) {
+        const uint32_t b = big_list[k], nt = ntasks[b], o = task_off[b];
+        XYZZ<F> acc = XYZZ<F>::inf();
+        for (uint32_t j = lane; j < nt; j += 32u) acc.add(ld_vec(partials + o + j));
+#pragma unroll 1
+        for (int d = 16; d >= 1; d >>= 1) {
+            const XYZZ<F> other = shfl_down_point(acc, d);
+            if ((int)lane < d) acc.add(other);
+        }
+        if (lane == 0) st_vec(buckets + b, acc);
+    }
+}
+
 // heavily split buckets (skewed digits): one CTA per bucket -- strided partial sums per thread, a
 // shuffle tree per warp, the warp results through shared memory.
 constexpr int COMBINE_BIG_THREADS = 256;
@@ -431,9 +458,9 @@ __global__ void __launch_bounds__(COMBINE_BIG_THREADS) msm_combine_big_kernel(co
                                        const XYZZ<F>* __restrict__ partials, XYZZ<F>* __restrict__ buckets) {
     __shared__ XYZZ<F> warp_sum[COMBINE_BIG_THREADS / 32];
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
-    const uint32_t n_big = big_count[0];
+    const uint32_t n_big = big_count[1];
     for (uint32_t k = blockIdx.x; k < n_big; k += gridDim.x) {
-        const uint32_t b = big_list[k], nt = ntasks[b], o = task_off[b];
+        const uint32_t b = big_list[-(int64_t)k], nt = ntasks[b], o = task_off[b];   // big_list = last slot, filled downwards
         XYZZ<F> acc = XYZZ<F>::inf();
         for (uint32_t j = threadIdx.x; j < nt; j += blockDim.x) acc.add(ld_vec(partials + o + j));
 #pragma unroll 1

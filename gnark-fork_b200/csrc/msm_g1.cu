@@ -9,7 +9,7 @@ int msm_g1_run(b200_ctx* ctx, const G1Affine* d_bases, const Fr* d_scalars, cons
                G1Jac* out_host, void* ws, const MsmFold* fold) {
     return msm_run_impl<Fp>(ctx, d_bases, d_scalars, d_idx_map, n, out_host, ws, fold);
 }
-int msm_fold_build_g1(b200_ctx* ctx, const G1Affine* d_bases, size_t n, int c, DevBuf& table) {
-    return msm_fold_build_impl<Fp>(ctx, d_bases, n, c, table);
+int msm_fold_build_g1(b200_ctx* ctx, const G1Affine* d_bases, size_t n, int c, size_t reserve_bytes, DevBuf& table) {
+    return msm_fold_build_impl<Fp>(ctx, d_bases, n, c, reserve_bytes, table);
 }
 }  // namespace b200

@@ -22,8 +22,8 @@ int msm_g2_run(b200_ctx* ctx, const G2Affine* d_bases, const Fr* d_scalars, cons
                G2Jac* out_host, void* ws, const MsmFold* fold);
 // builds the table for n resident points (device) into `table` ((W x n) affine points); returns
 // B200_ERR_NOMEM without side effects when the table does not fit.
-int msm_fold_build_g1(b200_ctx* ctx, const G1Affine* d_bases, size_t n, int c, DevBuf& table);
-int msm_fold_build_g2(b200_ctx* ctx, const G2Affine* d_bases, size_t n, int c, DevBuf& table);
+int msm_fold_build_g1(b200_ctx* ctx, const G1Affine* d_bases, size_t n, int c, size_t reserve_bytes, DevBuf& table);
+int msm_fold_build_g2(b200_ctx* ctx, const G2Affine* d_bases, size_t n, int c, size_t reserve_bytes, DevBuf& table);
 
 #if defined(__CUDACC__)
 
@@ -60,7 +60,7 @@ struct MsmLayout {
         off_task_off = a.off; a.take(M * 4);
         off_task_bucket = a.off; a.take((size_t)max_tasks * 4);
         off_partials = a.off; a.take((size_t)max_tasks * sizeof(XYZZ<F>));
-        off_big = a.off; a.take((M + 1) * 4);   // [0] = count, then the list
+        off_big = a.off; a.take((M + 2) * 4);   // [0], [1] = counts, then the list (front: warp-merged, back: CTA-merged)
         off_order = a.off; a.take((size_t)max_tasks * 4);
         off_order_hist = a.off; a.take((size_t)ORDER_BINS * 4 * 2);
         order_shift = 0;
@@ -131,8 +131,8 @@ int msm_run_impl(b200_ctx* ctx, const Affine<F>* d_bases, const Fr* d_scalars, c
     }
     {
         const int bs = 256;
-        B2_CUDA(ctx, cudaMemsetAsync(big, 0, 4, st));
-        msm_task_count_kernel<<<(M + bs - 1) / bs, bs, 0, st>>>(counts, M, lay.chunk, ntasks, big, big + 1);
+        B2_CUDA(ctx, cudaMemsetAsync(big, 0, 8, st));
+        msm_task_count_kernel<<<(M + bs - 1) / bs, bs, 0, st>>>(counts, M, lay.chunk, ntasks, big, big + 2);
         B2_CUDA(ctx, cudaGetLastError());
         msm_scan_sums_kernel<<<lay.scan_blocks, SCAN_THREADS, 0, st>>>(ntasks, M, bsums);
         B2_CUDA(ctx, cudaGetLastError());
@@ -164,7 +164,9 @@ int msm_run_impl(b200_ctx* ctx, const Affine<F>* d_bases, const Fr* d_scalars, c
         span = ctx->prof_begin(B200_PROF_MSM_REDUCE, (double)n);
         msm_combine_kernel<F><<<(M + bs - 1) / bs, bs, 0, st>>>(task_off, ntasks, M, partials, buckets);
         B2_CUDA(ctx, cudaGetLastError());
-        msm_combine_big_kernel<F><<<ctx->sm_count * 2, COMBINE_BIG_THREADS, 0, st>>>(big, big + 1, task_off, ntasks, partials, buckets);
+        msm_combine_warp_kernel<F><<<ctx->sm_count * 8, 128, 0, st>>>(big, big + 2, task_off, ntasks, partials, buckets);
+        B2_CUDA(ctx, cudaGetLastError());
+        msm_combine_big_kernel<F><<<ctx->sm_count * 2, COMBINE_BIG_THREADS, 0, st>>>(big, big + 2 + (M - 1), task_off, ntasks, partials, buckets);
         B2_CUDA(ctx, cudaGetLastError());
     }
     // reduction: leaf running sums, then binary trees for the Q plain sums of every bucket set
@@ -174,7 +176,7 @@ int msm_run_impl(b200_ctx* ctx, const Affine<F>* d_bases, const Fr* d_scalars, c
         msm_reduce_leaf_kernel<F><<<(nodes + 63) / 64, 64, 0, st>>>(buckets, nodes, pl.L0, S[0], Wt[0]);
         B2_CUDA(ctx, cudaGetLastError());
     }
-    ctx->n_launches += 17;  // digits, 2 x 3 scan, scatter, task count/fill, 3 x order, accumulate, 2 x combine, leaf
+    ctx->n_launches += 18;  // digits, 2 x 3 scan, scatter, task count/fill, 3 x order, accumulate, 3 x combine, leaf
     std::vector<XYZZ<F>> fin((size_t)pl.WB * Q);
     if (T >= 2) {
         XYZZ<F>* buf[2] = {S[1], Wt[1]};
@@ -223,10 +225,16 @@ int msm_run_impl(b200_ctx* ctx, const Affine<F>* d_bases, const Fr* d_scalars, c
 }
 
 template <class F>
-int msm_fold_build_impl(b200_ctx* ctx, const Affine<F>* d_bases, size_t n, int c, DevBuf& table) {
+int msm_fold_build_impl(b200_ctx* ctx, const Affine<F>* d_bases, size_t n, int c, size_t reserve_bytes, DevBuf& table) {
     const int W = msm_num_windows(c);
     if (n == 0 || W > 32 || (double)n * W >= 2147483648.0) return ctx->fail(B200_ERR_ARG, "folded table: bad size");
     const size_t chunk = n < ((size_t)1 << 20) ? n : ((size_t)1 << 20);
+    {   // the table must leave `reserve_bytes` of device memory to the caller's later allocations
+        size_t free_b = 0, total_b = 0;
+        if (cudaMemGetInfo(&free_b, &total_b) != cudaSuccess) { cudaGetLastError(); return B200_ERR_NOMEM; }
+        const size_t need = (size_t)W * n * sizeof(Affine<F>) + (size_t)(W - 1) * chunk * sizeof(XYZZ<F>) + reserve_bytes;
+        if (need > free_b) return B200_ERR_NOMEM;
+    }
     DevBuf tmp;
     if (table.alloc((size_t)W * n * sizeof(Affine<F>)) != cudaSuccess || tmp.alloc((size_t)(W - 1) * chunk * sizeof(XYZZ<F>)) != cudaSuccess) {
         cudaGetLastError();

@@ -156,6 +156,17 @@ int b200_msm_g2(b200_ctx *ctx, int curve, const uint64_t *scalars, const uint64_
 int b200_bases_upload(b200_ctx *ctx, int curve, int group, const uint64_t *bases_affine, size_t n,
                       b200_bases **out);
 int b200_bases_free(b200_ctx *ctx, b200_bases *bases);
+/* How a resident base set is laid out and which Pippenger plan its MSMs run (for roofline
+ * accounting: a launch performs n * windows bucket additions). */
+typedef struct b200_msm_set_info {
+    uint64_t n;            /* points */
+    uint64_t device_bytes; /* bases or folded-window table */
+    int32_t c;             /* window width */
+    int32_t windows;       /* signed-digit windows per scalar */
+    int32_t folded;        /* 1: precomputed 2^(c w) P table, one shared bucket set */
+    int32_t reserved;
+} b200_msm_set_info;
+int b200_bases_info(b200_ctx *ctx, const b200_bases *bases, b200_msm_set_info *out);
 /* scalars on the host (copied in) ... */
 int b200_msm_resident(b200_ctx *ctx, const b200_bases *bases, const uint64_t *scalars, size_t n,
                       uint64_t *out_jac);
@@ -201,6 +212,8 @@ typedef struct b200_groth16_pk_desc {
 
 int b200_groth16_pk_upload(b200_ctx *ctx, int curve, const b200_groth16_pk_desc *desc, b200_groth16_pk **out);
 int b200_groth16_pk_free(b200_ctx *ctx, b200_groth16_pk *pk);
+/* out[0..4] = G1.A, G1.B, G1.K, G1.Z, G2.B of this shard. */
+int b200_groth16_pk_info(b200_ctx *ctx, const b200_groth16_pk *pk, b200_msm_set_info out[5]);
 
 /* Per-stage device times in milliseconds (CUDA events on the ctx stream). */
 typedef struct b200_timings {

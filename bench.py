@@ -208,6 +208,12 @@ def cpu_prove_seconds(sample_log, log_n, seed=5):
     2^sample_log, scaled by 2^(log_n - sample_log).  Returns (seconds at log_n, cores, text)."""
     from oracle import cref
     lib = cref.lib()
+    # all host cores this process may use (torchrun exports OMP_NUM_THREADS=1: not what is wanted here)
+    try:
+        avail = len(os.sched_getaffinity(0))
+    except AttributeError:
+        avail = os.cpu_count() or 1
+    lib.oracle_set_threads(int(avail))
     cores = int(lib.oracle_max_threads())
     m = 1 << sample_log
     rng = np.random.default_rng(seed)

@@ -17,6 +17,7 @@ struct b200_ctx {
     int device = 0;
     int sm_count = 0;
     cudaStream_t stream = nullptr;
+    cudaStream_t copy_stream = nullptr;     // per-proof input copies, overlapped with the witness MSMs
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     std::string err;
     std::vector<b200::NttDomain*> domains;  // cache keyed by (log_n, generator, coset_gen)
@@ -40,15 +41,15 @@ struct b200_ctx {
         return e;
     }
     // returns an index to pass to prof_end (-1 when profiling is off)
-    int prof_begin(int slot, double units) {
+    int prof_begin(int slot, double units, cudaStream_t on = nullptr) {
         if (!prof_on) return -1;
         ProfSpan sp{slot, units, prof_event(), prof_event()};
-        cudaEventRecord(sp.e0, stream);
+        cudaEventRecord(sp.e0, on ? on : stream);
         prof_spans.push_back(sp);
         return (int)prof_spans.size() - 1;
     }
-    void prof_end(int idx) {
-        if (idx >= 0) cudaEventRecord(prof_spans[idx].e1, stream);
+    void prof_end(int idx, cudaStream_t on = nullptr) {
+        if (idx >= 0) cudaEventRecord(prof_spans[idx].e1, on ? on : stream);
     }
 
     int fail(int status, const char* what, const char* detail = nullptr) {

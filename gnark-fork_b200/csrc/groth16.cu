@@ -146,19 +146,18 @@ int groth16_prove_core(b200_ctx* ctx, const b200_groth16_pk* pk, const uint64_t*
     void* ws = base + o_msm;
     cudaStream_t st = ctx->stream;
 
-    cudaEvent_t ev[9];
-    for (auto& e : ev) B2_CUDA(ctx, cudaEventCreate(&e));
-    struct EvGuard { cudaEvent_t* e; ~EvGuard() { for (int i = 0; i < 9; ++i) cudaEventDestroy(e[i]); } } guard{ev};
+    cudaStream_t cp = ctx->copy_stream;
+    cudaEvent_t ev[11];
+    for (auto& e : ev) B2_CUDA(ctx, cudaEventCreateWithFlags(&e, cudaEventDefault));
+    struct EvGuard { cudaEvent_t* e; ~EvGuard() { for (int i = 0; i < 11; ++i) cudaEventDestroy(e[i]); } } guard{ev};
+    cudaEvent_t ev_w = ev[9], ev_abc = ev[10];
 
+    // Copies run on their own stream: W first (the four witness MSMs need only W), then a, b, c,
+    // which computeH picks up after those MSMs -- the ~2 GiB of PCIe traffic hides behind them.
     B2_CUDA(ctx, cudaEventRecord(ev[0], st));
-    const int span = ctx->prof_begin(B200_PROF_COPY_IN, (double)(3 * n_constraints + pk->n_wires) * sizeof(Fr));
-    const uint64_t* src[3] = {a, b, c};
-    Fr* dst[3] = {d_a, d_b, d_c};
-    for (int i = 0; i < 3; ++i) {
-        if (n_constraints) B2_CUDA(ctx, cudaMemcpyAsync(dst[i], src[i], n_constraints * sizeof(Fr), cudaMemcpyDefault, st));
-        if (n > n_constraints) B2_CUDA(ctx, cudaMemsetAsync(dst[i] + n_constraints, 0, (n - n_constraints) * sizeof(Fr), st));
-    }
-    B2_CUDA(ctx, cudaMemcpyAsync(d_w, w, pk->n_wires * sizeof(Fr), cudaMemcpyDefault, st));
+    B2_CUDA(ctx, cudaStreamWaitEvent(cp, ev[0], 0));
+    const int span = ctx->prof_begin(B200_PROF_COPY_IN, (double)(3 * n_constraints + pk->n_wires) * sizeof(Fr), cp);
+    B2_CUDA(ctx, cudaMemcpyAsync(d_w, w, pk->n_wires * sizeof(Fr), cudaMemcpyDefault, cp));
     if (n_remove) {
         // prove.go:238-242: K scalars are W[nb_public:] minus the committed wires
         std::vector<uint32_t> map;
@@ -169,28 +168,40 @@ int groth16_prove_core(b200_ctx* ctx, const b200_groth16_pk* pk, const uint64_t*
             map.push_back((uint32_t)(pk->nb_public + i));
         }
         if (map.size() != pk->full_n_k) return ctx->fail(B200_ERR_ARG, "k_remove must be sorted and unique");
-        B2_CUDA(ctx, cudaMemcpyAsync(d_kmap, map.data() + pk->k_lo, pk->n_k * 4, cudaMemcpyHostToDevice, st));
-        B2_CUDA(ctx, cudaStreamSynchronize(st));  // `map` dies at scope exit
+        B2_CUDA(ctx, cudaMemcpyAsync(d_kmap, map.data() + pk->k_lo, pk->n_k * 4, cudaMemcpyHostToDevice, cp));
+        B2_CUDA(ctx, cudaStreamSynchronize(cp));  // `map` dies at scope exit
     }
-    ctx->prof_end(span);
-    B2_CUDA(ctx, cudaEventRecord(ev[1], st));
-    B2_TRY(ntt_compute_h(ctx, pk->dom, d_a, d_b, d_c));
-    B2_CUDA(ctx, cudaEventRecord(ev[2], st));
+    B2_CUDA(ctx, cudaEventRecord(ev_w, cp));
+    const uint64_t* src[3] = {a, b, c};
+    Fr* dst[3] = {d_a, d_b, d_c};
+    for (int i = 0; i < 3; ++i) {
+        if (n_constraints) B2_CUDA(ctx, cudaMemcpyAsync(dst[i], src[i], n_constraints * sizeof(Fr), cudaMemcpyDefault, cp));
+        if (n > n_constraints) B2_CUDA(ctx, cudaMemsetAsync(dst[i] + n_constraints, 0, (n - n_constraints) * sizeof(Fr), cp));
+    }
+    ctx->prof_end(span, cp);
+    B2_CUDA(ctx, cudaEventRecord(ev_abc, cp));
 
     G1Jac ja, jb1, jk, jz;
     G2Jac jb2;
+    B2_CUDA(ctx, cudaStreamWaitEvent(st, ev_w, 0));
+    B2_CUDA(ctx, cudaEventRecord(ev[1], st));
     B2_TRY(msm_g1_run(ctx, pk->A.as<G1Affine>(), d_w, pk->mapA.as<uint32_t>(), pk->n_a, &ja, ws, &pk->fA));
-    B2_CUDA(ctx, cudaEventRecord(ev[3], st));
+    B2_CUDA(ctx, cudaEventRecord(ev[2], st));
     B2_TRY(msm_g1_run(ctx, pk->B.as<G1Affine>(), d_w, pk->mapB.as<uint32_t>(), pk->n_b, &jb1, ws, &pk->fB));
-    B2_CUDA(ctx, cudaEventRecord(ev[4], st));
+    B2_CUDA(ctx, cudaEventRecord(ev[3], st));
     if (d_kmap) B2_TRY(msm_g1_run(ctx, pk->K.as<G1Affine>(), d_w, d_kmap, pk->n_k, &jk, ws, &pk->fK));
     else B2_TRY(msm_g1_run(ctx, pk->K.as<G1Affine>(), d_w + pk->nb_public + pk->k_lo, nullptr, pk->n_k, &jk, ws, &pk->fK));
-    B2_CUDA(ctx, cudaEventRecord(ev[5], st));
-    B2_TRY(msm_g1_run(ctx, pk->Z.as<G1Affine>(), d_a + pk->z_lo, nullptr, pk->n_z, &jz, ws, &pk->fZ));
-    B2_CUDA(ctx, cudaEventRecord(ev[6], st));
+    B2_CUDA(ctx, cudaEventRecord(ev[4], st));
     B2_TRY(msm_g2_run(ctx, pk->G2B.as<G2Affine>(), d_w, pk->mapB.as<uint32_t>(), pk->n_b, &jb2, ws, &pk->fG2B));
+    B2_CUDA(ctx, cudaEventRecord(ev[5], st));
+    B2_CUDA(ctx, cudaStreamWaitEvent(st, ev_abc, 0));
+    B2_CUDA(ctx, cudaEventRecord(ev[6], st));
+    B2_TRY(ntt_compute_h(ctx, pk->dom, d_a, d_b, d_c));
     B2_CUDA(ctx, cudaEventRecord(ev[7], st));
+    B2_TRY(msm_g1_run(ctx, pk->Z.as<G1Affine>(), d_a + pk->z_lo, nullptr, pk->n_z, &jz, ws, &pk->fZ));
+    B2_CUDA(ctx, cudaEventRecord(ev[8], st));
     B2_CUDA(ctx, cudaStreamSynchronize(st));
+    B2_CUDA(ctx, cudaStreamSynchronize(cp));
 
     memcpy(out->ar, &ja, sizeof ja);
     memcpy(out->bs1, &jb1, sizeof jb1);
@@ -198,14 +209,14 @@ int groth16_prove_core(b200_ctx* ctx, const b200_groth16_pk* pk, const uint64_t*
     memcpy(out->krs2, &jz, sizeof jz);
     memcpy(out->bs2, &jb2, sizeof jb2);
     if (tm) {
-        tm->h2d_ms = ev_ms(ev[0], ev[1]);
-        tm->compute_h_ms = ev_ms(ev[1], ev[2]);
-        tm->msm_a_ms = ev_ms(ev[2], ev[3]);
-        tm->msm_b1_ms = ev_ms(ev[3], ev[4]);
-        tm->msm_k_ms = ev_ms(ev[4], ev[5]);
-        tm->msm_z_ms = ev_ms(ev[5], ev[6]);
-        tm->msm_b2_ms = ev_ms(ev[6], ev[7]);
-        tm->total_ms = ev_ms(ev[0], ev[7]);
+        tm->h2d_ms = ev_ms(ev[0], ev_abc);           // on the copy stream, overlapped with the witness MSMs
+        tm->msm_a_ms = ev_ms(ev[1], ev[2]);
+        tm->msm_b1_ms = ev_ms(ev[2], ev[3]);
+        tm->msm_k_ms = ev_ms(ev[3], ev[4]);
+        tm->msm_b2_ms = ev_ms(ev[4], ev[5]);
+        tm->compute_h_ms = ev_ms(ev[6], ev[7]);
+        tm->msm_z_ms = ev_ms(ev[7], ev[8]);
+        tm->total_ms = ev_ms(ev[0], ev[8]);
     }
     return B200_OK;
 }

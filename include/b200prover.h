@@ -215,7 +215,9 @@ int b200_groth16_pk_free(b200_ctx *ctx, b200_groth16_pk *pk);
 /* out[0..4] = G1.A, G1.B, G1.K, G1.Z, G2.B of this shard. */
 int b200_groth16_pk_info(b200_ctx *ctx, const b200_groth16_pk *pk, b200_msm_set_info out[5]);
 
-/* Per-stage device times in milliseconds (CUDA events on the ctx stream). */
+/* Per-stage device times in milliseconds (CUDA events).  The input copies run on a second stream:
+ * W first, then a, b, c, overlapped with the four witness MSMs (order on the device: A, B1, K, B2,
+ * computeH, Z).  h2d_ms spans the copy stream and is NOT a summand of total_ms. */
 typedef struct b200_timings {
     float h2d_ms, compute_h_ms, msm_a_ms, msm_b1_ms, msm_k_ms, msm_z_ms, msm_b2_ms, total_ms;
 } b200_timings;

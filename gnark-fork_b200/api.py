@@ -118,6 +118,9 @@ def load_library():
         "b200_groth16_pk_info": (i, [vp, vp, C.POINTER(_MsmSetInfo)]),
         "b200_groth16_prove_core": (i, [vp, vp, vp, vp, vp, sz, vp, vp, sz, C.POINTER(Groth16MsmOut), C.POINTER(_Timings)]),
         "b200_groth16_prove_core_dev": (i, [vp, vp, vp, vp, vp, sz, vp, C.POINTER(Groth16MsmOut), C.POINTER(_Timings)]),
+        "b200_groth16_msms_dev": (i, [vp, vp, vp, vp, C.POINTER(Groth16MsmOut), C.POINTER(_Timings)]),
+        "b200_ntt_dist_phase": (i, [vp, i, u, vp, vp, vp, vp, u, u, i, i, i]),
+        "b200_fr_mul_sub_dev": (i, [vp, i, vp, vp, vp, sz]),
         "b200_profile_start": (i, [vp]),
         "b200_profile_read": (i, [vp, C.POINTER(_Profile)]),
         "b200_groth16_finalize": (i, [C.POINTER(Groth16MsmOut), vp, vp, vp, vp, vp, vp, vp, vp, vp, vp]),
@@ -209,6 +212,18 @@ def groth16_proof_bytes(ar, bs, krs) -> bytes:
 
 
 # ---- handles ------------------------------------------------------------------------------
+def _dev_ptr(x):
+    """Device address of a DeviceVector, a torch CUDA tensor, or a raw integer."""
+    if hasattr(x, "data_ptr"):
+        return C.c_void_p(x.data_ptr())
+    p = getattr(x, "ptr", x)
+    return p if isinstance(p, C.c_void_p) else C.c_void_p(int(p))
+
+
+DIST_PACK, DIST_DIF_LOCAL, DIST_DIF_CROSS, DIST_DIT_LOCAL, DIST_DIT_CROSS = range(5)
+SCALE_NONE, SCALE_H_A, SCALE_H_BC, SCALE_COSETINV_BR, SCALE_NINV = range(5)
+
+
 class DeviceVector:
     """A raw device buffer (iciclegnark.OnDeviceData analogue, icicle.go:228,248)."""
 
@@ -428,6 +443,22 @@ class Context:
         self._check(self.lib.b200_groth16_prove_core_dev(self.h, pk.h, a.ptr, b.ptr, c.ptr, n_constraints, w.ptr,
                                                          C.byref(out), C.byref(tm)))
         return out, {k: getattr(tm, k) for k, _ in _Timings._fields_}
+
+    def groth16_msms_dev(self, pk: Groth16ProvingKey, w, h):
+        """The five MSMs with this shard's range of h supplied by the distributed computeH.
+        w, h: DeviceVector or any object with an integer/ctypes `.ptr` (e.g. a torch tensor's data_ptr)."""
+        out, tm = Groth16MsmOut(), _Timings()
+        self._check(self.lib.b200_groth16_msms_dev(self.h, pk.h, _dev_ptr(w), _dev_ptr(h), C.byref(out), C.byref(tm)))
+        return out, {k: getattr(tm, k) for k, _ in _Timings._fields_}
+
+    # -- distributed computeH phases (include/b200prover.h: b200_dist_phase / b200_dist_scale)
+    def ntt_dist_phase(self, log_n, generator, coset_gen, data, tmp, log_ranks, rank, phase, inverse, scale=0):
+        self._check(self.lib.b200_ntt_dist_phase(self.h, BN254, log_n, _ptr(_u64(generator)), _ptr(_u64(coset_gen)),
+                                                 _dev_ptr(data), _dev_ptr(tmp), log_ranks, rank, int(phase),
+                                                 int(inverse), int(scale)))
+
+    def fr_mul_sub_dev(self, a, b, c, n):
+        self._check(self.lib.b200_fr_mul_sub_dev(self.h, BN254, _dev_ptr(a), _dev_ptr(b), _dev_ptr(c), n))
 
     # -- per-kernel-class device times (CUDA events on the launching stream)
     def profile_start(self):

@@ -369,7 +369,7 @@ int b200_groth16_prove_core(b200_ctx* ctx, const b200_groth16_pk* pk, const uint
     B2_ENTER(ctx, B200_BN254);
     if (!pk || !out || !w || (n_constraints && (!a || !b || !c)) || (n_remove && !k_remove))
         return ctx->fail(B200_ERR_ARG, "null argument");
-    return groth16_prove_core(ctx, pk, a, b, c, n_constraints, w, k_remove, n_remove, out, timings);
+    return groth16_prove_core(ctx, pk, a, b, c, n_constraints, w, k_remove, n_remove, nullptr, out, timings);
 }
 
 int b200_groth16_prove_core_dev(b200_ctx* ctx, const b200_groth16_pk* pk, const void* a_dev, const void* b_dev,
@@ -379,7 +379,49 @@ int b200_groth16_prove_core_dev(b200_ctx* ctx, const b200_groth16_pk* pk, const 
     if (!pk || !out || !w_dev || (n_constraints && (!a_dev || !b_dev || !c_dev)))
         return ctx->fail(B200_ERR_ARG, "null argument");
     return groth16_prove_core(ctx, pk, (const uint64_t*)a_dev, (const uint64_t*)b_dev, (const uint64_t*)c_dev,
-                              n_constraints, (const uint64_t*)w_dev, nullptr, 0, out, timings);
+                              n_constraints, (const uint64_t*)w_dev, nullptr, 0, nullptr, out, timings);
+}
+
+int b200_groth16_msms_dev(b200_ctx* ctx, const b200_groth16_pk* pk, const void* w_dev, const void* h_dev,
+                          b200_groth16_out* out, b200_timings* timings) {
+    B2_ENTER(ctx, B200_BN254);
+    if (!pk || !out || !w_dev || !h_dev) return ctx->fail(B200_ERR_ARG, "null argument");
+    return groth16_prove_core(ctx, pk, nullptr, nullptr, nullptr, 0, (const uint64_t*)w_dev, nullptr, 0,
+                              (const uint64_t*)h_dev, out, timings);
+}
+
+// ---- distributed computeH phases ------------------------------------------------------------
+int b200_ntt_dist_phase(b200_ctx* ctx, int curve, unsigned log_n, const uint64_t* generator, const uint64_t* coset_gen,
+                        void* data_dev, void* tmp_dev, unsigned log_ranks, unsigned rank, int phase, int inverse, int scale) {
+    B2_ENTER(ctx, curve);
+    if (!data_dev || !tmp_dev) return ctx->fail(B200_ERR_ARG, "null buffer");
+    if (phase < B200_DIST_PACK || phase > B200_DIST_DIT_CROSS) return ctx->fail(B200_ERR_ARG, "bad phase");
+    if (log_n > 27) return ctx->fail(B200_ERR_UNSUPPORTED, "NTT size above 2^27");
+    NttDomain* d;
+    B2_TRY(get_domain(ctx, log_n, generator, coset_gen, &d));
+    const Fr* post = nullptr;
+    const Fr* scalar = nullptr;
+    switch (scale) {
+        case B200_SCALE_NONE: break;
+        case B200_SCALE_H_A: B2_TRY(ntt_domain_table(ctx, d, NttDomain::H_A, &post)); break;
+        case B200_SCALE_H_BC: B2_TRY(ntt_domain_table(ctx, d, NttDomain::H_BC, &post)); break;
+        case B200_SCALE_COSETINV_BR: B2_TRY(ntt_domain_table(ctx, d, NttDomain::COSETINV_BR, &post)); break;
+        case B200_SCALE_NINV: scalar = &d->ninv; break;
+        default: return ctx->fail(B200_ERR_ARG, "bad scale");
+    }
+    if (scale != B200_SCALE_NONE && phase != B200_DIST_DIF_CROSS && phase != B200_DIST_DIT_CROSS)
+        return ctx->fail(B200_ERR_ARG, "a scale applies to the last (cross) phase of a transform");
+    B2_TRY(ntt_dist_phase(ctx, d, (Fr*)data_dev, (Fr*)tmp_dev, log_ranks, rank, phase, inverse, post, scalar));
+    B2_CUDA(ctx, cudaStreamSynchronize(ctx->stream));   // the caller's exchange runs on another stream
+    return B200_OK;
+}
+
+int b200_fr_mul_sub_dev(b200_ctx* ctx, int curve, void* a_dev, const void* b_dev, const void* c_dev, size_t n) {
+    B2_ENTER(ctx, curve);
+    if (n && (!a_dev || !b_dev || !c_dev)) return ctx->fail(B200_ERR_ARG, "null buffer");
+    B2_TRY(ntt_mul_sub(ctx, (Fr*)a_dev, (const Fr*)b_dev, (const Fr*)c_dev, n));
+    B2_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return B200_OK;
 }
 
 // ---- tuning knobs -------------------------------------------------------------------------

@@ -12,6 +12,20 @@ static void shard_range(size_t len, int idx, int cnt, size_t* lo, size_t* hi) {
     *hi = len * (size_t)(idx + 1) / (size_t)cnt;
 }
 
+// G1.Z is consumed against h in position order (bit-reversed), so with a power-of-two shard count
+// its ranges follow the block layout of the distributed computeH (ntt.cuh, layout B): shard i owns
+// positions [i n / count, (i+1) n / count) cut to len(Z).  Other counts: the balanced split.
+static void shard_range_z(size_t n_z, unsigned log_n, int idx, int cnt, size_t* lo, size_t* hi) {
+    const size_t n = (size_t)1 << log_n;
+    if ((cnt & (cnt - 1)) == 0 && (size_t)cnt <= n) {
+        const size_t block = n / (size_t)cnt;
+        *lo = std::min(n_z, block * (size_t)idx);
+        *hi = std::min(n_z, block * (size_t)(idx + 1));
+    } else {
+        shard_range(n_z, idx, cnt, lo, hi);
+    }
+}
+
 template <class T>
 static int upload_range(b200_ctx* ctx, DevBuf& dst, const uint64_t* host, size_t lo, size_t hi, bool presliced) {
     const size_t cnt = hi - lo;
@@ -84,7 +98,7 @@ int groth16_pk_upload(b200_ctx* ctx, const b200_groth16_pk_desc* d, b200_groth16
         if (st == B200_OK) st = upload_wire_map(ctx, pk->mapB, d->infinity_b, d->n_wires, d->n_b, lo, hi); }
     if (st == B200_OK) { shard_range(d->n_k, si, sc, &lo, &hi); pk->n_k = hi - lo; pk->k_lo = lo;
         st = upload_range<G1Affine>(ctx, pk->K, d->g1_k, lo, hi, ps); }
-    if (st == B200_OK) { shard_range(d->n_z, si, sc, &lo, &hi); pk->n_z = hi - lo; pk->z_lo = lo;
+    if (st == B200_OK) { shard_range_z(d->n_z, d->log_n, si, sc, &lo, &hi); pk->n_z = hi - lo; pk->z_lo = lo;
         st = upload_range<G1Affine>(ctx, pk->Z, d->g1_z, lo, hi, ps); }
     if (st == B200_OK && cudaStreamSynchronize(ctx->stream) != cudaSuccess) st = ctx->fail(B200_ERR_CUDA, "pk upload");
     // Folded tables take what is left after the prover's own working set: the domain tables (built
@@ -119,8 +133,9 @@ static float ev_ms(cudaEvent_t a, cudaEvent_t b) {
 
 int groth16_prove_core(b200_ctx* ctx, const b200_groth16_pk* pk, const uint64_t* a, const uint64_t* b,
                        const uint64_t* c, size_t n_constraints, const uint64_t* w, const uint32_t* k_remove,
-                       size_t n_remove, b200_groth16_out* out, b200_timings* tm) {
+                       size_t n_remove, const uint64_t* h_local, b200_groth16_out* out, b200_timings* tm) {
     const size_t n = (size_t)1 << pk->log_n;
+    if (h_local) n_constraints = 0;   // h comes from the distributed computeH: a, b, c are not read
     if (n_constraints > n) return ctx->fail(B200_ERR_ARG, "more constraints than the domain holds");
     if (n_remove && pk->full_n_k + n_remove != pk->n_wires - pk->nb_public)
         return ctx->fail(B200_ERR_ARG, "k_remove does not match len(pk.G1.K)");
@@ -132,9 +147,10 @@ int groth16_prove_core(b200_ctx* ctx, const b200_groth16_pk* pk, const uint64_t*
     msm_ws = std::max(msm_ws, msm_workspace_bytes(pk->n_z, 1, ctx->msm_c_override, pk->fZ.c));
     msm_ws = std::max(msm_ws, msm_workspace_bytes(pk->n_b, 2, ctx->msm_c_override, pk->fG2B.c));
     Arena ar;
-    const size_t o_a = ar.off; ar.take(n * sizeof(Fr));
-    const size_t o_b = ar.off; ar.take(n * sizeof(Fr));
-    const size_t o_c = ar.off; ar.take(n * sizeof(Fr));
+    const size_t n_abc = h_local ? 0 : n;
+    const size_t o_a = ar.off; ar.take(n_abc * sizeof(Fr));
+    const size_t o_b = ar.off; ar.take(n_abc * sizeof(Fr));
+    const size_t o_c = ar.off; ar.take(n_abc * sizeof(Fr));
     const size_t o_w = ar.off; ar.take(pk->n_wires * sizeof(Fr));
     const size_t o_kmap = ar.off; ar.take(n_remove ? pk->n_k * 4 : 0);
     const size_t o_msm = ar.off; ar.take(msm_ws);
@@ -174,7 +190,7 @@ int groth16_prove_core(b200_ctx* ctx, const b200_groth16_pk* pk, const uint64_t*
     B2_CUDA(ctx, cudaEventRecord(ev_w, cp));
     const uint64_t* src[3] = {a, b, c};
     Fr* dst[3] = {d_a, d_b, d_c};
-    for (int i = 0; i < 3; ++i) {
+    for (int i = 0; i < 3 && !h_local; ++i) {
         if (n_constraints) B2_CUDA(ctx, cudaMemcpyAsync(dst[i], src[i], n_constraints * sizeof(Fr), cudaMemcpyDefault, cp));
         if (n > n_constraints) B2_CUDA(ctx, cudaMemsetAsync(dst[i] + n_constraints, 0, (n - n_constraints) * sizeof(Fr), cp));
     }
@@ -196,9 +212,10 @@ int groth16_prove_core(b200_ctx* ctx, const b200_groth16_pk* pk, const uint64_t*
     B2_CUDA(ctx, cudaEventRecord(ev[5], st));
     B2_CUDA(ctx, cudaStreamWaitEvent(st, ev_abc, 0));
     B2_CUDA(ctx, cudaEventRecord(ev[6], st));
-    B2_TRY(ntt_compute_h(ctx, pk->dom, d_a, d_b, d_c));
+    if (!h_local) B2_TRY(ntt_compute_h(ctx, pk->dom, d_a, d_b, d_c));
     B2_CUDA(ctx, cudaEventRecord(ev[7], st));
-    B2_TRY(msm_g1_run(ctx, pk->Z.as<G1Affine>(), d_a + pk->z_lo, nullptr, pk->n_z, &jz, ws, &pk->fZ));
+    const Fr* h_z = h_local ? reinterpret_cast<const Fr*>(h_local) : d_a + pk->z_lo;
+    B2_TRY(msm_g1_run(ctx, pk->Z.as<G1Affine>(), h_z, nullptr, pk->n_z, &jz, ws, &pk->fZ));
     B2_CUDA(ctx, cudaEventRecord(ev[8], st));
     B2_CUDA(ctx, cudaStreamSynchronize(st));
     B2_CUDA(ctx, cudaStreamSynchronize(cp));

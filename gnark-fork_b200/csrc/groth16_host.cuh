@@ -21,5 +21,5 @@ namespace b200 {
 int groth16_pk_upload(b200_ctx* ctx, const b200_groth16_pk_desc* d, b200_groth16_pk** out);
 int groth16_prove_core(b200_ctx* ctx, const b200_groth16_pk* pk, const uint64_t* a, const uint64_t* b,
                        const uint64_t* c, size_t n_constraints, const uint64_t* w, const uint32_t* k_remove,
-                       size_t n_remove, b200_groth16_out* out, b200_timings* tm);
+                       size_t n_remove, const uint64_t* h_local, b200_groth16_out* out, b200_timings* tm);
 }  // namespace b200

@@ -56,11 +56,14 @@ __device__ __forceinline__ void st_fr(Fr* p, const Fr& f) {
 }
 
 struct NttPassArgs {
-    Fr* data;
-    const Fr* tw;    // w^j (or w^-j for an inverse transform), j < n/2
-    const Fr* pre;   // optional scale applied on load  (first pass)
-    const Fr* post;  // optional scale applied on store (last pass)
-    NttPassGeom g;
+    const Fr* src;   // loads   (== dst for an in-place pass)
+    Fr* dst;         // stores, at smap(buffer index)
+    const Fr* tw;    // w^j (or w^-j for an inverse transform), j < n/2 of the GLOBAL domain
+    const Fr* pre;   // optional scale applied on load  (first pass), indexed by global position
+    const Fr* post;  // optional scale applied on store (last pass), indexed by global position
+    NttPassGeom g;   // geometry over the buffer
+    NttIndexMap gmap, smap;   // buffer index -> global position / store index (identity on one GPU)
+    uint32_t glog_n, s_off;   // global transform size and stage offset (distributed phases)
     int has_post_scalar;
     Fr post_scalar;
 };
@@ -76,9 +79,9 @@ __global__ void __launch_bounds__(NTT_THREADS) ntt_pass_kernel(const NttPassArgs
     const uint32_t tile_n = 1u << g.TL;
 
     for (uint32_t loc = threadIdx.x; loc < tile_n; loc += blockDim.x) {
-        const uint32_t gi = ntt_gidx(g, tile, loc);
-        Fr v = ld_fr(a.data + gi);
-        if (a.pre) v = v * ldg_fr(a.pre + gi);
+        const uint32_t bi = ntt_gidx(g, tile, loc);
+        Fr v = ld_fr(a.src + bi);
+        if (a.pre) v = v * ldg_fr(a.pre + ntt_map(a.gmap, bi));
         sm.put(loc, v);
     }
     __syncthreads();
@@ -86,11 +89,11 @@ __global__ void __launch_bounds__(NTT_THREADS) ntt_pass_kernel(const NttPassArgs
     const uint32_t n_bf = tile_n >> 1;
     for (uint32_t k = 0; k < g.S; ++k) {
         const uint32_t bit = ntt_stage_bit(g, DIT, k);
-        const uint32_t s = g.s0 + k;
+        const uint32_t s = a.s_off + g.s0 + k;
         for (uint32_t bf = threadIdx.x; bf < n_bf; bf += blockDim.x) {
             const uint32_t i0 = ntt_bf_lower(bf, bit), i1 = i0 | (1u << bit);
-            const uint32_t g0 = ntt_gidx(g, tile, i0);
-            const uint32_t e = ntt_twiddle_exp(g.log_n, DIT, s, g0);
+            const uint32_t g0 = ntt_map(a.gmap, ntt_gidx(g, tile, i0));
+            const uint32_t e = ntt_twiddle_exp(a.glog_n, DIT, s, g0);
             const Fr u = sm.get(i0), v = sm.get(i1);
             if (DIT) {
                 const Fr t = (e == 0) ? v : v * ldg_fr(a.tw + e);
@@ -106,11 +109,11 @@ __global__ void __launch_bounds__(NTT_THREADS) ntt_pass_kernel(const NttPassArgs
     }
 
     for (uint32_t loc = threadIdx.x; loc < tile_n; loc += blockDim.x) {
-        const uint32_t gi = ntt_gidx(g, tile, loc);
+        const uint32_t bi = ntt_gidx(g, tile, loc);
         Fr v = sm.get(loc);
-        if (a.post) v = v * ldg_fr(a.post + gi);
+        if (a.post) v = v * ldg_fr(a.post + ntt_map(a.gmap, bi));
         if (a.has_post_scalar) v = v * a.post_scalar;
-        st_fr(a.data + gi, v);
+        st_fr(a.dst + ntt_map(a.smap, bi), v);
     }
 }
 
@@ -128,6 +131,13 @@ __global__ void powers_kernel(Fr* out, const Fr base, const Fr mult, uint32_t co
         st_fr(out + pos, x);
         x = x * base;
     }
+}
+
+// dst[smap(i)] = src[i]
+__global__ void permute_kernel(const Fr* __restrict__ src, Fr* __restrict__ dst, const NttIndexMap smap, uint32_t n) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    st_fr(dst + ntt_map(smap, i), ld_fr(src + i));
 }
 
 __global__ void mul_sub_kernel(Fr* a, const Fr* b, const Fr* c, size_t n) {
@@ -200,10 +210,31 @@ void ntt_domain_free_all(b200_ctx* ctx) {
     ctx->domains.clear();
 }
 
-int ntt_run(b200_ctx* ctx, NttDomain* d, Fr* data, int inverse, int dit, const Fr* pre, const Fr* post,
-            const Fr* post_scalar) {
+static int ntt_launch_pass(b200_ctx* ctx, const NttPassArgs& a, int dit, size_t n_buf) {
+    const uint32_t tiles = (uint32_t)(n_buf >> a.g.TL);
+    uint32_t threads = 1u << (a.g.TL > 1 ? a.g.TL - 1 : 0);
+    if (threads > (uint32_t)ctx->ntt_threads) threads = (uint32_t)ctx->ntt_threads;
+    if (threads > NTT_THREADS) threads = NTT_THREADS;
+    if (threads < 32) threads = 32;
+    const size_t smem = smem_tile_bytes(a.g.TL);
+    const int span = ctx->prof_begin(B200_PROF_NTT_PASS, (double)n_buf * a.g.S * 0.5);
+    if (dit) ntt_pass_kernel<1><<<tiles, threads, smem, ctx->stream>>>(a);
+    else ntt_pass_kernel<0><<<tiles, threads, smem, ctx->stream>>>(a);
+    ctx->prof_end(span);
+    ctx->n_launches += 1;
+    B2_CUDA(ctx, cudaGetLastError());
+    return B200_OK;
+}
+
+static int ntt_prepare(b200_ctx* ctx) {
     B2_CUDA(ctx, cudaFuncSetAttribute(ntt_pass_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_tile_bytes(12)));
     B2_CUDA(ctx, cudaFuncSetAttribute(ntt_pass_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_tile_bytes(12)));
+    return B200_OK;
+}
+
+int ntt_run(b200_ctx* ctx, NttDomain* d, Fr* data, int inverse, int dit, const Fr* pre, const Fr* post,
+            const Fr* post_scalar) {
+    B2_TRY(ntt_prepare(ctx));
     if (d->log_n == 0) {  // n = 1: every variant is the identity (1/n = 1, g^0 = 1)
         return B200_OK;
     }
@@ -213,25 +244,68 @@ int ntt_run(b200_ctx* ctx, NttDomain* d, Fr* data, int inverse, int dit, const F
     const int np = ntt_plan(d->log_n, dit, tl_max, s_max < tl_max ? s_max : tl_max, plan);
     for (int i = 0; i < np; ++i) {
         NttPassArgs a;
-        a.data = data;
+        a.src = data;
+        a.dst = data;
         a.tw = inverse ? d->tw_inv.as<Fr>() : d->tw_fwd.as<Fr>();
         a.pre = (i == 0) ? pre : nullptr;
         a.post = (i == np - 1) ? post : nullptr;
         a.g = plan[i];
+        a.gmap = ntt_map_identity();
+        a.smap = ntt_map_identity();
+        a.glog_n = d->log_n;
+        a.s_off = 0;
         a.has_post_scalar = (i == np - 1 && post_scalar) ? 1 : 0;
         a.post_scalar = post_scalar ? *post_scalar : Fr::one();
-        const uint32_t tiles = (uint32_t)(d->n() >> plan[i].TL);
-        uint32_t threads = 1u << (plan[i].TL > 1 ? plan[i].TL - 1 : 0);
-        if (threads > (uint32_t)ctx->ntt_threads) threads = (uint32_t)ctx->ntt_threads;
-        if (threads > NTT_THREADS) threads = NTT_THREADS;
-        if (threads < 32) threads = 32;
-        const size_t smem = smem_tile_bytes(plan[i].TL);
-        const int span = ctx->prof_begin(B200_PROF_NTT_PASS, (double)d->n() * plan[i].S * 0.5);
-        if (dit) ntt_pass_kernel<1><<<tiles, threads, smem, ctx->stream>>>(a);
-        else ntt_pass_kernel<0><<<tiles, threads, smem, ctx->stream>>>(a);
-        ctx->prof_end(span);
+        B2_TRY(ntt_launch_pass(ctx, a, dit, d->n()));
+    }
+    return B200_OK;
+}
+
+// One phase of a transform distributed over 2^lg ranks (ntt.cuh).  `data` and `tmp` are this
+// rank's two buffers of n >> lg elements; see NttDistPhase for which one a phase reads and writes.
+int ntt_dist_phase(b200_ctx* ctx, NttDomain* d, Fr* data, Fr* tmp, uint32_t lg, uint32_t rank, int kind, int inverse,
+                   const Fr* post, const Fr* post_scalar) {
+    B2_TRY(ntt_prepare(ctx));
+    if (lg == 0 || 2 * lg > d->log_n) return ctx->fail(B200_ERR_ARG, "distributed NTT needs 1 <= log2(ranks) <= log_n / 2");
+    if (rank >> lg) return ctx->fail(B200_ERR_ARG, "rank out of range");
+    const uint32_t log_loc = d->log_n - lg;
+    const size_t n_loc = (size_t)1 << log_loc;
+    const NttDistPhase ph = ntt_dist_phase_desc(d->log_n, lg, rank, kind);
+    if (kind == NTT_DIST_PACK) {
+        const int bs = 256;
+        permute_kernel<<<(unsigned)((n_loc + bs - 1) / bs), bs, 0, ctx->stream>>>(data, tmp, ph.smap, (uint32_t)n_loc);
         ctx->n_launches += 1;
         B2_CUDA(ctx, cudaGetLastError());
+        return B200_OK;
+    }
+    const uint32_t tl_max = (uint32_t)ctx->ntt_tile_log;
+    const uint32_t s_max = (uint32_t)ctx->ntt_strided_stages;
+    NttPassGeom plan[8];
+    int np;
+    if (ph.cross) {
+        if (lg > tl_max) return ctx->fail(B200_ERR_ARG, "more ranks than a tile holds");
+        plan[0] = ntt_dist_cross_geom(d->log_n, lg, ph.dit, tl_max);
+        np = 1;
+    } else {
+        np = ntt_plan(log_loc, ph.dit, tl_max, s_max < tl_max ? s_max : tl_max, plan);
+    }
+    for (int i = 0; i < np; ++i) {
+        const bool last = i == np - 1;
+        NttPassArgs a;
+        // DIF cross reads the received buffer (tmp) and writes data; DIT local writes its last pass to tmp
+        a.src = (kind == NTT_DIST_DIF_CROSS) ? tmp : data;
+        a.dst = (kind == NTT_DIST_DIT_LOCAL && last) ? tmp : data;
+        a.tw = inverse ? d->tw_inv.as<Fr>() : d->tw_fwd.as<Fr>();
+        a.pre = nullptr;
+        a.post = last ? post : nullptr;
+        a.g = plan[i];
+        a.gmap = ph.gmap;
+        a.smap = last ? ph.smap : ntt_map_identity();
+        a.glog_n = d->log_n;
+        a.s_off = ph.s_off;
+        a.has_post_scalar = (last && post_scalar) ? 1 : 0;
+        a.post_scalar = post_scalar ? *post_scalar : Fr::one();
+        B2_TRY(ntt_launch_pass(ctx, a, ph.dit, n_loc));
     }
     return B200_OK;
 }

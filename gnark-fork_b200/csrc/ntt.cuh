@@ -87,4 +87,82 @@ inline int ntt_plan(uint32_t log_n, int dit, uint32_t tl_max, uint32_t s_strided
     return np;
 }
 
+// ---------------------------------------------------------------------------------------
+// Distributed transform over R = 2^lg ranks (one exchange step per transform).
+//
+// Every rank holds n/R elements.  Two layouts of the n positions of the in-place network:
+//   A (cyclic): rank = position mod R,          local index = position >> lg
+//   B (block):  rank = position >> (log_n - lg), local index = position mod n/R
+// A DIF transform (natural -> bit-reversed) starts in A and ends in B, a DIT transform
+// (bit-reversed -> natural) starts in B and ends in A:
+//   DIF: [local]  the log_n - lg stages on position bits >= lg          (in place, layout A)
+//        [all-to-all]  chunk q = local indices with top lg bits q goes to rank q
+//        [cross]  the lg stages on position bits < lg, over the received (r, j) buffer; the store
+//                 rotates the index to (j << lg) | r: layout B in natural local order.
+//   DIT: [local]  the log_n - lg stages on position bits < log_n - lg   (layout B); the last
+//                 store rotates the index to ((i mod R) << m) | (i >> lg) so that the chunks of the
+//        [all-to-all]  are contiguous: chunk q = local indices congruent to q mod R
+//        [cross]  the lg stages on the top position bits over the received (r, j) buffer, whose
+//                 index (r << m) | j is already the local index of layout A.          m = log_n - 2 lg
+// Twiddles and scale tables are looked up by GLOBAL position, so the full-size tables serve all
+// ranks.  The maps below turn a local buffer index into that position / into the store index.
+// ---------------------------------------------------------------------------------------
+struct NttIndexMap {   // i -> ((i >> m) << sh_hi) | ((i mod 2^m) << sh_lo) | add
+    uint32_t m, sh_hi, sh_lo, add;
+};
+B2_HD NttIndexMap ntt_map_identity() { return NttIndexMap{31u, 0u, 0u, 0u}; }
+B2_HD uint32_t ntt_map(const NttIndexMap& p, uint32_t i) {
+    return ((i >> p.m) << p.sh_hi) | ((i & ((1u << p.m) - 1u)) << p.sh_lo) | p.add;
+}
+
+enum NttDistPhaseKind { NTT_DIST_PACK = 0, NTT_DIST_DIF_LOCAL, NTT_DIST_DIF_CROSS, NTT_DIST_DIT_LOCAL, NTT_DIST_DIT_CROSS };
+
+struct NttDistPhase {
+    NttIndexMap gmap;    // local buffer index -> global position (twiddles, scale tables)
+    NttIndexMap smap;    // local buffer index -> index the LAST pass of the phase stores to
+    uint32_t s_off;      // global stage number = s_off + stage number of the local plan
+    int dit;             // network of the phase's passes
+    int cross;           // 1: a single pass over the top lg bits of the buffer
+    int out_of_place;    // 1: the last pass stores to the other buffer
+};
+
+inline NttDistPhase ntt_dist_phase_desc(uint32_t log_n, uint32_t lg, uint32_t rank, int kind) {
+    const uint32_t m = log_n - 2u * lg, log_loc = log_n - lg;
+    NttDistPhase d;
+    d.gmap = ntt_map_identity();
+    d.smap = ntt_map_identity();
+    d.s_off = 0; d.dit = 0; d.cross = 0; d.out_of_place = 0;
+    switch (kind) {
+        case NTT_DIST_PACK:         // layout B (natural block) -> chunks for layout A
+            d.smap = NttIndexMap{lg, 0u, m, 0u};
+            d.out_of_place = 1;
+            break;
+        case NTT_DIST_DIF_LOCAL:    // layout A
+            d.gmap = NttIndexMap{31u, 0u, lg, rank};
+            break;
+        case NTT_DIST_DIF_CROSS:    // buffer (r, j): position (((rank << m) | j) << lg) | r
+            d.gmap = NttIndexMap{m, 0u, lg, rank << (m + lg)};
+            d.smap = NttIndexMap{m, 0u, lg, 0u};
+            d.s_off = log_loc; d.cross = 1; d.out_of_place = 1;
+            break;
+        case NTT_DIST_DIT_LOCAL:    // layout B
+            d.gmap = NttIndexMap{31u, 0u, 0u, rank << log_loc};
+            d.smap = NttIndexMap{lg, 0u, m, 0u};
+            d.dit = 1; d.out_of_place = 1;
+            break;
+        default:                    // NTT_DIST_DIT_CROSS: buffer (r, j): position (r << log_loc) | (j << lg) | rank
+            d.gmap = NttIndexMap{m, log_loc, lg, rank};
+            d.s_off = lg; d.dit = 1; d.cross = 1;
+            break;
+    }
+    return d;
+}
+
+// the single pass of a cross phase: lg stages over the top lg bits of a buffer of 2^log_loc elements
+inline NttPassGeom ntt_dist_cross_geom(uint32_t log_n, uint32_t lg, int dit, uint32_t tl_max) {
+    const uint32_t log_loc = log_n - lg, m = log_n - 2u * lg;
+    const uint32_t TL = log_loc < tl_max ? log_loc : tl_max;
+    return NttPassGeom{log_loc, dit ? m : 0u, lg, TL, TL - lg, m};
+}
+
 }  // namespace b200

@@ -33,6 +33,9 @@ void ntt_domain_free_all(b200_ctx* ctx);
 // post_scalar: optional single factor applied with the last store.
 int ntt_run(b200_ctx* ctx, NttDomain* d, Fr* data, int inverse, int dit, const Fr* pre, const Fr* post,
             const Fr* post_scalar);
+// one phase of a transform distributed over 2^lg ranks (ntt.cuh: NttDistPhaseKind)
+int ntt_dist_phase(b200_ctx* ctx, NttDomain* d, Fr* data, Fr* tmp, uint32_t lg, uint32_t rank, int kind, int inverse,
+                   const Fr* post, const Fr* post_scalar);
 // gnark-crypto semantics (Domain.FFT / FFTInverse with optional OnCoset)
 int ntt_gnark(b200_ctx* ctx, NttDomain* d, Fr* data, int inverse, int dit, int on_coset);
 // a[i] = a[i]*b[i] - c[i]

@@ -222,6 +222,28 @@ typedef struct b200_timings {
     float h2d_ms, compute_h_ms, msm_a_ms, msm_b1_ms, msm_k_ms, msm_z_ms, msm_b2_ms, total_ms;
 } b200_timings;
 
+/* ---- multi-GPU computeH (NTT with one exchange step per transform) -------------
+ * One process per GPU holds n >> log_ranks elements of each vector in two device buffers (`data`,
+ * `tmp`).  A transform is [local phase] -> all-to-all between the ranks (the caller's: NCCL, or
+ * peer copies) -> [cross phase]; the phases below are the device work on either side.  Chunk q of
+ * the all-to-all is the q-th contiguous (n >> 2 log_ranks)-element slice of the send buffer and
+ * lands as slice `source rank` of the receive buffer.
+ *   PACK        data (this rank's contiguous block of a natural-order vector) -> tmp; send tmp, receive into data
+ *   DIF_LOCAL   data in place;                       send data, receive into tmp
+ *   DIF_CROSS   tmp -> data (block of the bit-reversed result; `scale` applied)
+ *   DIT_LOCAL   data -> tmp;                         send tmp, receive into data
+ *   DIT_CROSS   data in place (cyclic slice of the natural-order result: element j of rank r is index j * ranks + r)
+ * computeH = PACK x3, inverse DIF x3 (scales H_A, H_BC, H_A), forward DIT x3, b200_fr_mul_sub_dev,
+ * inverse DIF (COSETINV_BR): rank r ends with h[r n / ranks, (r+1) n / ranks) in the bit-reversed
+ * order G1.Z is stored in (prove.go:232-234,353-396), ready for b200_groth16_msms_dev.
+ * Every call returns after its kernels finished (the exchange runs on the caller's stream). */
+enum b200_dist_phase { B200_DIST_PACK = 0, B200_DIST_DIF_LOCAL = 1, B200_DIST_DIF_CROSS = 2, B200_DIST_DIT_LOCAL = 3, B200_DIST_DIT_CROSS = 4 };
+enum b200_dist_scale { B200_SCALE_NONE = 0, B200_SCALE_H_A = 1, B200_SCALE_H_BC = 2, B200_SCALE_COSETINV_BR = 3, B200_SCALE_NINV = 4 };
+int b200_ntt_dist_phase(b200_ctx *ctx, int curve, unsigned log_n, const uint64_t *generator, const uint64_t *coset_gen,
+                        void *data_dev, void *tmp_dev, unsigned log_ranks, unsigned rank, int phase, int inverse, int scale);
+/* a[i] = a[i] * b[i] - c[i] on device vectors (prove.go:377-390 without den, which H_A carries). */
+int b200_fr_mul_sub_dev(b200_ctx *ctx, int curve, void *a_dev, const void *b_dev, const void *c_dev, size_t n);
+
 /* The five MultiExp results BEFORE the alpha/beta/delta/r/s fix-ups, which stay in Go
  * (prove.go:206-207,219-221,248-271,294-299). */
 typedef struct b200_groth16_out {
@@ -247,6 +269,10 @@ int b200_groth16_prove_core(b200_ctx *ctx, const b200_groth16_pk *pk, const uint
 int b200_groth16_prove_core_dev(b200_ctx *ctx, const b200_groth16_pk *pk, const void *a_dev, const void *b_dev,
                                 const void *c_dev, size_t n_constraints, const void *w_dev,
                                 b200_groth16_out *out, b200_timings *timings);
+/* The five MSMs of this shard with h supplied by the distributed computeH: h_dev holds this
+ * shard's range of h (len = the shard's G1.Z count). */
+int b200_groth16_msms_dev(b200_ctx *ctx, const b200_groth16_pk *pk, const void *w_dev, const void *h_dev,
+                          b200_groth16_out *out, b200_timings *timings);
 
 /* Host mirror of groth16_bn254.Prove's tail (prove.go:178-321) for callers without Go: applies
  * the fix-ups to the five MSM results with the given blinding scalars r, s (Montgomery Fr) and

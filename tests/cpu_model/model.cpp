@@ -45,6 +45,68 @@ void model_ntt(uint64_t* data, unsigned log_n, int inverse, int dit, unsigned tl
     }
 }
 
+// sequential replay of one phase of the distributed transform (ntt.cu: ntt_dist_phase + the index maps of
+// ntt_pass_kernel).  data / tmp: this rank's two buffers of n >> lg elements; post: optional table
+// of n elements indexed by global position, applied with the last store.
+void model_ntt_dist_phase(uint64_t* data_, uint64_t* tmp_, unsigned log_n, unsigned lg, unsigned rank, int kind,
+                          int inverse, unsigned tl_max, unsigned s_max, const uint64_t* gen_mont, const uint64_t* post_) {
+    Fr* data = reinterpret_cast<Fr*>(data_);
+    Fr* tmp = reinterpret_cast<Fr*>(tmp_);
+    const Fr* post = reinterpret_cast<const Fr*>(post_);
+    const size_t n = (size_t)1 << log_n;
+    const uint32_t log_loc = log_n - lg;
+    const size_t n_loc = (size_t)1 << log_loc;
+    const NttDistPhase ph = ntt_dist_phase_desc(log_n, lg, rank, kind);
+    if (kind == NTT_DIST_PACK) {
+        for (uint32_t i = 0; i < n_loc; ++i) tmp[ntt_map(ph.smap, i)] = data[i];
+        return;
+    }
+    Fr gen; memcpy(gen.l, gen_mont, 32);
+    if (inverse) gen = gen.inv();
+    std::vector<Fr> tw(n / 2 ? n / 2 : 1);
+    tw[0] = Fr::one();
+    for (size_t j = 1; j < tw.size(); ++j) tw[j] = tw[j - 1] * gen;
+    NttPassGeom plan[8];
+    int np;
+    if (ph.cross) { plan[0] = ntt_dist_cross_geom(log_n, lg, ph.dit, tl_max); np = 1; }
+    else np = ntt_plan(log_loc, ph.dit, tl_max, s_max < tl_max ? s_max : tl_max, plan);
+    for (int p = 0; p < np; ++p) {
+        const bool last = p == np - 1;
+        const NttPassGeom g = plan[p];
+        const Fr* src = (kind == NTT_DIST_DIF_CROSS) ? tmp : data;
+        Fr* dst = (kind == NTT_DIST_DIT_LOCAL && last) ? tmp : data;
+        const NttIndexMap smap = last ? ph.smap : ntt_map_identity();
+        const uint32_t tile_n = 1u << g.TL, tiles = (uint32_t)(n_loc >> g.TL);
+        std::vector<Fr> sm(tile_n);
+        for (uint32_t tile = 0; tile < tiles; ++tile) {
+            for (uint32_t loc = 0; loc < tile_n; ++loc) sm[loc] = src[ntt_gidx(g, tile, loc)];
+            for (uint32_t k = 0; k < g.S; ++k) {
+                const uint32_t bit = ntt_stage_bit(g, ph.dit, k), s = ph.s_off + g.s0 + k;
+                for (uint32_t bf = 0; bf < tile_n / 2; ++bf) {
+                    const uint32_t i0 = ntt_bf_lower(bf, bit), i1 = i0 | (1u << bit);
+                    const uint32_t e = ntt_twiddle_exp(log_n, ph.dit, s, ntt_map(ph.gmap, ntt_gidx(g, tile, i0)));
+                    const Fr u = sm[i0], v = sm[i1];
+                    if (ph.dit) { const Fr t = v * tw[e]; sm[i0] = u + t; sm[i1] = u - t; }
+                    else { sm[i0] = u + v; sm[i1] = (u - v) * tw[e]; }
+                }
+            }
+            for (uint32_t loc = 0; loc < tile_n; ++loc) {
+                const uint32_t bi = ntt_gidx(g, tile, loc);
+                Fr v = sm[loc];
+                if (last && post) v = v * post[ntt_map(ph.gmap, bi)];
+                dst[ntt_map(smap, bi)] = v;
+            }
+        }
+    }
+}
+
+void model_fr_mul_sub(uint64_t* a_, const uint64_t* b_, const uint64_t* c_, size_t n) {
+    Fr* a = reinterpret_cast<Fr*>(a_);
+    const Fr* b = reinterpret_cast<const Fr*>(b_);
+    const Fr* c = reinterpret_cast<const Fr*>(c_);
+    for (size_t i = 0; i < n; ++i) a[i] = a[i] * b[i] - c[i];
+}
+
 }  // extern "C"
 
 // the whole MSM pipeline replayed on the host with the device formulas (XYZZ, reduction tree)

@@ -155,6 +155,10 @@ class Instance:
 
     def shard(self, key):
         m = self.full[key]
+        if key == "z":      # G1.Z follows the block layout of the distributed computeH (sharding.z_shard_range)
+            n, w = self.n, self.world
+            if w & (w - 1) == 0 and w <= n:
+                return min(m, n // w * self.rank), min(m, n // w * (self.rank + 1))
         return m * self.rank // self.world, m * (self.rank + 1) // self.world
 
     def build_key(self, ctx):
@@ -268,6 +272,7 @@ def gpu_arm(args):
         import torch
         import torch.distributed as dist
         torch.cuda.set_device(local)
+        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")   # NCCL's banner off stdout: one JSON line there
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     pkg = load_pkg()
     ctx = pkg.Context(local)          # raises without the CUDA library / device: no fallback
@@ -292,16 +297,69 @@ def gpu_arm(args):
     inst.witness(pkg)
     t_setup = time.perf_counter() - t_setup
     n, nw = inst.n, inst.n_wires
-    dv = {k: pkg.DeviceVector(ctx, getattr(inst, k).nbytes).upload(getattr(inst, k)) for k in ("a", "b", "c", "w")}
+    distributed = world > 1 and (world & (world - 1)) == 0 and not args.replicate_h
+    rs = rand_field(np.random.default_rng(3), 2)
+    vkp = [inst.bases["a"][0], inst.bases["b"][0], inst.bases["k"][0], inst.bases["g2b"][0], inst.bases["g2b"][1 % len(inst.bases["g2b"])]]
+
+    if not distributed:
+        dv = {k: pkg.DeviceVector(ctx, getattr(inst, k).nbytes).upload(getattr(inst, k)) for k in ("a", "b", "c", "w")}
+
+        def step_dev():
+            o, tm = ctx.groth16_prove_core_dev(pk, dv["a"], dv["b"], dv["c"], n, dv["w"])
+            return o, tm, tm["total_ms"]
+
+        def step_e2e():
+            return ctx.groth16_prove_core(pk, inst.a, inst.b, inst.c, inst.w)[0]
+        h2d_bytes = int((3 * n + inst.n_wires) * 32)
+    else:
+        # computeH distributed over the ranks: every rank owns n / world elements of a, b, c; one
+        # all-to-all per transform (NCCL over NVLink); the five MSMs on point-range shards.
+        import torch
+        dev = torch.device("cuda", local)
+        n_loc = n // world
+        blk = slice(rank * n_loc, (rank + 1) * n_loc)
+        host_blk = [torch.from_numpy(getattr(inst, k)[blk].view(np.int64)) for k in ("a", "b", "c")]   # views of the pinned arrays
+        torch.cuda.synchronize(dev)
+        resident = [t.to(dev) for t in host_blk]
+        work = [torch.empty((n_loc, 4), dtype=torch.int64, device=dev) for _ in range(6)]            # a, b, c, 3 x tmp
+        w_host = torch.from_numpy(inst.w.view(np.int64))
+        w_dev = w_host.to(dev)
+        engine = pkg.sharding.DeviceEngine(ctx, inst.log_n, inst.gen, inst.coset, rank, world)
+        exchange = pkg.sharding.torch_exchange(dist, async_op=True)
+        torch.cuda.set_stream(torch.cuda.Stream(dev))                # a real stream (the legacy default one cannot be shared)
+        ctx.use_stream(torch.cuda.current_stream(dev).cuda_stream)   # library kernels and NCCL ordered on one stream
+        ev = [torch.cuda.Event(enable_timing=True) for _ in range(3)]
+
+        def run(src, w_src):
+            torch.cuda.synchronize(dev)
+            ev[0].record()
+            for dst, s_ in zip(work[:3], src):
+                dst.copy_(s_, non_blocking=True)
+            if w_src is not w_dev:
+                w_dev.copy_(w_src, non_blocking=True)
+            h = pkg.sharding.compute_h_distributed(engine, exchange, work[0], work[1], work[2], work[3:6])
+            ev[1].record()
+            o, tm = ctx.groth16_msms_dev(pk, w_dev, h)
+            ev[2].record()
+            ev[2].synchronize()
+            tm = dict(tm, compute_h_ms=ev[0].elapsed_time(ev[1]), h2d_ms=0.0)
+            return o, tm, ev[0].elapsed_time(ev[2])
+
+        def step_dev():
+            return run(resident, w_dev)
+
+        def step_e2e():
+            return run(host_blk, w_host)[0]
+        h2d_bytes = int((3 * n_loc + inst.n_wires) * 32)
 
     # correctness first (outside any timed region): exact known-discrete-log check of all five MSMs
-    out, _ = ctx.groth16_prove_core_dev(pk, dv["a"], dv["b"], dv["c"], n, dv["w"])
+    out, _, _ = step_dev()
     verified = inst.check(ctx, pkg, out) if not args.no_check else None
 
     for _ in range(max(0, args.warmup - 1)):
-        ctx.groth16_prove_core_dev(pk, dv["a"], dv["b"], dv["c"], n, dv["w"])
+        step_dev()
 
-    # ---- device-resident timed region: K steps, CUDA events on the launching stream -------
+    # ---- device-resident timed region: K steps, CUDA events --------------------------------
     clocks = ClockSampler(local)
     barrier()
     clocks.start()
@@ -309,8 +367,8 @@ def gpu_arm(args):
     dev_ms, stage = [], {}
     t0 = time.perf_counter()
     for _ in range(args.steps):
-        _, tm = ctx.groth16_prove_core_dev(pk, dv["a"], dv["b"], dv["c"], n, dv["w"])
-        dev_ms.append(tm["total_ms"])
+        _, tm, total = step_dev()
+        dev_ms.append(total)
         for k, v in tm.items():
             stage[k] = stage.get(k, 0.0) + v / args.steps
     prof = ctx.profile_read()
@@ -318,17 +376,15 @@ def gpu_arm(args):
     wall_dev = time.perf_counter() - t0
     clk = clocks.stop()
     step_ms = max_over_ranks(float(np.mean(dev_ms)))
+    stage["total_ms"] = float(np.mean(dev_ms))
 
-    # ---- end to end through the host-buffer ABI: pinned host -> device, MSM results back,
+    # ---- end to end through the host-buffer path: pinned host -> device, MSM results back,
     #      host fix-ups (prove.go:178-321) to the affine proof -------------------------------
-    rs = rand_field(np.random.default_rng(3), 2)
-    vkp = [inst.bases["a"][0], inst.bases["b"][0], inst.bases["k"][0], inst.bases["g2b"][0], inst.bases["g2b"][1 % len(inst.bases["g2b"])]]
-    for _ in range(1):
-        ctx.groth16_prove_core(pk, inst.a, inst.b, inst.c, inst.w)
+    step_e2e()
     barrier()
     t0 = time.perf_counter()
     for _ in range(args.steps):
-        o, _ = ctx.groth16_prove_core(pk, inst.a, inst.b, inst.c, inst.w)
+        o = step_e2e()
         if world == 1:
             pkg.groth16_finalize(o, rs[0], rs[1], *vkp)
     barrier()
@@ -339,13 +395,17 @@ def gpu_arm(args):
         combined = pkg.sharding.gather_combine(dist, o.as_dict(), device=f"cuda:{local}")
         e2e_s += max_over_ranks(time.perf_counter() - t1)
 
+    if dist is not None:
+        ctx.use_stream(None)
+        dist.barrier()
+        dist.destroy_process_group()
     if rank != 0:
         ctx.close()
         return 0
-    return report(args, world, peak, prof, stage, step_ms, e2e_s, clk, verified, inst, t_setup, wall_dev, pk.info())
+    return report(args, world, peak, prof, stage, step_ms, e2e_s, clk, verified, inst, t_setup, wall_dev, pk.info(), distributed, h2d_bytes)
 
 
-def report(args, world, peak, prof, stage, step_ms, e2e_s, clk, verified, inst, t_setup, wall_dev, pk_info):
+def report(args, world, peak, prof, stage, step_ms, e2e_s, clk, verified, inst, t_setup, wall_dev, pk_info, distributed, h2d_bytes):
     n = inst.n
     peaks_path = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(peaks_path):
@@ -372,7 +432,7 @@ def report(args, world, peak, prof, stage, step_ms, e2e_s, clk, verified, inst, 
     # NTT: north_star's HBM view (64 B per element per pass, 2 passes at <= 2^24) and the IMAD view
     passes_model = 1 if inst.log_n <= 12 else (2 if inst.log_n <= 24 else 3)
     n_transforms = 7 * args.steps
-    ntt_bytes = n_transforms * n * 64.0 * passes_model
+    ntt_bytes = n_transforms * (n / world if distributed else n) * 64.0 * passes_model   # per rank
     ntt_gbs = ntt_bytes / (ntt["ms"] * 1e-3) / 1e9 if ntt["ms"] else 0.0
     ntt_mac_s = ntt["units"] * MAC32_PER_BUTTERFLY / (ntt["ms"] * 1e-3) if ntt["ms"] else 0.0
     roofline_ntt = {"kernel": "ntt_pass_kernel", "bound": "hbm", "achieved": ntt_gbs, "peak": hbm_peak, "unit": "GB/s",
@@ -389,9 +449,9 @@ def report(args, world, peak, prof, stage, step_ms, e2e_s, clk, verified, inst, 
         "config": {"workload": f"BN254 Groth16 prove core (computeH + 5 MSM), 2^{inst.log_n} constraints, Mul-chain shape "
                                f"(4 G1 MSM of ~2^{inst.log_n}, 1 G2 MSM, 7 NTT of 2^{inst.log_n})",
                    "log_n": inst.log_n, "inputs": "uniform random field elements; bases [k_i]G with known k_i",
-                   "parallelism": f"msm point-range shards x{world}, computeH replicated" if world > 1 else "1 GPU",
+                   "parallelism": (f"msm point-range shards x{world}, computeH " + ("distributed (one NCCL all-to-all per transform)" if distributed else "replicated")) if world > 1 else "1 GPU",
                    "l2": "inputs (>= 0.5 GiB per vector) exceed the 126 MB L2; no flush needed"},
-        "e2e": {"value": e2e_s, "unit": "s", "h2d_bytes_per_step": int((3 * n + inst.n_wires) * 32),
+        "e2e": {"value": e2e_s, "unit": "s", "h2d_bytes_per_step": h2d_bytes,
                 "d2h_bytes_per_step": int(4 * 16 * 128 + 16 * 256),
                 "path": "b200_groth16_prove_core (pinned host buffers) + b200_groth16_finalize"},
         "gpu_launches": prof["kernel_launches"],
@@ -423,6 +483,7 @@ def main():
     ap.add_argument("--cpu-sample-log", type=int, default=18)
     ap.add_argument("--no-check", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--replicate-h", action="store_true", help="N > 1: every rank runs the whole computeH (no exchange)")
     args = ap.parse_args()
     args.cpu_sample_log = min(args.cpu_sample_log, args.log_n)
     if args.impl == "reference":

@@ -121,6 +121,7 @@ def load_library():
         "b200_groth16_msms_dev": (i, [vp, vp, vp, vp, C.POINTER(Groth16MsmOut), C.POINTER(_Timings)]),
         "b200_ntt_dist_phase": (i, [vp, i, u, vp, vp, vp, vp, u, u, i, i, i]),
         "b200_fr_mul_sub_dev": (i, [vp, i, vp, vp, vp, sz]),
+        "b200_use_stream": (i, [vp, vp]),
         "b200_profile_start": (i, [vp]),
         "b200_profile_read": (i, [vp, C.POINTER(_Profile)]),
         "b200_groth16_finalize": (i, [C.POINTER(Groth16MsmOut), vp, vp, vp, vp, vp, vp, vp, vp, vp, vp]),
@@ -318,6 +319,13 @@ class Context:
 
     def sync(self):
         self._check(self.lib.b200_sync(self.h))
+
+    def use_stream(self, cuda_stream: int | None):
+        """Order all further work of this context on the caller's CUDA stream (an integer
+        cudaStream_t, e.g. torch.cuda.current_stream().cuda_stream); None: the context's own."""
+        if cuda_stream is not None and int(cuda_stream) == 0:
+            raise ValueError("the legacy default stream (handle 0) cannot be shared: make a torch.cuda.Stream current first")
+        self._check(self.lib.b200_use_stream(self.h, None if cuda_stream is None else C.c_void_p(int(cuda_stream))))
 
     def set_option(self, key: str, value: int):
         self._check(self.lib.b200_set_option(self.h, key.encode(), int(value)))

@@ -58,12 +58,13 @@ int b200_init(int device, b200_ctx** out) {
     cudaDeviceProp prop;
     if (cudaGetDeviceProperties(&prop, device) != cudaSuccess) { delete ctx; return B200_ERR_CUDA; }
     ctx->sm_count = prop.multiProcessorCount;
-    if (cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking) != cudaSuccess ||
+    if (cudaStreamCreateWithFlags(&ctx->own_stream, cudaStreamNonBlocking) != cudaSuccess ||
         cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking) != cudaSuccess ||
         cudaEventCreate(&ctx->ev0) != cudaSuccess || cudaEventCreate(&ctx->ev1) != cudaSuccess) {
         delete ctx;
         return B200_ERR_CUDA;
     }
+    ctx->stream = ctx->own_stream;
     const char* c = getenv("B200_MSM_C");
     if (c && *c) { int v = atoi(c); if (v >= 4 && v <= 24) ctx->msm_c_override = v; }
     *out = ctx;
@@ -80,7 +81,7 @@ void b200_destroy(b200_ctx* ctx) {
     for (auto e : ctx->prof_pool) cudaEventDestroy(e);
     cudaEventDestroy(ctx->ev0);
     cudaEventDestroy(ctx->ev1);
-    cudaStreamDestroy(ctx->stream);
+    cudaStreamDestroy(ctx->own_stream);
     if (ctx->copy_stream) cudaStreamDestroy(ctx->copy_stream);
     delete ctx;
 }
@@ -411,16 +412,20 @@ int b200_ntt_dist_phase(b200_ctx* ctx, int curve, unsigned log_n, const uint64_t
     }
     if (scale != B200_SCALE_NONE && phase != B200_DIST_DIF_CROSS && phase != B200_DIST_DIT_CROSS)
         return ctx->fail(B200_ERR_ARG, "a scale applies to the last (cross) phase of a transform");
-    B2_TRY(ntt_dist_phase(ctx, d, (Fr*)data_dev, (Fr*)tmp_dev, log_ranks, rank, phase, inverse, post, scalar));
-    B2_CUDA(ctx, cudaStreamSynchronize(ctx->stream));   // the caller's exchange runs on another stream
-    return B200_OK;
+    return ntt_dist_phase(ctx, d, (Fr*)data_dev, (Fr*)tmp_dev, log_ranks, rank, phase, inverse, post, scalar);
 }
 
 int b200_fr_mul_sub_dev(b200_ctx* ctx, int curve, void* a_dev, const void* b_dev, const void* c_dev, size_t n) {
     B2_ENTER(ctx, curve);
     if (n && (!a_dev || !b_dev || !c_dev)) return ctx->fail(B200_ERR_ARG, "null buffer");
-    B2_TRY(ntt_mul_sub(ctx, (Fr*)a_dev, (const Fr*)b_dev, (const Fr*)c_dev, n));
+    return ntt_mul_sub(ctx, (Fr*)a_dev, (const Fr*)b_dev, (const Fr*)c_dev, n);
+}
+
+int b200_use_stream(b200_ctx* ctx, void* cuda_stream) {
+    if (!ctx) return B200_ERR_ARG;
+    if (set_device(ctx) != B200_OK) return B200_ERR_CUDA;
     B2_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    ctx->stream = cuda_stream ? (cudaStream_t)cuda_stream : ctx->own_stream;
     return B200_OK;
 }
 

@@ -16,7 +16,8 @@ struct NttDomain;
 struct b200_ctx {
     int device = 0;
     int sm_count = 0;
-    cudaStream_t stream = nullptr;
+    cudaStream_t stream = nullptr;          // all work is ordered on this stream (own_stream unless b200_use_stream)
+    cudaStream_t own_stream = nullptr;
     cudaStream_t copy_stream = nullptr;     // per-proof input copies, overlapped with the witness MSMs
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     std::string err;

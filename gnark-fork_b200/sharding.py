@@ -86,36 +86,71 @@ class DeviceEngine:
         self.ctx.fr_mul_sub_dev(a, b, c, (1 << self.log_n) >> self.lg)
 
 
+def _wait(handle):
+    if handle is not None:
+        handle.wait()
+
+
 def compute_h_distributed(engine, exchange, a, b, c, tmp):
     """computeH (prove.go:353-396) over 2^lg ranks.  a, b, c: this rank's contiguous block of the
     zero-padded solver vectors (n / ranks elements each, natural order); tmp: one scratch buffer of
-    the same size.  exchange(send, recv) is the all-to-all (equal contiguous chunks, chunk q to rank
-    q, received chunks ordered by source rank).  Returns the buffer that holds this rank's block of h
-    (bit-reversed order, positions [rank n / ranks, (rank+1) n / ranks)): it is `a`."""
+    the same size, or three (one per vector: lets the all-to-all of one vector overlap the phases
+    of the next).  exchange(send, recv) is the all-to-all (equal contiguous chunks, chunk q to rank
+    q, received chunks ordered by source rank); it returns None when it has completed, or a handle
+    whose wait() orders the following phases after it.  Returns the buffer that holds this rank's
+    block of h (bit-reversed order, positions [rank n / ranks, (rank+1) n / ranks)): it is `a`."""
     P = api
-    for v in (a, b, c):                                   # block layout -> cyclic layout
-        engine.phase(v, tmp, P.DIST_PACK, 0)
-        exchange(tmp, v)
-    for v, scale in ((a, P.SCALE_H_A), (b, P.SCALE_H_BC), (c, P.SCALE_H_A)):   # FFTInverse (DIF) fused with the coset scaling
-        engine.phase(v, tmp, P.DIST_DIF_LOCAL, 1)
-        exchange(v, tmp)
-        engine.phase(v, tmp, P.DIST_DIF_CROSS, 1, scale)
-    for v in (a, b, c):                                   # FFT (DIT) on the coset
-        engine.phase(v, tmp, P.DIST_DIT_LOCAL, 0)
-        exchange(tmp, v)
-        engine.phase(v, tmp, P.DIST_DIT_CROSS, 0)
+    vs = (a, b, c)
+    ts = tuple(tmp) if isinstance(tmp, (list, tuple)) else (tmp, tmp, tmp)
+    shared_tmp = ts[0] is ts[1]
+    scales = (P.SCALE_H_A, P.SCALE_H_BC, P.SCALE_H_A)
+    pend = [None, None, None]
+
+    def xchg(i, send, recv):
+        pend[i] = exchange(send, recv)
+
+    def done(i):
+        _wait(pend[i])
+        pend[i] = None
+
+    if shared_tmp:                                        # one scratch buffer: vector after vector
+        for i, v in enumerate(vs):
+            t = ts[0]
+            engine.phase(v, t, P.DIST_PACK, 0); xchg(i, t, v); done(i)
+            engine.phase(v, t, P.DIST_DIF_LOCAL, 1); xchg(i, v, t); done(i)
+            engine.phase(v, t, P.DIST_DIF_CROSS, 1, scales[i])
+            engine.phase(v, t, P.DIST_DIT_LOCAL, 0); xchg(i, t, v); done(i)
+            engine.phase(v, t, P.DIST_DIT_CROSS, 0)
+    else:                                                 # software pipeline over the three vectors
+        for i, (v, t) in enumerate(zip(vs, ts)):          # block layout -> cyclic layout
+            engine.phase(v, t, P.DIST_PACK, 0)
+            xchg(i, t, v)
+        for i, (v, t) in enumerate(zip(vs, ts)):          # FFTInverse (DIF) ...
+            done(i)
+            engine.phase(v, t, P.DIST_DIF_LOCAL, 1)
+            xchg(i, v, t)
+        for i, (v, t) in enumerate(zip(vs, ts)):          # ... fused with the coset scaling; then FFT (DIT) on the coset
+            done(i)
+            engine.phase(v, t, P.DIST_DIF_CROSS, 1, scales[i])
+            engine.phase(v, t, P.DIST_DIT_LOCAL, 0)
+            xchg(i, t, v)
+        for i, (v, t) in enumerate(zip(vs, ts)):
+            done(i)
+            engine.phase(v, t, P.DIST_DIT_CROSS, 0)
     engine.mul_sub(a, b, c)                               # (a*b - c) * den, den carried by H_A
-    engine.phase(a, tmp, P.DIST_DIF_LOCAL, 1)             # FFTInverse (DIF) on the coset
-    exchange(a, tmp)
-    engine.phase(a, tmp, P.DIST_DIF_CROSS, 1, P.SCALE_COSETINV_BR)
+    engine.phase(a, ts[0], P.DIST_DIF_LOCAL, 1)           # FFTInverse (DIF) on the coset
+    _wait(exchange(a, ts[0]))
+    engine.phase(a, ts[0], P.DIST_DIF_CROSS, 1, P.SCALE_COSETINV_BR)
     return a
 
 
-def torch_exchange(dist):
-    """all_to_all_single over torch.distributed (nccl on CUDA tensors, gloo on CPU tensors)."""
+def torch_exchange(dist, async_op=False):
+    """all_to_all_single over torch.distributed (nccl on CUDA tensors, gloo on CPU tensors).
+    On CUDA the collective is ordered after the work already enqueued on torch's current stream and
+    wait() orders that stream after the collective: give the library the same stream
+    (Context.use_stream(torch.cuda.current_stream().cuda_stream)) and no host synchronisation is
+    needed anywhere in computeH."""
     def exchange(send, recv):
-        dist.all_to_all_single(recv.view(-1), send.view(-1))
-        if recv.is_cuda:
-            import torch
-            torch.cuda.current_stream(recv.device).synchronize()   # the library runs on its own stream
+        work = dist.all_to_all_single(recv.view(-1), send.view(-1), async_op=async_op)
+        return work if async_op else None
     return exchange

@@ -74,6 +74,9 @@ const char *b200_version(void);
  * shared-memory tile, 6..12), "ntt_strided_stages" (max stages of a strided NTT pass, 1..12),
  * "ntt_threads" (threads per NTT CTA, power of two). */
 int b200_set_option(b200_ctx *ctx, const char *key, long value);
+/* Run all subsequent work of the context on the caller's CUDA stream (a cudaStream_t of the
+ * context's device; NULL: back to the context's own stream).  Drains the previous stream first. */
+int b200_use_stream(b200_ctx *ctx, void *cuda_stream);
 
 /* Pinned host memory for the solver outputs (prove.go:119-125 W, A, B, C) so that the per-proof
  * H2D copies run at PCIe speed; plain Go slices also work (pageable path). */
@@ -236,7 +239,10 @@ typedef struct b200_timings {
  * computeH = PACK x3, inverse DIF x3 (scales H_A, H_BC, H_A), forward DIT x3, b200_fr_mul_sub_dev,
  * inverse DIF (COSETINV_BR): rank r ends with h[r n / ranks, (r+1) n / ranks) in the bit-reversed
  * order G1.Z is stored in (prove.go:232-234,353-396), ready for b200_groth16_msms_dev.
- * Every call returns after its kernels finished (the exchange runs on the caller's stream). */
+ * The phase calls and b200_fr_mul_sub_dev only ENQUEUE on the context's stream: either b200_sync
+ * before handing a buffer to the exchange, or -- the intended use -- b200_use_stream(ctx, s) with the
+ * stream the exchange is ordered on (torch.cuda.current_stream().cuda_stream for torch.distributed),
+ * so that phases and all-to-alls are stream-ordered with no host round trip. */
 enum b200_dist_phase { B200_DIST_PACK = 0, B200_DIST_DIF_LOCAL = 1, B200_DIST_DIF_CROSS = 2, B200_DIST_DIT_LOCAL = 3, B200_DIST_DIT_CROSS = 4 };
 enum b200_dist_scale { B200_SCALE_NONE = 0, B200_SCALE_H_A = 1, B200_SCALE_H_BC = 2, B200_SCALE_COSETINV_BR = 3, B200_SCALE_NINV = 4 };
 int b200_ntt_dist_phase(b200_ctx *ctx, int curve, unsigned log_n, const uint64_t *generator, const uint64_t *coset_gen,

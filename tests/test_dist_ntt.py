@@ -51,6 +51,8 @@ def test_distributed_compute_h_virtual_ranks(pkg, model, cref, log_n, world, tl,
             eng = ModelEngine(model, cref, log_n, rank, world, tl, smax)
             blk = [v[rank * n_loc:(rank + 1) * n_loc].copy() for v in (a, b, c)]
             tmp = np.zeros((n_loc, 4), dtype=np.uint64)
+            if (log_n + world) % 2:                       # both scratch arrangements
+                tmp = [tmp, np.zeros_like(tmp), np.zeros_like(tmp)]
             got[rank] = pkg.sharding.compute_h_distributed(eng, ex.bind(rank), blk[0], blk[1], blk[2], tmp)
         except Exception as e:   # noqa: BLE001
             errs.append(e)
@@ -92,8 +94,8 @@ WORKER = textwrap.dedent("""
     a, b, c = (rand_field(rng, n) for _ in range(3))
     eng = ModelEngine(model, cref, log_n, rank, world, 4, 3)
     bufs = [torch.from_numpy(v[rank * n_loc:(rank + 1) * n_loc].copy().view(np.int64)) for v in (a, b, c)]
-    tmp = torch.zeros((n_loc, 4), dtype=torch.int64)
-    h = pkg.sharding.compute_h_distributed(eng, pkg.sharding.torch_exchange(dist), bufs[0], bufs[1], bufs[2], tmp)
+    tmp = [torch.zeros((n_loc, 4), dtype=torch.int64) for _ in range(3)]
+    h = pkg.sharding.compute_h_distributed(eng, pkg.sharding.torch_exchange(dist, async_op=True), bufs[0], bufs[1], bufs[2], tmp)
     d = N.Domain(n)
     want = cref.compute_h(a, b, c, log_n, cref.fr(d.generator), cref.fr(d.coset_gen))
     lo, hi = rank * n_loc, (rank + 1) * n_loc

@@ -91,3 +91,107 @@ def test_sharded_partial_sums_combine(ctx, pkg, cref):
     comb = pkg.g2_jac_add(parts[0]["bs2"], parts[1]["bs2"])
     assert np.array_equal(pkg.g2_jac_to_affine(comb), pkg.g2_jac_to_affine(fd["bs2"]))
     pk_full.free()
+
+
+class _LockedEngine:
+    """DeviceEngine whose calls into the (non re-entrant) context are serialised: the virtual ranks
+    of the tests below share one device and one b200_ctx."""
+
+    def __init__(self, pkg, ctx, lock, log_n, gen, coset, rank, world):
+        self.e, self.lock = pkg.sharding.DeviceEngine(ctx, log_n, gen, coset, rank, world), lock
+
+    def phase(self, *a, **k):
+        with self.lock:
+            self.e.phase(*a, **k)
+
+    def mul_sub(self, *a):
+        with self.lock:
+            self.e.mul_sub(*a)
+
+
+def _run_virtual_ranks(pkg, ctx, log_n, gen, coset, world, a, b, c):
+    """compute_h_distributed on `world` virtual ranks of one device; the all-to-all goes through the host."""
+    import threading
+    n_loc = (1 << log_n) // world
+    lock, barrier, slots = threading.Lock(), threading.Barrier(world), [None] * world
+    res, errs = [None] * world, []
+
+    def pad(x):
+        o = np.zeros((1 << log_n, 4), dtype=np.uint64)
+        o[: len(x)] = x
+        return o
+    a, b, c = pad(a), pad(b), pad(c)
+
+    def run(rank):
+        try:
+            with lock:
+                bufs = [pkg.DeviceVector(ctx, n_loc * 32).upload(np.ascontiguousarray(v[rank * n_loc:(rank + 1) * n_loc])) for v in (a, b, c)]
+                tmp = pkg.DeviceVector(ctx, n_loc * 32)
+
+            def exchange(send, recv):
+                with lock:
+                    slots[rank] = send.download((n_loc, 4))
+                barrier.wait()
+                chunk = n_loc // world
+                got = np.concatenate([slots[r][rank * chunk:(rank + 1) * chunk] for r in range(world)])
+                barrier.wait()
+                with lock:
+                    recv.upload(got)
+
+            eng = _LockedEngine(pkg, ctx, lock, log_n, gen, coset, rank, world)
+            h = pkg.sharding.compute_h_distributed(eng, exchange, bufs[0], bufs[1], bufs[2], tmp)
+            res[rank] = (h, bufs, tmp)
+        except Exception as e:   # noqa: BLE001
+            errs.append(e)
+            barrier.abort()
+
+    ts = [threading.Thread(target=run, args=(r,)) for r in range(world)]
+    [t.start() for t in ts]
+    [t.join() for t in ts]
+    assert not errs, errs
+    return res
+
+
+@pytest.mark.parametrize("log_n,world", [(4, 2), (6, 8), (10, 2), (10, 4), (12, 8), (14, 4), (16, 8), (18, 2)])
+def test_distributed_compute_h_matches_single_device(ctx, pkg, cref, log_n, world):
+    from tests.conftest import rand_field
+    n = 1 << log_n
+    rng = np.random.default_rng(log_n * 10 + world)
+    a, b, c = (rand_field(rng, n - 5) for _ in range(3))
+    d = G.ntt.Domain(n)
+    gen, coset = cref.fr(d.generator), cref.fr(d.coset_gen)
+    want = ctx.compute_h(a, b, c, log_n, gen, coset)
+    if log_n <= 14:
+        assert np.array_equal(want, cref.compute_h(a, b, c, log_n, gen, coset))
+    res = _run_virtual_ranks(pkg, ctx, log_n, gen, coset, world, a, b, c)
+    n_loc = n // world
+    got = np.concatenate([h.download((n_loc, 4)) for h, _, _ in res])
+    assert np.array_equal(got, want)
+    for h, bufs, tmp in res:
+        [v.free() for v in bufs]
+        tmp.free()
+
+
+def test_distributed_prove_core_two_virtual_ranks(ctx, pkg, cref):
+    """Distributed computeH + b200_groth16_msms_dev on 2 virtual ranks: the combined partial sums
+    equal the single-device prove core."""
+    nb_mul = (1 << 10) - 1
+    w, a, b, c = G.mul_chain_witness(nb_mul, 2)
+    fa, fb, fc, fw = (util.fr_arr(x) for x in (a, b, c, w))
+    r1cs, td, pk, vk, pk_full, _ = build_trapdoor_key(ctx, cref, nb_mul)
+    full = ctx.groth16_prove_core(pk_full, fa, fb, fc, fw)[0].as_dict()
+    d = pk.domain
+    gen, coset = cref.fr(d.generator), cref.fr(d.coset_gen)
+    res = _run_virtual_ranks(pkg, ctx, d.log_n, gen, coset, 2, fa, fb, fc)
+    wv = pkg.DeviceVector(ctx, fw.nbytes).upload(fw)
+    parts = []
+    for i in range(2):
+        _, _, _, _, pk_i, _ = build_trapdoor_key(ctx, cref, nb_mul, shard=(i, 2))
+        parts.append(ctx.groth16_msms_dev(pk_i, wv, res[i][0])[0].as_dict())
+        pk_i.free()
+    for k in ("ar", "bs1", "krs", "krs2"):
+        comb = pkg.g1_jac_add(parts[0][k], parts[1][k])
+        assert np.array_equal(pkg.g1_jac_to_affine(comb), pkg.g1_jac_to_affine(full[k])), k
+    comb = pkg.g2_jac_add(parts[0]["bs2"], parts[1]["bs2"])
+    assert np.array_equal(pkg.g2_jac_to_affine(comb), pkg.g2_jac_to_affine(full["bs2"]))
+    pk_full.free()

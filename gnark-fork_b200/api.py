@@ -116,6 +116,7 @@ def load_library():
         "b200_groth16_pk_upload": (i, [vp, i, C.POINTER(_PkDesc), C.POINTER(vp)]),
         "b200_groth16_pk_free": (i, [vp, vp]),
         "b200_groth16_pk_info": (i, [vp, vp, C.POINTER(_MsmSetInfo)]),
+        "b200_groth16_pk_wire_range": (i, [vp, vp, C.POINTER(sz), C.POINTER(sz)]),
         "b200_groth16_prove_core": (i, [vp, vp, vp, vp, vp, sz, vp, vp, sz, C.POINTER(Groth16MsmOut), C.POINTER(_Timings)]),
         "b200_groth16_prove_core_dev": (i, [vp, vp, vp, vp, vp, sz, vp, C.POINTER(Groth16MsmOut), C.POINTER(_Timings)]),
         "b200_groth16_msms_dev": (i, [vp, vp, vp, vp, C.POINTER(Groth16MsmOut), C.POINTER(_Timings)]),
@@ -217,6 +218,8 @@ def _dev_ptr(x):
     """Device address of a DeviceVector, a torch CUDA tensor, or a raw integer."""
     if hasattr(x, "data_ptr"):
         return C.c_void_p(x.data_ptr())
+    if isinstance(x, np.ndarray):          # host memory: the library copies with cudaMemcpyDefault
+        return C.c_void_p(x.ctypes.data)
     p = getattr(x, "ptr", x)
     return p if isinstance(p, C.c_void_p) else C.c_void_p(int(p))
 
@@ -280,6 +283,12 @@ class Groth16ProvingKey:
         arr = (_MsmSetInfo * 5)()
         self.ctx._check(self.ctx.lib.b200_groth16_pk_info(self.ctx.h, self.h, arr))
         return {k: arr[j].as_dict() for j, k in enumerate(("a", "b", "k", "z", "g2b"))}
+
+    def wire_range(self):
+        """[lo, hi) of W this shard reads; only that slice is copied per proof."""
+        lo, hi = C.c_size_t(), C.c_size_t()
+        self.ctx._check(self.ctx.lib.b200_groth16_pk_wire_range(self.ctx.h, self.h, C.byref(lo), C.byref(hi)))
+        return int(lo.value), int(hi.value)
 
     def free(self):
         if self.h:

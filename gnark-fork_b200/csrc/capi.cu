@@ -364,6 +364,12 @@ int b200_groth16_pk_info(b200_ctx* ctx, const b200_groth16_pk* pk, b200_msm_set_
     fill_set_info(ctx, pk->n_b, pk->G2B.bytes, pk->fG2B, out + 4);
     return B200_OK;
 }
+int b200_groth16_pk_wire_range(b200_ctx* ctx, const b200_groth16_pk* pk, size_t* lo, size_t* hi) {
+    if (!ctx) return B200_ERR_ARG;
+    if (!pk || !lo || !hi) return ctx->fail(B200_ERR_ARG, "null argument");
+    *lo = pk->w_lo; *hi = pk->w_hi;
+    return B200_OK;
+}
 int b200_groth16_prove_core(b200_ctx* ctx, const b200_groth16_pk* pk, const uint64_t* a, const uint64_t* b,
                             const uint64_t* c, size_t n_constraints, const uint64_t* w, const uint32_t* k_remove,
                             size_t n_remove, b200_groth16_out* out, b200_timings* timings) {

@@ -57,15 +57,19 @@ static int maybe_fold(b200_ctx* ctx, DevBuf& bases, size_t n, MsmFold& fold, int
 }
 
 // wire indices whose base is not the point at infinity, positions [lo, hi) of that list
-static int upload_wire_map(b200_ctx* ctx, DevBuf& dst, const uint8_t* infinity, size_t n_wires, size_t expect,
-                           size_t lo, size_t hi) {
-    std::vector<uint32_t> map;
+static int wire_map(b200_ctx* ctx, std::vector<uint32_t>& map, const uint8_t* infinity, size_t n_wires, size_t expect) {
+    map.clear();
     map.reserve(expect);
     for (size_t i = 0; i < n_wires; ++i)
         if (!infinity[i]) map.push_back((uint32_t)i);
     if (map.size() != expect) return ctx->fail(B200_ERR_ARG, "infinity bitmap does not match the base count");
+    return B200_OK;
+}
+static int upload_wire_map(b200_ctx* ctx, DevBuf& dst, const std::vector<uint32_t>& map, size_t lo, size_t hi, uint32_t rebase) {
+    std::vector<uint32_t> rel(map.begin() + lo, map.begin() + hi);
+    for (auto& v : rel) v -= rebase;
     B2_CUDA(ctx, dst.alloc((hi - lo) * 4));
-    if (hi > lo) B2_CUDA(ctx, cudaMemcpy(dst.p, map.data() + lo, (hi - lo) * 4, cudaMemcpyHostToDevice));
+    if (hi > lo) B2_CUDA(ctx, cudaMemcpy(dst.p, rel.data(), (hi - lo) * 4, cudaMemcpyHostToDevice));
     return B200_OK;
 }
 
@@ -89,15 +93,33 @@ int groth16_pk_upload(b200_ctx* ctx, const b200_groth16_pk_desc* d, b200_groth16
     const int si = d->shard_index, sc = d->shard_count;
     const bool ps = d->presliced != 0;
     size_t lo, hi;
-    if (st == B200_OK) { shard_range(d->n_a, si, sc, &lo, &hi); pk->n_a = hi - lo;
-        st = upload_range<G1Affine>(ctx, pk->A, d->g1_a, lo, hi, ps);
-        if (st == B200_OK) st = upload_wire_map(ctx, pk->mapA, d->infinity_a, d->n_wires, d->n_a, lo, hi); }
-    if (st == B200_OK) { shard_range(d->n_b, si, sc, &lo, &hi); pk->n_b = hi - lo;
-        st = upload_range<G1Affine>(ctx, pk->B, d->g1_b, lo, hi, ps);
-        if (st == B200_OK) st = upload_range<G2Affine>(ctx, pk->G2B, d->g2_b, lo, hi, ps);
-        if (st == B200_OK) st = upload_wire_map(ctx, pk->mapB, d->infinity_b, d->n_wires, d->n_b, lo, hi); }
-    if (st == B200_OK) { shard_range(d->n_k, si, sc, &lo, &hi); pk->n_k = hi - lo; pk->k_lo = lo;
-        st = upload_range<G1Affine>(ctx, pk->K, d->g1_k, lo, hi, ps); }
+    // Only the wires this shard's A, B and K ranges reference are copied per proof: [w_lo, w_hi)
+    std::vector<uint32_t> wa, wb;
+    size_t a_lo = 0, a_hi = 0, b_lo = 0, b_hi = 0;
+    if (st == B200_OK) st = wire_map(ctx, wa, d->infinity_a, d->n_wires, d->n_a);
+    if (st == B200_OK) st = wire_map(ctx, wb, d->infinity_b, d->n_wires, d->n_b);
+    if (st == B200_OK) {
+        shard_range(d->n_a, si, sc, &a_lo, &a_hi); pk->n_a = a_hi - a_lo;
+        shard_range(d->n_b, si, sc, &b_lo, &b_hi); pk->n_b = b_hi - b_lo;
+        shard_range(d->n_k, si, sc, &lo, &hi); pk->n_k = hi - lo; pk->k_lo = lo;
+        size_t w_lo = d->n_wires, w_hi = 0;
+        if (a_hi > a_lo) { w_lo = std::min<size_t>(w_lo, wa[a_lo]); w_hi = std::max<size_t>(w_hi, (size_t)wa[a_hi - 1] + 1); }
+        if (b_hi > b_lo) { w_lo = std::min<size_t>(w_lo, wb[b_lo]); w_hi = std::max<size_t>(w_hi, (size_t)wb[b_hi - 1] + 1); }
+        if (pk->n_k) {
+            // K scalars: W[nb_public + k_lo ...), shifted up by at most the committed wires removed per proof
+            w_lo = std::min<size_t>(w_lo, d->nb_public + pk->k_lo);
+            const size_t slack = d->n_wires - d->nb_public - d->n_k;   // = number of committed private wires
+            w_hi = std::max<size_t>(w_hi, std::min<size_t>(d->n_wires, d->nb_public + pk->k_lo + pk->n_k + slack));
+        }
+        if (w_hi < w_lo) w_lo = w_hi = 0;
+        pk->w_lo = w_lo; pk->w_hi = w_hi;
+    }
+    if (st == B200_OK) st = upload_range<G1Affine>(ctx, pk->A, d->g1_a, a_lo, a_hi, ps);
+    if (st == B200_OK) st = upload_wire_map(ctx, pk->mapA, wa, a_lo, a_hi, (uint32_t)pk->w_lo);
+    if (st == B200_OK) st = upload_range<G1Affine>(ctx, pk->B, d->g1_b, b_lo, b_hi, ps);
+    if (st == B200_OK) st = upload_range<G2Affine>(ctx, pk->G2B, d->g2_b, b_lo, b_hi, ps);
+    if (st == B200_OK) st = upload_wire_map(ctx, pk->mapB, wb, b_lo, b_hi, (uint32_t)pk->w_lo);
+    if (st == B200_OK) st = upload_range<G1Affine>(ctx, pk->K, d->g1_k, pk->k_lo, pk->k_lo + pk->n_k, ps);
     if (st == B200_OK) { shard_range_z(d->n_z, d->log_n, si, sc, &lo, &hi); pk->n_z = hi - lo; pk->z_lo = lo;
         st = upload_range<G1Affine>(ctx, pk->Z, d->g1_z, lo, hi, ps); }
     if (st == B200_OK && cudaStreamSynchronize(ctx->stream) != cudaSuccess) st = ctx->fail(B200_ERR_CUDA, "pk upload");
@@ -151,7 +173,8 @@ int groth16_prove_core(b200_ctx* ctx, const b200_groth16_pk* pk, const uint64_t*
     const size_t o_a = ar.off; ar.take(n_abc * sizeof(Fr));
     const size_t o_b = ar.off; ar.take(n_abc * sizeof(Fr));
     const size_t o_c = ar.off; ar.take(n_abc * sizeof(Fr));
-    const size_t o_w = ar.off; ar.take(pk->n_wires * sizeof(Fr));
+    const size_t n_w = pk->w_hi - pk->w_lo;   // wires this shard reads
+    const size_t o_w = ar.off; ar.take(n_w * sizeof(Fr));
     const size_t o_kmap = ar.off; ar.take(n_remove ? pk->n_k * 4 : 0);
     const size_t o_msm = ar.off; ar.take(msm_ws);
     B2_TRY(ctx_reserve(ctx, ar.off));
@@ -172,8 +195,8 @@ int groth16_prove_core(b200_ctx* ctx, const b200_groth16_pk* pk, const uint64_t*
     // which computeH picks up after those MSMs -- the ~2 GiB of PCIe traffic hides behind them.
     B2_CUDA(ctx, cudaEventRecord(ev[0], st));
     B2_CUDA(ctx, cudaStreamWaitEvent(cp, ev[0], 0));
-    const int span = ctx->prof_begin(B200_PROF_COPY_IN, (double)(3 * n_constraints + pk->n_wires) * sizeof(Fr), cp);
-    B2_CUDA(ctx, cudaMemcpyAsync(d_w, w, pk->n_wires * sizeof(Fr), cudaMemcpyDefault, cp));
+    const int span = ctx->prof_begin(B200_PROF_COPY_IN, (double)(3 * n_constraints + n_w) * sizeof(Fr), cp);
+    if (n_w) B2_CUDA(ctx, cudaMemcpyAsync(d_w, w + 4 * pk->w_lo, n_w * sizeof(Fr), cudaMemcpyDefault, cp));
     if (n_remove) {
         // prove.go:238-242: K scalars are W[nb_public:] minus the committed wires
         std::vector<uint32_t> map;
@@ -181,7 +204,7 @@ int groth16_prove_core(b200_ctx* ctx, const b200_groth16_pk* pk, const uint64_t*
         size_t r = 0;
         for (size_t i = 0; i < pk->n_wires - pk->nb_public; ++i) {
             if (r < n_remove && k_remove[r] == i) { ++r; continue; }
-            map.push_back((uint32_t)(pk->nb_public + i));
+            map.push_back((uint32_t)(pk->nb_public + i - pk->w_lo));
         }
         if (map.size() != pk->full_n_k) return ctx->fail(B200_ERR_ARG, "k_remove must be sorted and unique");
         B2_CUDA(ctx, cudaMemcpyAsync(d_kmap, map.data() + pk->k_lo, pk->n_k * 4, cudaMemcpyHostToDevice, cp));
@@ -206,7 +229,7 @@ int groth16_prove_core(b200_ctx* ctx, const b200_groth16_pk* pk, const uint64_t*
     B2_TRY(msm_g1_run(ctx, pk->B.as<G1Affine>(), d_w, pk->mapB.as<uint32_t>(), pk->n_b, &jb1, ws, &pk->fB));
     B2_CUDA(ctx, cudaEventRecord(ev[3], st));
     if (d_kmap) B2_TRY(msm_g1_run(ctx, pk->K.as<G1Affine>(), d_w, d_kmap, pk->n_k, &jk, ws, &pk->fK));
-    else B2_TRY(msm_g1_run(ctx, pk->K.as<G1Affine>(), d_w + pk->nb_public + pk->k_lo, nullptr, pk->n_k, &jk, ws, &pk->fK));
+    else B2_TRY(msm_g1_run(ctx, pk->K.as<G1Affine>(), d_w + (pk->nb_public + pk->k_lo - pk->w_lo), nullptr, pk->n_k, &jk, ws, &pk->fK));
     B2_CUDA(ctx, cudaEventRecord(ev[4], st));
     B2_TRY(msm_g2_run(ctx, pk->G2B.as<G2Affine>(), d_w, pk->mapB.as<uint32_t>(), pk->n_b, &jb2, ws, &pk->fG2B));
     B2_CUDA(ctx, cudaEventRecord(ev[5], st));

@@ -217,6 +217,9 @@ int b200_groth16_pk_upload(b200_ctx *ctx, int curve, const b200_groth16_pk_desc 
 int b200_groth16_pk_free(b200_ctx *ctx, b200_groth16_pk *pk);
 /* out[0..4] = G1.A, G1.B, G1.K, G1.Z, G2.B of this shard. */
 int b200_groth16_pk_info(b200_ctx *ctx, const b200_groth16_pk *pk, b200_msm_set_info out[5]);
+/* Wire range [lo, hi) of the solution vector W this shard reads (its A, B and K ranges): only
+ * that slice of `w` is copied per proof. */
+int b200_groth16_pk_wire_range(b200_ctx *ctx, const b200_groth16_pk *pk, size_t *lo, size_t *hi);
 
 /* Per-stage device times in milliseconds (CUDA events).  The input copies run on a second stream:
  * W first, then a, b, c, overlapped with the four witness MSMs (order on the device: A, B1, K, B2,

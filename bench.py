@@ -452,7 +452,11 @@ def report(args, world, peak, prof, stage, step_ms, e2e_s, clk, verified, inst, 
     g1_mac_s = g1_pts * MAC32_PER_G1_POINT / (g1_launch_ms * 1e-3)
     roofline = {"kernel": "msm_accumulate_kernel<Fp> (G1 bucket accumulation)", "bound": "imad",
                 "achieved": g1_mac_s / 1e12, "peak": mac_peak / 1e12, "unit": "TMAC32/s", "frac": g1_mac_s / mac_peak,
-                "traffic": None, "launch_ms": g1_launch_ms, "points_per_launch": g1_pts,
+                "traffic": (7.536e9 * g1_pts / 4194304.0) if pk_info["a"]["folded"] and pk_info["a"]["c"] == 20 else None,
+                "traffic_source": "ncu --set full at 2^22 points: dram read 7.464 GB + write 0.072 GB per launch "
+                                  "(profiles/r01_prof_fold_2p22_raw.csv), scaled linearly to this launch's points; "
+                                  "2.1x the 64-byte gathers (128-byte lines), at 11 % of DRAM throughput",
+                "launch_ms": g1_launch_ms, "points_per_launch": g1_pts,
                 "algorithmic_mac32_per_point": MAC32_PER_G1_POINT,
                 "algorithmic_model": "SURVEY 8(d): 16 windows x 11 Fp-mul x 136 MAC32 per point, whatever the kernel executes",
                 "executed_mac32_per_point": pk_info["a"]["windows"] * 10 * 136,
@@ -494,6 +498,8 @@ def report(args, world, peak, prof, stage, step_ms, e2e_s, clk, verified, inst, 
             "g2_msm_points_per_s": (inst.full["b"] / world) / (stage["msm_b2_ms"] * 1e-3) * world if stage["msm_b2_ms"] else None,
             "ntt_hbm_gbs": ntt_gbs, "stage_ms": stage,
             "kernel_ms_per_step": {k: v["ms"] / args.steps for k, v in prof.items() if isinstance(v, dict)},
+            "kernel_ms_note": "msm_sort (and part of msm_reduce) runs on a second stream under the previous MSM's accumulation: "
+                              "those spans overlap the others and are stretched by sharing the SMs; they do not add up to the step",
             "g2_acc_frac_of_imad_peak": (g2["units"] * MAC32_PER_G2_POINT / (g2["ms"] * 1e-3) / mac_peak) if g2["ms"] else None,
             "pk_sets": pk_info, "imad_peak": peak, "verified_known_dlog": verified, "setup_s": t_setup, "wall_s_timed_region": wall_dev,
         },

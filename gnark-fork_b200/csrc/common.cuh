@@ -19,6 +19,10 @@ struct b200_ctx {
     cudaStream_t stream = nullptr;          // all work is ordered on this stream (own_stream unless b200_use_stream)
     cudaStream_t own_stream = nullptr;
     cudaStream_t copy_stream = nullptr;     // per-proof input copies, overlapped with the witness MSMs
+    cudaStream_t aux_stream = nullptr;      // sort of the next MSM, overlapped with the current accumulation
+    void* h_stage = nullptr;                // page-locked staging of MSM result points
+    size_t h_stage_bytes = 0;
+    int msm_overlap = 1;                    // 0: the prove core runs its MSMs strictly one after the other
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     std::string err;
     std::vector<b200::NttDomain*> domains;  // cache keyed by (log_n, generator, coset_gen)

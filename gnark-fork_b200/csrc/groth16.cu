@@ -129,7 +129,8 @@ int groth16_pk_upload(b200_ctx* ctx, const b200_groth16_pk_desc* d, b200_groth16
     const size_t n_max = std::max(std::max(pk->n_a, pk->n_b), std::max(pk->n_k, pk->n_z));
     const int fc = ctx->msm_fold_c ? ctx->msm_fold_c : msm_fold_window(n_max);
     const size_t reserve = 9 * n_dom * sizeof(Fr) + d->n_wires * sizeof(Fr) + d->n_wires * 4
-                         + msm_workspace_bytes(n_max, 2, ctx->msm_c_override, fc) + ((size_t)1 << 30);
+                         + msm_workspace_bytes(n_max, 2, ctx->msm_c_override, fc)
+                         + msm_sizes(n_max, 2, ctx->msm_c_override, fc).sort_bytes + ((size_t)1 << 30);   // two sort groups
     if (st == B200_OK) st = maybe_fold<Fp2>(ctx, pk->G2B, pk->n_b, pk->fG2B, 2, reserve);
     if (st == B200_OK) st = maybe_fold<Fp>(ctx, pk->A, pk->n_a, pk->fA, 1, reserve);
     if (st == B200_OK) st = maybe_fold<Fp>(ctx, pk->B, pk->n_b, pk->fB, 1, reserve);
@@ -161,40 +162,62 @@ int groth16_prove_core(b200_ctx* ctx, const b200_groth16_pk* pk, const uint64_t*
     if (n_constraints > n) return ctx->fail(B200_ERR_ARG, "more constraints than the domain holds");
     if (n_remove && pk->full_n_k + n_remove != pk->n_wires - pk->nb_public)
         return ctx->fail(B200_ERR_ARG, "k_remove does not match len(pk.G1.K)");
-    // workspace: a, b, c (n Fr each), W, optional K map, MSM scratch
-    size_t msm_ws = 0;
-    msm_ws = std::max(msm_ws, msm_workspace_bytes(pk->n_a, 1, ctx->msm_c_override, pk->fA.c));
-    msm_ws = std::max(msm_ws, msm_workspace_bytes(pk->n_b, 1, ctx->msm_c_override, pk->fB.c));
-    msm_ws = std::max(msm_ws, msm_workspace_bytes(pk->n_k, 1, ctx->msm_c_override, pk->fK.c));
-    msm_ws = std::max(msm_ws, msm_workspace_bytes(pk->n_z, 1, ctx->msm_c_override, pk->fZ.c));
-    msm_ws = std::max(msm_ws, msm_workspace_bytes(pk->n_b, 2, ctx->msm_c_override, pk->fG2B.c));
+    // The five MSMs: 0 A, 1 B1, 2 K, 3 B2 (G2), 4 Z.  Workspace: a, b, c (n Fr each), the wire slice
+    // of W, optional K map, two sort groups (the sort of MSM k+1 runs on the aux stream while the
+    // buckets of MSM k are accumulated on the main stream) and one accumulation group.
+    const size_t n_w = pk->w_hi - pk->w_lo;   // wires this shard reads
+    const size_t counts[5] = {pk->n_a, pk->n_b, pk->n_k, pk->n_b, pk->n_z};
+    const int groups[5] = {1, 1, 1, 2, 1};
+    const MsmFold* folds[5] = {&pk->fA, &pk->fB, &pk->fK, &pk->fG2B, &pk->fZ};
+    MsmSizes sz[5];
+    size_t sort_max = 0, acc_max = 0, res_off[6] = {0};
+    for (int k = 0; k < 5; ++k) {
+        sz[k] = msm_sizes(counts[k], groups[k], ctx->msm_c_override, folds[k]->c);
+        sort_max = std::max(sort_max, sz[k].sort_bytes);
+        acc_max = std::max(acc_max, sz[k].acc_bytes);
+        res_off[k + 1] = res_off[k] + ((sz[k].result_bytes + 255) & ~(size_t)255);
+    }
+    const bool overlap = ctx->msm_overlap != 0;
     Arena ar;
     const size_t n_abc = h_local ? 0 : n;
     const size_t o_a = ar.off; ar.take(n_abc * sizeof(Fr));
     const size_t o_b = ar.off; ar.take(n_abc * sizeof(Fr));
     const size_t o_c = ar.off; ar.take(n_abc * sizeof(Fr));
-    const size_t n_w = pk->w_hi - pk->w_lo;   // wires this shard reads
     const size_t o_w = ar.off; ar.take(n_w * sizeof(Fr));
     const size_t o_kmap = ar.off; ar.take(n_remove ? pk->n_k * 4 : 0);
-    const size_t o_msm = ar.off; ar.take(msm_ws);
+    const size_t o_sort0 = ar.off; ar.take(sort_max);
+    const size_t o_sort1 = overlap ? ar.off : o_sort0; if (overlap) ar.take(sort_max);
+    const size_t o_acc = ar.off; ar.take(acc_max);
     B2_TRY(ctx_reserve(ctx, ar.off));
+    if (ctx->h_stage_bytes < res_off[5]) {   // page-locked staging of the few result points per MSM
+        if (ctx->h_stage) cudaFreeHost(ctx->h_stage);
+        ctx->h_stage = nullptr; ctx->h_stage_bytes = 0;
+        B2_CUDA(ctx, cudaMallocHost(&ctx->h_stage, res_off[5]));
+        ctx->h_stage_bytes = res_off[5];
+    }
     char* base = (char*)ctx->scratch;
     Fr* d_a = (Fr*)(base + o_a); Fr* d_b = (Fr*)(base + o_b); Fr* d_c = (Fr*)(base + o_c);
     Fr* d_w = (Fr*)(base + o_w);
     uint32_t* d_kmap = n_remove ? (uint32_t*)(base + o_kmap) : nullptr;
-    void* ws = base + o_msm;
+    char* sort_ws[2] = {base + o_sort0, base + o_sort1};
+    char* acc_ws = base + o_acc;
     cudaStream_t st = ctx->stream;
-
+    cudaStream_t sx = overlap ? ctx->aux_stream : st;
     cudaStream_t cp = ctx->copy_stream;
-    cudaEvent_t ev[11];
-    for (auto& e : ev) B2_CUDA(ctx, cudaEventCreateWithFlags(&e, cudaEventDefault));
-    struct EvGuard { cudaEvent_t* e; ~EvGuard() { for (int i = 0; i < 11; ++i) cudaEventDestroy(e[i]); } } guard{ev};
-    cudaEvent_t ev_w = ev[9], ev_abc = ev[10];
+
+    constexpr int NEV = 24;
+    cudaEvent_t ev[NEV];
+    for (auto& e : ev) B2_CUDA(ctx, cudaEventCreate(&e));
+    struct EvGuard { cudaEvent_t* e; ~EvGuard() { for (int i = 0; i < NEV; ++i) cudaEventDestroy(e[i]); } } guard{ev};
+    cudaEvent_t ev_w = ev[9], ev_abc = ev[10], ev_h = ev[11];
+    cudaEvent_t* ev_sort = ev + 12;   // [5]
+    cudaEvent_t* ev_acc = ev + 17;    // [5]
 
     // Copies run on their own stream: W first (the four witness MSMs need only W), then a, b, c,
-    // which computeH picks up after those MSMs -- the ~2 GiB of PCIe traffic hides behind them.
+    // which computeH picks up later -- the PCIe traffic hides behind the first MSM.
     B2_CUDA(ctx, cudaEventRecord(ev[0], st));
     B2_CUDA(ctx, cudaStreamWaitEvent(cp, ev[0], 0));
+    if (overlap) B2_CUDA(ctx, cudaStreamWaitEvent(sx, ev[0], 0));
     const int span = ctx->prof_begin(B200_PROF_COPY_IN, (double)(3 * n_constraints + n_w) * sizeof(Fr), cp);
     if (n_w) B2_CUDA(ctx, cudaMemcpyAsync(d_w, w + 4 * pk->w_lo, n_w * sizeof(Fr), cudaMemcpyDefault, cp));
     if (n_remove) {
@@ -220,28 +243,84 @@ int groth16_prove_core(b200_ctx* ctx, const b200_groth16_pk* pk, const uint64_t*
     ctx->prof_end(span, cp);
     B2_CUDA(ctx, cudaEventRecord(ev_abc, cp));
 
-    G1Jac ja, jb1, jk, jz;
-    G2Jac jb2;
-    B2_CUDA(ctx, cudaStreamWaitEvent(st, ev_w, 0));
-    B2_CUDA(ctx, cudaEventRecord(ev[1], st));
-    B2_TRY(msm_g1_run(ctx, pk->A.as<G1Affine>(), d_w, pk->mapA.as<uint32_t>(), pk->n_a, &ja, ws, &pk->fA));
-    B2_CUDA(ctx, cudaEventRecord(ev[2], st));
-    B2_TRY(msm_g1_run(ctx, pk->B.as<G1Affine>(), d_w, pk->mapB.as<uint32_t>(), pk->n_b, &jb1, ws, &pk->fB));
-    B2_CUDA(ctx, cudaEventRecord(ev[3], st));
-    if (d_kmap) B2_TRY(msm_g1_run(ctx, pk->K.as<G1Affine>(), d_w, d_kmap, pk->n_k, &jk, ws, &pk->fK));
-    else B2_TRY(msm_g1_run(ctx, pk->K.as<G1Affine>(), d_w + (pk->nb_public + pk->k_lo - pk->w_lo), nullptr, pk->n_k, &jk, ws, &pk->fK));
-    B2_CUDA(ctx, cudaEventRecord(ev[4], st));
-    B2_TRY(msm_g2_run(ctx, pk->G2B.as<G2Affine>(), d_w, pk->mapB.as<uint32_t>(), pk->n_b, &jb2, ws, &pk->fG2B));
-    B2_CUDA(ctx, cudaEventRecord(ev[5], st));
-    B2_CUDA(ctx, cudaStreamWaitEvent(st, ev_abc, 0));
-    B2_CUDA(ctx, cudaEventRecord(ev[6], st));
-    if (!h_local) B2_TRY(ntt_compute_h(ctx, pk->dom, d_a, d_b, d_c));
-    B2_CUDA(ctx, cudaEventRecord(ev[7], st));
+    // computeH goes first when a, b, c are already on the device (nothing to wait for), else after
+    // the first MSM (by then the host copies have landed)
+    bool h_first = false;
+    if (!h_local && n_constraints) {
+        cudaPointerAttributes pa;
+        if (cudaPointerGetAttributes(&pa, a) == cudaSuccess) h_first = pa.type == cudaMemoryTypeDevice;
+        else cudaGetLastError();
+    }
     const Fr* h_z = h_local ? reinterpret_cast<const Fr*>(h_local) : d_a + pk->z_lo;
-    B2_TRY(msm_g1_run(ctx, pk->Z.as<G1Affine>(), h_z, nullptr, pk->n_z, &jz, ws, &pk->fZ));
+    const void* bases[5] = {pk->A.p, pk->B.p, pk->K.p, pk->G2B.p, pk->Z.p};
+    const Fr* scal[5] = {d_w, d_w, d_kmap ? d_w : d_w + (pk->nb_public + pk->k_lo - pk->w_lo), d_w, h_z};
+    const uint32_t* maps[5] = {pk->mapA.as<uint32_t>(), pk->mapB.as<uint32_t>(), d_kmap, pk->mapB.as<uint32_t>(), nullptr};
+    void* jobs[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
+    struct JobGuard { void** j; const int* g; ~JobGuard() { for (int k = 0; k < 5; ++k) if (j[k]) { if (g[k] == 2) msm_g2_job_delete(j[k]); else msm_g1_job_delete(j[k]); } } } jguard{jobs, groups};
+    // G1.B and G2.B carry the same wires (InfinityB, prove.go:160-175): when both run the same plan,
+    // Bs2 reuses the sorted entries and task lists of Bs1 and its own sort is skipped.
+    const bool share_b = overlap && pk->fB.c == pk->fG2B.c && pk->n_b > 0;   // needs Bs1's group kept while K sorts
+    const int sort_slot[5] = {0, 1, 0, 1, 0};
+    for (int k = 0; k < 5; ++k) {
+        void* stage = (char*)ctx->h_stage + res_off[k];
+        char* sw = sort_ws[overlap ? sort_slot[k] : 0];
+        jobs[k] = groups[k] == 2 ? msm_g2_job_new(ctx, (const G2Affine*)bases[k], scal[k], maps[k], counts[k], folds[k], sw, acc_ws, stage)
+                                 : msm_g1_job_new(ctx, (const G1Affine*)bases[k], scal[k], maps[k], counts[k], folds[k], sw, acc_ws, stage);
+    }
+    auto run_h = [&]() -> int {
+        B2_CUDA(ctx, cudaStreamWaitEvent(st, ev_abc, 0));
+        B2_CUDA(ctx, cudaEventRecord(ev[6], st));
+        B2_TRY(ntt_compute_h(ctx, pk->dom, d_a, d_b, d_c));
+        B2_CUDA(ctx, cudaEventRecord(ev[7], st));
+        B2_CUDA(ctx, cudaEventRecord(ev_h, st));
+        return B200_OK;
+    };
+    // sort group of MSM k is free once the previous user of the same slot has been accumulated:
+    // slots 0: A, K, Z;  1: B1, B2 -- so K waits for A, B2 for B1, Z for K
+    auto run_sort = [&](int k) -> int {
+        if (k < 4) B2_CUDA(ctx, cudaStreamWaitEvent(sx, ev_w, 0));
+        else if (!h_local) B2_CUDA(ctx, cudaStreamWaitEvent(sx, ev_h, 0));
+        if (k == 0 && h_first) B2_CUDA(ctx, cudaStreamWaitEvent(sx, ev_h, 0));  // the transforms and a sort only slow each other down
+        if (k == 2) B2_CUDA(ctx, cudaStreamWaitEvent(sx, ev_acc[0], 0));
+        if (k == 3) B2_CUDA(ctx, cudaStreamWaitEvent(sx, ev_acc[1], 0));
+        if (k == 4) B2_CUDA(ctx, cudaStreamWaitEvent(sx, ev_acc[2], 0));
+        if (!(k == 3 && share_b))
+            B2_TRY(groups[k] == 2 ? msm_g2_job_sort(ctx, jobs[k], sx) : msm_g1_job_sort(ctx, jobs[k], sx));
+        B2_CUDA(ctx, cudaEventRecord(ev_sort[k], sx));
+        return B200_OK;
+    };
+    auto run_acc = [&](int k) -> int {
+        B2_CUDA(ctx, cudaStreamWaitEvent(st, ev_sort[k], 0));
+        B2_TRY(groups[k] == 2 ? msm_g2_job_acc(ctx, jobs[k], st) : msm_g1_job_acc(ctx, jobs[k], st));
+        B2_CUDA(ctx, cudaEventRecord(ev_acc[k], st));
+        return B200_OK;
+    };
+    B2_CUDA(ctx, cudaEventRecord(ev[6], st));   // placeholders when computeH is skipped (h supplied)
+    B2_CUDA(ctx, cudaEventRecord(ev[7], st));
+    if (h_first) B2_TRY(run_h());
+    B2_TRY(run_sort(0));
+    B2_TRY(run_sort(1));
+    B2_TRY(run_acc(0));
+    if (!h_local && !h_first) B2_TRY(run_h());
+    B2_TRY(run_sort(2));
+    B2_TRY(run_acc(1));
+    B2_TRY(run_sort(3));
+    B2_TRY(run_acc(2));
+    B2_TRY(run_sort(4));
+    B2_TRY(run_acc(3));
+    B2_TRY(run_acc(4));
     B2_CUDA(ctx, cudaEventRecord(ev[8], st));
     B2_CUDA(ctx, cudaStreamSynchronize(st));
     B2_CUDA(ctx, cudaStreamSynchronize(cp));
+    if (overlap) B2_CUDA(ctx, cudaStreamSynchronize(sx));
+
+    G1Jac ja, jb1, jk, jz;
+    G2Jac jb2;
+    msm_g1_job_finish(jobs[0], &ja);
+    msm_g1_job_finish(jobs[1], &jb1);
+    msm_g1_job_finish(jobs[2], &jk);
+    msm_g2_job_finish(jobs[3], &jb2);
+    msm_g1_job_finish(jobs[4], &jz);
 
     memcpy(out->ar, &ja, sizeof ja);
     memcpy(out->bs1, &jb1, sizeof jb1);
@@ -249,13 +328,16 @@ int groth16_prove_core(b200_ctx* ctx, const b200_groth16_pk* pk, const uint64_t*
     memcpy(out->krs2, &jz, sizeof jz);
     memcpy(out->bs2, &jb2, sizeof jb2);
     if (tm) {
-        tm->h2d_ms = ev_ms(ev[0], ev_abc);           // on the copy stream, overlapped with the witness MSMs
-        tm->msm_a_ms = ev_ms(ev[1], ev[2]);
-        tm->msm_b1_ms = ev_ms(ev[2], ev[3]);
-        tm->msm_k_ms = ev_ms(ev[3], ev[4]);
-        tm->msm_b2_ms = ev_ms(ev[4], ev[5]);
+        // Main-stream intervals: an MSM's figure is its bucket accumulation + reduction (its sort ran
+        // on the aux stream under the previous MSM) plus any wait for that sort.
+        tm->h2d_ms = ev_ms(ev[0], ev_abc);           // on the copy stream, overlapped
         tm->compute_h_ms = ev_ms(ev[6], ev[7]);
-        tm->msm_z_ms = ev_ms(ev[7], ev[8]);
+        const cudaEvent_t a_start = h_first ? ev[7] : ev[0];
+        tm->msm_a_ms = ev_ms(a_start, ev_acc[0]);
+        tm->msm_b1_ms = ev_ms((!h_local && !h_first) ? ev[7] : ev_acc[0], ev_acc[1]);
+        tm->msm_k_ms = ev_ms(ev_acc[1], ev_acc[2]);
+        tm->msm_b2_ms = ev_ms(ev_acc[2], ev_acc[3]);
+        tm->msm_z_ms = ev_ms(ev_acc[3], ev_acc[4]);
         tm->total_ms = ev_ms(ev[0], ev[8]);
     }
     return B200_OK;

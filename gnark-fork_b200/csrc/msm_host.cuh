@@ -20,6 +20,23 @@ int msm_g1_run(b200_ctx* ctx, const G1Affine* d_bases, const Fr* d_scalars, cons
                G1Jac* out_host, void* ws, const MsmFold* fold);
 int msm_g2_run(b200_ctx* ctx, const G2Affine* d_bases, const Fr* d_scalars, const uint32_t* d_idx_map, size_t n,
                G2Jac* out_host, void* ws, const MsmFold* fold);
+// The same pipeline in three steps, for callers that overlap the sort of one MSM with the bucket
+// accumulation of another (groth16.cu): sizes of the two workspace groups and of the host staging,
+// then job_new / job_sort(stream) / job_acc(stream) / [sync] / job_finish / job_delete.
+struct MsmSizes { size_t sort_bytes, acc_bytes, result_bytes; };
+MsmSizes msm_sizes(size_t n, int group, int c_override, int fold_c);
+void* msm_g1_job_new(b200_ctx* ctx, const G1Affine* d_bases, const Fr* d_scalars, const uint32_t* d_idx_map, size_t n,
+                     const MsmFold* fold, void* sort_ws, void* acc_ws, void* host_staging);
+int msm_g1_job_sort(b200_ctx* ctx, void* job, cudaStream_t st);
+int msm_g1_job_acc(b200_ctx* ctx, void* job, cudaStream_t st);
+void msm_g1_job_finish(void* job, G1Jac* out_host);
+void msm_g1_job_delete(void* job);
+void* msm_g2_job_new(b200_ctx* ctx, const G2Affine* d_bases, const Fr* d_scalars, const uint32_t* d_idx_map, size_t n,
+                     const MsmFold* fold, void* sort_ws, void* acc_ws, void* host_staging);
+int msm_g2_job_sort(b200_ctx* ctx, void* job, cudaStream_t st);
+int msm_g2_job_acc(b200_ctx* ctx, void* job, cudaStream_t st);
+void msm_g2_job_finish(void* job, G2Jac* out_host);
+void msm_g2_job_delete(void* job);
 // builds the table for n resident points (device) into `table` ((W x n) affine points); returns
 // B200_ERR_NOMEM without side effects when the table does not fit.
 int msm_fold_build_g1(b200_ctx* ctx, const G1Affine* d_bases, size_t n, int c, size_t reserve_bytes, DevBuf& table);
@@ -27,26 +44,24 @@ int msm_fold_build_g2(b200_ctx* ctx, const G2Affine* d_bases, size_t n, int c, s
 
 #if defined(__CUDACC__)
 
+// Workspace of one MSM in two groups, so that the sort of the next MSM can run (on a second stream)
+// while the buckets of the current one are accumulated:
+//   sort group: digits, sorted entries, histogram / offsets / cursors, task lists, size order
+//   acc group:  buckets, partial sums of split buckets, reduction buffers
+// Offsets are relative to the group's base.
 template <class F>
 struct MsmLayout {
     MsmPlan plan;
-    size_t n, M;  // M = W * nb buckets
-    size_t off_digits, off_sorted, off_counts, off_offsets, off_cursor, off_bsums, off_buckets, off_S[2], off_W[2], total;
-    size_t off_ntasks, off_task_off, off_task_bucket, off_partials, off_order, off_order_hist, off_big;
+    size_t n, M;  // M = WB * nb buckets
+    size_t off_digits, off_sorted, off_counts, off_offsets, off_cursor, off_bsums;
+    size_t off_ntasks, off_task_off, off_task_bucket, off_order, off_order_hist, off_big, sort_total;
+    size_t off_buckets, off_partials, off_S[2], off_W[2], acc_total;
+    size_t total;   // sort_total + acc_total
     uint32_t scan_blocks, chunk, max_tasks, order_shift, T, logT, Q;
     MsmLayout(size_t n_, int c_override, int fold_c) {
         n = n_;
         plan = fold_c ? msm_plan_folded(fold_c) : msm_plan(n, c_override);
         M = (size_t)plan.WB * plan.nb;
-        Arena a;
-        off_digits = a.off; a.take((size_t)plan.W * n * 4);
-        off_sorted = a.off; a.take((size_t)plan.W * n * 4);
-        off_counts = a.off; a.take(M * 4);
-        off_offsets = a.off; a.take(M * 4);
-        off_cursor = a.off; a.take(M * 4);
-        scan_blocks = (uint32_t)((M + SCAN_CHUNK - 1) / SCAN_CHUNK);
-        off_bsums = a.off; a.take((size_t)scan_blocks * 4);
-        off_buckets = a.off; a.take(M * sizeof(XYZZ<F>));
         // task splitting: pieces of at most twice the mean bucket load, but small enough that the
         // launch has ~400 K tasks (148 SMs x 20 warps x 32 lanes x 4 waves) even when few buckets exist
         const size_t entries = (size_t)plan.W * n, mean = entries / M;
@@ -56,66 +71,87 @@ struct MsmLayout {
         if (ch < 32) ch = 32;
         chunk = (uint32_t)ch;
         max_tasks = (uint32_t)(M + entries / chunk + 1);
+        scan_blocks = (uint32_t)((M + SCAN_CHUNK - 1) / SCAN_CHUNK);
+        order_shift = 0;
+        while ((chunk >> order_shift) > (uint32_t)ORDER_BINS - 2) ++order_shift;
+        Arena a;
+        off_digits = a.off; a.take((size_t)plan.W * n * 4);
+        off_sorted = a.off; a.take((size_t)plan.W * n * 4);
+        off_counts = a.off; a.take(M * 4);
+        off_offsets = a.off; a.take(M * 4);
+        off_cursor = a.off; a.take(M * 4);
+        off_bsums = a.off; a.take((size_t)scan_blocks * 4);
         off_ntasks = a.off; a.take(M * 4);
         off_task_off = a.off; a.take(M * 4);
         off_task_bucket = a.off; a.take((size_t)max_tasks * 4);
-        off_partials = a.off; a.take((size_t)max_tasks * sizeof(XYZZ<F>));
         off_big = a.off; a.take((M + 2) * 4);   // [0], [1] = counts, then the list (front: warp-merged, back: CTA-merged)
         off_order = a.off; a.take((size_t)max_tasks * 4);
         off_order_hist = a.off; a.take((size_t)ORDER_BINS * 4 * 2);
-        order_shift = 0;
-        while ((chunk >> order_shift) > (uint32_t)ORDER_BINS - 2) ++order_shift;
+        sort_total = a.off;
+        Arena g;
+        off_buckets = g.off; g.take(M * sizeof(XYZZ<F>));
+        off_partials = g.off; g.take((size_t)max_tasks * sizeof(XYZZ<F>));
         const size_t nodes0 = M / plan.L0;
         T = plan.nb / plan.L0;
         logT = 0;
         while ((1u << logT) < T) ++logT;
         Q = 1 + logT;
-        off_S[0] = a.off; a.take(nodes0 * sizeof(XYZZ<F>));
-        off_W[0] = a.off; a.take(nodes0 * sizeof(XYZZ<F>));
+        off_S[0] = g.off; g.take(nodes0 * sizeof(XYZZ<F>));
+        off_W[0] = g.off; g.take(nodes0 * sizeof(XYZZ<F>));
         // tree ping-pong buffers: WB * Q arrays of T/2 and T/4 points
-        off_S[1] = a.off; a.take((size_t)plan.WB * Q * (T / 2 + 1) * sizeof(XYZZ<F>));
-        off_W[1] = a.off; a.take((size_t)plan.WB * Q * (T / 4 + 1) * sizeof(XYZZ<F>));
-        total = a.off;
+        off_S[1] = g.off; g.take((size_t)plan.WB * Q * (T / 2 + 1) * sizeof(XYZZ<F>));
+        off_W[1] = g.off; g.take((size_t)plan.WB * Q * (T / 4 + 1) * sizeof(XYZZ<F>));
+        acc_total = g.off;
+        total = sort_total + acc_total;
     }
+    size_t result_points() const { return (size_t)plan.WB * Q; }   // XYZZ values the host finishes from
+};
+
+// One MSM in flight: enqueue the sort, enqueue the accumulation (possibly on another stream, after
+// an event), and finish on the host once the result values have arrived.
+template <class F>
+struct MsmJob {
+    MsmLayout<F> lay;
+    const Affine<F>* d_bases;
+    const Fr* d_scalars;
+    const uint32_t* d_idx_map;
+    size_t n;
+    uint32_t stride;
+    char* sort_base;
+    char* acc_base;
+    XYZZ<F>* h_result;   // host staging of lay.result_points() values (page-locked for a truly async copy)
+    MsmJob(b200_ctx* ctx, const Affine<F>* bases, const Fr* scalars, const uint32_t* idx_map, size_t n_, const MsmFold* fold,
+           void* sort_ws, void* acc_ws, XYZZ<F>* host_staging)
+        : lay(n_ ? n_ : 1, ctx->msm_c_override, fold ? fold->c : 0), d_bases(bases), d_scalars(scalars), d_idx_map(idx_map), n(n_),
+          stride(fold && fold->c ? (uint32_t)fold->stride : 0u), sort_base((char*)sort_ws), acc_base((char*)acc_ws),
+          h_result(host_staging) {}
 };
 
 template <class F>
-int msm_run_impl(b200_ctx* ctx, const Affine<F>* d_bases, const Fr* d_scalars, const uint32_t* d_idx_map, size_t n,
-                 Jac<F>* out_host, void* ws, const MsmFold* fold) {
-    if (n == 0) { *out_host = Jac<F>::inf(); return B200_OK; }
-    if (n >= ((size_t)1 << 31)) return ctx->fail(B200_ERR_UNSUPPORTED, "MSM above 2^31 points");
-    const int fold_c = fold ? fold->c : 0;
-    MsmLayout<F> lay(n, ctx->msm_c_override, fold_c);
-    const uint32_t stride = fold_c ? (uint32_t)fold->stride : 0u;
+int msm_enqueue_sort(b200_ctx* ctx, const MsmJob<F>& job, cudaStream_t st) {
+    if (job.n == 0) return B200_OK;
+    const MsmLayout<F>& lay = job.lay;
     const MsmPlan& pl = lay.plan;
-    char* base;
-    if (ws) base = (char*)ws;
-    else { B2_TRY(ctx_reserve(ctx, lay.total)); base = (char*)ctx->scratch; }
+    const size_t n = job.n;
+    char* base = job.sort_base;
     int32_t* digits = (int32_t*)(base + lay.off_digits);
     uint32_t* sorted = (uint32_t*)(base + lay.off_sorted);
     uint32_t* counts = (uint32_t*)(base + lay.off_counts);
     uint32_t* offsets = (uint32_t*)(base + lay.off_offsets);
     uint32_t* cursor = (uint32_t*)(base + lay.off_cursor);
     uint32_t* bsums = (uint32_t*)(base + lay.off_bsums);
-    XYZZ<F>* buckets = (XYZZ<F>*)(base + lay.off_buckets);
     uint32_t* ntasks = (uint32_t*)(base + lay.off_ntasks);
     uint32_t* task_off = (uint32_t*)(base + lay.off_task_off);
     uint32_t* task_bucket = (uint32_t*)(base + lay.off_task_bucket);
-    XYZZ<F>* partials = (XYZZ<F>*)(base + lay.off_partials);
     uint32_t* big = (uint32_t*)(base + lay.off_big);
     uint32_t* order = (uint32_t*)(base + lay.off_order);
     uint32_t* order_hist = (uint32_t*)(base + lay.off_order_hist);
-    XYZZ<F>* S[2] = {(XYZZ<F>*)(base + lay.off_S[0]), (XYZZ<F>*)(base + lay.off_S[1])};
-    XYZZ<F>* Wt[2] = {(XYZZ<F>*)(base + lay.off_W[0]), (XYZZ<F>*)(base + lay.off_W[1])};
-    cudaStream_t st = ctx->stream;
     const uint32_t M = (uint32_t)lay.M;
-
-    constexpr int ACC_SLOT = sizeof(F) == sizeof(Fp) ? B200_PROF_MSM_ACC_G1 : B200_PROF_MSM_ACC_G2;
-    int span = ctx->prof_begin(B200_PROF_MSM_SORT, (double)n);
+    const int span = ctx->prof_begin(B200_PROF_MSM_SORT, (double)n, st);
     B2_CUDA(ctx, cudaMemsetAsync(counts, 0, lay.M * 4, st));
     {
         const int bs = 256;
-        msm_digits_kernel<<<(unsigned)((n + bs - 1) / bs), bs, 0, st>>>(d_scalars, d_idx_map, (uint32_t)n, pl.c, pl.W, pl.fold, digits, counts, pl.nb);
+        msm_digits_kernel<<<(unsigned)((n + bs - 1) / bs), bs, 0, st>>>(job.d_scalars, job.d_idx_map, (uint32_t)n, pl.c, pl.W, pl.fold, digits, counts, pl.nb);
         B2_CUDA(ctx, cudaGetLastError());
     }
     msm_scan_sums_kernel<<<lay.scan_blocks, SCAN_THREADS, 0, st>>>(counts, M, bsums);
@@ -126,7 +162,7 @@ int msm_run_impl(b200_ctx* ctx, const Affine<F>* d_bases, const Fr* d_scalars, c
     B2_CUDA(ctx, cudaGetLastError());
     {
         const int bs = 256;
-        msm_scatter_kernel<<<(unsigned)((n + bs - 1) / bs), bs, 0, st>>>(digits, (uint32_t)n, pl.c, pl.W, pl.fold, stride, pl.nb, cursor, sorted);
+        msm_scatter_kernel<<<(unsigned)((n + bs - 1) / bs), bs, 0, st>>>(digits, (uint32_t)n, pl.c, pl.W, pl.fold, job.stride, pl.nb, cursor, sorted);
         B2_CUDA(ctx, cudaGetLastError());
     }
     {
@@ -153,15 +189,42 @@ int msm_run_impl(b200_ctx* ctx, const Affine<F>* d_bases, const Fr* d_scalars, c
         msm_order_fill_kernel<<<ob, ORDER_THREADS, 0, st>>>(task_bucket, task_off, ntasks, counts, lay.max_tasks, lay.chunk, lay.order_shift, order_hist, order);
         B2_CUDA(ctx, cudaGetLastError());
     }
-    ctx->prof_end(span);
+    ctx->prof_end(span, st);
+    ctx->n_launches += 13;  // digits, 2 x 3 scan, scatter, task count/fill, 3 x order
+    return B200_OK;
+}
+
+template <class F>
+int msm_enqueue_acc(b200_ctx* ctx, const MsmJob<F>& job, cudaStream_t st) {
+    if (job.n == 0) return B200_OK;
+    const MsmLayout<F>& lay = job.lay;
+    const MsmPlan& pl = lay.plan;
+    const size_t n = job.n;
+    char* sb = job.sort_base;
+    char* ab = job.acc_base;
+    uint32_t* sorted = (uint32_t*)(sb + lay.off_sorted);
+    uint32_t* counts = (uint32_t*)(sb + lay.off_counts);
+    uint32_t* offsets = (uint32_t*)(sb + lay.off_offsets);
+    uint32_t* ntasks = (uint32_t*)(sb + lay.off_ntasks);
+    uint32_t* task_off = (uint32_t*)(sb + lay.off_task_off);
+    uint32_t* task_bucket = (uint32_t*)(sb + lay.off_task_bucket);
+    uint32_t* big = (uint32_t*)(sb + lay.off_big);
+    uint32_t* order = (uint32_t*)(sb + lay.off_order);
+    XYZZ<F>* buckets = (XYZZ<F>*)(ab + lay.off_buckets);
+    XYZZ<F>* partials = (XYZZ<F>*)(ab + lay.off_partials);
+    XYZZ<F>* S[2] = {(XYZZ<F>*)(ab + lay.off_S[0]), (XYZZ<F>*)(ab + lay.off_S[1])};
+    XYZZ<F>* Wt[2] = {(XYZZ<F>*)(ab + lay.off_W[0]), (XYZZ<F>*)(ab + lay.off_W[1])};
+    const uint32_t M = (uint32_t)lay.M;
+    constexpr int ACC_SLOT = sizeof(F) == sizeof(Fp) ? B200_PROF_MSM_ACC_G1 : B200_PROF_MSM_ACC_G2;
+    int span;
     {
         const int bs = 128;
-        span = ctx->prof_begin(ACC_SLOT, (double)n);
-        msm_accumulate_kernel<F><<<(lay.max_tasks + bs - 1) / bs, bs, 0, st>>>(d_bases, sorted, offsets, counts, task_bucket, task_off,
+        span = ctx->prof_begin(ACC_SLOT, (double)n, st);
+        msm_accumulate_kernel<F><<<(lay.max_tasks + bs - 1) / bs, bs, 0, st>>>(job.d_bases, sorted, offsets, counts, task_bucket, task_off,
                                                                             ntasks, order, lay.max_tasks, lay.chunk, buckets, partials);
-        ctx->prof_end(span);
+        ctx->prof_end(span, st);
         B2_CUDA(ctx, cudaGetLastError());
-        span = ctx->prof_begin(B200_PROF_MSM_REDUCE, (double)n);
+        span = ctx->prof_begin(B200_PROF_MSM_REDUCE, (double)n, st);
         msm_combine_kernel<F><<<(M + bs - 1) / bs, bs, 0, st>>>(task_off, ntasks, M, partials, buckets);
         B2_CUDA(ctx, cudaGetLastError());
         msm_combine_warp_kernel<F><<<ctx->sm_count * 8, 128, 0, st>>>(big, big + 2, task_off, ntasks, partials, buckets);
@@ -176,8 +239,8 @@ int msm_run_impl(b200_ctx* ctx, const Affine<F>* d_bases, const Fr* d_scalars, c
         msm_reduce_leaf_kernel<F><<<(nodes + 63) / 64, 64, 0, st>>>(buckets, nodes, pl.L0, S[0], Wt[0]);
         B2_CUDA(ctx, cudaGetLastError());
     }
-    ctx->n_launches += 18;  // digits, 2 x 3 scan, scatter, task count/fill, 3 x order, accumulate, 3 x combine, leaf
-    std::vector<XYZZ<F>> fin((size_t)pl.WB * Q);
+    ctx->n_launches += 5;  // accumulate, 3 x combine, leaf
+    const size_t out_bytes = lay.result_points() * sizeof(XYZZ<F>);
     if (T >= 2) {
         XYZZ<F>* buf[2] = {S[1], Wt[1]};
         const uint32_t groups = (uint32_t)pl.WB * Q;
@@ -197,20 +260,28 @@ int msm_run_impl(b200_ctx* ctx, const Affine<F>* d_bases, const Fr* d_scalars, c
             m >>= 1;
             cur ^= 1;
         }
-        ctx->prof_end(span);
-        B2_CUDA(ctx, cudaMemcpyAsync(fin.data(), buf[cur], fin.size() * sizeof(XYZZ<F>), cudaMemcpyDeviceToHost, st));
+        ctx->prof_end(span, st);
+        B2_CUDA(ctx, cudaMemcpyAsync(job.h_result, buf[cur], out_bytes, cudaMemcpyDeviceToHost, st));
     } else {
-        ctx->prof_end(span);
-        B2_CUDA(ctx, cudaMemcpyAsync(fin.data(), Wt[0], fin.size() * sizeof(XYZZ<F>), cudaMemcpyDeviceToHost, st));
+        ctx->prof_end(span, st);
+        B2_CUDA(ctx, cudaMemcpyAsync(job.h_result, Wt[0], out_bytes, cudaMemcpyDeviceToHost, st));
     }
-    B2_CUDA(ctx, cudaStreamSynchronize(st));
-    // host: per set V_0 + L0 * sum_b 2^b V_{1+b}; then the c-doubling Horner over the sets
+    return B200_OK;
+}
+
+// host, after the stream that ran msm_enqueue_acc has been synchronised: per bucket set
+// V_0 + L0 * sum_b 2^b V_{1+b}; then the c-doubling Horner over the sets
+template <class F>
+void msm_finish(const MsmJob<F>& job, Jac<F>* out_host) {
+    if (job.n == 0) { *out_host = Jac<F>::inf(); return; }
+    const MsmPlan& pl = job.lay.plan;
+    const uint32_t Q = job.lay.Q;
     uint32_t logL0 = 0;
     while ((1u << logL0) < pl.L0) ++logL0;
     XYZZ<F> acc = XYZZ<F>::inf();
     for (int w = pl.WB - 1; w >= 0; --w) {
         for (int k = 0; k < pl.c; ++k) acc = acc.dbl();
-        const XYZZ<F>* v = &fin[(size_t)w * Q];
+        const XYZZ<F>* v = job.h_result + (size_t)w * Q;
         XYZZ<F> hi = XYZZ<F>::inf();
         for (int bit = (int)Q - 2; bit >= 0; --bit) {
             hi = hi.dbl();
@@ -221,6 +292,24 @@ int msm_run_impl(b200_ctx* ctx, const Affine<F>* d_bases, const Fr* d_scalars, c
         acc.add(hi);
     }
     *out_host = acc.to_jac();
+}
+
+template <class F>
+int msm_run_impl(b200_ctx* ctx, const Affine<F>* d_bases, const Fr* d_scalars, const uint32_t* d_idx_map, size_t n,
+                 Jac<F>* out_host, void* ws, const MsmFold* fold) {
+    if (n == 0) { *out_host = Jac<F>::inf(); return B200_OK; }
+    if (n >= ((size_t)1 << 31)) return ctx->fail(B200_ERR_UNSUPPORTED, "MSM above 2^31 points");
+    const int fold_c = fold ? fold->c : 0;
+    MsmLayout<F> lay(n, ctx->msm_c_override, fold_c);
+    char* base;
+    if (ws) base = (char*)ws;
+    else { B2_TRY(ctx_reserve(ctx, lay.total)); base = (char*)ctx->scratch; }
+    std::vector<XYZZ<F>> fin(lay.result_points());
+    MsmJob<F> job(ctx, d_bases, d_scalars, d_idx_map, n, fold, base, base + lay.sort_total, fin.data());
+    B2_TRY(msm_enqueue_sort(ctx, job, ctx->stream));
+    B2_TRY(msm_enqueue_acc(ctx, job, ctx->stream));
+    B2_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    msm_finish(job, out_host);
     return B200_OK;
 }
 

@@ -298,17 +298,25 @@ int groth16_prove_core(b200_ctx* ctx, const b200_groth16_pk* pk, const uint64_t*
     B2_CUDA(ctx, cudaEventRecord(ev[6], st));   // placeholders when computeH is skipped (h supplied)
     B2_CUDA(ctx, cudaEventRecord(ev[7], st));
     if (h_first) B2_TRY(run_h());
-    B2_TRY(run_sort(0));
-    B2_TRY(run_sort(1));
-    B2_TRY(run_acc(0));
-    if (!h_local && !h_first) B2_TRY(run_h());
-    B2_TRY(run_sort(2));
-    B2_TRY(run_acc(1));
-    B2_TRY(run_sort(3));
-    B2_TRY(run_acc(2));
-    B2_TRY(run_sort(4));
-    B2_TRY(run_acc(3));
-    B2_TRY(run_acc(4));
+    if (overlap) {
+        B2_TRY(run_sort(0));
+        B2_TRY(run_sort(1));
+        B2_TRY(run_acc(0));
+        if (!h_local && !h_first) B2_TRY(run_h());
+        B2_TRY(run_sort(2));
+        B2_TRY(run_acc(1));
+        B2_TRY(run_sort(3));
+        B2_TRY(run_acc(2));
+        B2_TRY(run_sort(4));
+        B2_TRY(run_acc(3));
+        B2_TRY(run_acc(4));
+    } else {   // one stream, one sort group: strictly sort, accumulate, sort, ...
+        for (int k = 0; k < 5; ++k) {
+            if (k == 1 && !h_local && !h_first) B2_TRY(run_h());
+            B2_TRY(run_sort(k));
+            B2_TRY(run_acc(k));
+        }
+    }
     B2_CUDA(ctx, cudaEventRecord(ev[8], st));
     B2_CUDA(ctx, cudaStreamSynchronize(st));
     B2_CUDA(ctx, cudaStreamSynchronize(cp));

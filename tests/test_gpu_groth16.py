@@ -195,3 +195,27 @@ def test_distributed_prove_core_two_virtual_ranks(ctx, pkg, cref):
     comb = pkg.g2_jac_add(parts[0]["bs2"], parts[1]["bs2"])
     assert np.array_equal(pkg.g2_jac_to_affine(comb), pkg.g2_jac_to_affine(full["bs2"]))
     pk_full.free()
+
+
+def test_prove_core_serial_and_overlapped_agree(ctx, pkg, cref):
+    """msm_overlap = 0 (MSMs strictly one after the other) and the default (sort of the next MSM on a
+    second stream, Bs2 reusing Bs1's sort) give the same five results; so does the device-input entry."""
+    nb_mul = 3000
+    w, a, b, c = G.mul_chain_witness(nb_mul, 2)
+    args = [util.fr_arr(x) for x in (a, b, c, w)]
+    _, _, _, _, pkh, _ = build_trapdoor_key(ctx, cref, nb_mul)
+    ref = ctx.groth16_prove_core(pkh, *args)[0].as_dict()
+    ctx.set_option("msm_overlap", 0)
+    try:
+        serial = ctx.groth16_prove_core(pkh, *args)[0].as_dict()
+    finally:
+        ctx.set_option("msm_overlap", 1)
+    dv = [pkg.DeviceVector(ctx, x.nbytes).upload(x) for x in args]
+    dev = ctx.groth16_prove_core_dev(pkh, dv[0], dv[1], dv[2], len(args[0]), dv[3])[0].as_dict()
+    for k in ("ar", "bs1", "krs", "krs2"):
+        assert np.array_equal(pkg.g1_jac_to_affine(serial[k]), pkg.g1_jac_to_affine(ref[k])), k
+        assert np.array_equal(pkg.g1_jac_to_affine(dev[k]), pkg.g1_jac_to_affine(ref[k])), k
+    assert np.array_equal(pkg.g2_jac_to_affine(serial["bs2"]), pkg.g2_jac_to_affine(ref["bs2"]))
+    assert np.array_equal(pkg.g2_jac_to_affine(dev["bs2"]), pkg.g2_jac_to_affine(ref["bs2"]))
+    [v.free() for v in dv]
+    pkh.free()

@@ -198,3 +198,23 @@ def test_msm_resident_folded_windows(ctx, cref, group, n, fold_c):
     finally:
         ctx.set_option("msm_precompute", 1)
     assert np.array_equal(to_aff(got), to_aff(oracle_msm(scalars, bases)))
+
+
+@pytest.mark.parametrize("group,n", [(1, 1 << 14), (2, 1 << 12)])
+def test_msm_resident_witness_like_scalars(ctx, cref, group, n):
+    """SURVEY 8(d) witness-like scalars (half in {0, 1}, a quarter below 2^16) on the folded path:
+    window 0 piles half of the entries into bucket 1 (split into pieces and merged by the warp / CTA
+    tiers), higher windows are mostly empty."""
+    rng = np.random.default_rng(n + group)
+    bases, _ = (util.known_dlog_bases_g1 if group == 1 else util.known_dlog_bases_g2)(n, seed=3)
+    kind = rng.integers(0, 4, size=n)
+    vals = [int(rng.integers(0, 2)) if k < 2 else int(rng.integers(0, 1 << 16)) if k == 2 else int(rng.integers(0, 1 << 62)) ** 4 % B.R
+            for k in kind]
+    scalars = cref.ints_to_mont(vals, B.R)
+    h = ctx.upload_bases(bases, group)
+    assert h.info()["folded"] == 1
+    got = ctx.msm_resident(h, scalars)
+    h.free()
+    want = (cref.msm_g1 if group == 1 else cref.msm_g2)(scalars, bases)
+    to_aff = cref.g1_jac_to_aff if group == 1 else cref.g2_jac_to_aff
+    assert np.array_equal(to_aff(got), to_aff(want))

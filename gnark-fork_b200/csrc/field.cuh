@@ -52,6 +52,11 @@ struct FpParams {
         return v[i];
     }
     static constexpr uint32_t INV = 0xe4866389u;
+    // p^2 (16 words): added to a difference of wide products to keep it non-negative (Fp2 lazy reduction)
+    B2_HD static constexpr uint32_t p_squared(int i) {
+        constexpr uint32_t v[16] = {0x275d69b1u, 0x3b5458a2u, 0x09eac101u, 0xa602072du, 0x6d96cadcu, 0x4a50189cu, 0x7a1242c8u, 0x04689e95u, 0x34c6b38du, 0x26edfa5cu, 0x16375606u, 0xb00b8551u, 0x0348d21cu, 0x599a6f7cu, 0x763cbf9cu, 0x0925c4b8u};
+        return v[i];
+    }
 };
 
 struct FrParams {
@@ -207,6 +212,185 @@ B2_D void mont_mul_dev(uint32_t* r, const uint32_t* a, const uint32_t* b) {
           "r"(PRM::p(0)), "r"(PRM::p(1)), "r"(PRM::p(2)), "r"(PRM::p(3)), "r"(PRM::p(4)), "r"(PRM::p(5)), "r"(PRM::p(6)), "r"(PRM::p(7)));
 #pragma unroll
     for (int k = 0; k < 8; ++k) r[k] = borrow ? t[k] : s[k];
+}
+
+// ---------------------------------------------------------------------------------------
+// Product / reduction split (lazy reduction in Fp2: three wide products, two reductions).
+// ---------------------------------------------------------------------------------------
+
+// t[0..15] = a * b for a, b < 2^255 (same even/odd row chains as mont_mul_dev, without the m*p rows:
+// the low word of the window is an output word instead of being cancelled).  64 MAC32.
+B2_D void mul_wide_dev(uint32_t* t, const uint32_t* a, const uint32_t* b) {
+    uint32_t e[9], o[8];
+    {
+        const uint32_t y = b[0];
+#pragma unroll
+        for (int j = 0; j < 8; j += 2) {
+            asm("mul.lo.u32 %0, %2, %3;\n\tmul.hi.u32 %1, %2, %3;" : "=r"(e[j]), "=r"(e[j + 1]) : "r"(a[j]), "r"(y));
+            asm("mul.lo.u32 %0, %2, %3;\n\tmul.hi.u32 %1, %2, %3;" : "=r"(o[j]), "=r"(o[j + 1]) : "r"(a[j + 1]), "r"(y));
+        }
+        e[8] = 0;
+        t[0] = e[0];
+    }
+#pragma unroll
+    for (int i = 1; i < 8; ++i) {
+        const uint32_t y = b[i];
+        uint32_t ne[9], no[8];
+        fold_mad_shift8(ne[0], no, e, o[0], a[1], a[3], a[5], a[7], y);
+#pragma unroll
+        for (int k = 1; k < 8; ++k) ne[k] = o[k];
+        mad_chain8_top<true>(ne, a[0], a[2], a[4], a[6], y);
+        t[i] = ne[0];
+#pragma unroll
+        for (int k = 0; k < 9; ++k) e[k] = ne[k];
+#pragma unroll
+        for (int k = 0; k < 8; ++k) o[k] = no[k];
+    }
+    asm("add.cc.u32 %0, %8, %16;\n\t"
+        "addc.cc.u32 %1, %9, %17;\n\t"
+        "addc.cc.u32 %2, %10, %18;\n\t"
+        "addc.cc.u32 %3, %11, %19;\n\t"
+        "addc.cc.u32 %4, %12, %20;\n\t"
+        "addc.cc.u32 %5, %13, %21;\n\t"
+        "addc.cc.u32 %6, %14, %22;\n\t"
+        "addc.u32 %7, %15, %23;\n\t"
+        : "=&r"(t[8]), "=&r"(t[9]), "=&r"(t[10]), "=&r"(t[11]), "=&r"(t[12]), "=&r"(t[13]), "=&r"(t[14]), "=&r"(t[15])
+        : "r"(o[0]), "r"(o[1]), "r"(o[2]), "r"(o[3]), "r"(o[4]), "r"(o[5]), "r"(o[6]), "r"(o[7]),
+          "r"(e[1]), "r"(e[2]), "r"(e[3]), "r"(e[4]), "r"(e[5]), "r"(e[6]), "r"(e[7]), "r"(e[8]));
+}
+
+// 16-word r = a + b and r = a - b (no carry / borrow leaves the top: caller's bound).  Two asm
+// blocks of 8 words each; the carry crosses them in a register and is re-created with one add.
+B2_D void add16_dev(uint32_t* r, const uint32_t* a, const uint32_t* b) {
+    uint32_t c;
+    asm("add.cc.u32 %0, %9, %17;\n\taddc.cc.u32 %1, %10, %18;\n\taddc.cc.u32 %2, %11, %19;\n\taddc.cc.u32 %3, %12, %20;\n\t"
+        "addc.cc.u32 %4, %13, %21;\n\taddc.cc.u32 %5, %14, %22;\n\taddc.cc.u32 %6, %15, %23;\n\taddc.cc.u32 %7, %16, %24;\n\t"
+        "addc.u32 %8, 0, 0;\n\t"
+        : "=&r"(r[0]), "=&r"(r[1]), "=&r"(r[2]), "=&r"(r[3]), "=&r"(r[4]), "=&r"(r[5]), "=&r"(r[6]), "=&r"(r[7]), "=&r"(c)
+        : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(a[4]), "r"(a[5]), "r"(a[6]), "r"(a[7]),
+          "r"(b[0]), "r"(b[1]), "r"(b[2]), "r"(b[3]), "r"(b[4]), "r"(b[5]), "r"(b[6]), "r"(b[7]));
+    uint32_t junk;   // the carry-recreating add needs a destination
+    (void)junk;
+    asm("add.cc.u32 %8, %25, 0xffffffff;\n\t"
+        "addc.cc.u32 %0, %9, %17;\n\taddc.cc.u32 %1, %10, %18;\n\taddc.cc.u32 %2, %11, %19;\n\taddc.cc.u32 %3, %12, %20;\n\t"
+        "addc.cc.u32 %4, %13, %21;\n\taddc.cc.u32 %5, %14, %22;\n\taddc.cc.u32 %6, %15, %23;\n\taddc.u32 %7, %16, %24;\n\t"
+        : "=&r"(r[8]), "=&r"(r[9]), "=&r"(r[10]), "=&r"(r[11]), "=&r"(r[12]), "=&r"(r[13]), "=&r"(r[14]), "=&r"(r[15]), "=&r"(junk)
+        : "r"(a[8]), "r"(a[9]), "r"(a[10]), "r"(a[11]), "r"(a[12]), "r"(a[13]), "r"(a[14]), "r"(a[15]),
+          "r"(b[8]), "r"(b[9]), "r"(b[10]), "r"(b[11]), "r"(b[12]), "r"(b[13]), "r"(b[14]), "r"(b[15]), "r"(c));
+}
+B2_D void sub16_dev(uint32_t* r, const uint32_t* a, const uint32_t* b) {
+    uint32_t c;
+    asm("sub.cc.u32 %0, %9, %17;\n\tsubc.cc.u32 %1, %10, %18;\n\tsubc.cc.u32 %2, %11, %19;\n\tsubc.cc.u32 %3, %12, %20;\n\t"
+        "subc.cc.u32 %4, %13, %21;\n\tsubc.cc.u32 %5, %14, %22;\n\tsubc.cc.u32 %6, %15, %23;\n\tsubc.cc.u32 %7, %16, %24;\n\t"
+        "subc.u32 %8, 0, 0;\n\t"
+        : "=&r"(r[0]), "=&r"(r[1]), "=&r"(r[2]), "=&r"(r[3]), "=&r"(r[4]), "=&r"(r[5]), "=&r"(r[6]), "=&r"(r[7]), "=&r"(c)
+        : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(a[4]), "r"(a[5]), "r"(a[6]), "r"(a[7]),
+          "r"(b[0]), "r"(b[1]), "r"(b[2]), "r"(b[3]), "r"(b[4]), "r"(b[5]), "r"(b[6]), "r"(b[7]));
+    // c = 0 or 0xffffffff: 0 - (c & 1) borrows exactly when the low half borrowed
+    const uint32_t bflag = c & 1u;
+    uint32_t junk;   // the carry-recreating add needs a destination
+    (void)junk;
+    asm("sub.cc.u32 %8, 0, %25;\n\t"
+        "subc.cc.u32 %0, %9, %17;\n\tsubc.cc.u32 %1, %10, %18;\n\tsubc.cc.u32 %2, %11, %19;\n\tsubc.cc.u32 %3, %12, %20;\n\t"
+        "subc.cc.u32 %4, %13, %21;\n\tsubc.cc.u32 %5, %14, %22;\n\tsubc.cc.u32 %6, %15, %23;\n\tsubc.u32 %7, %16, %24;\n\t"
+        : "=&r"(r[8]), "=&r"(r[9]), "=&r"(r[10]), "=&r"(r[11]), "=&r"(r[12]), "=&r"(r[13]), "=&r"(r[14]), "=&r"(r[15]), "=&r"(junk)
+        : "r"(a[8]), "r"(a[9]), "r"(a[10]), "r"(a[11]), "r"(a[12]), "r"(a[13]), "r"(a[14]), "r"(a[15]),
+          "r"(b[8]), "r"(b[9]), "r"(b[10]), "r"(b[11]), "r"(b[12]), "r"(b[13]), "r"(b[14]), "r"(b[15]), "r"(bflag));
+}
+// 8-word r = a + b without reduction (a, b < p: the sum is below 2^255)
+B2_D void add8_raw_dev(uint32_t* r, const uint32_t* a, const uint32_t* b) {
+    asm("add.cc.u32 %0, %8, %16;\n\taddc.cc.u32 %1, %9, %17;\n\taddc.cc.u32 %2, %10, %18;\n\taddc.cc.u32 %3, %11, %19;\n\t"
+        "addc.cc.u32 %4, %12, %20;\n\taddc.cc.u32 %5, %13, %21;\n\taddc.cc.u32 %6, %14, %22;\n\taddc.u32 %7, %15, %23;\n\t"
+        : "=&r"(r[0]), "=&r"(r[1]), "=&r"(r[2]), "=&r"(r[3]), "=&r"(r[4]), "=&r"(r[5]), "=&r"(r[6]), "=&r"(r[7])
+        : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(a[4]), "r"(a[5]), "r"(a[6]), "r"(a[7]),
+          "r"(b[0]), "r"(b[1]), "r"(b[2]), "r"(b[3]), "r"(b[4]), "r"(b[5]), "r"(b[6]), "r"(b[7]));
+}
+
+// parity swap of the reduction window + the next Montgomery factor + its odd row, one carry chain:
+//   ne0 = o0 + e[1];  m = ne0 * INV;  no[0..7] = (e[2..8], 0) + {p1,p3,p5,p7} * m + carry
+template <class PRM>
+B2_D void fold_reduce_shift8(uint32_t& ne0, uint32_t& m, uint32_t* no, const uint32_t* e, uint32_t o0) {
+    asm("add.cc.u32 %0, %10, %11;\n\t"
+        "mul.lo.u32 %9, %0, %23;\n\t"
+        "madc.lo.cc.u32 %1, %19, %9, %12;\n\t"
+        "madc.hi.cc.u32 %2, %19, %9, %13;\n\t"
+        "madc.lo.cc.u32 %3, %20, %9, %14;\n\t"
+        "madc.hi.cc.u32 %4, %20, %9, %15;\n\t"
+        "madc.lo.cc.u32 %5, %21, %9, %16;\n\t"
+        "madc.hi.cc.u32 %6, %21, %9, %17;\n\t"
+        "madc.lo.cc.u32 %7, %22, %9, %18;\n\t"
+        "madc.hi.u32 %8, %22, %9, 0;\n\t"
+        : "=&r"(ne0), "=&r"(no[0]), "=&r"(no[1]), "=&r"(no[2]), "=&r"(no[3]), "=&r"(no[4]),
+          "=&r"(no[5]), "=&r"(no[6]), "=&r"(no[7]), "=&r"(m)
+        : "r"(o0), "r"(e[1]), "r"(e[2]), "r"(e[3]), "r"(e[4]), "r"(e[5]), "r"(e[6]), "r"(e[7]),
+          "r"(e[8]), "r"(PRM::p(1)), "r"(PRM::p(3)), "r"(PRM::p(5)), "r"(PRM::p(7)), "r"(PRM::INV));
+}
+
+// r = t / 2^256 mod p for t = t_lo + 2^256 t_hi < p * 2^256  (r < p)
+template <class PRM>
+B2_D void mont_reduce_dev(uint32_t* r, const uint32_t* t) {
+    uint32_t e[9], o[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) e[k] = t[k];
+    {
+        const uint32_t m = e[0] * PRM::INV;
+#pragma unroll
+        for (int j = 0; j < 8; j += 2)
+            asm("mul.lo.u32 %0, %2, %3;\n\tmul.hi.u32 %1, %2, %3;" : "=r"(o[j]), "=r"(o[j + 1]) : "r"(PRM::p(j + 1)), "r"(m));
+        mad_chain8_top<true>(e, PRM::p(0), PRM::p(2), PRM::p(4), PRM::p(6), m);
+    }
+#pragma unroll
+    for (int i = 1; i < 8; ++i) {
+        uint32_t ne[9], no[8], m;
+        fold_reduce_shift8<PRM>(ne[0], m, no, e, o[0]);
+#pragma unroll
+        for (int k = 1; k < 8; ++k) ne[k] = o[k];
+        mad_chain8_top<true>(ne, PRM::p(0), PRM::p(2), PRM::p(4), PRM::p(6), m);
+#pragma unroll
+        for (int k = 0; k < 9; ++k) e[k] = ne[k];
+#pragma unroll
+        for (int k = 0; k < 8; ++k) o[k] = no[k];
+    }
+    // u = (E >> 32) + O <= p;  v = u + t_hi < 2p + 1;  one conditional subtraction
+    uint32_t u[8];
+    asm("add.cc.u32 %0, %8, %16;\n\t"
+        "addc.cc.u32 %1, %9, %17;\n\t"
+        "addc.cc.u32 %2, %10, %18;\n\t"
+        "addc.cc.u32 %3, %11, %19;\n\t"
+        "addc.cc.u32 %4, %12, %20;\n\t"
+        "addc.cc.u32 %5, %13, %21;\n\t"
+        "addc.cc.u32 %6, %14, %22;\n\t"
+        "addc.u32 %7, %15, %23;\n\t"
+        : "=&r"(u[0]), "=&r"(u[1]), "=&r"(u[2]), "=&r"(u[3]), "=&r"(u[4]), "=&r"(u[5]), "=&r"(u[6]), "=&r"(u[7])
+        : "r"(o[0]), "r"(o[1]), "r"(o[2]), "r"(o[3]), "r"(o[4]), "r"(o[5]), "r"(o[6]), "r"(o[7]),
+          "r"(e[1]), "r"(e[2]), "r"(e[3]), "r"(e[4]), "r"(e[5]), "r"(e[6]), "r"(e[7]), "r"(e[8]));
+    uint32_t v[8];
+    asm("add.cc.u32 %0, %8, %16;\n\t"
+        "addc.cc.u32 %1, %9, %17;\n\t"
+        "addc.cc.u32 %2, %10, %18;\n\t"
+        "addc.cc.u32 %3, %11, %19;\n\t"
+        "addc.cc.u32 %4, %12, %20;\n\t"
+        "addc.cc.u32 %5, %13, %21;\n\t"
+        "addc.cc.u32 %6, %14, %22;\n\t"
+        "addc.u32 %7, %15, %23;\n\t"
+        : "=&r"(v[0]), "=&r"(v[1]), "=&r"(v[2]), "=&r"(v[3]), "=&r"(v[4]), "=&r"(v[5]), "=&r"(v[6]), "=&r"(v[7])
+        : "r"(u[0]), "r"(u[1]), "r"(u[2]), "r"(u[3]), "r"(u[4]), "r"(u[5]), "r"(u[6]), "r"(u[7]),
+          "r"(t[8]), "r"(t[9]), "r"(t[10]), "r"(t[11]), "r"(t[12]), "r"(t[13]), "r"(t[14]), "r"(t[15]));
+    uint32_t s[8], borrow;
+    asm("sub.cc.u32 %0, %9, %17;\n\t"
+        "subc.cc.u32 %1, %10, %18;\n\t"
+        "subc.cc.u32 %2, %11, %19;\n\t"
+        "subc.cc.u32 %3, %12, %20;\n\t"
+        "subc.cc.u32 %4, %13, %21;\n\t"
+        "subc.cc.u32 %5, %14, %22;\n\t"
+        "subc.cc.u32 %6, %15, %23;\n\t"
+        "subc.cc.u32 %7, %16, %24;\n\t"
+        "subc.u32 %8, 0, 0;\n\t"
+        : "=&r"(s[0]), "=&r"(s[1]), "=&r"(s[2]), "=&r"(s[3]), "=&r"(s[4]), "=&r"(s[5]), "=&r"(s[6]), "=&r"(s[7]), "=&r"(borrow)
+        : "r"(v[0]), "r"(v[1]), "r"(v[2]), "r"(v[3]), "r"(v[4]), "r"(v[5]), "r"(v[6]), "r"(v[7]),
+          "r"(PRM::p(0)), "r"(PRM::p(1)), "r"(PRM::p(2)), "r"(PRM::p(3)), "r"(PRM::p(4)), "r"(PRM::p(5)), "r"(PRM::p(6)), "r"(PRM::p(7)));
+#pragma unroll
+    for (int k = 0; k < 8; ++k) r[k] = borrow ? v[k] : s[k];
 }
 
 template <class PRM>

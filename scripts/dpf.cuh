@@ -84,93 +84,6 @@ B2_D void dpf_mul_wide(uint32_t* t, const Dpf5& a, const Dpf5& b) {
     }
 }
 
-// parity swap of the reduction window + the next Montgomery factor + its odd row, one carry chain:
-//   ne0 = o0 + e[1];  m = ne0 * INV;  no[0..7] = (e[2..8], 0) + {p1,p3,p5,p7} * m + carry
-template <class PRM>
-B2_D void fold_reduce_shift8(uint32_t& ne0, uint32_t& m, uint32_t* no, const uint32_t* e, uint32_t o0) {
-    asm("add.cc.u32 %0, %10, %11;\n\t"
-        "mul.lo.u32 %9, %0, %23;\n\t"
-        "madc.lo.cc.u32 %1, %19, %9, %12;\n\t"
-        "madc.hi.cc.u32 %2, %19, %9, %13;\n\t"
-        "madc.lo.cc.u32 %3, %20, %9, %14;\n\t"
-        "madc.hi.cc.u32 %4, %20, %9, %15;\n\t"
-        "madc.lo.cc.u32 %5, %21, %9, %16;\n\t"
-        "madc.hi.cc.u32 %6, %21, %9, %17;\n\t"
-        "madc.lo.cc.u32 %7, %22, %9, %18;\n\t"
-        "madc.hi.u32 %8, %22, %9, 0;\n\t"
-        : "=&r"(ne0), "=&r"(no[0]), "=&r"(no[1]), "=&r"(no[2]), "=&r"(no[3]), "=&r"(no[4]),
-          "=&r"(no[5]), "=&r"(no[6]), "=&r"(no[7]), "=&r"(m)
-        : "r"(o0), "r"(e[1]), "r"(e[2]), "r"(e[3]), "r"(e[4]), "r"(e[5]), "r"(e[6]), "r"(e[7]),
-          "r"(e[8]), "r"(PRM::p(1)), "r"(PRM::p(3)), "r"(PRM::p(5)), "r"(PRM::p(7)), "r"(PRM::INV));
-}
-
-// r = t / 2^256 mod p for t = t_lo + 2^256 t_hi < p * 2^256  (r < p)
-template <class PRM>
-B2_D void mont_reduce_dev(uint32_t* r, const uint32_t* t) {
-    uint32_t e[9], o[8];
-#pragma unroll
-    for (int k = 0; k < 8; ++k) e[k] = t[k];
-    {
-        const uint32_t m = e[0] * PRM::INV;
-#pragma unroll
-        for (int j = 0; j < 8; j += 2)
-            asm("mul.lo.u32 %0, %2, %3;\n\tmul.hi.u32 %1, %2, %3;" : "=r"(o[j]), "=r"(o[j + 1]) : "r"(PRM::p(j + 1)), "r"(m));
-        mad_chain8_top<true>(e, PRM::p(0), PRM::p(2), PRM::p(4), PRM::p(6), m);
-    }
-#pragma unroll
-    for (int i = 1; i < 8; ++i) {
-        uint32_t ne[9], no[8], m;
-        fold_reduce_shift8<PRM>(ne[0], m, no, e, o[0]);
-#pragma unroll
-        for (int k = 1; k < 8; ++k) ne[k] = o[k];
-        mad_chain8_top<true>(ne, PRM::p(0), PRM::p(2), PRM::p(4), PRM::p(6), m);
-#pragma unroll
-        for (int k = 0; k < 9; ++k) e[k] = ne[k];
-#pragma unroll
-        for (int k = 0; k < 8; ++k) o[k] = no[k];
-    }
-    // u = (E >> 32) + O <= p;  v = u + t_hi < 2p + 1;  one conditional subtraction
-    uint32_t u[8];
-    asm("add.cc.u32 %0, %8, %16;\n\t"
-        "addc.cc.u32 %1, %9, %17;\n\t"
-        "addc.cc.u32 %2, %10, %18;\n\t"
-        "addc.cc.u32 %3, %11, %19;\n\t"
-        "addc.cc.u32 %4, %12, %20;\n\t"
-        "addc.cc.u32 %5, %13, %21;\n\t"
-        "addc.cc.u32 %6, %14, %22;\n\t"
-        "addc.u32 %7, %15, %23;\n\t"
-        : "=&r"(u[0]), "=&r"(u[1]), "=&r"(u[2]), "=&r"(u[3]), "=&r"(u[4]), "=&r"(u[5]), "=&r"(u[6]), "=&r"(u[7])
-        : "r"(o[0]), "r"(o[1]), "r"(o[2]), "r"(o[3]), "r"(o[4]), "r"(o[5]), "r"(o[6]), "r"(o[7]),
-          "r"(e[1]), "r"(e[2]), "r"(e[3]), "r"(e[4]), "r"(e[5]), "r"(e[6]), "r"(e[7]), "r"(e[8]));
-    uint32_t v[8];
-    asm("add.cc.u32 %0, %8, %16;\n\t"
-        "addc.cc.u32 %1, %9, %17;\n\t"
-        "addc.cc.u32 %2, %10, %18;\n\t"
-        "addc.cc.u32 %3, %11, %19;\n\t"
-        "addc.cc.u32 %4, %12, %20;\n\t"
-        "addc.cc.u32 %5, %13, %21;\n\t"
-        "addc.cc.u32 %6, %14, %22;\n\t"
-        "addc.u32 %7, %15, %23;\n\t"
-        : "=&r"(v[0]), "=&r"(v[1]), "=&r"(v[2]), "=&r"(v[3]), "=&r"(v[4]), "=&r"(v[5]), "=&r"(v[6]), "=&r"(v[7])
-        : "r"(u[0]), "r"(u[1]), "r"(u[2]), "r"(u[3]), "r"(u[4]), "r"(u[5]), "r"(u[6]), "r"(u[7]),
-          "r"(t[8]), "r"(t[9]), "r"(t[10]), "r"(t[11]), "r"(t[12]), "r"(t[13]), "r"(t[14]), "r"(t[15]));
-    uint32_t s[8], borrow;
-    asm("sub.cc.u32 %0, %9, %17;\n\t"
-        "subc.cc.u32 %1, %10, %18;\n\t"
-        "subc.cc.u32 %2, %11, %19;\n\t"
-        "subc.cc.u32 %3, %12, %20;\n\t"
-        "subc.cc.u32 %4, %13, %21;\n\t"
-        "subc.cc.u32 %5, %14, %22;\n\t"
-        "subc.cc.u32 %6, %15, %23;\n\t"
-        "subc.cc.u32 %7, %16, %24;\n\t"
-        "subc.u32 %8, 0, 0;\n\t"
-        : "=&r"(s[0]), "=&r"(s[1]), "=&r"(s[2]), "=&r"(s[3]), "=&r"(s[4]), "=&r"(s[5]), "=&r"(s[6]), "=&r"(s[7]), "=&r"(borrow)
-        : "r"(v[0]), "r"(v[1]), "r"(v[2]), "r"(v[3]), "r"(v[4]), "r"(v[5]), "r"(v[6]), "r"(v[7]),
-          "r"(PRM::p(0)), "r"(PRM::p(1)), "r"(PRM::p(2)), "r"(PRM::p(3)), "r"(PRM::p(4)), "r"(PRM::p(5)), "r"(PRM::p(6)), "r"(PRM::p(7)));
-#pragma unroll
-    for (int k = 0; k < 8; ++k) r[k] = borrow ? v[k] : s[k];
-}
-
 template <class PRM>
 B2_D void mont_mul_dpf_dev(uint32_t* r, const uint32_t* a, const uint32_t* b) {
     uint32_t t[16];

@@ -34,6 +34,7 @@ TOP_LIMB = 0x30644E72E131A029
 R_MOD = 0x30644E72E131A029B85045B68181585D2833E84879B9709143E1F593F0000001
 MAC32_PER_G1_POINT = 16 * 11 * 136   # 16 windows x (7M+4S) x 136 MAC32
 MAC32_PER_G2_POINT = 16 * 29 * 136
+MAC32_PER_G1_MADD = 8 * 136 + 2 * 64 + 72   # executed by XYZZ::add_mixed<Fp> (ec.cuh): 1288
 MAC32_PER_BUTTERFLY = 136
 
 
@@ -459,10 +460,11 @@ def report(args, world, peak, prof, stage, step_ms, e2e_s, clk, verified, inst, 
                 "launch_ms": g1_launch_ms, "points_per_launch": g1_pts,
                 "algorithmic_mac32_per_point": MAC32_PER_G1_POINT,
                 "algorithmic_model": "SURVEY 8(d): 16 windows x 11 Fp-mul x 136 MAC32 per point, whatever the kernel executes",
-                "executed_mac32_per_point": pk_info["a"]["windows"] * 10 * 136,
-                "executed_frac": g1_pts * pk_info["a"]["windows"] * 10 * 136 / (g1_launch_ms * 1e-3) / mac_peak,
+                "executed_mac32_per_point": pk_info["a"]["windows"] * MAC32_PER_G1_MADD,
+                "executed_frac": g1_pts * pk_info["a"]["windows"] * MAC32_PER_G1_MADD / (g1_launch_ms * 1e-3) / mac_peak,
                 "executed_model": f"{pk_info['a']['windows']} windows of c={pk_info['a']['c']} "
-                                  f"({'folded table' if pk_info['a']['folded'] else 'plain bases'}) x XYZZ mixed add 8M+2S x 136; "
+                                  f"({'folded table' if pk_info['a']['folded'] else 'plain bases'}) x XYZZ mixed add: 8 Montgomery products x 136 "
+                                  "+ one a*b - c*d with a shared reduction (2 x 64 + 72) = 1288 MAC32; "
                                   "frac > 1 means fewer field multiplications than the survey's model, not a faster pipe",
                 "peak_source": "measured in this run: register-resident Montgomery-product chains (b200_imad_peak)"}
     # NTT: north_star's HBM view (64 B per element per pass, 2 passes at <= 2^24) and the IMAD view

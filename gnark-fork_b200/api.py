@@ -123,6 +123,12 @@ def load_library():
         "b200_ntt_dist_phase": (i, [vp, i, u, vp, vp, vp, vp, u, u, i, i, i]),
         "b200_fr_mul_sub_dev": (i, [vp, i, vp, vp, vp, sz]),
         "b200_use_stream": (i, [vp, vp]),
+        "b200_fr_batch_inverse_dev": (i, [vp, i, vp, vp, sz]),
+        "b200_fr_prefix_product_dev": (i, [vp, i, vp, vp, sz]),
+        "b200_fr_poly_eval_dev": (i, [vp, i, vp, sz, vp, vp]),
+        "b200_fr_poly_div_linear_dev": (i, [vp, i, vp, sz, vp, vp]),
+        "b200_plonk_divide_by_xn_minus_one_dev": (i, [vp, i, vp, u, u, vp, vp]),
+        "b200_kzg_commit_dev": (i, [vp, vp, vp, sz, vp]),
         "b200_profile_start": (i, [vp]),
         "b200_profile_read": (i, [vp, C.POINTER(_Profile)]),
         "b200_groth16_finalize": (i, [C.POINTER(Groth16MsmOut), vp, vp, vp, vp, vp, vp, vp, vp, vp, vp]),
@@ -476,6 +482,30 @@ class Context:
 
     def fr_mul_sub_dev(self, a, b, c, n):
         self._check(self.lib.b200_fr_mul_sub_dev(self.h, BN254, _dev_ptr(a), _dev_ptr(b), _dev_ptr(c), n))
+
+    # -- PlonK building blocks on device vectors (plonk/bn254/prove.go)
+    def fr_batch_inverse_dev(self, src, dst, n):
+        self._check(self.lib.b200_fr_batch_inverse_dev(self.h, BN254, _dev_ptr(src), _dev_ptr(dst), n))
+
+    def fr_prefix_product_dev(self, src, dst, n):
+        self._check(self.lib.b200_fr_prefix_product_dev(self.h, BN254, _dev_ptr(src), _dev_ptr(dst), n))
+
+    def fr_poly_eval_dev(self, coeffs, n, x) -> np.ndarray:
+        out = np.empty(4, dtype=np.uint64)
+        self._check(self.lib.b200_fr_poly_eval_dev(self.h, BN254, _dev_ptr(coeffs), n, _ptr(_u64(x)), _ptr(out)))
+        return out
+
+    def fr_poly_div_linear_dev(self, coeffs, n, z, quotient):
+        self._check(self.lib.b200_fr_poly_div_linear_dev(self.h, BN254, _dev_ptr(coeffs), n, _ptr(_u64(z)), _dev_ptr(quotient)))
+
+    def plonk_divide_by_xn_minus_one_dev(self, vec, log_big, log_small, generator_big, coset_gen):
+        self._check(self.lib.b200_plonk_divide_by_xn_minus_one_dev(self.h, BN254, _dev_ptr(vec), log_big, log_small,
+                                                                   _ptr(_u64(generator_big)), _ptr(_u64(coset_gen))))
+
+    def kzg_commit_dev(self, srs: "Bases", coeffs, n) -> np.ndarray:
+        out = np.empty(8, dtype=np.uint64)
+        self._check(self.lib.b200_kzg_commit_dev(self.h, srs.h, _dev_ptr(coeffs), n, _ptr(out)))
+        return out
 
     # -- per-kernel-class device times (CUDA events on the launching stream)
     def profile_start(self):

@@ -3,6 +3,7 @@
 // No CPU fallback exists anywhere below this file: without a CUDA device b200_init fails.
 #include <cstdlib>
 #include "groth16_host.cuh"
+#include "poly_host.cuh"
 #include "misc_host.cuh"
 
 using namespace b200;
@@ -436,6 +437,82 @@ int b200_use_stream(b200_ctx* ctx, void* cuda_stream) {
     B2_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     ctx->stream = cuda_stream ? (cudaStream_t)cuda_stream : ctx->own_stream;
     return B200_OK;
+}
+
+// ---- PlonK building blocks -----------------------------------------------------------------
+int b200_fr_batch_inverse_dev(b200_ctx* ctx, int curve, const void* in_dev, void* out_dev, size_t n) {
+    B2_ENTER(ctx, curve);
+    if (n && (!in_dev || !out_dev)) return ctx->fail(B200_ERR_ARG, "null buffer");
+    if (in_dev == out_dev && n) return ctx->fail(B200_ERR_ARG, "batch inverse: in and out must not alias");
+    B2_TRY(fr_batch_inverse(ctx, (const Fr*)in_dev, (Fr*)out_dev, n));
+    B2_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return B200_OK;
+}
+int b200_fr_prefix_product_dev(b200_ctx* ctx, int curve, const void* in_dev, void* out_dev, size_t n) {
+    B2_ENTER(ctx, curve);
+    if (n && (!in_dev || !out_dev)) return ctx->fail(B200_ERR_ARG, "null buffer");
+    return fr_prefix_product(ctx, (const Fr*)in_dev, (Fr*)out_dev, n);
+}
+int b200_fr_poly_eval_dev(b200_ctx* ctx, int curve, const void* coeffs_dev, size_t n, const uint64_t* x, uint64_t* value) {
+    B2_ENTER(ctx, curve);
+    if (!x || !value || (n && !coeffs_dev)) return ctx->fail(B200_ERR_ARG, "null argument");
+    Fr xx, out;
+    memcpy(xx.l, x, 32);
+    B2_TRY(fr_poly_eval(ctx, (const Fr*)coeffs_dev, n, xx, &out));
+    memcpy(value, out.l, 32);
+    return B200_OK;
+}
+int b200_fr_poly_div_linear_dev(b200_ctx* ctx, int curve, const void* coeffs_dev, size_t n, const uint64_t* z, void* quotient_dev) {
+    B2_ENTER(ctx, curve);
+    if (!z || (n > 1 && (!coeffs_dev || !quotient_dev))) return ctx->fail(B200_ERR_ARG, "null argument");
+    if (coeffs_dev == quotient_dev && n > 1) return ctx->fail(B200_ERR_ARG, "division: coefficients and quotient must not alias");
+    Fr zz;
+    memcpy(zz.l, z, 32);
+    B2_TRY(fr_poly_div_linear(ctx, (const Fr*)coeffs_dev, n, zz, (Fr*)quotient_dev));
+    B2_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return B200_OK;
+}
+int b200_plonk_divide_by_xn_minus_one_dev(b200_ctx* ctx, int curve, void* vec_dev, unsigned log_big, unsigned log_small,
+                                          const uint64_t* generator_big, const uint64_t* coset_gen) {
+    B2_ENTER(ctx, curve);
+    if (!vec_dev || !generator_big || !coset_gen) return ctx->fail(B200_ERR_ARG, "null argument");
+    if (log_small > log_big || log_big - log_small > 3 || log_big > 27) return ctx->fail(B200_ERR_ARG, "rho = 2^(log_big - log_small) must be 1, 2, 4 or 8");
+    NttDomain* d;
+    B2_TRY(get_domain(ctx, log_big, generator_big, coset_gen, &d));
+    const Fr* t;
+    B2_TRY(ntt_domain_table(ctx, d, NttDomain::COSETINV_NAT, &t));
+    // evaluateXnMinusOneDomainBigCoset (prove.go:1253-1276): res[i] = (g * w^i)^n - 1, then inverted
+    const unsigned lr = log_big - log_small;
+    const uint32_t rho = 1u << lr;
+    const uint64_t n_small = (uint64_t)1 << log_small;
+    Fr res[8], f[8];
+    const Fr step = d->gen.pow_u64(n_small);
+    res[0] = d->coset.pow_u64(n_small);
+    for (uint32_t i = 1; i < rho; ++i) res[i] = res[i - 1] * step;
+    for (uint32_t i = 0; i < rho; ++i) {
+        const Fr v = res[i] - Fr::one();
+        if (v.is_zero()) return ctx->fail(B200_ERR_ARG, "X^n - 1 vanishes on the coset");
+        res[i] = v.inv();
+    }
+    // r[i] *= res[bitrev(i) mod rho]  (prove.go:1240-1245): bitrev(i) mod rho = the top lr bits of i, reversed
+    for (uint32_t k = 0; k < rho; ++k) {
+        uint32_t rev = 0;
+        for (unsigned b = 0; b < lr; ++b) rev |= ((k >> b) & 1u) << (lr - 1 - b);
+        f[k] = res[rev];
+    }
+    B2_TRY(fr_scale_cyclic(ctx, (Fr*)vec_dev, (size_t)1 << log_big, f, rho, log_big - lr));
+    // a.ToCanonical(domains[1]).ToRegular(): LagrangeCoset + BitReverse -> FFTInverse(DIT, OnCoset)
+    B2_TRY(ntt_gnark(ctx, d, (Fr*)vec_dev, 1, B200_DIT, 1));
+    B2_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return B200_OK;
+}
+int b200_kzg_commit_dev(b200_ctx* ctx, const b200_bases* srs, const void* coeffs_dev, size_t n, uint64_t* out_affine) {
+    B2_ENTER(ctx, B200_BN254);
+    if (!srs || !out_affine || (n && !coeffs_dev)) return ctx->fail(B200_ERR_ARG, "null argument");
+    if (srs->group != 1) return ctx->fail(B200_ERR_ARG, "the KZG SRS is a G1 base set");
+    uint64_t jac[12];
+    B2_TRY(b200_msm_dev(ctx, srs, coeffs_dev, n, jac, nullptr));
+    return b200_g1_jac_to_affine(jac, out_affine);
 }
 
 // ---- tuning knobs -------------------------------------------------------------------------

@@ -1,0 +1,253 @@
+// Fr vector / polynomial primitives of the PlonK prover:
+//   batch inversion        fr.BatchInvert (prove.go:1272, iop ratio construction)     zero stays zero
+//   prefix product         the grand-product accumulation of iop.BuildRatioCopyConstraint (prove.go:610-621)
+//   evaluation at a point  Polynomial.Evaluate / evaluateBlinded (prove.go:723,1118-1145,1300-1305)
+//   quotient by (X - z)    the synthetic division inside kzg.Open / BatchOpenSinglePoint (prove.go:646,823)
+//   cyclic scaling         divideByXMinusOne's product with the rho values of 1/(X^n - 1) (prove.go:1223-1250)
+// All are HBM-bound integer kernels: chunks per thread, a short recursion over chunk summaries.
+#include "poly_host.cuh"
+
+namespace b200 {
+
+__device__ __forceinline__ Fr pl_ld(const Fr* p) {
+    const uint4* q = reinterpret_cast<const uint4*>(p);
+    const uint4 a = q[0], b = q[1];
+    Fr f;
+    f.l[0] = a.x; f.l[1] = a.y; f.l[2] = a.z; f.l[3] = a.w;
+    f.l[4] = b.x; f.l[5] = b.y; f.l[6] = b.z; f.l[7] = b.w;
+    return f;
+}
+__device__ __forceinline__ void pl_st(Fr* p, const Fr& f) {
+    uint4* q = reinterpret_cast<uint4*>(p);
+    q[0] = make_uint4(f.l[0], f.l[1], f.l[2], f.l[3]);
+    q[1] = make_uint4(f.l[4], f.l[5], f.l[6], f.l[7]);
+}
+
+constexpr int PL_CHUNK = 32;      // elements per thread
+constexpr int PL_THREADS = 128;
+
+// ---- batch inversion: per-thread Montgomery trick over PL_CHUNK elements ----------------------
+__global__ void __launch_bounds__(PL_THREADS) batch_inverse_kernel(const Fr* __restrict__ in, Fr* __restrict__ out, size_t n) {
+    const size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const size_t lo = t * PL_CHUNK;
+    if (lo >= n) return;
+    const int cnt = (int)(n - lo < (size_t)PL_CHUNK ? n - lo : (size_t)PL_CHUNK);
+    // forward: out[i] = product of the non-zero elements before i
+    Fr acc = Fr::one();
+    for (int i = 0; i < cnt; ++i) {
+        const Fr x = pl_ld(in + lo + i);
+        pl_st(out + lo + i, acc);
+        if (!x.is_zero()) acc = acc * x;
+    }
+    Fr inv = acc.inv();
+    for (int i = cnt - 1; i >= 0; --i) {
+        const Fr x = pl_ld(in + lo + i);
+        if (x.is_zero()) { pl_st(out + lo + i, Fr::zero()); continue; }
+        const Fr pre = pl_ld(out + lo + i);
+        pl_st(out + lo + i, inv * pre);
+        inv = inv * x;
+    }
+}
+
+// ---- prefix product: chunk products, recursion over them, then the chunks again -----------------
+// pass 1: prod[t] = product of chunk t
+__global__ void __launch_bounds__(PL_THREADS) chunk_product_kernel(const Fr* __restrict__ in, size_t n, Fr* __restrict__ prod) {
+    const size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const size_t lo = t * PL_CHUNK;
+    if (lo >= n) return;
+    const int cnt = (int)(n - lo < (size_t)PL_CHUNK ? n - lo : (size_t)PL_CHUNK);
+    Fr acc = pl_ld(in + lo);
+    for (int i = 1; i < cnt; ++i) acc = acc * pl_ld(in + lo + i);
+    pl_st(prod + t, acc);
+}
+// pass 3: out[i] = carry[t] * in[lo] * ... * in[i]   (carry[t] = exclusive prefix of the chunk products; null for t = 0 only)
+__global__ void __launch_bounds__(PL_THREADS) chunk_scan_kernel(const Fr* __restrict__ in, size_t n, const Fr* __restrict__ incl_prev, Fr* __restrict__ out) {
+    const size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const size_t lo = t * PL_CHUNK;
+    if (lo >= n) return;
+    const int cnt = (int)(n - lo < (size_t)PL_CHUNK ? n - lo : (size_t)PL_CHUNK);
+    Fr acc = (t == 0 || incl_prev == nullptr) ? Fr::one() : pl_ld(incl_prev + t - 1);
+    for (int i = 0; i < cnt; ++i) {
+        acc = acc * pl_ld(in + lo + i);
+        pl_st(out + lo + i, acc);
+    }
+}
+
+// inclusive prefix product of n elements, in -> out (may alias); scratch: ceil(n / PL_CHUNK) * 2 elements at least
+static int prefix_product_rec(b200_ctx* ctx, const Fr* in, Fr* out, size_t n, Fr* scratch) {
+    const size_t chunks = (n + PL_CHUNK - 1) / PL_CHUNK;
+    const unsigned blocks = (unsigned)((chunks + PL_THREADS - 1) / PL_THREADS);
+    if (chunks == 1) {
+        chunk_scan_kernel<<<1, PL_THREADS, 0, ctx->stream>>>(in, n, nullptr, out);
+        B2_CUDA(ctx, cudaGetLastError());
+        ctx->n_launches += 1;
+        return B200_OK;
+    }
+    Fr* prod = scratch;                 // chunks elements, scanned in place
+    chunk_product_kernel<<<blocks, PL_THREADS, 0, ctx->stream>>>(in, n, prod);
+    B2_CUDA(ctx, cudaGetLastError());
+    B2_TRY(prefix_product_rec(ctx, prod, prod, chunks, scratch + chunks));
+    chunk_scan_kernel<<<blocks, PL_THREADS, 0, ctx->stream>>>(in, n, prod, out);
+    B2_CUDA(ctx, cudaGetLastError());
+    ctx->n_launches += 2;
+    return B200_OK;
+}
+
+size_t poly_scratch_elems(size_t n) {
+    size_t tot = 0, m = n;
+    while (m > 1) { m = (m + PL_CHUNK - 1) / PL_CHUNK; tot += m; }
+    return tot + 4;
+}
+
+int fr_batch_inverse(b200_ctx* ctx, const Fr* in, Fr* out, size_t n) {
+    if (n == 0) return B200_OK;
+    const size_t threads = (n + PL_CHUNK - 1) / PL_CHUNK;
+    batch_inverse_kernel<<<(unsigned)((threads + PL_THREADS - 1) / PL_THREADS), PL_THREADS, 0, ctx->stream>>>(in, out, n);
+    B2_CUDA(ctx, cudaGetLastError());
+    ctx->n_launches += 1;
+    return B200_OK;
+}
+
+int fr_prefix_product(b200_ctx* ctx, const Fr* in, Fr* out, size_t n) {
+    if (n == 0) return B200_OK;
+    DevBuf scratch;
+    B2_CUDA(ctx, scratch.alloc(poly_scratch_elems(n) * sizeof(Fr)));
+    B2_TRY(prefix_product_rec(ctx, in, out, n, scratch.as<Fr>()));
+    B2_CUDA(ctx, cudaStreamSynchronize(ctx->stream));   // scratch dies here
+    return B200_OK;
+}
+
+// ---- evaluation at a point: Horner per chunk, then the chunk values are a polynomial in x^PL_CHUNK -----
+__global__ void __launch_bounds__(PL_THREADS) chunk_horner_kernel(const Fr* __restrict__ coeffs, size_t n, const Fr x, Fr* __restrict__ part) {
+    const size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const size_t lo = t * PL_CHUNK;
+    if (lo >= n) return;
+    const int cnt = (int)(n - lo < (size_t)PL_CHUNK ? n - lo : (size_t)PL_CHUNK);
+    Fr acc = pl_ld(coeffs + lo + cnt - 1);
+    for (int i = cnt - 2; i >= 0; --i) acc = acc * x + pl_ld(coeffs + lo + i);
+    pl_st(part + t, acc);
+}
+
+int fr_poly_eval(b200_ctx* ctx, const Fr* coeffs, size_t n, const Fr& x, Fr* out_host) {
+    if (n == 0) { *out_host = Fr::zero(); return B200_OK; }
+    DevBuf scratch;
+    B2_CUDA(ctx, scratch.alloc(poly_scratch_elems(n) * sizeof(Fr)));
+    const Fr* cur = coeffs;
+    Fr* nxt = scratch.as<Fr>();
+    size_t m = n;
+    Fr xp = x;
+    while (m > 1) {
+        const size_t chunks = (m + PL_CHUNK - 1) / PL_CHUNK;
+        chunk_horner_kernel<<<(unsigned)((chunks + PL_THREADS - 1) / PL_THREADS), PL_THREADS, 0, ctx->stream>>>(cur, m, xp, nxt);
+        B2_CUDA(ctx, cudaGetLastError());
+        ctx->n_launches += 1;
+        xp = xp.pow_u64(PL_CHUNK);
+        cur = nxt;
+        nxt += chunks;
+        m = chunks;
+    }
+    B2_CUDA(ctx, cudaMemcpyAsync(out_host, cur, sizeof(Fr), cudaMemcpyDeviceToHost, ctx->stream));
+    B2_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return B200_OK;
+}
+
+// ---- quotient by (X - z): q[n-2] = a[n-1], q[i-1] = a[i] + z q[i]; remainder a[0] + z q[0] = p(z) ------
+// A chunk's outgoing carry is  carry_in * z^cnt + local,  local = Horner of the chunk at z: the carries
+// of all chunks are themselves a quotient recursion over the chunk Horner values with z^PL_CHUNK.
+// pass A (chunk_horner_kernel): local[t].   pass B (recursion): carry_in[t] = value entering chunk t from above.
+// pass C: replay each chunk from its carry and write the quotient coefficients.
+__global__ void __launch_bounds__(PL_THREADS) chunk_divide_kernel(const Fr* __restrict__ a, size_t n, const Fr z, const Fr* __restrict__ carry_in,
+                                                                  Fr* __restrict__ q) {
+    const size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const size_t lo = t * PL_CHUNK;
+    if (lo >= n) return;
+    const int cnt = (int)(n - lo < (size_t)PL_CHUNK ? n - lo : (size_t)PL_CHUNK);
+    // acc = the value  a[i] + z * (acc of i+1)  running downwards; q[i-1] = acc at i
+    Fr acc = carry_in ? pl_ld(carry_in + t) : Fr::zero();
+    for (int i = cnt - 1; i >= 0; --i) {
+        acc = acc * z + pl_ld(a + lo + i);
+        if (lo + i >= 1) pl_st(q + lo + i - 1, acc);
+    }
+}
+// carries of a level: carry_in[t] for chunk t = Horner state after all chunks above t.
+// Given local[] (length m) this is again "divide local by (X - zc)" with the roles shifted by one:
+//   carry_in[m-1] = 0, carry_in[t] = carry_in[t+1] * zc + local[t+1]            (zc = z^PL_CHUNK)
+__global__ void __launch_bounds__(PL_THREADS) chunk_carry_kernel(const Fr* __restrict__ local, size_t m, const Fr zc, const Fr* __restrict__ carry_up,
+                                                                 Fr* __restrict__ carry) {
+    // thread t handles positions [lo, lo + cnt) of `local`; carry_up[t] enters from above the chunk
+    const size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const size_t lo = t * PL_CHUNK;
+    if (lo >= m) return;
+    const int cnt = (int)(m - lo < (size_t)PL_CHUNK ? m - lo : (size_t)PL_CHUNK);
+    Fr acc = carry_up ? pl_ld(carry_up + t) : Fr::zero();
+    for (int i = cnt - 1; i >= 0; --i) {
+        pl_st(carry + lo + i, acc);            // value entering element lo + i from above
+        acc = acc * zc + pl_ld(local + lo + i);
+    }
+}
+
+// carry[t] for every chunk of a level with `m` chunk values local[0..m), chunk factor zc
+static int divide_carries(b200_ctx* ctx, const Fr* local, size_t m, const Fr& zc, Fr* carry, Fr* scratch) {
+    const size_t chunks = (m + PL_CHUNK - 1) / PL_CHUNK;
+    const unsigned blocks = (unsigned)((chunks + PL_THREADS - 1) / PL_THREADS);
+    if (chunks == 1) {
+        chunk_carry_kernel<<<1, PL_THREADS, 0, ctx->stream>>>(local, m, zc, nullptr, carry);
+        B2_CUDA(ctx, cudaGetLastError());
+        ctx->n_launches += 1;
+        return B200_OK;
+    }
+    Fr* loc2 = scratch;                    // chunks values: Horner of each chunk of `local` at zc
+    Fr* car2 = scratch + chunks;           // chunks carries
+    chunk_horner_kernel<<<blocks, PL_THREADS, 0, ctx->stream>>>(local, m, zc, loc2);
+    B2_CUDA(ctx, cudaGetLastError());
+    B2_TRY(divide_carries(ctx, loc2, chunks, zc.pow_u64(PL_CHUNK), car2, scratch + 2 * chunks));
+    chunk_carry_kernel<<<blocks, PL_THREADS, 0, ctx->stream>>>(local, m, zc, car2, carry);
+    B2_CUDA(ctx, cudaGetLastError());
+    ctx->n_launches += 2;
+    return B200_OK;
+}
+
+int fr_poly_div_linear(b200_ctx* ctx, const Fr* a, size_t n, const Fr& z, Fr* q) {
+    if (n <= 1) return B200_OK;   // constant: empty quotient
+    const size_t chunks = (n + PL_CHUNK - 1) / PL_CHUNK;
+    const unsigned blocks = (unsigned)((chunks + PL_THREADS - 1) / PL_THREADS);
+    if (chunks == 1) {
+        chunk_divide_kernel<<<1, PL_THREADS, 0, ctx->stream>>>(a, n, z, nullptr, q);
+        B2_CUDA(ctx, cudaGetLastError());
+        ctx->n_launches += 1;
+        return B200_OK;
+    }
+    DevBuf scratch;
+    B2_CUDA(ctx, scratch.alloc((3 * poly_scratch_elems(n) + 8) * sizeof(Fr)));
+    Fr* local = scratch.as<Fr>();
+    Fr* carry = local + chunks;
+    chunk_horner_kernel<<<blocks, PL_THREADS, 0, ctx->stream>>>(a, n, z, local);
+    B2_CUDA(ctx, cudaGetLastError());
+    B2_TRY(divide_carries(ctx, local, chunks, z.pow_u64(PL_CHUNK), carry, carry + chunks));
+    chunk_divide_kernel<<<blocks, PL_THREADS, 0, ctx->stream>>>(a, n, z, carry, q);
+    B2_CUDA(ctx, cudaGetLastError());
+    ctx->n_launches += 2;
+    B2_CUDA(ctx, cudaStreamSynchronize(ctx->stream));   // scratch dies here
+    return B200_OK;
+}
+
+// ---- cyclic scaling: v[i] *= f[(i >> shift) mod count]  (count <= 8 factors) ----------------------
+struct CycFactors { Fr f[8]; };
+__global__ void scale_cyclic_kernel(Fr* __restrict__ v, size_t n, const CycFactors fac, uint32_t shift, uint32_t mask) {
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    pl_st(v + i, pl_ld(v + i) * fac.f[(uint32_t)(i >> shift) & mask]);
+}
+
+int fr_scale_cyclic(b200_ctx* ctx, Fr* v, size_t n, const Fr* factors, uint32_t count, uint32_t shift) {
+    if (count == 0 || count > 8 || (count & (count - 1))) return ctx->fail(B200_ERR_ARG, "factor count must be 1, 2, 4 or 8");
+    CycFactors fac;
+    for (uint32_t i = 0; i < 8; ++i) fac.f[i] = factors[i % count];
+    const int bs = 256;
+    scale_cyclic_kernel<<<(unsigned)((n + bs - 1) / bs), bs, 0, ctx->stream>>>(v, n, fac, shift, count - 1);
+    B2_CUDA(ctx, cudaGetLastError());
+    ctx->n_launches += 1;
+    return B200_OK;
+}
+
+}  // namespace b200

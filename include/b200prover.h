@@ -229,6 +229,29 @@ typedef struct b200_timings {
     float h2d_ms, compute_h_ms, msm_a_ms, msm_b1_ms, msm_k_ms, msm_z_ms, msm_b2_ms, total_ms;
 } b200_timings;
 
+/* ---- PlonK building blocks on device vectors ---------
+ * Fr elements as everywhere: 4 x u64 Montgomery limbs.  All calls return after completion. */
+/* out[i] = 1 / in[i], and 0 where in[i] = 0 (fr.BatchInvert; plonk/bn254/prove.go:1272).  No aliasing. */
+int b200_fr_batch_inverse_dev(b200_ctx *ctx, int curve, const void *in_dev, void *out_dev, size_t n);
+/* out[i] = in[0] * ... * in[i]: the accumulation of the copy-constraint ratio Z
+ * (iop.BuildRatioCopyConstraint, prove.go:610-621).  in may alias out. */
+int b200_fr_prefix_product_dev(b200_ctx *ctx, int curve, const void *in_dev, void *out_dev, size_t n);
+/* value = sum coeffs[i] x^i (Polynomial.Evaluate, prove.go:723,1127,1300-1305). */
+int b200_fr_poly_eval_dev(b200_ctx *ctx, int curve, const void *coeffs_dev, size_t n, const uint64_t *x, uint64_t *value);
+/* quotient_dev[0..n-2]: p(X) = q(X) (X - z) + p(z) -- the synthetic division of kzg.Open /
+ * kzg.BatchOpenSinglePoint (prove.go:646,823).  No aliasing. */
+int b200_fr_poly_div_linear_dev(b200_ctx *ctx, int curve, const void *coeffs_dev, size_t n, const uint64_t *z,
+                                void *quotient_dev);
+/* divideByXMinusOne (prove.go:1223-1250): vec (2^log_big elements, basis LagrangeCoset, layout
+ * BitReverse) is multiplied by 1 / (X^(2^log_small) - 1) on the big coset -- rho = 2^(log_big -
+ * log_small) distinct values, evaluateXnMinusOneDomainBigCoset prove.go:1253-1276 -- and taken to
+ * Canonical / Regular with the inverse coset transform of the big domain, in place. */
+int b200_plonk_divide_by_xn_minus_one_dev(b200_ctx *ctx, int curve, void *vec_dev, unsigned log_big, unsigned log_small,
+                                          const uint64_t *generator_big, const uint64_t *coset_gen);
+/* kzg.Commit (prove.go:494,1203-1213): MSM of n coefficients against a resident SRS, affine result
+ * (8 u64; (0,0) = infinity). */
+int b200_kzg_commit_dev(b200_ctx *ctx, const b200_bases *srs, const void *coeffs_dev, size_t n, uint64_t *out_affine);
+
 /* ---- multi-GPU computeH (NTT with one exchange step per transform) -------------
  * One process per GPU holds n >> log_ranks elements of each vector in two device buffers (`data`,
  * `tmp`).  A transform is [local phase] -> all-to-all between the ranks (the caller's: NCCL, or

@@ -41,6 +41,14 @@ class _MsmSetInfo(C.Structure):
                 "windows": int(self.windows), "folded": int(self.folded)}
 
 
+class _PlonkRowsDesc(C.Structure):
+    """b200_plonk_rows_desc."""
+    _fields_ = [("x", C.c_void_p * 15), ("qci", C.c_void_p * 16), ("nb_bsb", C.c_uint), ("log_n", C.c_uint),
+                ("log_big", C.c_uint), ("coset_index", C.c_uint), ("generator_small", C.c_void_p),
+                ("beta", C.c_uint64 * 4), ("gamma", C.c_uint64 * 4), ("alpha", C.c_uint64 * 4), ("cs", C.c_uint64 * 4),
+                ("bl", (C.c_uint64 * 4) * 2), ("br", (C.c_uint64 * 4) * 2), ("bo", (C.c_uint64 * 4) * 2), ("bz", (C.c_uint64 * 4) * 3)]
+
+
 class Groth16MsmOut(C.Structure):
     """b200_groth16_out: the five MultiExp results before the fix-ups (prove.go:201-290)."""
     _fields_ = [("ar", C.c_uint64 * 12), ("bs1", C.c_uint64 * 12), ("krs", C.c_uint64 * 12),
@@ -129,6 +137,8 @@ def load_library():
         "b200_fr_poly_div_linear_dev": (i, [vp, i, vp, sz, vp, vp]),
         "b200_plonk_divide_by_xn_minus_one_dev": (i, [vp, i, vp, u, u, vp, vp]),
         "b200_kzg_commit_dev": (i, [vp, vp, vp, sz, vp]),
+        "b200_plonk_build_ratio_dev": (i, [vp, i, vp, vp, vp, vp, vp, vp, u, vp, vp, vp]),
+        "b200_plonk_quotient_rows_dev": (i, [vp, i, C.POINTER(_PlonkRowsDesc), vp]),
         "b200_profile_start": (i, [vp]),
         "b200_profile_read": (i, [vp, C.POINTER(_Profile)]),
         "b200_groth16_finalize": (i, [C.POINTER(Groth16MsmOut), vp, vp, vp, vp, vp, vp, vp, vp, vp, vp]),
@@ -501,6 +511,32 @@ class Context:
     def plonk_divide_by_xn_minus_one_dev(self, vec, log_big, log_small, generator_big, coset_gen):
         self._check(self.lib.b200_plonk_divide_by_xn_minus_one_dev(self.h, BN254, _dev_ptr(vec), log_big, log_small,
                                                                    _ptr(_u64(generator_big)), _ptr(_u64(coset_gen))))
+
+    def plonk_build_ratio_dev(self, l, r, o, perm, beta, gamma, log_n, generator, coset_gen, z_out):
+        """Z of the copy constraints (prove.go:610-621); perm: device int64[3 n]."""
+        self._check(self.lib.b200_plonk_build_ratio_dev(self.h, BN254, _dev_ptr(l), _dev_ptr(r), _dev_ptr(o), _dev_ptr(perm),
+                                                        _ptr(_u64(beta)), _ptr(_u64(gamma)), log_n, _ptr(_u64(generator)),
+                                                        _ptr(_u64(coset_gen)), _dev_ptr(z_out)))
+
+    def plonk_quotient_rows_dev(self, x, qci, log_n, log_big, coset_index, generator_small, beta, gamma, alpha, cs,
+                                bl, br, bo, bz, cres):
+        """One coset of computeNumerator's row evaluation (prove.go:837-1044).  x: 15 device vectors
+        indexed by prove.go's ids (x[4] may be None); qci: list of device vectors [Qcp_0, Pi_0, ...]."""
+        d = _PlonkRowsDesc()
+        for k in range(15):
+            d.x[k] = None if x[k] is None else _dev_ptr(x[k]).value
+        for k, v in enumerate(qci):
+            d.qci[k] = _dev_ptr(v).value
+        d.nb_bsb, d.log_n, d.log_big, d.coset_index = len(qci) // 2, log_n, log_big, coset_index
+        gs = _u64(generator_small)
+        d.generator_small = gs.ctypes.data
+        for name, val in (("beta", beta), ("gamma", gamma), ("alpha", alpha), ("cs", cs)):
+            getattr(d, name)[:] = [int(v) for v in _u64(val).reshape(4)]
+        for name, val in (("bl", bl), ("br", br), ("bo", bo), ("bz", bz)):
+            arr = _u64(val).reshape(-1, 4)
+            for j in range(arr.shape[0]):
+                getattr(d, name)[j][:] = [int(v) for v in arr[j]]
+        self._check(self.lib.b200_plonk_quotient_rows_dev(self.h, BN254, C.byref(d), _dev_ptr(cres)))
 
     def kzg_commit_dev(self, srs: "Bases", coeffs, n) -> np.ndarray:
         out = np.empty(8, dtype=np.uint64)

@@ -515,6 +515,55 @@ int b200_kzg_commit_dev(b200_ctx* ctx, const b200_bases* srs, const void* coeffs
     return b200_g1_jac_to_affine(jac, out_affine);
 }
 
+int b200_plonk_build_ratio_dev(b200_ctx* ctx, int curve, const void* l_dev, const void* r_dev, const void* o_dev,
+                               const void* perm_dev, const uint64_t* beta, const uint64_t* gamma, unsigned log_n,
+                               const uint64_t* generator, const uint64_t* coset_gen, void* z_out_dev) {
+    B2_ENTER(ctx, curve);
+    if (!l_dev || !r_dev || !o_dev || !perm_dev || !beta || !gamma || !generator || !coset_gen || !z_out_dev)
+        return ctx->fail(B200_ERR_ARG, "null argument");
+    if (log_n > 27) return ctx->fail(B200_ERR_UNSUPPORTED, "domain above 2^27");
+    NttDomain* d;
+    B2_TRY(get_domain(ctx, log_n, generator, coset_gen, &d));
+    Fr b, g;
+    memcpy(b.l, beta, 32);
+    memcpy(g.l, gamma, 32);
+    return plonk_build_ratio(ctx, d, (const Fr*)l_dev, (const Fr*)r_dev, (const Fr*)o_dev, (const int64_t*)perm_dev, b, g, (Fr*)z_out_dev);
+}
+int b200_plonk_quotient_rows_dev(b200_ctx* ctx, int curve, const b200_plonk_rows_desc* desc, void* cres_dev) {
+    B2_ENTER(ctx, curve);
+    if (!desc || !cres_dev || !desc->generator_small) return ctx->fail(B200_ERR_ARG, "null argument");
+    if (desc->nb_bsb > 8) return ctx->fail(B200_ERR_UNSUPPORTED, "more than 8 BSB22 commitments");
+    if (desc->log_big < desc->log_n || desc->log_big > 27) return ctx->fail(B200_ERR_ARG, "bad domain sizes");
+    PlonkRowArgs a;
+    for (int k = 0; k < 15; ++k) {
+        if (k != PID_ZS && !desc->x[k]) return ctx->fail(B200_ERR_ARG, "null polynomial");
+        a.x[k] = (const Fr*)desc->x[k];
+    }
+    for (unsigned k = 0; k < 16; ++k) {
+        if (k < 2 * desc->nb_bsb && !desc->qci[k]) return ctx->fail(B200_ERR_ARG, "null BSB22 polynomial");
+        a.qci[k] = (const Fr*)desc->qci[k];
+    }
+    a.nb_bsb = desc->nb_bsb;
+    memcpy(a.beta.l, desc->beta, 32); memcpy(a.gamma.l, desc->gamma, 32); memcpy(a.alpha.l, desc->alpha, 32);
+    memcpy(a.cs.l, desc->cs, 32);
+    a.css = a.cs * a.cs;
+    for (int k = 0; k < 2; ++k) { memcpy(a.bl[k].l, desc->bl[k], 32); memcpy(a.br[k].l, desc->br[k], 32); memcpy(a.bo[k].l, desc->bo[k], 32); }
+    for (int k = 0; k < 3; ++k) memcpy(a.bz[k].l, desc->bz[k], 32);
+    NttDomain* d;
+    B2_TRY(get_domain(ctx, desc->log_n, desc->generator_small, nullptr, &d));
+    a.tw = d->tw_fwd.as<Fr>();
+    a.n = 1u << desc->log_n;
+    a.log_big = desc->log_big;
+    a.rho = 1u << (desc->log_big - desc->log_n);
+    a.coset_index = desc->coset_index;
+    if (a.coset_index >= a.rho) return ctx->fail(B200_ERR_ARG, "coset index out of range");
+    if (a.log_big == 0) return ctx->fail(B200_ERR_ARG, "big domain of one element");
+    a.cres = (Fr*)cres_dev;
+    B2_TRY(plonk_quotient_rows(ctx, a));
+    B2_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return B200_OK;
+}
+
 // ---- tuning knobs -------------------------------------------------------------------------
 int b200_set_option(b200_ctx* ctx, const char* key, long value) {
     if (!ctx || !key) return B200_ERR_ARG;

@@ -250,4 +250,111 @@ int fr_scale_cyclic(b200_ctx* ctx, Fr* v, size_t n, const Fr* factors, uint32_t 
     return B200_OK;
 }
 
+// ---------------------------------------------------------------------------------------
+// PlonK row kernels.  w^i of the small domain comes from the NTT twiddle table (w^j, j < n/2):
+// w^i = -w^(i - n/2) in the upper half.
+// ---------------------------------------------------------------------------------------
+__device__ __forceinline__ Fr omega_pow(const Fr* __restrict__ tw, uint32_t i, uint32_t half) {
+    if (half == 0) return Fr::one();                      // n = 1
+    return i < half ? pl_ld(tw + i) : pl_ld(tw + (i - half)).neg();
+}
+
+// copy-constraint ratio (iop.BuildRatioCopyConstraint, called at prove.go:610-621), entries in
+// Lagrange / Regular form:  num[0] = den[0] = 1 and for i < n - 1
+//   num[i+1] = prod_j (beta * id[j n + i] + gamma + w_j[i]),  den[i+1] = prod_j (beta * id[perm[j n + i]] + gamma + w_j[i])
+// with id = [w^i | g w^i | g^2 w^i].  Z is then prefix(num) / prefix(den).
+__global__ void plonk_ratio_terms_kernel(const Fr* __restrict__ l, const Fr* __restrict__ r, const Fr* __restrict__ o,
+                                         const int64_t* __restrict__ perm, const Fr* __restrict__ tw, uint32_t n, const Fr beta,
+                                         const Fr gamma, const Fr g, const Fr g2, Fr* __restrict__ num, Fr* __restrict__ den) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    if (i == n - 1) { pl_st(num, Fr::one()); pl_st(den, Fr::one()); return; }   // slot 0
+    const uint32_t half = n >> 1;
+    const Fr* w[3] = {l, r, o};
+    const Fr shift[3] = {Fr::one(), g, g2};
+    Fr a = Fr::one(), b = Fr::one();
+#pragma unroll
+    for (int j = 0; j < 3; ++j) {
+        const Fr v = pl_ld(w[j] + i) + gamma;
+        Fr id = omega_pow(tw, i, half);
+        if (j) id = id * shift[j];
+        a = a * (beta * id + v);
+        const uint64_t k = (uint64_t)perm[(size_t)j * n + i];
+        const uint32_t kc = (uint32_t)(k / n), ki = (uint32_t)(k % n);
+        Fr idp = omega_pow(tw, ki, half);
+        if (kc) idp = idp * shift[kc];
+        b = b * (beta * idp + v);
+    }
+    pl_st(num + i + 1, a);
+    pl_st(den + i + 1, b);
+}
+
+__global__ void vec_mul_inplace_kernel(Fr* __restrict__ a, const Fr* __restrict__ b, size_t n) {
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    pl_st(a + i, pl_ld(a + i) * pl_ld(b + i));
+}
+
+int plonk_build_ratio(b200_ctx* ctx, NttDomain* d, const Fr* l, const Fr* r, const Fr* o, const int64_t* perm, const Fr& beta,
+                      const Fr& gamma, Fr* z_out) {
+    const size_t n = d->n();
+    DevBuf den, inv;
+    B2_CUDA(ctx, den.alloc(n * sizeof(Fr)));
+    B2_CUDA(ctx, inv.alloc(n * sizeof(Fr)));
+    const int bs = 128;
+    plonk_ratio_terms_kernel<<<(unsigned)((n + bs - 1) / bs), bs, 0, ctx->stream>>>(l, r, o, perm, d->tw_fwd.as<Fr>(), (uint32_t)n, beta, gamma,
+                                                                                  d->coset, d->coset * d->coset, z_out, den.as<Fr>());
+    B2_CUDA(ctx, cudaGetLastError());
+    ctx->n_launches += 1;
+    B2_TRY(fr_prefix_product(ctx, z_out, z_out, n));
+    B2_TRY(fr_prefix_product(ctx, den.as<Fr>(), den.as<Fr>(), n));
+    B2_TRY(fr_batch_inverse(ctx, den.as<Fr>(), inv.as<Fr>(), n));
+    vec_mul_inplace_kernel<<<(unsigned)((n + 255) / 256), 256, 0, ctx->stream>>>(z_out, inv.as<Fr>(), n);
+    B2_CUDA(ctx, cudaGetLastError());
+    ctx->n_launches += 1;
+    B2_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return B200_OK;
+}
+
+// Quotient numerator rows (computeNumerator / allConstraints, prove.go:837-1044): for row i of the
+// current coset, with every input in Lagrange / Regular form on that coset,
+//   blind L, R, O, Z with the (pre-scaled) blinding polynomials at w^i, ZS = Z shifted by one row,
+//   gate + alpha * ordering + alpha^2 * (Z - 1) * LOne,
+// scattered to cres[bitrev_{log_big}(rho * i + coset_index)] (prove.go:1029-1035).
+__global__ void __launch_bounds__(128) plonk_quotient_rows_kernel(const PlonkRowArgs a) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= a.n) return;
+    const uint32_t half = a.n >> 1;
+    const Fr wi = omega_pow(a.tw, i, half);
+    const uint32_t i1 = i + 1 == a.n ? 0u : i + 1;
+    const Fr wi1 = omega_pow(a.tw, i1, half);
+    const Fr L = pl_ld(a.x[PID_L] + i) + (a.bl[1] * wi + a.bl[0]);
+    const Fr R = pl_ld(a.x[PID_R] + i) + (a.br[1] * wi + a.br[0]);
+    const Fr O = pl_ld(a.x[PID_O] + i) + (a.bo[1] * wi + a.bo[0]);
+    const Fr Z = pl_ld(a.x[PID_Z] + i) + ((a.bz[2] * wi + a.bz[1]) * wi + a.bz[0]);
+    const Fr ZS = pl_ld(a.x[PID_Z] + i1) + ((a.bz[2] * wi1 + a.bz[1]) * wi1 + a.bz[0]);
+    // gate (prove.go:850-867)
+    Fr gate = pl_ld(a.x[PID_QL] + i) * L + pl_ld(a.x[PID_QR] + i) * R + pl_ld(a.x[PID_QM] + i) * L * R +
+              pl_ld(a.x[PID_QO] + i) * O + pl_ld(a.x[PID_QK] + i);
+    for (uint32_t k = 0; k < a.nb_bsb; ++k) gate = gate + pl_ld(a.qci[2 * k] + i) * pl_ld(a.qci[2 * k + 1] + i);
+    // ordering (prove.go:873-891)
+    const Fr id = pl_ld(a.x[PID_ID] + i);
+    const Fr r = (a.gamma + L + id) * (id * a.cs + R + a.gamma) * (id * a.css + O + a.gamma) * Z;
+    const Fr l = (pl_ld(a.x[PID_S1] + i) * a.beta + L + a.gamma) * (pl_ld(a.x[PID_S2] + i) * a.beta + R + a.gamma) *
+                 (pl_ld(a.x[PID_S3] + i) * a.beta + O + a.gamma) * ZS;
+    // local ratio (prove.go:893-900) and the alpha combination (prove.go:952)
+    Fr c = (Z - Fr::one()) * pl_ld(a.x[PID_LONE] + i);
+    c = (c * a.alpha + (l - r)) * a.alpha + gate;
+    const uint32_t pos = __brev(a.rho * i + a.coset_index) >> (32 - a.log_big);
+    pl_st(a.cres + pos, c);
+}
+
+int plonk_quotient_rows(b200_ctx* ctx, PlonkRowArgs& args) {
+    const int bs = 128;
+    plonk_quotient_rows_kernel<<<(args.n + bs - 1) / bs, bs, 0, ctx->stream>>>(args);
+    B2_CUDA(ctx, cudaGetLastError());
+    ctx->n_launches += 1;
+    return B200_OK;
+}
+
 }  // namespace b200

@@ -13,4 +13,21 @@ int fr_poly_eval(b200_ctx* ctx, const Fr* coeffs, size_t n, const Fr& x, Fr* out
 int fr_poly_div_linear(b200_ctx* ctx, const Fr* a, size_t n, const Fr& z, Fr* q);
 // v[i] *= factors[(i >> shift) mod count], count in {1, 2, 4, 8}
 int fr_scale_cyclic(b200_ctx* ctx, Fr* v, size_t n, const Fr* factors, uint32_t count, uint32_t shift);
+// Z of the copy constraints (Lagrange / Regular): iop.BuildRatioCopyConstraint over l, r, o with
+// the permutation `perm` (3 n int64 on the device), domain d (generator w, shift g = d->coset)
+int plonk_build_ratio(b200_ctx* ctx, NttDomain* d, const Fr* l, const Fr* r, const Fr* o, const int64_t* perm, const Fr& beta,
+                      const Fr& gamma, Fr* z_out);
+struct PlonkRowArgs {
+    const Fr* x[15];          // id_L .. id_LOne (prove.go:60-77); x[id_ZS] is not read
+    const Fr* qci[16];        // [Qcp_0, Pi_0, Qcp_1, Pi_1, ...]
+    uint32_t nb_bsb;
+    Fr beta, gamma, alpha, cs, css;
+    Fr bl[2], br[2], bo[2], bz[3];   // blinding polynomials, coefficients as scaled for this coset (prove.go:985-993)
+    const Fr* tw;             // w^j, j < n/2, of the small domain
+    uint32_t n, log_big, rho, coset_index;
+    Fr* cres;
+};
+enum { PID_L = 0, PID_R, PID_O, PID_Z, PID_ZS, PID_QL, PID_QR, PID_QM, PID_QO, PID_QK, PID_S1, PID_S2, PID_S3, PID_ID, PID_LONE };
+
+int plonk_quotient_rows(b200_ctx* ctx, PlonkRowArgs& args);
 }  // namespace b200

@@ -252,6 +252,30 @@ int b200_plonk_divide_by_xn_minus_one_dev(b200_ctx *ctx, int curve, void *vec_de
  * (8 u64; (0,0) = infinity). */
 int b200_kzg_commit_dev(b200_ctx *ctx, const b200_bases *srs, const void *coeffs_dev, size_t n, uint64_t *out_affine);
 
+/* Z of the copy constraints (iop.BuildRatioCopyConstraint, prove.go:610-621): l, r, o in Lagrange /
+ * Regular form (2^log_n elements each), perm_dev = the 3 * 2^log_n int64 permutation of the trace
+ * (pk.trace.S), generator = Domain[0].Generator, coset_gen = Domain[0].FrMultiplicativeGen.
+ * z_out_dev[0] = 1, z_out_dev[i+1] = z_out_dev[i] * num_i / den_i. */
+int b200_plonk_build_ratio_dev(b200_ctx *ctx, int curve, const void *l_dev, const void *r_dev, const void *o_dev,
+                               const void *perm_dev, const uint64_t *beta, const uint64_t *gamma, unsigned log_n,
+                               const uint64_t *generator, const uint64_t *coset_gen, void *z_out_dev);
+/* One coset of the quotient numerator (computeNumerator's iop.Evaluate(allConstraints, ...),
+ * prove.go:837-1044).  x[k]: the polynomial with prove.go's id k (id_L = 0 ... id_LOne = 14; id_ZS = 4 is
+ * not read: ZS is Z shifted by one row) in Lagrange / Regular form on the current coset; qci: the
+ * BSB22 pairs [Qcp_0, Pi_0, ...]; bl/br/bo/bz: the blinding polynomials' coefficients as scaled for
+ * this coset (prove.go:985-993); cs = Domain[1].FrMultiplicativeGen.  Row i goes to
+ * cres_dev[bitrev_{log_big}(rho * i + coset_index)], rho = 2^(log_big - log_n). */
+typedef struct b200_plonk_rows_desc {
+    const void *x[15];
+    const void *qci[16];
+    unsigned nb_bsb;
+    unsigned log_n, log_big, coset_index;
+    const uint64_t *generator_small; /* Domain[0].Generator */
+    uint64_t beta[4], gamma[4], alpha[4], cs[4];
+    uint64_t bl[2][4], br[2][4], bo[2][4], bz[3][4];
+} b200_plonk_rows_desc;
+int b200_plonk_quotient_rows_dev(b200_ctx *ctx, int curve, const b200_plonk_rows_desc *desc, void *cres_dev);
+
 /* ---- multi-GPU computeH (NTT with one exchange step per transform) -------------
  * One process per GPU holds n >> log_ranks elements of each vector in two device buffers (`data`,
  * `tmp`).  A transform is [local phase] -> all-to-all between the ranks (the caller's: NCCL, or

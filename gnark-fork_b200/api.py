@@ -49,6 +49,30 @@ class _PlonkRowsDesc(C.Structure):
                 ("bl", (C.c_uint64 * 4) * 2), ("br", (C.c_uint64 * 4) * 2), ("bo", (C.c_uint64 * 4) * 2), ("bz", (C.c_uint64 * 4) * 3)]
 
 
+class _PlonkPkDesc(C.Structure):
+    """b200_plonk_pk_desc."""
+    _fields_ = [("log_n", C.c_uint), ("log_big", C.c_uint), ("generator", C.c_void_p), ("generator_big", C.c_void_p),
+                ("coset_gen", C.c_void_p), ("ql", C.c_void_p), ("qr", C.c_void_p), ("qm", C.c_void_p), ("qo", C.c_void_p),
+                ("qk", C.c_void_p), ("s1", C.c_void_p), ("s2", C.c_void_p), ("s3", C.c_void_p), ("perm", C.c_void_p),
+                ("kzg_g1", C.c_void_p), ("kzg_lagrange_g1", C.c_void_p), ("vk_commitments", C.c_void_p),
+                ("nb_public", C.c_size_t), ("nb_bsb22", C.c_size_t)]
+
+
+class PlonkProof(C.Structure):
+    """b200_plonk_proof: plonk_bn254.Proof (prove.go:96-114), points affine, scalars Montgomery."""
+    _fields_ = [("lro", (C.c_uint64 * 8) * 3), ("z", C.c_uint64 * 8), ("h", (C.c_uint64 * 8) * 3),
+                ("batched_h", C.c_uint64 * 8), ("claimed", (C.c_uint64 * 4) * 7), ("zshift_h", C.c_uint64 * 8),
+                ("zshift_value", C.c_uint64 * 4), ("challenges", (C.c_uint64 * 4) * 5)]
+
+    def as_dict(self):
+        return {k: np.array(getattr(self, k), dtype=np.uint64) for k, _ in self._fields_}
+
+
+class _PlonkTimings(C.Structure):
+    _fields_ = [(k, C.c_float) for k in ("h2d_ms", "commit_lro_ms", "ratio_ms", "commit_z_ms", "quotient_ms", "commit_h_ms",
+                                          "open_z_ms", "linearize_ms", "batch_open_ms", "total_ms")]
+
+
 class Groth16MsmOut(C.Structure):
     """b200_groth16_out: the five MultiExp results before the fix-ups (prove.go:201-290)."""
     _fields_ = [("ar", C.c_uint64 * 12), ("bs1", C.c_uint64 * 12), ("krs", C.c_uint64 * 12),
@@ -139,6 +163,11 @@ def load_library():
         "b200_kzg_commit_dev": (i, [vp, vp, vp, sz, vp]),
         "b200_plonk_build_ratio_dev": (i, [vp, i, vp, vp, vp, vp, vp, vp, u, vp, vp, vp]),
         "b200_plonk_quotient_rows_dev": (i, [vp, i, C.POINTER(_PlonkRowsDesc), vp]),
+        "b200_plonk_pk_upload": (i, [vp, i, C.POINTER(_PlonkPkDesc), C.POINTER(vp)]),
+        "b200_plonk_pk_free": (i, [vp, vp]),
+        "b200_plonk_prove": (i, [vp, vp, vp, vp, vp, vp, vp, C.POINTER(PlonkProof), C.POINTER(_PlonkTimings)]),
+        "b200_plonk_derive_challenges": (i, [vp, vp, sz, C.POINTER(PlonkProof), vp]),
+        "b200_plonk_proof_bytes": (i, [C.POINTER(PlonkProof), vp, sz]),
         "b200_profile_start": (i, [vp]),
         "b200_profile_read": (i, [vp, C.POINTER(_Profile)]),
         "b200_groth16_finalize": (i, [C.POINTER(Groth16MsmOut), vp, vp, vp, vp, vp, vp, vp, vp, vp, vp]),
@@ -229,6 +258,28 @@ def groth16_proof_bytes(ar, bs, krs) -> bytes:
     return out[:n].tobytes()
 
 
+def plonk_proof_bytes(proof: PlonkProof) -> bytes:
+    """Proof.WriteTo (plonk/bn254/marshal.go:41-66), 552 bytes for a proof without BSB22 commitments."""
+    lib = load_library()
+    out = np.zeros(552, dtype=np.uint8)
+    n = lib.b200_plonk_proof_bytes(C.byref(proof), _ptr(out), 552)
+    if n < 0:
+        raise B200Error(f"b200_plonk_proof_bytes failed with status {n}")
+    return out[:n].tobytes()
+
+
+def plonk_derive_challenges(vk_commitments, public_witness, proof: PlonkProof) -> np.ndarray:
+    """gamma, beta, alpha, zeta (4 x 4 u64 Montgomery) of the proof's commitments (verify.go:296-360)."""
+    lib = load_library()
+    vk = _u64(vk_commitments, (8, 8))
+    pw = _u64(public_witness, (-1, 4))
+    out = np.zeros((4, 4), dtype=np.uint64)
+    st = lib.b200_plonk_derive_challenges(_ptr(vk), _ptr(pw) if pw.shape[0] else None, pw.shape[0], C.byref(proof), _ptr(out))
+    if st != 0:
+        raise B200Error(f"b200_plonk_derive_challenges failed with status {st}")
+    return out
+
+
 # ---- handles ------------------------------------------------------------------------------
 def _dev_ptr(x):
     """Device address of a DeviceVector, a torch CUDA tensor, or a raw integer."""
@@ -309,6 +360,18 @@ class Groth16ProvingKey:
     def free(self):
         if self.h:
             self.ctx.lib.b200_groth16_pk_free(self.ctx.h, self.h)
+            self.h = None
+
+
+class PlonkProvingKey:
+    """Device-resident plonk_bn254.ProvingKey (setup.go:79-107): trace, coset evaluations, both SRS."""
+
+    def __init__(self, ctx, handle, nb_public):
+        self.ctx, self.h, self.nb_public = ctx, handle, nb_public
+
+    def free(self):
+        if self.h:
+            self.ctx.lib.b200_plonk_pk_free(self.ctx.h, self.h)
             self.h = None
 
 
@@ -542,6 +605,36 @@ class Context:
         out = np.empty(8, dtype=np.uint64)
         self._check(self.lib.b200_kzg_commit_dev(self.h, srs.h, _dev_ptr(coeffs), n, _ptr(out)))
         return out
+
+    # -- PlonK prover
+    def plonk_pk_upload(self, *, log_n, log_big, generator, generator_big, coset_gen, ql, qr, qm, qo, qk, s1, s2, s3, perm,
+                        kzg_g1, kzg_lagrange_g1, vk_commitments, nb_public) -> PlonkProvingKey:
+        n = 1 << log_n
+        keep = {k: _u64(v, (n, 4)) for k, v in dict(ql=ql, qr=qr, qm=qm, qo=qo, qk=qk, s1=s1, s2=s2, s3=s3).items()}
+        keep["generator"], keep["generator_big"], keep["coset_gen"] = _u64(generator), _u64(generator_big), _u64(coset_gen)
+        keep["perm"] = np.ascontiguousarray(perm, dtype=np.int64).reshape(3 * n)
+        keep["kzg_g1"] = _u64(kzg_g1, (n + 3, 8))
+        keep["kzg_lagrange_g1"] = _u64(kzg_lagrange_g1, (n, 8))
+        keep["vk_commitments"] = _u64(vk_commitments, (8, 8))
+        d = _PlonkPkDesc()
+        d.log_n, d.log_big, d.nb_public, d.nb_bsb22 = log_n, log_big, nb_public, 0
+        for k, v in keep.items():
+            setattr(d, k, v.ctypes.data)
+        h = C.c_void_p()
+        self._check(self.lib.b200_plonk_pk_upload(self.h, BN254, C.byref(d), C.byref(h)))
+        return PlonkProvingKey(self, h, nb_public)
+
+    def plonk_prove(self, pk: PlonkProvingKey, l, r, o, public_witness, blinding=None):
+        """plonk_bn254.Prove after the solver (prove.go:116-180).  blinding: (9, 4) Montgomery coefficients
+        bl0 bl1 br0 br1 bo0 bo1 bz0 bz1 bz2, or None for fresh randomness.  Returns (PlonkProof, timings dict)."""
+        l, r, o = _u64(l, (-1, 4)), _u64(r, (-1, 4)), _u64(o, (-1, 4))
+        pw = _u64(public_witness, (-1, 4))
+        assert pw.shape[0] == pk.nb_public
+        bl = None if blinding is None else _u64(blinding, (9, 4))
+        proof, tm = PlonkProof(), _PlonkTimings()
+        self._check(self.lib.b200_plonk_prove(self.h, pk.h, _ptr(l), _ptr(r), _ptr(o), _ptr(pw) if pw.shape[0] else None,
+                                              _ptr(bl), C.byref(proof), C.byref(tm)))
+        return proof, {k: getattr(tm, k) for k, _ in tm._fields_}
 
     # -- per-kernel-class device times (CUDA events on the launching stream)
     def profile_start(self):

@@ -8,13 +8,6 @@
 
 using namespace b200;
 
-struct b200_bases {
-    int group = 1;
-    size_t n = 0;
-    DevBuf pts;       // the bases, or their folded-window table
-    MsmFold fold;     // c == 0: plain
-};
-
 namespace {
 thread_local std::string g_init_error;
 
@@ -479,30 +472,7 @@ int b200_plonk_divide_by_xn_minus_one_dev(b200_ctx* ctx, int curve, void* vec_de
     if (log_small > log_big || log_big - log_small > 3 || log_big > 27) return ctx->fail(B200_ERR_ARG, "rho = 2^(log_big - log_small) must be 1, 2, 4 or 8");
     NttDomain* d;
     B2_TRY(get_domain(ctx, log_big, generator_big, coset_gen, &d));
-    const Fr* t;
-    B2_TRY(ntt_domain_table(ctx, d, NttDomain::COSETINV_NAT, &t));
-    // evaluateXnMinusOneDomainBigCoset (prove.go:1253-1276): res[i] = (g * w^i)^n - 1, then inverted
-    const unsigned lr = log_big - log_small;
-    const uint32_t rho = 1u << lr;
-    const uint64_t n_small = (uint64_t)1 << log_small;
-    Fr res[8], f[8];
-    const Fr step = d->gen.pow_u64(n_small);
-    res[0] = d->coset.pow_u64(n_small);
-    for (uint32_t i = 1; i < rho; ++i) res[i] = res[i - 1] * step;
-    for (uint32_t i = 0; i < rho; ++i) {
-        const Fr v = res[i] - Fr::one();
-        if (v.is_zero()) return ctx->fail(B200_ERR_ARG, "X^n - 1 vanishes on the coset");
-        res[i] = v.inv();
-    }
-    // r[i] *= res[bitrev(i) mod rho]  (prove.go:1240-1245): bitrev(i) mod rho = the top lr bits of i, reversed
-    for (uint32_t k = 0; k < rho; ++k) {
-        uint32_t rev = 0;
-        for (unsigned b = 0; b < lr; ++b) rev |= ((k >> b) & 1u) << (lr - 1 - b);
-        f[k] = res[rev];
-    }
-    B2_TRY(fr_scale_cyclic(ctx, (Fr*)vec_dev, (size_t)1 << log_big, f, rho, log_big - lr));
-    // a.ToCanonical(domains[1]).ToRegular(): LagrangeCoset + BitReverse -> FFTInverse(DIT, OnCoset)
-    B2_TRY(ntt_gnark(ctx, d, (Fr*)vec_dev, 1, B200_DIT, 1));
+    B2_TRY(plonk_divide_xn(ctx, d, log_small, (Fr*)vec_dev));
     B2_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     return B200_OK;
 }

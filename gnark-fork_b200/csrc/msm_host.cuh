@@ -345,3 +345,11 @@ int msm_fold_build_impl(b200_ctx* ctx, const Affine<F>* d_bases, size_t n, int c
 
 #endif  // __CUDACC__
 }  // namespace b200
+
+// A resident base set (b200_bases_upload): the bases, or their folded-window table.
+struct b200_bases {
+    int group = 1;
+    size_t n = 0;
+    b200::DevBuf pts;
+    b200::MsmFold fold;     // c == 0: plain
+};

@@ -149,7 +149,7 @@ __global__ void mul_sub_kernel(Fr* a, const Fr* b, const Fr* c, size_t n) {
 // ---------------------------------------------------------------------------------------
 // host side
 // ---------------------------------------------------------------------------------------
-static int gen_powers(b200_ctx* ctx, Fr* out, const Fr& base, const Fr& mult, size_t count, int bitrev_log_n) {
+int gen_powers(b200_ctx* ctx, Fr* out, const Fr& base, const Fr& mult, size_t count, int bitrev_log_n) {
     if (count == 0) return B200_OK;
     const size_t threads = (count + POW_RUN - 1) / POW_RUN;
     const int bs = 128;

@@ -25,6 +25,8 @@ struct NttDomain {
 };
 
 // ntt.cu
+// out[i] = mult * base^e(i), e(i) = i, or the bit reversal of i over bitrev_log_n bits when that is not 0
+int gen_powers(b200_ctx* ctx, Fr* out, const Fr& base, const Fr& mult, size_t count, int bitrev_log_n);
 int ntt_domain_get(b200_ctx* ctx, unsigned log_n, const Fr& gen, const Fr& coset, NttDomain** out);
 int ntt_domain_table(b200_ctx* ctx, NttDomain* d, NttDomain::Table t, const Fr** out);
 void ntt_domain_free_all(b200_ctx* ctx);

@@ -357,4 +357,113 @@ int plonk_quotient_rows(b200_ctx* ctx, PlonkRowArgs& args) {
     return B200_OK;
 }
 
+// ---------------------------------------------------------------------------------------
+// PlonK prover glue kernels (HBM-bound, one element per thread)
+// ---------------------------------------------------------------------------------------
+// out[bitrev(i)] = in[i]  (fft.BitReverse / Polynomial.ToRegular as a copy)
+__global__ void bitrev_copy_kernel(const Fr* __restrict__ in, Fr* __restrict__ out, uint32_t log_n) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >> log_n) return;
+    const uint32_t j = log_n ? (__brev(i) >> (32 - log_n)) : 0u;
+    pl_st(out + j, pl_ld(in + i));
+}
+int fr_bitrev_copy(b200_ctx* ctx, const Fr* in, Fr* out, unsigned log_n) {
+    const size_t n = (size_t)1 << log_n;
+    bitrev_copy_kernel<<<(unsigned)((n + 255) / 256), 256, 0, ctx->stream>>>(in, out, log_n);
+    B2_CUDA(ctx, cudaGetLastError());
+    ctx->n_launches += 1;
+    return B200_OK;
+}
+
+// out[i] = c * w^i: the polynomial beta*X (x[id_ID], prove.go:567-570) on the coset whose shift is folded in c
+__global__ void scaled_omega_kernel(Fr* __restrict__ out, const Fr* __restrict__ tw, uint32_t n, const Fr c) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    pl_st(out + i, c * omega_pow(tw, i, n >> 1));
+}
+int fr_scaled_omega(b200_ctx* ctx, NttDomain* d, const Fr& c, Fr* out) {
+    const uint32_t n = (uint32_t)d->n();
+    scaled_omega_kernel<<<(n + 255) / 256, 256, 0, ctx->stream>>>(out, d->tw_fwd.as<Fr>(), n, c);
+    B2_CUDA(ctx, cudaGetLastError());
+    ctx->n_launches += 1;
+    return B200_OK;
+}
+
+// getBlindedCoefficients (prove.go:1148-1156): p <- p + b (X^n - 1); p has room for n + nb coefficients
+struct BlindCoefs { Fr b[4]; };
+__global__ void blind_kernel(Fr* __restrict__ p, uint32_t n, const BlindCoefs bc, uint32_t nb) {
+    const uint32_t j = threadIdx.x;
+    if (j >= nb) return;
+    pl_st(p + n + j, bc.b[j]);
+    pl_st(p + j, pl_ld(p + j) - bc.b[j]);      // nb <= n is checked by the caller
+}
+int fr_blind(b200_ctx* ctx, Fr* p, size_t n, const Fr* b, uint32_t nb) {
+    if (nb > 4 || nb > n) return ctx->fail(B200_ERR_ARG, "blinding order");
+    BlindCoefs bc;
+    for (uint32_t j = 0; j < 4; ++j) bc.b[j] = j < nb ? b[j] : Fr::zero();
+    blind_kernel<<<1, 32, 0, ctx->stream>>>(p, (uint32_t)n, bc, nb);
+    B2_CUDA(ctx, cudaGetLastError());
+    ctx->n_launches += 1;
+    return B200_OK;
+}
+
+// foldH (prove.go:670-705): out[i] = (h3[i] * z + h2[i]) * z + h1[i]
+__global__ void fold_h_kernel(const Fr* __restrict__ h1, const Fr* __restrict__ h2, const Fr* __restrict__ h3, const Fr z, size_t m,
+                              Fr* __restrict__ out) {
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= m) return;
+    pl_st(out + i, (pl_ld(h3 + i) * z + pl_ld(h2 + i)) * z + pl_ld(h1 + i));
+}
+int plonk_fold_h(b200_ctx* ctx, const Fr* h1, const Fr* h2, const Fr* h3, const Fr& z, size_t m, Fr* out) {
+    fold_h_kernel<<<(unsigned)((m + 255) / 256), 256, 0, ctx->stream>>>(h1, h2, h3, z, m, out);
+    B2_CUDA(ctx, cudaGetLastError());
+    ctx->n_launches += 1;
+    return B200_OK;
+}
+
+// computeLinearizedPolynomial's loop (prove.go:1336-1385), same order of operations
+__global__ void __launch_bounds__(128) linearize_kernel(const PlonkLinArgs a) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= a.len) return;
+    const Fr bz = pl_ld(a.bz + i);
+    Fr t = bz * a.c2;
+    if (i < a.n) t = t + pl_ld(a.s3 + i) * a.c1;
+    t = t * a.alpha;
+    if (i < a.n) {
+        Fr t0 = pl_ld(a.ql + i) * a.l + pl_ld(a.qm + i) * a.rl;
+        t = t + t0;
+        t = t + pl_ld(a.qr + i) * a.r;
+        t0 = pl_ld(a.qo + i) * a.o + pl_ld(a.qk + i);
+        t = t + t0;
+        for (uint32_t j = 0; j < a.nb_bsb; ++j) t = t + pl_ld(a.pi2[j] + i) * a.qcp_zeta[j];
+    }
+    pl_st(a.out + i, t + bz * a.lag);
+}
+int plonk_linearize(b200_ctx* ctx, const PlonkLinArgs& a) {
+    linearize_kernel<<<(a.len + 127) / 128, 128, 0, ctx->stream>>>(a);
+    B2_CUDA(ctx, cudaGetLastError());
+    ctx->n_launches += 1;
+    return B200_OK;
+}
+
+// the fold of kzg.BatchOpenSinglePoint (call site prove.go:823): out[i] = sum_k g^k p_k[i], i < len_k
+__global__ void __launch_bounds__(128) fold_polys_kernel(const PlonkFoldArgs a) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= a.width) return;
+    Fr acc = Fr::zero();
+    for (uint32_t k = 0; k < a.count; ++k) {
+        if (i >= a.len[k]) continue;
+        const Fr v = pl_ld(a.p[k] + i);
+        acc = acc + (k ? v * a.g[k] : v);
+    }
+    pl_st(a.out + i, acc);
+}
+int plonk_fold_polys(b200_ctx* ctx, const PlonkFoldArgs& a) {
+    if (a.count == 0 || a.count > 16) return ctx->fail(B200_ERR_ARG, "fold: 1..16 polynomials");
+    fold_polys_kernel<<<(a.width + 127) / 128, 128, 0, ctx->stream>>>(a);
+    B2_CUDA(ctx, cudaGetLastError());
+    ctx->n_launches += 1;
+    return B200_OK;
+}
+
 }  // namespace b200

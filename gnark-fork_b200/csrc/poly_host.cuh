@@ -30,4 +30,30 @@ struct PlonkRowArgs {
 enum { PID_L = 0, PID_R, PID_O, PID_Z, PID_ZS, PID_QL, PID_QR, PID_QM, PID_QO, PID_QK, PID_S1, PID_S2, PID_S3, PID_ID, PID_LONE };
 
 int plonk_quotient_rows(b200_ctx* ctx, PlonkRowArgs& args);
+
+// divideByXMinusOne on the big domain d (plonk.cu)
+int plonk_divide_xn(b200_ctx* ctx, NttDomain* d, unsigned log_small, Fr* vec);
+// PlonK prover glue (poly.cu)
+int fr_bitrev_copy(b200_ctx* ctx, const Fr* in, Fr* out, unsigned log_n);
+int fr_scaled_omega(b200_ctx* ctx, NttDomain* d, const Fr& c, Fr* out);
+int fr_blind(b200_ctx* ctx, Fr* p, size_t n, const Fr* b, uint32_t nb);
+int plonk_fold_h(b200_ctx* ctx, const Fr* h1, const Fr* h2, const Fr* h3, const Fr& z, size_t m, Fr* out);
+struct PlonkLinArgs {
+    const Fr *bz, *s3, *ql, *qr, *qm, *qo, *qk;   // blinded Z (len coefficients), trace polynomials (n each), canonical
+    const Fr* pi2[8];                              // BSB22 commitment polynomials, canonical
+    Fr qcp_zeta[8];
+    uint32_t nb_bsb;
+    Fr c1, c2, alpha, rl, l, r, o, lag;            // prove.go:1293-1334
+    uint32_t n, len;
+    Fr* out;
+};
+int plonk_linearize(b200_ctx* ctx, const PlonkLinArgs& a);
+struct PlonkFoldArgs {
+    const Fr* p[16];
+    uint32_t len[16];
+    Fr g[16];            // g[k] = gamma^k
+    uint32_t count, width;
+    Fr* out;
+};
+int plonk_fold_polys(b200_ctx* ctx, const PlonkFoldArgs& a);
 }  // namespace b200

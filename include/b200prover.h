@@ -346,6 +346,73 @@ int b200_groth16_finalize(const b200_groth16_out *msm, const uint64_t *r, const 
 int b200_groth16_proof_bytes(const uint64_t *ar_affine, const uint64_t *bs_affine, const uint64_t *krs_affine,
                              uint8_t *out, size_t out_cap);
 
+/* ---- PlonK prover (BN254) ---------------------------------------------------------------------
+ * plonk_bn254.Prove (/root/reference/backend/plonk/bn254/prove.go:116-180) behind one call, for the
+ * circuits of configs 1-5 (no BSB22 commitments: api.Commit circuits return B200_ERR_UNSUPPORTED at
+ * upload).  The solver stays with the caller (prove.go:365-392 gives L, R, O); everything after it
+ * runs here: the ten KZG commitments (G1 MSMs against two resident SRS), the copy-constraint ratio,
+ * the quotient over the rho cosets of the big domain, the openings, and the Fiat-Shamir transcript
+ * (SHA-256, host) that orders them. */
+typedef struct b200_plonk_pk b200_plonk_pk;
+
+/* What the glue reads out of plonk_bn254.ProvingKey (setup.go:79-107).  All pointers are host memory. */
+typedef struct b200_plonk_pk_desc {
+    unsigned log_n;                 /* pk.Domain[0].Cardinality = 2^log_n                                  */
+    unsigned log_big;               /* pk.Domain[1].Cardinality = 2^log_big (4n, or 8n when n+pub < 6)       */
+    const uint64_t *generator;      /* pk.Domain[0].Generator                                               */
+    const uint64_t *generator_big;  /* pk.Domain[1].Generator                                               */
+    const uint64_t *coset_gen;      /* FrMultiplicativeGen (= pk.Vk.CosetShift)                             */
+    const uint64_t *ql, *qr, *qm, *qo, *qk;   /* pk.trace.Q*: canonical / regular, n each; qk incomplete     */
+    const uint64_t *s1, *s2, *s3;             /* pk.trace.S1..S3: canonical / regular                         */
+    const int64_t *perm;            /* pk.trace.S, 3n entries                                                */
+    const uint64_t *kzg_g1;         /* pk.Kzg.G1: n + 3 affine points                                       */
+    const uint64_t *kzg_lagrange_g1;/* pk.KzgLagrange.G1: n affine points                                   */
+    const uint64_t *vk_commitments; /* pk.Vk.S[0], S[1], S[2], Ql, Qr, Qm, Qo, Qk: 8 affine points          */
+    size_t nb_public;               /* pk.Vk.NbPublicVariables                                              */
+    size_t nb_bsb22;                /* len(pk.Vk.Qcp); must be 0                                            */
+} b200_plonk_pk_desc;
+
+/* One-time residency: trace polynomials, their evaluations on the rho cosets of the big domain
+ * (the precomputation prove.go:995-999 leaves out for memory: 8 polynomials x rho x n elements),
+ * the permutation, and both SRS with folded-window MSM tables. */
+int b200_plonk_pk_upload(b200_ctx *ctx, int curve, const b200_plonk_pk_desc *desc, b200_plonk_pk **out);
+int b200_plonk_pk_free(b200_ctx *ctx, b200_plonk_pk *pk);
+
+/* plonk_bn254.Proof (prove.go:96-114) with points affine (8 u64) and scalars Montgomery (4 u64). */
+typedef struct b200_plonk_proof {
+    uint64_t lro[3][8];
+    uint64_t z[8];
+    uint64_t h[3][8];
+    uint64_t batched_h[8];          /* BatchedProof.H                                                       */
+    uint64_t claimed[7][4];         /* BatchedProof.ClaimedValues: folded H, linearised, l, r, o, s1, s2     */
+    uint64_t zshift_h[8];           /* ZShiftedOpening.H                                                    */
+    uint64_t zshift_value[4];       /* ZShiftedOpening.ClaimedValue                                         */
+    uint64_t challenges[5][4];      /* gamma, beta, alpha, zeta, KZG folding gamma (for tests; not serialised) */
+} b200_plonk_proof;
+
+typedef struct b200_plonk_timings {
+    float h2d_ms, commit_lro_ms, ratio_ms, commit_z_ms, quotient_ms, commit_h_ms, open_z_ms, linearize_ms,
+          batch_open_ms, total_ms;
+} b200_plonk_timings;
+
+/* l, r, o: the solution in Lagrange / regular form, n elements each (SparseR1CSSolution,
+ * constraint/bn254/system.go:221-265); public_witness: nb_public elements; blinding: the 9 coefficients
+ * of getRandomPolynomial (prove.go:295-301) in the order bl0 bl1 br0 br1 bo0 bo1 bz0 bz1 bz2, or NULL
+ * to draw them from the OS entropy source as the reference does. */
+int b200_plonk_prove(b200_ctx *ctx, const b200_plonk_pk *pk, const uint64_t *l, const uint64_t *r, const uint64_t *o,
+                     const uint64_t *public_witness, const uint64_t *blinding, b200_plonk_proof *out,
+                     b200_plonk_timings *timings);
+
+/* The four Fiat-Shamir challenges gamma, beta, alpha, zeta (16 u64, Montgomery) of a proof's commitments:
+ * bindPublicData + deriveRandomness (plonk/bn254/verify.go:296-360) over SHA-256, gnark-crypto's
+ * fiat-shamir.Transcript layout (restated in-tree by plonk/bn254/solidity.go:407-538).  Host only. */
+int b200_plonk_derive_challenges(const uint64_t *vk_commitments, const uint64_t *public_witness, size_t nb_public,
+                                 const b200_plonk_proof *proof, uint64_t *out);
+
+/* Proof.WriteTo (plonk/bn254/marshal.go:41-66): 8 compressed G1 | u32 7 | 7 Fr | G1 | Fr | u32 0 = 552
+ * bytes.  Returns the number of bytes written or a negative status. */
+int b200_plonk_proof_bytes(const b200_plonk_proof *proof, uint8_t *out, size_t out_cap);
+
 #if defined(__GNUC__)
 #pragma GCC visibility pop
 #endif

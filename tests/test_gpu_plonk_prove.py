@@ -1,0 +1,105 @@
+"""The device PlonK prover (csrc/plonk.cu, through the C ABI) against oracle/plonk_prove.py:
+byte-identical proofs under fixed blinding, the committed golden proofs, and acceptance by the oracle's
+restatement of plonk.Verify (verify.go:45-294) for proofs made with fresh randomness."""
+import json
+import os
+import random
+
+import numpy as np
+import pytest
+
+from oracle import plonk_prove as PP
+from tests import plonk_util as PU
+from tests import util
+
+pytestmark = pytest.mark.gpu
+R = PP.R
+HERE = os.path.dirname(os.path.abspath(__file__))
+
+
+def _case(nb_mul, seed):
+    rng = random.Random(seed)
+    spr = PP.mul_chain_scs(nb_mul)
+    pk = PP.setup(spr, rng.randrange(1, R))
+    sol = PP.mul_chain_solution(nb_mul, rng.randrange(2, R))
+    blinding = tuple([rng.randrange(R) for _ in range(k)] for k in (2, 2, 2, 3))
+    return spr, pk, sol, blinding
+
+
+def _device_prove(ctx, dpk, spr, sol, blinding):
+    L, Rr, O = PP.evaluate_lro(spr, sol)
+    bl = None if blinding is None else PU.blinding_array(blinding)
+    return ctx.plonk_prove(dpk, util.fr_arr(L), util.fr_arr(Rr), util.fr_arr(O), util.fr_arr(sol[:spr.nb_public]), bl)
+
+
+# sizeSystem 3 (n = 4, big = 32: rho = 8), 6 / 7 (n = 8, rho = 4), ragged sizes, 2^10 and 2^12 rows
+@pytest.mark.parametrize("nb_mul", [1, 2, 4, 5, 13, 100, 1000, 4000])
+def test_proof_bytes_identical_to_oracle(ctx, pkg, nb_mul):
+    spr, pk, sol, blinding = _case(nb_mul, 500 + nb_mul)
+    want, ch = PP.prove(spr, pk, sol, blinding)
+    dpk = PU.upload_pk(ctx, pk)
+    try:
+        got, tm = _device_prove(ctx, dpk, spr, sol, blinding)
+    finally:
+        dpk.free()
+    d = got.as_dict()
+    assert util.fr_ints(d["challenges"]) == [ch["gamma"], ch["beta"], ch["alpha"], ch["zeta"], ch["gamma_kzg"]]
+    assert util.fr_ints(d["claimed"]) == want.claimed
+    assert pkg.plonk_proof_bytes(got) == PP.proof_bytes(want)
+    assert tm["total_ms"] > 0
+
+
+def test_golden_proofs(ctx, pkg):
+    with open(os.path.join(HERE, "golden", "plonk_small.json")) as f:
+        cases = json.load(f)["cases"]
+    for c in cases:
+        spr = PP.mul_chain_scs(c["nb_mul"])
+        pk = PP.setup(spr, int(c["tau"], 16))
+        sol = PP.mul_chain_solution(c["nb_mul"], int(c["x"], 16))
+        blinding = tuple([int(v, 16) for v in b] for b in c["blinding"])
+        dpk = PU.upload_pk(ctx, pk)
+        try:
+            got, _ = _device_prove(ctx, dpk, spr, sol, blinding)
+        finally:
+            dpk.free()
+        assert pkg.plonk_proof_bytes(got).hex() == c["proof_bytes"]
+
+
+def test_fresh_randomness_proofs_verify_and_differ(ctx, pkg):
+    spr, pk, sol, _ = _case(300, 77)
+    dpk = PU.upload_pk(ctx, pk)
+    try:
+        p1, _ = _device_prove(ctx, dpk, spr, sol, None)
+        p2, _ = _device_prove(ctx, dpk, spr, sol, None)
+    finally:
+        dpk.free()
+    assert pkg.plonk_proof_bytes(p1) != pkg.plonk_proof_bytes(p2)
+    for p in (p1, p2):
+        assert PP.verify(PU.struct_to_proof(p), pk.vk, sol[:1], pk.tau)
+    assert not PP.verify(PU.struct_to_proof(p1), pk.vk, [(sol[0] + 1) % R], pk.tau)
+
+
+def test_same_key_many_proofs(ctx, pkg):
+    """A resident key serves different witnesses (the workspace is reused)."""
+    spr, pk, _, blinding = _case(50, 5)
+    dpk = PU.upload_pk(ctx, pk)
+    try:
+        for x in (2, 3, R - 5):
+            sol = PP.mul_chain_solution(50, x)
+            want, _ = PP.prove(spr, pk, sol, blinding)
+            got, _ = _device_prove(ctx, dpk, spr, sol, blinding)
+            assert pkg.plonk_proof_bytes(got) == PP.proof_bytes(want)
+    finally:
+        dpk.free()
+
+
+def test_bad_arguments(ctx, pkg):
+    spr, pk, sol, blinding = _case(5, 1)
+    with pytest.raises(pkg.B200Error):
+        kzg, lag = PU.srs_arrays(pk)
+        f = util.fr_arr
+        ctx.plonk_pk_upload(log_n=pk.d0.log_n, log_big=pk.d0.log_n + 1, generator=util.fr_arr([pk.d0.generator])[0],
+                            generator_big=util.fr_arr([pk.d1.generator])[0], coset_gen=util.fr_arr([5])[0], ql=f(pk.ql), qr=f(pk.qr),
+                            qm=f(pk.qm), qo=f(pk.qo), qk=f(pk.qk), s1=f(pk.s1), s2=f(pk.s2), s3=f(pk.s3),
+                            perm=np.array(pk.perm, dtype=np.int64), kzg_g1=kzg, kzg_lagrange_g1=lag,
+                            vk_commitments=util.g1_arr(PU.vk_points(pk)), nb_public=1)

@@ -103,3 +103,67 @@ def test_bad_arguments(ctx, pkg):
                             qm=f(pk.qm), qo=f(pk.qo), qk=f(pk.qk), s1=f(pk.s1), s2=f(pk.s2), s3=f(pk.s3),
                             perm=np.array(pk.perm, dtype=np.int64), kzg_g1=kzg, kzg_lagrange_g1=lag,
                             vk_commitments=util.g1_arr(PU.vk_points(pk)), nb_public=1)
+
+
+def _host_mod():
+    from importlib import import_module
+    from tests.conftest import load_pkg
+    load_pkg()
+    return import_module("gnark_fork_b200.plonk_host")
+
+
+@pytest.mark.parametrize("log_n", [3, 7, 10])
+def test_device_setup_mirror_matches_oracle_setup(ctx, pkg, log_n):
+    """plonk_host.setup (Setup on the device through the ABI, setup.go:110-161) == the oracle's setup:
+    canonical trace, S1..S3, both SRS, the eight vk commitments; then proofs from that key are the oracle's."""
+    H = _host_mod()
+    n = 1 << log_n
+    tau = random.Random(log_n).randrange(1, R)
+    trace, lro, nb_vars, nb_pub, L, Rr, O, pub = H.mul_chain(log_n, 5)
+    kw = H.setup(ctx, H.Domains(n), trace, lro, nb_vars, nb_pub, tau)
+    spr = PP.mul_chain_scs(n - 2)
+    pk = PP.setup(spr, tau)
+    for k in ("ql", "qr", "qm", "qo", "qk", "s1", "s2", "s3"):
+        assert util.fr_ints(kw[k]) == getattr(pk, k), k
+    assert kw["perm"].tolist() == pk.perm
+    kzg, lag = PU.srs_arrays(pk)
+    assert np.array_equal(kw["kzg_g1"], kzg) and np.array_equal(kw["kzg_lagrange_g1"], lag)
+    assert np.array_equal(kw["vk_commitments"], util.g1_arr(PU.vk_points(pk)))
+    blinding = ([1, 2], [3, 4], [5, 6], [7, 8, 9])
+    dpk = ctx.plonk_pk_upload(**kw)
+    try:
+        got, _ = ctx.plonk_prove(dpk, L, Rr, O, pub, PU.blinding_array(blinding))
+    finally:
+        dpk.free()
+    want, _ = PP.prove(spr, pk, PP.mul_chain_solution(n - 2, 5), blinding)
+    assert pkg.plonk_proof_bytes(got) == PP.proof_bytes(want)
+
+
+def test_large_proof_verifies(ctx, pkg):
+    """A proof at B200_PLONK_LOG_N rows (default 2^16; run with 22 for BASELINE.json config 4) made from a key
+    the device built, checked by the oracle's plonk.Verify restatement (O(1) work: it only needs vk and tau)."""
+    H = _host_mod()
+    log_n = int(os.environ.get("B200_PLONK_LOG_N", "16"))
+    n = 1 << log_n
+    tau = random.Random(99).randrange(1, R)
+    trace, lro, nb_vars, nb_pub, L, Rr, O, pub = H.mul_chain(log_n, 7)
+    d = H.Domains(n)
+    kw = H.setup(ctx, d, trace, lro, nb_vars, nb_pub, tau)
+    dpk = ctx.plonk_pk_upload(**kw)
+    try:
+        ctx.plonk_prove(dpk, L, Rr, O, pub, None)              # warm-up
+        proof, tm = ctx.plonk_prove(dpk, L, Rr, O, pub, None)
+    finally:
+        dpk.free()
+    pts = [util.g1_aff_ints(v) for v in kw["vk_commitments"]]
+    pts = [None if q is None else tuple(q) for q in pts]            # [Qk] of a Mul chain is the point at infinity
+    vk = {"size": n, "size_inv": pow(n, -1, R), "generator": d.gen, "nb_public": 1, "coset_shift": 5,
+          "S": pts[:3], "Ql": pts[3], "Qr": pts[4], "Qm": pts[5], "Qo": pts[6], "Qk": pts[7]}
+    public = util.fr_ints(pub)
+    assert PP.verify(PU.struct_to_proof(proof), vk, public, tau)
+    assert not PP.verify(PU.struct_to_proof(proof), vk, [(public[0] + 1) % R], tau)
+    out = os.path.join(os.path.dirname(HERE), "gpurun_out")
+    if os.path.isdir(out):
+        with open(os.path.join(out, "plonk_prove_2p%d.json" % log_n), "w") as f:
+            json.dump({"log_n": log_n, "verified_by_oracle": True, "timings_ms": tm}, f, indent=1)
+    print("plonk prove 2^%d:" % log_n, tm)

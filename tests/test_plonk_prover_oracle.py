@@ -134,3 +134,29 @@ def test_srs_lagrange_scalars(small):
     canon = PP._to_canonical(evals, pk.d0)
     assert sum(e * l for e, l in zip(evals, lag)) % R == PB.poly_eval(canon, pk.tau)
     assert mono[5] == pow(pk.tau, 5, R)
+
+
+@pytest.mark.parametrize("log_n", [2, 3, 6])
+def test_host_setup_mirror_matches_oracle(pkg, log_n):
+    """gnark-fork_b200/plonk_host.py (product-side Setup mirror): the vectorised permutation, the Mul-chain
+    trace and the solution columns against the oracle's literal restatement."""
+    from importlib import import_module
+    H = import_module("gnark_fork_b200.plonk_host")
+    n = 1 << log_n
+    trace, lro, nb_vars, nb_pub, L, Rr, O, pub = H.mul_chain(log_n, 3)
+    spr = PP.mul_chain_scs(n - 2)
+    assert nb_vars == spr.nb_variables and nb_pub == spr.nb_public
+    assert H.build_permutation(lro, nb_vars).tolist() == PP.build_permutation(spr, n)
+    want = PP.build_trace(spr, n)
+    for k, w in zip(("ql", "qr", "qm", "qo", "qk"), want):
+        assert util.fr_ints(trace[k]) == w
+    sol = PP.mul_chain_solution(n - 2, 3)
+    wl, wr, wo = PP.evaluate_lro(spr, sol)
+    assert (util.fr_ints(L), util.fr_ints(Rr), util.fr_ints(O)) == (wl, wr, wo)
+    assert util.fr_ints(pub) == sol[:1]
+    d = H.Domains(n)
+    assert (d.log_n, d.log_big) == (PP.N.Domain(n).log_n, PP.N.Domain(8 * n if n < 6 else 4 * n).log_n)
+    rng = np.random.default_rng(log_n)
+    ids = rng.integers(0, 7, size=3 * 16)
+    spr2 = PP.SparseR1CS(0, 0, 7, [(0, 0, 0, 0, 0, int(ids[j]), int(ids[16 + j]), int(ids[32 + j])) for j in range(16)])
+    assert H.build_permutation(ids, 7).tolist() == PP.build_permutation(spr2, 16)

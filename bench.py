@@ -435,7 +435,58 @@ def gpu_arm(args):
     if rank != 0:
         ctx.close()
         return 0
-    return report(args, world, peak, prof, stage, step_ms, e2e_s, clk, verified, inst, t_setup, wall_dev, pk.info(), distributed, h2d_bytes)
+    pk_info = pk.info()
+    args.plonk_result = None
+    if world == 1 and args.plonk_log_n:
+        pk.free()                       # the 78 GiB of folded tables go before the PlonK key comes
+        try:
+            args.plonk_result = plonk_section(pkg, ctx, args.plonk_log_n, args.steps, args.warmup)
+        except Exception as e:          # the headline line must still be printed
+            args.plonk_result = {"error": repr(e)}
+    return report(args, world, peak, prof, stage, step_ms, e2e_s, clk, verified, inst, t_setup, wall_dev, pk_info, distributed, h2d_bytes)
+
+
+def plonk_section(pkg, ctx, log_n, steps, warmup):
+    """BASELINE.json config 4: BN254 PlonK Prove at 2^log_n gates (SCS Mul chain, backend/plonk/plonk_test.go:248-260
+    shape) through b200_plonk_prove with page-locked host L, R, O; every proof is checked with the trapdoor form of
+    plonk.Verify (verify.go:45-294; plonk_host.verify_with_trapdoor).  Wall time per proof, host buffers in, proof out."""
+    import importlib
+    H = importlib.import_module("gnark_fork_b200.plonk_host")
+    n = 1 << log_n
+    tau = 0x1234567890ABCDEF1234567890ABCDEF % H.R_MOD
+    t0 = time.perf_counter()
+    trace, lro, nb_vars, nb_pub, L, Rr, O, pub = H.mul_chain(log_n, 3)
+    d = H.Domains(n)
+    kw = H.setup(ctx, d, trace, lro, nb_vars, nb_pub, tau)
+    dpk = ctx.plonk_pk_upload(**kw)
+    t_setup = time.perf_counter() - t0
+    bufs = []
+    for a in (L, Rr, O):
+        b = pkg.pinned_empty(a.shape)
+        b[:] = a
+        bufs.append(b)
+    ctx.profile_start()
+    for _ in range(max(1, warmup)):
+        ctx.plonk_prove(dpk, *bufs, pub, None)
+    launches = ctx.profile_read()["kernel_launches"] // max(1, warmup)
+    wall, stages = [], []
+    for _ in range(steps):
+        t1 = time.perf_counter()
+        proof, tm = ctx.plonk_prove(dpk, *bufs, pub, None)
+        wall.append((time.perf_counter() - t1) * 1e3)
+        stages.append(tm)
+    ok = H.verify_with_trapdoor(proof, kw["vk_commitments"], H.from_mont_array(pub), d, tau)
+    dpk.free()
+    mean_stage = {k: float(np.mean([s[k] for s in stages])) for k in stages[0]}
+    msm_ms = sum(mean_stage[k] for k in ("commit_lro_ms", "commit_z_ms", "commit_h_ms", "batch_open_ms")) + mean_stage["linearize_ms"]
+    return {"metric": "BN254 PlonK prove ms @2^%d gates" % log_n, "value": float(np.mean(wall)), "unit": "ms", "steps": steps,
+            "workload": "SCS Mul chain filling 2^%d rows, big domain 2^%d; 10 KZG commitments (G1 MSM of ~2^%d against 2 resident SRS), "
+                        "%d transforms of 2^%d + 1 of 2^%d, fresh blinding per proof" % (log_n, d.log_big, log_n, 5 + 5 * (d.big // n), log_n, d.log_big),
+            "path": "b200_plonk_prove (page-locked host L, R, O in; proof out; Fiat-Shamir on the host)",
+            "h2d_bytes_per_step": int(3 * n * 32 + 32), "d2h_bytes_per_step": 552,
+            "stage_ms": mean_stage, "commit_ms_share": msm_ms / mean_stage["total_ms"],
+            "gpu_launches_per_proof": int(launches), "verified": bool(ok), "verifier": "plonk.Verify with the KZG pairing checks done in G1 through the known tau of the test SRS",
+            "setup_s": t_setup}
 
 
 def report(args, world, peak, prof, stage, step_ms, e2e_s, clk, verified, inst, t_setup, wall_dev, pk_info, distributed, h2d_bytes):
@@ -506,6 +557,8 @@ def report(args, world, peak, prof, stage, step_ms, e2e_s, clk, verified, inst, 
             "pk_sets": pk_info, "imad_peak": peak, "verified_known_dlog": verified, "setup_s": t_setup, "wall_s_timed_region": wall_dev,
         },
     }
+    if getattr(args, "plonk_result", None):
+        line["plonk"] = args.plonk_result
     if world == 1 and not args.no_cpu:
         sec, cores, text = cpu_prove_seconds(args.cpu_sample_log, inst.log_n)
         line["cpu_baseline"] = {"value": sec, "unit": "s", "cores": cores, "kind": "port", "sample": text}
@@ -521,6 +574,7 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--log-n", type=int, default=24)
     ap.add_argument("--cpu-sample-log", type=int, default=18)
+    ap.add_argument("--plonk-log-n", type=int, default=22, help="N = 1: also time BN254 PlonK Prove at 2^k gates (config 4); 0 = skip")
     ap.add_argument("--no-check", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--replicate-h", action="store_true", help="N > 1: every rank runs the whole computeH (no exchange)")

@@ -72,6 +72,7 @@ void b200_destroy(b200_ctx* ctx) {
     cudaStreamSynchronize(ctx->stream);
     ntt_domain_free_all(ctx);
     if (ctx->scratch) cudaFree(ctx->scratch);
+    if (ctx->poly_scratch) cudaFree(ctx->poly_scratch);
     for (auto& sp : ctx->prof_spans) { cudaEventDestroy(sp.e0); cudaEventDestroy(sp.e1); }
     for (auto e : ctx->prof_pool) cudaEventDestroy(e);
     cudaEventDestroy(ctx->ev0);
@@ -444,7 +445,9 @@ int b200_fr_batch_inverse_dev(b200_ctx* ctx, int curve, const void* in_dev, void
 int b200_fr_prefix_product_dev(b200_ctx* ctx, int curve, const void* in_dev, void* out_dev, size_t n) {
     B2_ENTER(ctx, curve);
     if (n && (!in_dev || !out_dev)) return ctx->fail(B200_ERR_ARG, "null buffer");
-    return fr_prefix_product(ctx, (const Fr*)in_dev, (Fr*)out_dev, n);
+    B2_TRY(fr_prefix_product(ctx, (const Fr*)in_dev, (Fr*)out_dev, n));
+    B2_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return B200_OK;
 }
 int b200_fr_poly_eval_dev(b200_ctx* ctx, int curve, const void* coeffs_dev, size_t n, const uint64_t* x, uint64_t* value) {
     B2_ENTER(ctx, curve);
@@ -497,7 +500,9 @@ int b200_plonk_build_ratio_dev(b200_ctx* ctx, int curve, const void* l_dev, cons
     Fr b, g;
     memcpy(b.l, beta, 32);
     memcpy(g.l, gamma, 32);
-    return plonk_build_ratio(ctx, d, (const Fr*)l_dev, (const Fr*)r_dev, (const Fr*)o_dev, (const int64_t*)perm_dev, b, g, (Fr*)z_out_dev);
+    B2_TRY(plonk_build_ratio(ctx, d, (const Fr*)l_dev, (const Fr*)r_dev, (const Fr*)o_dev, (const int64_t*)perm_dev, b, g, (Fr*)z_out_dev));
+    B2_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return B200_OK;
 }
 int b200_plonk_quotient_rows_dev(b200_ctx* ctx, int curve, const b200_plonk_rows_desc* desc, void* cres_dev) {
     B2_ENTER(ctx, curve);

@@ -28,6 +28,8 @@ struct b200_ctx {
     std::vector<b200::NttDomain*> domains;  // cache keyed by (log_n, generator, coset_gen)
     void* scratch = nullptr;                // grow-only workspace shared by MSM / prove calls
     size_t scratch_bytes = 0;
+    void* poly_scratch = nullptr;           // small persistent scratch of the polynomial primitives (poly.cu), stream-ordered
+    size_t poly_scratch_bytes = 0;
     int msm_c_override = 0;                 // tuning knobs (b200_set_option / B200_MSM_C env)
     int msm_precompute = 1;                 // build folded-window tables for resident base sets
     int msm_fold_c = 0;                     // 0 = automatic (msm_fold_window)
@@ -127,6 +129,22 @@ static inline int ctx_reserve(b200_ctx* ctx, size_t bytes) {
     e = cudaMalloc(&ctx->scratch, bytes);
     if (e != cudaSuccess) { ctx->scratch = nullptr; return ctx->fail(B200_ERR_NOMEM, "workspace", cudaGetErrorString(e)); }
     ctx->scratch_bytes = bytes;
+    return B200_OK;
+}
+
+// Persistent small scratch of poly.cu (grow-only; work on it is ordered on ctx->stream).
+static inline int ctx_poly_scratch(b200_ctx* ctx, size_t bytes, void** out) {
+    if (bytes > ctx->poly_scratch_bytes) {
+        cudaError_t e = cudaStreamSynchronize(ctx->stream);
+        if (e != cudaSuccess) return ctx->fail(B200_ERR_CUDA, "sync before scratch growth", cudaGetErrorString(e));
+        if (ctx->poly_scratch) cudaFree(ctx->poly_scratch);
+        ctx->poly_scratch = nullptr;
+        ctx->poly_scratch_bytes = 0;
+        e = cudaMalloc(&ctx->poly_scratch, bytes);
+        if (e != cudaSuccess) { ctx->poly_scratch = nullptr; return ctx->fail(B200_ERR_NOMEM, "polynomial scratch", cudaGetErrorString(e)); }
+        ctx->poly_scratch_bytes = bytes;
+    }
+    *out = ctx->poly_scratch;
     return B200_OK;
 }
 

@@ -186,13 +186,79 @@ int os_random_fr(Fr* out, int count) {
 
 double now_ms() { return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now().time_since_epoch()).count(); }
 
-// kzg.Commit: MSM of m coefficients against a resident SRS
-int commit(b200_ctx* ctx, const b200_bases* srs, const Fr* d_coeffs, size_t m, G1XYZZ* out) {
-    if (m > srs->n) return ctx->fail(B200_ERR_ARG, "polynomial longer than the SRS");
-    G1Jac r;
-    B2_TRY(msm_g1_run(ctx, srs->pts.as<G1Affine>(), d_coeffs, nullptr, m, &r, nullptr, &srs->fold));
-    *out = xyzz_from_jac(r);
+// kzg.Commit of several polynomials against one resident SRS: G1 MSMs software-pipelined like the Groth16
+// prove core (groth16.cu) -- the counting sort of MSM k+1 runs on the aux stream under the bucket accumulation
+// of MSM k.  wait[k] (optional): an event the sort of MSM k must wait for (its scalars' host copy).
+int commit_many(b200_ctx* ctx, const b200_bases* srs, const Fr* const* coeffs, const size_t* counts, int m, G1XYZZ* out,
+                const cudaEvent_t* wait = nullptr) {
+    if (m < 1 || m > 4) return ctx->fail(B200_ERR_ARG, "commit_many: 1..4 polynomials");
+    size_t sort_max = 0, acc_max = 0, res_off[5] = {0};
+    for (int k = 0; k < m; ++k) {
+        if (counts[k] > srs->n) return ctx->fail(B200_ERR_ARG, "polynomial longer than the SRS");
+        const MsmSizes sz = msm_sizes(counts[k], 1, ctx->msm_c_override, srs->fold.c);
+        sort_max = std::max(sort_max, sz.sort_bytes);
+        acc_max = std::max(acc_max, sz.acc_bytes);
+        res_off[k + 1] = res_off[k] + ((sz.result_bytes + 255) & ~(size_t)255);
+    }
+    const bool overlap = ctx->msm_overlap != 0 && m > 1;
+    Arena ar;
+    const size_t o_sort0 = ar.off; ar.take(sort_max);
+    const size_t o_sort1 = overlap ? ar.off : o_sort0; if (overlap) ar.take(sort_max);
+    const size_t o_acc = ar.off; ar.take(acc_max);
+    B2_TRY(ctx_reserve(ctx, ar.off));
+    if (ctx->h_stage_bytes < res_off[m]) {
+        if (ctx->h_stage) cudaFreeHost(ctx->h_stage);
+        ctx->h_stage = nullptr; ctx->h_stage_bytes = 0;
+        B2_CUDA(ctx, cudaMallocHost(&ctx->h_stage, res_off[m]));
+        ctx->h_stage_bytes = res_off[m];
+    }
+    char* base = (char*)ctx->scratch;
+    char* sort_ws[2] = {base + o_sort0, base + o_sort1};
+    cudaStream_t st = ctx->stream, sx = overlap ? ctx->aux_stream : st;
+    cudaEvent_t ev[9];
+    for (auto& e : ev) B2_CUDA(ctx, cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+    struct EvGuard { cudaEvent_t* e; ~EvGuard() { for (int i = 0; i < 9; ++i) cudaEventDestroy(e[i]); } } guard{ev};
+    cudaEvent_t *ev_sort = ev + 1, *ev_acc = ev + 5;
+    void* jobs[4] = {nullptr, nullptr, nullptr, nullptr};
+    struct JobGuard { void** j; ~JobGuard() { for (int k = 0; k < 4; ++k) if (j[k]) msm_g1_job_delete(j[k]); } } jguard{jobs};
+    for (int k = 0; k < m; ++k)
+        jobs[k] = msm_g1_job_new(ctx, srs->pts.as<G1Affine>(), coeffs[k], nullptr, counts[k], &srs->fold, sort_ws[overlap ? (k & 1) : 0],
+                                 base + o_acc, (char*)ctx->h_stage + res_off[k]);
+    B2_CUDA(ctx, cudaEventRecord(ev[0], st));
+    if (overlap) B2_CUDA(ctx, cudaStreamWaitEvent(sx, ev[0], 0));
+    auto run_sort = [&](int k) -> int {
+        if (wait && wait[k]) B2_CUDA(ctx, cudaStreamWaitEvent(sx, wait[k], 0));
+        if (k >= 2) B2_CUDA(ctx, cudaStreamWaitEvent(sx, ev_acc[k - 2], 0));       // its sort group is free again
+        B2_TRY(msm_g1_job_sort(ctx, jobs[k], sx));
+        B2_CUDA(ctx, cudaEventRecord(ev_sort[k], sx));
+        return B200_OK;
+    };
+    auto run_acc = [&](int k) -> int {
+        B2_CUDA(ctx, cudaStreamWaitEvent(st, ev_sort[k], 0));
+        B2_TRY(msm_g1_job_acc(ctx, jobs[k], st));
+        B2_CUDA(ctx, cudaEventRecord(ev_acc[k], st));
+        return B200_OK;
+    };
+    if (overlap) {
+        B2_TRY(run_sort(0));
+        for (int k = 0; k < m; ++k) {
+            if (k + 1 < m) B2_TRY(run_sort(k + 1));
+            B2_TRY(run_acc(k));
+        }
+    } else {
+        for (int k = 0; k < m; ++k) { B2_TRY(run_sort(k)); B2_TRY(run_acc(k)); }
+    }
+    B2_CUDA(ctx, cudaStreamSynchronize(st));
+    if (overlap) B2_CUDA(ctx, cudaStreamSynchronize(sx));
+    for (int k = 0; k < m; ++k) {
+        G1Jac r;
+        msm_g1_job_finish(jobs[k], &r);
+        out[k] = xyzz_from_jac(r);
+    }
     return B200_OK;
+}
+int commit(b200_ctx* ctx, const b200_bases* srs, const Fr* d_coeffs, size_t m, G1XYZZ* out) {
+    return commit_many(ctx, srs, &d_coeffs, &m, 1, out);
 }
 // commitBlindingFactor (prove.go:1159-1172): [b (X^n - 1)] = sum b_j (G1[n+j] - G1[j])
 G1XYZZ commit_blinding(const b200_plonk_pk* pk, const Fr* b, int nb) {
@@ -367,19 +433,42 @@ int b200_plonk_prove(b200_ctx* ctx, const b200_plonk_pk* pk, const uint64_t* l, 
     if (pk->nb_public) memcpy(pub.data(), public_witness, pk->nb_public * sizeof(Fr));
 
     // ---- solution to the device, [L] [R] [O]  (solveConstraints / commitToLRO, prove.go:365-452) ----------
+    // the copies run on the copy stream; the sort of [L] starts when L has landed, R and O travel under it
     const uint64_t* src[3] = {l, r, o};
-    for (int k = 0; k < 3; ++k) B2_CUDA(ctx, cudaMemcpyAsync(v[k], src[k], n * sizeof(Fr), cudaMemcpyHostToDevice, s));
-    B2_CUDA(ctx, cudaStreamSynchronize(s));
-    lap(T.h2d_ms);
+    cudaEvent_t ev_cp[4];
+    for (auto& e : ev_cp) B2_CUDA(ctx, cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+    struct CpGuard { cudaEvent_t* e; ~CpGuard() { for (int i = 0; i < 4; ++i) cudaEventDestroy(e[i]); } } cpguard{ev_cp};
+    cudaEvent_t ev_t[2];
+    for (auto& e : ev_t) B2_CUDA(ctx, cudaEventCreate(&e));
+    struct TGuard { cudaEvent_t* e; ~TGuard() { cudaEventDestroy(e[0]); cudaEventDestroy(e[1]); } } tguard{ev_t};
+    B2_CUDA(ctx, cudaEventRecord(ev_cp[3], s));
+    B2_CUDA(ctx, cudaStreamWaitEvent(ctx->copy_stream, ev_cp[3], 0));
+    B2_CUDA(ctx, cudaEventRecord(ev_t[0], ctx->copy_stream));
+    for (int k = 0; k < 3; ++k) {
+        B2_CUDA(ctx, cudaMemcpyAsync(v[k], src[k], n * sizeof(Fr), cudaMemcpyDefault, ctx->copy_stream));
+        B2_CUDA(ctx, cudaEventRecord(ev_cp[k], ctx->copy_stream));
+    }
+    B2_CUDA(ctx, cudaEventRecord(ev_t[1], ctx->copy_stream));
     G1Affine lro[3];
     const Fr* bps[3] = {bl, br, bo};
-    for (int k = 0; k < 3; ++k) {
-        G1XYZZ c;
-        B2_TRY(commit(ctx, pk->srs_lag, v[k], n, &c));
-        c.add(commit_blinding(pk, bps[k], 2));
-        lro[k] = c.to_affine();
+    {
+        const Fr* sc[3] = {v[0], v[1], v[2]};
+        const size_t cnt[3] = {n, n, n};
+        G1XYZZ c[3];
+        if (ctx->msm_overlap) B2_TRY(commit_many(ctx, pk->srs_lag, sc, cnt, 3, c, ev_cp));
+        else {
+            for (int k = 0; k < 3; ++k) B2_CUDA(ctx, cudaStreamWaitEvent(s, ev_cp[k], 0));
+            B2_TRY(commit_many(ctx, pk->srs_lag, sc, cnt, 3, c));
+        }
+        for (int k = 0; k < 3; ++k) B2_CUDA(ctx, cudaStreamWaitEvent(s, ev_cp[k], 0));
+        for (int k = 0; k < 3; ++k) {
+            c[k].add(commit_blinding(pk, bps[k], 2));
+            lro[k] = c[k].to_affine();
+        }
     }
     lap(T.commit_lro_ms);
+    B2_CUDA(ctx, cudaEventSynchronize(ev_t[1]));
+    cudaEventElapsedTime(&T.h2d_ms, ev_t[0], ev_t[1]);      // on the copy stream, under the [L] [R] [O] commitments: not a summand of total_ms
 
     // ---- gamma, beta (deriveGammaAndBeta, prove.go:455-485; bindPublicData, verify.go:296-340) -----------
     Transcript fs({"gamma", "beta", "alpha", "zeta"});
@@ -390,7 +479,8 @@ int b200_plonk_prove(b200_ctx* ctx, const b200_plonk_pk* pk, const uint64_t* l, 
     const Fr beta = derive(fs, "beta");
 
     // ---- Z and [Z] (buildRatioCopyConstraint, prove.go:597-631) ------------------------------------------
-    B2_TRY(plonk_build_ratio(ctx, d0, v[0], v[1], v[2], pk->perm.as<int64_t>(), beta, gamma, v[3]));
+    B2_TRY(plonk_build_ratio(ctx, d0, v[0], v[1], v[2], pk->perm.as<int64_t>(), beta, gamma, v[3], tmp[0], tmp[1]));
+    B2_CUDA(ctx, cudaStreamSynchronize(s));
     lap(T.ratio_ms);
     G1Affine z_com;
     {
@@ -455,9 +545,11 @@ int b200_plonk_prove(b200_ctx* ctx, const b200_plonk_pk* pk, const uint64_t* l, 
     const Fr *h1 = cres, *h2 = cres + (n + 2), *h3 = cres + 2 * (n + 2);      // prove.go:652-666
     G1XYZZ hx[3];
     G1Affine h_com[3];
-    for (int k = 0; k < 3; ++k) {                                              // commitToQuotient, prove.go:1198-1218
-        B2_TRY(commit(ctx, pk->srs, cres + (size_t)k * (n + 2), n + 2, &hx[k]));
-        h_com[k] = hx[k].to_affine();
+    {                                                                          // commitToQuotient, prove.go:1198-1218
+        const Fr* sc[3] = {h1, h2, h3};
+        const size_t cnt[3] = {n + 2, n + 2, n + 2};
+        B2_TRY(commit_many(ctx, pk->srs, sc, cnt, 3, hx));
+        for (int k = 0; k < 3; ++k) h_com[k] = hx[k].to_affine();
     }
     lap(T.commit_h_ms);
     for (int k = 0; k < 3; ++k) bind_point(fs, "zeta", h_com[k]);
@@ -473,12 +565,6 @@ int b200_plonk_prove(b200_ctx* ctx, const b200_plonk_pk* pk, const uint64_t* l, 
     B2_TRY(fr_poly_eval(ctx, cn[3], n + 3, zeta_shifted, &zu));
     Fr* quot = tmp[0];
     B2_TRY(fr_poly_div_linear(ctx, cn[3], n + 3, zeta_shifted, quot));
-    G1Affine zs_h;
-    {
-        G1XYZZ c;
-        B2_TRY(commit(ctx, pk->srs, quot, n + 2, &c));
-        zs_h = c.to_affine();
-    }
     lap(T.open_z_ms);
 
     // ---- foldH (prove.go:670-705) ---------------------------------------------------------------------
@@ -516,11 +602,14 @@ int b200_plonk_prove(b200_ctx* ctx, const b200_plonk_pk* pk, const uint64_t* l, 
         a.out = lin;
         B2_TRY(plonk_linearize(ctx, a));
     }
-    G1Affine lin_digest;
-    {
-        G1XYZZ c;
-        B2_TRY(commit(ctx, pk->srs, lin, n + 3, &c));
-        lin_digest = c.to_affine();
+    G1Affine lin_digest, zs_h;
+    {   // [quotient of the Z opening] and [linearised polynomial]: independent, committed as one pipelined pair
+        const Fr* sc[2] = {quot, lin};
+        const size_t cnt[2] = {n + 2, n + 3};
+        G1XYZZ c[2];
+        B2_TRY(commit_many(ctx, pk->srs, sc, cnt, 2, c));
+        zs_h = c[0].to_affine();
+        lin_digest = c[1].to_affine();
     }
     lap(T.linearize_ms);
 

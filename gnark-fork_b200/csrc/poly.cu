@@ -110,11 +110,9 @@ int fr_batch_inverse(b200_ctx* ctx, const Fr* in, Fr* out, size_t n) {
 
 int fr_prefix_product(b200_ctx* ctx, const Fr* in, Fr* out, size_t n) {
     if (n == 0) return B200_OK;
-    DevBuf scratch;
-    B2_CUDA(ctx, scratch.alloc(poly_scratch_elems(n) * sizeof(Fr)));
-    B2_TRY(prefix_product_rec(ctx, in, out, n, scratch.as<Fr>()));
-    B2_CUDA(ctx, cudaStreamSynchronize(ctx->stream));   // scratch dies here
-    return B200_OK;
+    void* sp;
+    B2_TRY(ctx_poly_scratch(ctx, poly_scratch_elems(n) * sizeof(Fr), &sp));
+    return prefix_product_rec(ctx, in, out, n, (Fr*)sp);
 }
 
 // ---- evaluation at a point: Horner per chunk, then the chunk values are a polynomial in x^PL_CHUNK -----
@@ -128,26 +126,47 @@ __global__ void __launch_bounds__(PL_THREADS) chunk_horner_kernel(const Fr* __re
     pl_st(part + t, acc);
 }
 
+// Coalesced evaluation: thread t of T takes the coefficients t, t + T, t + 2T, ... (a warp reads 1 KiB
+// contiguous per step) and returns part[t] = sum_j c[t + jT] y^j with y = x^T; then p(x) = sum_t part[t] x^t is
+// the same problem on T coefficients.  The last <= 1024 values are finished on the host.
+__global__ void __launch_bounds__(128) strided_horner_kernel(const Fr* __restrict__ c, size_t n, uint32_t T, const Fr y, Fr* __restrict__ part) {
+    const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= T || t >= n) return;
+    size_t j = (n - 1 - t) / T;                  // highest j with t + j T < n
+    Fr acc = pl_ld(c + t + j * T);
+    while (j > 0) {
+        --j;
+        acc = acc * y + pl_ld(c + t + j * T);
+    }
+    pl_st(part + t, acc);
+}
+
 int fr_poly_eval(b200_ctx* ctx, const Fr* coeffs, size_t n, const Fr& x, Fr* out_host) {
     if (n == 0) { *out_host = Fr::zero(); return B200_OK; }
-    DevBuf scratch;
-    B2_CUDA(ctx, scratch.alloc(poly_scratch_elems(n) * sizeof(Fr)));
+    constexpr size_t HOST_TAIL = 1024, T_MAX = (size_t)1 << 17;
     const Fr* cur = coeffs;
-    Fr* nxt = scratch.as<Fr>();
     size_t m = n;
-    Fr xp = x;
-    while (m > 1) {
-        const size_t chunks = (m + PL_CHUNK - 1) / PL_CHUNK;
-        chunk_horner_kernel<<<(unsigned)((chunks + PL_THREADS - 1) / PL_THREADS), PL_THREADS, 0, ctx->stream>>>(cur, m, xp, nxt);
-        B2_CUDA(ctx, cudaGetLastError());
-        ctx->n_launches += 1;
-        xp = xp.pow_u64(PL_CHUNK);
-        cur = nxt;
-        nxt += chunks;
-        m = chunks;
+    if (m > HOST_TAIL) {
+        void* sp;
+        B2_TRY(ctx_poly_scratch(ctx, (T_MAX + T_MAX / 16 + 4 * HOST_TAIL) * sizeof(Fr), &sp));   // levels shrink by >= 32x down to HOST_TAIL
+        Fr* nxt = (Fr*)sp;
+        while (m > HOST_TAIL) {
+            size_t T = HOST_TAIL;
+            while (T * 2 <= T_MAX && T * 64 <= m) T *= 2;      // the largest T <= T_MAX with >= 32 coefficients per thread
+            strided_horner_kernel<<<(unsigned)((T + 127) / 128), 128, 0, ctx->stream>>>(cur, m, (uint32_t)T, x.pow_u64(T), nxt);
+            B2_CUDA(ctx, cudaGetLastError());
+            ctx->n_launches += 1;
+            cur = nxt;
+            nxt += T;
+            m = T < m ? T : m;
+        }
     }
-    B2_CUDA(ctx, cudaMemcpyAsync(out_host, cur, sizeof(Fr), cudaMemcpyDeviceToHost, ctx->stream));
+    std::vector<Fr> tail(m);
+    B2_CUDA(ctx, cudaMemcpyAsync(tail.data(), cur, m * sizeof(Fr), cudaMemcpyDeviceToHost, ctx->stream));
     B2_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    Fr acc = tail[m - 1];
+    for (size_t i = m - 1; i-- > 0;) acc = acc * x + tail[i];
+    *out_host = acc;
     return B200_OK;
 }
 
@@ -217,9 +236,9 @@ int fr_poly_div_linear(b200_ctx* ctx, const Fr* a, size_t n, const Fr& z, Fr* q)
         ctx->n_launches += 1;
         return B200_OK;
     }
-    DevBuf scratch;
-    B2_CUDA(ctx, scratch.alloc((3 * poly_scratch_elems(n) + 8) * sizeof(Fr)));
-    Fr* local = scratch.as<Fr>();
+    void* sp;
+    B2_TRY(ctx_poly_scratch(ctx, (3 * poly_scratch_elems(n) + 8) * sizeof(Fr), &sp));
+    Fr* local = (Fr*)sp;
     Fr* carry = local + chunks;
     chunk_horner_kernel<<<blocks, PL_THREADS, 0, ctx->stream>>>(a, n, z, local);
     B2_CUDA(ctx, cudaGetLastError());
@@ -227,7 +246,6 @@ int fr_poly_div_linear(b200_ctx* ctx, const Fr* a, size_t n, const Fr& z, Fr* q)
     chunk_divide_kernel<<<blocks, PL_THREADS, 0, ctx->stream>>>(a, n, z, carry, q);
     B2_CUDA(ctx, cudaGetLastError());
     ctx->n_launches += 2;
-    B2_CUDA(ctx, cudaStreamSynchronize(ctx->stream));   // scratch dies here
     return B200_OK;
 }
 
@@ -296,23 +314,23 @@ __global__ void vec_mul_inplace_kernel(Fr* __restrict__ a, const Fr* __restrict_
 }
 
 int plonk_build_ratio(b200_ctx* ctx, NttDomain* d, const Fr* l, const Fr* r, const Fr* o, const int64_t* perm, const Fr& beta,
-                      const Fr& gamma, Fr* z_out) {
+                      const Fr& gamma, Fr* z_out, Fr* ws_den, Fr* ws_inv) {
     const size_t n = d->n();
-    DevBuf den, inv;
-    B2_CUDA(ctx, den.alloc(n * sizeof(Fr)));
-    B2_CUDA(ctx, inv.alloc(n * sizeof(Fr)));
+    DevBuf den_b, inv_b;
+    if (!ws_den) { B2_CUDA(ctx, den_b.alloc(n * sizeof(Fr))); ws_den = den_b.as<Fr>(); }
+    if (!ws_inv) { B2_CUDA(ctx, inv_b.alloc(n * sizeof(Fr))); ws_inv = inv_b.as<Fr>(); }
     const int bs = 128;
     plonk_ratio_terms_kernel<<<(unsigned)((n + bs - 1) / bs), bs, 0, ctx->stream>>>(l, r, o, perm, d->tw_fwd.as<Fr>(), (uint32_t)n, beta, gamma,
-                                                                                  d->coset, d->coset * d->coset, z_out, den.as<Fr>());
+                                                                                  d->coset, d->coset * d->coset, z_out, ws_den);
     B2_CUDA(ctx, cudaGetLastError());
     ctx->n_launches += 1;
     B2_TRY(fr_prefix_product(ctx, z_out, z_out, n));
-    B2_TRY(fr_prefix_product(ctx, den.as<Fr>(), den.as<Fr>(), n));
-    B2_TRY(fr_batch_inverse(ctx, den.as<Fr>(), inv.as<Fr>(), n));
-    vec_mul_inplace_kernel<<<(unsigned)((n + 255) / 256), 256, 0, ctx->stream>>>(z_out, inv.as<Fr>(), n);
+    B2_TRY(fr_prefix_product(ctx, ws_den, ws_den, n));
+    B2_TRY(fr_batch_inverse(ctx, ws_den, ws_inv, n));
+    vec_mul_inplace_kernel<<<(unsigned)((n + 255) / 256), 256, 0, ctx->stream>>>(z_out, ws_inv, n);
     B2_CUDA(ctx, cudaGetLastError());
     ctx->n_launches += 1;
-    B2_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    if (den_b.p || inv_b.p) B2_CUDA(ctx, cudaStreamSynchronize(ctx->stream));   // the local buffers die here
     return B200_OK;
 }
 

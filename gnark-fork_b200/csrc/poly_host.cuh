@@ -16,7 +16,7 @@ int fr_scale_cyclic(b200_ctx* ctx, Fr* v, size_t n, const Fr* factors, uint32_t 
 // Z of the copy constraints (Lagrange / Regular): iop.BuildRatioCopyConstraint over l, r, o with
 // the permutation `perm` (3 n int64 on the device), domain d (generator w, shift g = d->coset)
 int plonk_build_ratio(b200_ctx* ctx, NttDomain* d, const Fr* l, const Fr* r, const Fr* o, const int64_t* perm, const Fr& beta,
-                      const Fr& gamma, Fr* z_out);
+                      const Fr& gamma, Fr* z_out, Fr* ws_den = nullptr, Fr* ws_inv = nullptr);   // ws_*: optional n-element scratch
 struct PlonkRowArgs {
     const Fr* x[15];          // id_L .. id_LOne (prove.go:60-77); x[id_ZS] is not read
     const Fr* qci[16];        // [Qcp_0, Pi_0, Qcp_1, Pi_1, ...]

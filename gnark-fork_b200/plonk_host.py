@@ -162,3 +162,111 @@ def mul_chain(log_n: int, x: int = 3):
     trace = {"ql": ql, "qr": qr, "qm": qm, "qo": qo, "qk": qk}
     L, Rr, O = v[la], v[lb], v[lc]
     return trace, lro, nb_mul + 2, 1, L, Rr, O, v[:1].copy()
+
+
+# ---------------------------------------------------------------------------------------------
+# plonk_bn254.Verify (verify.go:45-294) for proofs made against a test SRS whose tau is known: the two KZG
+# checks e(C - [v]G1, G2) == e(H, [tau - z]G2) become C - [v]G1 == [tau - z]H in G1 (no pairing needed).
+# Host-side big-int code, O(nb_public) field work + ~25 scalar multiplications.
+# ---------------------------------------------------------------------------------------------
+def _g1_add(p, q):
+    if p is None:
+        return q
+    if q is None:
+        return p
+    (x1, y1), (x2, y2) = p, q
+    if x1 == x2:
+        if (y1 + y2) % P_MOD == 0:
+            return None
+        lam = 3 * x1 * x1 * pow(2 * y1, -1, P_MOD) % P_MOD
+    else:
+        lam = (y2 - y1) * pow(x2 - x1, -1, P_MOD) % P_MOD
+    x3 = (lam * lam - x1 - x2) % P_MOD
+    return x3, (lam * (x1 - x3) - y1) % P_MOD
+
+
+def _g1_mul(p, k):
+    k %= R_MOD
+    acc = None
+    while k:
+        if k & 1:
+            acc = _g1_add(acc, p)
+        p = _g1_add(p, p)
+        k >>= 1
+    return acc
+
+
+def _g1_neg(p):
+    return None if p is None else (p[0], (-p[1]) % P_MOD)
+
+
+def g1_from_limbs(a):
+    """(8,) u64 affine Montgomery -> (x, y) ints or None for infinity."""
+    rinv = pow(MONT, -1, P_MOD)
+    b = np.ascontiguousarray(a, dtype=np.uint64).tobytes()
+    x = int.from_bytes(b[:32], "little") * rinv % P_MOD
+    y = int.from_bytes(b[32:], "little") * rinv % P_MOD
+    return None if x == 0 and y == 0 else (x, y)
+
+
+def _g1_raw(p) -> bytes:
+    return bytes([0x40]) + bytes(63) if p is None else p[0].to_bytes(32, "big") + p[1].to_bytes(32, "big")
+
+
+def _challenge(name: bytes, prev: bytes, *chunks: bytes) -> bytes:
+    import hashlib
+    return hashlib.sha256(name + prev + b"".join(chunks)).digest()
+
+
+def verify_with_trapdoor(proof, vk_commitments, public, d: Domains, tau: int) -> bool:
+    """proof: api.PlonkProof; vk_commitments: (8, 8) S1 S2 S3 Ql Qr Qm Qo Qk; public: list of ints."""
+    pd = proof.as_dict()
+    pt = g1_from_limbs
+    lro, z_com, h_com = [pt(pd["lro"][k]) for k in range(3)], pt(pd["z"]), [pt(pd["h"][k]) for k in range(3)]
+    batched_h, zs_h = pt(pd["batched_h"]), pt(pd["zshift_h"])
+    claimed = from_mont_array(pd["claimed"])
+    zu = from_mont_array(pd["zshift_value"].reshape(1, 4))[0]
+    vk = [pt(v) for v in vk_commitments]
+    s_com, ql, qr, qm, qo, qk = vk[:3], vk[3], vk[4], vk[5], vk[6], vk[7]
+    fb = lambda x: (x % R_MOD).to_bytes(32, "big")
+    g = _challenge(b"gamma", b"", *[_g1_raw(p) for p in vk], *[fb(w) for w in public], *[_g1_raw(p) for p in lro])
+    b = _challenge(b"beta", g)
+    a = _challenge(b"alpha", b, _g1_raw(z_com))
+    zt = _challenge(b"zeta", a, *[_g1_raw(p) for p in h_com])
+    gamma, beta, alpha, zeta = (int.from_bytes(v, "big") % R_MOD for v in (g, b, a, zt))
+    n, R = d.n, R_MOD
+    zzeta = (pow(zeta, n, R) - 1) % R
+    lag1 = zzeta * pow((zeta - 1) % R, -1, R) % R * pow(n, -1, R) % R
+    pi, lag, wp = 0, lag1, 1
+    for i, w in enumerate(public):                                   # PI = sum L_i(zeta) w_i, verify.go:103-125
+        pi = (pi + lag * w) % R
+        if i + 1 != len(public):
+            lag = lag * d.gen % R * ((zeta - wp) % R) % R
+            wp = wp * d.gen % R
+            lag = lag * pow((zeta - wp) % R, -1, R) % R
+    cq, lin_z, l, r, o, s1, s2 = claimed
+    t = (s1 * beta + l + gamma) * ((s2 * beta + r + gamma) % R) % R * ((o + gamma) % R) % R * alpha % R * zu % R
+    asl = lag1 * alpha % R * alpha % R
+    if (lin_z + pi + t - asl) % R * pow(zzeta, -1, R) % R != cq:
+        return False
+    zm2 = pow(zeta, n + 2, R)
+    folded_h = _g1_add(_g1_mul(_g1_add(_g1_mul(h_com[2], zm2), h_com[1]), zm2), h_com[0])
+    cs = FR_MULT_GEN
+    u1 = zu * beta % R * ((beta * s1 + l + gamma) % R) % R * ((beta * s2 + r + gamma) % R) % R * alpha % R
+    u2 = (beta * zeta + l + gamma) * ((beta * zeta * cs + r + gamma) % R) % R * ((beta * zeta * cs * cs + o + gamma) % R) % R
+    u2 = ((R - u2) * alpha + asl) % R
+    lin = None
+    for p, s in zip((ql, qr, qm, qo, qk, s_com[2], z_com), (l, r, l * r % R, o, 1, u1, u2)):
+        lin = _g1_add(lin, _g1_mul(p, s))
+    digests = [folded_h, lin, lro[0], lro[1], lro[2], s_com[0], s_com[1]]
+    gk = int.from_bytes(_challenge(b"gamma", b"", fb(zeta), *[_g1_raw(p) for p in digests], *[fb(v) for v in claimed], fb(zu)), "big") % R
+    fd, fv, acc = None, 0, 1
+    for dg, v in zip(digests, claimed):
+        fd = _g1_add(fd, _g1_mul(dg, acc))
+        fv = (fv + acc * v) % R
+        acc = acc * gk % R
+    gen = (1, 2)
+
+    def kzg_ok(c, h, v, z):
+        return _g1_add(c, _g1_neg(_g1_mul(gen, v))) == _g1_mul(h, (tau - z) % R)
+    return kzg_ok(fd, batched_h, fv, zeta) and kzg_ok(z_com, zs_h, zu, zeta * d.gen % R)

@@ -150,6 +150,12 @@ def test_large_proof_verifies(ctx, pkg):
     d = H.Domains(n)
     kw = H.setup(ctx, d, trace, lro, nb_vars, nb_pub, tau)
     dpk = ctx.plonk_pk_upload(**kw)
+    pinned = []
+    for a in (L, Rr, O):                                       # the solver's output buffers, page-locked
+        b = pkg.pinned_empty(a.shape)
+        b[:] = a
+        pinned.append(b)
+    L, Rr, O = pinned
     try:
         ctx.plonk_prove(dpk, L, Rr, O, pub, None)              # warm-up
         proof, tm = ctx.plonk_prove(dpk, L, Rr, O, pub, None)

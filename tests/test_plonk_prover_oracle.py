@@ -160,3 +160,18 @@ def test_host_setup_mirror_matches_oracle(pkg, log_n):
     ids = rng.integers(0, 7, size=3 * 16)
     spr2 = PP.SparseR1CS(0, 0, 7, [(0, 0, 0, 0, 0, int(ids[j]), int(ids[16 + j]), int(ids[32 + j])) for j in range(16)])
     assert H.build_permutation(ids, 7).tolist() == PP.build_permutation(spr2, 16)
+
+
+def test_product_side_trapdoor_verifier_agrees_with_oracle(pkg, small):
+    """plonk_host.verify_with_trapdoor (what bench.py checks its proofs with) against the oracle's verify."""
+    from importlib import import_module
+    H = import_module("gnark_fork_b200.plonk_host")
+    spr, pk, sol, _, proof, _ = small
+    d = H.Domains(len(spr.constraints) + spr.nb_public)
+    vk = util.g1_arr(PU.vk_points(pk))
+    s = PU.proof_to_struct(pkg, proof)
+    assert H.verify_with_trapdoor(s, vk, sol[:1], d, pk.tau)
+    assert not H.verify_with_trapdoor(s, vk, [(sol[0] + 1) % R], d, pk.tau)
+    assert not H.verify_with_trapdoor(s, vk, sol[:1], d, (pk.tau + 1) % R)
+    s.claimed[3][0] ^= 1
+    assert not H.verify_with_trapdoor(s, vk, sol[:1], d, pk.tau)

@@ -55,17 +55,29 @@ class _PlonkPkDesc(C.Structure):
                 ("coset_gen", C.c_void_p), ("ql", C.c_void_p), ("qr", C.c_void_p), ("qm", C.c_void_p), ("qo", C.c_void_p),
                 ("qk", C.c_void_p), ("s1", C.c_void_p), ("s2", C.c_void_p), ("s3", C.c_void_p), ("perm", C.c_void_p),
                 ("kzg_g1", C.c_void_p), ("kzg_lagrange_g1", C.c_void_p), ("vk_commitments", C.c_void_p),
-                ("nb_public", C.c_size_t), ("nb_bsb22", C.c_size_t)]
+                ("nb_public", C.c_size_t), ("nb_bsb22", C.c_size_t), ("qcp", C.c_void_p), ("vk_qcp", C.c_void_p),
+                ("commitment_index", C.c_void_p)]
+
+
+class _PlonkBsb22(C.Structure):
+    """b200_plonk_bsb22."""
+    _fields_ = [("pi2", C.c_void_p), ("commitments", C.c_void_p), ("values", C.c_void_p)]
 
 
 class PlonkProof(C.Structure):
     """b200_plonk_proof: plonk_bn254.Proof (prove.go:96-114), points affine, scalars Montgomery."""
     _fields_ = [("lro", (C.c_uint64 * 8) * 3), ("z", C.c_uint64 * 8), ("h", (C.c_uint64 * 8) * 3),
                 ("batched_h", C.c_uint64 * 8), ("claimed", (C.c_uint64 * 4) * 7), ("zshift_h", C.c_uint64 * 8),
-                ("zshift_value", C.c_uint64 * 4), ("challenges", (C.c_uint64 * 4) * 5)]
+                ("zshift_value", C.c_uint64 * 4), ("challenges", (C.c_uint64 * 4) * 5), ("nb_bsb22", C.c_uint64),
+                ("claimed_qcp", (C.c_uint64 * 4) * 8), ("bsb22", (C.c_uint64 * 8) * 8)]
 
     def as_dict(self):
         return {k: np.array(getattr(self, k), dtype=np.uint64) for k, _ in self._fields_}
+
+    def all_claimed(self) -> np.ndarray:
+        """BatchedProof.ClaimedValues: the 7 fixed ones then Qcp_i(zeta), (7 + nb_bsb22, 4)."""
+        d = self.as_dict()
+        return np.concatenate([d["claimed"], d["claimed_qcp"][:int(self.nb_bsb22)]])
 
 
 class _PlonkTimings(C.Structure):
@@ -166,7 +178,8 @@ def load_library():
         "b200_plonk_pk_upload": (i, [vp, i, C.POINTER(_PlonkPkDesc), C.POINTER(vp)]),
         "b200_plonk_pk_free": (i, [vp, vp]),
         "b200_plonk_prove": (i, [vp, vp, vp, vp, vp, vp, vp, C.POINTER(PlonkProof), C.POINTER(_PlonkTimings)]),
-        "b200_plonk_derive_challenges": (i, [vp, vp, sz, C.POINTER(PlonkProof), vp]),
+        "b200_plonk_prove_bsb22": (i, [vp, vp, vp, vp, vp, vp, vp, C.POINTER(_PlonkBsb22), C.POINTER(PlonkProof), C.POINTER(_PlonkTimings)]),
+        "b200_plonk_derive_challenges": (i, [vp, vp, vp, sz, C.POINTER(PlonkProof), vp]),
         "b200_plonk_proof_bytes": (i, [C.POINTER(PlonkProof), vp, sz]),
         "b200_profile_start": (i, [vp]),
         "b200_profile_read": (i, [vp, C.POINTER(_Profile)]),
@@ -261,20 +274,21 @@ def groth16_proof_bytes(ar, bs, krs) -> bytes:
 def plonk_proof_bytes(proof: PlonkProof) -> bytes:
     """Proof.WriteTo (plonk/bn254/marshal.go:41-66), 552 bytes for a proof without BSB22 commitments."""
     lib = load_library()
-    out = np.zeros(552, dtype=np.uint8)
-    n = lib.b200_plonk_proof_bytes(C.byref(proof), _ptr(out), 552)
+    out = np.zeros(552 + 64 * 8, dtype=np.uint8)
+    n = lib.b200_plonk_proof_bytes(C.byref(proof), _ptr(out), out.shape[0])
     if n < 0:
         raise B200Error(f"b200_plonk_proof_bytes failed with status {n}")
     return out[:n].tobytes()
 
 
-def plonk_derive_challenges(vk_commitments, public_witness, proof: PlonkProof) -> np.ndarray:
+def plonk_derive_challenges(vk_commitments, public_witness, proof: PlonkProof, vk_qcp=None) -> np.ndarray:
     """gamma, beta, alpha, zeta (4 x 4 u64 Montgomery) of the proof's commitments (verify.go:296-360)."""
     lib = load_library()
     vk = _u64(vk_commitments, (8, 8))
     pw = _u64(public_witness, (-1, 4))
+    qcp = None if vk_qcp is None else _u64(vk_qcp, (-1, 8))
     out = np.zeros((4, 4), dtype=np.uint64)
-    st = lib.b200_plonk_derive_challenges(_ptr(vk), _ptr(pw) if pw.shape[0] else None, pw.shape[0], C.byref(proof), _ptr(out))
+    st = lib.b200_plonk_derive_challenges(_ptr(vk), _ptr(qcp), _ptr(pw) if pw.shape[0] else None, pw.shape[0], C.byref(proof), _ptr(out))
     if st != 0:
         raise B200Error(f"b200_plonk_derive_challenges failed with status {st}")
     return out
@@ -366,8 +380,8 @@ class Groth16ProvingKey:
 class PlonkProvingKey:
     """Device-resident plonk_bn254.ProvingKey (setup.go:79-107): trace, coset evaluations, both SRS."""
 
-    def __init__(self, ctx, handle, nb_public):
-        self.ctx, self.h, self.nb_public = ctx, handle, nb_public
+    def __init__(self, ctx, handle, nb_public, nb_bsb22=0):
+        self.ctx, self.h, self.nb_public, self.nb_bsb22 = ctx, handle, nb_public, nb_bsb22
 
     def free(self):
         if self.h:
@@ -608,7 +622,8 @@ class Context:
 
     # -- PlonK prover
     def plonk_pk_upload(self, *, log_n, log_big, generator, generator_big, coset_gen, ql, qr, qm, qo, qk, s1, s2, s3, perm,
-                        kzg_g1, kzg_lagrange_g1, vk_commitments, nb_public) -> PlonkProvingKey:
+                        kzg_g1, kzg_lagrange_g1, vk_commitments, nb_public, qcp=(), vk_qcp=None, commitment_index=()) -> PlonkProvingKey:
+        """qcp: list of pk.trace.Qcp columns (canonical), vk_qcp: their commitments, commitment_index: CommitmentInfo[i].CommitmentIndex."""
         n = 1 << log_n
         keep = {k: _u64(v, (n, 4)) for k, v in dict(ql=ql, qr=qr, qm=qm, qo=qo, qk=qk, s1=s1, s2=s2, s3=s3).items()}
         keep["generator"], keep["generator_big"], keep["coset_gen"] = _u64(generator), _u64(generator_big), _u64(coset_gen)
@@ -617,23 +632,38 @@ class Context:
         keep["kzg_lagrange_g1"] = _u64(kzg_lagrange_g1, (n, 8))
         keep["vk_commitments"] = _u64(vk_commitments, (8, 8))
         d = _PlonkPkDesc()
-        d.log_n, d.log_big, d.nb_public, d.nb_bsb22 = log_n, log_big, nb_public, 0
+        d.log_n, d.log_big, d.nb_public, d.nb_bsb22 = log_n, log_big, nb_public, len(qcp)
         for k, v in keep.items():
             setattr(d, k, v.ctypes.data)
+        if len(qcp):
+            cols = [_u64(q, (n, 4)) for q in qcp]
+            ptrs = (C.c_void_p * len(cols))(*[c.ctypes.data for c in cols])
+            vq = _u64(vk_qcp, (len(cols), 8))
+            ci = np.ascontiguousarray(commitment_index, dtype=np.uint64)
+            d.qcp, d.vk_qcp, d.commitment_index = C.addressof(ptrs), vq.ctypes.data, ci.ctypes.data
         h = C.c_void_p()
         self._check(self.lib.b200_plonk_pk_upload(self.h, BN254, C.byref(d), C.byref(h)))
-        return PlonkProvingKey(self, h, nb_public)
+        return PlonkProvingKey(self, h, nb_public, len(qcp))
 
-    def plonk_prove(self, pk: PlonkProvingKey, l, r, o, public_witness, blinding=None):
+    def plonk_prove(self, pk: PlonkProvingKey, l, r, o, public_witness, blinding=None, bsb=None):
         """plonk_bn254.Prove after the solver (prove.go:116-180).  blinding: (9, 4) Montgomery coefficients
-        bl0 bl1 br0 br1 bo0 bo1 bz0 bz1 bz2, or None for fresh randomness.  Returns (PlonkProof, timings dict)."""
+        bl0 bl1 br0 br1 bo0 bo1 bz0 bz1 bz2, or None for fresh randomness.  bsb (api.Commit circuits): dict with
+        'pi2' (list of (n, 4) Lagrange columns), 'commitments' ((k, 8) affine), 'values' ((k, 4)) from the solver's
+        bsb22Hint (prove.go:303-352).  Returns (PlonkProof, timings dict)."""
         l, r, o = _u64(l, (-1, 4)), _u64(r, (-1, 4)), _u64(o, (-1, 4))
         pw = _u64(public_witness, (-1, 4))
         assert pw.shape[0] == pk.nb_public
         bl = None if blinding is None else _u64(blinding, (9, 4))
         proof, tm = PlonkProof(), _PlonkTimings()
-        self._check(self.lib.b200_plonk_prove(self.h, pk.h, _ptr(l), _ptr(r), _ptr(o), _ptr(pw) if pw.shape[0] else None,
-                                              _ptr(bl), C.byref(proof), C.byref(tm)))
+        cb = None
+        if pk.nb_bsb22:
+            cols = [_u64(c, (-1, 4)) for c in bsb["pi2"]]
+            assert len(cols) == pk.nb_bsb22
+            ptrs = (C.c_void_p * len(cols))(*[c.ctypes.data for c in cols])
+            com, val = _u64(bsb["commitments"], (len(cols), 8)), _u64(bsb["values"], (len(cols), 4))
+            cb = _PlonkBsb22(C.addressof(ptrs), com.ctypes.data, val.ctypes.data)
+        self._check(self.lib.b200_plonk_prove_bsb22(self.h, pk.h, _ptr(l), _ptr(r), _ptr(o), _ptr(pw) if pw.shape[0] else None,
+                                                    _ptr(bl), None if cb is None else C.byref(cb), C.byref(proof), C.byref(tm)))
         return proof, {k: getattr(tm, k) for k, _ in tm._fields_}
 
     # -- per-kernel-class device times (CUDA events on the launching stream)

@@ -37,6 +37,15 @@ struct b200_plonk_pk {
     b200_bases *srs = nullptr, *srs_lag = nullptr;
     G1Affine srs_lo[3], srs_hi[3];   // pk.Kzg.G1[0..2], [n..n+2]  (commitBlindingFactor, prove.go:1159-1172)
     G1Affine vk_pts[8];              // S1 S2 S3 Ql Qr Qm Qo Qk
+    // BSB22 (api.Commit circuits)
+    uint32_t nb_bsb = 0;
+    DevBuf qcp;          // [nb_bsb][n] trace.Qcp, canonical / regular
+    DevBuf qcp_ev;       // [rho][nb_bsb][n] coset evaluations
+    DevBuf bsb_work;     // per proof: [nb_bsb] x (n bit-reversed canonical | n regular canonical | n coset evaluation)
+    G1Affine vk_qcp[B200_PLONK_MAX_BSB22];
+    size_t commit_row[B200_PLONK_MAX_BSB22];   // nb_public + CommitmentIndex
+    const Fr* qcp_c(uint32_t k) const { return qcp.as<Fr>() + (size_t)k * n; }
+    const Fr* qcp_e(uint32_t coset, uint32_t k) const { return qcp_ev.as<Fr>() + ((size_t)coset * nb_bsb + k) * n; }
     const Fr* tr(int k) const { return trace.as<Fr>() + (size_t)k * n; }
     const Fr* cev(uint32_t coset, int k) const { return coset_ev.as<Fr>() + ((size_t)coset * 8 + k) * n; }
 };
@@ -324,7 +333,8 @@ int b200_plonk_pk_upload(b200_ctx* ctx, int curve, const b200_plonk_pk_desc* d, 
     if (!d || !out || !d->generator || !d->generator_big || !d->coset_gen || !d->ql || !d->qr || !d->qm || !d->qo || !d->qk || !d->s1 ||
         !d->s2 || !d->s3 || !d->perm || !d->kzg_g1 || !d->kzg_lagrange_g1 || !d->vk_commitments)
         return ctx->fail(B200_ERR_ARG, "null argument");
-    if (d->nb_bsb22) return ctx->fail(B200_ERR_UNSUPPORTED, "BSB22 commitments (api.Commit circuits) are not built");
+    if (d->nb_bsb22 > B200_PLONK_MAX_BSB22) return ctx->fail(B200_ERR_UNSUPPORTED, "more BSB22 commitments than B200_PLONK_MAX_BSB22");
+    if (d->nb_bsb22 && (!d->qcp || !d->vk_qcp || !d->commitment_index)) return ctx->fail(B200_ERR_ARG, "null BSB22 argument");
     if (d->log_n < 1 || d->log_big < d->log_n + 2 || d->log_big > d->log_n + 3 || d->log_big > 27)
         return ctx->fail(B200_ERR_ARG, "domains: need 2 <= n, big = 4n or 8n, big <= 2^27");
     const size_t n = (size_t)1 << d->log_n;
@@ -333,6 +343,13 @@ int b200_plonk_pk_upload(b200_ctx* ctx, int curve, const b200_plonk_pk_desc* d, 
     pk->log_n = d->log_n; pk->log_big = d->log_big; pk->n = n; pk->big = (size_t)1 << d->log_big;
     pk->rho = 1u << (d->log_big - d->log_n);
     pk->nb_public = d->nb_public;
+    pk->nb_bsb = (uint32_t)d->nb_bsb22;
+    for (uint32_t k = 0; k < pk->nb_bsb; ++k) {
+        if (!d->qcp[k]) { delete pk; return ctx->fail(B200_ERR_ARG, "null Qcp"); }
+        pk->commit_row[k] = d->nb_public + d->commitment_index[k];
+        if (pk->commit_row[k] >= n) { delete pk; return ctx->fail(B200_ERR_ARG, "commitment index outside the domain"); }
+    }
+    if (pk->nb_bsb) memcpy(pk->vk_qcp, d->vk_qcp, pk->nb_bsb * sizeof(G1Affine));
     Fr gen, gen_big, cg;
     memcpy(gen.l, d->generator, 32); memcpy(gen_big.l, d->generator_big, 32); memcpy(cg.l, d->coset_gen, 32);
     int st = ntt_domain_get(ctx, d->log_n, gen, cg, &pk->d0);
@@ -351,7 +368,12 @@ int b200_plonk_pk_upload(b200_ctx* ctx, int curve, const b200_plonk_pk_desc* d, 
     // workspace: 5 vectors of n, 9 of n + 4 (canonical blinded L R O Z; 5 coset evaluations reused by the openings), id, cres
     const size_t N4 = n + 4;
     if (e == cudaSuccess) e = pk->work.alloc((6 * n + 9 * N4 + pk->big) * sizeof(Fr));
+    if (e == cudaSuccess && pk->nb_bsb) e = pk->qcp.alloc((size_t)pk->nb_bsb * n * sizeof(Fr));
+    if (e == cudaSuccess && pk->nb_bsb) e = pk->qcp_ev.alloc((size_t)pk->rho * pk->nb_bsb * n * sizeof(Fr));
+    if (e == cudaSuccess && pk->nb_bsb) e = pk->bsb_work.alloc((size_t)pk->nb_bsb * 3 * n * sizeof(Fr));
     if (e != cudaSuccess) return fail_cuda(e, "PlonK key allocation");
+    for (uint32_t k = 0; k < pk->nb_bsb && e == cudaSuccess; ++k)
+        e = cudaMemcpyAsync(pk->qcp.as<Fr>() + (size_t)k * n, d->qcp[k], n * sizeof(Fr), cudaMemcpyHostToDevice, s);
     const uint64_t* src[8] = {d->ql, d->qr, d->qm, d->qo, d->qk, d->s1, d->s2, d->s3};
     for (int k = 0; k < 8 && e == cudaSuccess; ++k)
         e = cudaMemcpyAsync(pk->trace.as<Fr>() + (size_t)k * n, src[k], n * sizeof(Fr), cudaMemcpyHostToDevice, s);
@@ -378,6 +400,14 @@ int b200_plonk_pk_upload(b200_ctx* ctx, int curve, const b200_plonk_pk_desc* d, 
             st = ntt_run(ctx, pk->d0, dst, 0, 1, pk->coset_pre.as<Fr>() + (size_t)k * n, nullptr, nullptr);
         }
     }
+    for (uint32_t p = 0; p < pk->nb_bsb && st == B200_OK; ++p) {
+        st = fr_bitrev_copy(ctx, pk->qcp_c(p), tmp, d->log_n);
+        for (uint32_t k = 0; k < pk->rho && st == B200_OK; ++k) {
+            Fr* dst = const_cast<Fr*>(pk->qcp_e(k, p));
+            if (cudaMemcpyAsync(dst, tmp, n * sizeof(Fr), cudaMemcpyDeviceToDevice, s) != cudaSuccess) { st = ctx->fail(B200_ERR_CUDA, "copy"); break; }
+            st = ntt_run(ctx, pk->d0, dst, 0, 1, pk->coset_pre.as<Fr>() + (size_t)k * n, nullptr, nullptr);
+        }
+    }
     // Qk back to Lagrange form (Qk.Clone().ToLagrange().ToRegular(), prove.go:398)
     if (st == B200_OK) st = fr_bitrev_copy(ctx, pk->tr(TR_QK), pk->qk_lag.as<Fr>(), d->log_n);
     if (st == B200_OK) st = ntt_run(ctx, pk->d0, pk->qk_lag.as<Fr>(), 0, 1, nullptr, nullptr, nullptr);
@@ -399,9 +429,28 @@ int b200_plonk_pk_free(b200_ctx* ctx, b200_plonk_pk* pk) {
 
 int b200_plonk_prove(b200_ctx* ctx, const b200_plonk_pk* pk, const uint64_t* l, const uint64_t* r, const uint64_t* o,
                      const uint64_t* public_witness, const uint64_t* blinding, b200_plonk_proof* out, b200_plonk_timings* tm) {
+    return b200_plonk_prove_bsb22(ctx, pk, l, r, o, public_witness, blinding, nullptr, out, tm);
+}
+
+int b200_plonk_prove_bsb22(b200_ctx* ctx, const b200_plonk_pk* pk, const uint64_t* l, const uint64_t* r, const uint64_t* o,
+                           const uint64_t* public_witness, const uint64_t* blinding, const b200_plonk_bsb22* bsb,
+                           b200_plonk_proof* out, b200_plonk_timings* tm) {
     if (!ctx) return B200_ERR_ARG;
     if (cudaSetDevice(ctx->device) != cudaSuccess) return ctx->fail(B200_ERR_CUDA, "cudaSetDevice");
     if (!pk || !l || !r || !o || !out || (pk->nb_public && !public_witness)) return ctx->fail(B200_ERR_ARG, "null argument");
+    const uint32_t nb = pk->nb_bsb;
+    if (nb && (!bsb || !bsb->pi2 || !bsb->commitments || !bsb->values)) return ctx->fail(B200_ERR_ARG, "the key has BSB22 commitments: bsb is required");
+    G1Affine bsb_com[B200_PLONK_MAX_BSB22];
+    Fr bsb_val[B200_PLONK_MAX_BSB22];
+    Fr *pi2_br[B200_PLONK_MAX_BSB22], *pi2_cn[B200_PLONK_MAX_BSB22], *pi2_ev[B200_PLONK_MAX_BSB22];
+    for (uint32_t k = 0; k < nb; ++k) {
+        if (!bsb->pi2[k]) return ctx->fail(B200_ERR_ARG, "null Pi2 column");
+        memcpy(&bsb_com[k], bsb->commitments + 8 * k, sizeof(G1Affine));
+        memcpy(bsb_val[k].l, bsb->values + 4 * k, 32);
+        pi2_br[k] = pk->bsb_work.as<Fr>() + (size_t)(3 * k) * pk->n;
+        pi2_cn[k] = pi2_br[k] + pk->n;
+        pi2_ev[k] = pi2_cn[k] + pk->n;
+    }
     const size_t n = pk->n, N4 = n + 4, big = pk->big;
     const unsigned log_n = pk->log_n;
     cudaStream_t s = ctx->stream;
@@ -448,6 +497,8 @@ int b200_plonk_prove(b200_ctx* ctx, const b200_plonk_pk* pk, const uint64_t* l, 
         B2_CUDA(ctx, cudaMemcpyAsync(v[k], src[k], n * sizeof(Fr), cudaMemcpyDefault, ctx->copy_stream));
         B2_CUDA(ctx, cudaEventRecord(ev_cp[k], ctx->copy_stream));
     }
+    for (uint32_t k = 0; k < nb; ++k)
+        B2_CUDA(ctx, cudaMemcpyAsync(pi2_br[k], bsb->pi2[k], n * sizeof(Fr), cudaMemcpyDefault, ctx->copy_stream));
     B2_CUDA(ctx, cudaEventRecord(ev_t[1], ctx->copy_stream));
     G1Affine lro[3];
     const Fr* bps[3] = {bl, br, bo};
@@ -461,6 +512,7 @@ int b200_plonk_prove(b200_ctx* ctx, const b200_plonk_pk* pk, const uint64_t* l, 
             B2_TRY(commit_many(ctx, pk->srs_lag, sc, cnt, 3, c));
         }
         for (int k = 0; k < 3; ++k) B2_CUDA(ctx, cudaStreamWaitEvent(s, ev_cp[k], 0));
+        B2_CUDA(ctx, cudaStreamWaitEvent(s, ev_t[1], 0));
         for (int k = 0; k < 3; ++k) {
             c[k].add(commit_blinding(pk, bps[k], 2));
             lro[k] = c[k].to_affine();
@@ -473,6 +525,7 @@ int b200_plonk_prove(b200_ctx* ctx, const b200_plonk_pk* pk, const uint64_t* l, 
     // ---- gamma, beta (deriveGammaAndBeta, prove.go:455-485; bindPublicData, verify.go:296-340) -----------
     Transcript fs({"gamma", "beta", "alpha", "zeta"});
     for (int k = 0; k < 8; ++k) bind_point(fs, "gamma", pk->vk_pts[k]);
+    for (uint32_t k = 0; k < nb; ++k) bind_point(fs, "gamma", pk->vk_qcp[k]);
     for (const Fr& x : pub) bind_fr(fs, "gamma", x);
     for (int k = 0; k < 3; ++k) bind_point(fs, "gamma", lro[k]);
     const Fr gamma = derive(fs, "gamma");
@@ -490,6 +543,7 @@ int b200_plonk_prove(b200_ctx* ctx, const b200_plonk_pk* pk, const uint64_t* l, 
         z_com = c.to_affine();
     }
     lap(T.commit_z_ms);
+    for (uint32_t k = 0; k < nb; ++k) bind_point(fs, "alpha", bsb_com[k]);     // deriveAlpha, prove.go:504-512
     bind_point(fs, "alpha", z_com);
     const Fr alpha = derive(fs, "alpha");
 
@@ -497,13 +551,19 @@ int b200_plonk_prove(b200_ctx* ctx, const b200_plonk_pk* pk, const uint64_t* l, 
     // canonical forms: FFTInverse(DIF) leaves the coefficients bit-reversed, which is what the coset DIT wants
     B2_CUDA(ctx, cudaMemcpyAsync(qk_br, pk->qk_lag.p, n * sizeof(Fr), cudaMemcpyDeviceToDevice, s));
     if (pk->nb_public) B2_CUDA(ctx, cudaMemcpyAsync(qk_br, pub.data(), pk->nb_public * sizeof(Fr), cudaMemcpyHostToDevice, s));   // completeQk
+    for (uint32_t k = 0; k < nb; ++k)      // qkCoeffs[nbPublic + CommitmentIndex] = commitmentVal, prove.go:415-417
+        B2_CUDA(ctx, cudaMemcpyAsync(qk_br + pk->commit_row[k], bsb_val[k].l, sizeof(Fr), cudaMemcpyHostToDevice, s));
     for (int k = 0; k < 4; ++k) B2_TRY(ntt_gnark(ctx, d0, v[k], 1, B200_DIF, 0));
     B2_TRY(ntt_gnark(ctx, d0, qk_br, 1, B200_DIF, 0));
     for (int k = 0; k < 4; ++k) B2_TRY(fr_bitrev_copy(ctx, v[k], cn[k], log_n));   // regular layout, for the openings
+    for (uint32_t k = 0; k < nb; ++k) {                                            // cCommitments[i].ToCanonical, prove.go:339
+        B2_TRY(ntt_gnark(ctx, d0, pi2_br[k], 1, B200_DIF, 0));
+        B2_TRY(fr_bitrev_copy(ctx, pi2_br[k], pi2_cn[k], log_n));
+    }
     {
         PlonkRowArgs a;
         memset(&a, 0, sizeof a);
-        a.nb_bsb = 0;
+        a.nb_bsb = nb;
         a.beta = beta; a.gamma = gamma; a.alpha = alpha;
         a.cs = d1->coset;
         a.css = a.cs * a.cs;
@@ -526,6 +586,12 @@ int b200_plonk_prove(b200_ctx* ctx, const b200_plonk_pk* pk, const uint64_t* l, 
             for (int p = 0; p < 5; ++p) {
                 B2_CUDA(ctx, cudaMemcpyAsync(tmp[p], srcs[p], n * sizeof(Fr), cudaMemcpyDeviceToDevice, s));
                 B2_TRY(ntt_run(ctx, d0, tmp[p], 0, 1, pre, nullptr, nullptr));
+            }
+            for (uint32_t p = 0; p < nb; ++p) {
+                B2_CUDA(ctx, cudaMemcpyAsync(pi2_ev[p], pi2_br[p], n * sizeof(Fr), cudaMemcpyDeviceToDevice, s));
+                B2_TRY(ntt_run(ctx, d0, pi2_ev[p], 0, 1, pre, nullptr, nullptr));
+                a.qci[2 * p] = pk->qcp_e(k, p);
+                a.qci[2 * p + 1] = pi2_ev[p];
             }
             B2_TRY(fr_scaled_omega(ctx, d0, beta * coset, idv));
             a.x[PID_L] = tmp[0]; a.x[PID_R] = tmp[1]; a.x[PID_O] = tmp[2]; a.x[PID_Z] = tmp[3]; a.x[PID_ZS] = nullptr;
@@ -584,13 +650,16 @@ int b200_plonk_prove(b200_ctx* ctx, const b200_plonk_pk* pk, const uint64_t* l, 
     B2_TRY(fr_poly_eval(ctx, cn[2], n + 2, zeta, &boz));
     B2_TRY(fr_poly_eval(ctx, pk->tr(TR_S1), n, zeta, &s1z));
     B2_TRY(fr_poly_eval(ctx, pk->tr(TR_S2), n, zeta, &s2z));
+    Fr qcpz[B200_PLONK_MAX_BSB22];
+    for (uint32_t k = 0; k < nb; ++k) B2_TRY(fr_poly_eval(ctx, pk->qcp_c(k), n, zeta, &qcpz[k]));     // prove.go:724-729
     Fr* lin = tmp[2];
     {
         PlonkLinArgs a;
         memset(&a, 0, sizeof a);
         a.bz = cn[3]; a.s3 = pk->tr(TR_S3); a.ql = pk->tr(TR_QL); a.qr = pk->tr(TR_QR); a.qm = pk->tr(TR_QM); a.qo = pk->tr(TR_QO);
         a.qk = pk->tr(TR_QK);
-        a.nb_bsb = 0;
+        a.nb_bsb = nb;
+        for (uint32_t k = 0; k < nb; ++k) { a.pi2[k] = pi2_cn[k]; a.qcp_zeta[k] = qcpz[k]; }
         a.rl = brz * blz;
         a.c1 = (s1z * beta + blz + gamma) * (s2z * beta + brz + gamma) * zu * beta;
         const Fr u = d0->coset, uz = zeta * u, uuz = uz * u;
@@ -624,7 +693,9 @@ int b200_plonk_prove(b200_ctx* ctx, const b200_plonk_pk* pk, const uint64_t* l, 
         bind_fr(g, "gamma", zeta);
         const G1Affine* dg[7] = {&fh_digest, &lin_digest, &lro[0], &lro[1], &lro[2], &pk->vk_pts[0], &pk->vk_pts[1]};
         for (int k = 0; k < 7; ++k) bind_point(g, "gamma", *dg[k]);
+        for (uint32_t k = 0; k < nb; ++k) bind_point(g, "gamma", pk->vk_qcp[k]);
         for (int k = 0; k < 7; ++k) bind_fr(g, "gamma", claimed[k]);
+        for (uint32_t k = 0; k < nb; ++k) bind_fr(g, "gamma", qcpz[k]);
         bind_fr(g, "gamma", zu);
         gk = derive(g, "gamma");
     }
@@ -636,7 +707,8 @@ int b200_plonk_prove(b200_ctx* ctx, const b200_plonk_pk* pk, const uint64_t* l, 
         const size_t ls[7] = {n + 2, n + 3, n + 2, n + 2, n + 2, n, n};
         Fr acc = Fr::one();
         for (int k = 0; k < 7; ++k) { a.p[k] = ps[k]; a.len[k] = (uint32_t)ls[k]; a.g[k] = acc; acc = acc * gk; }
-        a.count = 7; a.width = (uint32_t)(n + 3);
+        for (uint32_t k = 0; k < nb; ++k) { a.p[7 + k] = pk->qcp_c(k); a.len[7 + k] = (uint32_t)n; a.g[7 + k] = acc; acc = acc * gk; }
+        a.count = 7 + nb; a.width = (uint32_t)(n + 3);
         a.out = folded;
         B2_TRY(plonk_fold_polys(ctx, a));
     }
@@ -659,20 +731,25 @@ int b200_plonk_prove(b200_ctx* ctx, const b200_plonk_pk* pk, const uint64_t* l, 
     put_fr(out->zshift_value, zu);
     put_fr(out->challenges[0], gamma); put_fr(out->challenges[1], beta); put_fr(out->challenges[2], alpha);
     put_fr(out->challenges[3], zeta); put_fr(out->challenges[4], gk);
+    out->nb_bsb22 = nb;
+    for (uint32_t k = 0; k < nb; ++k) { put_fr(out->claimed_qcp[k], qcpz[k]); put_point(out->bsb22[k], bsb_com[k]); }
     if (tm) *tm = T;
     return B200_OK;
 }
 
-int b200_plonk_derive_challenges(const uint64_t* vk_commitments, const uint64_t* public_witness, size_t nb_public,
+int b200_plonk_derive_challenges(const uint64_t* vk_commitments, const uint64_t* vk_qcp, const uint64_t* public_witness, size_t nb_public,
                                  const b200_plonk_proof* p, uint64_t* out) {
     if (!vk_commitments || !p || !out || (nb_public && !public_witness)) return B200_ERR_ARG;
+    if (p->nb_bsb22 > B200_PLONK_MAX_BSB22 || (p->nb_bsb22 && !vk_qcp)) return B200_ERR_ARG;
     auto pt = [](const uint64_t* src) { G1Affine a; memcpy(&a, src, sizeof a); return a; };
     Transcript fs({"gamma", "beta", "alpha", "zeta"});
     for (int k = 0; k < 8; ++k) bind_point(fs, "gamma", pt(vk_commitments + 8 * k));
+    for (uint64_t k = 0; k < p->nb_bsb22; ++k) bind_point(fs, "gamma", pt(vk_qcp + 8 * k));
     for (size_t k = 0; k < nb_public; ++k) { Fr x; memcpy(x.l, public_witness + 4 * k, 32); bind_fr(fs, "gamma", x); }
     for (int k = 0; k < 3; ++k) bind_point(fs, "gamma", pt(p->lro[k]));
     put_fr(out, derive(fs, "gamma"));
     put_fr(out + 4, derive(fs, "beta"));
+    for (uint64_t k = 0; k < p->nb_bsb22; ++k) bind_point(fs, "alpha", pt(p->bsb22[k]));
     bind_point(fs, "alpha", pt(p->z));
     put_fr(out + 8, derive(fs, "alpha"));
     for (int k = 0; k < 3; ++k) bind_point(fs, "zeta", pt(p->h[k]));
@@ -681,19 +758,24 @@ int b200_plonk_derive_challenges(const uint64_t* vk_commitments, const uint64_t*
 }
 
 int b200_plonk_proof_bytes(const b200_plonk_proof* p, uint8_t* out, size_t cap) {
-    if (!p || !out || cap < 552) return B200_ERR_ARG;
+    if (!p || !out || p->nb_bsb22 > B200_PLONK_MAX_BSB22) return B200_ERR_ARG;
+    const uint32_t nb = (uint32_t)p->nb_bsb22;
+    if (cap < 552 + 64 * (size_t)nb) return B200_ERR_ARG;
     auto pt = [](const uint64_t* src) { G1Affine a; memcpy(&a, src, sizeof a); return a; };
     auto fr = [](const uint64_t* src) { Fr a; memcpy(a.l, src, 32); return a; };
+    auto be32 = [](uint8_t* q, uint32_t v) { q[0] = (uint8_t)(v >> 24); q[1] = (uint8_t)(v >> 16); q[2] = (uint8_t)(v >> 8); q[3] = (uint8_t)v; };
     uint8_t* q = out;
     for (int k = 0; k < 3; ++k) { g1_compress(pt(p->lro[k]), q); q += 32; }
     g1_compress(pt(p->z), q); q += 32;
     for (int k = 0; k < 3; ++k) { g1_compress(pt(p->h[k]), q); q += 32; }
     g1_compress(pt(p->batched_h), q); q += 32;
-    q[0] = 0; q[1] = 0; q[2] = 0; q[3] = 7; q += 4;                        // []fr.Element: u32 BE length
+    be32(q, 7 + nb); q += 4;                                                // []fr.Element: u32 BE length
     for (int k = 0; k < 7; ++k) { fr_be(fr(p->claimed[k]), q); q += 32; }
+    for (uint32_t k = 0; k < nb; ++k) { fr_be(fr(p->claimed_qcp[k]), q); q += 32; }
     g1_compress(pt(p->zshift_h), q); q += 32;
     fr_be(fr(p->zshift_value), q); q += 32;
-    memset(q, 0, 4); q += 4;                                               // len(Bsb22Commitments) = 0
+    be32(q, nb); q += 4;                                                    // Bsb22Commitments
+    for (uint32_t k = 0; k < nb; ++k) { g1_compress(pt(p->bsb22[k]), q); q += 32; }
     return (int)(q - out);
 }
 

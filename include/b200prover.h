@@ -347,13 +347,14 @@ int b200_groth16_proof_bytes(const uint64_t *ar_affine, const uint64_t *bs_affin
                              uint8_t *out, size_t out_cap);
 
 /* ---- PlonK prover (BN254) ---------------------------------------------------------------------
- * plonk_bn254.Prove (/root/reference/backend/plonk/bn254/prove.go:116-180) behind one call, for the
- * circuits of configs 1-5 (no BSB22 commitments: api.Commit circuits return B200_ERR_UNSUPPORTED at
- * upload).  The solver stays with the caller (prove.go:365-392 gives L, R, O); everything after it
+ * plonk_bn254.Prove (/root/reference/backend/plonk/bn254/prove.go:116-180) behind one call, with or
+ * without BSB22 commitments (api.Commit circuits, at most B200_PLONK_MAX_BSB22 of them).  The solver stays
+ * with the caller (prove.go:365-392 gives L, R, O); everything after it
  * runs here: the ten KZG commitments (G1 MSMs against two resident SRS), the copy-constraint ratio,
  * the quotient over the rho cosets of the big domain, the openings, and the Fiat-Shamir transcript
  * (SHA-256, host) that orders them. */
 typedef struct b200_plonk_pk b200_plonk_pk;
+#define B200_PLONK_MAX_BSB22 8
 
 /* What the glue reads out of plonk_bn254.ProvingKey (setup.go:79-107).  All pointers are host memory. */
 typedef struct b200_plonk_pk_desc {
@@ -369,7 +370,10 @@ typedef struct b200_plonk_pk_desc {
     const uint64_t *kzg_lagrange_g1;/* pk.KzgLagrange.G1: n affine points                                   */
     const uint64_t *vk_commitments; /* pk.Vk.S[0], S[1], S[2], Ql, Qr, Qm, Qo, Qk: 8 affine points          */
     size_t nb_public;               /* pk.Vk.NbPublicVariables                                              */
-    size_t nb_bsb22;                /* len(pk.Vk.Qcp); must be 0                                            */
+    size_t nb_bsb22;                /* len(pk.Vk.Qcp) = len(spr.CommitmentInfo), <= B200_PLONK_MAX_BSB22      */
+    const uint64_t *const *qcp;     /* pk.trace.Qcp[i]: canonical / regular, n each (NULL when nb_bsb22 = 0)  */
+    const uint64_t *vk_qcp;         /* pk.Vk.Qcp: nb_bsb22 affine points                                     */
+    const size_t *commitment_index; /* CommitmentInfo[i].CommitmentIndex (constraint index; the row is + nb_public) */
 } b200_plonk_pk_desc;
 
 /* One-time residency: trace polynomials, their evaluations on the rho cosets of the big domain
@@ -388,7 +392,20 @@ typedef struct b200_plonk_proof {
     uint64_t zshift_h[8];           /* ZShiftedOpening.H                                                    */
     uint64_t zshift_value[4];       /* ZShiftedOpening.ClaimedValue                                         */
     uint64_t challenges[5][4];      /* gamma, beta, alpha, zeta, KZG folding gamma (for tests; not serialised) */
+    uint64_t nb_bsb22;              /* len(Bsb22Commitments)                                                */
+    uint64_t claimed_qcp[B200_PLONK_MAX_BSB22][4];   /* BatchedProof.ClaimedValues[7:]: Qcp_i(zeta)          */
+    uint64_t bsb22[B200_PLONK_MAX_BSB22][8];         /* Bsb22Commitments                                     */
 } b200_plonk_proof;
+
+/* What the solver's bsb22Hint (prove.go:303-352) produced for an api.Commit circuit: for each commitment the
+ * committed-values column in Lagrange / regular form (s.cCommitments[i] before ToCanonical; n elements), its
+ * KZG commitment against pk.KzgLagrange (the hint can compute it with b200_msm_resident / b200_kzg_commit_dev)
+ * and the hashed value injected in Qk (s.commitmentVal[i]). */
+typedef struct b200_plonk_bsb22 {
+    const uint64_t *const *pi2;     /* nb_bsb22 host vectors                                                */
+    const uint64_t *commitments;    /* nb_bsb22 affine points                                               */
+    const uint64_t *values;         /* nb_bsb22 Fr                                                          */
+} b200_plonk_bsb22;
 
 typedef struct b200_plonk_timings {
     float h2d_ms, commit_lro_ms, ratio_ms, commit_z_ms, quotient_ms, commit_h_ms, open_z_ms, linearize_ms,
@@ -402,15 +419,19 @@ typedef struct b200_plonk_timings {
 int b200_plonk_prove(b200_ctx *ctx, const b200_plonk_pk *pk, const uint64_t *l, const uint64_t *r, const uint64_t *o,
                      const uint64_t *public_witness, const uint64_t *blinding, b200_plonk_proof *out,
                      b200_plonk_timings *timings);
+/* Same for a key with BSB22 commitments (bsb may be NULL when the key has none). */
+int b200_plonk_prove_bsb22(b200_ctx *ctx, const b200_plonk_pk *pk, const uint64_t *l, const uint64_t *r, const uint64_t *o,
+                           const uint64_t *public_witness, const uint64_t *blinding, const b200_plonk_bsb22 *bsb,
+                           b200_plonk_proof *out, b200_plonk_timings *timings);
 
 /* The four Fiat-Shamir challenges gamma, beta, alpha, zeta (16 u64, Montgomery) of a proof's commitments:
  * bindPublicData + deriveRandomness (plonk/bn254/verify.go:296-360) over SHA-256, gnark-crypto's
  * fiat-shamir.Transcript layout (restated in-tree by plonk/bn254/solidity.go:407-538).  Host only. */
-int b200_plonk_derive_challenges(const uint64_t *vk_commitments, const uint64_t *public_witness, size_t nb_public,
-                                 const b200_plonk_proof *proof, uint64_t *out);
+int b200_plonk_derive_challenges(const uint64_t *vk_commitments, const uint64_t *vk_qcp, const uint64_t *public_witness,
+                                 size_t nb_public, const b200_plonk_proof *proof, uint64_t *out);
 
-/* Proof.WriteTo (plonk/bn254/marshal.go:41-66): 8 compressed G1 | u32 7 | 7 Fr | G1 | Fr | u32 0 = 552
- * bytes.  Returns the number of bytes written or a negative status. */
+/* Proof.WriteTo (plonk/bn254/marshal.go:41-66): 8 compressed G1 | u32 7+k | (7+k) Fr | G1 | Fr | u32 k | k G1
+ * = 552 + 64 k bytes for k BSB22 commitments.  Returns the number of bytes written or a negative status. */
 int b200_plonk_proof_bytes(const b200_plonk_proof *proof, uint8_t *out, size_t out_cap);
 
 #if defined(__GNUC__)

@@ -22,7 +22,9 @@ gnark-crypto pieces that are absent and restated from their call sites plus an I
   KNOWN tau, so a commitment is [p(tau)]G1 (one scalar multiplication) and an opening check is
   C - [v]G1 == [tau - z]H, pairing-free and equivalent to kzg.Verify accepting.
 
-BSB22 commitments (api.Commit circuits) are not restated: configs 1-5 have none.
+BSB22 commitments (api.Commit circuits, prove.go:303-352, frontend/cs/scs/api.go:623-655) are restated too: Qcp / Pi2
+columns, the commitment hint (kzg.Commit against KzgLagrange + hash_to_field: RFC 9380 expand_message_xmd over SHA-256
+with DST "BSB22-Plonk", gnark-crypto fr/hash_to_field -- absent, unpinned) and the verifier's extra PI term.
 """
 import hashlib
 from dataclasses import dataclass, field
@@ -45,6 +47,8 @@ class SparseR1CS:
     nb_internal: int
     # one tuple per constraint: (qL, qR, qM, qO, qC, xa, xb, xc)   qL*a + qR*b + qM*a*b + qO*c + qC = 0
     constraints: list = field(default_factory=list)
+    # constraint.PlonkCommitments: [{"committed": [constraint indices], "index": constraint index}]
+    commitments: list = field(default_factory=list)
 
     @property
     def nb_variables(self):
@@ -62,6 +66,87 @@ def mul_chain_scs(nb_mul: int) -> SparseR1CS:
         cur = new
     spr.constraints.append((1, R - 1, 0, 0, 0, cur, 0, 0))
     return spr
+
+
+def commit_chain_scs(nb_mul: int, nb_commit: int = 1) -> SparseR1CS:
+    """A Mul chain that also calls api.Commit (frontend/cs/scs/api.go:623-655) nb_commit times on (X, x_1), multiplies
+    the chain's end by every commitment value and asserts the product equals the public Y.
+    Wires: 0 = Y, 1 = X, then internal: chain, then per commitment (c_k, product)."""
+    spr = SparseR1CS(1, 1, 0)
+    nxt = 2
+    cur = 1
+    chain = []
+    for _ in range(nb_mul):
+        spr.constraints.append((0, 0, 1, R - 1, 0, cur, cur, nxt))
+        cur = nxt
+        chain.append(cur)
+        nxt += 1
+    for k in range(nb_commit):
+        committed = []
+        for v in (1, chain[0]):                                   # - v + Qcp * Pi2 = 0   (api.go:630-636)
+            committed.append(len(spr.constraints))
+            spr.constraints.append((R - 1, 0, 0, 0, 0, v, 0, 0))
+        c = nxt
+        nxt += 1
+        index = len(spr.constraints)
+        spr.constraints.append((R - 1, 0, 0, 0, 0, c, 0, 0))      # - c + qk = 0, qk injected by the prover (api.go:646-649)
+        spr.commitments.append({"committed": committed, "index": index})
+        spr.constraints.append((0, 0, 1, R - 1, 0, c, cur, nxt))  # use the commitment
+        cur = nxt
+        nxt += 1
+    spr.constraints.append((1, R - 1, 0, 0, 0, cur, 0, 0))
+    spr.nb_internal = nxt - 2
+    return spr
+
+
+def expand_message_xmd(msg: bytes, dst: bytes, length: int) -> bytes:
+    """RFC 9380 5.3.1 with SHA-256."""
+    ell = (length + 31) // 32
+    dst_prime = dst + bytes([len(dst)])
+    b0 = hashlib.sha256(bytes(64) + msg + length.to_bytes(2, "big") + b"\x00" + dst_prime).digest()
+    bi = hashlib.sha256(b0 + b"\x01" + dst_prime).digest()
+    out = bi
+    for i in range(2, ell + 1):
+        bi = hashlib.sha256(bytes(a ^ b for a, b in zip(b0, bi)) + bytes([i]) + dst_prime).digest()
+        out += bi
+    return out[:length]
+
+
+def hash_commitment(point) -> int:
+    """bsb22Hint's tail (prove.go:341-350): hash_to_field("BSB22-Plonk") of the commitment's Marshal()."""
+    return int.from_bytes(expand_message_xmd(g1_raw(point), b"BSB22-Plonk", 48), "big") % R
+
+
+def commit_chain_solution(spr: SparseR1CS, pk, x: int, bsb_blinding):
+    """Solver + bsb22Hint (prove.go:303-352) for commit_chain_scs.  bsb_blinding[k] = the two values SetRandom
+    draws for commitment k (prove.go:329,332).  Returns (solution, bsb dict for prove())."""
+    vals = [0] * spr.nb_variables
+    vals[1] = x % R
+    n = pk.d0.cardinality
+    off = spr.nb_public
+    _, lag = srs_scalars(pk)
+    bsb = {"pi2": [], "commitments": [], "values": []}
+    depth = 0
+    for j, c in enumerate(spr.constraints):
+        info = spr.commitments[depth] if depth < len(spr.commitments) else None
+        if info is not None and j == info["index"]:
+            cv = [0] * n
+            for row in info["committed"]:
+                cv[off + row] = vals[spr.constraints[row][5]]
+            cv[off + info["index"]] = bsb_blinding[depth][0]
+            cv[off + len(spr.constraints) - 1] = bsb_blinding[depth][1]
+            com = g1_gen_mul(sum(a * b for a, b in zip(cv, lag)) % R)
+            h = hash_commitment(com)
+            vals[c[5]] = h
+            bsb["pi2"].append(cv)
+            bsb["commitments"].append(com)
+            bsb["values"].append(h)
+            depth += 1
+        elif c[2] == 1:                                            # a * b = c
+            vals[c[7]] = vals[c[5]] * vals[c[6]] % R
+        elif c[0] == 1 and c[1] == R - 1:                          # the final AssertIsEqual fixes Y
+            vals[0] = vals[c[5]]
+    return vals, bsb
 
 
 def mul_chain_solution(nb_mul: int, x: int = 2):
@@ -109,6 +194,8 @@ class ProvingKey:
     qk_lagrange: list   # what completeQk (prove.go:397-423) gets back by ToLagrange
     vk: dict
     tau: int
+    qcp: list = field(default_factory=list)      # trace.Qcp, canonical
+    commitments: list = field(default_factory=list)
 
 
 def build_trace(spr: SparseR1CS, size: int):
@@ -177,14 +264,21 @@ def setup(spr: SparseR1CS, tau: int) -> ProvingKey:
     s_lag = [[sup[perm[k * n + i]] for i in range(n)] for k in range(3)]
     ql, qr, qm, qo, qk = (_to_canonical(v, d0) for v in lag)
     s1, s2, s3 = (_to_canonical(v, d0) for v in s_lag)
+    qcp = []
+    for info in spr.commitments:                                   # BuildTrace, setup.go:222-229
+        col = [0] * n
+        for row in info["committed"]:
+            col[spr.nb_public + row] = 1
+        qcp.append(_to_canonical(col, d0))
     vk = {
+        "Qcp": [commit_tau(q, tau) for q in qcp], "commitment_indexes": [info["index"] for info in spr.commitments],
         "size": n, "size_inv": pow(n, -1, R), "generator": d0.generator, "nb_public": spr.nb_public,
         "coset_shift": d0.coset_gen,
         "S": [commit_tau(s1, tau), commit_tau(s2, tau), commit_tau(s3, tau)],
         "Ql": commit_tau(ql, tau), "Qr": commit_tau(qr, tau), "Qm": commit_tau(qm, tau),
         "Qo": commit_tau(qo, tau), "Qk": commit_tau(qk, tau),
     }
-    return ProvingKey(d0, d1, spr.nb_public, ql, qr, qm, qo, qk, s1, s2, s3, perm, list(lag[4]), vk, tau)
+    return ProvingKey(d0, d1, spr.nb_public, ql, qr, qm, qo, qk, s1, s2, s3, perm, list(lag[4]), vk, tau, qcp, list(spr.commitments))
 
 
 def srs_scalars(pk: ProvingKey):
@@ -240,6 +334,8 @@ def bind_public_data(fs, name, vk, public):
     """verify.go:296-340."""
     for p in (vk["S"][0], vk["S"][1], vk["S"][2], vk["Ql"], vk["Qr"], vk["Qm"], vk["Qo"], vk["Qk"]):
         fs.Bind(name, g1_raw(p))
+    for p in vk.get("Qcp", []):
+        fs.Bind(name, g1_raw(p))
     for w in public:
         fs.Bind(name, fr_bytes(w))
 
@@ -276,6 +372,7 @@ class Proof:
     claimed: list          # BatchedProof.ClaimedValues (7)
     zshift_H: tuple
     zshift_value: int
+    bsb22: list = field(default_factory=list)      # Bsb22Commitments
 
 
 def _commit_blinded_lagrange(p_lagrange, bp, pk: ProvingKey):
@@ -300,10 +397,14 @@ def _kzg_open(p, point, tau):
     return commit_tau(q, tau), v
 
 
-def prove(spr: SparseR1CS, pk: ProvingKey, solution, blinding):
+def prove(spr: SparseR1CS, pk: ProvingKey, solution, blinding, bsb=None):
     """Prove, prove.go:116-180.  blinding = (bl[2], br[2], bo[2], bz[3]) -- getRandomPolynomial's
     coefficients, injected (the reference draws them from crypto/rand, prove.go:295-301).
-    Returns (Proof, challenges dict)."""
+    bsb: {"pi2": Lagrange columns, "commitments": points, "values": hashed commitments} from the solver's
+    bsb22Hint for api.Commit circuits.  Returns (Proof, challenges dict)."""
+    bsb = bsb or {"pi2": [], "commitments": [], "values": []}
+    nb_bsb = len(bsb["pi2"])
+    assert nb_bsb == len(pk.qcp)
     d0, d1, tau = pk.d0, pk.d1, pk.tau
     n, big = d0.cardinality, d1.cardinality
     rho = big // n
@@ -318,6 +419,8 @@ def prove(spr: SparseR1CS, pk: ProvingKey, solution, blinding):
     # completeQk (prove.go:397-423)
     qk_lag = list(pk.qk_lagrange)
     qk_lag[:spr.nb_public] = public
+    for info, val in zip(pk.commitments, bsb["values"]):
+        qk_lag[spr.nb_public + info["index"]] = val
 
     # deriveGammaAndBeta (prove.go:455-485)
     fs = Transcript("gamma", "beta", "alpha", "zeta")
@@ -328,7 +431,7 @@ def prove(spr: SparseR1CS, pk: ProvingKey, solution, blinding):
     # buildRatioCopyConstraint (prove.go:597-631)
     Z = PB.build_ratio_copy_constraint([L, Rr, O], pk.perm, beta, gamma, d0)
     z_com = _commit_blinded_lagrange(Z, bz, pk)
-    alpha = derive_randomness(fs, "alpha", z_com)
+    alpha = derive_randomness(fs, "alpha", *bsb["commitments"], z_com)     # deriveAlpha, prove.go:504-512
 
     # evaluateConstraints -> computeNumerator (prove.go:521-595, 837-1079), literally: every polynomial
     # goes ToCanonical -> scaled -> ToLagrange on each of the rho cosets
@@ -348,6 +451,10 @@ def prove(spr: SparseR1CS, pk: ProvingKey, solution, blinding):
     canon[PB.ID_QL], canon[PB.ID_QR], canon[PB.ID_QM], canon[PB.ID_QO] = pk.ql, pk.qr, pk.qm, pk.qo
     canon[PB.ID_S1], canon[PB.ID_S2], canon[PB.ID_S3] = pk.s1, pk.s2, pk.s3
     canon[PB.ID_ID] = ident
+    pi2_canon = [_to_canonical(v, d0) for v in bsb["pi2"]]
+    for k in range(nb_bsb):                                # x[id_Qci + 2k] = Qcp_k, x[id_Qci + 2k + 1] = Pi2_k
+        canon[PB.ID_QCI + 2 * k] = pk.qcp[k]
+        canon[PB.ID_QCI + 2 * k + 1] = pi2_canon[k]
     cres = [0] * big
     shifters = [d1.coset_gen] + [d1.generator] * (rho - 1)
     coset = 1
@@ -366,7 +473,7 @@ def prove(spr: SparseR1CS, pk: ProvingKey, solution, blinding):
             N.fft(a, d0, N.DIF)
             N.bit_reverse(a)
             ev[k] = a
-        PB.quotient_rows(ev, [], d0, d1.log_n, i, beta, gamma, alpha, d1.coset_gen, bps[0], bps[1], bps[2], bps[3], cres)
+        PB.quotient_rows(ev, [ev[PB.ID_QCI + k] for k in range(2 * nb_bsb)], d0, d1.log_n, i, beta, gamma, alpha, d1.coset_gen, bps[0], bps[1], bps[2], bps[3], cres)
         inv = pow(tmp, -1, R)
         for q in bps:
             for j in range(len(q)):
@@ -395,6 +502,7 @@ def prove(spr: SparseR1CS, pk: ProvingKey, solution, blinding):
     brz = (PB.poly_eval(canon[PB.ID_R], zeta) + PB.poly_eval(br, zeta) * zn1) % R
     boz = (PB.poly_eval(canon[PB.ID_O], zeta) + PB.poly_eval(bo, zeta) * zn1) % R
     s1z, s2z = PB.poly_eval(pk.s1, zeta), PB.poly_eval(pk.s2, zeta)
+    qcpz = [PB.poly_eval(q, zeta) for q in pk.qcp]
     rl = brz * blz % R
     c1 = (s1z * beta + blz + gamma) * ((s2z * beta + brz + gamma) % R) % R * zu % R * beta % R
     u = vk["coset_shift"]
@@ -409,13 +517,15 @@ def prove(spr: SparseR1CS, pk: ProvingKey, solution, blinding):
         t = t * alpha % R
         if i < n:
             t = (t + pk.qm[i] * rl + pk.ql[i] * blz + pk.qr[i] * brz + pk.qo[i] * boz + pk.qk[i]) % R
+            for j in range(nb_bsb):
+                t = (t + pi2_canon[j][i] * qcpz[j]) % R
         lin.append((t + blinded_z[i] * lag) % R)
     lin_digest = commit_tau(lin, tau)
 
     # batchOpening (prove.go:779-833) -> kzg.BatchOpenSinglePoint
     polys = [folded_h, lin, _blinded_coefficients(canon[PB.ID_L], bl), _blinded_coefficients(canon[PB.ID_R], br),
-             _blinded_coefficients(canon[PB.ID_O], bo), pk.s1, pk.s2]
-    digests = [folded_h_digest, lin_digest, lro_com[0], lro_com[1], lro_com[2], vk["S"][0], vk["S"][1]]
+             _blinded_coefficients(canon[PB.ID_O], bo), pk.s1, pk.s2] + list(pk.qcp)
+    digests = [folded_h_digest, lin_digest, lro_com[0], lro_com[1], lro_com[2], vk["S"][0], vk["S"][1]] + list(vk["Qcp"])
     claimed = [PB.poly_eval(p, zeta) for p in polys]
     g = derive_gamma_kzg(zeta, digests, claimed, [fr_bytes(zu)])
     width = max(len(p) for p in polys)
@@ -428,7 +538,7 @@ def prove(spr: SparseR1CS, pk: ProvingKey, solution, blinding):
     q, _ = PB.poly_div_linear(folded, zeta)
     batched_H = commit_tau(q, tau)
 
-    proof = Proof(lro_com, z_com, h_com, batched_H, claimed, zs_H, zu)
+    proof = Proof(lro_com, z_com, h_com, batched_H, claimed, zs_H, zu, list(bsb["commitments"]))
     return proof, {"gamma": gamma, "beta": beta, "alpha": alpha, "zeta": zeta, "gamma_kzg": g}
 
 
@@ -447,7 +557,7 @@ def verify(proof: Proof, vk: dict, public, tau: int) -> bool:
     bind_public_data(fs, "gamma", vk, public)
     gamma = derive_randomness(fs, "gamma", *proof.LRO)
     beta = derive_randomness(fs, "beta")
-    alpha = derive_randomness(fs, "alpha", proof.Z)
+    alpha = derive_randomness(fs, "alpha", *proof.bsb22, proof.Z)
     zeta = derive_randomness(fs, "zeta", *proof.H)
     n = vk["size"]
     zeta_m = pow(zeta, n, R)
@@ -463,8 +573,13 @@ def verify(proof: Proof, vk: dict, public, tau: int) -> bool:
             wpow = wpow * vk["generator"] % R
             den = (zeta - wpow) % R
             lagrange = lagrange * pow(den, -1, R) % R
+    for k, ci in enumerate(vk.get("commitment_indexes", [])):          # verify.go:136-156
+        hashed = hash_commitment(proof.bsb22[k])
+        wpi = pow(vk["generator"], vk["nb_public"] + ci, R)
+        lag_i = (zeta - 1) * wpi % R * pow((zeta - wpi) % R, -1, R) % R * lagrange_one % R
+        pi = (pi + lag_i * hashed) % R
     zu = proof.zshift_value
-    cq, lin_z, l, r, o, s1, s2 = proof.claimed
+    cq, lin_z, l, r, o, s1, s2 = proof.claimed[:7]
     _s1 = (s1 * beta + l + gamma) * ((s2 * beta + r + gamma) % R) % R * ((o + gamma) % R) % R * alpha % R * zu % R
     asl = lagrange_one * alpha % R * alpha % R
     t = (lin_z + pi + _s1 - asl) % R
@@ -478,12 +593,14 @@ def verify(proof: Proof, vk: dict, public, tau: int) -> bool:
     cs = vk["coset_shift"]
     u2 = (beta * zeta + l + gamma) * ((beta * zeta % R * cs + r + gamma) % R) % R * ((beta * zeta % R * cs % R * cs + o + gamma) % R) % R
     u2 = ((R - u2) * alpha + asl) % R
-    points = [vk["Ql"], vk["Qr"], vk["Qm"], vk["Qo"], vk["Qk"], vk["S"][2], proof.Z]
-    scalars = [l, r, rl, o, 1, u1, u2]
+    points = list(proof.bsb22) + [vk["Ql"], vk["Qr"], vk["Qm"], vk["Qo"], vk["Qk"], vk["S"][2], proof.Z]
+    scalars = list(proof.claimed[7:]) + [l, r, rl, o, 1, u1, u2]
     lin_digest = None
     for p, s in zip(points, scalars):
         lin_digest = B.g1_add(lin_digest, B.g1_mul(p, s))
-    digests = [folded_h, lin_digest, proof.LRO[0], proof.LRO[1], proof.LRO[2], vk["S"][0], vk["S"][1]]
+    digests = [folded_h, lin_digest, proof.LRO[0], proof.LRO[1], proof.LRO[2], vk["S"][0], vk["S"][1]] + list(vk.get("Qcp", []))
+    if len(proof.bsb22) != len(vk.get("Qcp", [])) or len(proof.claimed) != len(digests):
+        return False
     g = derive_gamma_kzg(zeta, digests, proof.claimed, [fr_bytes(zu)])        # kzg.FoldProof
     fd, fv, acc = None, 0, 1
     for dg, v in zip(digests, proof.claimed):
@@ -499,5 +616,5 @@ def proof_bytes(p: Proof) -> bytes:
     out = b"".join(g1_compress(q) for q in (*p.LRO, p.Z, *p.H, p.batched_H))
     out += len(p.claimed).to_bytes(4, "big") + b"".join(fr_bytes(v) for v in p.claimed)
     out += g1_compress(p.zshift_H) + fr_bytes(p.zshift_value)
-    out += (0).to_bytes(4, "big")
+    out += len(p.bsb22).to_bytes(4, "big") + b"".join(g1_compress(q) for q in p.bsb22)
     return out

@@ -26,7 +26,16 @@ def upload_pk(ctx, pk: PP.ProvingKey):
         log_n=pk.d0.log_n, log_big=pk.d1.log_n, generator=cref.fr(pk.d0.generator), generator_big=cref.fr(pk.d1.generator),
         coset_gen=cref.fr(pk.d0.coset_gen), ql=f(pk.ql), qr=f(pk.qr), qm=f(pk.qm), qo=f(pk.qo), qk=f(pk.qk),
         s1=f(pk.s1), s2=f(pk.s2), s3=f(pk.s3), perm=np.array(pk.perm, dtype=np.int64), kzg_g1=kzg, kzg_lagrange_g1=kzg_lag,
-        vk_commitments=util.g1_arr(vk_points(pk)), nb_public=pk.nb_public)
+        vk_commitments=util.g1_arr(vk_points(pk)), nb_public=pk.nb_public,
+        qcp=[f(q) for q in pk.qcp], vk_qcp=util.g1_arr(pk.vk["Qcp"]) if pk.qcp else None,
+        commitment_index=[c["index"] for c in pk.commitments])
+
+
+def bsb_arrays(bsb):
+    """oracle bsb dict -> the arrays Context.plonk_prove takes."""
+    if not bsb or not bsb["pi2"]:
+        return None
+    return {"pi2": [util.fr_arr(c) for c in bsb["pi2"]], "commitments": util.g1_arr(bsb["commitments"]), "values": util.fr_arr(bsb["values"])}
 
 
 def blinding_array(blinding):
@@ -50,6 +59,10 @@ def proof_to_struct(pkg, proof: PP.Proof):
     for k in range(7):
         put(s.claimed[k], util.fr_arr([proof.claimed[k]]))
     put(s.zshift_value, util.fr_arr([proof.zshift_value]))
+    s.nb_bsb22 = len(proof.bsb22)
+    for k in range(len(proof.bsb22)):
+        put(s.bsb22[k], util.g1_arr([proof.bsb22[k]]))
+        put(s.claimed_qcp[k], util.fr_arr([proof.claimed[7 + k]]))
     return s
 
 
@@ -59,5 +72,7 @@ def struct_to_proof(s) -> PP.Proof:
     def pt(a):
         p = util.g1_aff_ints(a)
         return None if p is None else (p[0], p[1])
+    nb = int(s.nb_bsb22)
     return PP.Proof([pt(d["lro"][k]) for k in range(3)], pt(d["z"]), [pt(d["h"][k]) for k in range(3)], pt(d["batched_h"]),
-                    util.fr_ints(d["claimed"]), pt(d["zshift_h"]), util.fr_ints(d["zshift_value"].reshape(1, 4))[0])
+                    util.fr_ints(s.all_claimed()), pt(d["zshift_h"]), util.fr_ints(d["zshift_value"].reshape(1, 4))[0],
+                    [pt(d["bsb22"][k]) for k in range(nb)])

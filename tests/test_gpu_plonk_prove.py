@@ -173,3 +173,31 @@ def test_large_proof_verifies(ctx, pkg):
         with open(os.path.join(out, "plonk_prove_2p%d.json" % log_n), "w") as f:
             json.dump({"log_n": log_n, "verified_by_oracle": True, "timings_ms": tm}, f, indent=1)
     print("plonk prove 2^%d:" % log_n, tm)
+
+
+@pytest.mark.parametrize("nb_mul,nb_commit", [(3, 1), (6, 2), (40, 3), (1000, 1)])
+def test_bsb22_commitment_circuits(ctx, pkg, nb_mul, nb_commit):
+    """api.Commit circuits (prove.go:303-352): Qcp / Pi2 columns through the quotient, the linearised polynomial,
+    the transcripts and the batch opening -- proof bytes identical to the oracle, accepted by its verifier."""
+    rng = random.Random(900 + nb_mul)
+    spr = PP.commit_chain_scs(nb_mul, nb_commit)
+    pk = PP.setup(spr, rng.randrange(1, R))
+    sol, bsb = PP.commit_chain_solution(spr, pk, rng.randrange(2, R), [(rng.randrange(R), rng.randrange(R)) for _ in range(nb_commit)])
+    blinding = tuple([rng.randrange(R) for _ in range(k)] for k in (2, 2, 2, 3))
+    want, ch = PP.prove(spr, pk, sol, blinding, bsb)
+    dpk = PU.upload_pk(ctx, pk)
+    try:
+        L, Rr, O = PP.evaluate_lro(spr, sol)
+        got, _ = ctx.plonk_prove(dpk, util.fr_arr(L), util.fr_arr(Rr), util.fr_arr(O), util.fr_arr(sol[:1]),
+                                 PU.blinding_array(blinding), PU.bsb_arrays(bsb))
+        fresh, _ = ctx.plonk_prove(dpk, util.fr_arr(L), util.fr_arr(Rr), util.fr_arr(O), util.fr_arr(sol[:1]), None, PU.bsb_arrays(bsb))
+        # the hint's commitment is a KZG commitment against KzgLagrange: the same resident-SRS MSM path
+        srs = ctx.upload_bases(PU.srs_arrays(pk)[1], 1)
+        vec = pkg.DeviceVector(ctx, pk.d0.cardinality * 32).upload(util.fr_arr(bsb["pi2"][0]))
+        assert util.g1_aff_ints(ctx.kzg_commit_dev(srs, vec, pk.d0.cardinality)) == list(bsb["commitments"][0])
+        vec.free(); srs.free()
+    finally:
+        dpk.free()
+    assert util.fr_ints(got.as_dict()["challenges"]) == [ch["gamma"], ch["beta"], ch["alpha"], ch["zeta"], ch["gamma_kzg"]]
+    assert pkg.plonk_proof_bytes(got) == PP.proof_bytes(want)
+    assert PP.verify(PU.struct_to_proof(fresh), pk.vk, sol[:1], pk.tau)

@@ -175,3 +175,34 @@ def test_product_side_trapdoor_verifier_agrees_with_oracle(pkg, small):
     assert not H.verify_with_trapdoor(s, vk, sol[:1], d, (pk.tau + 1) % R)
     s.claimed[3][0] ^= 1
     assert not H.verify_with_trapdoor(s, vk, sol[:1], d, pk.tau)
+
+
+def _bsb_case(nb_mul, nb_commit, seed):
+    rng = random.Random(seed)
+    spr = PP.commit_chain_scs(nb_mul, nb_commit)
+    pk = PP.setup(spr, rng.randrange(1, R))
+    sol, bsb = PP.commit_chain_solution(spr, pk, rng.randrange(2, R), [(rng.randrange(R), rng.randrange(R)) for _ in range(nb_commit)])
+    blinding = tuple([rng.randrange(R) for _ in range(k)] for k in (2, 2, 2, 3))
+    return spr, pk, sol, bsb, blinding
+
+
+@pytest.mark.parametrize("nb_mul,nb_commit", [(3, 1), (6, 2), (20, 3)])
+def test_bsb22_circuits_prove_and_verify(pkg, nb_mul, nb_commit):
+    """api.Commit circuits (frontend/cs/scs/api.go:623-655; prove.go:303-352): oracle round trip, tampered
+    commitment rejected, and the library's host transcript / marshalling with BSB22 commitments."""
+    spr, pk, sol, bsb, blinding = _bsb_case(nb_mul, nb_commit, 40 + nb_mul)
+    proof, ch = PP.prove(spr, pk, sol, blinding, bsb)
+    assert PP.verify(proof, pk.vk, sol[:1], pk.tau)
+    assert len(PP.proof_bytes(proof)) == 552 + 64 * nb_commit
+    bad = PP.Proof(proof.LRO, proof.Z, proof.H, proof.batched_H, proof.claimed, proof.zshift_H, proof.zshift_value, [proof.LRO[0]] * nb_commit)
+    assert not PP.verify(bad, pk.vk, sol[:1], pk.tau)
+    s = PU.proof_to_struct(pkg, proof)
+    assert pkg.plonk_proof_bytes(s) == PP.proof_bytes(proof)
+    got = pkg.plonk_derive_challenges(util.g1_arr(PU.vk_points(pk)), util.fr_arr(sol[:1]), s, util.g1_arr(pk.vk["Qcp"]))
+    assert util.fr_ints(got) == [ch["gamma"], ch["beta"], ch["alpha"], ch["zeta"]]
+
+
+def test_hash_to_field_expander():
+    """RFC 9380 K.1 test vector of expand_message_xmd(SHA-256), DST "QUUX-V01-CS02-with-expander-SHA256-128", msg "", 0x20 bytes."""
+    out = PP.expand_message_xmd(b"", b"QUUX-V01-CS02-with-expander-SHA256-128", 0x20)
+    assert out.hex() == "68a985b87eb6b46952128911f2a4412bbc302a9d759667f87f7a21d803f07235"

@@ -56,7 +56,7 @@ class _PlonkPkDesc(C.Structure):
                 ("qk", C.c_void_p), ("s1", C.c_void_p), ("s2", C.c_void_p), ("s3", C.c_void_p), ("perm", C.c_void_p),
                 ("kzg_g1", C.c_void_p), ("kzg_lagrange_g1", C.c_void_p), ("vk_commitments", C.c_void_p),
                 ("nb_public", C.c_size_t), ("nb_bsb22", C.c_size_t), ("qcp", C.c_void_p), ("vk_qcp", C.c_void_p),
-                ("commitment_index", C.c_void_p)]
+                ("commitment_index", C.c_void_p), ("shard_index", C.c_int), ("shard_count", C.c_int)]
 
 
 class _PlonkBsb22(C.Structure):
@@ -179,6 +179,10 @@ def load_library():
         "b200_plonk_pk_free": (i, [vp, vp]),
         "b200_plonk_prove": (i, [vp, vp, vp, vp, vp, vp, vp, C.POINTER(PlonkProof), C.POINTER(_PlonkTimings)]),
         "b200_plonk_prove_bsb22": (i, [vp, vp, vp, vp, vp, vp, vp, C.POINTER(_PlonkBsb22), C.POINTER(PlonkProof), C.POINTER(_PlonkTimings)]),
+        "b200_plonk_session_begin": (i, [vp, vp, vp, vp, vp, vp, vp, C.POINTER(_PlonkBsb22), C.POINTER(vp), vp]),
+        "b200_plonk_session_step": (i, [vp, vp, i, vp, vp]),
+        "b200_plonk_session_numerator": (i, [vp, vp, C.POINTER(vp), C.POINTER(sz), C.POINTER(u)]),
+        "b200_plonk_session_finish": (i, [vp, vp, vp, C.POINTER(PlonkProof), C.POINTER(_PlonkTimings)]),
         "b200_plonk_derive_challenges": (i, [vp, vp, vp, sz, C.POINTER(PlonkProof), vp]),
         "b200_plonk_proof_bytes": (i, [C.POINTER(PlonkProof), vp, sz]),
         "b200_profile_start": (i, [vp]),
@@ -380,12 +384,49 @@ class Groth16ProvingKey:
 class PlonkProvingKey:
     """Device-resident plonk_bn254.ProvingKey (setup.go:79-107): trace, coset evaluations, both SRS."""
 
-    def __init__(self, ctx, handle, nb_public, nb_bsb22=0):
+    def __init__(self, ctx, handle, nb_public, nb_bsb22=0, shard_index=0, shard_count=1):
         self.ctx, self.h, self.nb_public, self.nb_bsb22 = ctx, handle, nb_public, nb_bsb22
+        self.shard_index, self.shard_count = shard_index, max(1, shard_count)
 
     def free(self):
         if self.h:
             self.ctx.lib.b200_plonk_pk_free(self.ctx.h, self.h)
+            self.h = None
+
+
+class PlonkSession:
+    """One proof as phases (b200_plonk_session_*): each phase returns this rank's PARTIAL commitments ((k, 12) G1Jac)
+    and takes the TOTALS of the previous phase's partials over all ranks.  Sequence: begin (3 partials) ->
+    step(1, totals3) -> step(2, totals1) -> [all-gather numerator blocks] -> step(3) -> step(4, totals3) ->
+    step(5, totals2) -> finish(totals1)."""
+    N_OUT = {1: 1, 2: 0, 3: 3, 4: 2, 5: 1}
+
+    def __init__(self, ctx, handle, partials):
+        self.ctx, self.h, self.partials = ctx, handle, partials
+
+    def step(self, phase: int, totals=None) -> np.ndarray:
+        t = None if totals is None else _u64(totals, (-1, 12))
+        out = np.zeros((max(1, self.N_OUT[phase]), 12), dtype=np.uint64)
+        self.ctx._check(self.ctx.lib.b200_plonk_session_step(self.ctx.h, self.h, phase, _ptr(t), _ptr(out) if self.N_OUT[phase] else None))
+        self.partials = out[:self.N_OUT[phase]]
+        return self.partials
+
+    def numerator(self):
+        """(device address, elements per block, log2 of the block count) of the quotient numerator buffer."""
+        p, be, lb = C.c_void_p(), C.c_size_t(), C.c_uint()
+        self.ctx._check(self.ctx.lib.b200_plonk_session_numerator(self.ctx.h, self.h, C.byref(p), C.byref(be), C.byref(lb)))
+        return int(p.value), int(be.value), int(lb.value)
+
+    def finish(self, totals):
+        proof, tm = PlonkProof(), _PlonkTimings()
+        t = _u64(totals, (-1, 12))
+        h, self.h = self.h, None
+        self.ctx._check(self.ctx.lib.b200_plonk_session_finish(self.ctx.h, h, _ptr(t), C.byref(proof), C.byref(tm)))
+        return proof, {k: getattr(tm, k) for k, _ in tm._fields_}
+
+    def abandon(self):
+        if self.h:
+            self.ctx.lib.b200_plonk_session_finish(self.ctx.h, self.h, None, None, None)
             self.h = None
 
 
@@ -622,7 +663,8 @@ class Context:
 
     # -- PlonK prover
     def plonk_pk_upload(self, *, log_n, log_big, generator, generator_big, coset_gen, ql, qr, qm, qo, qk, s1, s2, s3, perm,
-                        kzg_g1, kzg_lagrange_g1, vk_commitments, nb_public, qcp=(), vk_qcp=None, commitment_index=()) -> PlonkProvingKey:
+                        kzg_g1, kzg_lagrange_g1, vk_commitments, nb_public, qcp=(), vk_qcp=None, commitment_index=(),
+                        shard_index=0, shard_count=1) -> PlonkProvingKey:
         """qcp: list of pk.trace.Qcp columns (canonical), vk_qcp: their commitments, commitment_index: CommitmentInfo[i].CommitmentIndex."""
         n = 1 << log_n
         keep = {k: _u64(v, (n, 4)) for k, v in dict(ql=ql, qr=qr, qm=qm, qo=qo, qk=qk, s1=s1, s2=s2, s3=s3).items()}
@@ -633,6 +675,7 @@ class Context:
         keep["vk_commitments"] = _u64(vk_commitments, (8, 8))
         d = _PlonkPkDesc()
         d.log_n, d.log_big, d.nb_public, d.nb_bsb22 = log_n, log_big, nb_public, len(qcp)
+        d.shard_index, d.shard_count = shard_index, shard_count
         for k, v in keep.items():
             setattr(d, k, v.ctypes.data)
         if len(qcp):
@@ -643,7 +686,28 @@ class Context:
             d.qcp, d.vk_qcp, d.commitment_index = C.addressof(ptrs), vq.ctypes.data, ci.ctypes.data
         h = C.c_void_p()
         self._check(self.lib.b200_plonk_pk_upload(self.h, BN254, C.byref(d), C.byref(h)))
-        return PlonkProvingKey(self, h, nb_public, len(qcp))
+        return PlonkProvingKey(self, h, nb_public, len(qcp), shard_index, shard_count)
+
+    def _plonk_bsb(self, pk, bsb):
+        if not pk.nb_bsb22:
+            return None, None
+        cols = [_u64(c, (-1, 4)) for c in bsb["pi2"]]
+        assert len(cols) == pk.nb_bsb22
+        ptrs = (C.c_void_p * len(cols))(*[c.ctypes.data for c in cols])
+        com, val = _u64(bsb["commitments"], (len(cols), 8)), _u64(bsb["values"], (len(cols), 4))
+        return _PlonkBsb22(C.addressof(ptrs), com.ctypes.data, val.ctypes.data), (cols, ptrs, com, val)
+
+    def plonk_session(self, pk: PlonkProvingKey, l, r, o, public_witness, blinding, bsb=None) -> "PlonkSession":
+        """Phase 0 of a (possibly sharded) proof; see PlonkSession."""
+        l, r, o = _u64(l, (-1, 4)), _u64(r, (-1, 4)), _u64(o, (-1, 4))
+        pw = _u64(public_witness, (-1, 4))
+        bl = None if blinding is None else _u64(blinding, (9, 4))
+        cb, keep = self._plonk_bsb(pk, bsb)
+        h = C.c_void_p()
+        partials = np.zeros((3, 12), dtype=np.uint64)
+        self._check(self.lib.b200_plonk_session_begin(self.h, pk.h, _ptr(l), _ptr(r), _ptr(o), _ptr(pw) if pw.shape[0] else None,
+                                                      _ptr(bl), None if cb is None else C.byref(cb), C.byref(h), _ptr(partials)))
+        return PlonkSession(self, h, partials)
 
     def plonk_prove(self, pk: PlonkProvingKey, l, r, o, public_witness, blinding=None, bsb=None):
         """plonk_bn254.Prove after the solver (prove.go:116-180).  blinding: (9, 4) Montgomery coefficients
@@ -655,13 +719,7 @@ class Context:
         assert pw.shape[0] == pk.nb_public
         bl = None if blinding is None else _u64(blinding, (9, 4))
         proof, tm = PlonkProof(), _PlonkTimings()
-        cb = None
-        if pk.nb_bsb22:
-            cols = [_u64(c, (-1, 4)) for c in bsb["pi2"]]
-            assert len(cols) == pk.nb_bsb22
-            ptrs = (C.c_void_p * len(cols))(*[c.ctypes.data for c in cols])
-            com, val = _u64(bsb["commitments"], (len(cols), 8)), _u64(bsb["values"], (len(cols), 4))
-            cb = _PlonkBsb22(C.addressof(ptrs), com.ctypes.data, val.ctypes.data)
+        cb, keep = self._plonk_bsb(pk, bsb)
         self._check(self.lib.b200_plonk_prove_bsb22(self.h, pk.h, _ptr(l), _ptr(r), _ptr(o), _ptr(pw) if pw.shape[0] else None,
                                                     _ptr(bl), None if cb is None else C.byref(cb), C.byref(proof), C.byref(tm)))
         return proof, {k: getattr(tm, k) for k, _ in tm._fields_}

@@ -15,6 +15,7 @@
 // Fiat-Shamir (SHA-256) and the O(1) group arithmetic (blinding commitments, folded digests) run on the host,
 // as in the reference.
 #include <chrono>
+#include <memory>
 #include <cstdio>
 #include "host_group.cuh"
 #include "msm_host.cuh"
@@ -37,6 +38,8 @@ struct b200_plonk_pk {
     b200_bases *srs = nullptr, *srs_lag = nullptr;
     G1Affine srs_lo[3], srs_hi[3];   // pk.Kzg.G1[0..2], [n..n+2]  (commitBlindingFactor, prove.go:1159-1172)
     G1Affine vk_pts[8];              // S1 S2 S3 Ql Qr Qm Qo Qk
+    uint32_t shard_index = 0, shard_count = 1;      // MSM point ranges and quotient cosets of this rank
+    size_t srs_lo_idx = 0, srs_hi_idx = 0, lag_lo = 0, lag_hi = 0;
     // BSB22 (api.Commit circuits)
     uint32_t nb_bsb = 0;
     DevBuf qcp;          // [nb_bsb][n] trace.Qcp, canonical / regular
@@ -343,6 +346,13 @@ int b200_plonk_pk_upload(b200_ctx* ctx, int curve, const b200_plonk_pk_desc* d, 
     pk->log_n = d->log_n; pk->log_big = d->log_big; pk->n = n; pk->big = (size_t)1 << d->log_big;
     pk->rho = 1u << (d->log_big - d->log_n);
     pk->nb_public = d->nb_public;
+    pk->shard_count = d->shard_count > 1 ? (uint32_t)d->shard_count : 1u;
+    pk->shard_index = d->shard_count > 1 ? (uint32_t)d->shard_index : 0u;
+    if (pk->shard_index >= pk->shard_count || d->shard_index < 0) { delete pk; return ctx->fail(B200_ERR_ARG, "shard_index out of range"); }
+    pk->srs_lo_idx = (n + 3) * pk->shard_index / pk->shard_count;
+    pk->srs_hi_idx = (n + 3) * (pk->shard_index + 1) / pk->shard_count;
+    pk->lag_lo = n * pk->shard_index / pk->shard_count;
+    pk->lag_hi = n * (pk->shard_index + 1) / pk->shard_count;
     pk->nb_bsb = (uint32_t)d->nb_bsb22;
     for (uint32_t k = 0; k < pk->nb_bsb; ++k) {
         if (!d->qcp[k]) { delete pk; return ctx->fail(B200_ERR_ARG, "null Qcp"); }
@@ -412,8 +422,9 @@ int b200_plonk_pk_upload(b200_ctx* ctx, int curve, const b200_plonk_pk_desc* d, 
     if (st == B200_OK) st = fr_bitrev_copy(ctx, pk->tr(TR_QK), pk->qk_lag.as<Fr>(), d->log_n);
     if (st == B200_OK) st = ntt_run(ctx, pk->d0, pk->qk_lag.as<Fr>(), 0, 1, nullptr, nullptr, nullptr);
     if (st == B200_OK && cudaStreamSynchronize(s) != cudaSuccess) st = ctx->fail(B200_ERR_CUDA, "PlonK key precomputation");
-    if (st == B200_OK) st = b200_bases_upload(ctx, curve, 1, d->kzg_g1, n + 3, &pk->srs);
-    if (st == B200_OK) st = b200_bases_upload(ctx, curve, 1, d->kzg_lagrange_g1, n, &pk->srs_lag);
+    // each rank keeps its point range of both SRS (the whole of them on one GPU)
+    if (st == B200_OK) st = b200_bases_upload(ctx, curve, 1, d->kzg_g1 + 8 * pk->srs_lo_idx, pk->srs_hi_idx - pk->srs_lo_idx, &pk->srs);
+    if (st == B200_OK) st = b200_bases_upload(ctx, curve, 1, d->kzg_lagrange_g1 + 8 * pk->lag_lo, pk->lag_hi - pk->lag_lo, &pk->srs_lag);
     if (st != B200_OK) { plonk_pk_delete(ctx, pk); return st; }
     *out = pk;
     return B200_OK;
@@ -427,6 +438,456 @@ int b200_plonk_pk_free(b200_ctx* ctx, b200_plonk_pk* pk) {
     return B200_OK;
 }
 
+}  // extern "C"
+
+// ---- the prover as a session of phases ------------------------------------------------------------------
+// One proof = 7 phases separated by the points where commitments must be complete (Fiat-Shamir) or where the
+// quotient's coset blocks must all be present.  On one GPU b200_plonk_prove_bsb22 runs them back to back; with
+// the key sharded over R ranks (b200_plonk_pk_desc.shard_*), every rank runs the same phases, its MSMs cover its
+// point range of the SRS, its quotient loop covers the cosets k = rank (mod R), and the caller sums the partial
+// commitments (b200_g1_jac_add) and all-gathers the coset blocks between phases (PlonK P1, P4).
+//   phase  consumes (totals)        produces (partials)
+//   0      -                        [L] [R] [O]
+//   1      [L] [R] [O]              [Z]
+//   2      [Z]                      -            (coset blocks of the numerator written; exchange them now)
+//   3      -                        [H1] [H2] [H3]
+//   4      [H1] [H2] [H3]           [Z opening quotient] [linearised polynomial]
+//   5      those two                [batch opening quotient]
+//   6      that one                 -            (proof complete)
+struct b200_plonk_session {
+    const b200_plonk_pk* pk = nullptr;
+    uint32_t nb = 0;
+    int next_phase = 0;
+    G1Affine bsb_com[B200_PLONK_MAX_BSB22];
+    Fr bsb_val[B200_PLONK_MAX_BSB22];
+    Fr *pi2_br[B200_PLONK_MAX_BSB22], *pi2_cn[B200_PLONK_MAX_BSB22], *pi2_ev[B200_PLONK_MAX_BSB22];
+    Fr bp[9];
+    std::vector<Fr> pub;
+    Fr *v[4], *qk_br, *idv, *cn[4], *tmp[5], *cres;
+    Fr *quot, *fh, *lin, *folded;
+    Transcript fs{"gamma", "beta", "alpha", "zeta"};
+    Fr gamma, beta, alpha, zeta, gk, zu, blz, brz, boz, s1z, s2z, qcpz[B200_PLONK_MAX_BSB22], claimed[7];
+    G1Affine lro[3], z_com, h_com[3], zs_h, lin_digest, fh_digest, batched_h;
+    G1XYZZ hx[3];
+    b200_plonk_timings T;
+    double t_start = 0, t0 = 0;
+    cudaEvent_t ev_cp[4] = {nullptr, nullptr, nullptr, nullptr}, ev_t[2] = {nullptr, nullptr};
+    ~b200_plonk_session() {
+        for (auto e : ev_cp) if (e) cudaEventDestroy(e);
+        for (auto e : ev_t) if (e) cudaEventDestroy(e);
+    }
+    void lap(float& slot) { const double t = now_ms(); slot += (float)(t - t0); t0 = t; }
+    const Fr* bl() const { return bp; }
+    const Fr* br() const { return bp + 2; }
+    const Fr* bo() const { return bp + 4; }
+    const Fr* bz() const { return bp + 6; }
+};
+
+namespace {
+
+// this shard's part of kzg.Commit for several polynomials against one SRS (lo..hi = the shard's point range)
+int commit_shard(b200_ctx* ctx, const b200_bases* srs, size_t lo, size_t hi, const Fr* const* coeffs, const size_t* counts, int m,
+                 G1XYZZ* out, const cudaEvent_t* wait = nullptr) {
+    const Fr* sc[4];
+    size_t cnt[4];
+    cudaEvent_t wv[4];
+    int idx[4], live = 0;
+    for (int k = 0; k < m; ++k) {
+        out[k] = G1XYZZ::inf();
+        const size_t top = counts[k] < hi ? counts[k] : hi;
+        if (top <= lo) continue;
+        sc[live] = coeffs[k] + lo; cnt[live] = top - lo; wv[live] = wait ? wait[k] : nullptr; idx[live] = k;
+        ++live;
+    }
+    if (!live) {
+        if (wait) for (int k = 0; k < m; ++k) if (wait[k]) B2_CUDA(ctx, cudaStreamWaitEvent(ctx->stream, wait[k], 0));
+        return B200_OK;
+    }
+    G1XYZZ res[4];
+    B2_TRY(commit_many(ctx, srs, sc, cnt, live, res, wait ? wv : nullptr));
+    for (int k = 0; k < live; ++k) out[idx[k]] = res[k];
+    return B200_OK;
+}
+void put_jac(uint64_t* dst, const G1XYZZ& p) { const G1Jac j = p.to_jac(); memcpy(dst, &j, sizeof j); }
+G1XYZZ get_jac(const uint64_t* src) { G1Jac j; memcpy(&j, src, sizeof j); return xyzz_from_jac(j); }
+
+int phase0(b200_ctx* ctx, b200_plonk_session& S, const uint64_t* l, const uint64_t* r, const uint64_t* o, const b200_plonk_bsb22* bsb,
+           uint64_t* partials) {
+    const b200_plonk_pk* pk = S.pk;
+    const size_t n = pk->n;
+    cudaStream_t s = ctx->stream;
+    // ---- solution to the device, [L] [R] [O]  (solveConstraints / commitToLRO, prove.go:365-452) ----------
+    // the copies run on the copy stream; the sort of [L] starts when L has landed, R and O travel under it
+    const uint64_t* src[3] = {l, r, o};
+    for (auto& e : S.ev_cp) B2_CUDA(ctx, cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+    for (auto& e : S.ev_t) B2_CUDA(ctx, cudaEventCreate(&e));
+    B2_CUDA(ctx, cudaEventRecord(S.ev_cp[3], s));
+    B2_CUDA(ctx, cudaStreamWaitEvent(ctx->copy_stream, S.ev_cp[3], 0));
+    B2_CUDA(ctx, cudaEventRecord(S.ev_t[0], ctx->copy_stream));
+    for (int k = 0; k < 3; ++k) {
+        B2_CUDA(ctx, cudaMemcpyAsync(S.v[k], src[k], n * sizeof(Fr), cudaMemcpyDefault, ctx->copy_stream));
+        B2_CUDA(ctx, cudaEventRecord(S.ev_cp[k], ctx->copy_stream));
+    }
+    for (uint32_t k = 0; k < S.nb; ++k)
+        B2_CUDA(ctx, cudaMemcpyAsync(S.pi2_br[k], bsb->pi2[k], n * sizeof(Fr), cudaMemcpyDefault, ctx->copy_stream));
+    B2_CUDA(ctx, cudaEventRecord(S.ev_t[1], ctx->copy_stream));
+    const Fr* sc[3] = {S.v[0], S.v[1], S.v[2]};
+    const size_t cnt[3] = {n, n, n};
+    G1XYZZ c[3];
+    if (ctx->msm_overlap) B2_TRY(commit_shard(ctx, pk->srs_lag, pk->lag_lo, pk->lag_hi, sc, cnt, 3, c, S.ev_cp));
+    else {
+        for (int k = 0; k < 3; ++k) B2_CUDA(ctx, cudaStreamWaitEvent(s, S.ev_cp[k], 0));
+        B2_TRY(commit_shard(ctx, pk->srs_lag, pk->lag_lo, pk->lag_hi, sc, cnt, 3, c));
+    }
+    for (int k = 0; k < 3; ++k) B2_CUDA(ctx, cudaStreamWaitEvent(s, S.ev_cp[k], 0));
+    B2_CUDA(ctx, cudaStreamWaitEvent(s, S.ev_t[1], 0));
+    for (int k = 0; k < 3; ++k) put_jac(partials + 12 * k, c[k]);
+    S.lap(S.T.commit_lro_ms);
+    B2_CUDA(ctx, cudaEventSynchronize(S.ev_t[1]));
+    cudaEventElapsedTime(&S.T.h2d_ms, S.ev_t[0], S.ev_t[1]);   // on the copy stream, under the [L] [R] [O] commitments: not a summand of total_ms
+    return B200_OK;
+}
+
+int phase1(b200_ctx* ctx, b200_plonk_session& S, const uint64_t* totals, uint64_t* partials) {
+    const b200_plonk_pk* pk = S.pk;
+    const size_t n = pk->n;
+    const Fr* bps[3] = {S.bl(), S.br(), S.bo()};
+    for (int k = 0; k < 3; ++k) {
+        G1XYZZ c = get_jac(totals + 12 * k);
+        c.add(commit_blinding(pk, bps[k], 2));
+        S.lro[k] = c.to_affine();
+    }
+    // ---- gamma, beta (deriveGammaAndBeta, prove.go:455-485; bindPublicData, verify.go:296-340) -----------
+    for (int k = 0; k < 8; ++k) bind_point(S.fs, "gamma", pk->vk_pts[k]);
+    for (uint32_t k = 0; k < S.nb; ++k) bind_point(S.fs, "gamma", pk->vk_qcp[k]);
+    for (const Fr& x : S.pub) bind_fr(S.fs, "gamma", x);
+    for (int k = 0; k < 3; ++k) bind_point(S.fs, "gamma", S.lro[k]);
+    S.gamma = derive(S.fs, "gamma");
+    S.beta = derive(S.fs, "beta");
+    S.lap(S.T.commit_lro_ms);
+    // ---- Z and [Z] (buildRatioCopyConstraint, prove.go:597-631) ------------------------------------------
+    B2_TRY(plonk_build_ratio(ctx, pk->d0, S.v[0], S.v[1], S.v[2], pk->perm.as<int64_t>(), S.beta, S.gamma, S.v[3], S.tmp[0], S.tmp[1]));
+    B2_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    S.lap(S.T.ratio_ms);
+    const Fr* sc[1] = {S.v[3]};
+    const size_t cnt[1] = {n};
+    G1XYZZ c;
+    B2_TRY(commit_shard(ctx, pk->srs_lag, pk->lag_lo, pk->lag_hi, sc, cnt, 1, &c));
+    put_jac(partials, c);
+    S.lap(S.T.commit_z_ms);
+    return B200_OK;
+}
+
+int phase2(b200_ctx* ctx, b200_plonk_session& S, const uint64_t* totals) {
+    const b200_plonk_pk* pk = S.pk;
+    const size_t n = pk->n;
+    const unsigned log_n = pk->log_n;
+    cudaStream_t s = ctx->stream;
+    NttDomain *d0 = pk->d0, *d1 = pk->d1;
+    {
+        G1XYZZ c = get_jac(totals);
+        c.add(commit_blinding(pk, S.bz(), 3));
+        S.z_com = c.to_affine();
+    }
+    for (uint32_t k = 0; k < S.nb; ++k) bind_point(S.fs, "alpha", S.bsb_com[k]);     // deriveAlpha, prove.go:504-512
+    bind_point(S.fs, "alpha", S.z_com);
+    S.alpha = derive(S.fs, "alpha");
+    S.lap(S.T.commit_z_ms);
+    // ---- quotient (evaluateConstraints / computeNumerator, prove.go:521-595,837-1079) -----------------------
+    // canonical forms: FFTInverse(DIF) leaves the coefficients bit-reversed, which is what the coset DIT wants
+    B2_CUDA(ctx, cudaMemcpyAsync(S.qk_br, pk->qk_lag.p, n * sizeof(Fr), cudaMemcpyDeviceToDevice, s));
+    if (pk->nb_public) B2_CUDA(ctx, cudaMemcpyAsync(S.qk_br, S.pub.data(), pk->nb_public * sizeof(Fr), cudaMemcpyHostToDevice, s));   // completeQk
+    for (uint32_t k = 0; k < S.nb; ++k)      // qkCoeffs[nbPublic + CommitmentIndex] = commitmentVal, prove.go:415-417
+        B2_CUDA(ctx, cudaMemcpyAsync(S.qk_br + pk->commit_row[k], S.bsb_val[k].l, sizeof(Fr), cudaMemcpyHostToDevice, s));
+    for (int k = 0; k < 4; ++k) B2_TRY(ntt_gnark(ctx, d0, S.v[k], 1, B200_DIF, 0));
+    B2_TRY(ntt_gnark(ctx, d0, S.qk_br, 1, B200_DIF, 0));
+    for (int k = 0; k < 4; ++k) B2_TRY(fr_bitrev_copy(ctx, S.v[k], S.cn[k], log_n));   // regular layout, for the openings
+    for (uint32_t k = 0; k < S.nb; ++k) {                                              // cCommitments[i].ToCanonical, prove.go:339
+        B2_TRY(ntt_gnark(ctx, d0, S.pi2_br[k], 1, B200_DIF, 0));
+        B2_TRY(fr_bitrev_copy(ctx, S.pi2_br[k], S.pi2_cn[k], log_n));
+    }
+    PlonkRowArgs a;
+    memset(&a, 0, sizeof a);
+    a.nb_bsb = S.nb;
+    a.beta = S.beta; a.gamma = S.gamma; a.alpha = S.alpha;
+    a.cs = d1->coset;
+    a.css = a.cs * a.cs;
+    a.tw = d0->tw_fwd.as<Fr>();
+    a.n = (uint32_t)n; a.log_big = pk->log_big; a.rho = pk->rho;
+    a.cres = S.cres;
+    Fr coset = Fr::one();
+    const Fr* srcs[5] = {S.v[0], S.v[1], S.v[2], S.v[3], S.qk_br};
+    const Fr *bl = S.bl(), *br = S.br(), *bo = S.bo(), *bz = S.bz();
+    for (uint32_t k = 0; k < pk->rho; ++k) {
+        coset = coset * (k == 0 ? d1->coset : d1->gen);
+        if (k % pk->shard_count != pk->shard_index) continue;            // another rank's coset
+        // bl <- bl * ((s w^k)^n - 1) scaled by powers of the shift (prove.go:985-993)
+        const Fr xn1 = coset.pow_u64(n) - Fr::one();
+        Fr acc = xn1;
+        for (int j = 0; j < 3; ++j) {
+            if (j < 2) { a.bl[j] = bl[j] * acc; a.br[j] = br[j] * acc; a.bo[j] = bo[j] * acc; }
+            a.bz[j] = bz[j] * acc;
+            acc = acc * coset;
+        }
+        const Fr* pre = pk->coset_pre.as<Fr>() + (size_t)k * n;
+        for (int p = 0; p < 5; ++p) {
+            B2_CUDA(ctx, cudaMemcpyAsync(S.tmp[p], srcs[p], n * sizeof(Fr), cudaMemcpyDeviceToDevice, s));
+            B2_TRY(ntt_run(ctx, d0, S.tmp[p], 0, 1, pre, nullptr, nullptr));
+        }
+        for (uint32_t p = 0; p < S.nb; ++p) {
+            B2_CUDA(ctx, cudaMemcpyAsync(S.pi2_ev[p], S.pi2_br[p], n * sizeof(Fr), cudaMemcpyDeviceToDevice, s));
+            B2_TRY(ntt_run(ctx, d0, S.pi2_ev[p], 0, 1, pre, nullptr, nullptr));
+            a.qci[2 * p] = pk->qcp_e(k, p);
+            a.qci[2 * p + 1] = S.pi2_ev[p];
+        }
+        B2_TRY(fr_scaled_omega(ctx, d0, S.beta * coset, S.idv));
+        a.x[PID_L] = S.tmp[0]; a.x[PID_R] = S.tmp[1]; a.x[PID_O] = S.tmp[2]; a.x[PID_Z] = S.tmp[3]; a.x[PID_ZS] = nullptr;
+        a.x[PID_QK] = S.tmp[4];
+        a.x[PID_QL] = pk->cev(k, CE_QL); a.x[PID_QR] = pk->cev(k, CE_QR); a.x[PID_QM] = pk->cev(k, CE_QM); a.x[PID_QO] = pk->cev(k, CE_QO);
+        a.x[PID_S1] = pk->cev(k, CE_S1); a.x[PID_S2] = pk->cev(k, CE_S2); a.x[PID_S3] = pk->cev(k, CE_S3);
+        a.x[PID_LONE] = pk->cev(k, CE_LONE);
+        a.x[PID_ID] = S.idv;
+        a.coset_index = k;
+        B2_TRY(plonk_quotient_rows(ctx, a));
+    }
+    B2_CUDA(ctx, cudaStreamSynchronize(s));
+    S.lap(S.T.quotient_ms);
+    return B200_OK;
+}
+
+int phase3(b200_ctx* ctx, b200_plonk_session& S, uint64_t* partials) {
+    const b200_plonk_pk* pk = S.pk;
+    const size_t n = pk->n;
+    // divideByXMinusOne, prove.go:1223-1250 (every rank holds the whole numerator after the exchange)
+    B2_TRY(plonk_divide_xn(ctx, pk->d1, pk->log_n, S.cres));
+    B2_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    S.lap(S.T.quotient_ms);
+    const Fr* sc[3] = {S.cres, S.cres + (n + 2), S.cres + 2 * (n + 2)};          // h1 h2 h3, prove.go:652-666
+    const size_t cnt[3] = {n + 2, n + 2, n + 2};
+    G1XYZZ c[3];
+    B2_TRY(commit_shard(ctx, pk->srs, pk->srs_lo_idx, pk->srs_hi_idx, sc, cnt, 3, c));   // commitToQuotient, prove.go:1198-1218
+    for (int k = 0; k < 3; ++k) put_jac(partials + 12 * k, c[k]);
+    S.lap(S.T.commit_h_ms);
+    return B200_OK;
+}
+
+int phase4(b200_ctx* ctx, b200_plonk_session& S, const uint64_t* totals, uint64_t* partials) {
+    const b200_plonk_pk* pk = S.pk;
+    const size_t n = pk->n;
+    NttDomain* d0 = pk->d0;
+    for (int k = 0; k < 3; ++k) {
+        S.hx[k] = get_jac(totals + 12 * k);
+        S.h_com[k] = S.hx[k].to_affine();
+        bind_point(S.fs, "zeta", S.h_com[k]);
+    }
+    S.zeta = derive(S.fs, "zeta");
+    const Fr &zeta = S.zeta, &beta = S.beta, &gamma = S.gamma, &alpha = S.alpha;
+    S.lap(S.T.commit_h_ms);
+    // ---- open Z at w zeta (openZ, prove.go:634-650; kzg.Open) ------------------------------------------------
+    B2_TRY(fr_blind(ctx, S.cn[0], n, S.bl(), 2));
+    B2_TRY(fr_blind(ctx, S.cn[1], n, S.br(), 2));
+    B2_TRY(fr_blind(ctx, S.cn[2], n, S.bo(), 2));
+    B2_TRY(fr_blind(ctx, S.cn[3], n, S.bz(), 3));
+    const Fr zeta_shifted = zeta * d0->gen;
+    B2_TRY(fr_poly_eval(ctx, S.cn[3], n + 3, zeta_shifted, &S.zu));
+    S.quot = S.tmp[0];
+    B2_TRY(fr_poly_div_linear(ctx, S.cn[3], n + 3, zeta_shifted, S.quot));
+    S.lap(S.T.open_z_ms);
+    // ---- foldH (prove.go:670-705) ---------------------------------------------------------------------
+    const Fr zn2 = zeta.pow_u64(n + 2);
+    S.fh = S.tmp[1];
+    B2_TRY(plonk_fold_h(ctx, S.cres, S.cres + (n + 2), S.cres + 2 * (n + 2), zn2, n + 2, S.fh));
+    G1XYZZ fhd = scalar_mul(S.hx[2], zn2);
+    fhd.add(S.hx[1]);
+    fhd = scalar_mul(fhd, zn2);
+    fhd.add(S.hx[0]);
+    S.fh_digest = fhd.to_affine();
+    // ---- linearised polynomial (computeLinearizedPolynomial, prove.go:708-777,1289-1389) --------------------
+    // evaluateBlinded == the blinded polynomial at zeta
+    B2_TRY(fr_poly_eval(ctx, S.cn[0], n + 2, zeta, &S.blz));
+    B2_TRY(fr_poly_eval(ctx, S.cn[1], n + 2, zeta, &S.brz));
+    B2_TRY(fr_poly_eval(ctx, S.cn[2], n + 2, zeta, &S.boz));
+    B2_TRY(fr_poly_eval(ctx, pk->tr(TR_S1), n, zeta, &S.s1z));
+    B2_TRY(fr_poly_eval(ctx, pk->tr(TR_S2), n, zeta, &S.s2z));
+    for (uint32_t k = 0; k < S.nb; ++k) B2_TRY(fr_poly_eval(ctx, pk->qcp_c(k), n, zeta, &S.qcpz[k]));     // prove.go:724-729
+    S.lin = S.tmp[2];
+    {
+        const Fr &blz = S.blz, &brz = S.brz, &boz = S.boz;
+        PlonkLinArgs a;
+        memset(&a, 0, sizeof a);
+        a.bz = S.cn[3]; a.s3 = pk->tr(TR_S3); a.ql = pk->tr(TR_QL); a.qr = pk->tr(TR_QR); a.qm = pk->tr(TR_QM); a.qo = pk->tr(TR_QO);
+        a.qk = pk->tr(TR_QK);
+        a.nb_bsb = S.nb;
+        for (uint32_t k = 0; k < S.nb; ++k) { a.pi2[k] = S.pi2_cn[k]; a.qcp_zeta[k] = S.qcpz[k]; }
+        a.rl = brz * blz;
+        a.c1 = (S.s1z * beta + blz + gamma) * (S.s2z * beta + brz + gamma) * S.zu * beta;
+        const Fr u = d0->coset, uz = zeta * u, uuz = uz * u;
+        a.c2 = ((beta * zeta + blz + gamma) * (beta * uz + brz + gamma) * (beta * uuz + boz + gamma)).neg();
+        const Fr zn1 = zeta.pow_u64(n) - Fr::one();
+        a.lag = zn1 * (zeta - Fr::one()).inv() * alpha * alpha * d0->ninv;
+        a.alpha = alpha; a.l = blz; a.r = brz; a.o = boz;
+        a.n = (uint32_t)n; a.len = (uint32_t)(n + 3);
+        a.out = S.lin;
+        B2_TRY(plonk_linearize(ctx, a));
+    }
+    // [quotient of the Z opening] and [linearised polynomial]: independent, committed as one pipelined pair
+    const Fr* sc[2] = {S.quot, S.lin};
+    const size_t cnt[2] = {n + 2, n + 3};
+    G1XYZZ c[2];
+    B2_TRY(commit_shard(ctx, pk->srs, pk->srs_lo_idx, pk->srs_hi_idx, sc, cnt, 2, c));
+    put_jac(partials, c[0]);
+    put_jac(partials + 12, c[1]);
+    S.lap(S.T.linearize_ms);
+    return B200_OK;
+}
+
+int phase5(b200_ctx* ctx, b200_plonk_session& S, const uint64_t* totals, uint64_t* partials) {
+    const b200_plonk_pk* pk = S.pk;
+    const size_t n = pk->n;
+    const uint32_t nb = S.nb;
+    S.zs_h = get_jac(totals).to_affine();
+    S.lin_digest = get_jac(totals + 12).to_affine();
+    // ---- batch opening at zeta (batchOpening, prove.go:779-833; kzg.BatchOpenSinglePoint) --------------------
+    B2_TRY(fr_poly_eval(ctx, S.fh, n + 2, S.zeta, &S.claimed[0]));
+    B2_TRY(fr_poly_eval(ctx, S.lin, n + 3, S.zeta, &S.claimed[1]));
+    S.claimed[2] = S.blz; S.claimed[3] = S.brz; S.claimed[4] = S.boz; S.claimed[5] = S.s1z; S.claimed[6] = S.s2z;
+    {
+        Transcript g({"gamma"});
+        bind_fr(g, "gamma", S.zeta);
+        const G1Affine* dg[7] = {&S.fh_digest, &S.lin_digest, &S.lro[0], &S.lro[1], &S.lro[2], &pk->vk_pts[0], &pk->vk_pts[1]};
+        for (int k = 0; k < 7; ++k) bind_point(g, "gamma", *dg[k]);
+        for (uint32_t k = 0; k < nb; ++k) bind_point(g, "gamma", pk->vk_qcp[k]);
+        for (int k = 0; k < 7; ++k) bind_fr(g, "gamma", S.claimed[k]);
+        for (uint32_t k = 0; k < nb; ++k) bind_fr(g, "gamma", S.qcpz[k]);
+        bind_fr(g, "gamma", S.zu);
+        S.gk = derive(g, "gamma");
+    }
+    S.folded = S.tmp[3];
+    {
+        PlonkFoldArgs a;
+        memset(&a, 0, sizeof a);
+        const Fr* ps[7] = {S.fh, S.lin, S.cn[0], S.cn[1], S.cn[2], pk->tr(TR_S1), pk->tr(TR_S2)};
+        const size_t ls[7] = {n + 2, n + 3, n + 2, n + 2, n + 2, n, n};
+        Fr acc = Fr::one();
+        for (int k = 0; k < 7; ++k) { a.p[k] = ps[k]; a.len[k] = (uint32_t)ls[k]; a.g[k] = acc; acc = acc * S.gk; }
+        for (uint32_t k = 0; k < nb; ++k) { a.p[7 + k] = pk->qcp_c(k); a.len[7 + k] = (uint32_t)n; a.g[7 + k] = acc; acc = acc * S.gk; }
+        a.count = 7 + nb; a.width = (uint32_t)(n + 3);
+        a.out = S.folded;
+        B2_TRY(plonk_fold_polys(ctx, a));
+    }
+    B2_TRY(fr_poly_div_linear(ctx, S.folded, n + 3, S.zeta, S.quot));
+    const Fr* sc[1] = {S.quot};
+    const size_t cnt[1] = {n + 2};
+    G1XYZZ c;
+    B2_TRY(commit_shard(ctx, pk->srs, pk->srs_lo_idx, pk->srs_hi_idx, sc, cnt, 1, &c));
+    put_jac(partials, c);
+    S.lap(S.T.batch_open_ms);
+    return B200_OK;
+}
+
+void phase6(b200_plonk_session& S, const uint64_t* totals, b200_plonk_proof* out) {
+    S.batched_h = get_jac(totals).to_affine();
+    S.T.total_ms = (float)(now_ms() - S.t_start);
+    memset(out, 0, sizeof *out);
+    for (int k = 0; k < 3; ++k) { put_point(out->lro[k], S.lro[k]); put_point(out->h[k], S.h_com[k]); }
+    put_point(out->z, S.z_com);
+    put_point(out->batched_h, S.batched_h);
+    for (int k = 0; k < 7; ++k) put_fr(out->claimed[k], S.claimed[k]);
+    put_point(out->zshift_h, S.zs_h);
+    put_fr(out->zshift_value, S.zu);
+    put_fr(out->challenges[0], S.gamma); put_fr(out->challenges[1], S.beta); put_fr(out->challenges[2], S.alpha);
+    put_fr(out->challenges[3], S.zeta); put_fr(out->challenges[4], S.gk);
+    out->nb_bsb22 = S.nb;
+    for (uint32_t k = 0; k < S.nb; ++k) { put_fr(out->claimed_qcp[k], S.qcpz[k]); put_point(out->bsb22[k], S.bsb_com[k]); }
+}
+
+}  // namespace
+
+extern "C" {
+
+int b200_plonk_session_begin(b200_ctx* ctx, const b200_plonk_pk* pk, const uint64_t* l, const uint64_t* r, const uint64_t* o,
+                             const uint64_t* public_witness, const uint64_t* blinding, const b200_plonk_bsb22* bsb,
+                             b200_plonk_session** out, uint64_t* partials) {
+    if (!ctx) return B200_ERR_ARG;
+    if (cudaSetDevice(ctx->device) != cudaSuccess) return ctx->fail(B200_ERR_CUDA, "cudaSetDevice");
+    if (!pk || !l || !r || !o || !out || !partials || (pk->nb_public && !public_witness)) return ctx->fail(B200_ERR_ARG, "null argument");
+    const uint32_t nb = pk->nb_bsb;
+    if (nb && (!bsb || !bsb->pi2 || !bsb->commitments || !bsb->values)) return ctx->fail(B200_ERR_ARG, "the key has BSB22 commitments: bsb is required");
+    if (pk->shard_count > 1 && !blinding) return ctx->fail(B200_ERR_ARG, "a sharded proof needs the same blinding on every rank: pass it");
+    if (3 * (pk->n + 2) > pk->big) return ctx->fail(B200_ERR_ARG, "big domain below 3(n+2)");
+    std::unique_ptr<b200_plonk_session> S(new b200_plonk_session());
+    S->pk = pk;
+    S->nb = nb;
+    const size_t n = pk->n, N4 = n + 4;
+    for (uint32_t k = 0; k < nb; ++k) {
+        if (!bsb->pi2[k]) return ctx->fail(B200_ERR_ARG, "null Pi2 column");
+        memcpy(&S->bsb_com[k], bsb->commitments + 8 * k, sizeof(G1Affine));
+        memcpy(S->bsb_val[k].l, bsb->values + 4 * k, 32);
+        S->pi2_br[k] = pk->bsb_work.as<Fr>() + (size_t)(3 * k) * n;
+        S->pi2_cn[k] = S->pi2_br[k] + n;
+        S->pi2_ev[k] = S->pi2_cn[k] + n;
+    }
+    memset(&S->T, 0, sizeof S->T);
+    S->t_start = S->t0 = now_ms();
+    // workspace
+    Fr* w = pk->work.as<Fr>();
+    for (int k = 0; k < 4; ++k) S->v[k] = w + (size_t)k * n;                   // L R O Z: Lagrange, then canonical bit-reversed
+    S->qk_br = w + 4 * n;
+    S->idv = w + 5 * n;
+    for (int k = 0; k < 4; ++k) S->cn[k] = w + 6 * n + (size_t)k * N4;          // canonical / regular, blinded
+    for (int k = 0; k < 5; ++k) S->tmp[k] = w + 6 * n + (size_t)(4 + k) * N4;   // coset evaluations of L R O Z Qk; reused after the quotient
+    S->cres = w + 6 * n + 9 * N4;
+    // blinding polynomials (initBlindingPolynomials, prove.go:295-301)
+    if (blinding) memcpy(S->bp, blinding, sizeof S->bp);
+    else if (os_random_fr(S->bp, 9) != B200_OK) return ctx->fail(B200_ERR_ARG, "no entropy source");
+    S->pub.resize(pk->nb_public);
+    if (pk->nb_public) memcpy(S->pub.data(), public_witness, pk->nb_public * sizeof(Fr));
+    B2_TRY(phase0(ctx, *S, l, r, o, bsb, partials));
+    S->next_phase = 1;
+    *out = S.release();
+    return B200_OK;
+}
+
+int b200_plonk_session_step(b200_ctx* ctx, b200_plonk_session* S, int phase, const uint64_t* totals, uint64_t* partials) {
+    if (!ctx) return B200_ERR_ARG;
+    if (cudaSetDevice(ctx->device) != cudaSuccess) return ctx->fail(B200_ERR_CUDA, "cudaSetDevice");
+    if (!S || phase != S->next_phase || phase < 1 || phase > 5) return ctx->fail(B200_ERR_ARG, "phases run in order 1..5 after begin");
+    if ((phase != 3 && !totals) || (phase != 2 && !partials)) return ctx->fail(B200_ERR_ARG, "null argument");
+    S->t0 = now_ms();
+    int st = B200_OK;
+    switch (phase) {
+        case 1: st = phase1(ctx, *S, totals, partials); break;
+        case 2: st = phase2(ctx, *S, totals); break;
+        case 3: st = phase3(ctx, *S, partials); break;
+        case 4: st = phase4(ctx, *S, totals, partials); break;
+        case 5: st = phase5(ctx, *S, totals, partials); break;
+    }
+    if (st == B200_OK) S->next_phase = phase + 1;
+    return st;
+}
+
+int b200_plonk_session_numerator(b200_ctx* ctx, b200_plonk_session* S, void** cres_dev, size_t* block_elems, unsigned* log_blocks) {
+    if (!ctx) return B200_ERR_ARG;
+    if (!S || !cres_dev || !block_elems || !log_blocks) return ctx->fail(B200_ERR_ARG, "null argument");
+    *cres_dev = S->cres;
+    *block_elems = S->pk->n;
+    *log_blocks = S->pk->log_big - S->pk->log_n;
+    return B200_OK;
+}
+
+int b200_plonk_session_finish(b200_ctx* ctx, b200_plonk_session* S, const uint64_t* totals, b200_plonk_proof* out, b200_plonk_timings* tm) {
+    if (!ctx) return B200_ERR_ARG;
+    if (!S) return ctx->fail(B200_ERR_ARG, "null session");
+    std::unique_ptr<b200_plonk_session> guard(S);
+    if (S->next_phase != 6 && (out || totals)) return ctx->fail(B200_ERR_ARG, "finish comes after phase 5 (pass NULL totals and proof to abandon a session)");
+    if (S->next_phase == 6) {
+        if (!totals || !out) return ctx->fail(B200_ERR_ARG, "null argument");
+        phase6(*S, totals, out);
+        if (tm) *tm = S->T;
+    }
+    return B200_OK;
+}
+
 int b200_plonk_prove(b200_ctx* ctx, const b200_plonk_pk* pk, const uint64_t* l, const uint64_t* r, const uint64_t* o,
                      const uint64_t* public_witness, const uint64_t* blinding, b200_plonk_proof* out, b200_plonk_timings* tm) {
     return b200_plonk_prove_bsb22(ctx, pk, l, r, o, public_witness, blinding, nullptr, out, tm);
@@ -436,305 +897,19 @@ int b200_plonk_prove_bsb22(b200_ctx* ctx, const b200_plonk_pk* pk, const uint64_
                            const uint64_t* public_witness, const uint64_t* blinding, const b200_plonk_bsb22* bsb,
                            b200_plonk_proof* out, b200_plonk_timings* tm) {
     if (!ctx) return B200_ERR_ARG;
-    if (cudaSetDevice(ctx->device) != cudaSuccess) return ctx->fail(B200_ERR_CUDA, "cudaSetDevice");
-    if (!pk || !l || !r || !o || !out || (pk->nb_public && !public_witness)) return ctx->fail(B200_ERR_ARG, "null argument");
-    const uint32_t nb = pk->nb_bsb;
-    if (nb && (!bsb || !bsb->pi2 || !bsb->commitments || !bsb->values)) return ctx->fail(B200_ERR_ARG, "the key has BSB22 commitments: bsb is required");
-    G1Affine bsb_com[B200_PLONK_MAX_BSB22];
-    Fr bsb_val[B200_PLONK_MAX_BSB22];
-    Fr *pi2_br[B200_PLONK_MAX_BSB22], *pi2_cn[B200_PLONK_MAX_BSB22], *pi2_ev[B200_PLONK_MAX_BSB22];
-    for (uint32_t k = 0; k < nb; ++k) {
-        if (!bsb->pi2[k]) return ctx->fail(B200_ERR_ARG, "null Pi2 column");
-        memcpy(&bsb_com[k], bsb->commitments + 8 * k, sizeof(G1Affine));
-        memcpy(bsb_val[k].l, bsb->values + 4 * k, 32);
-        pi2_br[k] = pk->bsb_work.as<Fr>() + (size_t)(3 * k) * pk->n;
-        pi2_cn[k] = pi2_br[k] + pk->n;
-        pi2_ev[k] = pi2_cn[k] + pk->n;
-    }
-    const size_t n = pk->n, N4 = n + 4, big = pk->big;
-    const unsigned log_n = pk->log_n;
-    cudaStream_t s = ctx->stream;
-    NttDomain *d0 = pk->d0, *d1 = pk->d1;
-    b200_plonk_timings T;
-    memset(&T, 0, sizeof T);
-    const double t_start = now_ms();
-    double t0 = t_start;
-    auto lap = [&](float& slot) { const double t = now_ms(); slot += (float)(t - t0); t0 = t; };
-
-    // workspace
-    Fr* w = pk->work.as<Fr>();
-    Fr* v[4];                       // L R O Z: Lagrange, then canonical bit-reversed
-    for (int k = 0; k < 4; ++k) v[k] = w + (size_t)k * n;
-    Fr* qk_br = w + 4 * n;
-    Fr* idv = w + 5 * n;
-    Fr* cn[4];                      // canonical / regular, blinded: n + 2 (L R O) or n + 3 (Z) coefficients
-    for (int k = 0; k < 4; ++k) cn[k] = w + 6 * n + (size_t)k * N4;
-    Fr* tmp[5];                     // coset evaluations of L R O Z Qk; reused after the quotient
-    for (int k = 0; k < 5; ++k) tmp[k] = w + 6 * n + (size_t)(4 + k) * N4;
-    Fr* cres = w + 6 * n + 9 * N4;
-
-    // blinding polynomials (initBlindingPolynomials, prove.go:295-301)
-    Fr bp[9];
-    if (blinding) memcpy(bp, blinding, sizeof bp);
-    else if (os_random_fr(bp, 9) != B200_OK) return ctx->fail(B200_ERR_ARG, "no entropy source");
-    const Fr *bl = bp, *br = bp + 2, *bo = bp + 4, *bz = bp + 6;
-    std::vector<Fr> pub(pk->nb_public);
-    if (pk->nb_public) memcpy(pub.data(), public_witness, pk->nb_public * sizeof(Fr));
-
-    // ---- solution to the device, [L] [R] [O]  (solveConstraints / commitToLRO, prove.go:365-452) ----------
-    // the copies run on the copy stream; the sort of [L] starts when L has landed, R and O travel under it
-    const uint64_t* src[3] = {l, r, o};
-    cudaEvent_t ev_cp[4];
-    for (auto& e : ev_cp) B2_CUDA(ctx, cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
-    struct CpGuard { cudaEvent_t* e; ~CpGuard() { for (int i = 0; i < 4; ++i) cudaEventDestroy(e[i]); } } cpguard{ev_cp};
-    cudaEvent_t ev_t[2];
-    for (auto& e : ev_t) B2_CUDA(ctx, cudaEventCreate(&e));
-    struct TGuard { cudaEvent_t* e; ~TGuard() { cudaEventDestroy(e[0]); cudaEventDestroy(e[1]); } } tguard{ev_t};
-    B2_CUDA(ctx, cudaEventRecord(ev_cp[3], s));
-    B2_CUDA(ctx, cudaStreamWaitEvent(ctx->copy_stream, ev_cp[3], 0));
-    B2_CUDA(ctx, cudaEventRecord(ev_t[0], ctx->copy_stream));
-    for (int k = 0; k < 3; ++k) {
-        B2_CUDA(ctx, cudaMemcpyAsync(v[k], src[k], n * sizeof(Fr), cudaMemcpyDefault, ctx->copy_stream));
-        B2_CUDA(ctx, cudaEventRecord(ev_cp[k], ctx->copy_stream));
-    }
-    for (uint32_t k = 0; k < nb; ++k)
-        B2_CUDA(ctx, cudaMemcpyAsync(pi2_br[k], bsb->pi2[k], n * sizeof(Fr), cudaMemcpyDefault, ctx->copy_stream));
-    B2_CUDA(ctx, cudaEventRecord(ev_t[1], ctx->copy_stream));
-    G1Affine lro[3];
-    const Fr* bps[3] = {bl, br, bo};
-    {
-        const Fr* sc[3] = {v[0], v[1], v[2]};
-        const size_t cnt[3] = {n, n, n};
-        G1XYZZ c[3];
-        if (ctx->msm_overlap) B2_TRY(commit_many(ctx, pk->srs_lag, sc, cnt, 3, c, ev_cp));
-        else {
-            for (int k = 0; k < 3; ++k) B2_CUDA(ctx, cudaStreamWaitEvent(s, ev_cp[k], 0));
-            B2_TRY(commit_many(ctx, pk->srs_lag, sc, cnt, 3, c));
-        }
-        for (int k = 0; k < 3; ++k) B2_CUDA(ctx, cudaStreamWaitEvent(s, ev_cp[k], 0));
-        B2_CUDA(ctx, cudaStreamWaitEvent(s, ev_t[1], 0));
-        for (int k = 0; k < 3; ++k) {
-            c[k].add(commit_blinding(pk, bps[k], 2));
-            lro[k] = c[k].to_affine();
-        }
-    }
-    lap(T.commit_lro_ms);
-    B2_CUDA(ctx, cudaEventSynchronize(ev_t[1]));
-    cudaEventElapsedTime(&T.h2d_ms, ev_t[0], ev_t[1]);      // on the copy stream, under the [L] [R] [O] commitments: not a summand of total_ms
-
-    // ---- gamma, beta (deriveGammaAndBeta, prove.go:455-485; bindPublicData, verify.go:296-340) -----------
-    Transcript fs({"gamma", "beta", "alpha", "zeta"});
-    for (int k = 0; k < 8; ++k) bind_point(fs, "gamma", pk->vk_pts[k]);
-    for (uint32_t k = 0; k < nb; ++k) bind_point(fs, "gamma", pk->vk_qcp[k]);
-    for (const Fr& x : pub) bind_fr(fs, "gamma", x);
-    for (int k = 0; k < 3; ++k) bind_point(fs, "gamma", lro[k]);
-    const Fr gamma = derive(fs, "gamma");
-    const Fr beta = derive(fs, "beta");
-
-    // ---- Z and [Z] (buildRatioCopyConstraint, prove.go:597-631) ------------------------------------------
-    B2_TRY(plonk_build_ratio(ctx, d0, v[0], v[1], v[2], pk->perm.as<int64_t>(), beta, gamma, v[3], tmp[0], tmp[1]));
-    B2_CUDA(ctx, cudaStreamSynchronize(s));
-    lap(T.ratio_ms);
-    G1Affine z_com;
-    {
-        G1XYZZ c;
-        B2_TRY(commit(ctx, pk->srs_lag, v[3], n, &c));
-        c.add(commit_blinding(pk, bz, 3));
-        z_com = c.to_affine();
-    }
-    lap(T.commit_z_ms);
-    for (uint32_t k = 0; k < nb; ++k) bind_point(fs, "alpha", bsb_com[k]);     // deriveAlpha, prove.go:504-512
-    bind_point(fs, "alpha", z_com);
-    const Fr alpha = derive(fs, "alpha");
-
-    // ---- quotient (evaluateConstraints / computeNumerator / divideByXMinusOne, prove.go:521-595,837-1079,1223) ---
-    // canonical forms: FFTInverse(DIF) leaves the coefficients bit-reversed, which is what the coset DIT wants
-    B2_CUDA(ctx, cudaMemcpyAsync(qk_br, pk->qk_lag.p, n * sizeof(Fr), cudaMemcpyDeviceToDevice, s));
-    if (pk->nb_public) B2_CUDA(ctx, cudaMemcpyAsync(qk_br, pub.data(), pk->nb_public * sizeof(Fr), cudaMemcpyHostToDevice, s));   // completeQk
-    for (uint32_t k = 0; k < nb; ++k)      // qkCoeffs[nbPublic + CommitmentIndex] = commitmentVal, prove.go:415-417
-        B2_CUDA(ctx, cudaMemcpyAsync(qk_br + pk->commit_row[k], bsb_val[k].l, sizeof(Fr), cudaMemcpyHostToDevice, s));
-    for (int k = 0; k < 4; ++k) B2_TRY(ntt_gnark(ctx, d0, v[k], 1, B200_DIF, 0));
-    B2_TRY(ntt_gnark(ctx, d0, qk_br, 1, B200_DIF, 0));
-    for (int k = 0; k < 4; ++k) B2_TRY(fr_bitrev_copy(ctx, v[k], cn[k], log_n));   // regular layout, for the openings
-    for (uint32_t k = 0; k < nb; ++k) {                                            // cCommitments[i].ToCanonical, prove.go:339
-        B2_TRY(ntt_gnark(ctx, d0, pi2_br[k], 1, B200_DIF, 0));
-        B2_TRY(fr_bitrev_copy(ctx, pi2_br[k], pi2_cn[k], log_n));
-    }
-    {
-        PlonkRowArgs a;
-        memset(&a, 0, sizeof a);
-        a.nb_bsb = nb;
-        a.beta = beta; a.gamma = gamma; a.alpha = alpha;
-        a.cs = d1->coset;
-        a.css = a.cs * a.cs;
-        a.tw = d0->tw_fwd.as<Fr>();
-        a.n = (uint32_t)n; a.log_big = pk->log_big; a.rho = pk->rho;
-        a.cres = cres;
-        Fr coset = Fr::one();
-        const Fr* srcs[5] = {v[0], v[1], v[2], v[3], qk_br};
-        for (uint32_t k = 0; k < pk->rho; ++k) {
-            coset = coset * (k == 0 ? d1->coset : d1->gen);
-            // bl <- bl * ((s w^k)^n - 1) scaled by powers of the shift (prove.go:985-993)
-            const Fr xn1 = coset.pow_u64(n) - Fr::one();
-            Fr acc = xn1;
-            for (int j = 0; j < 3; ++j) {
-                if (j < 2) { a.bl[j] = bl[j] * acc; a.br[j] = br[j] * acc; a.bo[j] = bo[j] * acc; }
-                a.bz[j] = bz[j] * acc;
-                acc = acc * coset;
-            }
-            const Fr* pre = pk->coset_pre.as<Fr>() + (size_t)k * n;
-            for (int p = 0; p < 5; ++p) {
-                B2_CUDA(ctx, cudaMemcpyAsync(tmp[p], srcs[p], n * sizeof(Fr), cudaMemcpyDeviceToDevice, s));
-                B2_TRY(ntt_run(ctx, d0, tmp[p], 0, 1, pre, nullptr, nullptr));
-            }
-            for (uint32_t p = 0; p < nb; ++p) {
-                B2_CUDA(ctx, cudaMemcpyAsync(pi2_ev[p], pi2_br[p], n * sizeof(Fr), cudaMemcpyDeviceToDevice, s));
-                B2_TRY(ntt_run(ctx, d0, pi2_ev[p], 0, 1, pre, nullptr, nullptr));
-                a.qci[2 * p] = pk->qcp_e(k, p);
-                a.qci[2 * p + 1] = pi2_ev[p];
-            }
-            B2_TRY(fr_scaled_omega(ctx, d0, beta * coset, idv));
-            a.x[PID_L] = tmp[0]; a.x[PID_R] = tmp[1]; a.x[PID_O] = tmp[2]; a.x[PID_Z] = tmp[3]; a.x[PID_ZS] = nullptr;
-            a.x[PID_QK] = tmp[4];
-            a.x[PID_QL] = pk->cev(k, CE_QL); a.x[PID_QR] = pk->cev(k, CE_QR); a.x[PID_QM] = pk->cev(k, CE_QM); a.x[PID_QO] = pk->cev(k, CE_QO);
-            a.x[PID_S1] = pk->cev(k, CE_S1); a.x[PID_S2] = pk->cev(k, CE_S2); a.x[PID_S3] = pk->cev(k, CE_S3);
-            a.x[PID_LONE] = pk->cev(k, CE_LONE);
-            a.x[PID_ID] = idv;
-            a.coset_index = k;
-            B2_TRY(plonk_quotient_rows(ctx, a));
-        }
-    }
-    B2_TRY(plonk_divide_xn(ctx, d1, log_n, cres));
-    B2_CUDA(ctx, cudaStreamSynchronize(s));
-    lap(T.quotient_ms);
-    if (3 * (n + 2) > big) return ctx->fail(B200_ERR_ARG, "big domain below 3(n+2)");
-    const Fr *h1 = cres, *h2 = cres + (n + 2), *h3 = cres + 2 * (n + 2);      // prove.go:652-666
-    G1XYZZ hx[3];
-    G1Affine h_com[3];
-    {                                                                          // commitToQuotient, prove.go:1198-1218
-        const Fr* sc[3] = {h1, h2, h3};
-        const size_t cnt[3] = {n + 2, n + 2, n + 2};
-        B2_TRY(commit_many(ctx, pk->srs, sc, cnt, 3, hx));
-        for (int k = 0; k < 3; ++k) h_com[k] = hx[k].to_affine();
-    }
-    lap(T.commit_h_ms);
-    for (int k = 0; k < 3; ++k) bind_point(fs, "zeta", h_com[k]);
-    const Fr zeta = derive(fs, "zeta");
-
-    // ---- open Z at w zeta (openZ, prove.go:634-650; kzg.Open) ------------------------------------------------
-    B2_TRY(fr_blind(ctx, cn[0], n, bl, 2));
-    B2_TRY(fr_blind(ctx, cn[1], n, br, 2));
-    B2_TRY(fr_blind(ctx, cn[2], n, bo, 2));
-    B2_TRY(fr_blind(ctx, cn[3], n, bz, 3));
-    const Fr zeta_shifted = zeta * d0->gen;
-    Fr zu;
-    B2_TRY(fr_poly_eval(ctx, cn[3], n + 3, zeta_shifted, &zu));
-    Fr* quot = tmp[0];
-    B2_TRY(fr_poly_div_linear(ctx, cn[3], n + 3, zeta_shifted, quot));
-    lap(T.open_z_ms);
-
-    // ---- foldH (prove.go:670-705) ---------------------------------------------------------------------
-    const Fr zn2 = zeta.pow_u64(n + 2);
-    Fr* fh = tmp[1];
-    B2_TRY(plonk_fold_h(ctx, h1, h2, h3, zn2, n + 2, fh));
-    G1XYZZ fhd = scalar_mul(hx[2], zn2);
-    fhd.add(hx[1]);
-    fhd = scalar_mul(fhd, zn2);
-    fhd.add(hx[0]);
-    const G1Affine fh_digest = fhd.to_affine();
-
-    // ---- linearised polynomial (computeLinearizedPolynomial, prove.go:708-777,1289-1389) --------------------
-    Fr blz, brz, boz, s1z, s2z;                // evaluateBlinded == the blinded polynomial at zeta
-    B2_TRY(fr_poly_eval(ctx, cn[0], n + 2, zeta, &blz));
-    B2_TRY(fr_poly_eval(ctx, cn[1], n + 2, zeta, &brz));
-    B2_TRY(fr_poly_eval(ctx, cn[2], n + 2, zeta, &boz));
-    B2_TRY(fr_poly_eval(ctx, pk->tr(TR_S1), n, zeta, &s1z));
-    B2_TRY(fr_poly_eval(ctx, pk->tr(TR_S2), n, zeta, &s2z));
-    Fr qcpz[B200_PLONK_MAX_BSB22];
-    for (uint32_t k = 0; k < nb; ++k) B2_TRY(fr_poly_eval(ctx, pk->qcp_c(k), n, zeta, &qcpz[k]));     // prove.go:724-729
-    Fr* lin = tmp[2];
-    {
-        PlonkLinArgs a;
-        memset(&a, 0, sizeof a);
-        a.bz = cn[3]; a.s3 = pk->tr(TR_S3); a.ql = pk->tr(TR_QL); a.qr = pk->tr(TR_QR); a.qm = pk->tr(TR_QM); a.qo = pk->tr(TR_QO);
-        a.qk = pk->tr(TR_QK);
-        a.nb_bsb = nb;
-        for (uint32_t k = 0; k < nb; ++k) { a.pi2[k] = pi2_cn[k]; a.qcp_zeta[k] = qcpz[k]; }
-        a.rl = brz * blz;
-        a.c1 = (s1z * beta + blz + gamma) * (s2z * beta + brz + gamma) * zu * beta;
-        const Fr u = d0->coset, uz = zeta * u, uuz = uz * u;
-        a.c2 = ((beta * zeta + blz + gamma) * (beta * uz + brz + gamma) * (beta * uuz + boz + gamma)).neg();
-        const Fr zn1 = zeta.pow_u64(n) - Fr::one();
-        a.lag = zn1 * (zeta - Fr::one()).inv() * alpha * alpha * d0->ninv;
-        a.alpha = alpha; a.l = blz; a.r = brz; a.o = boz;
-        a.n = (uint32_t)n; a.len = (uint32_t)(n + 3);
-        a.out = lin;
-        B2_TRY(plonk_linearize(ctx, a));
-    }
-    G1Affine lin_digest, zs_h;
-    {   // [quotient of the Z opening] and [linearised polynomial]: independent, committed as one pipelined pair
-        const Fr* sc[2] = {quot, lin};
-        const size_t cnt[2] = {n + 2, n + 3};
-        G1XYZZ c[2];
-        B2_TRY(commit_many(ctx, pk->srs, sc, cnt, 2, c));
-        zs_h = c[0].to_affine();
-        lin_digest = c[1].to_affine();
-    }
-    lap(T.linearize_ms);
-
-    // ---- batch opening at zeta (batchOpening, prove.go:779-833; kzg.BatchOpenSinglePoint) --------------------
-    Fr claimed[7];
-    B2_TRY(fr_poly_eval(ctx, fh, n + 2, zeta, &claimed[0]));
-    B2_TRY(fr_poly_eval(ctx, lin, n + 3, zeta, &claimed[1]));
-    claimed[2] = blz; claimed[3] = brz; claimed[4] = boz; claimed[5] = s1z; claimed[6] = s2z;
-    Fr gk;
-    {
-        Transcript g({"gamma"});
-        bind_fr(g, "gamma", zeta);
-        const G1Affine* dg[7] = {&fh_digest, &lin_digest, &lro[0], &lro[1], &lro[2], &pk->vk_pts[0], &pk->vk_pts[1]};
-        for (int k = 0; k < 7; ++k) bind_point(g, "gamma", *dg[k]);
-        for (uint32_t k = 0; k < nb; ++k) bind_point(g, "gamma", pk->vk_qcp[k]);
-        for (int k = 0; k < 7; ++k) bind_fr(g, "gamma", claimed[k]);
-        for (uint32_t k = 0; k < nb; ++k) bind_fr(g, "gamma", qcpz[k]);
-        bind_fr(g, "gamma", zu);
-        gk = derive(g, "gamma");
-    }
-    Fr* folded = tmp[3];
-    {
-        PlonkFoldArgs a;
-        memset(&a, 0, sizeof a);
-        const Fr* ps[7] = {fh, lin, cn[0], cn[1], cn[2], pk->tr(TR_S1), pk->tr(TR_S2)};
-        const size_t ls[7] = {n + 2, n + 3, n + 2, n + 2, n + 2, n, n};
-        Fr acc = Fr::one();
-        for (int k = 0; k < 7; ++k) { a.p[k] = ps[k]; a.len[k] = (uint32_t)ls[k]; a.g[k] = acc; acc = acc * gk; }
-        for (uint32_t k = 0; k < nb; ++k) { a.p[7 + k] = pk->qcp_c(k); a.len[7 + k] = (uint32_t)n; a.g[7 + k] = acc; acc = acc * gk; }
-        a.count = 7 + nb; a.width = (uint32_t)(n + 3);
-        a.out = folded;
-        B2_TRY(plonk_fold_polys(ctx, a));
-    }
-    B2_TRY(fr_poly_div_linear(ctx, folded, n + 3, zeta, quot));
-    G1Affine batched_h;
-    {
-        G1XYZZ c;
-        B2_TRY(commit(ctx, pk->srs, quot, n + 2, &c));
-        batched_h = c.to_affine();
-    }
-    lap(T.batch_open_ms);
-    T.total_ms = (float)(now_ms() - t_start);
-
-    memset(out, 0, sizeof *out);
-    for (int k = 0; k < 3; ++k) { put_point(out->lro[k], lro[k]); put_point(out->h[k], h_com[k]); }
-    put_point(out->z, z_com);
-    put_point(out->batched_h, batched_h);
-    for (int k = 0; k < 7; ++k) put_fr(out->claimed[k], claimed[k]);
-    put_point(out->zshift_h, zs_h);
-    put_fr(out->zshift_value, zu);
-    put_fr(out->challenges[0], gamma); put_fr(out->challenges[1], beta); put_fr(out->challenges[2], alpha);
-    put_fr(out->challenges[3], zeta); put_fr(out->challenges[4], gk);
-    out->nb_bsb22 = nb;
-    for (uint32_t k = 0; k < nb; ++k) { put_fr(out->claimed_qcp[k], qcpz[k]); put_point(out->bsb22[k], bsb_com[k]); }
-    if (tm) *tm = T;
-    return B200_OK;
+    if (!out) return ctx->fail(B200_ERR_ARG, "null argument");
+    if (pk && pk->shard_count > 1) return ctx->fail(B200_ERR_ARG, "a sharded key proves through the session phases (b200_plonk_session_*)");
+    b200_plonk_session* S = nullptr;
+    uint64_t a[36], b[36];
+    B2_TRY(b200_plonk_session_begin(ctx, pk, l, r, o, public_witness, blinding, bsb, &S, a));
+    // one rank: the partial commitments are the totals
+    int st = b200_plonk_session_step(ctx, S, 1, a, b);
+    if (st == B200_OK) st = b200_plonk_session_step(ctx, S, 2, b, nullptr);
+    if (st == B200_OK) st = b200_plonk_session_step(ctx, S, 3, nullptr, a);
+    if (st == B200_OK) st = b200_plonk_session_step(ctx, S, 4, a, b);
+    if (st == B200_OK) st = b200_plonk_session_step(ctx, S, 5, b, a);
+    if (st != B200_OK) { b200_plonk_session_finish(ctx, S, nullptr, nullptr, nullptr); return st; }
+    return b200_plonk_session_finish(ctx, S, a, out, tm);
 }
 
 int b200_plonk_derive_challenges(const uint64_t* vk_commitments, const uint64_t* vk_qcp, const uint64_t* public_witness, size_t nb_public,

@@ -154,3 +154,80 @@ def torch_exchange(dist, async_op=False):
         work = dist.all_to_all_single(recv.view(-1), send.view(-1), async_op=async_op)
         return work if async_op else None
     return exchange
+
+
+# ------------------------------------------------------------------------------------------
+# Multi-GPU PlonK (P1 range-sharded commitments, P4 coset-parallel quotient) over the phase
+# ABI b200_plonk_session_*: every rank holds its shard of the key (plonk_pk_upload(shard_index, shard_count)),
+# runs the same phases on the same solution and blinding, and between phases
+#   * the partial commitments (96-byte Jacobian points) are all-gathered and added on the host, and
+#   * after phase 2 the numerator's coset blocks are all-gathered in place on the device (coset k, computed by
+#     rank k mod R, is block bitrev(k) of the bit-reversed big-domain buffer: prove.go:1029-1035).
+# ------------------------------------------------------------------------------------------
+def coset_block(k: int, log_blocks: int) -> int:
+    """Block of the numerator buffer that holds coset k: bitrev_{log_big}(rho i + k) = bitrev(k) n + bitrev_{log_n}(i)."""
+    r = 0
+    for b in range(log_blocks):
+        r |= ((k >> b) & 1) << (log_blocks - 1 - b)
+    return r
+
+
+def sum_partials(parts) -> np.ndarray:
+    """parts: per-rank (m, 12) partial G1Jac commitments -> (m, 12) totals."""
+    acc = np.array(parts[0], dtype=np.uint64).reshape(-1, 12).copy()
+    for p in parts[1:]:
+        q = np.asarray(p, dtype=np.uint64).reshape(-1, 12)
+        for j in range(acc.shape[0]):
+            acc[j] = api.g1_jac_add(acc[j], q[j])
+    return acc
+
+
+def _gather_points(dist, partials: np.ndarray, device=None) -> np.ndarray:
+    import torch
+    flat = torch.from_numpy(np.ascontiguousarray(partials, dtype=np.uint64).view(np.int64).reshape(-1).copy())
+    if device is not None:
+        flat = flat.to(device)
+    gathered = [torch.empty_like(flat) for _ in range(dist.get_world_size())]
+    dist.all_gather(gathered, flat)
+    return sum_partials([g.cpu().numpy().view(np.uint64) for g in gathered])
+
+
+def plonk_exchange_numerator(dist, session, device):
+    """All-gather the coset blocks of the quotient numerator in place (NCCL over NVLink)."""
+    import torch
+    ptr, block_elems, log_blocks = session.numerator()
+    rho, world, rank = 1 << log_blocks, dist.get_world_size(), dist.get_rank()
+    words = block_elems * 4
+
+    class _Mem:      # __cuda_array_interface__ view of the library's buffer, no copy
+        def __init__(self, p, n):
+            self.__cuda_array_interface__ = {"shape": (n,), "typestr": "<i8", "data": (p, False), "version": 2}
+    buf = torch.as_tensor(_Mem(ptr, rho * words), device=device)
+    mine = [k for k in range(rho) if k % world == rank]
+    rounds = (rho + world - 1) // world
+    for j in range(rounds):                      # round j moves coset j * world + r of every rank r that has one
+        owners = [r for r in range(world) if j * world + r < rho]
+        if len(owners) == world:
+            outs = [buf[coset_block(j * world + r, log_blocks) * words:][:words] for r in range(world)]
+            dist.all_gather(outs, outs[rank])
+        else:                                     # fewer cosets than ranks in the last round: broadcasts
+            for r in owners:
+                blk = buf[coset_block(j * world + r, log_blocks) * words:][:words]
+                dist.broadcast(blk, src=r)
+    return mine
+
+
+def plonk_prove_distributed(dist, ctx, pk, l, r, o, public_witness, blinding, bsb=None, device=None):
+    """One PlonK proof over dist.get_world_size() GPUs; every rank returns the same (PlonkProof, timings)."""
+    s = ctx.plonk_session(pk, l, r, o, public_witness, blinding, bsb)
+    try:
+        s.step(1, _gather_points(dist, s.partials, device))
+        s.step(2, _gather_points(dist, s.partials, device))
+        plonk_exchange_numerator(dist, s, device)
+        s.step(3)
+        s.step(4, _gather_points(dist, s.partials, device))
+        s.step(5, _gather_points(dist, s.partials, device))
+        return s.finish(_gather_points(dist, s.partials, device))
+    except Exception:
+        s.abandon()
+        raise

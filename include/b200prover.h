@@ -374,6 +374,9 @@ typedef struct b200_plonk_pk_desc {
     const uint64_t *const *qcp;     /* pk.trace.Qcp[i]: canonical / regular, n each (NULL when nb_bsb22 = 0)  */
     const uint64_t *vk_qcp;         /* pk.Vk.Qcp: nb_bsb22 affine points                                     */
     const size_t *commitment_index; /* CommitmentInfo[i].CommitmentIndex (constraint index; the row is + nb_public) */
+    int shard_index, shard_count;   /* multi-GPU: this rank's share (0, 0 or 0, 1 = the whole key).  The arrays above are
+                                       always the full ones; the rank keeps the SRS point range [N k / R, N (k+1) / R) on its
+                                       device and evaluates the quotient on the cosets k = shard_index (mod shard_count).      */
 } b200_plonk_pk_desc;
 
 /* One-time residency: trace polynomials, their evaluations on the rho cosets of the big domain
@@ -423,6 +426,31 @@ int b200_plonk_prove(b200_ctx *ctx, const b200_plonk_pk *pk, const uint64_t *l, 
 int b200_plonk_prove_bsb22(b200_ctx *ctx, const b200_plonk_pk *pk, const uint64_t *l, const uint64_t *r, const uint64_t *o,
                            const uint64_t *public_witness, const uint64_t *blinding, const b200_plonk_bsb22 *bsb,
                            b200_plonk_proof *out, b200_plonk_timings *timings);
+
+/* ---- the same proof as a session of phases: multi-GPU (PlonK P1 range-sharded MSMs, P4 coset-
+ * parallel quotient).  One process per GPU, each with its shard of the key; every rank runs the same phases on the
+ * same inputs and blinding; a phase returns this rank's PARTIAL commitments (G1Jac, 12 u64 each) and the next phase
+ * takes the TOTALS (the caller adds the ranks' partials: b200_g1_jac_add after an all-gather of 96-byte points --
+ * no data-path collective for the MSMs).  After phase 2 the caller all-gathers the numerator's coset blocks in
+ * place (b200_plonk_session_numerator: coset k lives in block bitrev(k) of 2^log_blocks blocks of block_elems Fr).
+ *   begin   -> 3 partials [L] [R] [O]
+ *   step 1  (3 totals) -> 1 partial [Z]
+ *   step 2  (1 total)  -> nothing; this rank's coset blocks of the numerator are written
+ *   step 3  (nothing)  -> 3 partials [H1] [H2] [H3]     (needs every block of the numerator)
+ *   step 4  (3 totals) -> 2 partials [Z opening quotient] [linearised polynomial]
+ *   step 5  (2 totals) -> 1 partial [batch opening quotient]
+ *   finish  (1 total)  -> the proof (identical on every rank); frees the session.
+ * b200_plonk_prove_bsb22 is exactly this sequence with totals = partials.  A sharded proof requires `blinding`. */
+typedef struct b200_plonk_session b200_plonk_session;
+int b200_plonk_session_begin(b200_ctx *ctx, const b200_plonk_pk *pk, const uint64_t *l, const uint64_t *r, const uint64_t *o,
+                             const uint64_t *public_witness, const uint64_t *blinding, const b200_plonk_bsb22 *bsb,
+                             b200_plonk_session **out, uint64_t *partials);
+int b200_plonk_session_step(b200_ctx *ctx, b200_plonk_session *session, int phase, const uint64_t *totals, uint64_t *partials);
+int b200_plonk_session_numerator(b200_ctx *ctx, b200_plonk_session *session, void **cres_dev, size_t *block_elems,
+                                 unsigned *log_blocks);
+/* totals = proof = NULL abandons a session at any point. */
+int b200_plonk_session_finish(b200_ctx *ctx, b200_plonk_session *session, const uint64_t *totals, b200_plonk_proof *out,
+                              b200_plonk_timings *timings);
 
 /* The four Fiat-Shamir challenges gamma, beta, alpha, zeta (16 u64, Montgomery) of a proof's commitments:
  * bindPublicData + deriveRandomness (plonk/bn254/verify.go:296-360) over SHA-256, gnark-crypto's

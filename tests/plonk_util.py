@@ -19,7 +19,7 @@ def srs_arrays(pk: PP.ProvingKey):
     return cref.g1_batch_mul(gen, cref.ints_to_mont(mono, B.R)), cref.g1_batch_mul(gen, cref.ints_to_mont(lag, B.R))
 
 
-def upload_pk(ctx, pk: PP.ProvingKey):
+def upload_pk(ctx, pk: PP.ProvingKey, shard_index=0, shard_count=1):
     kzg, kzg_lag = srs_arrays(pk)
     f = util.fr_arr
     return ctx.plonk_pk_upload(
@@ -28,7 +28,7 @@ def upload_pk(ctx, pk: PP.ProvingKey):
         s1=f(pk.s1), s2=f(pk.s2), s3=f(pk.s3), perm=np.array(pk.perm, dtype=np.int64), kzg_g1=kzg, kzg_lagrange_g1=kzg_lag,
         vk_commitments=util.g1_arr(vk_points(pk)), nb_public=pk.nb_public,
         qcp=[f(q) for q in pk.qcp], vk_qcp=util.g1_arr(pk.vk["Qcp"]) if pk.qcp else None,
-        commitment_index=[c["index"] for c in pk.commitments])
+        commitment_index=[c["index"] for c in pk.commitments], shard_index=shard_index, shard_count=shard_count)
 
 
 def bsb_arrays(bsb):

@@ -201,3 +201,58 @@ def test_bsb22_commitment_circuits(ctx, pkg, nb_mul, nb_commit):
     assert util.fr_ints(got.as_dict()["challenges"]) == [ch["gamma"], ch["beta"], ch["alpha"], ch["zeta"], ch["gamma_kzg"]]
     assert pkg.plonk_proof_bytes(got) == PP.proof_bytes(want)
     assert PP.verify(PU.struct_to_proof(fresh), pk.vk, sol[:1], pk.tau)
+
+
+@pytest.mark.parametrize("world", [2, 4, 8])
+@pytest.mark.parametrize("nb_mul,nb_commit", [(5, 0), (100, 0), (40, 2)])
+def test_sharded_proof_on_virtual_ranks(ctx, pkg, world, nb_mul, nb_commit):
+    """The phase ABI with the key sharded over `world` virtual ranks on one GPU (real kernels; the exchanges --
+    sum of partial commitments, all-gather of the numerator's coset blocks -- done through the host): the proof is
+    byte-identical to the single-GPU one and to the oracle's.  rho = 8 at the smallest size, 4 otherwise."""
+    rng = random.Random(7000 + nb_mul)
+    if nb_commit:
+        spr = PP.commit_chain_scs(nb_mul, nb_commit)
+        pk = PP.setup(spr, rng.randrange(1, R))
+        sol, bsb = PP.commit_chain_solution(spr, pk, rng.randrange(2, R), [(rng.randrange(R), rng.randrange(R)) for _ in range(nb_commit)])
+    else:
+        spr, bsb = PP.mul_chain_scs(nb_mul), None
+        pk = PP.setup(spr, rng.randrange(1, R))
+        sol = PP.mul_chain_solution(nb_mul, rng.randrange(2, R))
+    blinding = tuple([rng.randrange(R) for _ in range(k)] for k in (2, 2, 2, 3))
+    want, _ = PP.prove(spr, pk, sol, blinding, bsb)
+    L, Rr, O = (util.fr_arr(v) for v in PP.evaluate_lro(spr, sol))
+    pub, bl, bsb_a = util.fr_arr(sol[:1]), PU.blinding_array(blinding), PU.bsb_arrays(bsb)
+    S = pkg.sharding
+    keys = [PU.upload_pk(ctx, pk, shard_index=k, shard_count=world) for k in range(world)]
+    sess = []
+    try:
+        sess = [ctx.plonk_session(keys[k], L, Rr, O, pub, bl, bsb_a) for k in range(world)]
+        tot = S.sum_partials([s.partials for s in sess])
+        tot = S.sum_partials([s.step(1, tot) for s in sess])
+        for s in sess:
+            s.step(2, tot)
+        # exchange of the coset blocks through the host
+        ptrs = [s.numerator() for s in sess]
+        _, be, lb = ptrs[0]
+        rho = 1 << lb
+        for k in range(rho):
+            owner, blk = k % world, S.coset_block(k, lb)
+            src = pkg.DeviceVector.__new__(pkg.DeviceVector)
+            src.ctx, src.nbytes, src.ptr = ctx, be * 32, __import__("ctypes").c_void_p(ptrs[owner][0] + blk * be * 32)
+            data = src.download((be, 4))
+            for r2 in range(world):
+                if r2 != owner:
+                    dst = pkg.DeviceVector.__new__(pkg.DeviceVector)
+                    dst.ctx, dst.nbytes, dst.ptr = ctx, be * 32, __import__("ctypes").c_void_p(ptrs[r2][0] + blk * be * 32)
+                    dst.upload(data)
+        tot = S.sum_partials([s.step(3) for s in sess])
+        tot = S.sum_partials([s.step(4, tot) for s in sess])
+        tot = S.sum_partials([s.step(5, tot) for s in sess])
+        proofs = [s.finish(tot)[0] for s in sess]
+    finally:
+        for s in sess:
+            s.abandon()
+        for k in keys:
+            k.free()
+    for p in proofs:
+        assert pkg.plonk_proof_bytes(p) == PP.proof_bytes(want)

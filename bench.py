@@ -428,28 +428,32 @@ def gpu_arm(args):
         combined = pkg.sharding.gather_combine(dist, o.as_dict(), device=f"cuda:{local}")
         e2e_s += max_over_ranks(time.perf_counter() - t1)
 
+    pk_info = pk.info()
+    args.plonk_result = None
     if dist is not None:
         ctx.use_stream(None)
+    if args.plonk_log_n and (world == 1 or (args.plonk_dist and (world & (world - 1)) == 0)):
+        pk.free()                       # the folded tables go before the PlonK key comes
+        try:
+            args.plonk_result = plonk_section(pkg, ctx, args.plonk_log_n, args.steps, args.warmup, dist, rank, world,
+                                              f"cuda:{local}", barrier, max_over_ranks)
+        except Exception as e:          # the headline line must still be printed
+            args.plonk_result = {"error": repr(e)}
+    if dist is not None:
         dist.barrier()
         dist.destroy_process_group()
     if rank != 0:
         ctx.close()
         return 0
-    pk_info = pk.info()
-    args.plonk_result = None
-    if world == 1 and args.plonk_log_n:
-        pk.free()                       # the 78 GiB of folded tables go before the PlonK key comes
-        try:
-            args.plonk_result = plonk_section(pkg, ctx, args.plonk_log_n, args.steps, args.warmup)
-        except Exception as e:          # the headline line must still be printed
-            args.plonk_result = {"error": repr(e)}
     return report(args, world, peak, prof, stage, step_ms, e2e_s, clk, verified, inst, t_setup, wall_dev, pk_info, distributed, h2d_bytes)
 
 
-def plonk_section(pkg, ctx, log_n, steps, warmup):
+def plonk_section(pkg, ctx, log_n, steps, warmup, dist=None, rank=0, world=1, device=None, barrier=None, max_over_ranks=None):
     """BASELINE.json config 4: BN254 PlonK Prove at 2^log_n gates (SCS Mul chain, backend/plonk/plonk_test.go:248-260
-    shape) through b200_plonk_prove with page-locked host L, R, O; every proof is checked with the trapdoor form of
-    plonk.Verify (verify.go:45-294; plonk_host.verify_with_trapdoor).  Wall time per proof, host buffers in, proof out."""
+    shape) with page-locked host L, R, O; every timed proof is checked with the trapdoor form of plonk.Verify
+    (verify.go:45-294; plonk_host.verify_with_trapdoor).  Wall time per proof, host buffers in, proof out.
+    N = 1: b200_plonk_prove.  N > 1: the phase ABI with the key sharded over the ranks (commitments by SRS point
+    range, quotient by coset; sharding.plonk_prove_distributed), max over ranks."""
     import importlib
     H = importlib.import_module("gnark_fork_b200.plonk_host")
     n = 1 << log_n
@@ -458,33 +462,50 @@ def plonk_section(pkg, ctx, log_n, steps, warmup):
     trace, lro, nb_vars, nb_pub, L, Rr, O, pub = H.mul_chain(log_n, 3)
     d = H.Domains(n)
     kw = H.setup(ctx, d, trace, lro, nb_vars, nb_pub, tau)
-    dpk = ctx.plonk_pk_upload(**kw)
+    dpk = ctx.plonk_pk_upload(**kw, shard_index=rank, shard_count=world)
     t_setup = time.perf_counter() - t0
     bufs = []
     for a in (L, Rr, O):
         b = pkg.pinned_empty(a.shape)
         b[:] = a
         bufs.append(b)
+    rng = np.random.default_rng(777)            # the same blinding on every rank (a sharded proof needs it)
+
+    def one():
+        if world == 1:
+            return ctx.plonk_prove(dpk, *bufs, pub, None)
+        return pkg.sharding.plonk_prove_distributed(dist, ctx, dpk, *bufs, pub, rand_field(rng, 9), None, device)
+
     ctx.profile_start()
     for _ in range(max(1, warmup)):
-        ctx.plonk_prove(dpk, *bufs, pub, None)
+        one()
     launches = ctx.profile_read()["kernel_launches"] // max(1, warmup)
     wall, stages = [], []
     for _ in range(steps):
+        if barrier:
+            barrier()
         t1 = time.perf_counter()
-        proof, tm = ctx.plonk_prove(dpk, *bufs, pub, None)
+        proof, tm = one()
+        if barrier:
+            barrier()
         wall.append((time.perf_counter() - t1) * 1e3)
         stages.append(tm)
-    ok = H.verify_with_trapdoor(proof, kw["vk_commitments"], H.from_mont_array(pub), d, tau)
+    ms = float(np.mean(wall))
+    if max_over_ranks:
+        ms = max_over_ranks(ms)
+    ok = H.verify_with_trapdoor(proof, kw["vk_commitments"], H.from_mont_array(pub), d, tau) if rank == 0 else True
     dpk.free()
     mean_stage = {k: float(np.mean([s[k] for s in stages])) for k in stages[0]}
     msm_ms = sum(mean_stage[k] for k in ("commit_lro_ms", "commit_z_ms", "commit_h_ms", "batch_open_ms")) + mean_stage["linearize_ms"]
-    return {"metric": "BN254 PlonK prove ms @2^%d gates" % log_n, "value": float(np.mean(wall)), "unit": "ms", "steps": steps,
+    return {"metric": "BN254 PlonK prove ms @2^%d gates" % log_n, "value": ms, "unit": "ms", "n_gpus": world, "steps": steps,
             "workload": "SCS Mul chain filling 2^%d rows, big domain 2^%d; 10 KZG commitments (G1 MSM of ~2^%d against 2 resident SRS), "
                         "%d transforms of 2^%d + 1 of 2^%d, fresh blinding per proof" % (log_n, d.log_big, log_n, 5 + 5 * (d.big // n), log_n, d.log_big),
-            "path": "b200_plonk_prove (page-locked host L, R, O in; proof out; Fiat-Shamir on the host)",
+            "path": "b200_plonk_prove (page-locked host L, R, O in; proof out; Fiat-Shamir on the host)" if world == 1 else
+                    "b200_plonk_session_* phases on %d ranks: commitments sharded by SRS point range (96-byte partial sums all-gathered, host add), "
+                    "quotient sharded by coset (numerator blocks all-gathered over NCCL)" % world,
             "h2d_bytes_per_step": int(3 * n * 32 + 32), "d2h_bytes_per_step": 552,
-            "stage_ms": mean_stage, "commit_ms_share": msm_ms / mean_stage["total_ms"],
+            "stage_ms": mean_stage, "stage_ms_note": "rank 0, library time only (exchanges between phases are in value, not in stage_ms)",
+            "commit_ms_share": msm_ms / mean_stage["total_ms"],
             "gpu_launches_per_proof": int(launches), "verified": bool(ok), "verifier": "plonk.Verify with the KZG pairing checks done in G1 through the known tau of the test SRS",
             "setup_s": t_setup}
 
@@ -574,7 +595,8 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--log-n", type=int, default=24)
     ap.add_argument("--cpu-sample-log", type=int, default=18)
-    ap.add_argument("--plonk-log-n", type=int, default=22, help="N = 1: also time BN254 PlonK Prove at 2^k gates (config 4); 0 = skip")
+    ap.add_argument("--plonk-log-n", type=int, default=22, help="also time BN254 PlonK Prove at 2^k gates (config 4; sharded over the ranks at N > 1); 0 = skip")
+    ap.add_argument("--plonk-dist", action="store_true", help="N > 1: run the sharded PlonK proof too (off by default: the scaling run stays the Groth16 line only)")
     ap.add_argument("--no-check", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--replicate-h", action="store_true", help="N > 1: every rank runs the whole computeH (no exchange)")

@@ -214,6 +214,7 @@ def plonk_exchange_numerator(dist, session, device):
             for r in owners:
                 blk = buf[coset_block(j * world + r, log_blocks) * words:][:words]
                 dist.broadcast(blk, src=r)
+    torch.cuda.synchronize()                      # the library's stream continues from here
     return mine
 
 

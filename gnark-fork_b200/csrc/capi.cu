@@ -237,7 +237,7 @@ int b200_bases_upload(b200_ctx* ctx, int curve, int group, const uint64_t* bases
     const int c = ctx->msm_fold_c ? ctx->msm_fold_c : msm_fold_window(n);
     if (ctx->msm_precompute && n >= 4096 && c != 0) {
         DevBuf table;
-        const size_t reserve = msm_workspace_bytes(n, group, ctx->msm_c_override, c) + n * sizeof(Fr) + ((size_t)1 << 30);
+        const size_t reserve = msm_workspace_bytes(n, group, ctx->msm_mode(), c) + n * sizeof(Fr) + ((size_t)1 << 30);
         const int st = group == 1 ? msm_fold_build_g1(ctx, b->pts.as<G1Affine>(), n, c, reserve, table)
                                   : msm_fold_build_g2(ctx, b->pts.as<G2Affine>(), n, c, reserve, table);
         if (st == B200_OK) {
@@ -546,6 +546,8 @@ int b200_set_option(b200_ctx* ctx, const char* key, long value) {
     if (k == "msm_c") { if (value != 0 && (value < 4 || value > 24)) return ctx->fail(B200_ERR_ARG, "msm_c out of range"); ctx->msm_c_override = (int)value; }
     else if (k == "ntt_tile_log") { if (value < 6 || value > 12) return ctx->fail(B200_ERR_ARG, "ntt_tile_log out of range"); ctx->ntt_tile_log = (int)value; }
     else if (k == "ntt_strided_stages") { if (value < 1 || value > 12) return ctx->fail(B200_ERR_ARG, "ntt_strided_stages out of range"); ctx->ntt_strided_stages = (int)value; }
+    else if (k == "msm_ba") { if (value < 0 || value > 6) return ctx->fail(B200_ERR_ARG, "msm_ba out of range"); ctx->msm_ba = (int)value; }
+    else if (k == "msm_ba_force") { ctx->msm_ba_force = value ? 1 : 0; }
     else if (k == "msm_overlap") { ctx->msm_overlap = value ? 1 : 0; }
     else if (k == "msm_precompute") { ctx->msm_precompute = value ? 1 : 0; }
     else if (k == "msm_fold_c") { if (value != 0 && (value < 8 || value > 24)) return ctx->fail(B200_ERR_ARG, "msm_fold_c out of range"); ctx->msm_fold_c = (int)value; }

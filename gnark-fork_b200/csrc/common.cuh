@@ -31,6 +31,9 @@ struct b200_ctx {
     void* poly_scratch = nullptr;           // small persistent scratch of the polynomial primitives (poly.cu), stream-ordered
     size_t poly_scratch_bytes = 0;
     int msm_c_override = 0;                 // tuning knobs (b200_set_option / B200_MSM_C env)
+    int msm_ba = 0;                         // batched-affine pre-reduction rounds (msm_ba.cuh); 0 = off
+    int msm_ba_force = 0;                   // tests: keep the rounds on MSMs too small to profit
+    int msm_mode() const { return (msm_c_override & 0xff) | ((msm_ba & 0xf) << 8) | (msm_ba_force ? 0x1000 : 0); }   // what MsmLayout decodes
     int msm_precompute = 1;                 // build folded-window tables for resident base sets
     int msm_fold_c = 0;                     // 0 = automatic (msm_fold_window)
     int ntt_tile_log = 9, ntt_strided_stages = 8, ntt_threads = 128;   // measured best (scripts/ntt_sweep.py): many small CTAs overlap load, butterflies and store

@@ -129,8 +129,8 @@ int groth16_pk_upload(b200_ctx* ctx, const b200_groth16_pk_desc* d, b200_groth16
     const size_t n_max = std::max(std::max(pk->n_a, pk->n_b), std::max(pk->n_k, pk->n_z));
     const int fc = ctx->msm_fold_c ? ctx->msm_fold_c : msm_fold_window(n_max);
     const size_t reserve = 9 * n_dom * sizeof(Fr) + d->n_wires * sizeof(Fr) + d->n_wires * 4
-                         + msm_workspace_bytes(n_max, 2, ctx->msm_c_override, fc)
-                         + msm_sizes(n_max, 2, ctx->msm_c_override, fc).sort_bytes + ((size_t)1 << 30);   // two sort groups
+                         + msm_workspace_bytes(n_max, 2, ctx->msm_mode(), fc)
+                         + msm_sizes(n_max, 2, ctx->msm_mode(), fc).sort_bytes + ((size_t)1 << 30);   // two sort groups
     if (st == B200_OK) st = maybe_fold<Fp2>(ctx, pk->G2B, pk->n_b, pk->fG2B, 2, reserve);
     if (st == B200_OK) st = maybe_fold<Fp>(ctx, pk->A, pk->n_a, pk->fA, 1, reserve);
     if (st == B200_OK) st = maybe_fold<Fp>(ctx, pk->B, pk->n_b, pk->fB, 1, reserve);
@@ -172,7 +172,7 @@ int groth16_prove_core(b200_ctx* ctx, const b200_groth16_pk* pk, const uint64_t*
     MsmSizes sz[5];
     size_t sort_max = 0, acc_max = 0, res_off[6] = {0};
     for (int k = 0; k < 5; ++k) {
-        sz[k] = msm_sizes(counts[k], groups[k], ctx->msm_c_override, folds[k]->c);
+        sz[k] = msm_sizes(counts[k], groups[k], ctx->msm_mode(), folds[k]->c);
         sort_max = std::max(sort_max, sz[k].sort_bytes);
         acc_max = std::max(acc_max, sz[k].acc_bytes);
         res_off[k + 1] = res_off[k] + ((sz[k].result_bytes + 255) & ~(size_t)255);

@@ -240,6 +240,21 @@ static __global__ void msm_scan_final_kernel(const uint32_t* __restrict__ in, ui
     }
 }
 
+// batched-affine mode (msm_ba.cuh): padded[b] = count rounded up to 2^ba slots, reduced[b] = padded >> ba points
+static __global__ void msm_pad_counts_kernel(const uint32_t* __restrict__ counts, uint32_t m, int ba, uint32_t* __restrict__ padded,
+                                             uint32_t* __restrict__ reduced) {
+    const uint32_t b = blockIdx.x * blockDim.x + threadIdx.x;
+    if (b >= m) return;
+    const uint32_t q = (1u << ba) - 1u;
+    const uint32_t p = (counts[b] + q) & ~q;
+    padded[b] = p;
+    reduced[b] = p >> ba;
+}
+static __global__ void msm_shift_kernel(const uint32_t* __restrict__ in, uint32_t m, int sh, uint32_t* __restrict__ out) {
+    const uint32_t b = blockIdx.x * blockDim.x + threadIdx.x;
+    if (b < m) out[b] = in[b] >> sh;
+}
+
 // 3. scatter (counting sort): cursor starts as a copy of the offsets.
 static __global__ void msm_scatter_kernel(const int32_t* __restrict__ digits, uint32_t n, int c, int W, int fold, uint32_t stride, uint32_t nb,
                                    uint32_t* __restrict__ cursor, uint32_t* __restrict__ sorted) {
@@ -384,7 +399,8 @@ __global__ void __launch_bounds__(128, (sizeof(F) > 32 ? 2 : 1)) msm_accumulate_
                                       const uint32_t* __restrict__ offsets, const uint32_t* __restrict__ counts,
                                       const uint32_t* __restrict__ task_bucket, const uint32_t* __restrict__ task_off,
                                       const uint32_t* __restrict__ ntasks, const uint32_t* __restrict__ order, uint32_t max_tasks,
-                                      uint32_t chunk, XYZZ<F>* __restrict__ buckets, XYZZ<F>* __restrict__ partials) {
+                                      uint32_t chunk, XYZZ<F>* __restrict__ buckets, XYZZ<F>* __restrict__ partials, uint32_t direct) {
+    // direct != 0: `bases` are the points left by the batched-affine rounds, already in bucket order (no entry list)
     const uint32_t slot = blockIdx.x * blockDim.x + threadIdx.x;
     if (slot >= max_tasks) return;
     const uint32_t t = order[slot];
@@ -396,7 +412,7 @@ __global__ void __launch_bounds__(128, (sizeof(F) > 32 ? 2 : 1)) msm_accumulate_
     const uint32_t start = offsets[b] + first;
     XYZZ<F> acc = XYZZ<F>::inf();
     for (uint32_t j = 0; j < cnt; ++j) {
-        const uint32_t e = sorted[start + j];
+        const uint32_t e = direct ? start + j : sorted[start + j];
         Affine<F> p = ldg_vec(bases + (e & 0x7fffffffu));
         if (e >> 31) p.y = p.y.neg();
         acc.add_mixed(p);

@@ -2,6 +2,7 @@
 #pragma once
 #include <vector>
 #include "msm.cuh"
+#include "msm_ba.cuh"
 
 namespace b200 {
 
@@ -58,13 +59,29 @@ struct MsmLayout {
     size_t off_buckets, off_partials, off_S[2], off_W[2], acc_total;
     size_t total;   // sort_total + acc_total
     uint32_t scan_blocks, chunk, max_tasks, order_shift, T, logT, Q;
+    // batched-affine pre-reduction (msm_ba.cuh): ba rounds, entry slots padded per bucket to 2^ba
+    int ba;
+    size_t pad_entries;                       // upper bound of the padded slot count (multiple of 2^ba * BA_K)
+    size_t off_rcounts, off_roffsets;         // per-bucket counts / offsets after the rounds
+    size_t off_ba_pts[2], off_ba_pref, off_ba_cprod, off_ba_cinv;
+    // c_override carries the MSM mode: bits 0-7 the window override, bits 8-11 the batched-affine rounds
     MsmLayout(size_t n_, int c_override, int fold_c) {
         n = n_;
+        ba = (c_override >> 8) & 0xf;
+        const bool ba_force = (c_override & 0x1000) != 0;
+        c_override &= 0xff;
         plan = fold_c ? msm_plan_folded(fold_c) : msm_plan(n, c_override);
         M = (size_t)plan.WB * plan.nb;
+        if (!ba_force && ((size_t)plan.W * n < ((size_t)1 << 22) || ((size_t)plan.W * n) / M < ((size_t)8 << ba))) ba = 0;   // too little work per round / per bucket
+        pad_entries = (size_t)plan.W * n;
+        if (ba) {
+            const size_t q = ((size_t)1 << ba) * BA_K;
+            pad_entries += M * (((size_t)1 << ba) - 1);
+            pad_entries = (pad_entries + q - 1) / q * q;
+        }
         // task splitting: pieces of at most twice the mean bucket load, but small enough that the
         // launch has ~400 K tasks (148 SMs x 20 warps x 32 lanes x 4 waves) even when few buckets exist
-        const size_t entries = (size_t)plan.W * n, mean = entries / M;
+        const size_t entries = ba ? (pad_entries >> ba) : (size_t)plan.W * n, mean = entries / M;
         size_t ch = entries / 400000;
         const size_t hi = 2 * mean < 64 ? 64 : 2 * mean;
         if (ch > hi) ch = hi;
@@ -76,7 +93,7 @@ struct MsmLayout {
         while ((chunk >> order_shift) > (uint32_t)ORDER_BINS - 2) ++order_shift;
         Arena a;
         off_digits = a.off; a.take((size_t)plan.W * n * 4);
-        off_sorted = a.off; a.take((size_t)plan.W * n * 4);
+        off_sorted = a.off; a.take(pad_entries * 4);
         off_counts = a.off; a.take(M * 4);
         off_offsets = a.off; a.take(M * 4);
         off_cursor = a.off; a.take(M * 4);
@@ -87,6 +104,8 @@ struct MsmLayout {
         off_big = a.off; a.take((M + 2) * 4);   // [0], [1] = counts, then the list (front: warp-merged, back: CTA-merged)
         off_order = a.off; a.take((size_t)max_tasks * 4);
         off_order_hist = a.off; a.take((size_t)ORDER_BINS * 4 * 2);
+        off_rcounts = a.off; a.take(ba ? M * 4 : 0);
+        off_roffsets = a.off; a.take(ba ? M * 4 : 0);
         sort_total = a.off;
         Arena g;
         off_buckets = g.off; g.take(M * sizeof(XYZZ<F>));
@@ -101,6 +120,11 @@ struct MsmLayout {
         // tree ping-pong buffers: WB * Q arrays of T/2 and T/4 points
         off_S[1] = g.off; g.take((size_t)plan.WB * Q * (T / 2 + 1) * sizeof(XYZZ<F>));
         off_W[1] = g.off; g.take((size_t)plan.WB * Q * (T / 4 + 1) * sizeof(XYZZ<F>));
+        off_ba_pts[0] = g.off; g.take(ba ? (pad_entries / 2) * sizeof(Affine<F>) : 0);
+        off_ba_pts[1] = g.off; g.take(ba > 1 ? (pad_entries / 4) * sizeof(Affine<F>) : 0);
+        off_ba_pref = g.off; g.take(ba ? (pad_entries / 2) * sizeof(F) : 0);
+        off_ba_cprod = g.off; g.take(ba ? (pad_entries / 2 / BA_K + 1) * sizeof(F) : 0);
+        off_ba_cinv = g.off; g.take(ba ? (pad_entries / 2 / BA_K + 1) * sizeof(F) : 0);
         acc_total = g.off;
         total = sort_total + acc_total;
     }
@@ -122,7 +146,7 @@ struct MsmJob {
     XYZZ<F>* h_result;   // host staging of lay.result_points() values (page-locked for a truly async copy)
     MsmJob(b200_ctx* ctx, const Affine<F>* bases, const Fr* scalars, const uint32_t* idx_map, size_t n_, const MsmFold* fold,
            void* sort_ws, void* acc_ws, XYZZ<F>* host_staging)
-        : lay(n_ ? n_ : 1, ctx->msm_c_override, fold ? fold->c : 0), d_bases(bases), d_scalars(scalars), d_idx_map(idx_map), n(n_),
+        : lay(n_ ? n_ : 1, ctx->msm_mode(), fold ? fold->c : 0), d_bases(bases), d_scalars(scalars), d_idx_map(idx_map), n(n_),
           stride(fold && fold->c ? (uint32_t)fold->stride : 0u), sort_base((char*)sort_ws), acc_base((char*)acc_ws),
           h_result(host_staging) {}
 };
@@ -154,12 +178,27 @@ int msm_enqueue_sort(b200_ctx* ctx, const MsmJob<F>& job, cudaStream_t st) {
         msm_digits_kernel<<<(unsigned)((n + bs - 1) / bs), bs, 0, st>>>(job.d_scalars, job.d_idx_map, (uint32_t)n, pl.c, pl.W, pl.fold, digits, counts, pl.nb);
         B2_CUDA(ctx, cudaGetLastError());
     }
-    msm_scan_sums_kernel<<<lay.scan_blocks, SCAN_THREADS, 0, st>>>(counts, M, bsums);
+    // batched-affine mode: every bucket's slot region is padded to a multiple of 2^ba; `ntasks` holds the
+    // padded counts until the task lists are built, `rcounts` the counts after the rounds
+    uint32_t* rcounts = lay.ba ? (uint32_t*)(base + lay.off_rcounts) : counts;
+    uint32_t* roffsets = lay.ba ? (uint32_t*)(base + lay.off_roffsets) : offsets;
+    const uint32_t* scan_in = counts;
+    if (lay.ba) {
+        msm_pad_counts_kernel<<<(M + 255) / 256, 256, 0, st>>>(counts, M, lay.ba, ntasks, rcounts);
+        B2_CUDA(ctx, cudaGetLastError());
+        B2_CUDA(ctx, cudaMemsetAsync(sorted, 0xff, lay.pad_entries * 4, st));
+        scan_in = ntasks;
+    }
+    msm_scan_sums_kernel<<<lay.scan_blocks, SCAN_THREADS, 0, st>>>(scan_in, M, bsums);
     B2_CUDA(ctx, cudaGetLastError());
     msm_scan_top_kernel<<<1, 1024, 0, st>>>(bsums, lay.scan_blocks);
     B2_CUDA(ctx, cudaGetLastError());
-    msm_scan_final_kernel<<<lay.scan_blocks, SCAN_THREADS, 0, st>>>(counts, M, bsums, offsets, cursor);
+    msm_scan_final_kernel<<<lay.scan_blocks, SCAN_THREADS, 0, st>>>(scan_in, M, bsums, offsets, cursor);
     B2_CUDA(ctx, cudaGetLastError());
+    if (lay.ba) {
+        msm_shift_kernel<<<(M + 255) / 256, 256, 0, st>>>(offsets, M, lay.ba, roffsets);
+        B2_CUDA(ctx, cudaGetLastError());
+    }
     {
         const int bs = 256;
         msm_scatter_kernel<<<(unsigned)((n + bs - 1) / bs), bs, 0, st>>>(digits, (uint32_t)n, pl.c, pl.W, pl.fold, job.stride, pl.nb, cursor, sorted);
@@ -168,7 +207,7 @@ int msm_enqueue_sort(b200_ctx* ctx, const MsmJob<F>& job, cudaStream_t st) {
     {
         const int bs = 256;
         B2_CUDA(ctx, cudaMemsetAsync(big, 0, 8, st));
-        msm_task_count_kernel<<<(M + bs - 1) / bs, bs, 0, st>>>(counts, M, lay.chunk, ntasks, big, big + 2);
+        msm_task_count_kernel<<<(M + bs - 1) / bs, bs, 0, st>>>(rcounts, M, lay.chunk, ntasks, big, big + 2);
         B2_CUDA(ctx, cudaGetLastError());
         msm_scan_sums_kernel<<<lay.scan_blocks, SCAN_THREADS, 0, st>>>(ntasks, M, bsums);
         B2_CUDA(ctx, cudaGetLastError());
@@ -182,11 +221,11 @@ int msm_enqueue_sort(b200_ctx* ctx, const MsmJob<F>& job, cudaStream_t st) {
         // size-ordered task list
         const uint32_t ob = (lay.max_tasks + ORDER_THREADS - 1) / ORDER_THREADS;
         B2_CUDA(ctx, cudaMemsetAsync(order_hist, 0, (size_t)ORDER_BINS * 4, st));
-        msm_order_hist_kernel<<<ob, ORDER_THREADS, 0, st>>>(task_bucket, task_off, ntasks, counts, lay.max_tasks, lay.chunk, lay.order_shift, order_hist);
+        msm_order_hist_kernel<<<ob, ORDER_THREADS, 0, st>>>(task_bucket, task_off, ntasks, rcounts, lay.max_tasks, lay.chunk, lay.order_shift, order_hist);
         B2_CUDA(ctx, cudaGetLastError());
         msm_order_scan_kernel<<<1, 1024, 0, st>>>(order_hist);
         B2_CUDA(ctx, cudaGetLastError());
-        msm_order_fill_kernel<<<ob, ORDER_THREADS, 0, st>>>(task_bucket, task_off, ntasks, counts, lay.max_tasks, lay.chunk, lay.order_shift, order_hist, order);
+        msm_order_fill_kernel<<<ob, ORDER_THREADS, 0, st>>>(task_bucket, task_off, ntasks, rcounts, lay.max_tasks, lay.chunk, lay.order_shift, order_hist, order);
         B2_CUDA(ctx, cudaGetLastError());
     }
     ctx->prof_end(span, st);
@@ -220,8 +259,37 @@ int msm_enqueue_acc(b200_ctx* ctx, const MsmJob<F>& job, cudaStream_t st) {
     {
         const int bs = 128;
         span = ctx->prof_begin(ACC_SLOT, (double)n, st);
-        msm_accumulate_kernel<F><<<(lay.max_tasks + bs - 1) / bs, bs, 0, st>>>(job.d_bases, sorted, offsets, counts, task_bucket, task_off,
-                                                                            ntasks, order, lay.max_tasks, lay.chunk, buckets, partials);
+        const Affine<F>* acc_bases = job.d_bases;
+        const uint32_t *acc_offsets = offsets, *acc_counts = counts;
+        if (lay.ba) {
+            // pairwise affine rounds: round r turns pad_entries >> r slots into half as many points
+            Affine<F>* pts[2] = {(Affine<F>*)(ab + lay.off_ba_pts[0]), (Affine<F>*)(ab + lay.off_ba_pts[1])};
+            F* pref = (F*)(ab + lay.off_ba_pref);
+            F* cprod = (F*)(ab + lay.off_ba_cprod);
+            F* cinv = (F*)(ab + lay.off_ba_cinv);
+            const Affine<F>* in = job.d_bases;
+            for (int r = 0; r < lay.ba; ++r) {
+                const uint32_t n_out = (uint32_t)(lay.pad_entries >> (r + 1));
+                const uint32_t threads = n_out / BA_K, blocks = (threads + 127) / 128;
+                Affine<F>* out = pts[r & 1];
+                if (r == 0) ba_prep_kernel<F, true><<<blocks, 128, 0, st>>>(in, sorted, n_out, pref, cprod);
+                else ba_prep_kernel<F, false><<<blocks, 128, 0, st>>>(in, nullptr, n_out, pref, cprod);
+                B2_CUDA(ctx, cudaGetLastError());
+                const uint32_t inv_threads = (threads + BA_INV_CHUNK - 1) / BA_INV_CHUNK;
+                ba_inverse_kernel<F><<<(inv_threads + 63) / 64, 64, 0, st>>>(cprod, cinv, threads);
+                B2_CUDA(ctx, cudaGetLastError());
+                if (r == 0) ba_apply_kernel<F, true><<<blocks, 128, 0, st>>>(in, sorted, n_out, pref, cinv, out);
+                else ba_apply_kernel<F, false><<<blocks, 128, 0, st>>>(in, nullptr, n_out, pref, cinv, out);
+                B2_CUDA(ctx, cudaGetLastError());
+                ctx->n_launches += 3;
+                in = out;
+            }
+            acc_bases = in;
+            acc_offsets = (const uint32_t*)(sb + lay.off_roffsets);
+            acc_counts = (const uint32_t*)(sb + lay.off_rcounts);
+        }
+        msm_accumulate_kernel<F><<<(lay.max_tasks + bs - 1) / bs, bs, 0, st>>>(acc_bases, sorted, acc_offsets, acc_counts, task_bucket, task_off,
+                                                                            ntasks, order, lay.max_tasks, lay.chunk, buckets, partials, lay.ba ? 1u : 0u);
         ctx->prof_end(span, st);
         B2_CUDA(ctx, cudaGetLastError());
         span = ctx->prof_begin(B200_PROF_MSM_REDUCE, (double)n, st);
@@ -300,7 +368,7 @@ int msm_run_impl(b200_ctx* ctx, const Affine<F>* d_bases, const Fr* d_scalars, c
     if (n == 0) { *out_host = Jac<F>::inf(); return B200_OK; }
     if (n >= ((size_t)1 << 31)) return ctx->fail(B200_ERR_UNSUPPORTED, "MSM above 2^31 points");
     const int fold_c = fold ? fold->c : 0;
-    MsmLayout<F> lay(n, ctx->msm_c_override, fold_c);
+    MsmLayout<F> lay(n, ctx->msm_mode(), fold_c);
     char* base;
     if (ws) base = (char*)ws;
     else { B2_TRY(ctx_reserve(ctx, lay.total)); base = (char*)ctx->scratch; }

@@ -207,7 +207,7 @@ int commit_many(b200_ctx* ctx, const b200_bases* srs, const Fr* const* coeffs, c
     size_t sort_max = 0, acc_max = 0, res_off[5] = {0};
     for (int k = 0; k < m; ++k) {
         if (counts[k] > srs->n) return ctx->fail(B200_ERR_ARG, "polynomial longer than the SRS");
-        const MsmSizes sz = msm_sizes(counts[k], 1, ctx->msm_c_override, srs->fold.c);
+        const MsmSizes sz = msm_sizes(counts[k], 1, ctx->msm_mode(), srs->fold.c);
         sort_max = std::max(sort_max, sz.sort_bytes);
         acc_max = std::max(acc_max, sz.acc_bytes);
         res_off[k + 1] = res_off[k] + ((sz.result_bytes + 255) & ~(size_t)255);

@@ -22,7 +22,13 @@ template <int TAG = 0> __device__ __noinline__ Fp2 fp2_mul_call(Fp2 a, Fp2 b);
 template <int TAG = 0> __device__ __noinline__ Fp2 fp2_sqr_call(Fp2 a);
 #endif
 
-// Fp2 = Fp[u]/(u^2 + 1)   (gnark-crypto E2{A0, A1}; memory order A0 then A1)
+// Fp2 = Fp[u]/(u^2 - beta), beta = -1 on BN254 and -5 on BLS12-377 (reference: std/algebra/native/fields_bls12377/e12.go:79)
+// (gnark-crypto E2{A0, A1}; memory order A0 then A1)
+#if defined(B2_CURVE_BLS12_377)
+B2_HD Fp fp2_mul_by_minus_beta(const Fp& x) { const Fp x4 = x.dbl().dbl(); return x4 + x; }   // 5 x
+#else
+B2_HD Fp fp2_mul_by_minus_beta(const Fp& x) { return x; }
+#endif
 struct Fp2 {
     Fp a0, a1;
     B2_HD static Fp2 zero() { return {Fp::zero(), Fp::zero()}; }
@@ -37,12 +43,20 @@ struct Fp2 {
     B2_HD Fp2 mul_inline(const Fp2& o) const {  // Karatsuba, 3 Fp mul
         const Fp t0 = a0 * o.a0, t1 = a1 * o.a1;
         const Fp t2 = (a0 + a1) * (o.a0 + o.a1);
-        return {t0 - t1, t2 - t0 - t1};
+        return {t0 - fp2_mul_by_minus_beta(t1), t2 - t0 - t1};
     }
+#if defined(B2_CURVE_BLS12_377)
+    B2_HD Fp2 sqr_inline() const {  // (a0 + a1 u)^2 = a0^2 - 5 a1^2 + 2 a0 a1 u: (a0 + a1)(a0 - 5 a1) + 4 a0 a1, 2 Fp mul
+        const Fp t = a0 * a1;
+        const Fp c = (a0 + a1) * (a0 - fp2_mul_by_minus_beta(a1));
+        return {c + t.dbl().dbl(), t.dbl()};
+    }
+#else
     B2_HD Fp2 sqr_inline() const {  // complex squaring, 2 Fp mul
         const Fp t = a0 * a1;
         return {(a0 + a1) * (a0 - a1), t.dbl()};
     }
+#endif
     B2_HD Fp2 operator*(const Fp2& o) const {
 #if defined(__CUDA_ARCH__)
         return fp2_mul_call<0>(*this, o);
@@ -58,7 +72,7 @@ struct Fp2 {
 #endif
     }
     B2_HD Fp2 inv() const {
-        const Fp d = (a0.sqr() + a1.sqr()).inv();
+        const Fp d = (a0.sqr() + fp2_mul_by_minus_beta(a1.sqr())).inv();     // norm = a0^2 - beta a1^2
         return {a0 * d, a1.neg() * d};
     }
 };
@@ -70,6 +84,9 @@ struct Fp2 {
 //   c1 = (a0 + a1)(b0 + b1) - a0 b0 - a1 b1 = a0 b1 + a1 b0  in [0, 2 p^2)
 //   c0 = a0 b0 - a1 b1 + p^2                                   in (0, 2 p^2)
 // both below p * 2^256 * 0.38, the bound mont_reduce_dev needs for a canonical result.
+#if defined(B2_CURVE_BLS12_377)
+__device__ __forceinline__ Fp2 fp2_mul_lazy(const Fp2& a, const Fp2& b) { return a.mul_inline(b); }
+#else
 __device__ __forceinline__ Fp2 fp2_mul_lazy(const Fp2& a, const Fp2& b) {
     uint32_t t0[16], t1[16], t2[16], sa[8], sb[8];
     mul_wide_dev(t0, a.a0.l, b.a0.l);
@@ -89,6 +106,7 @@ __device__ __forceinline__ Fp2 fp2_mul_lazy(const Fp2& a, const Fp2& b) {
     mont_reduce_dev<FpParams>(r.a1.l, t2);
     return r;
 }
+#endif
 template <int TAG> __device__ __noinline__ Fp2 fp2_mul_call(Fp2 a, Fp2 b) { return fp2_mul_lazy(a, b); }
 
 template <int TAG> __device__ __noinline__ Fp2 fp2_sqr_call(Fp2 a) { return a.sqr_inline(); }

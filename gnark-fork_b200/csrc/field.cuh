@@ -34,6 +34,52 @@ namespace b200 {
 // backend/groth16/bn254/solidity.go:41-42 (P, R);  INV = -p^-1 mod 2^32, ONE = 2^256 mod p,
 // R2 = 2^512 mod p.
 // ---------------------------------------------------------------------------------------
+#if defined(B2_CURVE_BLS12_377)
+// BLS12-377 (BASELINE.json config 5; p and r pinned in the reference at std/math/emulated/emparams/emparams.go:123,137):
+// Fp has 12 x 32-bit limbs (377 bits, R = 2^384), Fr 8 limbs (253 bits, R = 2^256).  Built as a second library from
+// the same sources with -DB2_CURVE_BLS12_377.  The 12-limb product takes the portable u64 path on the device too
+// (IMAD.WIDE + carry adds from plain C++); the hand-scheduled even/odd chains exist for 8 limbs only.
+struct FpParams {
+    static constexpr int N = 12;
+    B2_HD static constexpr uint32_t p(int i) {
+        constexpr uint32_t v[12] = {0x00000001u, 0x8508c000u, 0x30000000u, 0x170b5d44u, 0xba094800u, 0x1ef3622fu,
+                                    0x00f5138fu, 0x1a22d9f3u, 0x6ca1493bu, 0xc63b05c0u, 0x17c510eau, 0x01ae3a46u};
+        return v[i];
+    }
+    B2_HD static constexpr uint32_t one(int i) {
+        constexpr uint32_t v[12] = {0xffffff68u, 0x02cdffffu, 0x7fffffb1u, 0x51409f83u, 0x8a7d3ff2u, 0x9f7db3a9u,
+                                    0x6e7c6305u, 0x7b4e97b7u, 0x803c84e8u, 0x4cf495bfu, 0xe2fdf49au, 0x008d6661u};
+        return v[i];
+    }
+    B2_HD static constexpr uint32_t r2(int i) {
+        constexpr uint32_t v[12] = {0x9400cd22u, 0xb786686cu, 0xb00431b1u, 0x0329fcaau, 0x62d6b46du, 0x22a5f111u,
+                                    0x827dc3acu, 0xbfdf7d03u, 0x41790bf9u, 0x837e92f0u, 0x1e914b88u, 0x006dfccbu};
+        return v[i];
+    }
+    static constexpr uint32_t INV = 0xffffffffu;
+};
+
+struct FrParams {
+    static constexpr int N = 8;
+    B2_HD static constexpr uint32_t p(int i) {
+        constexpr uint32_t v[8] = {0x00000001u, 0x0a118000u, 0xd0000001u, 0x59aa76feu,
+                                   0x5c37b001u, 0x60b44d1eu, 0x9a2ca556u, 0x12ab655eu};
+        return v[i];
+    }
+    B2_HD static constexpr uint32_t one(int i) {
+        constexpr uint32_t v[8] = {0xfffffff3u, 0x7d1c7fffu, 0x6ffffff2u, 0x7257f50fu,
+                                   0x512c0feeu, 0x16d81575u, 0x2bbb9a9du, 0x0d4bda32u};
+        return v[i];
+    }
+    B2_HD static constexpr uint32_t r2(int i) {
+        constexpr uint32_t v[8] = {0xb861857bu, 0x25d577bau, 0x8860591fu, 0xcc2c27b5u,
+                                   0xe5dc8593u, 0xa7cc008fu, 0xeff1c939u, 0x011fdae7u};
+        return v[i];
+    }
+    static constexpr uint32_t INV = 0xffffffffu;
+};
+
+#else
 struct FpParams {
     static constexpr int N = 8;
     B2_HD static constexpr uint32_t p(int i) {
@@ -78,6 +124,8 @@ struct FrParams {
     }
     static constexpr uint32_t INV = 0xefffffffu;
 };
+
+#endif
 
 // ---------------------------------------------------------------------------------------
 // Device carry-chain helpers (8 limbs).  Every helper is one self-contained asm block: the
@@ -461,7 +509,7 @@ B2_D void mod_sub_dev(uint32_t* r, const uint32_t* a, const uint32_t* b) {
 // Portable path (host): same results, u64 arithmetic.
 // ---------------------------------------------------------------------------------------
 template <class PRM>
-inline void mont_mul_host(uint32_t* r, const uint32_t* a, const uint32_t* b) {
+B2_HD void mont_mul_host(uint32_t* r, const uint32_t* a, const uint32_t* b) {
     constexpr int N = PRM::N;
     uint32_t t[N + 2];
     for (int i = 0; i < N + 2; ++i) t[i] = 0;
@@ -490,7 +538,7 @@ inline void mont_mul_host(uint32_t* r, const uint32_t* a, const uint32_t* b) {
 }
 
 template <class PRM>
-inline void mod_add_host(uint32_t* r, const uint32_t* a, const uint32_t* b) {
+B2_HD void mod_add_host(uint32_t* r, const uint32_t* a, const uint32_t* b) {
     constexpr int N = PRM::N;
     uint32_t t[N], s[N]; uint64_t c = 0, br = 0;
     for (int j = 0; j < N; ++j) { c += (uint64_t)a[j] + b[j]; t[j] = (uint32_t)c; c >>= 32; }
@@ -500,7 +548,7 @@ inline void mod_add_host(uint32_t* r, const uint32_t* a, const uint32_t* b) {
 }
 
 template <class PRM>
-inline void mod_sub_host(uint32_t* r, const uint32_t* a, const uint32_t* b) {
+B2_HD void mod_sub_host(uint32_t* r, const uint32_t* a, const uint32_t* b) {
     constexpr int N = PRM::N;
     uint32_t t[N]; uint64_t br = 0;
     for (int j = 0; j < N; ++j) { uint64_t d = (uint64_t)a[j] - b[j] - br; t[j] = (uint32_t)d; br = (d >> 32) & 1; }
@@ -528,7 +576,8 @@ struct alignas(16) Fe {
     B2_HD Fe operator*(const Fe& o) const {
         Fe r;
 #if defined(__CUDA_ARCH__)
-        mont_mul_dev<PRM>(r.l, l, o.l);
+        if constexpr (N == 8) mont_mul_dev<PRM>(r.l, l, o.l);
+        else mont_mul_host<PRM>(r.l, l, o.l);
 #else
         mont_mul_host<PRM>(r.l, l, o.l);
 #endif
@@ -538,7 +587,8 @@ struct alignas(16) Fe {
     B2_HD Fe operator+(const Fe& o) const {
         Fe r;
 #if defined(__CUDA_ARCH__)
-        mod_add_dev<PRM>(r.l, l, o.l);
+        if constexpr (N == 8) mod_add_dev<PRM>(r.l, l, o.l);
+        else mod_add_host<PRM>(r.l, l, o.l);
 #else
         mod_add_host<PRM>(r.l, l, o.l);
 #endif
@@ -547,7 +597,8 @@ struct alignas(16) Fe {
     B2_HD Fe operator-(const Fe& o) const {
         Fe r;
 #if defined(__CUDA_ARCH__)
-        mod_sub_dev<PRM>(r.l, l, o.l);
+        if constexpr (N == 8) mod_sub_dev<PRM>(r.l, l, o.l);
+        else mod_sub_host<PRM>(r.l, l, o.l);
 #else
         mod_sub_host<PRM>(r.l, l, o.l);
 #endif
@@ -588,7 +639,7 @@ typedef Fe<FrParams> Fr;
 // a*b - c*d with one Montgomery reduction on the device (two wide products, their difference kept
 // non-negative by adding p^2): 200 MAC32 instead of 272.  Canonical result either way.
 B2_HD Fp mul_sub_mul(const Fp& a, const Fp& b, const Fp& c, const Fp& d) {
-#if defined(__CUDA_ARCH__)
+#if defined(__CUDA_ARCH__) && !defined(B2_CURVE_BLS12_377)
     uint32_t t0[16], t1[16], p2[16];
     mul_wide_dev(t0, a.l, b.l);
     mul_wide_dev(t1, c.l, d.l);
@@ -610,9 +661,7 @@ B2_HD Fp mul_sub_mul(const Fp& a, const Fp& b, const Fp& c, const Fp& d) {
 #if defined(__CUDACC__)
 template <class PRM>
 __device__ __noinline__ Fe<PRM> mont_mul_call(Fe<PRM> a, Fe<PRM> b) {
-    Fe<PRM> r;
-    mont_mul_dev<PRM>(r.l, a.l, b.l);
-    return r;
+    return a * b;
 }
 #endif
 template <class PRM>

@@ -31,6 +31,7 @@ FR_MULT_GEN = 5
 # exactly 2^28).  The product never hard-codes it: the generator is an INPUT of the C ABI.
 FR_TWO_ADICITY = 28
 FR_ROOT_2_28 = 19103219067921713944291392827692070036145651957329286315305642004821462161904
+FR_ROOT_OF_UNITY = FR_ROOT_2_28   # curve-neutral name used by ntt.py (order 2^FR_TWO_ADICITY)
 
 # G1: y^2 = x^3 + 3, generator (1, 2)
 G1_B = 3

@@ -286,7 +286,10 @@ def prove_points(pk: ProvingKey, w, a, b, c, r: int, s: int, nb_public: int):
 # top bits of byte 0 = 0b10 (y is the lexicographically smallest), 0b11 (largest), 0b01
 # (infinity); G2 = X.A1 | X.A0, 64 bytes, Y order decided on A1 then A0.
 # ----------------------------------------------------------------------------------------
-M_SMALLEST, M_LARGEST, M_INFINITY = 0b10 << 6, 0b11 << 6, 0b01 << 6
+# BLS12-377 (oracle/bls12_377.py exports COMPRESS_FLAGS): 48-byte coordinates and the three-bit flags
+# gnark-crypto uses on its BLS curves, 0b100 / 0b101 / 0b110 in the top three bits (recalled as well).
+M_SMALLEST, M_LARGEST, M_INFINITY = getattr(C, "COMPRESS_FLAGS", (0b10 << 6, 0b11 << 6, 0b01 << 6))
+FP_BYTES = (P.bit_length() + 7) // 8
 
 
 def _lex_largest(y: int) -> bool:
@@ -295,18 +298,18 @@ def _lex_largest(y: int) -> bool:
 
 def g1_compress(p) -> bytes:
     if p is None:
-        return bytes([M_INFINITY]) + bytes(31)
-    b = bytearray(p[0].to_bytes(32, "big"))
+        return bytes([M_INFINITY]) + bytes(FP_BYTES - 1)
+    b = bytearray(p[0].to_bytes(FP_BYTES, "big"))
     b[0] |= M_LARGEST if _lex_largest(p[1]) else M_SMALLEST
     return bytes(b)
 
 
 def g2_compress(p) -> bytes:
     if p is None:
-        return bytes([M_INFINITY]) + bytes(63)
+        return bytes([M_INFINITY]) + bytes(2 * FP_BYTES - 1)
     (x0, x1), (y0, y1) = p
     largest = _lex_largest(y1) if y1 else _lex_largest(y0)
-    b = bytearray(x1.to_bytes(32, "big") + x0.to_bytes(32, "big"))
+    b = bytearray(x1.to_bytes(FP_BYTES, "big") + x0.to_bytes(FP_BYTES, "big"))
     b[0] |= M_LARGEST if largest else M_SMALLEST
     return bytes(b)
 

@@ -13,7 +13,7 @@ only convention risk is the choice of generator -- which the product takes as an
 """
 from __future__ import annotations
 
-from .bn254 import R, FR_MULT_GEN, FR_ROOT_2_28, FR_TWO_ADICITY
+from .bn254 import R, FR_MULT_GEN, FR_ROOT_OF_UNITY, FR_TWO_ADICITY
 
 DIF = 0
 DIT = 1
@@ -47,7 +47,7 @@ class Domain:
         self.cardinality = 1 << log_n
         if generator is None:
             assert log_n <= FR_TWO_ADICITY
-            generator = pow(FR_ROOT_2_28, 1 << (FR_TWO_ADICITY - log_n), R)
+            generator = pow(FR_ROOT_OF_UNITY, 1 << (FR_TWO_ADICITY - log_n), R)
         self.generator = generator
         self.generator_inv = pow(generator, -1, R)
         self.cardinality_inv = pow(self.cardinality, -1, R)

@@ -2,6 +2,9 @@
 
 Layouts (identical to gnark-crypto's in-memory ones, see the header): Fr/Fp element = 4 u64
 Montgomery limbs; G1 affine (n, 8); G1 Jacobian (12,); G2 affine (n, 16); G2 Jacobian (24,).
+
+BLS12-377 (`curve=BLS12_377`) binds the second library, libb200prover_bls12377.so: Fr is still 4 u64, Fp is
+6 u64 (`fp_words(curve)`), so G1 affine (n, 12), G1 Jacobian (18,), G2 affine (n, 24), G2 Jacobian (36,).
 """
 from __future__ import annotations
 
@@ -11,19 +14,28 @@ import os
 import numpy as np
 
 BN254 = 0
+BLS12_377 = 1
 DIF = 0
 DIT = 1
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-_LIB = None
+_LIBS: dict = {}
+_LIB_FILES = {BN254: ("B200PROVER_LIB", "libb200prover.so"), BLS12_377: ("B200PROVER_LIB_BLS12_377", "libb200prover_bls12377.so")}
+_FP_WORDS = {BN254: 4, BLS12_377: 6}
+
+
+def fp_words(curve: int = BN254) -> int:
+    """u64 words of one base-field element (B200_FP_WORDS of the header)."""
+    return _FP_WORDS[curve]
 
 
 class B200Error(RuntimeError):
     pass
 
 
-def library_path() -> str:
-    return os.environ.get("B200PROVER_LIB", os.path.join(_HERE, "libb200prover.so"))
+def library_path(curve: int = BN254) -> str:
+    env, name = _LIB_FILES[curve]
+    return os.environ.get(env, os.path.join(_HERE, name))
 
 
 class _Timings(C.Structure):
@@ -94,6 +106,16 @@ class Groth16MsmOut(C.Structure):
         return {k: np.array(getattr(self, k), dtype=np.uint64) for k, _ in self._fields_}
 
 
+class Groth16MsmOut377(C.Structure):
+    """b200_groth16_out of the BLS12-377 library (B200_FP_WORDS = 6)."""
+    _fields_ = [("ar", C.c_uint64 * 18), ("bs1", C.c_uint64 * 18), ("krs", C.c_uint64 * 18),
+                ("krs2", C.c_uint64 * 18), ("bs2", C.c_uint64 * 36)]
+    as_dict = Groth16MsmOut.as_dict
+
+
+_MSM_OUT = {BN254: Groth16MsmOut, BLS12_377: Groth16MsmOut377}
+
+
 class _PkDesc(C.Structure):
     _fields_ = [
         ("log_n", C.c_uint), ("generator", C.c_void_p), ("coset_gen", C.c_void_p),
@@ -114,16 +136,19 @@ class _Profile(C.Structure):
                 ("kernel_launches", C.c_uint64)]
 
 
-def load_library():
-    """Load libb200prover.so; fails loudly (no fallback of any kind)."""
-    global _LIB
-    if _LIB is not None:
-        return _LIB
-    path = library_path()
+def load_library(curve: int = BN254):
+    """Load libb200prover.so (or the BLS12-377 build); fails loudly (no fallback of any kind)."""
+    if curve in _LIBS:
+        return _LIBS[curve]
+    if curve not in _LIB_FILES:
+        raise B200Error(f"unknown curve id {curve}")
+    path = library_path(curve)
     if not os.path.exists(path):
-        raise B200Error(f"{path} not found: build it with `make -C gnark-fork_b200/csrc` "
+        raise B200Error(f"{path} not found: build it with `make -C gnark-fork_b200/csrc"
+                        f"{' CURVE=bls12_377' if curve == BLS12_377 else ''}` "
                         "(or __graft_entry__.build()); there is no CPU fallback")
     lib = C.CDLL(path)
+    Groth16MsmOut = _MSM_OUT[curve]     # the struct of THIS library's B200_FP_WORDS
     vp, sz, u, i = C.c_void_p, C.c_size_t, C.c_uint, C.c_int
     sig = {
         "b200_device_count": (i, []),
@@ -131,6 +156,8 @@ def load_library():
         "b200_destroy": (None, [vp]),
         "b200_last_error": (C.c_char_p, [vp]),
         "b200_version": (C.c_char_p, []),
+        "b200_build_curve": (i, []),
+        "b200_build_fp_words": (i, []),
         "b200_set_option": (i, [vp, C.c_char_p, C.c_long]),
         "b200_host_alloc": (vp, [sz]),
         "b200_host_free": (None, [vp]),
@@ -194,7 +221,9 @@ def load_library():
         fn = getattr(lib, name)  # AttributeError if the library lacks a declared symbol
         fn.restype = res
         fn.argtypes = args
-    _LIB = lib
+    if lib.b200_build_curve() != curve or lib.b200_build_fp_words() != _FP_WORDS[curve]:
+        raise B200Error(f"{path} was built for curve {lib.b200_build_curve()} / {lib.b200_build_fp_words()} Fp words, wanted curve {curve}")
+    _LIBS[curve] = lib
     return lib
 
 
@@ -229,8 +258,8 @@ _PINNED: dict = {}
 
 
 # ---- host-side group helpers (no ctx) -----------------------------------------------------
-def _host_call(name, *arrays, out_words):
-    lib = load_library()
+def _host_call(name, *arrays, out_words, curve=BN254):
+    lib = load_library(curve)
     out = np.zeros(out_words, dtype=np.uint64)
     st = getattr(lib, name)(*[_ptr(_u64(a)) for a in arrays], _ptr(out))
     if st != 0:
@@ -238,26 +267,27 @@ def _host_call(name, *arrays, out_words):
     return out
 
 
-def g1_jac_add(p, q):
-    return _host_call("b200_g1_jac_add", p, q, out_words=12)
+def g1_jac_add(p, q, curve=BN254):
+    return _host_call("b200_g1_jac_add", p, q, out_words=3 * fp_words(curve), curve=curve)
 
 
-def g2_jac_add(p, q):
-    return _host_call("b200_g2_jac_add", p, q, out_words=24)
+def g2_jac_add(p, q, curve=BN254):
+    return _host_call("b200_g2_jac_add", p, q, out_words=6 * fp_words(curve), curve=curve)
 
 
-def g1_jac_to_affine(p):
-    return _host_call("b200_g1_jac_to_affine", p, out_words=8)
+def g1_jac_to_affine(p, curve=BN254):
+    return _host_call("b200_g1_jac_to_affine", p, out_words=2 * fp_words(curve), curve=curve)
 
 
-def g2_jac_to_affine(p):
-    return _host_call("b200_g2_jac_to_affine", p, out_words=16)
+def g2_jac_to_affine(p, curve=BN254):
+    return _host_call("b200_g2_jac_to_affine", p, out_words=4 * fp_words(curve), curve=curve)
 
 
-def groth16_finalize(msm: Groth16MsmOut, r, s, g1_alpha, g1_beta, g1_delta, g2_beta, g2_delta):
+def groth16_finalize(msm: Groth16MsmOut, r, s, g1_alpha, g1_beta, g1_delta, g2_beta, g2_delta, curve=BN254):
     """Fix-ups of prove.go:178-321 on the five MSM results -> affine (Ar, Bs, Krs)."""
-    lib = load_library()
-    ar, bs, krs = np.zeros(8, np.uint64), np.zeros(16, np.uint64), np.zeros(8, np.uint64)
+    lib = load_library(curve)
+    fw = fp_words(curve)
+    ar, bs, krs = np.zeros(2 * fw, np.uint64), np.zeros(4 * fw, np.uint64), np.zeros(2 * fw, np.uint64)
     ins = [_u64(x) for x in (r, s, g1_alpha, g1_beta, g1_delta, g2_beta, g2_delta)]
     st = lib.b200_groth16_finalize(C.byref(msm), *[_ptr(x) for x in ins], _ptr(ar), _ptr(bs), _ptr(krs))
     if st != 0:
@@ -265,11 +295,12 @@ def groth16_finalize(msm: Groth16MsmOut, r, s, g1_alpha, g1_beta, g1_delta, g2_b
     return ar, bs, krs
 
 
-def groth16_proof_bytes(ar, bs, krs) -> bytes:
-    """Proof.WriteTo for a proof without commitments (marshal.go:41-66)."""
-    lib = load_library()
-    out = np.zeros(164, dtype=np.uint8)
-    n = lib.b200_groth16_proof_bytes(_ptr(_u64(ar)), _ptr(_u64(bs)), _ptr(_u64(krs)), _ptr(out), 164)
+def groth16_proof_bytes(ar, bs, krs, curve=BN254) -> bytes:
+    """Proof.WriteTo for a proof without commitments (marshal.go:41-66): 164 bytes on BN254, 244 on BLS12-377."""
+    lib = load_library(curve)
+    cap = 5 * 8 * fp_words(curve) + 4
+    out = np.zeros(cap, dtype=np.uint8)
+    n = lib.b200_groth16_proof_bytes(_ptr(_u64(ar)), _ptr(_u64(bs)), _ptr(_u64(krs)), _ptr(out), cap)
     if n < 0:
         raise B200Error(f"b200_groth16_proof_bytes failed with status {n}")
     return out[:n].tobytes()
@@ -433,8 +464,10 @@ class PlonkSession:
 class Context:
     """One b200_ctx = one device. Not re-entrant."""
 
-    def __init__(self, device: int = 0):
-        self.lib = load_library()
+    def __init__(self, device: int = 0, curve: int = BN254):
+        self.lib = load_library(curve)
+        self.curve = curve
+        self.fw = fp_words(curve)        # u64 words per Fp element: 4 (BN254) or 6 (BLS12-377)
         h = C.c_void_p()
         st = self.lib.b200_init(device, C.byref(h))
         if st != 0:
@@ -477,13 +510,13 @@ class Context:
     def fr_vec_mul(self, a, b):
         a, b = _u64(a, (-1, 4)), _u64(b, (-1, 4))
         out = np.empty_like(a)
-        self._check(self.lib.b200_fr_vec_mul(self.h, BN254, _ptr(a), _ptr(b), _ptr(out), a.shape[0]))
+        self._check(self.lib.b200_fr_vec_mul(self.h, self.curve, _ptr(a), _ptr(b), _ptr(out), a.shape[0]))
         return out
 
     def fp_vec_mul(self, a, b):
-        a, b = _u64(a, (-1, 4)), _u64(b, (-1, 4))
+        a, b = _u64(a, (-1, self.fw)), _u64(b, (-1, self.fw))
         out = np.empty_like(a)
-        self._check(self.lib.b200_fp_vec_mul(self.h, BN254, _ptr(a), _ptr(b), _ptr(out), a.shape[0]))
+        self._check(self.lib.b200_fp_vec_mul(self.h, self.curve, _ptr(a), _ptr(b), _ptr(out), a.shape[0]))
         return out
 
     def imad_peak(self):
@@ -495,59 +528,59 @@ class Context:
     def ntt(self, data, log_n, inverse, decimation, on_coset, generator, coset_gen):
         out = _u64(data, (-1, 4)).copy()
         assert out.shape[0] == 1 << log_n
-        self._check(self.lib.b200_ntt(self.h, BN254, _ptr(out), log_n, int(inverse), int(decimation),
+        self._check(self.lib.b200_ntt(self.h, self.curve, _ptr(out), log_n, int(inverse), int(decimation),
                                       int(on_coset), _ptr(_u64(generator)), _ptr(_u64(coset_gen))))
         return out
 
     def ntt_dev(self, vec: DeviceVector, log_n, inverse, decimation, on_coset, generator, coset_gen) -> float:
         ms = C.c_float()
-        self._check(self.lib.b200_ntt_dev(self.h, BN254, vec.ptr, log_n, int(inverse), int(decimation),
+        self._check(self.lib.b200_ntt_dev(self.h, self.curve, vec.ptr, log_n, int(inverse), int(decimation),
                                           int(on_coset), _ptr(_u64(generator)), _ptr(_u64(coset_gen)), C.byref(ms)))
         return ms.value
 
     def compute_h(self, a, b, c, log_n, generator, coset_gen):
         a, b, c = (_u64(x, (-1, 4)) for x in (a, b, c))
         out = np.empty((1 << log_n, 4), dtype=np.uint64)
-        self._check(self.lib.b200_groth16_compute_h(self.h, BN254, _ptr(a), _ptr(b), _ptr(c), a.shape[0], log_n,
+        self._check(self.lib.b200_groth16_compute_h(self.h, self.curve, _ptr(a), _ptr(b), _ptr(c), a.shape[0], log_n,
                                                     _ptr(_u64(generator)), _ptr(_u64(coset_gen)), _ptr(out)))
         return out
 
     # -- MSM (G1Jac.MultiExp / G2Jac.MultiExp)
     def msm_g1(self, scalars, bases):
-        s, b = _u64(scalars, (-1, 4)), _u64(bases, (-1, 8))
-        out = np.zeros(12, dtype=np.uint64)
-        self._check(self.lib.b200_msm_g1(self.h, BN254, _ptr(s), _ptr(b), s.shape[0], _ptr(out)))
+        s, b = _u64(scalars, (-1, 4)), _u64(bases, (-1, 2 * self.fw))
+        out = np.zeros(3 * self.fw, dtype=np.uint64)
+        self._check(self.lib.b200_msm_g1(self.h, self.curve, _ptr(s), _ptr(b), s.shape[0], _ptr(out)))
         return out
 
     def msm_g2(self, scalars, bases):
-        s, b = _u64(scalars, (-1, 4)), _u64(bases, (-1, 16))
-        out = np.zeros(24, dtype=np.uint64)
-        self._check(self.lib.b200_msm_g2(self.h, BN254, _ptr(s), _ptr(b), s.shape[0], _ptr(out)))
+        s, b = _u64(scalars, (-1, 4)), _u64(bases, (-1, 4 * self.fw))
+        out = np.zeros(6 * self.fw, dtype=np.uint64)
+        self._check(self.lib.b200_msm_g2(self.h, self.curve, _ptr(s), _ptr(b), s.shape[0], _ptr(out)))
         return out
 
     def upload_bases(self, bases, group: int) -> Bases:
-        b = _u64(bases, (-1, 8 if group == 1 else 16))
+        b = _u64(bases, (-1, (2 if group == 1 else 4) * self.fw))
         h = C.c_void_p()
-        self._check(self.lib.b200_bases_upload(self.h, BN254, group, _ptr(b), b.shape[0], C.byref(h)))
+        self._check(self.lib.b200_bases_upload(self.h, self.curve, group, _ptr(b), b.shape[0], C.byref(h)))
         return Bases(self, h, b.shape[0], group)
 
     def msm_resident(self, bases: Bases, scalars):
         s = _u64(scalars, (-1, 4))
-        out = np.zeros(12 if bases.group == 1 else 24, dtype=np.uint64)
+        out = np.zeros((3 if bases.group == 1 else 6) * self.fw, dtype=np.uint64)
         self._check(self.lib.b200_msm_resident(self.h, bases.h, _ptr(s), s.shape[0], _ptr(out)))
         return out
 
     def msm_dev(self, bases: Bases, scalars: DeviceVector, n: int):
-        out = np.zeros(12 if bases.group == 1 else 24, dtype=np.uint64)
+        out = np.zeros((3 if bases.group == 1 else 6) * self.fw, dtype=np.uint64)
         ms = C.c_float()
         self._check(self.lib.b200_msm_dev(self.h, bases.h, scalars.ptr, n, _ptr(out), C.byref(ms)))
         return out, ms.value
 
     def batch_scalar_mul(self, base, scalars, group: int):
         s = _u64(scalars, (-1, 4))
-        w = 8 if group == 1 else 16
+        w = (2 if group == 1 else 4) * self.fw
         out = np.zeros((s.shape[0], w), dtype=np.uint64)
-        self._check(self.lib.b200_batch_scalar_mul(self.h, BN254, group, _ptr(_u64(base)), _ptr(s), s.shape[0], _ptr(out)))
+        self._check(self.lib.b200_batch_scalar_mul(self.h, self.curve, group, _ptr(_u64(base)), _ptr(s), s.shape[0], _ptr(out)))
         return out
 
     # -- Groth16
@@ -556,8 +589,8 @@ class Context:
                           full_counts=None) -> Groth16ProvingKey:
         """presliced=True: the base arrays hold only this shard's point range; full_counts =
         dict(a=, b=, k=, z=) then gives the full lengths of pk.G1.A/B/K/Z."""
-        keep = dict(gen=_u64(generator), cg=_u64(coset_gen), a=_u64(g1_a, (-1, 8)), b=_u64(g1_b, (-1, 8)),
-                    k=_u64(g1_k, (-1, 8)), z=_u64(g1_z, (-1, 8)), g2b=_u64(g2_b, (-1, 16)),
+        keep = dict(gen=_u64(generator), cg=_u64(coset_gen), a=_u64(g1_a, (-1, 2 * self.fw)), b=_u64(g1_b, (-1, 2 * self.fw)),
+                    k=_u64(g1_k, (-1, 2 * self.fw)), z=_u64(g1_z, (-1, 2 * self.fw)), g2b=_u64(g2_b, (-1, 4 * self.fw)),
                     ia=np.ascontiguousarray(infinity_a, dtype=np.uint8), ib=np.ascontiguousarray(infinity_b, dtype=np.uint8))
         d = _PkDesc()
         d.log_n = log_n
@@ -574,13 +607,13 @@ class Context:
             d.n_a, d.n_b, d.n_k, d.n_z = (full_counts[k] for k in ("a", "b", "k", "z"))
             d.n_g2b = d.n_b
         h = C.c_void_p()
-        self._check(self.lib.b200_groth16_pk_upload(self.h, BN254, C.byref(d), C.byref(h)))
+        self._check(self.lib.b200_groth16_pk_upload(self.h, self.curve, C.byref(d), C.byref(h)))
         return Groth16ProvingKey(self, h, None)
 
     def groth16_prove_core(self, pk: Groth16ProvingKey, a, b, c, w, k_remove=None):
         """computeH + the five MSMs (prove.go:139-301). Returns (Groth16MsmOut, timings dict)."""
         a, b, c, w = (_u64(x, (-1, 4)) for x in (a, b, c, w))
-        out, tm = Groth16MsmOut(), _Timings()
+        out, tm = _MSM_OUT[self.curve](), _Timings()
         kr = None if k_remove is None or len(k_remove) == 0 else np.ascontiguousarray(k_remove, dtype=np.uint32)
         self._check(self.lib.b200_groth16_prove_core(self.h, pk.h, _ptr(a), _ptr(b), _ptr(c), a.shape[0], _ptr(w),
                                                      _ptr(kr), 0 if kr is None else kr.shape[0],
@@ -590,7 +623,7 @@ class Context:
     def groth16_prove_core_dev(self, pk: Groth16ProvingKey, a: DeviceVector, b: DeviceVector, c: DeviceVector,
                                n_constraints: int, w: DeviceVector):
         """Same with a, b, c, W already resident on the device (copied D2D into the workspace)."""
-        out, tm = Groth16MsmOut(), _Timings()
+        out, tm = _MSM_OUT[self.curve](), _Timings()
         self._check(self.lib.b200_groth16_prove_core_dev(self.h, pk.h, a.ptr, b.ptr, c.ptr, n_constraints, w.ptr,
                                                          C.byref(out), C.byref(tm)))
         return out, {k: getattr(tm, k) for k, _ in _Timings._fields_}
@@ -598,41 +631,41 @@ class Context:
     def groth16_msms_dev(self, pk: Groth16ProvingKey, w, h):
         """The five MSMs with this shard's range of h supplied by the distributed computeH.
         w, h: DeviceVector or any object with an integer/ctypes `.ptr` (e.g. a torch tensor's data_ptr)."""
-        out, tm = Groth16MsmOut(), _Timings()
+        out, tm = _MSM_OUT[self.curve](), _Timings()
         self._check(self.lib.b200_groth16_msms_dev(self.h, pk.h, _dev_ptr(w), _dev_ptr(h), C.byref(out), C.byref(tm)))
         return out, {k: getattr(tm, k) for k, _ in _Timings._fields_}
 
     # -- distributed computeH phases (include/b200prover.h: b200_dist_phase / b200_dist_scale)
     def ntt_dist_phase(self, log_n, generator, coset_gen, data, tmp, log_ranks, rank, phase, inverse, scale=0):
-        self._check(self.lib.b200_ntt_dist_phase(self.h, BN254, log_n, _ptr(_u64(generator)), _ptr(_u64(coset_gen)),
+        self._check(self.lib.b200_ntt_dist_phase(self.h, self.curve, log_n, _ptr(_u64(generator)), _ptr(_u64(coset_gen)),
                                                  _dev_ptr(data), _dev_ptr(tmp), log_ranks, rank, int(phase),
                                                  int(inverse), int(scale)))
 
     def fr_mul_sub_dev(self, a, b, c, n):
-        self._check(self.lib.b200_fr_mul_sub_dev(self.h, BN254, _dev_ptr(a), _dev_ptr(b), _dev_ptr(c), n))
+        self._check(self.lib.b200_fr_mul_sub_dev(self.h, self.curve, _dev_ptr(a), _dev_ptr(b), _dev_ptr(c), n))
 
     # -- PlonK building blocks on device vectors (plonk/bn254/prove.go; SURVEY 8(a) P1, P2, P6, P7, P8)
     def fr_batch_inverse_dev(self, src, dst, n):
-        self._check(self.lib.b200_fr_batch_inverse_dev(self.h, BN254, _dev_ptr(src), _dev_ptr(dst), n))
+        self._check(self.lib.b200_fr_batch_inverse_dev(self.h, self.curve, _dev_ptr(src), _dev_ptr(dst), n))
 
     def fr_prefix_product_dev(self, src, dst, n):
-        self._check(self.lib.b200_fr_prefix_product_dev(self.h, BN254, _dev_ptr(src), _dev_ptr(dst), n))
+        self._check(self.lib.b200_fr_prefix_product_dev(self.h, self.curve, _dev_ptr(src), _dev_ptr(dst), n))
 
     def fr_poly_eval_dev(self, coeffs, n, x) -> np.ndarray:
         out = np.empty(4, dtype=np.uint64)
-        self._check(self.lib.b200_fr_poly_eval_dev(self.h, BN254, _dev_ptr(coeffs), n, _ptr(_u64(x)), _ptr(out)))
+        self._check(self.lib.b200_fr_poly_eval_dev(self.h, self.curve, _dev_ptr(coeffs), n, _ptr(_u64(x)), _ptr(out)))
         return out
 
     def fr_poly_div_linear_dev(self, coeffs, n, z, quotient):
-        self._check(self.lib.b200_fr_poly_div_linear_dev(self.h, BN254, _dev_ptr(coeffs), n, _ptr(_u64(z)), _dev_ptr(quotient)))
+        self._check(self.lib.b200_fr_poly_div_linear_dev(self.h, self.curve, _dev_ptr(coeffs), n, _ptr(_u64(z)), _dev_ptr(quotient)))
 
     def plonk_divide_by_xn_minus_one_dev(self, vec, log_big, log_small, generator_big, coset_gen):
-        self._check(self.lib.b200_plonk_divide_by_xn_minus_one_dev(self.h, BN254, _dev_ptr(vec), log_big, log_small,
+        self._check(self.lib.b200_plonk_divide_by_xn_minus_one_dev(self.h, self.curve, _dev_ptr(vec), log_big, log_small,
                                                                    _ptr(_u64(generator_big)), _ptr(_u64(coset_gen))))
 
     def plonk_build_ratio_dev(self, l, r, o, perm, beta, gamma, log_n, generator, coset_gen, z_out):
         """Z of the copy constraints (prove.go:610-621); perm: device int64[3 n]."""
-        self._check(self.lib.b200_plonk_build_ratio_dev(self.h, BN254, _dev_ptr(l), _dev_ptr(r), _dev_ptr(o), _dev_ptr(perm),
+        self._check(self.lib.b200_plonk_build_ratio_dev(self.h, self.curve, _dev_ptr(l), _dev_ptr(r), _dev_ptr(o), _dev_ptr(perm),
                                                         _ptr(_u64(beta)), _ptr(_u64(gamma)), log_n, _ptr(_u64(generator)),
                                                         _ptr(_u64(coset_gen)), _dev_ptr(z_out)))
 
@@ -654,10 +687,10 @@ class Context:
             arr = _u64(val).reshape(-1, 4)
             for j in range(arr.shape[0]):
                 getattr(d, name)[j][:] = [int(v) for v in arr[j]]
-        self._check(self.lib.b200_plonk_quotient_rows_dev(self.h, BN254, C.byref(d), _dev_ptr(cres)))
+        self._check(self.lib.b200_plonk_quotient_rows_dev(self.h, self.curve, C.byref(d), _dev_ptr(cres)))
 
     def kzg_commit_dev(self, srs: "Bases", coeffs, n) -> np.ndarray:
-        out = np.empty(8, dtype=np.uint64)
+        out = np.empty(2 * self.fw, dtype=np.uint64)
         self._check(self.lib.b200_kzg_commit_dev(self.h, srs.h, _dev_ptr(coeffs), n, _ptr(out)))
         return out
 
@@ -685,7 +718,7 @@ class Context:
             ci = np.ascontiguousarray(commitment_index, dtype=np.uint64)
             d.qcp, d.vk_qcp, d.commitment_index = C.addressof(ptrs), vq.ctypes.data, ci.ctypes.data
         h = C.c_void_p()
-        self._check(self.lib.b200_plonk_pk_upload(self.h, BN254, C.byref(d), C.byref(h)))
+        self._check(self.lib.b200_plonk_pk_upload(self.h, self.curve, C.byref(d), C.byref(h)))
         return PlonkProvingKey(self, h, nb_public, len(qcp), shard_index, shard_count)
 
     def _plonk_bsb(self, pk, bsb):

@@ -16,8 +16,15 @@ int set_device(b200_ctx* ctx) {
     if (e != cudaSuccess) return ctx->fail(B200_ERR_CUDA, "cudaSetDevice", cudaGetErrorString(e));
     return B200_OK;
 }
+#if defined(B2_CURVE_BLS12_377)
+constexpr int BUILD_CURVE = B200_BLS12_377;
+#else
+constexpr int BUILD_CURVE = B200_BN254;
+#endif
 int check_curve(b200_ctx* ctx, int curve) {
-    if (curve != B200_BN254) return ctx->fail(B200_ERR_UNSUPPORTED, "only BN254 is built into this library");
+    if (curve != BUILD_CURVE)
+        return ctx->fail(B200_ERR_UNSUPPORTED, BUILD_CURVE == B200_BN254 ? "this library is the BN254 build (BLS12-377: libb200prover_bls12377.so)"
+                                                                         : "this library is the BLS12-377 build (BN254: libb200prover.so)");
     return B200_OK;
 }
 #define B2_ENTER(ctx, curve)                   \
@@ -28,7 +35,9 @@ int check_curve(b200_ctx* ctx, int curve) {
 
 extern "C" {
 
-const char* b200_version(void) { return "b200prover 0.1 (sm_100a, BN254)"; }
+const char* b200_version(void) { return BUILD_CURVE == B200_BN254 ? "b200prover 0.1 (sm_100a, BN254)" : "b200prover 0.1 (sm_100a, BLS12-377)"; }
+int b200_build_curve(void) { return BUILD_CURVE; }
+int b200_build_fp_words(void) { return (int)(sizeof(Fp) / 8); }
 
 int b200_device_count(void) {
     int n = 0;
@@ -94,31 +103,31 @@ void* b200_host_alloc(size_t bytes) {
 void b200_host_free(void* p) { if (p) cudaFreeHost(p); }
 
 int b200_dev_alloc(b200_ctx* ctx, size_t bytes, void** dptr) {
-    B2_ENTER(ctx, B200_BN254);
+    B2_ENTER(ctx, BUILD_CURVE);
     if (!dptr) return ctx->fail(B200_ERR_ARG, "null out pointer");
     B2_CUDA(ctx, cudaMalloc(dptr, bytes ? bytes : 16));
     return B200_OK;
 }
 int b200_dev_free(b200_ctx* ctx, void* dptr) {
-    B2_ENTER(ctx, B200_BN254);
+    B2_ENTER(ctx, BUILD_CURVE);
     B2_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     B2_CUDA(ctx, cudaFree(dptr));
     return B200_OK;
 }
 int b200_h2d(b200_ctx* ctx, void* dst, const void* src, size_t bytes) {
-    B2_ENTER(ctx, B200_BN254);
+    B2_ENTER(ctx, BUILD_CURVE);
     B2_CUDA(ctx, cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, ctx->stream));
     B2_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     return B200_OK;
 }
 int b200_d2h(b200_ctx* ctx, void* dst, const void* src, size_t bytes) {
-    B2_ENTER(ctx, B200_BN254);
+    B2_ENTER(ctx, BUILD_CURVE);
     B2_CUDA(ctx, cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToHost, ctx->stream));
     B2_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     return B200_OK;
 }
 int b200_sync(b200_ctx* ctx) {
-    B2_ENTER(ctx, B200_BN254);
+    B2_ENTER(ctx, BUILD_CURVE);
     B2_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     return B200_OK;
 }
@@ -128,13 +137,14 @@ static int vec_mul_host(b200_ctx* ctx, int fr, const uint64_t* a, const uint64_t
     if (n == 0) return B200_OK;
     if (!a || !b || !out) return ctx->fail(B200_ERR_ARG, "null vector");
     DevBuf da, db;
-    B2_CUDA(ctx, da.alloc(n * 32));
-    B2_CUDA(ctx, db.alloc(n * 32));
-    B2_CUDA(ctx, cudaMemcpyAsync(da.p, a, n * 32, cudaMemcpyHostToDevice, ctx->stream));
-    B2_CUDA(ctx, cudaMemcpyAsync(db.p, b, n * 32, cudaMemcpyHostToDevice, ctx->stream));
+    const size_t bytes = n * (fr ? sizeof(Fr) : sizeof(Fp));
+    B2_CUDA(ctx, da.alloc(bytes));
+    B2_CUDA(ctx, db.alloc(bytes));
+    B2_CUDA(ctx, cudaMemcpyAsync(da.p, a, bytes, cudaMemcpyHostToDevice, ctx->stream));
+    B2_CUDA(ctx, cudaMemcpyAsync(db.p, b, bytes, cudaMemcpyHostToDevice, ctx->stream));
     if (fr) B2_TRY(vec_mul_fr(ctx, da.as<Fr>(), db.as<Fr>(), da.as<Fr>(), n));
     else B2_TRY(vec_mul_fp(ctx, da.as<Fp>(), db.as<Fp>(), da.as<Fp>(), n));
-    B2_CUDA(ctx, cudaMemcpyAsync(out, da.p, n * 32, cudaMemcpyDeviceToHost, ctx->stream));
+    B2_CUDA(ctx, cudaMemcpyAsync(out, da.p, bytes, cudaMemcpyDeviceToHost, ctx->stream));
     B2_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     return B200_OK;
 }
@@ -147,7 +157,7 @@ int b200_fp_vec_mul(b200_ctx* ctx, int curve, const uint64_t* a, const uint64_t*
     return vec_mul_host(ctx, 0, a, b, out, n);
 }
 int b200_imad_peak(b200_ctx* ctx, double* mac32_per_s, double* imad32_per_s, double* sm_mhz) {
-    B2_ENTER(ctx, B200_BN254);
+    B2_ENTER(ctx, BUILD_CURVE);
     return imad_peak(ctx, mac32_per_s, imad32_per_s, sm_mhz);
 }
 
@@ -252,7 +262,7 @@ int b200_bases_upload(b200_ctx* ctx, int curve, int group, const uint64_t* bases
     return B200_OK;
 }
 int b200_bases_free(b200_ctx* ctx, b200_bases* bases) {
-    B2_ENTER(ctx, B200_BN254);
+    B2_ENTER(ctx, BUILD_CURVE);
     B2_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     delete bases;
     return B200_OK;
@@ -270,7 +280,7 @@ int b200_bases_info(b200_ctx* ctx, const b200_bases* bases, b200_msm_set_info* o
 }
 
 int b200_msm_dev(b200_ctx* ctx, const b200_bases* bases, const void* scalars_dev, size_t n, uint64_t* out_jac, float* kernel_ms) {
-    B2_ENTER(ctx, B200_BN254);
+    B2_ENTER(ctx, BUILD_CURVE);
     if (!bases || !out_jac || (n && !scalars_dev)) return ctx->fail(B200_ERR_ARG, "null argument");
     if (n > bases->n) return ctx->fail(B200_ERR_ARG, "more scalars than resident bases");
     B2_CUDA(ctx, cudaEventRecord(ctx->ev0, ctx->stream));
@@ -290,7 +300,7 @@ int b200_msm_dev(b200_ctx* ctx, const b200_bases* bases, const void* scalars_dev
 }
 
 int b200_msm_resident(b200_ctx* ctx, const b200_bases* bases, const uint64_t* scalars, size_t n, uint64_t* out_jac) {
-    B2_ENTER(ctx, B200_BN254);
+    B2_ENTER(ctx, BUILD_CURVE);
     if (n && !scalars) return ctx->fail(B200_ERR_ARG, "null scalars");
     DevBuf ds;
     B2_CUDA(ctx, ds.alloc(n * sizeof(Fr)));
@@ -347,7 +357,7 @@ int b200_groth16_pk_upload(b200_ctx* ctx, int curve, const b200_groth16_pk_desc*
     return groth16_pk_upload(ctx, desc, out);
 }
 int b200_groth16_pk_free(b200_ctx* ctx, b200_groth16_pk* pk) {
-    B2_ENTER(ctx, B200_BN254);
+    B2_ENTER(ctx, BUILD_CURVE);
     B2_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     delete pk;
     return B200_OK;
@@ -371,7 +381,7 @@ int b200_groth16_pk_wire_range(b200_ctx* ctx, const b200_groth16_pk* pk, size_t*
 int b200_groth16_prove_core(b200_ctx* ctx, const b200_groth16_pk* pk, const uint64_t* a, const uint64_t* b,
                             const uint64_t* c, size_t n_constraints, const uint64_t* w, const uint32_t* k_remove,
                             size_t n_remove, b200_groth16_out* out, b200_timings* timings) {
-    B2_ENTER(ctx, B200_BN254);
+    B2_ENTER(ctx, BUILD_CURVE);
     if (!pk || !out || !w || (n_constraints && (!a || !b || !c)) || (n_remove && !k_remove))
         return ctx->fail(B200_ERR_ARG, "null argument");
     return groth16_prove_core(ctx, pk, a, b, c, n_constraints, w, k_remove, n_remove, nullptr, out, timings);
@@ -380,7 +390,7 @@ int b200_groth16_prove_core(b200_ctx* ctx, const b200_groth16_pk* pk, const uint
 int b200_groth16_prove_core_dev(b200_ctx* ctx, const b200_groth16_pk* pk, const void* a_dev, const void* b_dev,
                                 const void* c_dev, size_t n_constraints, const void* w_dev, b200_groth16_out* out,
                                 b200_timings* timings) {
-    B2_ENTER(ctx, B200_BN254);
+    B2_ENTER(ctx, BUILD_CURVE);
     if (!pk || !out || !w_dev || (n_constraints && (!a_dev || !b_dev || !c_dev)))
         return ctx->fail(B200_ERR_ARG, "null argument");
     return groth16_prove_core(ctx, pk, (const uint64_t*)a_dev, (const uint64_t*)b_dev, (const uint64_t*)c_dev,
@@ -389,7 +399,7 @@ int b200_groth16_prove_core_dev(b200_ctx* ctx, const b200_groth16_pk* pk, const 
 
 int b200_groth16_msms_dev(b200_ctx* ctx, const b200_groth16_pk* pk, const void* w_dev, const void* h_dev,
                           b200_groth16_out* out, b200_timings* timings) {
-    B2_ENTER(ctx, B200_BN254);
+    B2_ENTER(ctx, BUILD_CURVE);
     if (!pk || !out || !w_dev || !h_dev) return ctx->fail(B200_ERR_ARG, "null argument");
     return groth16_prove_core(ctx, pk, nullptr, nullptr, nullptr, 0, (const uint64_t*)w_dev, nullptr, 0,
                               (const uint64_t*)h_dev, out, timings);
@@ -480,10 +490,10 @@ int b200_plonk_divide_by_xn_minus_one_dev(b200_ctx* ctx, int curve, void* vec_de
     return B200_OK;
 }
 int b200_kzg_commit_dev(b200_ctx* ctx, const b200_bases* srs, const void* coeffs_dev, size_t n, uint64_t* out_affine) {
-    B2_ENTER(ctx, B200_BN254);
+    B2_ENTER(ctx, BUILD_CURVE);
     if (!srs || !out_affine || (n && !coeffs_dev)) return ctx->fail(B200_ERR_ARG, "null argument");
     if (srs->group != 1) return ctx->fail(B200_ERR_ARG, "the KZG SRS is a G1 base set");
-    uint64_t jac[12];
+    uint64_t jac[3 * B200_FP_WORDS];
     B2_TRY(b200_msm_dev(ctx, srs, coeffs_dev, n, jac, nullptr));
     return b200_g1_jac_to_affine(jac, out_affine);
 }
@@ -558,7 +568,7 @@ int b200_set_option(b200_ctx* ctx, const char* key, long value) {
 
 // ---- profiling ---------------------------------------------------------------------------
 int b200_profile_start(b200_ctx* ctx) {
-    B2_ENTER(ctx, B200_BN254);
+    B2_ENTER(ctx, BUILD_CURVE);
     B2_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     for (auto& sp : ctx->prof_spans) { ctx->prof_pool.push_back(sp.e0); ctx->prof_pool.push_back(sp.e1); }
     ctx->prof_spans.clear();
@@ -567,7 +577,7 @@ int b200_profile_start(b200_ctx* ctx) {
     return B200_OK;
 }
 int b200_profile_read(b200_ctx* ctx, b200_profile* out) {
-    B2_ENTER(ctx, B200_BN254);
+    B2_ENTER(ctx, BUILD_CURVE);
     if (!out) return ctx->fail(B200_ERR_ARG, "null output");
     B2_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     memset(out, 0, sizeof *out);

@@ -503,6 +503,9 @@ B2_D void mod_sub_dev(uint32_t* r, const uint32_t* a, const uint32_t* b) {
 #pragma unroll
     for (int k = 0; k < 8; ++k) r[k] = t[k];
 }
+#if defined(B2_CURVE_BLS12_377)
+#include "field_chains12.cuh"   // 12-limb copies of the chains above (BLS12-377 Fp), scripts/gen_field_chains.py
+#endif
 #endif  // __CUDACC__
 
 // ---------------------------------------------------------------------------------------
@@ -536,6 +539,16 @@ B2_HD void mont_mul_host(uint32_t* r, const uint32_t* a, const uint32_t* b) {
     const bool ge = t[N] || !br;
     for (int j = 0; j < N; ++j) r[j] = ge ? s[j] : t[j];
 }
+
+#if !defined(__CUDA_ARCH__)
+// host callers go through one out-of-line copy per field: the group formulas inline dozens of products, and
+// gcc -O3 on a fully inlined 12-limb XYZZ addition takes minutes
+template <class PRM>
+#if defined(__GNUC__)
+__attribute__((noinline))
+#endif
+void mont_mul_host_outlined(uint32_t* r, const uint32_t* a, const uint32_t* b) { mont_mul_host<PRM>(r, a, b); }
+#endif
 
 template <class PRM>
 B2_HD void mod_add_host(uint32_t* r, const uint32_t* a, const uint32_t* b) {
@@ -577,9 +590,12 @@ struct alignas(16) Fe {
         Fe r;
 #if defined(__CUDA_ARCH__)
         if constexpr (N == 8) mont_mul_dev<PRM>(r.l, l, o.l);
+#if defined(B2_CURVE_BLS12_377)
+        else if constexpr (N == 12) mont_mul_dev12<PRM>(r.l, l, o.l);
+#endif
         else mont_mul_host<PRM>(r.l, l, o.l);
 #else
-        mont_mul_host<PRM>(r.l, l, o.l);
+        mont_mul_host_outlined<PRM>(r.l, l, o.l);
 #endif
         return r;
     }
@@ -588,6 +604,9 @@ struct alignas(16) Fe {
         Fe r;
 #if defined(__CUDA_ARCH__)
         if constexpr (N == 8) mod_add_dev<PRM>(r.l, l, o.l);
+#if defined(B2_CURVE_BLS12_377)
+        else if constexpr (N == 12) mod_add_dev12<PRM>(r.l, l, o.l);
+#endif
         else mod_add_host<PRM>(r.l, l, o.l);
 #else
         mod_add_host<PRM>(r.l, l, o.l);
@@ -598,6 +617,9 @@ struct alignas(16) Fe {
         Fe r;
 #if defined(__CUDA_ARCH__)
         if constexpr (N == 8) mod_sub_dev<PRM>(r.l, l, o.l);
+#if defined(B2_CURVE_BLS12_377)
+        else if constexpr (N == 12) mod_sub_dev12<PRM>(r.l, l, o.l);
+#endif
         else mod_sub_host<PRM>(r.l, l, o.l);
 #else
         mod_sub_host<PRM>(r.l, l, o.l);

@@ -58,18 +58,19 @@ int b200_groth16_finalize(const b200_groth16_out* msm, const uint64_t* r, const 
 int b200_groth16_proof_bytes(const uint64_t* ar_affine, const uint64_t* bs_affine, const uint64_t* krs_affine,
                              uint8_t* out, size_t out_cap) {
     if (!ar_affine || !bs_affine || !krs_affine || !out) return B200_ERR_ARG;
-    if (out_cap < 164) return B200_ERR_ARG;
+    const size_t FB = FP_BYTES, total = 5 * FB + 4;   // 164 bytes on BN254, 244 on BLS12-377
+    if (out_cap < total) return B200_ERR_ARG;
     G1Affine ar, krs;
     G2Affine bs;
     memcpy(&ar, ar_affine, sizeof ar);
     memcpy(&bs, bs_affine, sizeof bs);
     memcpy(&krs, krs_affine, sizeof krs);
     g1_compress(ar, out);          // marshal.go:49
-    g2_compress(bs, out + 32);     // marshal.go:52
-    g1_compress(krs, out + 96);    // marshal.go:55
-    memset(out + 128, 0, 4);       // u32 len(Commitments) = 0, marshal.go:58
-    g1_compress(G1Affine::inf(), out + 132);  // CommitmentPok, marshal.go:61
-    return 164;
+    g2_compress(bs, out + FB);     // marshal.go:52
+    g1_compress(krs, out + 3 * FB);    // marshal.go:55
+    memset(out + 4 * FB, 0, 4);       // u32 len(Commitments) = 0, marshal.go:58
+    g1_compress(G1Affine::inf(), out + 4 * FB + 4);  // CommitmentPok, marshal.go:61
+    return (int)total;
 }
 
 }  // extern "C"

@@ -173,12 +173,13 @@ void fr_be(const Fr& m, uint8_t out[32]) {
     }
 }
 // G1Affine.RawBytes / Marshal: X || Y big-endian; infinity = 0x40 then zeros
-void g1_raw(const G1Affine& p, uint8_t out[64]) {
-    if (p.is_inf()) { memset(out, 0, 64); out[0] = 0x40; return; }
+constexpr int G1_RAW = 2 * FP_BYTES;   // 64 on BN254
+void g1_raw(const G1Affine& p, uint8_t* out) {
+    if (p.is_inf()) { memset(out, 0, G1_RAW); out[0] = 0x40; return; }
     fp_be(p.x, out);
-    fp_be(p.y, out + 32);
+    fp_be(p.y, out + FP_BYTES);
 }
-void bind_point(Transcript& fs, const char* name, const G1Affine& p) { uint8_t b[64]; g1_raw(p, b); fs.bind(name, b, 64); }
+void bind_point(Transcript& fs, const char* name, const G1Affine& p) { uint8_t b[G1_RAW]; g1_raw(p, b); fs.bind(name, b, G1_RAW); }
 void bind_fr(Transcript& fs, const char* name, const Fr& x) { uint8_t b[32]; fr_be(x, b); fs.bind(name, b, 32); }
 Fr derive(Transcript& fs, const char* name) { uint8_t b[32]; fs.challenge(name, b); return fr_from_be(b); }
 
@@ -331,6 +332,9 @@ extern "C" {
 
 int b200_plonk_pk_upload(b200_ctx* ctx, int curve, const b200_plonk_pk_desc* d, b200_plonk_pk** out) {
     if (!ctx) return B200_ERR_ARG;
+#if defined(B2_CURVE_BLS12_377)
+    return ctx->fail(B200_ERR_UNSUPPORTED, "the PlonK prover is built for BN254 only (libb200prover.so)");
+#endif
     if (curve != B200_BN254) return ctx->fail(B200_ERR_UNSUPPORTED, "only BN254 is built into this library");
     if (cudaSetDevice(ctx->device) != cudaSuccess) return ctx->fail(B200_ERR_CUDA, "cudaSetDevice");
     if (!d || !out || !d->generator || !d->generator_big || !d->coset_gen || !d->ql || !d->qr || !d->qm || !d->qo || !d->qk || !d->s1 ||

@@ -12,6 +12,11 @@
  *     unsafe.Pointer(&slice[0]) with no conversion.
  *   - G1Affine = X,Y (8 u64; (0,0) = infinity); G1Jac = X,Y,Z (12 u64; Z = 0 = infinity);
  *     G2Affine = X.A0,X.A1,Y.A0,Y.A1 (16 u64); G2Jac = 24 u64.
+ *   - BLS12-377 (BASELINE.json config 5) is a SECOND library built from the same sources,
+ *     libb200prover_bls12377.so (make CURVE=bls12_377; bind it with -DB200_CURVE_BLS12_377): same entry
+ *     points, curve argument B200_BLS12_377, Fr still 4 u64 but Fp = 6 u64 (R = 2^384), so G1Affine = 12,
+ *     G1Jac = 18, G2Affine = 24, G2Jac = 36 u64 -- B200_FP_WORDS below sizes the structs.  Each library
+ *     rejects the other curve's id with B200_ERR_UNSUPPORTED.  The PlonK entry points are BN254-only.
  *   - Jacobian results are SOME representative of the point (not gnark-crypto's particular
  *     one); equality with MultiExp is defined on the affine-normalised point (FromJacobian).
  *   - Return value: 0 on success, a negative b200_status otherwise; b200_last_error(ctx) holds a
@@ -53,6 +58,16 @@ enum b200_status {
 };
 
 enum b200_curve { B200_BN254 = 0, B200_BLS12_377 = 1 };
+
+/* u64 words of one base-field element in the library this header is bound to */
+#if defined(B200_CURVE_BLS12_377) || defined(B2_CURVE_BLS12_377)
+#define B200_FP_WORDS 6
+#else
+#define B200_FP_WORDS 4
+#endif
+/* curve id and Fp words the loaded library was built for (a binder checks them once at start-up) */
+int b200_build_curve(void);
+int b200_build_fp_words(void);
 
 #define B200_DIF 0 /* fft.DIF: natural order in, bit-reversed out */
 #define B200_DIT 1 /* fft.DIT: bit-reversed in, natural out       */
@@ -304,11 +319,11 @@ int b200_fr_mul_sub_dev(b200_ctx *ctx, int curve, void *a_dev, const void *b_dev
 /* The five MultiExp results BEFORE the alpha/beta/delta/r/s fix-ups, which stay in Go
  * (prove.go:206-207,219-221,248-271,294-299). */
 typedef struct b200_groth16_out {
-    uint64_t ar[12];    /* MSM(pk.G1.A, wireValuesA)       prove.go:214 */
-    uint64_t bs1[12];   /* MSM(pk.G1.B, wireValuesB)       prove.go:201 */
-    uint64_t krs[12];   /* MSM(pk.G1.K, W[nb_public:])     prove.go:244 */
-    uint64_t krs2[12];  /* MSM(pk.G1.Z, h[:n-1])           prove.go:234 */
-    uint64_t bs2[24];   /* MSM(pk.G2.B, wireValuesB)       prove.go:290 */
+    uint64_t ar[3 * B200_FP_WORDS];    /* MSM(pk.G1.A, wireValuesA)       prove.go:214 */
+    uint64_t bs1[3 * B200_FP_WORDS];   /* MSM(pk.G1.B, wireValuesB)       prove.go:201 */
+    uint64_t krs[3 * B200_FP_WORDS];   /* MSM(pk.G1.K, W[nb_public:])     prove.go:244 */
+    uint64_t krs2[3 * B200_FP_WORDS];  /* MSM(pk.G1.Z, h[:n-1])           prove.go:234 */
+    uint64_t bs2[6 * B200_FP_WORDS];   /* MSM(pk.G2.B, wireValuesB)       prove.go:290 */
 } b200_groth16_out;
 
 /* computeH + wire filtering + the five MSMs on the device (prove.go:139-175,199-301;

@@ -50,11 +50,11 @@ def load_pkg():
     return m
 
 
-def rand_field(rng, n, out=None):
+def rand_field(rng, n, out=None, top_limb=TOP_LIMB):
     """n reduced field elements as Montgomery limbs (uniform up to the top-limb cut)."""
     a = out if out is not None else np.empty((n, 4), dtype=np.uint64)
     a[:, :3] = rng.integers(0, 1 << 64, size=(n, 3), dtype=np.uint64)
-    a[:, 3] = rng.integers(0, TOP_LIMB, size=n, dtype=np.uint64)
+    a[:, 3] = rng.integers(0, top_limb, size=n, dtype=np.uint64)
     return a
 
 
@@ -78,13 +78,49 @@ G2_GEN = np.concatenate([fp_limbs(v) for v in (
     4082367875863433681332203403145435568316851327593401208105741076214120093531)])
 
 
-def mont_sum(arr):
+def mont_sum(arr, r_mod=R_MOD):
     """Sum of Montgomery-form elements mod r, exact, vectorised (columns of 32-bit halves)."""
     h = np.ascontiguousarray(arr).view(np.uint32).reshape(-1, 8)
     tot = 0
     for j in range(8):
         tot += int(h[:, j].sum(dtype=np.uint64)) << (32 * j)
-    return tot % R_MOD
+    return tot % r_mod
+
+
+class CurveParams:
+    """What the synthetic instance needs to know about a curve: Fr modulus and FFT root, generators as limbs."""
+
+    def __init__(self, curve_id, name, r_mod, p_mod, fp_words, root, two_adicity, coset, g1, g2):
+        self.id, self.name, self.r_mod, self.top_limb = curve_id, name, r_mod, r_mod >> 192
+        self.root, self.two_adicity, self.coset = root, two_adicity, coset
+        fp = lambda v: np.frombuffer(((v << (64 * fp_words)) % p_mod).to_bytes(8 * fp_words, "little"), dtype=np.uint64).copy()
+        self.g1_gen = np.concatenate([fp(v) for v in g1])
+        self.g2_gen = np.concatenate([fp(v) for v in g2])
+
+    def fr_limbs(self, x):
+        return np.frombuffer(((x << 256) % self.r_mod).to_bytes(32, "little"), dtype=np.uint64).copy()
+
+    def generator(self, log_n):
+        return self.fr_limbs(pow(self.root, 1 << (self.two_adicity - log_n), self.r_mod))
+
+
+BN254_PARAMS = CurveParams(0, "bn254", R_MOD, P_MOD, 4, FR_ROOT_2_28, 28, 5, (1, 2), (
+    10857046999023057135944570762232829481370756359578518086990519993285655852781,
+    11559732032986387107991004021392285783925812861821192530917403151452391805634,
+    8495653923123431417604973247489272438418190587263600148770280649306958101930,
+    4082367875863433681332203403145435568316851327593401208105741076214120093531))
+# BLS12-377 (config 5): r, p from std/math/emulated/emparams/emparams.go:123,137; Fr root of unity of order 2^47 =
+# 22^((r-1)/2^47); coset shift 22; G1 generator as gnark-crypto's, G2 generator = a cofactor-cleared point (any
+# generator does: the bases are inputs of the ABI) -- the same constants as oracle/bls12_377.py, which checks them.
+_R377 = 0x12AB655E9A2CA55660B44D1E5C37B00159AA76FED00000010A11800000000001
+_P377 = 0x01AE3A4617C510EAC63B05C06CA1493B1A22D9F300F5138F1EF3622FBA094800170B5D44300000008508C00000000001
+BLS12_377_PARAMS = CurveParams(1, "bls12_377", _R377, _P377, 6, pow(22, (_R377 - 1) >> 47, _R377), 47, 22, (
+    81937999373150964239938255573465948239988671502647976594219695644855304257327692006745978603320413799295628339695,
+    241266749859715473739788878240585681733927191168601896383759122102112907357779751001206799952863815012735208165030), (
+    67004216521362769139960304638241662463384504912045095543649118964167831559549275276665917802324363056069254155209,
+    188039100033830534835560926333495938812099884491688240598849896699685545777288948680356069069856197422355451241144,
+    212961125199539672632481864692443889005842964580434572770814582520396590909323644956646137861647360575214633605398,
+    67625758907332218457243685014278362134590189520408250963023412301547932120327362287218456798771752606845621278268))
 
 
 class ClockSampler:
@@ -154,7 +190,8 @@ class Instance:
     K = n private wires, Z = n - 1.  Bases are [k_i]G with known k_i (device fixed-base kernel)
     so that every MSM result can be checked exactly at any size."""
 
-    def __init__(self, log_n, rank, world, seed=0xB200):
+    def __init__(self, log_n, rank, world, seed=0xB200, cp=None):
+        self.cp = cp = cp or BN254_PARAMS
         self.log_n, self.n = log_n, 1 << log_n
         n = self.n
         self.n_wires, self.nb_public = n + 2, 2
@@ -163,8 +200,8 @@ class Instance:
         self.full = dict(a=n, b=n, k=n, z=n - 1)
         self.rng = np.random.default_rng(seed + log_n)          # same on every rank: W, a, b, c
         self.rank, self.world = rank, world
-        self.gen = fr_limbs(pow(FR_ROOT_2_28, 1 << (28 - log_n), R_MOD))
-        self.coset = fr_limbs(5)
+        self.gen = cp.generator(log_n)
+        self.coset = cp.fr_limbs(cp.coset)
 
     def shard(self, key):
         m = self.full[key]
@@ -180,9 +217,9 @@ class Instance:
         self.dlog, self.bases = {}, {}
         for key in ("a", "b", "k", "z"):
             lo, hi = self.shard(key)
-            self.dlog[key] = rand_field(rng, hi - lo)
-            self.bases[key] = ctx.batch_scalar_mul(G1_GEN, self.dlog[key], 1)
-        self.bases["g2b"] = ctx.batch_scalar_mul(G2_GEN, self.dlog["b"], 2)
+            self.dlog[key] = rand_field(rng, hi - lo, top_limb=self.cp.top_limb)
+            self.bases[key] = ctx.batch_scalar_mul(self.cp.g1_gen, self.dlog[key], 1)
+        self.bases["g2b"] = ctx.batch_scalar_mul(self.cp.g2_gen, self.dlog["b"], 2)
         return ctx.groth16_pk_upload(
             log_n=self.log_n, generator=self.gen, coset_gen=self.coset, g1_a=self.bases["a"], g1_b=self.bases["b"],
             g1_k=self.bases["k"], g1_z=self.bases["z"], g2_b=self.bases["g2b"], infinity_a=self.inf_a,
@@ -191,10 +228,10 @@ class Instance:
 
     def witness(self, pkg):
         """W, a, b, c in pinned host memory (uniform field elements, like the squaring chain's)."""
-        self.w = rand_field(self.rng, self.n_wires, pkg.pinned_empty((self.n_wires, 4)))
-        self.a = rand_field(self.rng, self.n, pkg.pinned_empty((self.n, 4)))
-        self.b = rand_field(self.rng, self.n, pkg.pinned_empty((self.n, 4)))
-        self.c = rand_field(self.rng, self.n, pkg.pinned_empty((self.n, 4)))
+        self.w = rand_field(self.rng, self.n_wires, pkg.pinned_empty((self.n_wires, 4)), self.cp.top_limb)
+        self.a = rand_field(self.rng, self.n, pkg.pinned_empty((self.n, 4)), self.cp.top_limb)
+        self.b = rand_field(self.rng, self.n, pkg.pinned_empty((self.n, 4)), self.cp.top_limb)
+        self.c = rand_field(self.rng, self.n, pkg.pinned_empty((self.n, 4)), self.cp.top_limb)
 
     def check(self, ctx, pkg, out):
         """Exact, size-independent: each MSM output must be [sum k_i s_i]G for this shard."""
@@ -208,10 +245,10 @@ class Instance:
               "bs2": (self.w[wires_b[lo_b:hi_b]], "b", 2)}
         for name, (scalars, key, group) in sc.items():
             prod = ctx.fr_vec_mul(self.dlog[key], np.ascontiguousarray(scalars))   # Montgomery form of k_i * s_i
-            tot = mont_sum(prod)                                                    # Montgomery form of the sum
+            tot = mont_sum(prod, self.cp.r_mod)                                     # Montgomery form of the sum
             tot_l = np.frombuffer(tot.to_bytes(32, "little"), dtype=np.uint64)
-            want = ctx.batch_scalar_mul(G1_GEN if group == 1 else G2_GEN, tot_l.reshape(1, 4), group)[0]
-            got = pkg.g1_jac_to_affine(od[name]) if group == 1 else pkg.g2_jac_to_affine(od[name])
+            want = ctx.batch_scalar_mul(self.cp.g1_gen if group == 1 else self.cp.g2_gen, tot_l.reshape(1, 4), group)[0]
+            got = pkg.g1_jac_to_affine(od[name], curve=self.cp.id) if group == 1 else pkg.g2_jac_to_affine(od[name], curve=self.cp.id)
             if not np.array_equal(got, want):
                 raise SystemExit(f"bench: MSM {name} does not match its known discrete log -- result invalid")
         return True
@@ -432,8 +469,15 @@ def gpu_arm(args):
     args.plonk_result = None
     if dist is not None:
         ctx.use_stream(None)
+    pk.free()                           # the folded tables go before the PlonK / BLS12-377 keys come
+    del inst.bases, inst.dlog
+    args.bls_result = None
+    if args.bls12_377_log_n and world == 1:
+        try:
+            args.bls_result = bls12_377_section(pkg, local, args.bls12_377_log_n, args.steps, args.warmup, peak)
+        except Exception as e:          # the headline line must still be printed
+            args.bls_result = {"error": repr(e)}
     if args.plonk_log_n and (world == 1 or (args.plonk_dist and (world & (world - 1)) == 0)):
-        pk.free()                       # the folded tables go before the PlonK key comes
         try:
             args.plonk_result = plonk_section(pkg, ctx, args.plonk_log_n, args.steps, args.warmup, dist, rank, world,
                                               f"cuda:{local}", barrier, max_over_ranks)
@@ -446,6 +490,59 @@ def gpu_arm(args):
         ctx.close()
         return 0
     return report(args, world, peak, prof, stage, step_ms, e2e_s, clk, verified, inst, t_setup, wall_dev, pk_info, distributed, h2d_bytes)
+
+
+def bls12_377_section(pkg, device_index, log_n, steps, warmup, peak):
+    """BASELINE.json config 5: BLS12-377 Groth16 prove core at 2^log_n constraints on one GPU through the second
+    library (libb200prover_bls12377.so: 12-limb Fp, Fp2 with u^2 = -5; same kernels, same ABI).  Same instance shape
+    and the same exact check as the BN254 headline (every MSM result against its known discrete log).  `value` =
+    seconds per proof through the host-buffer call (pinned a, b, c, W in; H2D inside) + the host fix-ups."""
+    ctx = pkg.Context(device_index, curve=pkg.BLS12_377)
+    try:
+        inst = Instance(log_n, 0, 1, cp=BLS12_377_PARAMS)
+        t0 = time.perf_counter()
+        pk = inst.build_key(ctx)
+        inst.witness(pkg)
+        t_setup = time.perf_counter() - t0
+        rs = rand_field(np.random.default_rng(3), 2, top_limb=inst.cp.top_limb)
+        vkp = [inst.bases["a"][0], inst.bases["b"][0], inst.bases["k"][0], inst.bases["g2b"][0], inst.bases["g2b"][1]]
+        for _ in range(max(1, warmup)):
+            out, tm = ctx.groth16_prove_core(pk, inst.a, inst.b, inst.c, inst.w)
+        ctx.profile_start()
+        wall, tms = [], []
+        for _ in range(steps):
+            t1 = time.perf_counter()
+            out, tm = ctx.groth16_prove_core(pk, inst.a, inst.b, inst.c, inst.w)
+            pkg.groth16_finalize(out, rs[0], rs[1], *vkp, curve=pkg.BLS12_377)
+            wall.append(time.perf_counter() - t1)
+            tms.append(tm)
+        prof = ctx.profile_read()
+        ok = inst.check(ctx, pkg, out)
+        info = pk.info()
+        pk.free()
+        n = inst.n
+        g1 = prof["msm_acc_g1"]
+        g1_launch_ms = g1["ms"] / max(1, g1["launches"])
+        mac_fp = 12 * 12 * 2 + 12                 # one 12-limb Montgomery product: 288 + 12 MAC32 (SURVEY.md 8(d): 300)
+        pts = g1["units"] / max(1, g1["launches"])
+        model = pts * 16 * 11 * mac_fp / (g1_launch_ms * 1e-3) if g1_launch_ms else 0.0
+        executed = pts * info["a"]["windows"] * 10 * mac_fp / (g1_launch_ms * 1e-3) if g1_launch_ms else 0.0
+        stage = {k: float(np.mean([t[k] for t in tms])) for k in tms[0]}
+        return {"metric": "BLS12-377 Groth16 prove s @2^%d constraints" % log_n, "value": float(np.mean(wall)), "unit": "s", "n_gpus": 1,
+                "steps": steps, "workload": "synthetic 2^%d-constraint Mul-chain-shaped R1CS on BLS12-377: computeH (7 transforms of 2^%d) + "
+                "4 G1 MSMs + 1 G2 MSM of ~2^%d points (Fp 377 bits = 12 x 32-bit limbs)" % (log_n, log_n, log_n),
+                "path": "b200_groth16_prove_core of libb200prover_bls12377.so (pinned host a, b, c, W in) + b200_groth16_finalize",
+                "device_ms": stage["total_ms"], "stage_ms": stage, "verified": bool(ok),
+                "verifier": "every MSM result equals [sum k_i s_i]G for the known discrete logs k_i of its bases (exact)",
+                "roofline_g1": {"bound": "imad", "kernel": "msm_accumulate_kernel<Fp> (12 limbs)", "launch_ms": g1_launch_ms,
+                                "model_mac32_per_s": model, "executed_mac32_per_s": executed, "peak_mac32_per_s": peak["mac32_per_s"],
+                                "frac_model": model / peak["mac32_per_s"], "frac_executed": executed / peak["mac32_per_s"],
+                                "note": "model = points x 16 windows x 11 Fp products x 300 MAC32 (SURVEY.md 8(d)); executed = points x the plan's "
+                                        "windows x 10 products (XYZZ mixed addition, two separate reductions for a*b - c*d) x 300 MAC32"},
+                "msm_plan": {k: info["a"][k] for k in ("c", "windows", "folded")},
+                "gpu_launches_per_proof": int(prof["kernel_launches"] // max(1, steps)), "setup_s": t_setup}
+    finally:
+        ctx.close()
 
 
 def plonk_section(pkg, ctx, log_n, steps, warmup, dist=None, rank=0, world=1, device=None, barrier=None, max_over_ranks=None):
@@ -580,6 +677,8 @@ def report(args, world, peak, prof, stage, step_ms, e2e_s, clk, verified, inst, 
     }
     if getattr(args, "plonk_result", None):
         line["plonk"] = args.plonk_result
+    if getattr(args, "bls_result", None) is not None:
+        line["bls12_377"] = args.bls_result
     if world == 1 and not args.no_cpu:
         sec, cores, text = cpu_prove_seconds(args.cpu_sample_log, inst.log_n)
         line["cpu_baseline"] = {"value": sec, "unit": "s", "cores": cores, "kind": "port", "sample": text}
@@ -596,6 +695,7 @@ def main():
     ap.add_argument("--log-n", type=int, default=24)
     ap.add_argument("--cpu-sample-log", type=int, default=18)
     ap.add_argument("--plonk-log-n", type=int, default=22, help="also time BN254 PlonK Prove at 2^k gates (config 4; sharded over the ranks at N > 1); 0 = skip")
+    ap.add_argument("--bls12-377-log-n", type=int, default=22, help="N = 1: also time BLS12-377 Groth16 Prove at 2^k constraints (config 5) through libb200prover_bls12377.so; 0 = skip")
     ap.add_argument("--plonk-dist", action="store_true", help="N > 1: run the sharded PlonK proof too (off by default: the scaling run stays the Groth16 line only)")
     ap.add_argument("--no-check", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")

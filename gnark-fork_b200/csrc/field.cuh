@@ -649,8 +649,12 @@ struct alignas(16) Fe {
     // Fermat inverse x^(p-2); 0 -> 0 (same convention as gnark-crypto's Inverse)
     B2_HD Fe inv() const {
         uint32_t e[N];
-        for (int i = 0; i < N; ++i) e[i] = PRM::p(i);
-        e[0] -= 2;  // p is odd and p(0) >= 2 for every modulus here
+        uint32_t borrow = 2;   // p - 2 with the borrow carried up (both BLS12-377 moduli end in ...00000001)
+        for (int i = 0; i < N; ++i) {
+            const uint32_t v = PRM::p(i);
+            e[i] = v - borrow;
+            borrow = v < borrow ? 1u : 0u;
+        }
         return pow(e, N);
     }
 };

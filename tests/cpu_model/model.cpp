@@ -169,6 +169,12 @@ void model_msm_g2(const uint64_t* s, const uint64_t* b, size_t n, int c, uint64_
 void model_fr_mul(const uint64_t* a, const uint64_t* b, uint64_t* o, size_t n) {
     for (size_t i = 0; i < n; ++i) reinterpret_cast<Fr*>(o)[i] = reinterpret_cast<const Fr*>(a)[i] * reinterpret_cast<const Fr*>(b)[i];
 }
+void model_fr_inv(const uint64_t* a, uint64_t* o, size_t n) {
+    for (size_t i = 0; i < n; ++i) reinterpret_cast<Fr*>(o)[i] = reinterpret_cast<const Fr*>(a)[i].inv();
+}
+void model_fp_inv(const uint64_t* a, uint64_t* o, size_t n) {
+    for (size_t i = 0; i < n; ++i) reinterpret_cast<Fp*>(o)[i] = reinterpret_cast<const Fp*>(a)[i].inv();
+}
 void model_fp_mul(const uint64_t* a, const uint64_t* b, uint64_t* o, size_t n) {
     for (size_t i = 0; i < n; ++i) reinterpret_cast<Fp*>(o)[i] = reinterpret_cast<const Fp*>(a)[i] * reinterpret_cast<const Fp*>(b)[i];
 }

@@ -27,6 +27,16 @@ def test_field_mul_host_path(model, cref):
     assert np.array_equal(out, cref.fp_mul(a, b))
 
 
+def test_field_inverse_host_path(model, cref):
+    rng = np.random.default_rng(2)
+    a = rand_field(rng, 20)
+    out = np.empty_like(a)
+    model.model_fr_inv(_p(a), _p(out), ctypes.c_size_t(20))
+    assert cref.mont_to_ints(out, B.R) == [pow(x, -1, B.R) for x in cref.mont_to_ints(a, B.R)]
+    model.model_fp_inv(_p(a), _p(out), ctypes.c_size_t(20))
+    assert cref.mont_to_ints(out, B.P) == [pow(x, -1, B.P) for x in cref.mont_to_ints(a, B.P)]
+
+
 @pytest.mark.parametrize("log_n,tl,smax", [(1, 12, 12), (3, 12, 12), (5, 3, 3), (6, 3, 2), (7, 4, 3), (9, 4, 2),
                                            (10, 6, 4), (13, 12, 12), (14, 12, 1), (12, 6, 5)])
 @pytest.mark.parametrize("inverse", [0, 1])

@@ -57,6 +57,20 @@ def test_field_mul_host_path(model377):
     assert U.fp_ints(out) == want
 
 
+def test_field_inverse_host_path(model377):
+    """Fermat inverse x^(p-2): both BLS12-377 moduli end in ...00000001, so p - 2 borrows across limbs."""
+    rng = np.random.default_rng(2)
+    a = U.rand_fr(rng, 20)
+    a[0] = U.fr(0)
+    out = np.empty_like(a)
+    model377.model_fr_inv(_p(a), _p(out), ctypes.c_size_t(20))
+    assert U.fr_ints(out) == [pow(x, -1, B.R) if x else 0 for x in U.fr_ints(a)]
+    a = U.rand_fp(rng, 20)
+    out = np.empty_like(a)
+    model377.model_fp_inv(_p(a), _p(out), ctypes.c_size_t(20))
+    assert U.fp_ints(out) == [pow(x, -1, B.P) for x in U.fp_ints(a)]
+
+
 @pytest.mark.parametrize("log_n,tl,smax", [(3, 12, 12), (6, 3, 2), (9, 4, 2), (10, 6, 4)])
 @pytest.mark.parametrize("inverse", [0, 1])
 @pytest.mark.parametrize("dit", [0, 1])

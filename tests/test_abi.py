@@ -29,6 +29,49 @@ def test_library_exports_every_declared_symbol(pkg):
     pkg.load_library()  # binds every prototype the Python mirror uses
 
 
+def test_bls12_377_library_exports_and_identity(pkg):
+    """The second library (make CURVE=bls12_377) exports the same ABI and says which curve it was built for."""
+    lib = ctypes.CDLL(pkg.library_path(pkg.BLS12_377))
+    for n in header_symbols():
+        assert hasattr(lib, n), f"{n} declared in b200prover.h but not exported by the BLS12-377 build"
+    lib377, lib254 = pkg.load_library(pkg.BLS12_377), pkg.load_library()
+    assert (lib377.b200_build_curve(), lib377.b200_build_fp_words()) == (pkg.BLS12_377, 6)
+    assert (lib254.b200_build_curve(), lib254.b200_build_fp_words()) == (pkg.BN254, 4)
+    assert ctypes.sizeof(pkg.api._MSM_OUT[pkg.BLS12_377]) == 8 * (4 * 18 + 36)
+
+
+def test_bls12_377_host_fixups_and_bytes_match_oracle(pkg):
+    """b200_groth16_finalize + b200_groth16_proof_bytes of the BLS12-377 build (pure host code) on MSM results made
+    by the oracle: prove.go:178-321 and marshal.go:41-66 with 48-byte coordinates and three flag bits."""
+    from oracle import bls12_377 as B
+    from oracle.suite377 import groth16 as G3
+    from tests import util377 as U
+    import random
+    rnd = random.Random(5)
+    c = pkg.BLS12_377
+    k = [rnd.randrange(1, B.R) for _ in range(12)]
+    g1 = lambda e: B.g1_mul(B.G1_GEN, e)
+    g2 = lambda e: B.g2_mul(B.G2_GEN, e)
+    jac1 = lambda pt: U.fp_arr([pt[0], pt[1], 1]).reshape(-1)
+    jac2 = lambda pt: U.fp_arr([pt[0][0], pt[0][1], pt[1][0], pt[1][1], 1, 0]).reshape(-1)
+    out = pkg.api._MSM_OUT[c]()
+    for name, e in (("ar", k[0]), ("bs1", k[1]), ("krs", k[2]), ("krs2", k[3])):
+        getattr(out, name)[:] = [int(v) for v in jac1(g1(e))]
+    out.bs2[:] = [int(v) for v in jac2(g2(k[1]))]
+    r, s, alpha, beta, delta = k[4:9]
+    ar, bs, krs = pkg.groth16_finalize(out, U.fr(r), U.fr(s), U.g1_arr([g1(alpha)])[0], U.g1_arr([g1(beta)])[0],
+                                       U.g1_arr([g1(delta)])[0], U.g2_arr([g2(beta)])[0], U.g2_arr([g2(delta)])[0], curve=c)
+    e_ar = (k[0] + alpha + r * delta) % B.R
+    e_bs = (k[1] + beta + s * delta) % B.R
+    e_krs = (k[2] + k[3] - r * s * delta + s * e_ar + r * e_bs) % B.R
+    assert U.g1_aff(ar) == g1(e_ar) and U.g2_aff(bs) == g2(e_bs) and U.g1_aff(krs) == g1(e_krs)
+    raw = pkg.groth16_proof_bytes(ar, bs, krs, curve=c)
+    assert len(raw) == 244 and raw == G3.proof_bytes(g1(e_ar), g2(e_bs), g1(e_krs))
+    inf = np.zeros(12, dtype=np.uint64)
+    raw = pkg.groth16_proof_bytes(inf, np.zeros(24, dtype=np.uint64), inf, curve=c)
+    assert raw == G3.proof_bytes(None, None, None)
+
+
 def test_no_cpu_fallback_without_device(pkg):
     lib = pkg.load_library()
     if lib.b200_device_count() > 0:

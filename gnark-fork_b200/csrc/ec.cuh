@@ -85,7 +85,31 @@ struct Fp2 {
 //   c0 = a0 b0 - a1 b1 + p^2                                   in (0, 2 p^2)
 // both below p * 2^256 * 0.38, the bound mont_reduce_dev needs for a canonical result.
 #if defined(B2_CURVE_BLS12_377)
-__device__ __forceinline__ Fp2 fp2_mul_lazy(const Fp2& a, const Fp2& b) { return a.mul_inline(b); }
+// u^2 = -5:  c0 = a0 b0 - 5 a1 b1 + 5 p^2 in (0, 6 p^2),  c1 = (a0 + a1)(b0 + b1) - a0 b0 - a1 b1 in [0, 2 p^2);
+// 6 p^2 < p * 2^384 (p has 7 spare bits).  3 x 144 + 2 x 156 = 744 MAC32 instead of 3 x 300.
+__device__ __forceinline__ Fp2 fp2_mul_lazy(const Fp2& a, const Fp2& b) {
+    uint32_t t0[24], t1[24], t2[24], sa[12], sb[12];
+    mul_wide_dev12(t0, a.a0.l, b.a0.l);
+    mul_wide_dev12(t1, a.a1.l, b.a1.l);
+    add_chain12(sa, a.a0.l, a.a1.l);
+    add_chain12(sb, b.a0.l, b.a1.l);
+    mul_wide_dev12(t2, sa, sb);
+    sub24_dev(t2, t2, t0);
+    sub24_dev(t2, t2, t1);
+    uint32_t x[24];
+    add24_dev(x, t1, t1);
+    add24_dev(x, x, x);
+    add24_dev(x, x, t1);          // 5 a1 b1 < 5 p^2
+    uint32_t p2[24];
+#pragma unroll
+    for (int i = 0; i < 24; ++i) p2[i] = FpParams::p_squared_x5(i);
+    add24_dev(t0, t0, p2);
+    sub24_dev(t0, t0, x);
+    Fp2 r;
+    mont_reduce_dev12<FpParams>(r.a0.l, t0);
+    mont_reduce_dev12<FpParams>(r.a1.l, t2);
+    return r;
+}
 #else
 __device__ __forceinline__ Fp2 fp2_mul_lazy(const Fp2& a, const Fp2& b) {
     uint32_t t0[16], t1[16], t2[16], sa[8], sb[8];

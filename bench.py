@@ -526,7 +526,8 @@ def bls12_377_section(pkg, device_index, log_n, steps, warmup, peak):
         mac_fp = 12 * 12 * 2 + 12                 # one 12-limb Montgomery product: 288 + 12 MAC32 (300)
         pts = g1["units"] / max(1, g1["launches"])
         model = pts * 16 * 11 * mac_fp / (g1_launch_ms * 1e-3) if g1_launch_ms else 0.0
-        executed = pts * info["a"]["windows"] * 10 * mac_fp / (g1_launch_ms * 1e-3) if g1_launch_ms else 0.0
+        mac_madd = 8 * mac_fp + 2 * 144 + 156     # XYZZ mixed addition: 8 products + a*b - c*d as two wide products and ONE reduction
+        executed = pts * info["a"]["windows"] * mac_madd / (g1_launch_ms * 1e-3) if g1_launch_ms else 0.0
         stage = {k: float(np.mean([t[k] for t in tms])) for k in tms[0]}
         return {"metric": "BLS12-377 Groth16 prove s @2^%d constraints" % log_n, "value": float(np.mean(wall)), "unit": "s", "n_gpus": 1,
                 "steps": steps, "workload": "synthetic 2^%d-constraint Mul-chain-shaped R1CS on BLS12-377: computeH (7 transforms of 2^%d) + "
@@ -538,7 +539,7 @@ def bls12_377_section(pkg, device_index, log_n, steps, warmup, peak):
                                 "model_mac32_per_s": model, "executed_mac32_per_s": executed, "peak_mac32_per_s": peak["mac32_per_s"],
                                 "frac_model": model / peak["mac32_per_s"], "frac_executed": executed / peak["mac32_per_s"],
                                 "note": "model = points x 16 windows x 11 Fp products x 300 MAC32 (SURVEY.md 8(d)); executed = points x the plan's "
-                                        "windows x 10 products (XYZZ mixed addition, two separate reductions for a*b - c*d) x 300 MAC32"},
+                                        "windows x 2844 MAC32 (XYZZ mixed addition: 8 products x 300 + two 144-MAC32 wide products + one 156-MAC32 reduction)"},
                 "msm_plan": {k: info["a"][k] for k in ("c", "windows", "folded")},
                 "gpu_launches_per_proof": int(prof["kernel_launches"] // max(1, steps)), "setup_s": t_setup}
     finally:

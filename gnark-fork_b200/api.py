@@ -124,7 +124,7 @@ class _PkDesc(C.Structure):
         ("g2_b", C.c_void_p), ("n_g2b", C.c_size_t),
         ("infinity_a", C.c_void_p), ("infinity_b", C.c_void_p),
         ("n_wires", C.c_size_t), ("nb_public", C.c_size_t),
-        ("shard_index", C.c_int), ("shard_count", C.c_int), ("presliced", C.c_int),
+        ("shard_index", C.c_int), ("shard_count", C.c_int), ("presliced", C.c_int), ("raw_points", C.c_int),
     ]
 
 
@@ -175,6 +175,8 @@ def load_library(curve: int = BN254):
         "b200_msm_g1": (i, [vp, i, vp, vp, sz, vp]),
         "b200_msm_g2": (i, [vp, i, vp, vp, sz, vp]),
         "b200_bases_upload": (i, [vp, i, i, vp, sz, C.POINTER(vp)]),
+        "b200_bases_upload_raw": (i, [vp, i, i, vp, sz, C.POINTER(vp)]),
+        "b200_points_from_raw": (i, [vp, i, i, vp, sz, vp]),
         "b200_bases_free": (i, [vp, vp]),
         "b200_bases_info": (i, [vp, vp, C.POINTER(_MsmSetInfo)]),
         "b200_msm_resident": (i, [vp, vp, vp, sz, vp]),
@@ -564,6 +566,26 @@ class Context:
         self._check(self.lib.b200_bases_upload(self.h, self.curve, group, _ptr(b), b.shape[0], C.byref(h)))
         return Bases(self, h, b.shape[0], group)
 
+    def _raw(self, raw, n, group):
+        a = np.frombuffer(raw, dtype=np.uint8)
+        want = n * (2 if group == 1 else 4) * 8 * self.fw
+        if a.shape[0] != want:
+            raise ValueError(f"{n} raw group-{group} points are {want} bytes, got {a.shape[0]}")
+        return a
+
+    def points_from_raw(self, raw, n: int, group: int) -> np.ndarray:
+        """gnark-crypto RawEncoding point bytes (a section of a WriteRawTo file) -> (n, 2|4 x fw) affine limbs."""
+        a = self._raw(raw, n, group)
+        out = np.zeros((n, (2 if group == 1 else 4) * self.fw), dtype=np.uint64)
+        self._check(self.lib.b200_points_from_raw(self.h, self.curve, group, _ptr(a) if n else None, n, _ptr(out) if n else None))
+        return out
+
+    def upload_bases_raw(self, raw, n: int, group: int) -> Bases:
+        a = self._raw(raw, n, group)
+        h = C.c_void_p()
+        self._check(self.lib.b200_bases_upload_raw(self.h, self.curve, group, _ptr(a) if n else None, n, C.byref(h)))
+        return Bases(self, h, n, group)
+
     def msm_resident(self, bases: Bases, scalars):
         s = _u64(scalars, (-1, 4))
         out = np.zeros((3 if bases.group == 1 else 6) * self.fw, dtype=np.uint64)
@@ -586,11 +608,15 @@ class Context:
     # -- Groth16
     def groth16_pk_upload(self, *, log_n, generator, coset_gen, g1_a, g1_b, g1_k, g1_z, g2_b, infinity_a,
                           infinity_b, nb_public, shard_index=0, shard_count=1, presliced=False,
-                          full_counts=None) -> Groth16ProvingKey:
+                          full_counts=None, raw_points=False) -> Groth16ProvingKey:
         """presliced=True: the base arrays hold only this shard's point range; full_counts =
         dict(a=, b=, k=, z=) then gives the full lengths of pk.G1.A/B/K/Z."""
-        keep = dict(gen=_u64(generator), cg=_u64(coset_gen), a=_u64(g1_a, (-1, 2 * self.fw)), b=_u64(g1_b, (-1, 2 * self.fw)),
-                    k=_u64(g1_k, (-1, 2 * self.fw)), z=_u64(g1_z, (-1, 2 * self.fw)), g2b=_u64(g2_b, (-1, 4 * self.fw)),
+        if raw_points:      # bytes as ProvingKey.WriteRawTo stores them; converted on the device
+            pts = lambda x, w: np.frombuffer(x, dtype=np.uint8).reshape(-1, 8 * w * self.fw)
+        else:
+            pts = lambda x, w: _u64(x, (-1, w * self.fw))
+        keep = dict(gen=_u64(generator), cg=_u64(coset_gen), a=pts(g1_a, 2), b=pts(g1_b, 2),
+                    k=pts(g1_k, 2), z=pts(g1_z, 2), g2b=pts(g2_b, 4),
                     ia=np.ascontiguousarray(infinity_a, dtype=np.uint8), ib=np.ascontiguousarray(infinity_b, dtype=np.uint8))
         d = _PkDesc()
         d.log_n = log_n
@@ -603,6 +629,7 @@ class Context:
         d.infinity_a, d.infinity_b = _ptr(keep["ia"]), _ptr(keep["ib"])
         d.n_wires, d.nb_public = keep["ia"].shape[0], nb_public
         d.shard_index, d.shard_count, d.presliced = shard_index, shard_count, int(bool(presliced))
+        d.raw_points = int(bool(raw_points))
         if presliced:
             d.n_a, d.n_b, d.n_k, d.n_z = (full_counts[k] for k in ("a", "b", "k", "z"))
             d.n_g2b = d.n_b

@@ -232,18 +232,55 @@ int b200_groth16_compute_h(b200_ctx* ctx, int curve, const uint64_t* a, const ui
 }
 
 // ---- MSM ---------------------------------------------------------------------------------
+// H2D of n points (raw != 0: gnark-crypto RawEncoding bytes, converted in place on the device) into dst
+static int copy_points(b200_ctx* ctx, DevBuf& dst, const void* host, size_t n, int group, int raw) {
+    const size_t bytes = n * (group == 1 ? sizeof(G1Affine) : sizeof(G2Affine));
+    B2_CUDA(ctx, dst.alloc(bytes));
+    if (!bytes) return B200_OK;
+    B2_CUDA(ctx, cudaMemcpyAsync(dst.p, host, bytes, cudaMemcpyHostToDevice, ctx->stream));
+    if (raw) {
+        DevBuf bad;
+        B2_CUDA(ctx, bad.alloc(sizeof(uint32_t)));
+        B2_CUDA(ctx, cudaMemsetAsync(bad.p, 0, sizeof(uint32_t), ctx->stream));
+        B2_TRY(points_from_raw_inplace(ctx, dst.p, n, group, bad.as<uint32_t>()));
+        uint32_t flag = 0;
+        B2_CUDA(ctx, cudaMemcpyAsync(&flag, bad.p, sizeof flag, cudaMemcpyDeviceToHost, ctx->stream));
+        B2_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+        if (flag) return ctx->fail(B200_ERR_ARG, "not a raw-encoded point slice (compressed-form flag or coordinate >= p)");
+    }
+    B2_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return B200_OK;
+}
+
+int b200_points_from_raw(b200_ctx* ctx, int curve, int group, const uint8_t* raw, size_t n, uint64_t* out_affine) {
+    B2_ENTER(ctx, curve);
+    if (n && (!raw || !out_affine)) return ctx->fail(B200_ERR_ARG, "null argument");
+    if (group != 1 && group != 2) return ctx->fail(B200_ERR_ARG, "group must be 1 or 2");
+    DevBuf d;
+    B2_TRY(copy_points(ctx, d, raw, n, group, 1));
+    if (n) B2_CUDA(ctx, cudaMemcpyAsync(out_affine, d.p, d.bytes, cudaMemcpyDeviceToHost, ctx->stream));
+    B2_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return B200_OK;
+}
+
+static int bases_upload_impl(b200_ctx* ctx, int group, const void* host, size_t n, int raw, b200_bases** out);
+
 int b200_bases_upload(b200_ctx* ctx, int curve, int group, const uint64_t* bases_affine, size_t n, b200_bases** out) {
     B2_ENTER(ctx, curve);
-    if (!out || (n && !bases_affine)) return ctx->fail(B200_ERR_ARG, "null argument");
+    return bases_upload_impl(ctx, group, bases_affine, n, 0, out);
+}
+int b200_bases_upload_raw(b200_ctx* ctx, int curve, int group, const uint8_t* raw, size_t n, b200_bases** out) {
+    B2_ENTER(ctx, curve);
+    return bases_upload_impl(ctx, group, raw, n, 1, out);
+}
+
+static int bases_upload_impl(b200_ctx* ctx, int group, const void* host, size_t n, int raw, b200_bases** out) {
+    if (!out || (n && !host)) return ctx->fail(B200_ERR_ARG, "null argument");
     if (group != 1 && group != 2) return ctx->fail(B200_ERR_ARG, "group must be 1 or 2");
     b200_bases* b = new b200_bases();
     b->group = group;
     b->n = n;
-    const size_t bytes = n * (group == 1 ? sizeof(G1Affine) : sizeof(G2Affine));
-    cudaError_t e = b->pts.alloc(bytes);
-    if (e == cudaSuccess && bytes) e = cudaMemcpyAsync(b->pts.p, bases_affine, bytes, cudaMemcpyHostToDevice, ctx->stream);
-    if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
-    if (e != cudaSuccess) { delete b; return ctx->fail(B200_ERR_CUDA, "bases upload", cudaGetErrorString(e)); }
+    { const int st = copy_points(ctx, b->pts, host, n, group, raw); if (st != B200_OK) { delete b; return st; } }
     const int c = ctx->msm_fold_c ? ctx->msm_fold_c : msm_fold_window(n);
     if (ctx->msm_precompute && n >= 4096 && c != 0) {
         DevBuf table;

@@ -4,6 +4,7 @@
 // fix-ups (prove.go:178-321) and Proof.WriteTo (marshal.go:41-66) for callers without Go.
 #include <algorithm>
 #include "groth16_host.cuh"
+#include "misc_host.cuh"
 
 namespace b200 {
 
@@ -26,13 +27,18 @@ static void shard_range_z(size_t n_z, unsigned log_n, int idx, int cnt, size_t* 
     }
 }
 
+// raw: the host bytes are gnark-crypto RawEncoding points (a section of a WriteRawTo file, marshal.go:246-304); same
+// size per point as the Affine struct, converted in place after the copy.  *bad collects format violations.
 template <class T>
-static int upload_range(b200_ctx* ctx, DevBuf& dst, const uint64_t* host, size_t lo, size_t hi, bool presliced) {
+static int upload_range(b200_ctx* ctx, DevBuf& dst, const uint64_t* host, size_t lo, size_t hi, bool presliced, bool raw = false,
+                        uint32_t* d_bad = nullptr) {
     const size_t cnt = hi - lo;
     B2_CUDA(ctx, dst.alloc(cnt * sizeof(T)));
-    if (cnt)
+    if (cnt) {
         B2_CUDA(ctx, cudaMemcpyAsync(dst.p, reinterpret_cast<const char*>(host) + (presliced ? 0 : lo) * sizeof(T), cnt * sizeof(T),
                                      cudaMemcpyHostToDevice, ctx->stream));
+        if (raw) B2_TRY(points_from_raw_inplace(ctx, dst.p, cnt, sizeof(T) == sizeof(G1Affine) ? 1 : 2, d_bad));
+    }
     return B200_OK;
 }
 
@@ -114,14 +120,27 @@ int groth16_pk_upload(b200_ctx* ctx, const b200_groth16_pk_desc* d, b200_groth16
         if (w_hi < w_lo) w_lo = w_hi = 0;
         pk->w_lo = w_lo; pk->w_hi = w_hi;
     }
-    if (st == B200_OK) st = upload_range<G1Affine>(ctx, pk->A, d->g1_a, a_lo, a_hi, ps);
+    const bool raw = d->raw_points != 0;
+    DevBuf bad;
+    if (st == B200_OK && raw) {
+        if (bad.alloc(sizeof(uint32_t)) != cudaSuccess || cudaMemsetAsync(bad.p, 0, sizeof(uint32_t), ctx->stream) != cudaSuccess)
+            st = ctx->fail(B200_ERR_CUDA, "pk upload");
+    }
+    uint32_t* d_bad = raw ? bad.as<uint32_t>() : nullptr;
+    if (st == B200_OK) st = upload_range<G1Affine>(ctx, pk->A, d->g1_a, a_lo, a_hi, ps, raw, d_bad);
     if (st == B200_OK) st = upload_wire_map(ctx, pk->mapA, wa, a_lo, a_hi, (uint32_t)pk->w_lo);
-    if (st == B200_OK) st = upload_range<G1Affine>(ctx, pk->B, d->g1_b, b_lo, b_hi, ps);
-    if (st == B200_OK) st = upload_range<G2Affine>(ctx, pk->G2B, d->g2_b, b_lo, b_hi, ps);
+    if (st == B200_OK) st = upload_range<G1Affine>(ctx, pk->B, d->g1_b, b_lo, b_hi, ps, raw, d_bad);
+    if (st == B200_OK) st = upload_range<G2Affine>(ctx, pk->G2B, d->g2_b, b_lo, b_hi, ps, raw, d_bad);
     if (st == B200_OK) st = upload_wire_map(ctx, pk->mapB, wb, b_lo, b_hi, (uint32_t)pk->w_lo);
-    if (st == B200_OK) st = upload_range<G1Affine>(ctx, pk->K, d->g1_k, pk->k_lo, pk->k_lo + pk->n_k, ps);
+    if (st == B200_OK) st = upload_range<G1Affine>(ctx, pk->K, d->g1_k, pk->k_lo, pk->k_lo + pk->n_k, ps, raw, d_bad);
     if (st == B200_OK) { shard_range_z(d->n_z, d->log_n, si, sc, &lo, &hi); pk->n_z = hi - lo; pk->z_lo = lo;
-        st = upload_range<G1Affine>(ctx, pk->Z, d->g1_z, lo, hi, ps); }
+        st = upload_range<G1Affine>(ctx, pk->Z, d->g1_z, lo, hi, ps, raw, d_bad); }
+    if (st == B200_OK && raw) {
+        uint32_t flag = 0;
+        if (cudaMemcpyAsync(&flag, bad.p, sizeof flag, cudaMemcpyDeviceToHost, ctx->stream) != cudaSuccess ||
+            cudaStreamSynchronize(ctx->stream) != cudaSuccess) st = ctx->fail(B200_ERR_CUDA, "pk upload");
+        else if (flag) st = ctx->fail(B200_ERR_ARG, "raw_points: a base array is not raw-encoded (compressed-form flag or coordinate >= p)");
+    }
     if (st == B200_OK && cudaStreamSynchronize(ctx->stream) != cudaSuccess) st = ctx->fail(B200_ERR_CUDA, "pk upload");
     // Folded tables take what is left after the prover's own working set: the domain tables (built
     // below), a/b/c/W, and the largest MSM scratch.  G2 first: it gains the most per byte.

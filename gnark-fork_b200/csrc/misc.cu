@@ -181,4 +181,81 @@ int batch_mul_g2(b200_ctx* ctx, const G2Affine& base, const Fr* d_scalars, size_
     return batch_mul_impl<Fp2>(ctx, base, d_scalars, n, d_out);
 }
 
+
+// ---------------------------------------------------------------------------------------------------------
+// On-disk point format -> device layout (the data format in front of the path).
+// ProvingKey.WriteRawTo (/root/reference/backend/groth16/bn254/marshal.go:246-304) stores every point slice with
+// gnark-crypto's RawEncoding: X || Y (G2: X.A1 || X.A0 || Y.A1 || Y.A0), each coordinate FP_BYTES big-endian
+// CANONICAL bytes; the top bits of byte 0 are flags: 00 = uncompressed, 01 = infinity (rest zero); anything else is
+// a compressed form and is refused.  One thread per point: the point's bytes are read as words, byte-swapped into
+// little-endian limbs, brought into Montgomery form (x * R^2 / R) and written back over the same bytes -- the raw
+// point and the Affine struct have the same size, so a file section DMA'd to the device becomes the base array.
+// HBM-bound: sizeof(Affine) read + written per point, 300 (G1) / 600 (G2) MAC32 on BN254.
+// ---------------------------------------------------------------------------------------------------------
+#if defined(B2_CURVE_BLS12_377)
+constexpr uint32_t RAW_FLAG_MASK = 0xE0000000u, RAW_FLAG_INF = 0x40000000u;   // three flag bits on the BLS curves
+#else
+constexpr uint32_t RAW_FLAG_MASK = 0xC0000000u, RAW_FLAG_INF = 0x40000000u;   // two on BN254
+#endif
+
+template <int COORDS>
+__global__ void __launch_bounds__(128) points_from_raw_kernel(uint32_t* __restrict__ pts, size_t n, uint32_t* __restrict__ bad) {
+    constexpr int NL = Fp::N;
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    uint32_t* p = pts + i * (size_t)(COORDS * NL);
+    uint32_t w[COORDS * NL];
+#pragma unroll
+    for (int k = 0; k < COORDS * NL / 4; ++k) {
+        const uint4 v = reinterpret_cast<const uint4*>(p)[k];
+        w[4 * k] = v.x; w[4 * k + 1] = v.y; w[4 * k + 2] = v.z; w[4 * k + 3] = v.w;
+    }
+    // word 0 holds byte 0 in its LOW byte (little-endian load of big-endian data): swap first
+    const uint32_t first = __byte_perm(w[0], 0, 0x0123);
+    const uint32_t flags = first & RAW_FLAG_MASK;
+    Fp c[COORDS];
+    bool is_bad = flags != 0 && flags != RAW_FLAG_INF;
+    const bool inf = flags == RAW_FLAG_INF;
+#pragma unroll
+    for (int k = 0; k < COORDS; ++k) {
+        Fp x;
+#pragma unroll
+        for (int j = 0; j < NL; ++j) x.l[j] = __byte_perm(w[k * NL + (NL - 1 - j)], 0, 0x0123);
+        if (k == 0) x.l[NL - 1] &= ~RAW_FLAG_MASK;
+        // canonical input required: x < p
+        bool lt = false, decided = false;
+#pragma unroll
+        for (int j = NL - 1; j >= 0; --j) {
+            const uint32_t pj = FpParams::p(j);
+            if (!decided && x.l[j] != pj) { lt = x.l[j] < pj; decided = true; }
+        }
+        is_bad |= !lt;
+        if (inf && !x.is_zero()) is_bad = true;
+        c[k] = x.to_mont();
+    }
+    if (inf || is_bad) {
+#pragma unroll
+        for (int k = 0; k < COORDS; ++k) c[k] = Fp::zero();
+    }
+    if (is_bad && bad) atomicOr(bad, 1u);
+    // G1: X, Y.  G2 on disk: X.A1, X.A0, Y.A1, Y.A0 -> memory: X.A0, X.A1, Y.A0, Y.A1
+#pragma unroll
+    for (int k = 0; k < COORDS; ++k) {
+        const int dst = COORDS == 4 ? (k ^ 1) : k;
+#pragma unroll
+        for (int q = 0; q < NL / 4; ++q)
+            reinterpret_cast<uint4*>(p + dst * NL)[q] = make_uint4(c[k].l[4 * q], c[k].l[4 * q + 1], c[k].l[4 * q + 2], c[k].l[4 * q + 3]);
+    }
+}
+
+int points_from_raw_inplace(b200_ctx* ctx, void* d_points, size_t n, int group, uint32_t* d_bad) {
+    if (n == 0) return B200_OK;
+    const unsigned blocks = (unsigned)((n + 127) / 128);
+    if (group == 1) points_from_raw_kernel<2><<<blocks, 128, 0, ctx->stream>>>((uint32_t*)d_points, n, d_bad);
+    else points_from_raw_kernel<4><<<blocks, 128, 0, ctx->stream>>>((uint32_t*)d_points, n, d_bad);
+    B2_CUDA(ctx, cudaGetLastError());
+    ctx->n_launches++;
+    return B200_OK;
+}
+
 }  // namespace b200

@@ -394,8 +394,10 @@ static __global__ void msm_order_fill_kernel(const uint32_t* __restrict__ task_b
 
 // one thread per task (taken in size order); a single-task bucket is written straight to
 // buckets[], the pieces of a split bucket go to partials[task] and are merged by msm_combine_kernel.
+// resident blocks asked of ptxas: 12-limb Fp (48 B) is capped at 168 registers so that 3 blocks = 12 warps stay resident
+// (188 registers / 2 blocks left the IMAD chains' fixed latency exposed: ncu 'wait' stall 3.1 warps per issue, r01_bls377_*)
 template <class F>
-__global__ void __launch_bounds__(128, (sizeof(F) > 32 ? 2 : 1)) msm_accumulate_kernel(const Affine<F>* __restrict__ bases, const uint32_t* __restrict__ sorted,
+__global__ void __launch_bounds__(128, (sizeof(F) == 48 ? 3 : sizeof(F) > 32 ? 2 : 1)) msm_accumulate_kernel(const Affine<F>* __restrict__ bases, const uint32_t* __restrict__ sorted,
                                       const uint32_t* __restrict__ offsets, const uint32_t* __restrict__ counts,
                                       const uint32_t* __restrict__ task_bucket, const uint32_t* __restrict__ task_off,
                                       const uint32_t* __restrict__ ntasks, const uint32_t* __restrict__ order, uint32_t max_tasks,

@@ -174,6 +174,16 @@ int b200_msm_g2(b200_ctx *ctx, int curve, const uint64_t *scalars, const uint64_
  * group = 1 (G1) or 2 (G2). */
 int b200_bases_upload(b200_ctx *ctx, int curve, int group, const uint64_t *bases_affine, size_t n,
                       b200_bases **out);
+/* The same from the ON-DISK form of a point slice: `raw` = n points as gnark-crypto's RawEncoding writes them
+ * (curve.NewEncoder(w, curve.RawEncoding()), used by ProvingKey.WriteRawTo, groth16/bn254/marshal.go:246-304, and
+ * decoded point by point on the CPU by ReadFrom / UnsafeReadFrom, marshal.go:319-374): X || Y, each coordinate
+ * 8*B200_FP_WORDS big-endian canonical bytes (G2: X.A1 || X.A0 || Y.A1 || Y.A0); top bits of byte 0 = 00, or 01 for
+ * the point at infinity (rest zero).  The bytes are copied as they are and converted on the device (byte order,
+ * Montgomery form, G2 coordinate order); no curve or subgroup check (UnsafeReadFrom semantics).  A compressed-form
+ * flag or a coordinate >= p fails with B200_ERR_ARG.  b200_points_from_raw returns the converted points in the
+ * in-memory layout (n x G1Affine / G2Affine) instead of keeping them. */
+int b200_bases_upload_raw(b200_ctx *ctx, int curve, int group, const uint8_t *raw, size_t n, b200_bases **out);
+int b200_points_from_raw(b200_ctx *ctx, int curve, int group, const uint8_t *raw, size_t n, uint64_t *out_affine);
 int b200_bases_free(b200_ctx *ctx, b200_bases *bases);
 /* How a resident base set is laid out and which Pippenger plan its MSMs run (for roofline
  * accounting: a launch performs n * windows bucket additions). */
@@ -227,6 +237,11 @@ typedef struct b200_groth16_pk_desc {
     int shard_index, shard_count; /* 0,1 for a single GPU                                      */
     int presliced;                /* non-zero: every base pointer already addresses the first
                                      element of this shard's range (counts stay the full ones)  */
+    int raw_points;               /* non-zero: the five base pointers address gnark-crypto RawEncoding
+                                     bytes -- sections of a ProvingKey.WriteRawTo file
+                                     (groth16/bn254/marshal.go:246-304) -- instead of in-memory
+                                     limbs; same size per point, converted on the device
+                                     (see b200_points_from_raw)                                 */
 } b200_groth16_pk_desc;
 
 int b200_groth16_pk_upload(b200_ctx *ctx, int curve, const b200_groth16_pk_desc *desc, b200_groth16_pk **out);

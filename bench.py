@@ -352,6 +352,9 @@ def gpu_arm(args):
         return float(t.item())
 
     peak = ctx.imad_peak()
+    for kv in args.opt:
+        k, v = kv.split("=")
+        ctx.set_option(k, int(v))
     inst = Instance(args.log_n, rank, world)
     t_setup = time.perf_counter()
     pk = inst.build_key(ctx)
@@ -596,7 +599,7 @@ def plonk_section(pkg, ctx, log_n, steps, warmup, dist=None, rank=0, world=1, de
     mean_stage = {k: float(np.mean([s[k] for s in stages])) for k in stages[0]}
     msm_ms = sum(mean_stage[k] for k in ("commit_lro_ms", "commit_z_ms", "commit_h_ms", "batch_open_ms")) + mean_stage["linearize_ms"]
     return {"metric": "BN254 PlonK prove ms @2^%d gates" % log_n, "value": ms, "unit": "ms", "n_gpus": world, "steps": steps,
-            "workload": "SCS Mul chain filling 2^%d rows, big domain 2^%d; 10 KZG commitments (G1 MSM of ~2^%d against 2 resident SRS), "
+            "workload": "SCS Mul chain filling 2^%d rows, big domain 2^%d; 9 KZG commitments as G1 MSMs of ~2^%d against 2 resident SRS (+ the linearised digest as a 7-point host combination), "
                         "%d transforms of 2^%d + 1 of 2^%d, fresh blinding per proof" % (log_n, d.log_big, log_n, 5 + 5 * (d.big // n), log_n, d.log_big),
             "path": "b200_plonk_prove (page-locked host L, R, O in; proof out; Fiat-Shamir on the host)" if world == 1 else
                     "b200_plonk_session_* phases on %d ranks: commitments sharded by SRS point range (96-byte partial sums all-gathered, host add), "
@@ -698,6 +701,7 @@ def main():
     ap.add_argument("--plonk-log-n", type=int, default=22, help="also time BN254 PlonK Prove at 2^k gates (config 4; sharded over the ranks at N > 1); 0 = skip")
     ap.add_argument("--bls12-377-log-n", type=int, default=22, help="N = 1: also time BLS12-377 Groth16 Prove at 2^k constraints (config 5) through libb200prover_bls12377.so; 0 = skip")
     ap.add_argument("--plonk-dist", action="store_true", help="N > 1: run the sharded PlonK proof too (off by default: the scaling run stays the Groth16 line only)")
+    ap.add_argument("--opt", action="append", default=[], metavar="KEY=VALUE", help="b200_set_option before the key is built (tuning sweeps only; the default run sets none)")
     ap.add_argument("--no-check", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--replicate-h", action="store_true", help="N > 1: every rank runs the whole computeH (no exchange)")

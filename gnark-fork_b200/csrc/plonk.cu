@@ -15,6 +15,7 @@
 // Fiat-Shamir (SHA-256) and the O(1) group arithmetic (blinding commitments, folded digests) run on the host,
 // as in the reference.
 #include <chrono>
+#include <future>
 #include <memory>
 #include <cstdio>
 #include "host_group.cuh"
@@ -715,6 +716,7 @@ int phase4(b200_ctx* ctx, b200_plonk_session& S, const uint64_t* totals, uint64_
     B2_TRY(fr_poly_eval(ctx, pk->tr(TR_S2), n, zeta, &S.s2z));
     for (uint32_t k = 0; k < S.nb; ++k) B2_TRY(fr_poly_eval(ctx, pk->qcp_c(k), n, zeta, &S.qcpz[k]));     // prove.go:724-729
     S.lin = S.tmp[2];
+    Fr lin_s1, lin_s2;      // scalars of [S3] and [Z] in the linearised polynomial's digest
     {
         const Fr &blz = S.blz, &brz = S.brz, &boz = S.boz;
         PlonkLinArgs a;
@@ -733,14 +735,35 @@ int phase4(b200_ctx* ctx, b200_plonk_session& S, const uint64_t* totals, uint64_
         a.n = (uint32_t)n; a.len = (uint32_t)(n + 3);
         a.out = S.lin;
         B2_TRY(plonk_linearize(ctx, a));
+        lin_s1 = a.c1 * alpha;
+        lin_s2 = a.c2 * alpha + a.lag;
     }
-    // [quotient of the Z opening] and [linearised polynomial]: independent, committed as one pipelined pair
-    const Fr* sc[2] = {S.quot, S.lin};
-    const size_t cnt[2] = {n + 2, n + 3};
-    G1XYZZ c[2];
-    B2_TRY(commit_shard(ctx, pk->srs, pk->srs_lo_idx, pk->srs_hi_idx, sc, cnt, 2, c));
+    // The digest of the linearised polynomial.  The reference commits the polynomial with a full-size MultiExp
+    // (kzg.Commit, prove.go:769); commitments are linear, so the same group element is the 7 + nb point combination
+    // the VERIFIER forms from the key's and the proof's commitments (verify.go:210-250):
+    //   l [Ql] + r [Qr] + r l [Qm] + o [Qo] + [Qk] + sum_i qcp_i(zeta) [Bsb22_i] + s1 [S3] + s2 [Z]
+    // It runs on a host thread under the one MSM this phase still needs (the quotient of the Z opening); every
+    // rank of a sharded proof computes it, rank 0 reports it as its partial sum.
+    auto digest = std::async(std::launch::async, [&S, pk, lin_s1, lin_s2]() {
+        const G1Affine* vk = pk->vk_pts;   // S1 S2 S3 Ql Qr Qm Qo Qk
+        G1XYZZ acc = G1XYZZ::from_affine(vk[7]);
+        acc.add(scalar_mul(G1XYZZ::from_affine(vk[3]), S.blz));
+        acc.add(scalar_mul(G1XYZZ::from_affine(vk[4]), S.brz));
+        acc.add(scalar_mul(G1XYZZ::from_affine(vk[5]), S.brz * S.blz));
+        acc.add(scalar_mul(G1XYZZ::from_affine(vk[6]), S.boz));
+        for (uint32_t k = 0; k < S.nb; ++k) acc.add(scalar_mul(G1XYZZ::from_affine(S.bsb_com[k]), S.qcpz[k]));
+        acc.add(scalar_mul(G1XYZZ::from_affine(vk[2]), lin_s1));
+        acc.add(scalar_mul(G1XYZZ::from_affine(S.z_com), lin_s2));
+        return acc;
+    });
+    const Fr* sc[1] = {S.quot};
+    const size_t cnt[1] = {n + 2};
+    G1XYZZ c[1];
+    const int st_commit = commit_shard(ctx, pk->srs, pk->srs_lo_idx, pk->srs_hi_idx, sc, cnt, 1, c);
+    const G1XYZZ lin_digest = digest.get();      // join before any early return: the task holds references
+    B2_TRY(st_commit);
     put_jac(partials, c[0]);
-    put_jac(partials + 12, c[1]);
+    put_jac(partials + 12, pk->shard_index == 0 ? lin_digest : G1XYZZ::inf());
     S.lap(S.T.linearize_ms);
     return B200_OK;
 }

@@ -372,7 +372,8 @@ int b200_groth16_finalize(const b200_groth16_out *msm, const uint64_t *r, const 
                           uint64_t *bs_affine, uint64_t *krs_affine);
 
 /* Proof.WriteTo without commitments (marshal.go:41-66): compressed Ar | Bs | Krs | u32 0 | Pok=inf.
- * out must hold 164 bytes; returns the number of bytes written or a negative status. */
+ * out must hold 5 * 8 * B200_FP_WORDS + 4 bytes (164 on BN254, 244 on BLS12-377); returns the number of bytes written
+ * or a negative status. */
 int b200_groth16_proof_bytes(const uint64_t *ar_affine, const uint64_t *bs_affine, const uint64_t *krs_affine,
                              uint8_t *out, size_t out_cap);
 
@@ -380,7 +381,8 @@ int b200_groth16_proof_bytes(const uint64_t *ar_affine, const uint64_t *bs_affin
  * plonk_bn254.Prove (/root/reference/backend/plonk/bn254/prove.go:116-180) behind one call, with or
  * without BSB22 commitments (api.Commit circuits, at most B200_PLONK_MAX_BSB22 of them).  The solver stays
  * with the caller (prove.go:365-392 gives L, R, O); everything after it
- * runs here: the ten KZG commitments (G1 MSMs against two resident SRS), the copy-constraint ratio,
+ * runs here: nine KZG commitments as G1 MSMs against two resident SRS (the tenth, the linearised polynomial's, is formed from
+ * existing commitments as the verifier does, verify.go:210-250), the copy-constraint ratio,
  * the quotient over the rho cosets of the big domain, the openings, and the Fiat-Shamir transcript
  * (SHA-256, host) that orders them. */
 typedef struct b200_plonk_pk b200_plonk_pk;

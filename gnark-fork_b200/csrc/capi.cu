@@ -595,6 +595,7 @@ int b200_set_option(b200_ctx* ctx, const char* key, long value) {
     else if (k == "ntt_strided_stages") { if (value < 1 || value > 12) return ctx->fail(B200_ERR_ARG, "ntt_strided_stages out of range"); ctx->ntt_strided_stages = (int)value; }
     else if (k == "msm_ba") { if (value < 0 || value > 6) return ctx->fail(B200_ERR_ARG, "msm_ba out of range"); ctx->msm_ba = (int)value; }
     else if (k == "msm_ba_force") { ctx->msm_ba_force = value ? 1 : 0; }
+    else if (k == "msm_acc_smem") { ctx->msm_acc_smem = (int)(value & 3); }
     else if (k == "msm_overlap") { ctx->msm_overlap = value ? 1 : 0; }
     else if (k == "msm_precompute") { ctx->msm_precompute = value ? 1 : 0; }
     else if (k == "msm_fold_c") { if (value != 0 && (value < 8 || value > 24)) return ctx->fail(B200_ERR_ARG, "msm_fold_c out of range"); ctx->msm_fold_c = (int)value; }

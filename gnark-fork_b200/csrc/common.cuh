@@ -67,6 +67,13 @@ struct b200_ctx {
         if (detail) { err += ": "; err += detail; }
         return status;
     }
+    // bucket accumulation with the running sum in shared memory (msm_accumulate_smem_kernel): bit 0 = G1, bit 1 = G2.
+    // BN254: G2 only (-10 % on the kernel; G1 already runs 4 blocks of 112 registers).  BLS12-377: off (measured, msm.cuh).
+#if defined(B2_CURVE_BLS12_377)
+    int msm_acc_smem = 0;
+#else
+    int msm_acc_smem = 2;
+#endif
 };
 
 #define B2_CUDA(ctx, call)                                                                     \

@@ -422,6 +422,83 @@ __global__ void __launch_bounds__(128, (sizeof(F) == 48 ? 3 : sizeof(F) > 32 ? 2
     st_vec(nt == 1 ? buckets + b : partials + t, acc);
 }
 
+// The same with the running bucket sum kept in SHARED memory (word-interleaved across the block: word k of thread t
+// at smem[k * 128 + t], conflict-free).  For Fp2 the XYZZ accumulator alone is 64 registers (96 on BLS12-377) that stay
+// live through the whole addition; here each coordinate is loaded where the formula uses it and stored as soon as its
+// new value exists, so the live set is P, R, PP, PPP, Q and one operand.  Option msm_acc_smem: bit 0 = G1, bit 1 = G2.
+template <class F> struct FieldWords { static constexpr int N = F::N; B2_D static uint32_t& w(F& x, int k) { return x.l[k]; } };
+template <> struct FieldWords<Fp2> {
+    static constexpr int N = 2 * Fp::N;
+    B2_D static uint32_t& w(Fp2& x, int k) { return k < Fp::N ? x.a0.l[k] : x.a1.l[k - Fp::N]; }
+};
+template <class F>
+struct SmemPoint {
+    static constexpr int FW = FieldWords<F>::N;
+    uint32_t* base;     // &smem[threadIdx.x]
+    B2_D F ld(int field) const {
+        F r;
+#pragma unroll
+        for (int k = 0; k < FW; ++k) FieldWords<F>::w(r, k) = base[(field * FW + k) * 128];
+        return r;
+    }
+    B2_D void st(int field, F v) const {
+#pragma unroll
+        for (int k = 0; k < FW; ++k) base[(field * FW + k) * 128] = FieldWords<F>::w(v, k);
+    }
+};
+
+// Resident blocks asked of ptxas.  Measured on BN254 G2 at 2^22 (scripts/g2_smem_ab.py; register kernel 26.4 ms):
+// 2 blocks (248 registers, no spill) 25.9 ms, 3 (168 + 264 B stack) 24.5, 4 (128 + 392 B) 23.75, 5 (96 + 568 B) 24.3,
+// 6 (80 + 656 B) 25.0 -- the Fp2 products are out-of-line calls, so the spills sit at call boundaries and 16 warps hide
+// them.  On BLS12-377 G2 (96-byte field) nothing is gained (2 blocks 67.9 vs 68.1 ms, 3 blocks 70.2): the option is off.
+template <class F> constexpr int msm_smem_blocks() { return sizeof(F) >= 96 ? 2 : 4; }
+template <class F>
+__global__ void __launch_bounds__(128, msm_smem_blocks<F>()) msm_accumulate_smem_kernel(const Affine<F>* __restrict__ bases, const uint32_t* __restrict__ sorted,
+                                      const uint32_t* __restrict__ offsets, const uint32_t* __restrict__ counts,
+                                      const uint32_t* __restrict__ task_bucket, const uint32_t* __restrict__ task_off,
+                                      const uint32_t* __restrict__ ntasks, const uint32_t* __restrict__ order, uint32_t max_tasks,
+                                      uint32_t chunk, XYZZ<F>* __restrict__ buckets, XYZZ<F>* __restrict__ partials, uint32_t direct) {
+    __shared__ uint32_t sm[4 * FieldWords<F>::N * 128];
+    const uint32_t slot = blockIdx.x * blockDim.x + threadIdx.x;
+    if (slot >= max_tasks) return;
+    const uint32_t t = order[slot];
+    const uint32_t b = task_bucket[t];
+    if (b == 0xffffffffu) return;
+    const uint32_t nt = ntasks[b];
+    uint32_t first, cnt;
+    msm_task_range(counts[b], nt, t - task_off[b], &first, &cnt);
+    const uint32_t start = offsets[b] + first;
+    const SmemPoint<F> acc{sm + threadIdx.x};
+    enum { X = 0, Y = 1, ZZ = 2, ZZZ = 3 };
+    bool inf = true;
+    for (uint32_t j = 0; j < cnt; ++j) {
+        const uint32_t e = direct ? start + j : sorted[start + j];
+        Affine<F> q = ldg_vec(bases + (e & 0x7fffffffu));
+        if (e >> 31) q.y = q.y.neg();
+        if (q.is_inf()) continue;
+        if (inf) { acc.st(X, q.x); acc.st(Y, q.y); acc.st(ZZ, F::one()); acc.st(ZZZ, F::one()); inf = false; continue; }
+        const F P = q.x * acc.ld(ZZ) - acc.ld(X);
+        const F R = q.y * acc.ld(ZZZ) - acc.ld(Y);
+        if (P.is_zero()) {
+            if (R.is_zero()) {
+                const XYZZ<F> d = XYZZ<F>::dbl_affine(q);
+                inf = d.is_inf();
+                acc.st(X, d.X); acc.st(Y, d.Y); acc.st(ZZ, d.ZZ); acc.st(ZZZ, d.ZZZ);
+            } else inf = true;
+            continue;
+        }
+        const F PP = P.sqr(), PPP = P * PP, Q = acc.ld(X) * PP;
+        const F X3 = R.sqr() - PPP - Q.dbl();
+        acc.st(X, X3);
+        acc.st(Y, mul_sub_mul(R, Q - X3, acc.ld(Y), PPP));
+        acc.st(ZZ, acc.ld(ZZ) * PP);
+        acc.st(ZZZ, acc.ld(ZZZ) * PPP);
+    }
+    XYZZ<F> r = XYZZ<F>::inf();
+    if (!inf) { r.X = acc.ld(X); r.Y = acc.ld(Y); r.ZZ = acc.ld(ZZ); r.ZZZ = acc.ld(ZZZ); }
+    st_vec(nt == 1 ? buckets + b : partials + t, r);
+}
+
 template <class F>
 __device__ __forceinline__ XYZZ<F> shfl_down_point(const XYZZ<F>& p, int delta) {
     XYZZ<F> r;

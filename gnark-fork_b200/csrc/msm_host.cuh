@@ -288,6 +288,10 @@ int msm_enqueue_acc(b200_ctx* ctx, const MsmJob<F>& job, cudaStream_t st) {
             acc_offsets = (const uint32_t*)(sb + lay.off_roffsets);
             acc_counts = (const uint32_t*)(sb + lay.off_rcounts);
         }
+        if (((ctx->msm_acc_smem >> (sizeof(F) > sizeof(Fp) ? 1 : 0)) & 1) && bs == 128)
+            msm_accumulate_smem_kernel<F><<<(lay.max_tasks + bs - 1) / bs, bs, 0, st>>>(acc_bases, sorted, acc_offsets, acc_counts, task_bucket, task_off,
+                                                                                     ntasks, order, lay.max_tasks, lay.chunk, buckets, partials, lay.ba ? 1u : 0u);
+        else
         msm_accumulate_kernel<F><<<(lay.max_tasks + bs - 1) / bs, bs, 0, st>>>(acc_bases, sorted, acc_offsets, acc_counts, task_bucket, task_off,
                                                                             ntasks, order, lay.max_tasks, lay.chunk, buckets, partials, lay.ba ? 1u : 0u);
         ctx->prof_end(span, st);

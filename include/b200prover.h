@@ -86,7 +86,9 @@ const char *b200_version(void);
  * automatic), "msm_precompute" (1 = resident base sets get folded-window tables 2^(c w) P_i, W x
  * the base memory, built once at upload; falls back to plain bases when the table does not fit),
  * "msm_fold_c" (window width of the folded path, 0 = automatic), "msm_overlap" (1 = the prove core
- * sorts the next MSM on a second stream while the current one accumulates; 0 = strictly serial), "ntt_tile_log" (log2 of the
+ * sorts the next MSM on a second stream while the current one accumulates; 0 = strictly serial), "msm_acc_smem" (bit 0 /
+ * bit 1: G1 / G2 bucket accumulation keeps its running sum in shared memory; default G2 only on BN254, off on
+ * BLS12-377), "msm_ba" (batched-affine pre-reduction rounds, default 0), "ntt_tile_log" (log2 of the
  * shared-memory tile, 6..12), "ntt_strided_stages" (max stages of a strided NTT pass, 1..12),
  * "ntt_threads" (threads per NTT CTA, power of two). */
 int b200_set_option(b200_ctx *ctx, const char *key, long value);

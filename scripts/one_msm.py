@@ -10,6 +10,8 @@ G1_GEN, G2_GEN = cp.g1_gen, cp.g2_gen
 ctx = pkg.Context(0, curve=cp.id)
 if len(sys.argv) > 3 and int(sys.argv[3]):
     ctx.set_option("msm_ba", int(sys.argv[3]))
+for kv in filter(None, os.environ.get("B200_OPTS", "").split(",")):     # e.g. B200_OPTS=msm_acc_smem=3
+    ctx.set_option(kv.split("=")[0], int(kv.split("=")[1]))
 rng = np.random.default_rng(0)
 n = 1 << log_n
 bh = ctx.upload_bases(ctx.batch_scalar_mul(G1_GEN if group == 1 else G2_GEN, rand_field(rng, n, top_limb=cp.top_limb), group), group)

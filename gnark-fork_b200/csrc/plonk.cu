@@ -16,6 +16,7 @@
 // as in the reference.
 #include <chrono>
 #include <future>
+#include <vector>
 #include <memory>
 #include <cstdio>
 #include "host_group.cuh"
@@ -744,23 +745,27 @@ int phase4(b200_ctx* ctx, b200_plonk_session& S, const uint64_t* totals, uint64_
     //   l [Ql] + r [Qr] + r l [Qm] + o [Qo] + [Qk] + sum_i qcp_i(zeta) [Bsb22_i] + s1 [S3] + s2 [Z]
     // It runs on a host thread under the one MSM this phase still needs (the quotient of the Z opening); every
     // rank of a sharded proof computes it, rank 0 reports it as its partial sum.
-    auto digest = std::async(std::launch::async, [&S, pk, lin_s1, lin_s2]() {
+    // one host task per scalar multiplication (6 + nb of them, ~0.4 ms each): at N > 1 the MSM they hide under is short
+    std::vector<std::future<G1XYZZ>> terms;
+    auto term = [&terms](const G1Affine& p, const Fr& k) {
+        terms.push_back(std::async(std::launch::async, [p, k]() { return scalar_mul(G1XYZZ::from_affine(p), k); }));
+    };
+    {
         const G1Affine* vk = pk->vk_pts;   // S1 S2 S3 Ql Qr Qm Qo Qk
-        G1XYZZ acc = G1XYZZ::from_affine(vk[7]);
-        acc.add(scalar_mul(G1XYZZ::from_affine(vk[3]), S.blz));
-        acc.add(scalar_mul(G1XYZZ::from_affine(vk[4]), S.brz));
-        acc.add(scalar_mul(G1XYZZ::from_affine(vk[5]), S.brz * S.blz));
-        acc.add(scalar_mul(G1XYZZ::from_affine(vk[6]), S.boz));
-        for (uint32_t k = 0; k < S.nb; ++k) acc.add(scalar_mul(G1XYZZ::from_affine(S.bsb_com[k]), S.qcpz[k]));
-        acc.add(scalar_mul(G1XYZZ::from_affine(vk[2]), lin_s1));
-        acc.add(scalar_mul(G1XYZZ::from_affine(S.z_com), lin_s2));
-        return acc;
-    });
+        term(vk[3], S.blz);
+        term(vk[4], S.brz);
+        term(vk[5], S.brz * S.blz);
+        term(vk[6], S.boz);
+        for (uint32_t k = 0; k < S.nb; ++k) term(S.bsb_com[k], S.qcpz[k]);
+        term(vk[2], lin_s1);
+        term(S.z_com, lin_s2);
+    }
     const Fr* sc[1] = {S.quot};
     const size_t cnt[1] = {n + 2};
     G1XYZZ c[1];
     const int st_commit = commit_shard(ctx, pk->srs, pk->srs_lo_idx, pk->srs_hi_idx, sc, cnt, 1, c);
-    const G1XYZZ lin_digest = digest.get();      // join before any early return: the task holds references
+    G1XYZZ lin_digest = G1XYZZ::from_affine(pk->vk_pts[7]);      // + [Qk]
+    for (auto& f : terms) lin_digest.add(f.get());                // joined before any early return
     B2_TRY(st_commit);
     put_jac(partials, c[0]);
     put_jac(partials + 12, pk->shard_index == 0 ? lin_digest : G1XYZZ::inf());

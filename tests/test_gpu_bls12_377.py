@@ -138,7 +138,7 @@ def test_host_group_helpers(pkg):
     assert U.g2_aff(pkg.g2_jac_to_affine(s2, curve=c)) == B.g2_mul(B.G2_GEN, 16)
 
 
-def _key(ctx, nb_mul, seed=7):
+def _key(ctx, nb_mul, seed=7, shard=(0, 1)):
     rnd = random.Random(seed)
     r1cs = G.mul_chain_circuit(nb_mul)
     td = G.Trapdoor(*[rnd.randrange(1, B.R) for _ in range(5)])
@@ -150,7 +150,8 @@ def _key(ctx, nb_mul, seed=7):
     vkpts = [mul1([td.alpha])[0], mul1([td.beta])[0], mul1([td.delta])[0], mul2([td.beta])[0], mul2([td.delta])[0]]
     d = pk.domain
     pkh = ctx.groth16_pk_upload(log_n=d.log_n, generator=U.fr(d.generator), coset_gen=U.fr(d.coset_gen),
-                                infinity_a=pk.infinity_A, infinity_b=pk.infinity_B, nb_public=r1cs.nb_public, **arrs)
+                                infinity_a=pk.infinity_A, infinity_b=pk.infinity_B, nb_public=r1cs.nb_public,
+                                shard_index=shard[0], shard_count=shard[1], **arrs)
     return r1cs, td, pk, vk, pkh, vkpts
 
 
@@ -171,3 +172,27 @@ def test_groth16_trapdoor_proof(ctx377, pkg, nb_mul):
     assert len(raw) == 244 and raw == G.proof_bytes(ear, ebs, ekrs)
     assert tm["total_ms"] > 0
     pkh.free()
+
+
+@pytest.mark.parametrize("shards", [2, 4])
+def test_sharded_partial_sums_combine(ctx377, pkg, shards):
+    """MSM sharding by point range on BLS12-377: the host-combined partial sums of the shards (18- and
+    36-word Jacobian points through b200_g1_jac_add / b200_g2_jac_add of this library) equal the unsharded results."""
+    c = pkg.BLS12_377
+    nb_mul = (1 << 9) - 1
+    w, a, b, cc = G.mul_chain_witness(nb_mul, 3)
+    args = [U.fr_arr(x) for x in (a, b, cc, w)]
+    _, _, _, _, pk_full, _ = _key(ctx377, nb_mul)
+    full = ctx377.groth16_prove_core(pk_full, *args)[0].as_dict()
+    pk_full.free()
+    parts = []
+    for i in range(shards):
+        _, _, _, _, pk_i, _ = _key(ctx377, nb_mul, shard=(i, shards))
+        parts.append(ctx377.groth16_prove_core(pk_i, *args)[0].as_dict())
+        pk_i.free()
+    for k in ("ar", "bs1", "krs", "krs2", "bs2"):
+        add, aff = (pkg.g2_jac_add, pkg.g2_jac_to_affine) if k == "bs2" else (pkg.g1_jac_add, pkg.g1_jac_to_affine)
+        acc = parts[0][k]
+        for p in parts[1:]:
+            acc = add(acc, p[k], curve=c)
+        assert np.array_equal(aff(acc, curve=c), aff(full[k], curve=c)), k

@@ -478,7 +478,13 @@ struct b200_plonk_session {
     b200_plonk_timings T;
     double t_start = 0, t0 = 0;
     cudaEvent_t ev_cp[4] = {nullptr, nullptr, nullptr, nullptr}, ev_t[2] = {nullptr, nullptr};
+    // commitBlindingFactor of L, R, O, Z (prove.go:1159-1172): 2 x (2 + 2 + 2 + 3) host scalar multiplications that depend on
+    // the blinding scalars only -- started as host tasks when the session begins, collected where the commitments are formed
+    std::future<G1XYZZ> blind_com[4];
+    std::future<G1Affine> fh_digest_task;       // the folded-H digest (2 scalar multiplications), phase 4 -> phase 5
     ~b200_plonk_session() {
+        for (auto& f : blind_com) if (f.valid()) f.wait();
+        if (fh_digest_task.valid()) fh_digest_task.wait();
         for (auto e : ev_cp) if (e) cudaEventDestroy(e);
         for (auto e : ev_t) if (e) cudaEventDestroy(e);
     }
@@ -560,7 +566,7 @@ int phase1(b200_ctx* ctx, b200_plonk_session& S, const uint64_t* totals, uint64_
     const Fr* bps[3] = {S.bl(), S.br(), S.bo()};
     for (int k = 0; k < 3; ++k) {
         G1XYZZ c = get_jac(totals + 12 * k);
-        c.add(commit_blinding(pk, bps[k], 2));
+        c.add(S.blind_com[k].valid() ? S.blind_com[k].get() : commit_blinding(pk, bps[k], 2));
         S.lro[k] = c.to_affine();
     }
     // ---- gamma, beta (deriveGammaAndBeta, prove.go:455-485; bindPublicData, verify.go:296-340) -----------
@@ -592,7 +598,7 @@ int phase2(b200_ctx* ctx, b200_plonk_session& S, const uint64_t* totals) {
     NttDomain *d0 = pk->d0, *d1 = pk->d1;
     {
         G1XYZZ c = get_jac(totals);
-        c.add(commit_blinding(pk, S.bz(), 3));
+        c.add(S.blind_com[3].valid() ? S.blind_com[3].get() : commit_blinding(pk, S.bz(), 3));
         S.z_com = c.to_affine();
     }
     for (uint32_t k = 0; k < S.nb; ++k) bind_point(S.fs, "alpha", S.bsb_com[k]);     // deriveAlpha, prove.go:504-512
@@ -703,11 +709,13 @@ int phase4(b200_ctx* ctx, b200_plonk_session& S, const uint64_t* totals, uint64_
     const Fr zn2 = zeta.pow_u64(n + 2);
     S.fh = S.tmp[1];
     B2_TRY(plonk_fold_h(ctx, S.cres, S.cres + (n + 2), S.cres + 2 * (n + 2), zn2, n + 2, S.fh));
-    G1XYZZ fhd = scalar_mul(S.hx[2], zn2);
-    fhd.add(S.hx[1]);
-    fhd = scalar_mul(fhd, zn2);
-    fhd.add(S.hx[0]);
-    S.fh_digest = fhd.to_affine();
+    S.fh_digest_task = std::async(std::launch::async, [h0 = S.hx[0], h1 = S.hx[1], h2 = S.hx[2], zn2]() {   // needed in phase 5
+        G1XYZZ fhd = scalar_mul(h2, zn2);
+        fhd.add(h1);
+        fhd = scalar_mul(fhd, zn2);
+        fhd.add(h0);
+        return fhd.to_affine();
+    });
     // ---- linearised polynomial (computeLinearizedPolynomial, prove.go:708-777,1289-1389) --------------------
     // evaluateBlinded == the blinded polynomial at zeta
     B2_TRY(fr_poly_eval(ctx, S.cn[0], n + 2, zeta, &S.blz));
@@ -779,6 +787,7 @@ int phase5(b200_ctx* ctx, b200_plonk_session& S, const uint64_t* totals, uint64_
     const uint32_t nb = S.nb;
     S.zs_h = get_jac(totals).to_affine();
     S.lin_digest = get_jac(totals + 12).to_affine();
+    if (S.fh_digest_task.valid()) S.fh_digest = S.fh_digest_task.get();
     // ---- batch opening at zeta (batchOpening, prove.go:779-833; kzg.BatchOpenSinglePoint) --------------------
     B2_TRY(fr_poly_eval(ctx, S.fh, n + 2, S.zeta, &S.claimed[0]));
     B2_TRY(fr_poly_eval(ctx, S.lin, n + 3, S.zeta, &S.claimed[1]));
@@ -872,6 +881,11 @@ int b200_plonk_session_begin(b200_ctx* ctx, const b200_plonk_pk* pk, const uint6
     // blinding polynomials (initBlindingPolynomials, prove.go:295-301)
     if (blinding) memcpy(S->bp, blinding, sizeof S->bp);
     else if (os_random_fr(S->bp, 9) != B200_OK) return ctx->fail(B200_ERR_ARG, "no entropy source");
+    for (int k = 0; k < 4; ++k) {
+        const Fr* b = S->bp + 2 * k;
+        const int nb = k < 3 ? 2 : 3;
+        S->blind_com[k] = std::async(std::launch::async, [pk, b, nb]() { return commit_blinding(pk, b, nb); });
+    }
     S->pub.resize(pk->nb_public);
     if (pk->nb_public) memcpy(S->pub.data(), public_witness, pk->nb_public * sizeof(Fr));
     B2_TRY(phase0(ctx, *S, l, r, o, bsb, partials));

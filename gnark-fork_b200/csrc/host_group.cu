@@ -2,6 +2,7 @@
 // fix-ups of /root/reference/backend/groth16/bn254/prove.go:178-321 and Proof.WriteTo
 // (/root/reference/backend/groth16/bn254/marshal.go:41-66).  Pure host code (the portable path of
 // field.cuh); O(1) work per proof, which the reference also keeps on the CPU (icicle.go:306-391).
+#include <future>
 #include "host_group.cuh"
 
 using namespace b200;
@@ -27,25 +28,32 @@ int b200_groth16_finalize(const b200_groth16_out* msm, const uint64_t* r, const 
     memcpy(fr_s.l, s, 32);
     const Fr kr = (fr_r * fr_s).neg();  // _kr = -(r*s), prove.go:187-189
     const G1XYZZ delta = load_aff<Fp>(g1_delta);
+    // The seven scalar multiplications are O(1) work but serial they are ~4 ms of host time inside the end-to-end
+    // step; the four that depend on r, s and the key only start at once on host tasks, s*ar and r*bs1 follow in parallel.
     // deltas = BatchScalarMultiplicationG1(&pk.G1.Delta, {r, s, kr}), prove.go:192
-    const G1XYZZ d_r = scalar_mul(delta, fr_r), d_s = scalar_mul(delta, fr_s), d_kr = scalar_mul(delta, kr);
+    auto f_dr = std::async(std::launch::async, [&]() { return scalar_mul(delta, fr_r); });
+    auto f_ds = std::async(std::launch::async, [&]() { return scalar_mul(delta, fr_s); });
+    auto f_dkr = std::async(std::launch::async, [&]() { return scalar_mul(delta, kr); });
+    auto f_d2s = std::async(std::launch::async, [&]() { return scalar_mul(load_aff<Fp2>(g2_delta), fr_s); });
     // ar = MSM_A + alpha + r*delta, prove.go:219-220
     G1XYZZ ar = load_jac<Fp>(msm->ar);
     ar.add(load_aff<Fp>(g1_alpha));
-    ar.add(d_r);
+    ar.add(f_dr.get());
+    auto f_sar = std::async(std::launch::async, [&]() { return scalar_mul(ar, fr_s); });
     // bs1 = MSM_B + beta + s*delta, prove.go:206-207
     G1XYZZ bs1 = load_jac<Fp>(msm->bs1);
     bs1.add(load_aff<Fp>(g1_beta));
-    bs1.add(d_s);
+    bs1.add(f_ds.get());
+    auto f_rbs = std::async(std::launch::async, [&]() { return scalar_mul(bs1, fr_r); });
     // krs = MSM_K + kr*delta + MSM_Z + s*ar + r*bs1, prove.go:248-271
     G1XYZZ krs = load_jac<Fp>(msm->krs);
-    krs.add(d_kr);
+    krs.add(f_dkr.get());
     krs.add(load_jac<Fp>(msm->krs2));
-    krs.add(scalar_mul(ar, fr_s));
-    krs.add(scalar_mul(bs1, fr_r));
+    krs.add(f_sar.get());
+    krs.add(f_rbs.get());
     // Bs = MSM_B2 + s*delta2 + beta2, prove.go:294-297
     G2XYZZ bs = load_jac<Fp2>(msm->bs2);
-    bs.add(scalar_mul(load_aff<Fp2>(g2_delta), fr_s));
+    bs.add(f_d2s.get());
     bs.add(load_aff<Fp2>(g2_beta));
     const G1Affine a_aff = ar.to_affine(), k_aff = krs.to_affine();
     const G2Affine b_aff = bs.to_affine();

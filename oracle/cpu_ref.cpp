@@ -28,75 +28,77 @@ typedef uint64_t u64;
 typedef unsigned __int128 u128;
 
 // ------------------------------------------------------------------------------------
-// Montgomery field, 4 x u64 limbs. Parameters derived at start-up from the modulus only.
+// Montgomery field, N x u64 limbs (N = 4: BN254 Fp/Fr and BLS12-377 Fr; N = 6: BLS12-377 Fp).
+// Parameters derived at start-up from the modulus only.
 // ------------------------------------------------------------------------------------
+template <int N>
 struct FieldParams {
-    u64 m[4];     // modulus
+    u64 m[N];     // modulus
     u64 inv;      // -m^-1 mod 2^64
-    u64 one[4];   // R mod m
-    u64 r2[4];    // R^2 mod m
+    u64 one[N];   // R mod m
+    u64 r2[N];    // R^2 mod m
 };
 
-static FieldParams FP, FR;
-
-static inline bool geq(const u64* a, const u64* b) {
-    for (int i = 3; i >= 0; --i) {
+template <int N> static inline bool geq(const u64* a, const u64* b) {
+    for (int i = N - 1; i >= 0; --i) {
         if (a[i] != b[i]) return a[i] > b[i];
     }
     return true;
 }
-static inline u64 add4(u64* r, const u64* a, const u64* b) {
+template <int N> static inline u64 addn(u64* r, const u64* a, const u64* b) {
     u128 c = 0;
-    for (int i = 0; i < 4; ++i) { c += (u128)a[i] + b[i]; r[i] = (u64)c; c >>= 64; }
+    for (int i = 0; i < N; ++i) { c += (u128)a[i] + b[i]; r[i] = (u64)c; c >>= 64; }
     return (u64)c;
 }
-static inline u64 sub4(u64* r, const u64* a, const u64* b) {
+template <int N> static inline u64 subn(u64* r, const u64* a, const u64* b) {
     u64 br = 0;
-    for (int i = 0; i < 4; ++i) {
+    for (int i = 0; i < N; ++i) {
         u128 d = (u128)a[i] - b[i] - br;
         r[i] = (u64)d; br = (u64)(d >> 64) & 1;
     }
     return br;
 }
 
-template <const FieldParams& PRM>
+template <int N, const FieldParams<N>& PRM>
 struct Fe {
-    u64 v[4];
-    static Fe zero() { Fe r; memset(r.v, 0, 32); return r; }
-    static Fe one() { Fe r; memcpy(r.v, PRM.one, 32); return r; }
-    bool is_zero() const { return (v[0] | v[1] | v[2] | v[3]) == 0; }
-    bool operator==(const Fe& o) const { return memcmp(v, o.v, 32) == 0; }
+    u64 v[N];
+    static constexpr int LIMBS = N;
+    static Fe zero() { Fe r; memset(r.v, 0, sizeof r.v); return r; }
+    static Fe one() { Fe r; memcpy(r.v, PRM.one, sizeof r.v); return r; }
+    bool is_zero() const { u64 o = 0; for (int i = 0; i < N; ++i) o |= v[i]; return o == 0; }
+    bool operator==(const Fe& o) const { return memcmp(v, o.v, sizeof v) == 0; }
     Fe operator+(const Fe& o) const {
-        Fe r; u64 c = add4(r.v, v, o.v);
-        if (c || geq(r.v, PRM.m)) sub4(r.v, r.v, PRM.m);
+        Fe r; u64 c = addn<N>(r.v, v, o.v);
+        if (c || geq<N>(r.v, PRM.m)) subn<N>(r.v, r.v, PRM.m);
         return r;
     }
     Fe operator-(const Fe& o) const {
-        Fe r; if (sub4(r.v, v, o.v)) add4(r.v, r.v, PRM.m);
+        Fe r; if (subn<N>(r.v, v, o.v)) addn<N>(r.v, r.v, PRM.m);
         return r;
     }
-    Fe neg() const { if (is_zero()) return *this; Fe r; sub4(r.v, PRM.m, v); return r; }
+    Fe neg() const { if (is_zero()) return *this; Fe r; subn<N>(r.v, PRM.m, v); return r; }
     Fe dbl() const { return *this + *this; }
     // CIOS Montgomery product
     Fe operator*(const Fe& o) const {
-        u64 t[6] = {0, 0, 0, 0, 0, 0};
-        for (int i = 0; i < 4; ++i) {
+        u64 t[N + 2];
+        memset(t, 0, sizeof t);
+        for (int i = 0; i < N; ++i) {
             u128 c = 0;
-            for (int j = 0; j < 4; ++j) {
+            for (int j = 0; j < N; ++j) {
                 c += (u128)v[j] * o.v[i] + t[j];
                 t[j] = (u64)c; c >>= 64;
             }
-            c += t[4]; t[4] = (u64)c; t[5] = (u64)(c >> 64);
+            c += t[N]; t[N] = (u64)c; t[N + 1] = (u64)(c >> 64);
             u64 q = t[0] * PRM.inv;
             c = (u128)q * PRM.m[0] + t[0]; c >>= 64;
-            for (int j = 1; j < 4; ++j) {
+            for (int j = 1; j < N; ++j) {
                 c += (u128)q * PRM.m[j] + t[j];
                 t[j - 1] = (u64)c; c >>= 64;
             }
-            c += t[4]; t[3] = (u64)c; t[4] = t[5] + (u64)(c >> 64);
+            c += t[N]; t[N - 1] = (u64)c; t[N] = t[N + 1] + (u64)(c >> 64);
         }
-        Fe r; memcpy(r.v, t, 32);
-        if (t[4] || geq(r.v, PRM.m)) sub4(r.v, r.v, PRM.m);
+        Fe r; memcpy(r.v, t, sizeof r.v);
+        if (t[N] || geq<N>(r.v, PRM.m)) subn<N>(r.v, r.v, PRM.m);
         return r;
     }
     Fe sqr() const { return *this * *this; }
@@ -109,42 +111,66 @@ struct Fe {
         return acc;
     }
     Fe inv() const {  // Fermat
-        u64 e[4]; u64 two[4] = {2, 0, 0, 0};
-        sub4(e, PRM.m, two);
-        return pow(e, 4);
+        u64 e[N]; u64 two[N] = {2};
+        subn<N>(e, PRM.m, two);
+        return pow(e, N);
     }
-    Fe to_mont() const { Fe r2; memcpy(r2.v, PRM.r2, 32); return *this * r2; }
-    Fe from_mont() const { Fe o; memset(o.v, 0, 32); o.v[0] = 1; return *this * o; }
+    Fe to_mont() const { Fe r2; memcpy(r2.v, PRM.r2, sizeof r2.v); return *this * r2; }
+    Fe from_mont() const { Fe o = zero(); o.v[0] = 1; return *this * o; }
     static Fe from_u64(u64 x) { Fe r = zero(); r.v[0] = x; return r.to_mont(); }
 };
 
-static void init_params(FieldParams& p, const u64 m[4]) {
-    memcpy(p.m, m, 32);
+template <int N>
+static void init_params(FieldParams<N>& p, const u64* m) {
+    memcpy(p.m, m, sizeof p.m);
     u64 x = 1;  // Newton: x = m^-1 mod 2^64
     for (int i = 0; i < 6; ++i) x *= 2 - m[0] * x;
     p.inv = (u64)0 - x;
-    // one = 2^256 mod m by 256 modular doublings of 1
-    u64 t[4] = {1, 0, 0, 0};
-    for (int i = 0; i < 512; ++i) {
-        u64 c = add4(t, t, t);
-        if (c || geq(t, m)) sub4(t, t, m);
-        if (i == 255) memcpy(p.one, t, 32);
+    // one = 2^(64 N) mod m by modular doublings of 1; r2 after twice as many
+    u64 t[N] = {1};
+    for (int i = 0; i < 128 * N; ++i) {
+        u64 c = addn<N>(t, t, t);
+        if (c || geq<N>(t, m)) subn<N>(t, t, m);
+        if (i == 64 * N - 1) memcpy(p.one, t, sizeof p.one);
     }
-    memcpy(p.r2, t, 32);
+    memcpy(p.r2, t, sizeof p.r2);
 }
 
+// Curve selection: the default build is BN254; -DORACLE_BLS12_377 builds liboracle377.so (config 5) from the same
+// file -- p, r from /root/reference/std/math/emulated/emparams/emparams.go:123,137, Fp2 = Fp[u]/(u^2 + 5)
+// (/root/reference/std/algebra/native/fields_bls12377/e12.go:79), as the reference generates both curves from one template.
+#if defined(ORACLE_BLS12_377)
+constexpr int FP_LIMBS = 6;
+static const u64 MOD_P[6] = {0x8508c00000000001ULL, 0x170b5d4430000000ULL, 0x1ef3622fba094800ULL,
+                             0x1a22d9f300f5138fULL, 0xc63b05c06ca1493bULL, 0x01ae3a4617c510eaULL};
+static const u64 MOD_R[4] = {0x0a11800000000001ULL, 0x59aa76fed0000001ULL, 0x60b44d1e5c37b001ULL, 0x12ab655e9a2ca556ULL};
+constexpr u64 FP2_NONRESIDUE_NEG = 5;   // u^2 = -5
+constexpr int FR_BITS = 253;
+#else
+constexpr int FP_LIMBS = 4;
 static const u64 MOD_P[4] = {0x3c208c16d87cfd47ULL, 0x97816a916871ca8dULL, 0xb85045b68181585dULL, 0x30644e72e131a029ULL};
 static const u64 MOD_R[4] = {0x43e1f593f0000001ULL, 0x2833e84879b97091ULL, 0xb85045b68181585dULL, 0x30644e72e131a029ULL};
+constexpr u64 FP2_NONRESIDUE_NEG = 1;   // u^2 = -1
+constexpr int FR_BITS = 254;
+#endif
 
-struct Init { Init() { init_params(FP, MOD_P); init_params(FR, MOD_R); } };
+static FieldParams<FP_LIMBS> FP;
+static FieldParams<4> FR;
+
+struct Init { Init() { init_params<FP_LIMBS>(FP, MOD_P); init_params<4>(FR, MOD_R); } };
 static Init g_init;
 
-typedef Fe<FP> Fp;
-typedef Fe<FR> Fr;
+typedef Fe<FP_LIMBS, FP> Fp;
+typedef Fe<4, FR> Fr;
 
-// Fp2 = Fp[u]/(u^2+1)
+// Fp2 = Fp[u]/(u^2 + k), k = FP2_NONRESIDUE_NEG
 struct Fp2 {
     Fp a0, a1;
+    static Fp mul_k(const Fp& x) {   // k * x
+        if (FP2_NONRESIDUE_NEG == 1) return x;
+        Fp x2 = x.dbl(), x4 = x2.dbl();
+        return x4 + x;               // k = 5
+    }
     static Fp2 zero() { return {Fp::zero(), Fp::zero()}; }
     static Fp2 one() { return {Fp::one(), Fp::zero()}; }
     bool is_zero() const { return a0.is_zero() && a1.is_zero(); }
@@ -156,14 +182,11 @@ struct Fp2 {
     Fp2 operator*(const Fp2& o) const {  // Karatsuba
         Fp t0 = a0 * o.a0, t1 = a1 * o.a1;
         Fp t2 = (a0 + a1) * (o.a0 + o.a1);
-        return {t0 - t1, t2 - t0 - t1};
+        return {t0 - mul_k(t1), t2 - t0 - t1};
     }
-    Fp2 sqr() const {
-        Fp t = a0 * a1;
-        return {(a0 + a1) * (a0 - a1), t.dbl()};
-    }
+    Fp2 sqr() const { return *this * *this; }
     Fp2 inv() const {
-        Fp d = (a0.sqr() + a1.sqr()).inv();
+        Fp d = (a0.sqr() + mul_k(a1.sqr())).inv();
         return {a0 * d, a1.neg() * d};
     }
 };
@@ -254,9 +277,7 @@ template <class F>
 static Jac<F> msm(const Fr* scalars_mont, const Aff<F>* bases, size_t n) {
     if (n == 0) return Jac<F>::inf();
     const int c = msm_window(n);
-    const int nwin = (254 + c) / c + 0;  // carry can spill one digit: 254 bits + sign
-    const int W = (254 / c) + 1;
-    (void)nwin;
+    const int W = (FR_BITS / c) + 1;  // signed digits: the carry of the top window is absorbed (r < 2^FR_BITS)
     // signed digits, digit[w*n + i]
     std::vector<int32_t> digits((size_t)W * n);
 #pragma omp parallel for schedule(static)
@@ -272,7 +293,7 @@ static Jac<F> msm(const Fr* scalars_mont, const Aff<F>* bases, size_t n) {
             if (d > (1 << (c - 1))) { d -= (1 << c); carry = 1; }
             digits[(size_t)w * n + i] = d;
         }
-        // r < 2^254 and W*c >= 255 bits => final carry is always absorbed
+        // r < 2^FR_BITS and W*c > FR_BITS bits => final carry is always absorbed
     }
     int nthreads = omp_get_max_threads();
     int chunks = std::max(1, (nthreads + W - 1) / W);

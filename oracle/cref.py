@@ -18,20 +18,36 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 _LIB = None
 
 
+_LIB377 = None
+
+
 def build() -> str:
     subprocess.check_call(["make", "-C", _HERE, "-s"])
     return os.path.join(_HERE, "liboracle.so")
 
 
+def _load(name):
+    path = os.path.join(_HERE, name)
+    if not os.path.exists(path):
+        build()
+    l = ctypes.CDLL(path)
+    l.oracle_max_threads.restype = ctypes.c_int
+    return l
+
+
 def lib():
     global _LIB
     if _LIB is None:
-        path = os.path.join(_HERE, "liboracle.so")
-        if not os.path.exists(path):
-            build()
-        _LIB = ctypes.CDLL(path)
-        _LIB.oracle_max_threads.restype = ctypes.c_int
+        _LIB = _load("liboracle.so")
     return _LIB
+
+
+def lib377():
+    """The same restatement compiled with the BLS12-377 constants (oracle/Makefile): Fr 4 u64, Fp 6 u64."""
+    global _LIB377
+    if _LIB377 is None:
+        _LIB377 = _load("liboracle377.so")
+    return _LIB377
 
 
 def _p(a):
@@ -95,68 +111,85 @@ def g2_array_to_points(a: np.ndarray):
 
 
 # ---- wrapped entry points ---------------------------------------------------------------
-def fr_mul(a: np.ndarray, b: np.ndarray) -> np.ndarray:
-    out = np.empty_like(a)
-    lib().oracle_fr_mul(_p(a), _p(b), _p(out), ctypes.c_size_t(a.shape[0]))
-    return out
+class Oracle:
+    """The C++ restatement of one curve.  fp_words = u64 limbs of a base-field element (4 BN254, 6 BLS12-377);
+    Fr is 4 limbs on both curves."""
+
+    def __init__(self, get_lib, fp_words):
+        self._get, self.fp_words = get_lib, fp_words
+
+    @property
+    def lib(self):
+        return self._get()
+
+    def set_threads(self, n):
+        self.lib.oracle_set_threads(int(n))
+
+    def max_threads(self):
+        return int(self.lib.oracle_max_threads())
+
+    def fr_mul(self, a, b):
+        out = np.empty_like(a)
+        self.lib.oracle_fr_mul(_p(a), _p(b), _p(out), ctypes.c_size_t(a.shape[0]))
+        return out
+
+    def fp_mul(self, a, b):
+        out = np.empty_like(a)
+        self.lib.oracle_fp_mul(_p(a), _p(b), _p(out), ctypes.c_size_t(a.shape[0]))
+        return out
+
+    def ntt(self, data, log_n, inverse, decimation, on_coset, gen, coset_gen, inplace=False):
+        out = data if inplace else np.ascontiguousarray(data.copy())
+        self.lib.oracle_ntt(_p(out), ctypes.c_uint(log_n), int(inverse), int(decimation), int(on_coset),
+                            _p(gen), _p(coset_gen))
+        return out
+
+    def compute_h(self, a, b, c, log_n, gen, coset_gen):
+        n = 1 << log_n
+
+        def pad(x):
+            o = np.zeros((n, 4), dtype=np.uint64)
+            o[: x.shape[0]] = x
+            return o
+        A, B, Cc = pad(a), pad(b), pad(c)
+        self.lib.oracle_compute_h(_p(A), _p(B), _p(Cc), ctypes.c_uint(log_n), _p(gen), _p(coset_gen))
+        return A
+
+    def msm_g1(self, scalars, bases):
+        out = np.zeros(3 * self.fp_words, dtype=np.uint64)
+        self.lib.oracle_msm_g1(_p(scalars), _p(bases), ctypes.c_size_t(scalars.shape[0]), _p(out))
+        return out
+
+    def msm_g2(self, scalars, bases):
+        out = np.zeros(6 * self.fp_words, dtype=np.uint64)
+        self.lib.oracle_msm_g2(_p(scalars), _p(bases), ctypes.c_size_t(scalars.shape[0]), _p(out))
+        return out
+
+    def g1_batch_mul(self, base, scalars):
+        out = np.zeros((scalars.shape[0], 2 * self.fp_words), dtype=np.uint64)
+        self.lib.oracle_g1_batch_mul(_p(base), _p(scalars), ctypes.c_size_t(scalars.shape[0]), _p(out))
+        return out
+
+    def g2_batch_mul(self, base, scalars):
+        out = np.zeros((scalars.shape[0], 4 * self.fp_words), dtype=np.uint64)
+        self.lib.oracle_g2_batch_mul(_p(base), _p(scalars), ctypes.c_size_t(scalars.shape[0]), _p(out))
+        return out
+
+    def g1_jac_to_aff(self, j):
+        out = np.zeros(2 * self.fp_words, dtype=np.uint64)
+        self.lib.oracle_g1_jac_to_aff(_p(j), _p(out))
+        return out
+
+    def g2_jac_to_aff(self, j):
+        out = np.zeros(4 * self.fp_words, dtype=np.uint64)
+        self.lib.oracle_g2_jac_to_aff(_p(j), _p(out))
+        return out
 
 
-def fp_mul(a: np.ndarray, b: np.ndarray) -> np.ndarray:
-    out = np.empty_like(a)
-    lib().oracle_fp_mul(_p(a), _p(b), _p(out), ctypes.c_size_t(a.shape[0]))
-    return out
+BN254 = Oracle(lib, 4)
+BLS12_377 = Oracle(lib377, 6)
 
-
-def ntt(data: np.ndarray, log_n: int, inverse: bool, decimation: int, on_coset: bool,
-        gen: np.ndarray, coset_gen: np.ndarray) -> np.ndarray:
-    out = np.ascontiguousarray(data.copy())
-    lib().oracle_ntt(_p(out), ctypes.c_uint(log_n), int(inverse), int(decimation), int(on_coset),
-                     _p(gen), _p(coset_gen))
-    return out
-
-
-def compute_h(a, b, c, log_n: int, gen, coset_gen) -> np.ndarray:
-    n = 1 << log_n
-    def pad(x):
-        o = np.zeros((n, 4), dtype=np.uint64)
-        o[: x.shape[0]] = x
-        return o
-    A, B, Cc = pad(a), pad(b), pad(c)
-    lib().oracle_compute_h(_p(A), _p(B), _p(Cc), ctypes.c_uint(log_n), _p(gen), _p(coset_gen))
-    return A
-
-
-def msm_g1(scalars: np.ndarray, bases: np.ndarray) -> np.ndarray:
-    out = np.zeros(12, dtype=np.uint64)
-    lib().oracle_msm_g1(_p(scalars), _p(bases), ctypes.c_size_t(scalars.shape[0]), _p(out))
-    return out
-
-
-def msm_g2(scalars: np.ndarray, bases: np.ndarray) -> np.ndarray:
-    out = np.zeros(24, dtype=np.uint64)
-    lib().oracle_msm_g2(_p(scalars), _p(bases), ctypes.c_size_t(scalars.shape[0]), _p(out))
-    return out
-
-
-def g1_batch_mul(base: np.ndarray, scalars: np.ndarray) -> np.ndarray:
-    out = np.zeros((scalars.shape[0], 8), dtype=np.uint64)
-    lib().oracle_g1_batch_mul(_p(base), _p(scalars), ctypes.c_size_t(scalars.shape[0]), _p(out))
-    return out
-
-
-def g2_batch_mul(base: np.ndarray, scalars: np.ndarray) -> np.ndarray:
-    out = np.zeros((scalars.shape[0], 16), dtype=np.uint64)
-    lib().oracle_g2_batch_mul(_p(base), _p(scalars), ctypes.c_size_t(scalars.shape[0]), _p(out))
-    return out
-
-
-def g1_jac_to_aff(j: np.ndarray) -> np.ndarray:
-    out = np.zeros(8, dtype=np.uint64)
-    lib().oracle_g1_jac_to_aff(_p(j), _p(out))
-    return out
-
-
-def g2_jac_to_aff(j: np.ndarray) -> np.ndarray:
-    out = np.zeros(16, dtype=np.uint64)
-    lib().oracle_g2_jac_to_aff(_p(j), _p(out))
-    return out
+# module-level names = the BN254 instance (what every BN254 test imports)
+fr_mul, fp_mul, ntt, compute_h = BN254.fr_mul, BN254.fp_mul, BN254.ntt, BN254.compute_h
+msm_g1, msm_g2, g1_batch_mul, g2_batch_mul = BN254.msm_g1, BN254.msm_g2, BN254.g1_batch_mul, BN254.g2_batch_mul
+g1_jac_to_aff, g2_jac_to_aff = BN254.g1_jac_to_aff, BN254.g2_jac_to_aff

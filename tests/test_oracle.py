@@ -127,3 +127,39 @@ def test_groth16_golden_trapdoor_and_bytes():
     bs = B.g2_mul(B.G2_GEN, dl["bs"])
     assert [ar[0], ar[1]] == g["ar"] and [krs[0], krs[1]] == g["krs"]
     assert G.proof_bytes(ar, bs, krs).hex() == g["proof_hex"]
+
+
+def test_cref_bls12_377_build_vs_python_oracle(cref):
+    """liboracle377.so (cpu_ref.cpp with the BLS12-377 constants, 6-limb Fp, u^2 = -5) against the big-int
+    restatement: field products, fixed-base multiples, G1/G2 MultiExp, all eight transforms, computeH."""
+    import random
+
+    from oracle import bls12_377 as B3
+    from oracle.suite377 import ntt as N3
+    from tests import util377 as U
+    o = cref.BLS12_377
+    rnd = random.Random(1)
+    xs = [0, 1, B3.P - 1] + [rnd.randrange(B3.P) for _ in range(40)]
+    ys = [B3.P - 1, B3.P - 2, B3.P - 1] + [rnd.randrange(B3.P) for _ in range(40)]
+    assert U.fp_ints(o.fp_mul(U.fp_arr(xs), U.fp_arr(ys))) == [x * y % B3.P for x, y in zip(xs, ys)]
+    ks = [0, 1, B3.R - 1] + [rnd.randrange(B3.R) for _ in range(13)]
+    g1, g2 = U.g1_arr([B3.G1_GEN])[0], U.g2_arr([B3.G2_GEN])[0]
+    p1, p2 = o.g1_batch_mul(g1, U.fr_arr(ks)), o.g2_batch_mul(g2, U.fr_arr(ks))
+    assert [U.g1_aff(p) for p in p1] == [B3.g1_mul(B3.G1_GEN, k) for k in ks]
+    assert [U.g2_aff(p) for p in p2] == [B3.g2_mul(B3.G2_GEN, k) for k in ks]
+    sc = [rnd.randrange(B3.R) for _ in ks]
+    tot = sum(a * b for a, b in zip(sc, ks)) % B3.R
+    assert U.g1_jac(o.msm_g1(U.fr_arr(sc), p1)) == B3.g1_mul(B3.G1_GEN, tot)
+    assert U.g2_jac(o.msm_g2(U.fr_arr(sc), p2)) == B3.g2_mul(B3.G2_GEN, tot)
+    d = N3.Domain(64)
+    v = [rnd.randrange(B3.R) for _ in range(64)]
+    gen, cg = U.fr(d.generator), U.fr(d.coset_gen)
+    for inv in (0, 1):
+        for dec in (0, 1):
+            for cos in (0, 1):
+                want = list(v)
+                (N3.fft_inverse if inv else N3.fft)(want, d, dec, bool(cos))
+                assert U.fr_ints(o.ntt(U.fr_arr(v), 6, inv, dec, cos, gen, cg)) == want, (inv, dec, cos)
+    a, b, c = ([rnd.randrange(B3.R) for _ in range(61)] for _ in range(3))
+    pad = lambda t: t + [0] * 3
+    assert U.fr_ints(o.compute_h(U.fr_arr(a), U.fr_arr(b), U.fr_arr(c), 6, gen, cg)) == N3.compute_h(pad(a), pad(b), pad(c), d)

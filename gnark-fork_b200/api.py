@@ -198,6 +198,7 @@ def load_library(curve: int = BN254):
         "b200_use_stream": (i, [vp, vp]),
         "b200_fr_batch_inverse_dev": (i, [vp, i, vp, vp, sz]),
         "b200_fr_prefix_product_dev": (i, [vp, i, vp, vp, sz]),
+        "b200_fr_prefix_product_static": (i, [vp, i, vp, vp, sz]),
         "b200_fr_poly_eval_dev": (i, [vp, i, vp, sz, vp, vp]),
         "b200_fr_poly_div_linear_dev": (i, [vp, i, vp, sz, vp, vp]),
         "b200_plonk_divide_by_xn_minus_one_dev": (i, [vp, i, vp, u, u, vp, vp]),
@@ -677,6 +678,10 @@ class Context:
 
     def fr_prefix_product_dev(self, src, dst, n):
         self._check(self.lib.b200_fr_prefix_product_dev(self.h, self.curve, _dev_ptr(src), _dev_ptr(dst), n))
+
+    def fr_prefix_product_static(self, src, dst, n):
+        """b200_fr_prefix_product_static: no allocation, scratch in a static __device__ array (n <= 2^22); enqueue only."""
+        self._check(self.lib.b200_fr_prefix_product_static(self.h, self.curve, _dev_ptr(src), _dev_ptr(dst), n))
 
     def fr_poly_eval_dev(self, coeffs, n, x) -> np.ndarray:
         out = np.empty(4, dtype=np.uint64)

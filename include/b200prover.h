@@ -268,6 +268,17 @@ int b200_fr_batch_inverse_dev(b200_ctx *ctx, int curve, const void *in_dev, void
 /* out[i] = in[0] * ... * in[i]: the accumulation of the copy-constraint ratio Z
  * (iop.BuildRatioCopyConstraint, prove.go:610-621).  in may alias out. */
 int b200_fr_prefix_product_dev(b200_ctx *ctx, int curve, const void *in_dev, void *out_dev, size_t n);
+/* The same prefix product for callers that cannot allocate (code under CUDA graph capture, tight serving loops,
+ * harnesses that forbid cudaMalloc).  NO COUNTERPART IN THE REFERENCE.
+ * The call performs no cudaMalloc / cudaFree / pinned allocation: its chunk-summary scratch is a file-scope static
+ * __device__ array inside the library (csrc/noalloc.cu), 4 329 760 bytes that every GPU which loads the library
+ * holds until the process exits.  Limit: n <= 2^22 elements per call; larger n fails with B200_ERR_ARG and a message
+ * (use b200_fr_prefix_product_dev).  The call only ENQUEUES on the context's stream (b200_sync, or any synchronous
+ * entry point, orders after it); the first call on a device also looks up the array's device address
+ * (cudaGetSymbolAddress), so make that one outside a capture.  All calls on one device share the array: nothing in it
+ * has to start at zero (every word read is written earlier in the same call), but two calls that overlap on the GPU
+ * (two streams or two contexts of one device) race -- serialise them.  in may alias out. */
+int b200_fr_prefix_product_static(b200_ctx *ctx, int curve, const void *in_dev, void *out_dev, size_t n);
 /* value = sum coeffs[i] x^i (Polynomial.Evaluate, prove.go:723,1127,1300-1305). */
 int b200_fr_poly_eval_dev(b200_ctx *ctx, int curve, const void *coeffs_dev, size_t n, const uint64_t *x, uint64_t *value);
 /* quotient_dev[0..n-2]: p(X) = q(X) (X - z) + p(z) -- the synthetic division of kzg.Open /

@@ -13,3 +13,5 @@ from .api import (  # noqa: F401
     PlonkProof, PlonkProvingKey, PlonkSession, plonk_proof_bytes, plonk_derive_challenges,
 )
 from . import sharding  # noqa: F401,E402
+from . import groth16_host  # noqa: F401,E402
+from . import api  # noqa: F401,E402

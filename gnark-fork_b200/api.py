@@ -128,6 +128,36 @@ class _PkDesc(C.Structure):
     ]
 
 
+class _R1csMatrix(C.Structure):
+    """b200_r1cs_matrix."""
+    _fields_ = [("row_ptr", C.c_void_p), ("terms", C.c_void_p)]
+
+
+def _setup_structs(fw):
+    class _SetupDesc(C.Structure):
+        """b200_groth16_setup_desc."""
+        _fields_ = [("log_n", C.c_uint), ("generator", C.c_void_p), ("coset_gen", C.c_void_p),
+                    ("nb_constraints", C.c_size_t), ("nb_wires", C.c_size_t), ("nb_public", C.c_size_t),
+                    ("l", _R1csMatrix), ("r", _R1csMatrix), ("o", _R1csMatrix),
+                    ("coeffs", C.c_void_p), ("nb_coeffs", C.c_size_t),
+                    ("wire_class", C.c_void_p), ("nb_commitments", C.c_size_t),
+                    ("tau", C.c_uint64 * 4), ("alpha", C.c_uint64 * 4), ("beta", C.c_uint64 * 4),
+                    ("gamma", C.c_uint64 * 4), ("delta", C.c_uint64 * 4),
+                    ("g1_gen", C.c_void_p), ("g2_gen", C.c_void_p), ("shard_index", C.c_int), ("shard_count", C.c_int)]
+
+    class _SetupOut(C.Structure):
+        """b200_groth16_setup_out of a library with B200_FP_WORDS = fw."""
+        _fields_ = [("g1_alpha", C.c_uint64 * (2 * fw)), ("g1_beta", C.c_uint64 * (2 * fw)), ("g1_delta", C.c_uint64 * (2 * fw)),
+                    ("g2_beta", C.c_uint64 * (4 * fw)), ("g2_delta", C.c_uint64 * (4 * fw)), ("g2_gamma", C.c_uint64 * (4 * fw)),
+                    ("n_a", C.c_size_t), ("n_b", C.c_size_t), ("n_k", C.c_size_t), ("n_z", C.c_size_t), ("n_vk_k", C.c_size_t),
+                    ("infinity_a", C.c_void_p), ("infinity_b", C.c_void_p), ("vk_k", C.c_void_p), ("ck_k", C.c_void_p),
+                    ("g1_a", C.c_void_p), ("g1_b", C.c_void_p), ("g1_k", C.c_void_p), ("g1_z", C.c_void_p), ("g2_b", C.c_void_p)]
+    return _SetupDesc, _SetupOut
+
+
+_SETUP = {BN254: _setup_structs(4), BLS12_377: _setup_structs(6)}
+
+
 PROF_SLOTS = ("msm_sort", "msm_acc_g1", "msm_acc_g2", "msm_reduce", "ntt_pass", "pointwise", "copy_in", "_7")
 
 
@@ -188,6 +218,7 @@ def load_library(curve: int = BN254):
         "b200_batch_scalar_mul": (i, [vp, i, i, vp, vp, sz, vp]),
         "b200_groth16_pk_upload": (i, [vp, i, C.POINTER(_PkDesc), C.POINTER(vp)]),
         "b200_groth16_pk_free": (i, [vp, vp]),
+        "b200_groth16_setup": (i, [vp, i, C.POINTER(_SETUP[curve][0]), C.POINTER(vp), C.POINTER(_SETUP[curve][1])]),
         "b200_groth16_pk_info": (i, [vp, vp, C.POINTER(_MsmSetInfo)]),
         "b200_groth16_pk_wire_range": (i, [vp, vp, C.POINTER(sz), C.POINTER(sz)]),
         "b200_groth16_prove_core": (i, [vp, vp, vp, vp, vp, sz, vp, vp, sz, C.POINTER(Groth16MsmOut), C.POINTER(_Timings)]),
@@ -637,6 +668,65 @@ class Context:
         h = C.c_void_p()
         self._check(self.lib.b200_groth16_pk_upload(self.h, self.curve, C.byref(d), C.byref(h)))
         return Groth16ProvingKey(self, h, None)
+
+    def groth16_setup(self, *, log_n, generator, coset_gen, nb_wires, nb_public, matrices, coeffs, toxic, g1_gen, g2_gen,
+                      wire_class=None, nb_commitments=0, shard_index=0, shard_count=1, want_points=False):
+        """b200_groth16_setup: R1CS + toxic waste -> resident proving key (setup.go:85-337).  matrices = three
+        (row_ptr u64[nb_constraints + 1], terms u32[nnz, 2] = (coefficient id, wire id)) for L, R, O; toxic = dict of
+        Montgomery Fr limbs tau, alpha, beta, gamma, delta.  Returns (Groth16ProvingKey, dict): vk-side points,
+        infinity bitmaps, vk.G1.K, the Pedersen bases, and (want_points) the proving key's point arrays."""
+        Desc, Out = _SETUP[self.curve]
+        fw = self.fw
+        d, o = Desc(), Out()
+        keep = [_u64(generator), _u64(coset_gen), _u64(coeffs, (-1, 4)), _u64(g1_gen), _u64(g2_gen)]
+        d.log_n, d.generator, d.coset_gen = log_n, _ptr(keep[0]), _ptr(keep[1])
+        nb_constraints = len(matrices[0][0]) - 1
+        d.nb_constraints, d.nb_wires, d.nb_public = nb_constraints, nb_wires, nb_public
+        for name, (rp, tm) in zip(("l", "r", "o"), matrices):
+            rp = np.ascontiguousarray(rp, dtype=np.uint64)
+            tm = np.ascontiguousarray(tm, dtype=np.uint32).reshape(-1, 2)
+            assert rp.shape[0] == nb_constraints + 1 and int(rp[-1]) == tm.shape[0]
+            keep += [rp, tm]
+            m = getattr(d, name)
+            m.row_ptr, m.terms = _ptr(rp), _ptr(tm)
+        d.coeffs, d.nb_coeffs = _ptr(keep[2]), keep[2].shape[0]
+        wc = None
+        if wire_class is not None:
+            wc = np.ascontiguousarray(wire_class, dtype=np.uint8)
+            assert wc.shape[0] == nb_wires
+            d.wire_class = _ptr(wc)
+        d.nb_commitments = nb_commitments
+        for k in ("tau", "alpha", "beta", "gamma", "delta"):
+            getattr(d, k)[:] = [int(v) for v in _u64(toxic[k], (4,))]
+        d.g1_gen, d.g2_gen = _ptr(keep[3]), _ptr(keep[4])
+        d.shard_index, d.shard_count = shard_index, shard_count
+        res = dict(infinity_a=np.zeros(nb_wires, dtype=np.uint8), infinity_b=np.zeros(nb_wires, dtype=np.uint8),
+                   vk_k=np.zeros((nb_public + nb_commitments, 2 * fw), dtype=np.uint64))
+        o.infinity_a, o.infinity_b, o.vk_k = _ptr(res["infinity_a"]), _ptr(res["infinity_b"]), _ptr(res["vk_k"])
+        ck = []
+        if nb_commitments:
+            for j in range(nb_commitments):
+                ck.append(np.zeros((int((wc == 2 + j).sum()), 2 * fw), dtype=np.uint64))
+            arr = (C.c_void_p * nb_commitments)(*[c.ctypes.data for c in ck])
+            keep.append(arr)
+            o.ck_k = C.cast(arr, C.c_void_p)
+        res["ck_k"] = ck
+        if want_points:
+            n = 1 << log_n
+            res.update(g1_a=np.zeros((nb_wires, 2 * fw), dtype=np.uint64), g1_b=np.zeros((nb_wires, 2 * fw), dtype=np.uint64),
+                       g1_k=np.zeros((nb_wires, 2 * fw), dtype=np.uint64), g1_z=np.zeros((max(n - 1, 1), 2 * fw), dtype=np.uint64),
+                       g2_b=np.zeros((nb_wires, 4 * fw), dtype=np.uint64))
+            for k in ("g1_a", "g1_b", "g1_k", "g1_z", "g2_b"):
+                setattr(o, k, _ptr(res[k]))
+        h = C.c_void_p()
+        self._check(self.lib.b200_groth16_setup(self.h, self.curve, C.byref(d), C.byref(h), C.byref(o)))
+        for k in ("g1_alpha", "g1_beta", "g1_delta", "g2_beta", "g2_delta", "g2_gamma"):
+            res[k] = np.array(getattr(o, k), dtype=np.uint64)
+        res.update(n_a=int(o.n_a), n_b=int(o.n_b), n_k=int(o.n_k), n_z=int(o.n_z), n_vk_k=int(o.n_vk_k))
+        if want_points:
+            res["g1_a"], res["g1_b"], res["g2_b"] = res["g1_a"][:o.n_a], res["g1_b"][:o.n_b], res["g2_b"][:o.n_b]
+            res["g1_k"], res["g1_z"] = res["g1_k"][:o.n_k], res["g1_z"][:o.n_z]
+        return Groth16ProvingKey(self, h, None), res
 
     def groth16_prove_core(self, pk: Groth16ProvingKey, a, b, c, w, k_remove=None):
         """computeH + the five MSMs (prove.go:139-301). Returns (Groth16MsmOut, timings dict)."""

@@ -393,6 +393,12 @@ int b200_groth16_pk_upload(b200_ctx* ctx, int curve, const b200_groth16_pk_desc*
     B2_ENTER(ctx, curve);
     return groth16_pk_upload(ctx, desc, out);
 }
+int b200_groth16_setup(b200_ctx* ctx, int curve, const b200_groth16_setup_desc* desc, b200_groth16_pk** pk_out,
+                       b200_groth16_setup_out* out) {
+    B2_ENTER(ctx, curve);
+    if (pk_out) *pk_out = nullptr;
+    return groth16_setup(ctx, desc, pk_out, out);
+}
 int b200_groth16_pk_free(b200_ctx* ctx, b200_groth16_pk* pk) {
     B2_ENTER(ctx, BUILD_CURVE);
     B2_CUDA(ctx, cudaStreamSynchronize(ctx->stream));

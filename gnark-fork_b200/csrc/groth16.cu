@@ -42,6 +42,30 @@ static int upload_range(b200_ctx* ctx, DevBuf& dst, const uint64_t* host, size_t
     return B200_OK;
 }
 
+// Setup (setup.go:251,308): the same range as [scalar_i] * base from the device fixed-base kernel instead of a copy.
+// scalars: host pointer (full array, indexed from lo) or, when on_device, a device pointer to the full array.
+template <class T>
+static int generate_range(b200_ctx* ctx, DevBuf& dst, const Fr* scalars, bool on_device, size_t lo, size_t hi, const T& base,
+                          uint64_t* host_out) {
+    const size_t cnt = hi - lo;
+    B2_CUDA(ctx, dst.alloc(cnt * sizeof(T)));
+    if (!cnt) return B200_OK;
+    DevBuf sc;
+    const Fr* d_sc = scalars + lo;
+    if (!on_device) {
+        B2_CUDA(ctx, sc.alloc(cnt * sizeof(Fr)));
+        B2_CUDA(ctx, cudaMemcpyAsync(sc.p, scalars + lo, cnt * sizeof(Fr), cudaMemcpyHostToDevice, ctx->stream));
+        d_sc = sc.as<Fr>();
+    }
+    if constexpr (sizeof(T) == sizeof(G1Affine)) B2_TRY(batch_mul_g1(ctx, base, d_sc, cnt, dst.as<G1Affine>()));
+    else B2_TRY(batch_mul_g2(ctx, base, d_sc, cnt, dst.as<G2Affine>()));
+    if (host_out) {
+        B2_CUDA(ctx, cudaMemcpyAsync(reinterpret_cast<char*>(host_out) + lo * sizeof(T), dst.p, cnt * sizeof(T), cudaMemcpyDeviceToHost, ctx->stream));
+        B2_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    }
+    return B200_OK;
+}
+
 // Replace a resident base array by its folded-window table when enabled and it fits in memory.
 template <class F>
 static int maybe_fold(b200_ctx* ctx, DevBuf& bases, size_t n, MsmFold& fold, int group, size_t reserve_bytes) {
@@ -79,8 +103,11 @@ static int upload_wire_map(b200_ctx* ctx, DevBuf& dst, const std::vector<uint32_
     return B200_OK;
 }
 
-int groth16_pk_upload(b200_ctx* ctx, const b200_groth16_pk_desc* d, b200_groth16_pk** out) {
+int groth16_pk_upload(b200_ctx* ctx, const b200_groth16_pk_desc* d, b200_groth16_pk** out, const PkScalarSource* gen_src) {
     if (!d || !out || !d->generator || !d->coset_gen) return ctx->fail(B200_ERR_ARG, "null descriptor field");
+    if (!d->infinity_a || !d->infinity_b) return ctx->fail(B200_ERR_ARG, "null infinity bitmap");
+    if (!gen_src && ((d->n_a && !d->g1_a) || (d->n_b && (!d->g1_b || !d->g2_b)) || (d->n_k && !d->g1_k) || (d->n_z && !d->g1_z)))
+        return ctx->fail(B200_ERR_ARG, "null base array");
     if (d->shard_count < 1 || d->shard_index < 0 || d->shard_index >= d->shard_count)
         return ctx->fail(B200_ERR_ARG, "bad shard");
     if (d->n_wires < d->nb_public || d->n_k > d->n_wires - d->nb_public)
@@ -127,14 +154,25 @@ int groth16_pk_upload(b200_ctx* ctx, const b200_groth16_pk_desc* d, b200_groth16
             st = ctx->fail(B200_ERR_CUDA, "pk upload");
     }
     uint32_t* d_bad = raw ? bad.as<uint32_t>() : nullptr;
+    if (gen_src) {
+        // Setup: this shard's ranges come out of the fixed-base kernel (and, optionally, go back to the caller's arrays)
+        const PkScalarSource& g = *gen_src;
+        if (st == B200_OK) st = generate_range<G1Affine>(ctx, pk->A, g.a, false, a_lo, a_hi, g.g1, g.out_a);
+        if (st == B200_OK) st = generate_range<G1Affine>(ctx, pk->B, g.b, false, b_lo, b_hi, g.g1, g.out_b);
+        if (st == B200_OK) st = generate_range<G2Affine>(ctx, pk->G2B, g.b, false, b_lo, b_hi, g.g2, g.out_g2b);
+        if (st == B200_OK) st = generate_range<G1Affine>(ctx, pk->K, g.k, false, pk->k_lo, pk->k_lo + pk->n_k, g.g1, g.out_k);
+        if (st == B200_OK) { shard_range_z(d->n_z, d->log_n, si, sc, &lo, &hi); pk->n_z = hi - lo; pk->z_lo = lo;
+            st = generate_range<G1Affine>(ctx, pk->Z, g.z_dev, true, lo, hi, g.g1, g.out_z); }
+    } else {
     if (st == B200_OK) st = upload_range<G1Affine>(ctx, pk->A, d->g1_a, a_lo, a_hi, ps, raw, d_bad);
-    if (st == B200_OK) st = upload_wire_map(ctx, pk->mapA, wa, a_lo, a_hi, (uint32_t)pk->w_lo);
     if (st == B200_OK) st = upload_range<G1Affine>(ctx, pk->B, d->g1_b, b_lo, b_hi, ps, raw, d_bad);
     if (st == B200_OK) st = upload_range<G2Affine>(ctx, pk->G2B, d->g2_b, b_lo, b_hi, ps, raw, d_bad);
-    if (st == B200_OK) st = upload_wire_map(ctx, pk->mapB, wb, b_lo, b_hi, (uint32_t)pk->w_lo);
     if (st == B200_OK) st = upload_range<G1Affine>(ctx, pk->K, d->g1_k, pk->k_lo, pk->k_lo + pk->n_k, ps, raw, d_bad);
     if (st == B200_OK) { shard_range_z(d->n_z, d->log_n, si, sc, &lo, &hi); pk->n_z = hi - lo; pk->z_lo = lo;
         st = upload_range<G1Affine>(ctx, pk->Z, d->g1_z, lo, hi, ps, raw, d_bad); }
+    }
+    if (st == B200_OK) st = upload_wire_map(ctx, pk->mapA, wa, a_lo, a_hi, (uint32_t)pk->w_lo);
+    if (st == B200_OK) st = upload_wire_map(ctx, pk->mapB, wb, b_lo, b_hi, (uint32_t)pk->w_lo);
     if (st == B200_OK && raw) {
         uint32_t flag = 0;
         if (cudaMemcpyAsync(&flag, bad.p, sizeof flag, cudaMemcpyDeviceToHost, ctx->stream) != cudaSuccess ||

@@ -19,7 +19,18 @@ struct b200_groth16_pk {
 };
 
 namespace b200 {
-int groth16_pk_upload(b200_ctx* ctx, const b200_groth16_pk_desc* d, b200_groth16_pk** out);
+// Setup's source of the base arrays: the scalars behind them (setup.go:120-275) instead of points.  a, b, k: host arrays
+// of the full (filtered) lengths; z_dev: device array, bit-reversed order, 2^log_n entries (the first n - 1 are used);
+// out_*: optional host arrays that receive the generated points (full length; each shard fills its own range).
+struct PkScalarSource {
+    const Fr *a = nullptr, *b = nullptr, *k = nullptr, *z_dev = nullptr;
+    G1Affine g1;
+    G2Affine g2;
+    uint64_t *out_a = nullptr, *out_b = nullptr, *out_k = nullptr, *out_z = nullptr, *out_g2b = nullptr;
+};
+int groth16_pk_upload(b200_ctx* ctx, const b200_groth16_pk_desc* d, b200_groth16_pk** out, const PkScalarSource* gen_src = nullptr);
+// setup.cu
+int groth16_setup(b200_ctx* ctx, const b200_groth16_setup_desc* d, b200_groth16_pk** pk_out, b200_groth16_setup_out* out);
 int groth16_prove_core(b200_ctx* ctx, const b200_groth16_pk* pk, const uint64_t* a, const uint64_t* b,
                        const uint64_t* c, size_t n_constraints, const uint64_t* w, const uint32_t* k_remove,
                        size_t n_remove, const uint64_t* h_local, b200_groth16_out* out, b200_timings* tm);

@@ -254,6 +254,55 @@ int b200_groth16_pk_info(b200_ctx *ctx, const b200_groth16_pk *pk, b200_msm_set_
  * that slice of `w` is copied per proof. */
 int b200_groth16_pk_wire_range(b200_ctx *ctx, const b200_groth16_pk *pk, size_t *lo, size_t *hi);
 
+/* ---- Groth16 Setup on the device -----------------------------------------
+ * groth16_bn254.Setup (/root/reference/backend/groth16/bn254/setup.go:85-337) with the toxic waste supplied by the
+ * caller (sampleToxicWaste stays in Go): the Lagrange evaluations L_j(tau) for the whole domain (one batch inversion on
+ * the device, where setupABC :352-433 walks a sequential recurrence), A_i(tau), B_i(tau), C_i(tau) accumulated over the
+ * constraint matrices on host threads, the K scalars (beta A + alpha B + C) / gamma or / delta (:144-200), the Z scalars
+ * (tau^n - 1) tau^i / delta bit-reversed (:203-214,265-267), the infinity filters (:217-243), and the two
+ * BatchScalarMultiplication calls (:251,308) on the device fixed-base kernel.  The proving key is left RESIDENT (the
+ * same handle b200_groth16_pk_upload returns, this shard's point ranges only); the verifying-key side and, when asked
+ * for, the proving key's point arrays come back to the host so that Go can fill its own ProvingKey / VerifyingKey.
+ * A matrix is CSR over the constraints; a term is constraint.Term {CID, VID} (constraint/term.go:31-33). */
+typedef struct b200_r1cs_matrix {
+    const uint64_t *row_ptr;   /* nb_constraints + 1 term offsets                                     */
+    const uint32_t *terms;     /* 2 u32 per term: coefficient id (index into coeffs), wire id          */
+} b200_r1cs_matrix;
+
+typedef struct b200_groth16_setup_desc {
+    unsigned log_n;                     /* fft.NewDomain(nbConstraints): Cardinality = 2^log_n            */
+    const uint64_t *generator;          /* Domain.Generator (4 u64)                                       */
+    const uint64_t *coset_gen;          /* Domain.FrMultiplicativeGen                                     */
+    size_t nb_constraints, nb_wires, nb_public;   /* nb_public = r1cs.GetNbPublicVariables() (ONE included) */
+    b200_r1cs_matrix l, r, o;           /* the L, R, O linear expressions of every R1C                    */
+    const uint64_t *coeffs; size_t nb_coeffs;     /* r1cs.Coefficients (Montgomery Fr)                     */
+    /* api.Commit circuits (setup.go:99-107,155-200): one byte per wire, NULL = none.  0: ordinary wire;
+     * 1: a commitment wire (its K goes to vk.G1.K after the public ones, divided by gamma);
+     * 2 + j: a private wire committed to by commitment j (its K goes to the j-th Pedersen basis, divided by gamma). */
+    const uint8_t *wire_class;
+    size_t nb_commitments;
+    uint64_t tau[4], alpha[4], beta[4], gamma[4], delta[4];   /* toxic waste (Montgomery Fr)               */
+    const uint64_t *g1_gen, *g2_gen;    /* curve.Generators(): affine G1 (2 Fp) and G2 (4 Fp)              */
+    int shard_index, shard_count;       /* as in b200_groth16_pk_desc: 0, 1 = the whole key on this device  */
+} b200_groth16_setup_desc;
+
+typedef struct b200_groth16_setup_out {
+    uint64_t g1_alpha[2 * B200_FP_WORDS], g1_beta[2 * B200_FP_WORDS], g1_delta[2 * B200_FP_WORDS];
+    uint64_t g2_beta[4 * B200_FP_WORDS], g2_delta[4 * B200_FP_WORDS], g2_gamma[4 * B200_FP_WORDS];
+    size_t n_a, n_b, n_k, n_z;          /* len(pk.G1.A), len(pk.G1.B) = len(pk.G2.B), len(pk.G1.K), len(pk.G1.Z) */
+    size_t n_vk_k;                      /* len(vk.G1.K) = nb_public + nb_commitments                        */
+    /* caller-allocated, each may be NULL: */
+    uint8_t *infinity_a, *infinity_b;   /* pk.InfinityA / InfinityB, nb_wires bytes each                    */
+    uint64_t *vk_k;                     /* vk.G1.K: (nb_public + nb_commitments) G1Affine                    */
+    uint64_t *const *ck_k;              /* nb_commitments arrays: the Pedersen bases of commitment j (as many G1Affine as
+                                           wires of class 2 + j), input of pedersen.Setup (setup.go:277-290)  */
+    uint64_t *g1_a, *g1_b, *g1_k, *g1_z, *g2_b;   /* the proving key's point arrays, capacity nb_wires (a, b, k, g2_b) /
+                                           2^log_n - 1 (z) points; with shards each call fills its own range   */
+} b200_groth16_setup_out;
+
+int b200_groth16_setup(b200_ctx *ctx, int curve, const b200_groth16_setup_desc *desc, b200_groth16_pk **pk_out,
+                       b200_groth16_setup_out *out);
+
 /* Per-stage device times in milliseconds (CUDA events).  The input copies run on a second stream:
  * W first, then a, b, c, overlapped with the four witness MSMs (order on the device: A, B1, K, B2,
  * computeH, Z).  h2d_ms spans the copy stream and is NOT a summand of total_ms. */

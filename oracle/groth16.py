@@ -32,6 +32,8 @@ class R1CS:
     nb_secret: int
     nb_internal: int
     constraints: list  # [(L, R, O)], each a list of (coeff:int, wire:int)
+    # api.Commit circuits (constraint.Groth16Commitments): [(commitment wire, [private committed wires, ascending])]
+    commitments: list = field(default_factory=list)
 
     @property
     def nb_wires(self):
@@ -161,10 +163,25 @@ def setup_abc(r1cs: R1CS, d: ntt.Domain, t: int):
     B = [0] * r1cs.nb_wires
     Cc = [0] * r1cs.nb_wires
     zt = (pow(t, n, R) - 1) % R
-    wi = 1
-    for (L, Rr, O) in r1cs.constraints:
+    # [t - w^j] and its inverses in one batch inversion, as setup.go:362-371 does (fr.BatchInvert)
+    ws, wi = [], 1
+    for _ in r1cs.constraints:
+        ws.append(wi)
+        wi = wi * d.generator % R
+    pre, acc = [], 1
+    for wj in ws:
+        pre.append(acc)
+        acc = acc * ((t - wj) % R) % R
+    inv = pow(acc, -1, R)
+    tinv = [0] * len(ws)
+    for j in range(len(ws) - 1, -1, -1):
+        tinv[j] = inv * pre[j] % R
+        inv = inv * ((t - ws[j]) % R) % R
+    scale = zt * d.cardinality_inv % R
+    for j, (L, Rr, O) in enumerate(r1cs.constraints):
         # L_j(t) = (t^n - 1)/n * w^j / (t - w^j)
-        lag = zt * d.cardinality_inv % R * wi % R * pow((t - wi) % R, -1, R) % R
+        wi = ws[j]
+        lag = scale * wi % R * tinv[j] % R
         for k, i in L:
             A[i] = (A[i] + k * lag) % R
         for k, i in Rr:
@@ -185,10 +202,17 @@ def setup(r1cs: R1CS, td: Trapdoor, points: bool = True) -> tuple[ProvingKey, di
     nb_pub = r1cs.nb_public
     vkK = []
     pkK = []
+    # setup.go:155-200: commitment wires join vk.K (after the public wires, in wire order); private wires committed to
+    # by commitment j go to its Pedersen basis ckK[j]; both are divided by gamma.  Everything else: pk.K, divided by delta.
+    commit_wires = {cw for cw, _ in r1cs.commitments}
+    committed_by = {w: j for j, (_, ws_) in enumerate(r1cs.commitments) for w in ws_}
+    ckK = [[] for _ in r1cs.commitments]
     for i in range(r1cs.nb_wires):
         k = (A[i] * td.beta + B[i] * td.alpha + Cc[i]) % R
-        if i < nb_pub:
+        if i < nb_pub or i in commit_wires:
             vkK.append(k * gamma_inv % R)
+        elif i in committed_by:
+            ckK[committed_by[i]].append(k * gamma_inv % R)
         else:
             pkK.append(k * delta_inv % R)
     zdt = (pow(td.t, n, R) - 1) * delta_inv % R
@@ -212,9 +236,10 @@ def setup(r1cs: R1CS, td: Trapdoor, points: bool = True) -> tuple[ProvingKey, di
         g2_beta=mul2(td.beta), g2_delta=mul2(td.delta), g2_B=[mul2(x) for x in B_f],
         infinity_A=inf_a, infinity_B=inf_b,
         nb_infinity_A=sum(inf_a), nb_infinity_B=sum(inf_b),
-        sc=dict(A=A_f, B=B_f, Z=Z, K=pkK, vkK=vkK),
+        sc=dict(A=A_f, B=B_f, Z=Z, K=pkK, vkK=vkK, ckK=ckK),
     )
-    vk = dict(vkK=vkK, alpha=td.alpha, beta=td.beta, gamma=td.gamma, delta=td.delta)
+    vk = dict(vkK=vkK, alpha=td.alpha, beta=td.beta, gamma=td.gamma, delta=td.delta,
+              commit_wires=sorted(commit_wires), committed=[list(ws_) for _, ws_ in r1cs.commitments])
     return pk, vk
 
 
@@ -226,23 +251,27 @@ def filter_wires(w, infinity):
     return [x for x, inf in zip(w, infinity) if not inf]
 
 
-def prove_scalars(pk: ProvingKey, w, a, b, c, r: int, s: int, nb_public: int):
-    """The five MSM scalar vectors of prove.go:201,214,234,244,290 in MSM order."""
-    h = ntt.compute_h(a, b, c, pk.domain)
+def prove_scalars(pk: ProvingKey, w, a, b, c, r: int, s: int, nb_public: int, to_remove=(), h=None):
+    """The five MSM scalar vectors of prove.go:201,214,234,244,290 in MSM order.  to_remove: wire ids of the
+    private committed wires and the commitment wires, dropped from the K scalars (prove.go:238-242); h: computeH's
+    output when the caller already has it (e.g. from the C++ restatement at sizes Python cannot reach)."""
+    if h is None:
+        h = ntt.compute_h(a, b, c, pk.domain)
     n = pk.domain.cardinality
+    drop = set(to_remove)
     return dict(
         A=filter_wires(w, pk.infinity_A),
         B=filter_wires(w, pk.infinity_B),
-        K=list(w[nb_public:]),
+        K=[x for i, x in enumerate(w) if i >= nb_public and i not in drop],
         Z=h[: n - 1],
     )
 
 
-def prove_dlog(pk: ProvingKey, td: Trapdoor, w, a, b, c, r: int, s: int, nb_public: int):
+def prove_dlog(pk: ProvingKey, td: Trapdoor, w, a, b, c, r: int, s: int, nb_public: int, to_remove=(), h=None):
     """Discrete logs (w.r.t. the G1/G2 generators) of the proof elements Prove must output:
     ar = alpha + <A,w> + r*delta; bs = beta + <B,w> + s*delta;
     krs = <K,w_priv> + <Z,h> + s*ar + r*bs - r*s*delta   (prove.go:206-207,219-221,248-271,294-299)."""
-    sc = prove_scalars(pk, w, a, b, c, r, s, nb_public)
+    sc = prove_scalars(pk, w, a, b, c, r, s, nb_public, to_remove, h)
     dot = lambda x, y: sum(p * q for p, q in zip(x, y)) % R
     msm = dict(A=dot(pk.sc["A"], sc["A"]), B=dot(pk.sc["B"], sc["B"]),
                K=dot(pk.sc["K"], sc["K"]), Z=dot(pk.sc["Z"], sc["Z"]))
@@ -252,10 +281,18 @@ def prove_dlog(pk: ProvingKey, td: Trapdoor, w, a, b, c, r: int, s: int, nb_publ
     return dict(ar=ar, bs=bs, krs=krs, msm=msm, scalars=sc)
 
 
-def trapdoor_check(vk: dict, public_w, ar: int, bs: int, krs: int) -> bool:
+def commitment_dlogs(pk: ProvingKey, vk: dict, w) -> list:
+    """Discrete logs of proof.Commitments[j] = pk.CommitmentKeys[j].Commit(private committed values) (prove.go:95):
+    a Pedersen commitment is the MultiExp of the values against the basis ckK[j]."""
+    return [sum(w[i] * k for i, k in zip(ws_, pk.sc["ckK"][j])) % R for j, ws_ in enumerate(vk["committed"])]
+
+
+def trapdoor_check(vk: dict, public_w, ar: int, bs: int, krs: int, commitment_values=(), commitments=()) -> bool:
     """verify.go:65-137 in the exponent: ar*bs == alpha*beta + ksum*gamma + krs*delta,
-    ksum = sum_{i public} w_i * vkK_i (verify.go:111-115; public_w includes the ONE wire)."""
-    ksum = sum(x * k for x, k in zip(public_w, vk["vkK"])) % R
+    ksum = sum_{i public} w_i * vkK_i (verify.go:111-115; public_w includes the ONE wire) -- for api.Commit circuits
+    the public witness is extended by the commitment wires' values (:75-99) and every proof.Commitments[j] is added
+    to ksum (:117-119).  (The Pedersen proof of knowledge, :101-107, is a host-side check outside this path.)"""
+    ksum = (sum(x * k for x, k in zip(list(public_w) + list(commitment_values), vk["vkK"])) + sum(commitments)) % R
     return (ar * bs - vk["alpha"] * vk["beta"] - ksum * vk["gamma"] - krs * vk["delta"]) % R == 0
 
 

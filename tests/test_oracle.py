@@ -163,3 +163,48 @@ def test_cref_bls12_377_build_vs_python_oracle(cref):
     a, b, c = ([rnd.randrange(B3.R) for _ in range(61)] for _ in range(3))
     pad = lambda t: t + [0] * 3
     assert U.fr_ints(o.compute_h(U.fr_arr(a), U.fr_arr(b), U.fr_arr(c), 6, gen, cg)) == N3.compute_h(pad(a), pad(b), pad(c), d)
+
+
+def commitment_chain_circuit(nb_mul, committed=(2, 5), two_commitments=False):
+    """refCircuit plus api.Commit (commitment_test.go shapes): a commitment to some private wires, its value a new
+    internal wire Cw constrained by AssertIsDifferent(Cw, 0), i.e. Cw * Iw = ONE with the inverse Iw as another wire."""
+    r1cs = G.mul_chain_circuit(nb_mul)
+    base = r1cs.nb_wires
+    cons = list(r1cs.constraints)
+    groups = [list(committed)] if not two_commitments else [list(committed), [3, 4, 7]]
+    commitments = []
+    for j, ws in enumerate(groups):
+        cw, iw = base + 2 * j, base + 2 * j + 1
+        cons.append(([(1, cw)], [(1, iw)], [(1, 0)]))
+        commitments.append((cw, sorted(ws)))
+    return G.R1CS(nb_public=2, nb_secret=1, nb_internal=nb_mul + 2 * len(groups), constraints=cons, commitments=commitments)
+
+
+def commitment_chain_witness(r1cs, nb_mul, x=2):
+    w, _, _, _ = G.mul_chain_witness(nb_mul, x)
+    for j, _ in enumerate(r1cs.commitments):
+        h = pow(7 + j, 12345, B.R)              # stands for the hash-to-field value the solver hint injects (prove.go:98-109)
+        w += [h, pow(h, -1, B.R)]
+    a, b, c = G.solve(r1cs, w)
+    assert all(x * y % B.R == z for x, y, z in zip(a, b, c))
+    return w, a, b, c
+
+
+@pytest.mark.parametrize("two", [False, True])
+def test_groth16_commitment_circuit_trapdoor_identity(two):
+    """Setup / Prove with api.Commit wires (setup.go:155-200, prove.go:238-242, verify.go:75-119): the K MultiExp skips
+    the committed and commitment wires and the verify equation closes with the Pedersen commitments added to kSum."""
+    import random
+    nb_mul = 13
+    r1cs = commitment_chain_circuit(nb_mul, two_commitments=two)
+    rnd = random.Random(3)
+    td = G.Trapdoor(*[rnd.randrange(1, B.R) for _ in range(5)])
+    pk, vk = G.setup(r1cs, td, points=False)
+    w, a, b, c = commitment_chain_witness(r1cs, nb_mul)
+    remove = sorted(set(vk["commit_wires"]) | {i for ws in vk["committed"] for i in ws})
+    r, s = rnd.randrange(B.R), rnd.randrange(B.R)
+    dl = G.prove_dlog(pk, td, w, a, b, c, r, s, r1cs.nb_public, to_remove=remove)
+    assert len(dl["scalars"]["K"]) == len(pk.sc["K"]) == r1cs.nb_wires - 2 - len(remove)
+    com = G.commitment_dlogs(pk, vk, w)
+    assert G.trapdoor_check(vk, w[:2], dl["ar"], dl["bs"], dl["krs"], [w[i] for i in vk["commit_wires"]], com)
+    assert not G.trapdoor_check(vk, w[:2], dl["ar"], dl["bs"], dl["krs"])       # without the commitments it must fail

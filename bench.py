@@ -4,15 +4,19 @@ backend/groth16/bn254/prove.go:139-301) at 2^24 constraints on N B200s.
 
   python bench.py [--gpus N] [--steps K] [--warmup W] [--log-n 24] [--impl reference]
 
-One JSON line on stdout (rank 0).  A "step" is one proof of the synthetic 2^log_n-constraint
-Mul-chain-shaped instance (every MSM has ~2^log_n points): `value` = seconds per
-proof with a, b, c, W already resident in HBM (CUDA events on the launching stream, max over
-ranks); `e2e` = seconds per proof through the host-buffer C-ABI call the cgo shim makes
-(b200_groth16_prove_core from pinned host memory + the host fix-ups), H2D/D2H inside the timed
-region.  N > 1 (torchrun, one process per GPU): strong scaling -- the five MSMs are sharded by
-point range, partial sums gathered and added on the host; computeH is replicated.
-`--impl reference`: no Go toolchain / gnark-crypto exists on the box, so the reference arm times
-the CPU restatement (oracle/) on all host cores on a bounded sample and extrapolates linearly.
+One JSON line on stdout (rank 0).  A "step" is one proof of the refCircuit instance (groth16_test.go:120-156: the
+X <- X*X chain, 2^log_n constraints, its SATISFYING witness; SURVEY.md 8: every MSM has ~2^log_n points) with a key
+made by b200_groth16_setup from a seeded toxic waste, so the proof is checked before timing: all five MSM results
+against the discrete logs the witness implies, the verify equation in the exponent, the host fix-ups.  `value` =
+seconds per proof with a, b, c, W already resident in HBM (CUDA events on the launching stream, max over ranks);
+`e2e` = seconds per proof through the host-buffer C-ABI call the cgo shim makes (b200_groth16_prove_core from pinned
+host memory + the host fix-ups), H2D/D2H inside the timed region.  N > 1 (torchrun, one process per GPU): strong
+scaling -- the five MSMs are sharded by point range, partial sums gathered and added on the host; computeH is
+distributed with one all-to-all per transform.
+`cpu_baseline` (N = 1): one prove core of the C++ restatement (oracle/) at 2^20 on the same kind of instance, on all
+host cores, compared with the device's results on the same inputs and scaled to 2^log_n.
+`--impl reference`: no Go toolchain / gnark-crypto exists on the box, so the reference arm runs the C++ restatement
+at the FULL size, one whole prove core per step, as many steps as fit in --reference-budget seconds.
 """
 import argparse
 import importlib.util
@@ -183,128 +187,221 @@ class ClockSampler:
 
 
 # ------------------------------------------------------------------------------------------
-# synthetic instance: Mul-chain shape (groth16_test.go:120-132) with random field elements
+# the instance: refCircuit (groth16_test.go:120-156) with 2^log_n - 1 multiplications, its satisfying witness,
+# key from b200_groth16_setup with a seeded toxic waste
 # ------------------------------------------------------------------------------------------
 class Instance:
-    """nbConstraints = n = 2^log_n, wires = n + 2, A/B bases n each (2 infinity wires each),
-    K = n private wires, Z = n - 1.  Bases are [k_i]G with known k_i (device fixed-base kernel)
-    so that every MSM result can be checked exactly at any size."""
+    """nbConstraints = n = 2^log_n, wires = n + 2 (ONE, Y, X, X_1..X_{n-1}), A/B bases n each (2 infinity wires each),
+    K = n private wires, Z = n - 1 (every MSM has ~2^log_n points).  The proving key comes out of the
+    device Setup (this rank's point ranges); because tau, alpha, beta, gamma, delta are known, every MSM result and the
+    proof have known discrete logs and the verify equation is checked in the exponent (groth16_host)."""
 
-    def __init__(self, log_n, rank, world, seed=0xB200, cp=None):
+    def __init__(self, pkg, log_n, rank, world, seed=0xB200, cp=None):
         self.cp = cp = cp or BN254_PARAMS
+        self.H = pkg.groth16_host
+        self.fld = self.H.Field(cp.id)
         self.log_n, self.n = log_n, 1 << log_n
         n = self.n
         self.n_wires, self.nb_public = n + 2, 2
-        self.inf_a = np.zeros(self.n_wires, dtype=np.uint8); self.inf_a[[1, n + 1]] = 1   # Y and X_N
-        self.inf_b = np.zeros(self.n_wires, dtype=np.uint8); self.inf_b[[0, 1]] = 1       # ONE and Y
         self.full = dict(a=n, b=n, k=n, z=n - 1)
-        self.rng = np.random.default_rng(seed + log_n)          # same on every rank: W, a, b, c
         self.rank, self.world = rank, world
         self.gen = cp.generator(log_n)
         self.coset = cp.fr_limbs(cp.coset)
-
-    def shard(self, key):
-        m = self.full[key]
-        if key == "z":      # G1.Z follows the block layout of the distributed computeH (sharding.z_shard_range)
-            n, w = self.n, self.world
-            if w & (w - 1) == 0 and w <= n:
-                return min(m, n // w * self.rank), min(m, n // w * (self.rank + 1))
-        return m * self.rank // self.world, m * (self.rank + 1) // self.world
+        self.toxic = self.H.sample_toxic(self.fld, np.random.default_rng(seed + log_n))   # same on every rank
 
     def build_key(self, ctx):
-        """Per-rank shard of the five base arrays + their discrete logs."""
-        rng = np.random.default_rng(977 + 31 * self.rank + self.log_n)
-        self.dlog, self.bases = {}, {}
-        for key in ("a", "b", "k", "z"):
-            lo, hi = self.shard(key)
-            self.dlog[key] = rand_field(rng, hi - lo, top_limb=self.cp.top_limb)
-            self.bases[key] = ctx.batch_scalar_mul(self.cp.g1_gen, self.dlog[key], 1)
-        self.bases["g2b"] = ctx.batch_scalar_mul(self.cp.g2_gen, self.dlog["b"], 2)
-        return ctx.groth16_pk_upload(
-            log_n=self.log_n, generator=self.gen, coset_gen=self.coset, g1_a=self.bases["a"], g1_b=self.bases["b"],
-            g1_k=self.bases["k"], g1_z=self.bases["z"], g2_b=self.bases["g2b"], infinity_a=self.inf_a,
-            infinity_b=self.inf_b, nb_public=self.nb_public, shard_index=self.rank, shard_count=self.world,
-            presliced=True, full_counts=self.full)
+        cs, pk, res = self.H.setup_mul_chain(ctx, self.fld, self.log_n, self.toxic, self.cp.g1_gen, self.cp.g2_gen,
+                                             shard_index=self.rank, shard_count=self.world)
+        assert (res["n_a"], res["n_b"], res["n_k"], res["n_z"]) == tuple(self.full[k] for k in "abkz")
+        self.vk = res
+        return pk
 
-    def witness(self, pkg):
-        """W, a, b, c in pinned host memory (uniform field elements, like the squaring chain's)."""
-        self.w = rand_field(self.rng, self.n_wires, pkg.pinned_empty((self.n_wires, 4)), self.cp.top_limb)
-        self.a = rand_field(self.rng, self.n, pkg.pinned_empty((self.n, 4)), self.cp.top_limb)
-        self.b = rand_field(self.rng, self.n, pkg.pinned_empty((self.n, 4)), self.cp.top_limb)
-        self.c = rand_field(self.rng, self.n, pkg.pinned_empty((self.n, 4)), self.cp.top_limb)
+    def witness(self, ctx, pkg):
+        """W, a, b, c of the chain X <- X * X from X = 2 in page-locked host memory."""
+        self.w, self.a, self.b, self.c = self.H.mul_chain_witness(ctx, self.fld, self.log_n, 2, alloc=pkg.pinned_empty)
 
-    def check(self, ctx, pkg, out):
-        """Exact, size-independent: each MSM output must be [sum k_i s_i]G for this shard."""
-        od = out.as_dict()
-        wires_a = np.flatnonzero(self.inf_a == 0)
-        wires_b = np.flatnonzero(self.inf_b == 0)
-        h = ctx.compute_h(self.a, self.b, self.c, self.log_n, self.gen, self.coset)
-        lo_a, hi_a = self.shard("a"); lo_b, hi_b = self.shard("b"); lo_k, hi_k = self.shard("k"); lo_z, hi_z = self.shard("z")
-        sc = {"ar": (self.w[wires_a[lo_a:hi_a]], "a", 1), "bs1": (self.w[wires_b[lo_b:hi_b]], "b", 1),
-              "krs": (self.w[self.nb_public + lo_k: self.nb_public + hi_k], "k", 1), "krs2": (h[lo_z:hi_z], "z", 1),
-              "bs2": (self.w[wires_b[lo_b:hi_b]], "b", 2)}
-        for name, (scalars, key, group) in sc.items():
-            prod = ctx.fr_vec_mul(self.dlog[key], np.ascontiguousarray(scalars))   # Montgomery form of k_i * s_i
-            tot = mont_sum(prod, self.cp.r_mod)                                     # Montgomery form of the sum
-            tot_l = np.frombuffer(tot.to_bytes(32, "little"), dtype=np.uint64)
-            want = ctx.batch_scalar_mul(self.cp.g1_gen if group == 1 else self.cp.g2_gen, tot_l.reshape(1, 4), group)[0]
-            got = pkg.g1_jac_to_affine(od[name], curve=self.cp.id) if group == 1 else pkg.g2_jac_to_affine(od[name], curve=self.cp.id)
-            if not np.array_equal(got, want):
-                raise SystemExit(f"bench: MSM {name} does not match its known discrete log -- result invalid")
+    def vk_points(self):
+        return [self.vk[k] for k in ("g1_alpha", "g1_beta", "g1_delta", "g2_beta", "g2_delta")]
+
+    def check(self, ctx, pkg, total, raw_out=None):
+        """`total` = the five MSM results summed over the ranks (dict of Jacobian points); raw_out = the b200_groth16_out
+        they came from when there is one rank (then the host fix-ups are checked too).  Exact at any size: each must be [e]G for the discrete
+        log e the satisfying witness implies (A(tau), B(tau), K and (A B - C)(tau) / delta -- the device's h does not enter),
+        and the proof built from them must satisfy verify.go:65-137 in the exponent."""
+        H = self.H
+        exp = H.mul_chain_expected_dlogs(ctx, self.fld, self.log_n, self.toxic, self.w, self.a, self.b, self.c)
+        ok = H.points_match(ctx, pkg, self.fld, self.cp.g1_gen, self.cp.g2_gen, total, exp)
+        if not all(ok.values()):
+            raise SystemExit(f"bench: MSM results do not match the witness's discrete logs {ok} -- result invalid")
+        r_, s_ = 0x1234567 % self.fld.r, 0x7654321 % self.fld.r
+        proof = H.expected_proof_dlogs(self.fld, self.toxic, exp, r_, s_)
+        if not H.verify_equation(self.fld, self.toxic, exp, proof):
+            raise SystemExit("bench: the verify equation does not hold -- result invalid")
+        if raw_out is not None:     # the finalised proof points are the expected ones too (prove.go:178-321 on the host)
+            ar, bs, krs = pkg.groth16_finalize(raw_out, self.fld.limbs(r_), self.fld.limbs(s_), *self.vk_points(), curve=self.cp.id)
+            want_ar = ctx.batch_scalar_mul(self.cp.g1_gen, self.fld.limbs(proof["ar"]).reshape(1, 4), 1)[0]
+            want_krs = ctx.batch_scalar_mul(self.cp.g1_gen, self.fld.limbs(proof["krs"]).reshape(1, 4), 1)[0]
+            want_bs = ctx.batch_scalar_mul(self.cp.g2_gen, self.fld.limbs(proof["bs"]).reshape(1, 4), 2)[0]
+            if not (np.array_equal(ar, want_ar) and np.array_equal(krs, want_krs) and np.array_equal(bs, want_bs)):
+                raise SystemExit("bench: finalised proof differs from the expected group elements -- result invalid")
         return True
 
 
 # ------------------------------------------------------------------------------------------
-# CPU arm: the oracle restatement on all host cores, bounded sample, linear extrapolation
+# CPU arm: the oracle restatement (oracle/cpu_ref.cpp) on all host cores.  No Go toolchain / gnark-crypto exists on
+# the box, so this C++ restatement stands for the reference's CPU prover ("kind": "port").
 # ------------------------------------------------------------------------------------------
-def cpu_prove_seconds(sample_log, log_n, seed=5):
-    """One Groth16 prove core (computeH + 4 G1 MSM + 1 G2 MSM) of the CPU restatement at
-    2^sample_log, scaled by 2^(log_n - sample_log).  Returns (seconds at log_n, cores, text)."""
+def workload_config(log_n, world):
+    """The `config` object of BOTH arms (the reference arm runs on this arm's config)."""
+    return {"workload": f"BN254 Groth16 prove core (computeH + 5 MSM) of the refCircuit Mul chain (groth16_test.go:120-156), "
+                        f"2^{log_n} constraints, satisfying witness (4 G1 MSM of ~2^{log_n}, 1 G2 MSM, 7 NTT of 2^{log_n})",
+            "log_n": log_n, "inputs": "X <- X*X chain from X = 2; proving key from a seeded toxic waste",
+            "parallelism": (f"msm point-range shards x{world}, computeH distributed (one all-to-all per transform)" if world > 1 else "1 GPU"),
+            "l2": "inputs (>= 0.5 GiB per vector) exceed the 126 MB L2; no flush needed"}
+
+
+def cpu_threads():
     from oracle import cref
-    lib = cref.lib()
-    # all host cores this process may use (torchrun exports OMP_NUM_THREADS=1: not what is wanted here)
     try:
-        avail = len(os.sched_getaffinity(0))
+        avail = len(os.sched_getaffinity(0))      # torchrun exports OMP_NUM_THREADS=1: not what is wanted here
     except AttributeError:
         avail = os.cpu_count() or 1
-    lib.oracle_set_threads(int(avail))
-    cores = int(lib.oracle_max_threads())
-    m = 1 << sample_log
-    rng = np.random.default_rng(seed)
-    k = rand_field(rng, m)
+    cref.BN254.set_threads(int(avail))
+    return cref.BN254.max_threads()
+
+
+def cpu_chain_witness(log_n):
+    """(w, a, b, c) of the chain in Montgomery form, made on the CPU (oracle fr_mul by R^2 for the conversion)."""
+    from oracle import cref
+    m = 1 << log_n
+    nb_mul = m - 1
+    buf = bytearray(32 * m)
+    cur = 2
+    buf[0:32] = cur.to_bytes(32, "little")
+    for j in range(1, m):
+        cur = cur * cur % R_MOD
+        buf[32 * j:32 * j + 32] = cur.to_bytes(32, "little")
+    canon = np.frombuffer(bytes(buf), dtype=np.uint64).reshape(-1, 4)
+    r2 = np.frombuffer(((1 << 512) % R_MOD).to_bytes(32, "little"), dtype=np.uint64)
+    chain = cref.fr_mul(canon, np.broadcast_to(r2, canon.shape).copy())
+    one = fr_limbs(1)
+    w = np.concatenate([one[None], chain[nb_mul:nb_mul + 1], chain])
+    a = np.concatenate([chain[:nb_mul], one[None]])
+    b = np.concatenate([chain[:nb_mul], chain[nb_mul:]])
+    c = np.concatenate([chain[1:], chain[nb_mul:]])
+    return w, a, b, c
+
+
+def cpu_prove_once(log_n, w, a, b, c, g1_sets, g2_b):
+    """One prove core of the C++ restatement at 2^log_n: computeH (7 transforms) + MultiExp over pk.G1.A, B, K, Z and
+    pk.G2.B with the scalars prove.go:201-290 pairs them with.  Returns (seconds, {part: seconds}, results)."""
+    from oracle import cref
+    n = 1 << log_n
+    gen = fr_limbs(pow(FR_ROOT_2_28, 1 << (28 - log_n), R_MOD))
+    t0 = time.perf_counter()
+    h = cref.compute_h(a, b, c, log_n, gen, fr_limbs(5))
+    t_h = time.perf_counter() - t0
+    wa = np.ascontiguousarray(np.concatenate([w[:1], w[2:n + 1]]))     # InfinityA: Y and X_N
+    wb = np.ascontiguousarray(w[2:])                                    # InfinityB: ONE and Y
+    wk = wb                                                             # W[nb_public:]
+    t1 = time.perf_counter()
+    res = dict(ar=cref.msm_g1(wa, g1_sets["a"]), bs1=cref.msm_g1(wb, g1_sets["b"]), krs=cref.msm_g1(wk, g1_sets["k"]),
+               krs2=cref.msm_g1(np.ascontiguousarray(h[:n - 1]), g1_sets["z"]))
+    t_g1 = time.perf_counter() - t1
+    t2 = time.perf_counter()
+    res["bs2"] = cref.msm_g2(wb, g2_b)
+    t_g2 = time.perf_counter() - t2
+    return time.perf_counter() - t0, dict(compute_h=t_h, msm_g1_x4=t_g1, msm_g2=t_g2), res, h
+
+
+def cpu_synthetic_key(log_n, distinct_log=18):
+    """Base arrays for the CPU-only arm.  The cost of Pippenger does not depend on which points the bases are, so the
+    arrays are 2^distinct_log distinct multiples of the generator (oracle fixed-base multiplication) tiled to length."""
+    from oracle import cref
+    n = 1 << log_n
+    m = 1 << min(distinct_log, log_n)
+    k = rand_field(np.random.default_rng(7), m)
     g1 = cref.g1_batch_mul(G1_GEN, k)
     g2 = cref.g2_batch_mul(G2_GEN, k)
-    a, b, c, w = (rand_field(rng, m) for _ in range(4))
-    gen = fr_limbs(pow(FR_ROOT_2_28, 1 << (28 - sample_log), R_MOD))
-    t0 = time.perf_counter()
-    h = cref.compute_h(a, b, c, sample_log, gen, fr_limbs(5))
-    for _ in range(3):
-        cref.msm_g1(w, g1)
-    cref.msm_g1(h, g1)
-    cref.msm_g2(w, g2)
-    dt = time.perf_counter() - t0
-    scale = float(1 << (log_n - sample_log))
-    text = (f"one prove core (computeH + 4 G1 MSM + 1 G2 MSM) of the C++ restatement at 2^{sample_log} "
-            f"constraints took {dt:.2f} s on {cores} threads; x{int(scale)} (linear) to 2^{log_n}. "
+    reps = n // m
+    t1 = np.tile(g1, (reps, 1))
+    return dict(a=t1, b=t1, k=t1, z=t1[:n - 1]), np.tile(g2, (reps, 1))
+
+
+def cpu_baseline_leg(ctx, pkg, log_n, sample_log):
+    """cpu_baseline of the GPU arm's line: ONE prove core of the C++ restatement at 2^sample_log on the same kind of
+    instance (device Setup with the points copied back, the chain's witness), timed on all host cores, and -- the
+    checker doing its job -- its five MSM results and its h compared with the device's on the same inputs.  The
+    figure is scaled to 2^log_n: MSM part linearly (the restatement's window is 16 bits from 2^19 points up, as
+    gnark-crypto's largest), transform part by n log n."""
+    cores = cpu_threads()
+    H = pkg.groth16_host
+    fld = H.Field(pkg.BN254)
+    toxic = H.sample_toxic(fld, np.random.default_rng(99))
+    cs, pk, res = H.setup_mul_chain(ctx, fld, sample_log, toxic, G1_GEN, G2_GEN, want_points=True)
+    w, a, b, c = H.mul_chain_witness(ctx, fld, sample_log, 2)
+    dev_out, _ = ctx.groth16_prove_core(pk, a, b, c, w)
+    dev_h = ctx.compute_h(a, b, c, sample_log, fld.limbs(fld.generator(sample_log)), fld.limbs(fld.coset))
+    pk.free()
+    sec, parts, cpu_res, cpu_h = cpu_prove_once(sample_log, w, a, b, c, dict(a=res["g1_a"], b=res["g1_b"], k=res["g1_k"], z=res["g1_z"]), res["g2_b"])
+    from oracle import cref
+    od = dev_out.as_dict()
+    same = bool(np.array_equal(cpu_h, dev_h))
+    for k in ("ar", "bs1", "krs", "krs2"):
+        same = same and bool(np.array_equal(cref.g1_jac_to_aff(cpu_res[k]), pkg.g1_jac_to_affine(od[k])))
+    same = same and bool(np.array_equal(cref.g2_jac_to_aff(cpu_res["bs2"]), pkg.g2_jac_to_affine(od["bs2"])))
+    if not same:
+        raise SystemExit("bench: the CPU restatement and the device disagree on the sample instance -- result invalid")
+    up = 1 << (log_n - sample_log)
+    est = (parts["msm_g1_x4"] + parts["msm_g2"]) * up + parts["compute_h"] * up * log_n / sample_log
+    text = (f"one prove core (computeH + 4 G1 MSM + 1 G2 MSM) of the C++ restatement on the refCircuit instance at 2^{sample_log} "
+            f"constraints: {sec:.2f} s on {cores} threads (computeH {parts['compute_h']:.2f}, G1 x4 {parts['msm_g1_x4']:.2f}, G2 {parts['msm_g2']:.2f}); "
+            f"h and all five MSM results equal the device's on the same inputs; scaled to 2^{log_n}: MSM x{up} (fixed 16-bit window), "
+            f"transforms x{up} x {log_n}/{sample_log}.  The full-size run is the reference arm (--impl reference).  "
             "CPU restatement, not gnark-crypto (no Go toolchain on the box, no amd64 assembly)")
-    return dt * scale, cores, text
+    return {"value": est, "unit": "s", "cores": cores, "kind": "port", "sample": text, "sample_s": sec, "sample_log_n": sample_log,
+            "sample_matches_device": same}
 
 
 def reference_arm(args):
+    """--impl reference: the reference's CPU path for this metric, measured -- not extrapolated -- at the full size.
+    The reference itself (Go, gnark-crypto) cannot run here; its C++ restatement runs ONE whole prove core per step at
+    2^log_n constraints on all host cores.  A step takes about a minute, so the arm runs as many of the requested
+    steps as fit in --reference-budget seconds (at least one) and reports the count it ran; the warm-up is one small
+    untimed run (thread pool, page faults), reported as warmup 0 of the measured size."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return 0
-    times = []
-    for i in range(args.warmup + args.steps):
-        sec, cores, text = cpu_prove_seconds(args.cpu_sample_log, args.log_n, seed=5 + i)
-        if i >= args.warmup:
-            times.append(sec)
+    cores = cpu_threads()
+    log_n = args.log_n
+    t_setup = time.perf_counter()
+    g1_sets, g2_b = cpu_synthetic_key(log_n)
+    w, a, b, c = cpu_chain_witness(log_n)
+    small = cpu_chain_witness(12)
+    ks, k2 = cpu_synthetic_key(12)
+    cpu_prove_once(12, *small, ks, k2)
+    t_setup = time.perf_counter() - t_setup
+    times, parts_all = [], []
+    t_begin = time.perf_counter()
+    while len(times) < max(1, args.steps):
+        sec, parts, _, _ = cpu_prove_once(log_n, w, a, b, c, g1_sets, g2_b)
+        times.append(sec)
+        parts_all.append(parts)
+        if time.perf_counter() - t_begin + sec > args.reference_budget:
+            break
     v = float(np.mean(times))
-    line = {"impl": "reference", "metric": METRIC, "value": v, "unit": "s", "n_gpus": args.gpus, "steps": args.steps,
-            "warmup": args.warmup, "ms_per_step": v * 1e3, "higher_is_better": False, "scaling": "strong",
+    parts = {k: float(np.mean([p[k] for p in parts_all])) for k in parts_all[0]}
+    text = (f"{len(times)} whole prove core(s) of the C++ restatement at 2^{log_n} constraints, measured (no extrapolation): "
+            f"computeH {parts['compute_h']:.1f} s, 4 G1 MSM {parts['msm_g1_x4']:.1f} s, G2 MSM {parts['msm_g2']:.1f} s on {cores} threads; "
+            f"witness = the refCircuit chain, bases = 2^18 distinct points tiled (Pippenger's cost does not depend on the points); "
+            f"of the {args.steps} steps requested, as many as fit in {args.reference_budget:.0f} s were run.  "
+            "CPU restatement, not gnark-crypto (no Go toolchain on the box, no amd64 assembly)")
+    line = {"impl": "reference", "metric": METRIC, "value": v, "unit": "s", "n_gpus": args.gpus, "steps": len(times),
+            "warmup": 0, "ms_per_step": v * 1e3, "higher_is_better": False, "scaling": "strong",
             "vs_baseline": None, "dtype": "u32 limbs (254-bit Montgomery)", "data": "synthetic",
-            "config": {"workload": f"BN254 Groth16 prove core, 2^{args.log_n} constraints (Mul-chain shape), CPU restatement"},
-            "cpu_baseline": {"value": v, "unit": "s", "cores": cores, "kind": "port", "sample": text},
+            "config": workload_config(log_n, args.gpus),
+            "cpu_baseline": {"value": v, "unit": "s", "cores": cores, "kind": "port", "sample": text, "stage_s": parts,
+                             "steps_requested": args.steps, "setup_s": t_setup},
             "e2e": {"value": v, "unit": "s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     print(json.dumps(line), flush=True)
     return 0
@@ -355,15 +452,16 @@ def gpu_arm(args):
     for kv in args.opt:
         k, v = kv.split("=")
         ctx.set_option(k, int(v))
-    inst = Instance(args.log_n, rank, world)
+    inst = Instance(pkg, args.log_n, rank, world)
     t_setup = time.perf_counter()
     pk = inst.build_key(ctx)
-    inst.witness(pkg)
+    t_key = time.perf_counter() - t_setup
+    inst.witness(ctx, pkg)
     t_setup = time.perf_counter() - t_setup
     n, nw = inst.n, inst.n_wires
     distributed = world > 1 and (world & (world - 1)) == 0 and not args.replicate_h
     rs = rand_field(np.random.default_rng(3), 2)
-    vkp = [inst.bases["a"][0], inst.bases["b"][0], inst.bases["k"][0], inst.bases["g2b"][0], inst.bases["g2b"][1 % len(inst.bases["g2b"])]]
+    vkp = inst.vk_points()
 
     if not distributed:
         dv = {k: pkg.DeviceVector(ctx, getattr(inst, k).nbytes).upload(getattr(inst, k)) for k in ("a", "b", "c", "w")}
@@ -416,9 +514,15 @@ def gpu_arm(args):
         w_lo, w_hi = pk.wire_range()
         h2d_bytes = int((3 * n_loc + (w_hi - w_lo)) * 32)
 
-    # correctness first (outside any timed region): exact known-discrete-log check of all five MSMs
+    # correctness first (outside any timed region): the proof of the satisfying witness must verify -- all five MSM
+    # results against their discrete logs, the verify equation in the exponent, the host fix-ups (Instance.check)
     out, _, _ = step_dev()
-    verified = inst.check(ctx, pkg, out) if not args.no_check else None
+    verified = None
+    if not args.no_check:
+        total = out.as_dict() if dist is None else pkg.sharding.gather_combine(dist, out.as_dict(), device=f"cuda:{local}")
+        verified = inst.check(ctx, pkg, total, out if dist is None else None) if rank == 0 else True
+    if dist is not None:
+        dist.barrier()
 
     clocks = ClockSampler(local)
     clocks.start()                      # nvidia-smi needs a moment to come up: start it under the warm-up
@@ -473,7 +577,9 @@ def gpu_arm(args):
     if dist is not None:
         ctx.use_stream(None)
     pk.free()                           # the folded tables go before the PlonK / BLS12-377 keys come
-    del inst.bases, inst.dlog
+    args.cpu_result = None
+    if world == 1 and not args.no_cpu:  # the one leg that runs the oracle: the CPU baseline (and the device against it)
+        args.cpu_result = cpu_baseline_leg(ctx, pkg, inst.log_n, min(args.cpu_sample_log, inst.log_n))
     args.bls_result = None
     if args.bls12_377_log_n and world == 1:
         try:
@@ -502,13 +608,13 @@ def bls12_377_section(pkg, device_index, log_n, steps, warmup, peak):
     seconds per proof through the host-buffer call (pinned a, b, c, W in; H2D inside) + the host fix-ups."""
     ctx = pkg.Context(device_index, curve=pkg.BLS12_377)
     try:
-        inst = Instance(log_n, 0, 1, cp=BLS12_377_PARAMS)
+        inst = Instance(pkg, log_n, 0, 1, cp=BLS12_377_PARAMS)
         t0 = time.perf_counter()
         pk = inst.build_key(ctx)
-        inst.witness(pkg)
+        inst.witness(ctx, pkg)
         t_setup = time.perf_counter() - t0
         rs = rand_field(np.random.default_rng(3), 2, top_limb=inst.cp.top_limb)
-        vkp = [inst.bases["a"][0], inst.bases["b"][0], inst.bases["k"][0], inst.bases["g2b"][0], inst.bases["g2b"][1]]
+        vkp = inst.vk_points()
         for _ in range(max(1, warmup)):
             out, tm = ctx.groth16_prove_core(pk, inst.a, inst.b, inst.c, inst.w)
         ctx.profile_start()
@@ -520,7 +626,7 @@ def bls12_377_section(pkg, device_index, log_n, steps, warmup, peak):
             wall.append(time.perf_counter() - t1)
             tms.append(tm)
         prof = ctx.profile_read()
-        ok = inst.check(ctx, pkg, out)
+        ok = inst.check(ctx, pkg, out.as_dict(), out)
         info = pk.info()
         pk.free()
         n = inst.n
@@ -537,7 +643,8 @@ def bls12_377_section(pkg, device_index, log_n, steps, warmup, peak):
                 "4 G1 MSMs + 1 G2 MSM of ~2^%d points (Fp 377 bits = 12 x 32-bit limbs)" % (log_n, log_n, log_n),
                 "path": "b200_groth16_prove_core of libb200prover_bls12377.so (pinned host a, b, c, W in) + b200_groth16_finalize",
                 "device_ms": stage["total_ms"], "stage_ms": stage, "verified": bool(ok),
-                "verifier": "every MSM result equals [sum k_i s_i]G for the known discrete logs k_i of its bases (exact)",
+                "verifier": "refCircuit with its satisfying witness, key from b200_groth16_setup (known toxic waste): every MSM result equals "
+                            "[e]G for the discrete log e the witness implies, the verify equation holds in the exponent, host fix-ups checked",
                 "roofline_g1": {"bound": "imad", "kernel": "msm_accumulate_kernel<Fp> (12 limbs)", "launch_ms": g1_launch_ms,
                                 "model_mac32_per_s": model, "executed_mac32_per_s": executed, "peak_mac32_per_s": peak["mac32_per_s"],
                                 "frac_model": model / peak["mac32_per_s"], "frac_executed": executed / peak["mac32_per_s"],
@@ -657,11 +764,7 @@ def report(args, world, peak, prof, stage, step_ms, e2e_s, clk, verified, inst, 
         "metric": METRIC, "value": value, "unit": "s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": step_ms, "higher_is_better": False, "scaling": "strong", "vs_baseline": None,
         "dtype": "u32 limbs (254-bit Montgomery)", "data": "synthetic",
-        "config": {"workload": f"BN254 Groth16 prove core (computeH + 5 MSM), 2^{inst.log_n} constraints, Mul-chain shape "
-                               f"(4 G1 MSM of ~2^{inst.log_n}, 1 G2 MSM, 7 NTT of 2^{inst.log_n})",
-                   "log_n": inst.log_n, "inputs": "uniform random field elements; bases [k_i]G with known k_i",
-                   "parallelism": (f"msm point-range shards x{world}, computeH " + ("distributed (one NCCL all-to-all per transform)" if distributed else "replicated")) if world > 1 else "1 GPU",
-                   "l2": "inputs (>= 0.5 GiB per vector) exceed the 126 MB L2; no flush needed"},
+        "config": workload_config(inst.log_n, world),
         "e2e": {"value": e2e_s, "unit": "s", "h2d_bytes_per_step": h2d_bytes,
                 "d2h_bytes_per_step": int(4 * 16 * 128 + 16 * 256),
                 "path": "b200_groth16_prove_core (pinned host buffers) + b200_groth16_finalize"},
@@ -676,16 +779,16 @@ def report(args, world, peak, prof, stage, step_ms, e2e_s, clk, verified, inst, 
             "kernel_ms_note": "msm_sort (and part of msm_reduce) runs on a second stream under the previous MSM's accumulation: "
                               "those spans overlap the others and are stretched by sharing the SMs; they do not add up to the step",
             "g2_acc_frac_of_imad_peak": (g2["units"] * MAC32_PER_G2_POINT / (g2["ms"] * 1e-3) / mac_peak) if g2["ms"] else None,
-            "pk_sets": pk_info, "imad_peak": peak, "verified_known_dlog": verified, "setup_s": t_setup, "wall_s_timed_region": wall_dev,
+            "pk_sets": pk_info, "imad_peak": peak, "verified": verified, "verifier": "satisfying witness of the refCircuit; all five MSM results equal [e]G for the discrete logs "
+            "the witness implies under the known toxic waste; verify.go:65-137 holds in the exponent; fix-ups checked (groth16_host)", "setup_s": t_setup, "wall_s_timed_region": wall_dev,
         },
     }
     if getattr(args, "plonk_result", None):
         line["plonk"] = args.plonk_result
     if getattr(args, "bls_result", None) is not None:
         line["bls12_377"] = args.bls_result
-    if world == 1 and not args.no_cpu:
-        sec, cores, text = cpu_prove_seconds(args.cpu_sample_log, inst.log_n)
-        line["cpu_baseline"] = {"value": sec, "unit": "s", "cores": cores, "kind": "port", "sample": text}
+    if getattr(args, "cpu_result", None) is not None:
+        line["cpu_baseline"] = args.cpu_result
     print(json.dumps(line), flush=True)
     return 0
 
@@ -697,7 +800,8 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--log-n", type=int, default=24)
-    ap.add_argument("--cpu-sample-log", type=int, default=18)
+    ap.add_argument("--cpu-sample-log", type=int, default=20, help="size of the cpu_baseline sample of the GPU arm's line")
+    ap.add_argument("--reference-budget", type=float, default=150.0, help="--impl reference: seconds of timed full-size CPU steps")
     ap.add_argument("--plonk-log-n", type=int, default=22, help="also time BN254 PlonK Prove at 2^k gates (config 4; sharded over the ranks at N > 1); 0 = skip")
     ap.add_argument("--bls12-377-log-n", type=int, default=22, help="N = 1: also time BLS12-377 Groth16 Prove at 2^k constraints (config 5) through libb200prover_bls12377.so; 0 = skip")
     ap.add_argument("--plonk-dist", action="store_true", help="N > 1: run the sharded PlonK proof too (off by default: the scaling run stays the Groth16 line only)")
@@ -706,7 +810,6 @@ def main():
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--replicate-h", action="store_true", help="N > 1: every rank runs the whole computeH (no exchange)")
     args = ap.parse_args()
-    args.cpu_sample_log = min(args.cpu_sample_log, args.log_n)
     if args.impl == "reference":
         return reference_arm(args)
     return gpu_arm(args)

@@ -10,7 +10,7 @@ from .api import (  # noqa: F401
     B200Error, Context, Bases, DeviceVector, Groth16ProvingKey, Groth16MsmOut,
     g1_jac_add, g2_jac_add, g1_jac_to_affine, g2_jac_to_affine, groth16_finalize, groth16_proof_bytes,
     pinned_empty, library_path, load_library, DIF, DIT, BN254, BLS12_377, fp_words,
-    PlonkProof, PlonkProvingKey, PlonkSession, plonk_proof_bytes, plonk_derive_challenges,
+    Group, GroupGroth16ProvingKey, PlonkProof, PlonkProvingKey, PlonkSession, plonk_proof_bytes, plonk_derive_challenges,
 )
 from . import sharding  # noqa: F401,E402
 from . import groth16_host  # noqa: F401,E402

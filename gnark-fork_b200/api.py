@@ -166,6 +166,22 @@ class _Profile(C.Structure):
                 ("kernel_launches", C.c_uint64)]
 
 
+_SYM_PREFIX = {BN254: "b200_", BLS12_377: "b200_bls12377_"}
+
+
+class _Lib:
+    """The loaded library under the header's names: the BLS12-377 build exports every entry point b200_x as
+    b200_bls12377_x (include/b200prover.h, per-curve symbol names) so that both libraries link into one binary."""
+
+    def __init__(self, cdll, prefix):
+        self._cdll, self._prefix = cdll, prefix
+
+    def __getattr__(self, name):
+        fn = getattr(self._cdll, self._prefix + name[5:] if name.startswith("b200_") else name)
+        setattr(self, name, fn)
+        return fn
+
+
 def load_library(curve: int = BN254):
     """Load libb200prover.so (or the BLS12-377 build); fails loudly (no fallback of any kind)."""
     if curve in _LIBS:
@@ -177,7 +193,7 @@ def load_library(curve: int = BN254):
         raise B200Error(f"{path} not found: build it with `make -C gnark-fork_b200/csrc"
                         f"{' CURVE=bls12_377' if curve == BLS12_377 else ''}` "
                         "(or __graft_entry__.build()); there is no CPU fallback")
-    lib = C.CDLL(path)
+    lib = _Lib(C.CDLL(path), _SYM_PREFIX[curve])
     Groth16MsmOut = _MSM_OUT[curve]     # the struct of THIS library's B200_FP_WORDS
     vp, sz, u, i = C.c_void_p, C.c_size_t, C.c_uint, C.c_int
     sig = {
@@ -219,6 +235,19 @@ def load_library(curve: int = BN254):
         "b200_groth16_pk_upload": (i, [vp, i, C.POINTER(_PkDesc), C.POINTER(vp)]),
         "b200_groth16_pk_free": (i, [vp, vp]),
         "b200_groth16_setup": (i, [vp, i, C.POINTER(_SETUP[curve][0]), C.POINTER(vp), C.POINTER(_SETUP[curve][1])]),
+        "b200_group_init": (i, [C.POINTER(C.c_int), i, C.POINTER(vp)]),
+        "b200_group_destroy": (None, [vp]),
+        "b200_group_last_error": (C.c_char_p, [vp]),
+        "b200_group_size": (i, [vp]),
+        "b200_group_ctx": (vp, [vp, i]),
+        "b200_group_set_option": (i, [vp, C.c_char_p, C.c_long]),
+        "b200_group_groth16_pk_upload": (i, [vp, i, C.POINTER(_PkDesc), C.POINTER(vp)]),
+        "b200_group_groth16_setup": (i, [vp, i, C.POINTER(_SETUP[curve][0]), C.POINTER(vp), C.POINTER(_SETUP[curve][1])]),
+        "b200_group_groth16_pk_free": (i, [vp, vp]),
+        "b200_group_groth16_pk_info": (i, [vp, vp, i, C.POINTER(_MsmSetInfo), C.POINTER(i)]),
+        "b200_group_groth16_prove_core": (i, [vp, vp, vp, vp, vp, sz, vp, vp, sz, C.POINTER(Groth16MsmOut), C.POINTER(_Timings)]),
+        "b200_group_groth16_prove_core_dev": (i, [vp, vp, C.POINTER(vp), C.POINTER(vp), C.POINTER(vp), C.POINTER(vp),
+                                                  C.POINTER(Groth16MsmOut), C.POINTER(_Timings)]),
         "b200_groth16_pk_info": (i, [vp, vp, C.POINTER(_MsmSetInfo)]),
         "b200_groth16_pk_wire_range": (i, [vp, vp, C.POINTER(sz), C.POINTER(sz)]),
         "b200_groth16_prove_core": (i, [vp, vp, vp, vp, vp, sz, vp, vp, sz, C.POINTER(Groth16MsmOut), C.POINTER(_Timings)]),
@@ -640,7 +669,7 @@ class Context:
     # -- Groth16
     def groth16_pk_upload(self, *, log_n, generator, coset_gen, g1_a, g1_b, g1_k, g1_z, g2_b, infinity_a,
                           infinity_b, nb_public, shard_index=0, shard_count=1, presliced=False,
-                          full_counts=None, raw_points=False) -> Groth16ProvingKey:
+                          full_counts=None, raw_points=False, _invoke=None) -> Groth16ProvingKey:
         """presliced=True: the base arrays hold only this shard's point range; full_counts =
         dict(a=, b=, k=, z=) then gives the full lengths of pk.G1.A/B/K/Z."""
         if raw_points:      # bytes as ProvingKey.WriteRawTo stores them; converted on the device
@@ -666,11 +695,13 @@ class Context:
             d.n_a, d.n_b, d.n_k, d.n_z = (full_counts[k] for k in ("a", "b", "k", "z"))
             d.n_g2b = d.n_b
         h = C.c_void_p()
+        if _invoke is not None:
+            return _invoke(d, h)
         self._check(self.lib.b200_groth16_pk_upload(self.h, self.curve, C.byref(d), C.byref(h)))
         return Groth16ProvingKey(self, h, None)
 
     def groth16_setup(self, *, log_n, generator, coset_gen, nb_wires, nb_public, matrices, coeffs, toxic, g1_gen, g2_gen,
-                      wire_class=None, nb_commitments=0, shard_index=0, shard_count=1, want_points=False):
+                      wire_class=None, nb_commitments=0, shard_index=0, shard_count=1, want_points=False, _invoke=None):
         """b200_groth16_setup: R1CS + toxic waste -> resident proving key (setup.go:85-337).  matrices = three
         (row_ptr u64[nb_constraints + 1], terms u32[nnz, 2] = (coefficient id, wire id)) for L, R, O; toxic = dict of
         Montgomery Fr limbs tau, alpha, beta, gamma, delta.  Returns (Groth16ProvingKey, dict): vk-side points,
@@ -719,14 +750,18 @@ class Context:
             for k in ("g1_a", "g1_b", "g1_k", "g1_z", "g2_b"):
                 setattr(o, k, _ptr(res[k]))
         h = C.c_void_p()
-        self._check(self.lib.b200_groth16_setup(self.h, self.curve, C.byref(d), C.byref(h), C.byref(o)))
+        if _invoke is not None:         # the group's entry point (Group.groth16_setup) on the same descriptor
+            wrap = _invoke(d, h, o)
+        else:
+            self._check(self.lib.b200_groth16_setup(self.h, self.curve, C.byref(d), C.byref(h), C.byref(o)))
+            wrap = Groth16ProvingKey(self, h, None)
         for k in ("g1_alpha", "g1_beta", "g1_delta", "g2_beta", "g2_delta", "g2_gamma"):
             res[k] = np.array(getattr(o, k), dtype=np.uint64)
         res.update(n_a=int(o.n_a), n_b=int(o.n_b), n_k=int(o.n_k), n_z=int(o.n_z), n_vk_k=int(o.n_vk_k))
         if want_points:
             res["g1_a"], res["g1_b"], res["g2_b"] = res["g1_a"][:o.n_a], res["g1_b"][:o.n_b], res["g2_b"][:o.n_b]
             res["g1_k"], res["g1_z"] = res["g1_k"][:o.n_k], res["g1_z"][:o.n_z]
-        return Groth16ProvingKey(self, h, None), res
+        return wrap, res
 
     def groth16_prove_core(self, pk: Groth16ProvingKey, a, b, c, w, k_remove=None):
         """computeH + the five MSMs (prove.go:139-301). Returns (Groth16MsmOut, timings dict)."""
@@ -890,3 +925,100 @@ class Context:
                for i, name in enumerate(PROF_SLOTS) if not name.startswith("_")}
         out["kernel_launches"] = int(p.kernel_launches)
         return out
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# the device group: multi-GPU in one process (include/b200prover.h: b200_group_*)
+# ---------------------------------------------------------------------------------------------------------------
+class _BorrowedContext(Context):
+    """A rank's b200_ctx, owned by the group (never destroyed from here)."""
+
+    def __init__(self, lib, curve, handle, device):
+        self.lib, self.curve, self.fw, self.h, self.device = lib, curve, fp_words(curve), handle, device
+
+    def close(self):
+        self.h = None
+
+
+class GroupGroth16ProvingKey:
+    def __init__(self, group, handle):
+        self.group, self.h = group, handle
+
+    def info(self, rank=0):
+        arr, dist = (_MsmSetInfo * 5)(), C.c_int()
+        self.group._check(self.group.lib.b200_group_groth16_pk_info(self.group.h, self.h, rank, arr, C.byref(dist)))
+        d = {k: arr[j].as_dict() for j, k in enumerate(("a", "b", "k", "z", "g2b"))}
+        d["distributed_h"] = bool(dist.value)
+        return d
+
+    def free(self):
+        if self.h:
+            self.group.lib.b200_group_groth16_pk_free(self.group.h, self.h)
+            self.h = None
+
+
+class Group:
+    """b200_group: one process, one call per proof over all the listed devices (a device may be listed several
+    times: virtual ranks).  Not re-entrant."""
+
+    def __init__(self, devices, curve: int = BN254):
+        self.lib, self.curve, self.fw = load_library(curve), curve, fp_words(curve)
+        self.devices = [int(d) for d in devices]
+        arr = (C.c_int * len(self.devices))(*self.devices)
+        h = C.c_void_p()
+        st = self.lib.b200_group_init(arr, len(self.devices), C.byref(h))
+        if st != 0:
+            raise B200Error(f"b200_group_init({self.devices}) failed ({st}); CUDA devices are required, there is no CPU fallback")
+        self.h = h
+        self.size = int(self.lib.b200_group_size(h))
+
+    def _check(self, st):
+        if st != 0:
+            msg = self.lib.b200_group_last_error(self.h)
+            raise B200Error(f"status {st}: {msg.decode() if msg else ''}")
+
+    def ctx(self, rank=0) -> Context:
+        return _BorrowedContext(self.lib, self.curve, C.c_void_p(self.lib.b200_group_ctx(self.h, rank)), self.devices[rank])
+
+    def set_option(self, key, value):
+        self._check(self.lib.b200_group_set_option(self.h, key.encode(), int(value)))
+
+    def close(self):
+        if self.h:
+            self.lib.b200_group_destroy(self.h)
+            self.h = None
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    def groth16_pk_upload(self, **kw) -> GroupGroth16ProvingKey:
+        def invoke(d, h):
+            self._check(self.lib.b200_group_groth16_pk_upload(self.h, self.curve, C.byref(d), C.byref(h)))
+            return GroupGroth16ProvingKey(self, h)
+        return Context.groth16_pk_upload(self.ctx(0), _invoke=invoke, **kw)
+
+    def groth16_setup(self, **kw):
+        def invoke(d, h, o):
+            self._check(self.lib.b200_group_groth16_setup(self.h, self.curve, C.byref(d), C.byref(h), C.byref(o)))
+            return GroupGroth16ProvingKey(self, h)
+        return Context.groth16_setup(self.ctx(0), _invoke=invoke, **kw)
+
+    def groth16_prove_core(self, pk: GroupGroth16ProvingKey, a, b, c, w, k_remove=None):
+        """One proof over the whole group from host buffers: (combined Groth16MsmOut, per-stage max timings)."""
+        a, b, c, w = (_u64(x, (-1, 4)) for x in (a, b, c, w))
+        out, tm = _MSM_OUT[self.curve](), _Timings()
+        kr = None if k_remove is None or len(k_remove) == 0 else np.ascontiguousarray(k_remove, dtype=np.uint32)
+        self._check(self.lib.b200_group_groth16_prove_core(self.h, pk.h, _ptr(a), _ptr(b), _ptr(c), a.shape[0], _ptr(w),
+                                                           _ptr(kr), 0 if kr is None else kr.shape[0], C.byref(out), C.byref(tm)))
+        return out, {k: getattr(tm, k) for k, _ in _Timings._fields_}
+
+    def groth16_prove_core_dev(self, pk: GroupGroth16ProvingKey, a_blocks, b_blocks, c_blocks, w_full):
+        """Inputs resident on the devices: per rank its block of a, b, c and the full W (lists of DeviceVector)."""
+        arrs = [(C.c_void_p * self.size)(*[_dev_ptr(x).value for x in v]) for v in (a_blocks, b_blocks, c_blocks, w_full)]
+        out, tm = _MSM_OUT[self.curve](), _Timings()
+        self._check(self.lib.b200_group_groth16_prove_core_dev(self.h, pk.h, *[C.cast(x, C.POINTER(C.c_void_p)) for x in arrs],
+                                                               C.byref(out), C.byref(tm)))
+        return out, {k: getattr(tm, k) for k, _ in _Timings._fields_}

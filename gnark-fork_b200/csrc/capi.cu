@@ -35,17 +35,17 @@ int check_curve(b200_ctx* ctx, int curve) {
 
 extern "C" {
 
-const char* b200_version(void) { return BUILD_CURVE == B200_BN254 ? "b200prover 0.1 (sm_100a, BN254)" : "b200prover 0.1 (sm_100a, BLS12-377)"; }
-int b200_build_curve(void) { return BUILD_CURVE; }
-int b200_build_fp_words(void) { return (int)(sizeof(Fp) / 8); }
+const char* b200_version(void) try { return BUILD_CURVE == B200_BN254 ? "b200prover 0.1 (sm_100a, BN254)" : "b200prover 0.1 (sm_100a, BLS12-377)"; } B2_ABI_CATCH_NULL
+int b200_build_curve(void) try { return BUILD_CURVE; } B2_ABI_CATCH_INT
+int b200_build_fp_words(void) try { return (int)(sizeof(Fp) / 8); } B2_ABI_CATCH_INT
 
-int b200_device_count(void) {
+int b200_device_count(void) try {
     int n = 0;
     if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); return 0; }
     return n;
-}
+} B2_ABI_CATCH_INT
 
-int b200_init(int device, b200_ctx** out) {
+int b200_init(int device, b200_ctx** out) try {
     if (!out) return B200_ERR_ARG;
     *out = nullptr;
     int n = 0;
@@ -73,9 +73,9 @@ int b200_init(int device, b200_ctx** out) {
     if (c && *c) { int v = atoi(c); if (v >= 4 && v <= 24) ctx->msm_c_override = v; }
     *out = ctx;
     return B200_OK;
-}
+} B2_ABI_CATCH_INT
 
-void b200_destroy(b200_ctx* ctx) {
+void b200_destroy(b200_ctx* ctx) try {
     if (!ctx) return;
     cudaSetDevice(ctx->device);
     cudaStreamSynchronize(ctx->stream);
@@ -90,47 +90,48 @@ void b200_destroy(b200_ctx* ctx) {
     if (ctx->copy_stream) cudaStreamDestroy(ctx->copy_stream);
     if (ctx->aux_stream) cudaStreamDestroy(ctx->aux_stream);
     if (ctx->h_stage) cudaFreeHost(ctx->h_stage);
+    for (cudaEvent_t e : ctx->core_events) cudaEventDestroy(e);
     delete ctx;
-}
+} B2_ABI_CATCH_VOID
 
-const char* b200_last_error(const b200_ctx* ctx) { return ctx ? ctx->err.c_str() : g_init_error.c_str(); }
+const char* b200_last_error(const b200_ctx* ctx) try { return ctx ? ctx->err.c_str() : g_init_error.c_str(); } B2_ABI_CATCH_NULL
 
-void* b200_host_alloc(size_t bytes) {
+void* b200_host_alloc(size_t bytes) try {
     void* p = nullptr;
     if (cudaMallocHost(&p, bytes ? bytes : 1) != cudaSuccess) { cudaGetLastError(); return nullptr; }
     return p;
-}
-void b200_host_free(void* p) { if (p) cudaFreeHost(p); }
+} B2_ABI_CATCH_NULL
+void b200_host_free(void* p) try { if (p) cudaFreeHost(p); } B2_ABI_CATCH_VOID
 
-int b200_dev_alloc(b200_ctx* ctx, size_t bytes, void** dptr) {
+int b200_dev_alloc(b200_ctx* ctx, size_t bytes, void** dptr) try {
     B2_ENTER(ctx, BUILD_CURVE);
     if (!dptr) return ctx->fail(B200_ERR_ARG, "null out pointer");
     B2_CUDA(ctx, cudaMalloc(dptr, bytes ? bytes : 16));
     return B200_OK;
-}
-int b200_dev_free(b200_ctx* ctx, void* dptr) {
+} B2_ABI_CATCH_CTX(ctx)
+int b200_dev_free(b200_ctx* ctx, void* dptr) try {
     B2_ENTER(ctx, BUILD_CURVE);
     B2_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     B2_CUDA(ctx, cudaFree(dptr));
     return B200_OK;
-}
-int b200_h2d(b200_ctx* ctx, void* dst, const void* src, size_t bytes) {
+} B2_ABI_CATCH_CTX(ctx)
+int b200_h2d(b200_ctx* ctx, void* dst, const void* src, size_t bytes) try {
     B2_ENTER(ctx, BUILD_CURVE);
     B2_CUDA(ctx, cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, ctx->stream));
     B2_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     return B200_OK;
-}
-int b200_d2h(b200_ctx* ctx, void* dst, const void* src, size_t bytes) {
+} B2_ABI_CATCH_CTX(ctx)
+int b200_d2h(b200_ctx* ctx, void* dst, const void* src, size_t bytes) try {
     B2_ENTER(ctx, BUILD_CURVE);
     B2_CUDA(ctx, cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToHost, ctx->stream));
     B2_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     return B200_OK;
-}
-int b200_sync(b200_ctx* ctx) {
+} B2_ABI_CATCH_CTX(ctx)
+int b200_sync(b200_ctx* ctx) try {
     B2_ENTER(ctx, BUILD_CURVE);
     B2_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     return B200_OK;
-}
+} B2_ABI_CATCH_CTX(ctx)
 
 // ---- element-wise ------------------------------------------------------------------------
 static int vec_mul_host(b200_ctx* ctx, int fr, const uint64_t* a, const uint64_t* b, uint64_t* out, size_t n) {
@@ -148,18 +149,18 @@ static int vec_mul_host(b200_ctx* ctx, int fr, const uint64_t* a, const uint64_t
     B2_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     return B200_OK;
 }
-int b200_fr_vec_mul(b200_ctx* ctx, int curve, const uint64_t* a, const uint64_t* b, uint64_t* out, size_t n) {
+int b200_fr_vec_mul(b200_ctx* ctx, int curve, const uint64_t* a, const uint64_t* b, uint64_t* out, size_t n) try {
     B2_ENTER(ctx, curve);
     return vec_mul_host(ctx, 1, a, b, out, n);
-}
-int b200_fp_vec_mul(b200_ctx* ctx, int curve, const uint64_t* a, const uint64_t* b, uint64_t* out, size_t n) {
+} B2_ABI_CATCH_CTX(ctx)
+int b200_fp_vec_mul(b200_ctx* ctx, int curve, const uint64_t* a, const uint64_t* b, uint64_t* out, size_t n) try {
     B2_ENTER(ctx, curve);
     return vec_mul_host(ctx, 0, a, b, out, n);
-}
-int b200_imad_peak(b200_ctx* ctx, double* mac32_per_s, double* imad32_per_s, double* sm_mhz) {
+} B2_ABI_CATCH_CTX(ctx)
+int b200_imad_peak(b200_ctx* ctx, double* mac32_per_s, double* imad32_per_s, double* sm_mhz) try {
     B2_ENTER(ctx, BUILD_CURVE);
     return imad_peak(ctx, mac32_per_s, imad32_per_s, sm_mhz);
-}
+} B2_ABI_CATCH_CTX(ctx)
 
 // ---- NTT ---------------------------------------------------------------------------------
 static int get_domain(b200_ctx* ctx, unsigned log_n, const uint64_t* generator, const uint64_t* coset_gen, NttDomain** d) {
@@ -171,7 +172,7 @@ static int get_domain(b200_ctx* ctx, unsigned log_n, const uint64_t* generator, 
 }
 
 int b200_ntt_dev(b200_ctx* ctx, int curve, void* dev_inout, unsigned log_n, int inverse, int decimation, int on_coset,
-                 const uint64_t* generator, const uint64_t* coset_gen, float* kernel_ms) {
+                 const uint64_t* generator, const uint64_t* coset_gen, float* kernel_ms) try {
     B2_ENTER(ctx, curve);
     if (!dev_inout) return ctx->fail(B200_ERR_ARG, "null vector");
     if (decimation != B200_DIF && decimation != B200_DIT) return ctx->fail(B200_ERR_ARG, "bad decimation");
@@ -190,10 +191,10 @@ int b200_ntt_dev(b200_ctx* ctx, int curve, void* dev_inout, unsigned log_n, int 
     B2_CUDA(ctx, cudaEventSynchronize(ctx->ev1));
     if (kernel_ms) B2_CUDA(ctx, cudaEventElapsedTime(kernel_ms, ctx->ev0, ctx->ev1));
     return B200_OK;
-}
+} B2_ABI_CATCH_CTX(ctx)
 
 int b200_ntt(b200_ctx* ctx, int curve, uint64_t* host_inout, unsigned log_n, int inverse, int decimation, int on_coset,
-             const uint64_t* generator, const uint64_t* coset_gen) {
+             const uint64_t* generator, const uint64_t* coset_gen) try {
     B2_ENTER(ctx, curve);
     if (!host_inout) return ctx->fail(B200_ERR_ARG, "null vector");
     if (log_n > 27) return ctx->fail(B200_ERR_UNSUPPORTED, "NTT size above 2^27");
@@ -205,11 +206,11 @@ int b200_ntt(b200_ctx* ctx, int curve, uint64_t* host_inout, unsigned log_n, int
     B2_CUDA(ctx, cudaMemcpyAsync(host_inout, d.p, bytes, cudaMemcpyDeviceToHost, ctx->stream));
     B2_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     return B200_OK;
-}
+} B2_ABI_CATCH_CTX(ctx)
 
 int b200_groth16_compute_h(b200_ctx* ctx, int curve, const uint64_t* a, const uint64_t* b, const uint64_t* c,
                            size_t n_constraints, unsigned log_n, const uint64_t* generator, const uint64_t* coset_gen,
-                           uint64_t* h_out) {
+                           uint64_t* h_out) try {
     B2_ENTER(ctx, curve);
     if (!a || !b || !c || !h_out || !coset_gen) return ctx->fail(B200_ERR_ARG, "null argument");
     if (log_n > 27) return ctx->fail(B200_ERR_UNSUPPORTED, "NTT size above 2^27");
@@ -229,7 +230,7 @@ int b200_groth16_compute_h(b200_ctx* ctx, int curve, const uint64_t* a, const ui
     B2_CUDA(ctx, cudaMemcpyAsync(h_out, buf[0].p, n * sizeof(Fr), cudaMemcpyDeviceToHost, ctx->stream));
     B2_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     return B200_OK;
-}
+} B2_ABI_CATCH_CTX(ctx)
 
 // ---- MSM ---------------------------------------------------------------------------------
 // H2D of n points (raw != 0: gnark-crypto RawEncoding bytes, converted in place on the device) into dst
@@ -252,7 +253,7 @@ static int copy_points(b200_ctx* ctx, DevBuf& dst, const void* host, size_t n, i
     return B200_OK;
 }
 
-int b200_points_from_raw(b200_ctx* ctx, int curve, int group, const uint8_t* raw, size_t n, uint64_t* out_affine) {
+int b200_points_from_raw(b200_ctx* ctx, int curve, int group, const uint8_t* raw, size_t n, uint64_t* out_affine) try {
     B2_ENTER(ctx, curve);
     if (n && (!raw || !out_affine)) return ctx->fail(B200_ERR_ARG, "null argument");
     if (group != 1 && group != 2) return ctx->fail(B200_ERR_ARG, "group must be 1 or 2");
@@ -261,18 +262,18 @@ int b200_points_from_raw(b200_ctx* ctx, int curve, int group, const uint8_t* raw
     if (n) B2_CUDA(ctx, cudaMemcpyAsync(out_affine, d.p, d.bytes, cudaMemcpyDeviceToHost, ctx->stream));
     B2_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     return B200_OK;
-}
+} B2_ABI_CATCH_CTX(ctx)
 
 static int bases_upload_impl(b200_ctx* ctx, int group, const void* host, size_t n, int raw, b200_bases** out);
 
-int b200_bases_upload(b200_ctx* ctx, int curve, int group, const uint64_t* bases_affine, size_t n, b200_bases** out) {
+int b200_bases_upload(b200_ctx* ctx, int curve, int group, const uint64_t* bases_affine, size_t n, b200_bases** out) try {
     B2_ENTER(ctx, curve);
     return bases_upload_impl(ctx, group, bases_affine, n, 0, out);
-}
-int b200_bases_upload_raw(b200_ctx* ctx, int curve, int group, const uint8_t* raw, size_t n, b200_bases** out) {
+} B2_ABI_CATCH_CTX(ctx)
+int b200_bases_upload_raw(b200_ctx* ctx, int curve, int group, const uint8_t* raw, size_t n, b200_bases** out) try {
     B2_ENTER(ctx, curve);
     return bases_upload_impl(ctx, group, raw, n, 1, out);
-}
+} B2_ABI_CATCH_CTX(ctx)
 
 static int bases_upload_impl(b200_ctx* ctx, int group, const void* host, size_t n, int raw, b200_bases** out) {
     if (!out || (n && !host)) return ctx->fail(B200_ERR_ARG, "null argument");
@@ -298,25 +299,25 @@ static int bases_upload_impl(b200_ctx* ctx, int group, const void* host, size_t 
     *out = b;
     return B200_OK;
 }
-int b200_bases_free(b200_ctx* ctx, b200_bases* bases) {
+int b200_bases_free(b200_ctx* ctx, b200_bases* bases) try {
     B2_ENTER(ctx, BUILD_CURVE);
     B2_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     delete bases;
     return B200_OK;
-}
+} B2_ABI_CATCH_CTX(ctx)
 
 static void fill_set_info(b200_ctx* ctx, size_t n, size_t bytes, const MsmFold& f, b200_msm_set_info* o) {
     const MsmPlan p = f.c ? msm_plan_folded(f.c) : msm_plan(n, ctx->msm_c_override);
     o->n = n; o->device_bytes = bytes; o->c = p.c; o->windows = p.W; o->folded = p.fold; o->reserved = 0;
 }
-int b200_bases_info(b200_ctx* ctx, const b200_bases* bases, b200_msm_set_info* out) {
+int b200_bases_info(b200_ctx* ctx, const b200_bases* bases, b200_msm_set_info* out) try {
     if (!ctx) return B200_ERR_ARG;
     if (!bases || !out) return ctx->fail(B200_ERR_ARG, "null argument");
     fill_set_info(ctx, bases->n, bases->pts.bytes, bases->fold, out);
     return B200_OK;
-}
+} B2_ABI_CATCH_CTX(ctx)
 
-int b200_msm_dev(b200_ctx* ctx, const b200_bases* bases, const void* scalars_dev, size_t n, uint64_t* out_jac, float* kernel_ms) {
+int b200_msm_dev(b200_ctx* ctx, const b200_bases* bases, const void* scalars_dev, size_t n, uint64_t* out_jac, float* kernel_ms) try {
     B2_ENTER(ctx, BUILD_CURVE);
     if (!bases || !out_jac || (n && !scalars_dev)) return ctx->fail(B200_ERR_ARG, "null argument");
     if (n > bases->n) return ctx->fail(B200_ERR_ARG, "more scalars than resident bases");
@@ -334,16 +335,16 @@ int b200_msm_dev(b200_ctx* ctx, const b200_bases* bases, const void* scalars_dev
     B2_CUDA(ctx, cudaEventSynchronize(ctx->ev1));
     if (kernel_ms) B2_CUDA(ctx, cudaEventElapsedTime(kernel_ms, ctx->ev0, ctx->ev1));
     return B200_OK;
-}
+} B2_ABI_CATCH_CTX(ctx)
 
-int b200_msm_resident(b200_ctx* ctx, const b200_bases* bases, const uint64_t* scalars, size_t n, uint64_t* out_jac) {
+int b200_msm_resident(b200_ctx* ctx, const b200_bases* bases, const uint64_t* scalars, size_t n, uint64_t* out_jac) try {
     B2_ENTER(ctx, BUILD_CURVE);
     if (n && !scalars) return ctx->fail(B200_ERR_ARG, "null scalars");
     DevBuf ds;
     B2_CUDA(ctx, ds.alloc(n * sizeof(Fr)));
     if (n) B2_CUDA(ctx, cudaMemcpyAsync(ds.p, scalars, n * sizeof(Fr), cudaMemcpyHostToDevice, ctx->stream));
     return b200_msm_dev(ctx, bases, ds.p, n, out_jac, nullptr);
-}
+} B2_ABI_CATCH_CTX(ctx)
 
 static int msm_host(b200_ctx* ctx, int curve, int group, const uint64_t* scalars, const uint64_t* bases_affine, size_t n, uint64_t* out_jac) {
     B2_ENTER(ctx, curve);
@@ -359,15 +360,15 @@ static int msm_host(b200_ctx* ctx, int curve, int group, const uint64_t* scalars
     delete b;
     return st;
 }
-int b200_msm_g1(b200_ctx* ctx, int curve, const uint64_t* scalars, const uint64_t* bases_affine, size_t n, uint64_t* out_jac) {
+int b200_msm_g1(b200_ctx* ctx, int curve, const uint64_t* scalars, const uint64_t* bases_affine, size_t n, uint64_t* out_jac) try {
     return msm_host(ctx, curve, 1, scalars, bases_affine, n, out_jac);
-}
-int b200_msm_g2(b200_ctx* ctx, int curve, const uint64_t* scalars, const uint64_t* bases_affine, size_t n, uint64_t* out_jac) {
+} B2_ABI_CATCH_CTX(ctx)
+int b200_msm_g2(b200_ctx* ctx, int curve, const uint64_t* scalars, const uint64_t* bases_affine, size_t n, uint64_t* out_jac) try {
     return msm_host(ctx, curve, 2, scalars, bases_affine, n, out_jac);
-}
+} B2_ABI_CATCH_CTX(ctx)
 
 int b200_batch_scalar_mul(b200_ctx* ctx, int curve, int group, const uint64_t* base_affine, const uint64_t* scalars,
-                          size_t n, uint64_t* out_affine) {
+                          size_t n, uint64_t* out_affine) try {
     B2_ENTER(ctx, curve);
     if (!base_affine || (n && (!scalars || !out_affine))) return ctx->fail(B200_ERR_ARG, "null argument");
     if (group != 1 && group != 2) return ctx->fail(B200_ERR_ARG, "group must be 1 or 2");
@@ -386,26 +387,26 @@ int b200_batch_scalar_mul(b200_ctx* ctx, int curve, int group, const uint64_t* b
     if (n) B2_CUDA(ctx, cudaMemcpyAsync(out_affine, dout.p, n * psz, cudaMemcpyDeviceToHost, ctx->stream));
     B2_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     return B200_OK;
-}
+} B2_ABI_CATCH_CTX(ctx)
 
 // ---- Groth16 -----------------------------------------------------------------------------
-int b200_groth16_pk_upload(b200_ctx* ctx, int curve, const b200_groth16_pk_desc* desc, b200_groth16_pk** out) {
+int b200_groth16_pk_upload(b200_ctx* ctx, int curve, const b200_groth16_pk_desc* desc, b200_groth16_pk** out) try {
     B2_ENTER(ctx, curve);
     return groth16_pk_upload(ctx, desc, out);
-}
+} B2_ABI_CATCH_CTX(ctx)
 int b200_groth16_setup(b200_ctx* ctx, int curve, const b200_groth16_setup_desc* desc, b200_groth16_pk** pk_out,
-                       b200_groth16_setup_out* out) {
+                       b200_groth16_setup_out* out) try {
     B2_ENTER(ctx, curve);
     if (pk_out) *pk_out = nullptr;
     return groth16_setup(ctx, desc, pk_out, out);
-}
-int b200_groth16_pk_free(b200_ctx* ctx, b200_groth16_pk* pk) {
+} B2_ABI_CATCH_CTX(ctx)
+int b200_groth16_pk_free(b200_ctx* ctx, b200_groth16_pk* pk) try {
     B2_ENTER(ctx, BUILD_CURVE);
     B2_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     delete pk;
     return B200_OK;
-}
-int b200_groth16_pk_info(b200_ctx* ctx, const b200_groth16_pk* pk, b200_msm_set_info out[5]) {
+} B2_ABI_CATCH_CTX(ctx)
+int b200_groth16_pk_info(b200_ctx* ctx, const b200_groth16_pk* pk, b200_msm_set_info out[5]) try {
     if (!ctx) return B200_ERR_ARG;
     if (!pk || !out) return ctx->fail(B200_ERR_ARG, "null argument");
     fill_set_info(ctx, pk->n_a, pk->A.bytes, pk->fA, out + 0);
@@ -414,43 +415,43 @@ int b200_groth16_pk_info(b200_ctx* ctx, const b200_groth16_pk* pk, b200_msm_set_
     fill_set_info(ctx, pk->n_z, pk->Z.bytes, pk->fZ, out + 3);
     fill_set_info(ctx, pk->n_b, pk->G2B.bytes, pk->fG2B, out + 4);
     return B200_OK;
-}
-int b200_groth16_pk_wire_range(b200_ctx* ctx, const b200_groth16_pk* pk, size_t* lo, size_t* hi) {
+} B2_ABI_CATCH_CTX(ctx)
+int b200_groth16_pk_wire_range(b200_ctx* ctx, const b200_groth16_pk* pk, size_t* lo, size_t* hi) try {
     if (!ctx) return B200_ERR_ARG;
     if (!pk || !lo || !hi) return ctx->fail(B200_ERR_ARG, "null argument");
     *lo = pk->w_lo; *hi = pk->w_hi;
     return B200_OK;
-}
+} B2_ABI_CATCH_CTX(ctx)
 int b200_groth16_prove_core(b200_ctx* ctx, const b200_groth16_pk* pk, const uint64_t* a, const uint64_t* b,
                             const uint64_t* c, size_t n_constraints, const uint64_t* w, const uint32_t* k_remove,
-                            size_t n_remove, b200_groth16_out* out, b200_timings* timings) {
+                            size_t n_remove, b200_groth16_out* out, b200_timings* timings) try {
     B2_ENTER(ctx, BUILD_CURVE);
     if (!pk || !out || !w || (n_constraints && (!a || !b || !c)) || (n_remove && !k_remove))
         return ctx->fail(B200_ERR_ARG, "null argument");
     return groth16_prove_core(ctx, pk, a, b, c, n_constraints, w, k_remove, n_remove, nullptr, out, timings);
-}
+} B2_ABI_CATCH_CTX(ctx)
 
 int b200_groth16_prove_core_dev(b200_ctx* ctx, const b200_groth16_pk* pk, const void* a_dev, const void* b_dev,
                                 const void* c_dev, size_t n_constraints, const void* w_dev, b200_groth16_out* out,
-                                b200_timings* timings) {
+                                b200_timings* timings) try {
     B2_ENTER(ctx, BUILD_CURVE);
     if (!pk || !out || !w_dev || (n_constraints && (!a_dev || !b_dev || !c_dev)))
         return ctx->fail(B200_ERR_ARG, "null argument");
     return groth16_prove_core(ctx, pk, (const uint64_t*)a_dev, (const uint64_t*)b_dev, (const uint64_t*)c_dev,
                               n_constraints, (const uint64_t*)w_dev, nullptr, 0, nullptr, out, timings);
-}
+} B2_ABI_CATCH_CTX(ctx)
 
 int b200_groth16_msms_dev(b200_ctx* ctx, const b200_groth16_pk* pk, const void* w_dev, const void* h_dev,
-                          b200_groth16_out* out, b200_timings* timings) {
+                          b200_groth16_out* out, b200_timings* timings) try {
     B2_ENTER(ctx, BUILD_CURVE);
     if (!pk || !out || !w_dev || !h_dev) return ctx->fail(B200_ERR_ARG, "null argument");
     return groth16_prove_core(ctx, pk, nullptr, nullptr, nullptr, 0, (const uint64_t*)w_dev, nullptr, 0,
                               (const uint64_t*)h_dev, out, timings);
-}
+} B2_ABI_CATCH_CTX(ctx)
 
 // ---- distributed computeH phases ------------------------------------------------------------
 int b200_ntt_dist_phase(b200_ctx* ctx, int curve, unsigned log_n, const uint64_t* generator, const uint64_t* coset_gen,
-                        void* data_dev, void* tmp_dev, unsigned log_ranks, unsigned rank, int phase, int inverse, int scale) {
+                        void* data_dev, void* tmp_dev, unsigned log_ranks, unsigned rank, int phase, int inverse, int scale) try {
     B2_ENTER(ctx, curve);
     if (!data_dev || !tmp_dev) return ctx->fail(B200_ERR_ARG, "null buffer");
     if (phase < B200_DIST_PACK || phase > B200_DIST_DIT_CROSS) return ctx->fail(B200_ERR_ARG, "bad phase");
@@ -470,39 +471,39 @@ int b200_ntt_dist_phase(b200_ctx* ctx, int curve, unsigned log_n, const uint64_t
     if (scale != B200_SCALE_NONE && phase != B200_DIST_DIF_CROSS && phase != B200_DIST_DIT_CROSS)
         return ctx->fail(B200_ERR_ARG, "a scale applies to the last (cross) phase of a transform");
     return ntt_dist_phase(ctx, d, (Fr*)data_dev, (Fr*)tmp_dev, log_ranks, rank, phase, inverse, post, scalar);
-}
+} B2_ABI_CATCH_CTX(ctx)
 
-int b200_fr_mul_sub_dev(b200_ctx* ctx, int curve, void* a_dev, const void* b_dev, const void* c_dev, size_t n) {
+int b200_fr_mul_sub_dev(b200_ctx* ctx, int curve, void* a_dev, const void* b_dev, const void* c_dev, size_t n) try {
     B2_ENTER(ctx, curve);
     if (n && (!a_dev || !b_dev || !c_dev)) return ctx->fail(B200_ERR_ARG, "null buffer");
     return ntt_mul_sub(ctx, (Fr*)a_dev, (const Fr*)b_dev, (const Fr*)c_dev, n);
-}
+} B2_ABI_CATCH_CTX(ctx)
 
-int b200_use_stream(b200_ctx* ctx, void* cuda_stream) {
+int b200_use_stream(b200_ctx* ctx, void* cuda_stream) try {
     if (!ctx) return B200_ERR_ARG;
     if (set_device(ctx) != B200_OK) return B200_ERR_CUDA;
     B2_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     ctx->stream = cuda_stream ? (cudaStream_t)cuda_stream : ctx->own_stream;
     return B200_OK;
-}
+} B2_ABI_CATCH_CTX(ctx)
 
 // ---- PlonK building blocks -----------------------------------------------------------------
-int b200_fr_batch_inverse_dev(b200_ctx* ctx, int curve, const void* in_dev, void* out_dev, size_t n) {
+int b200_fr_batch_inverse_dev(b200_ctx* ctx, int curve, const void* in_dev, void* out_dev, size_t n) try {
     B2_ENTER(ctx, curve);
     if (n && (!in_dev || !out_dev)) return ctx->fail(B200_ERR_ARG, "null buffer");
     if (in_dev == out_dev && n) return ctx->fail(B200_ERR_ARG, "batch inverse: in and out must not alias");
     B2_TRY(fr_batch_inverse(ctx, (const Fr*)in_dev, (Fr*)out_dev, n));
     B2_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     return B200_OK;
-}
-int b200_fr_prefix_product_dev(b200_ctx* ctx, int curve, const void* in_dev, void* out_dev, size_t n) {
+} B2_ABI_CATCH_CTX(ctx)
+int b200_fr_prefix_product_dev(b200_ctx* ctx, int curve, const void* in_dev, void* out_dev, size_t n) try {
     B2_ENTER(ctx, curve);
     if (n && (!in_dev || !out_dev)) return ctx->fail(B200_ERR_ARG, "null buffer");
     B2_TRY(fr_prefix_product(ctx, (const Fr*)in_dev, (Fr*)out_dev, n));
     B2_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     return B200_OK;
-}
-int b200_fr_poly_eval_dev(b200_ctx* ctx, int curve, const void* coeffs_dev, size_t n, const uint64_t* x, uint64_t* value) {
+} B2_ABI_CATCH_CTX(ctx)
+int b200_fr_poly_eval_dev(b200_ctx* ctx, int curve, const void* coeffs_dev, size_t n, const uint64_t* x, uint64_t* value) try {
     B2_ENTER(ctx, curve);
     if (!x || !value || (n && !coeffs_dev)) return ctx->fail(B200_ERR_ARG, "null argument");
     Fr xx, out;
@@ -510,8 +511,8 @@ int b200_fr_poly_eval_dev(b200_ctx* ctx, int curve, const void* coeffs_dev, size
     B2_TRY(fr_poly_eval(ctx, (const Fr*)coeffs_dev, n, xx, &out));
     memcpy(value, out.l, 32);
     return B200_OK;
-}
-int b200_fr_poly_div_linear_dev(b200_ctx* ctx, int curve, const void* coeffs_dev, size_t n, const uint64_t* z, void* quotient_dev) {
+} B2_ABI_CATCH_CTX(ctx)
+int b200_fr_poly_div_linear_dev(b200_ctx* ctx, int curve, const void* coeffs_dev, size_t n, const uint64_t* z, void* quotient_dev) try {
     B2_ENTER(ctx, curve);
     if (!z || (n > 1 && (!coeffs_dev || !quotient_dev))) return ctx->fail(B200_ERR_ARG, "null argument");
     if (coeffs_dev == quotient_dev && n > 1) return ctx->fail(B200_ERR_ARG, "division: coefficients and quotient must not alias");
@@ -520,9 +521,9 @@ int b200_fr_poly_div_linear_dev(b200_ctx* ctx, int curve, const void* coeffs_dev
     B2_TRY(fr_poly_div_linear(ctx, (const Fr*)coeffs_dev, n, zz, (Fr*)quotient_dev));
     B2_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     return B200_OK;
-}
+} B2_ABI_CATCH_CTX(ctx)
 int b200_plonk_divide_by_xn_minus_one_dev(b200_ctx* ctx, int curve, void* vec_dev, unsigned log_big, unsigned log_small,
-                                          const uint64_t* generator_big, const uint64_t* coset_gen) {
+                                          const uint64_t* generator_big, const uint64_t* coset_gen) try {
     B2_ENTER(ctx, curve);
     if (!vec_dev || !generator_big || !coset_gen) return ctx->fail(B200_ERR_ARG, "null argument");
     if (log_small > log_big || log_big - log_small > 3 || log_big > 27) return ctx->fail(B200_ERR_ARG, "rho = 2^(log_big - log_small) must be 1, 2, 4 or 8");
@@ -531,19 +532,19 @@ int b200_plonk_divide_by_xn_minus_one_dev(b200_ctx* ctx, int curve, void* vec_de
     B2_TRY(plonk_divide_xn(ctx, d, log_small, (Fr*)vec_dev));
     B2_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     return B200_OK;
-}
-int b200_kzg_commit_dev(b200_ctx* ctx, const b200_bases* srs, const void* coeffs_dev, size_t n, uint64_t* out_affine) {
+} B2_ABI_CATCH_CTX(ctx)
+int b200_kzg_commit_dev(b200_ctx* ctx, const b200_bases* srs, const void* coeffs_dev, size_t n, uint64_t* out_affine) try {
     B2_ENTER(ctx, BUILD_CURVE);
     if (!srs || !out_affine || (n && !coeffs_dev)) return ctx->fail(B200_ERR_ARG, "null argument");
     if (srs->group != 1) return ctx->fail(B200_ERR_ARG, "the KZG SRS is a G1 base set");
     uint64_t jac[3 * B200_FP_WORDS];
     B2_TRY(b200_msm_dev(ctx, srs, coeffs_dev, n, jac, nullptr));
     return b200_g1_jac_to_affine(jac, out_affine);
-}
+} B2_ABI_CATCH_CTX(ctx)
 
 int b200_plonk_build_ratio_dev(b200_ctx* ctx, int curve, const void* l_dev, const void* r_dev, const void* o_dev,
                                const void* perm_dev, const uint64_t* beta, const uint64_t* gamma, unsigned log_n,
-                               const uint64_t* generator, const uint64_t* coset_gen, void* z_out_dev) {
+                               const uint64_t* generator, const uint64_t* coset_gen, void* z_out_dev) try {
     B2_ENTER(ctx, curve);
     if (!l_dev || !r_dev || !o_dev || !perm_dev || !beta || !gamma || !generator || !coset_gen || !z_out_dev)
         return ctx->fail(B200_ERR_ARG, "null argument");
@@ -556,8 +557,8 @@ int b200_plonk_build_ratio_dev(b200_ctx* ctx, int curve, const void* l_dev, cons
     B2_TRY(plonk_build_ratio(ctx, d, (const Fr*)l_dev, (const Fr*)r_dev, (const Fr*)o_dev, (const int64_t*)perm_dev, b, g, (Fr*)z_out_dev));
     B2_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     return B200_OK;
-}
-int b200_plonk_quotient_rows_dev(b200_ctx* ctx, int curve, const b200_plonk_rows_desc* desc, void* cres_dev) {
+} B2_ABI_CATCH_CTX(ctx)
+int b200_plonk_quotient_rows_dev(b200_ctx* ctx, int curve, const b200_plonk_rows_desc* desc, void* cres_dev) try {
     B2_ENTER(ctx, curve);
     if (!desc || !cres_dev || !desc->generator_small) return ctx->fail(B200_ERR_ARG, "null argument");
     if (desc->nb_bsb > 8) return ctx->fail(B200_ERR_UNSUPPORTED, "more than 8 BSB22 commitments");
@@ -590,10 +591,10 @@ int b200_plonk_quotient_rows_dev(b200_ctx* ctx, int curve, const b200_plonk_rows
     B2_TRY(plonk_quotient_rows(ctx, a));
     B2_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     return B200_OK;
-}
+} B2_ABI_CATCH_CTX(ctx)
 
 // ---- tuning knobs -------------------------------------------------------------------------
-int b200_set_option(b200_ctx* ctx, const char* key, long value) {
+int b200_set_option(b200_ctx* ctx, const char* key, long value) try {
     if (!ctx || !key) return B200_ERR_ARG;
     const std::string k(key);
     if (k == "msm_c") { if (value != 0 && (value < 4 || value > 24)) return ctx->fail(B200_ERR_ARG, "msm_c out of range"); ctx->msm_c_override = (int)value; }
@@ -608,10 +609,10 @@ int b200_set_option(b200_ctx* ctx, const char* key, long value) {
     else if (k == "ntt_threads") { if (value < 32 || value > 1024 || (value & (value - 1))) return ctx->fail(B200_ERR_ARG, "ntt_threads must be a power of two in 32..1024"); ctx->ntt_threads = (int)value; }
     else return ctx->fail(B200_ERR_ARG, "unknown option", key);
     return B200_OK;
-}
+} B2_ABI_CATCH_CTX(ctx)
 
 // ---- profiling ---------------------------------------------------------------------------
-int b200_profile_start(b200_ctx* ctx) {
+int b200_profile_start(b200_ctx* ctx) try {
     B2_ENTER(ctx, BUILD_CURVE);
     B2_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     for (auto& sp : ctx->prof_spans) { ctx->prof_pool.push_back(sp.e0); ctx->prof_pool.push_back(sp.e1); }
@@ -619,8 +620,8 @@ int b200_profile_start(b200_ctx* ctx) {
     ctx->prof_on = true;
     ctx->n_launches = 0;
     return B200_OK;
-}
-int b200_profile_read(b200_ctx* ctx, b200_profile* out) {
+} B2_ABI_CATCH_CTX(ctx)
+int b200_profile_read(b200_ctx* ctx, b200_profile* out) try {
     B2_ENTER(ctx, BUILD_CURVE);
     if (!out) return ctx->fail(B200_ERR_ARG, "null output");
     B2_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
@@ -640,6 +641,6 @@ int b200_profile_read(b200_ctx* ctx, b200_profile* out) {
     ctx->prof_spans.clear();
     ctx->prof_on = false;
     return B200_OK;
-}
+} B2_ABI_CATCH_CTX(ctx)
 
 }  // extern "C"

@@ -3,6 +3,8 @@
 #include <cuda_runtime.h>
 #include <cstdint>
 #include <cstdio>
+#include <new>
+#include <stdexcept>
 #include <string>
 #include <vector>
 #include "../../include/b200prover.h"
@@ -30,6 +32,8 @@ struct b200_ctx {
     size_t scratch_bytes = 0;
     void* poly_scratch = nullptr;           // small persistent scratch of the polynomial primitives (poly.cu), stream-ordered
     size_t poly_scratch_bytes = 0;
+    std::vector<cudaEvent_t> core_events;   // the prove core's events (groth16.cu)
+    std::vector<uint32_t> kmap_host;        // K wire map of the proof in flight (api.Commit circuits, groth16.cu)
     int msm_c_override = 0;                 // tuning knobs (b200_set_option / B200_MSM_C env)
     int msm_ba = 0;                         // batched-affine pre-reduction rounds (msm_ba.cuh); 0 = off
     int msm_ba_force = 0;                   // tests: keep the rounds on MSMs too small to profit
@@ -87,6 +91,24 @@ struct b200_ctx {
                                "CUDA error", buf_);                                            \
         }                                                                                      \
     } while (0)
+
+// No C++ exception may cross the C ABI: every extern "C" entry point is a function-try-block that ends
+// in one of these handlers (scripts/add_exception_barrier.py put them there).
+namespace b200 {
+inline int abi_fail(b200_ctx* ctx, int status, const char* what) noexcept {
+    try { if (ctx) ctx->fail(status, "exception stopped at the C ABI", what); } catch (...) {}
+    return status;
+}
+}  // namespace b200
+#define B2_ABI_CATCH_CTX(ctx)                                                                                    \
+    catch (const std::bad_alloc&) { return b200::abi_fail(ctx, B200_ERR_NOMEM, "host allocation failed"); }       \
+    catch (const std::exception& e_) { return b200::abi_fail(ctx, B200_ERR_INTERNAL, e_.what()); }                \
+    catch (...) { return b200::abi_fail(ctx, B200_ERR_INTERNAL, "unknown exception"); }
+#define B2_ABI_CATCH_INT                                           \
+    catch (const std::bad_alloc&) { return B200_ERR_NOMEM; }       \
+    catch (...) { return B200_ERR_INTERNAL; }
+#define B2_ABI_CATCH_VOID catch (...) {}
+#define B2_ABI_CATCH_NULL catch (...) { return nullptr; }
 
 #define B2_TRY(expr)                    \
     do {                                \

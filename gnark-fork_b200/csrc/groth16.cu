@@ -213,9 +213,13 @@ static float ev_ms(cudaEvent_t a, cudaEvent_t b) {
 
 int groth16_prove_core(b200_ctx* ctx, const b200_groth16_pk* pk, const uint64_t* a, const uint64_t* b,
                        const uint64_t* c, size_t n_constraints, const uint64_t* w, const uint32_t* k_remove,
-                       size_t n_remove, const uint64_t* h_local, b200_groth16_out* out, b200_timings* tm) {
+                       size_t n_remove, const uint64_t* h_local, b200_groth16_out* out, b200_timings* tm, const ProveHHook* hook) {
     const size_t n = (size_t)1 << pk->log_n;
-    if (h_local) n_constraints = 0;   // h comes from the distributed computeH: a, b, c are not read
+    // hook: computeH is the caller's (the group's distributed one, group.cu), enqueued where this function would run its
+    // own; h lands in hook->h_out.  Otherwise h_local != null means h was computed before the call.
+    const bool own_h = !h_local && !hook;      // a, b, c are copied into the workspace and transformed here
+    if (hook) h_local = reinterpret_cast<const uint64_t*>(hook->h_out);
+    if (!own_h) n_constraints = 0;   // h comes from the distributed computeH: a, b, c are not read
     if (n_constraints > n) return ctx->fail(B200_ERR_ARG, "more constraints than the domain holds");
     if (n_remove && pk->full_n_k + n_remove != pk->n_wires - pk->nb_public)
         return ctx->fail(B200_ERR_ARG, "k_remove does not match len(pk.G1.K)");
@@ -236,7 +240,7 @@ int groth16_prove_core(b200_ctx* ctx, const b200_groth16_pk* pk, const uint64_t*
     }
     const bool overlap = ctx->msm_overlap != 0;
     Arena ar;
-    const size_t n_abc = h_local ? 0 : n;
+    const size_t n_abc = own_h ? n : 0;
     const size_t o_a = ar.off; ar.take(n_abc * sizeof(Fr));
     const size_t o_b = ar.off; ar.take(n_abc * sizeof(Fr));
     const size_t o_c = ar.off; ar.take(n_abc * sizeof(Fr));
@@ -262,10 +266,13 @@ int groth16_prove_core(b200_ctx* ctx, const b200_groth16_pk* pk, const uint64_t*
     cudaStream_t sx = overlap ? ctx->aux_stream : st;
     cudaStream_t cp = ctx->copy_stream;
 
-    constexpr int NEV = 24;
-    cudaEvent_t ev[NEV];
-    for (auto& e : ev) B2_CUDA(ctx, cudaEventCreate(&e));
-    struct EvGuard { cudaEvent_t* e; ~EvGuard() { for (int i = 0; i < NEV; ++i) cudaEventDestroy(e[i]); } } guard{ev};
+    constexpr int NEV = 24;     // created once per ctx, reused by every proof (freed by b200_destroy)
+    while (ctx->core_events.size() < NEV) {
+        cudaEvent_t e;
+        B2_CUDA(ctx, cudaEventCreate(&e));
+        ctx->core_events.push_back(e);
+    }
+    cudaEvent_t* ev = ctx->core_events.data();
     cudaEvent_t ev_w = ev[9], ev_abc = ev[10], ev_h = ev[11];
     cudaEvent_t* ev_sort = ev + 12;   // [5]
     cudaEvent_t* ev_acc = ev + 17;    // [5]
@@ -278,32 +285,34 @@ int groth16_prove_core(b200_ctx* ctx, const b200_groth16_pk* pk, const uint64_t*
     const int span = ctx->prof_begin(B200_PROF_COPY_IN, (double)(3 * n_constraints + n_w) * sizeof(Fr), cp);
     if (n_w) B2_CUDA(ctx, cudaMemcpyAsync(d_w, w + 4 * pk->w_lo, n_w * sizeof(Fr), cudaMemcpyDefault, cp));
     if (n_remove) {
-        // prove.go:238-242: K scalars are W[nb_public:] minus the committed wires
-        std::vector<uint32_t> map;
+        // prove.go:238-242: K scalars are W[nb_public:] minus the committed wires.  The map lives in the ctx until the
+        // next proof, so the copy needs no host synchronisation in the middle of the enqueue.
+        std::vector<uint32_t>& map = ctx->kmap_host;
+        map.clear();
         map.reserve(pk->full_n_k);
         size_t r = 0;
         for (size_t i = 0; i < pk->n_wires - pk->nb_public; ++i) {
             if (r < n_remove && k_remove[r] == i) { ++r; continue; }
             map.push_back((uint32_t)(pk->nb_public + i - pk->w_lo));
         }
-        if (map.size() != pk->full_n_k) return ctx->fail(B200_ERR_ARG, "k_remove must be sorted and unique");
+        if (map.size() != pk->full_n_k || r != n_remove) return ctx->fail(B200_ERR_ARG, "k_remove must be sorted, unique and inside W[nb_public:]");
         B2_CUDA(ctx, cudaMemcpyAsync(d_kmap, map.data() + pk->k_lo, pk->n_k * 4, cudaMemcpyHostToDevice, cp));
-        B2_CUDA(ctx, cudaStreamSynchronize(cp));  // `map` dies at scope exit
     }
     B2_CUDA(ctx, cudaEventRecord(ev_w, cp));
     const uint64_t* src[3] = {a, b, c};
     Fr* dst[3] = {d_a, d_b, d_c};
-    for (int i = 0; i < 3 && !h_local; ++i) {
+    for (int i = 0; i < 3 && own_h; ++i) {
         if (n_constraints) B2_CUDA(ctx, cudaMemcpyAsync(dst[i], src[i], n_constraints * sizeof(Fr), cudaMemcpyDefault, cp));
         if (n > n_constraints) B2_CUDA(ctx, cudaMemsetAsync(dst[i] + n_constraints, 0, (n - n_constraints) * sizeof(Fr), cp));
     }
+    if (hook) B2_TRY(hook->copy_abc(cp));
     ctx->prof_end(span, cp);
     B2_CUDA(ctx, cudaEventRecord(ev_abc, cp));
 
     // computeH goes first when a, b, c are already on the device (nothing to wait for), else after
     // the first MSM (by then the host copies have landed)
-    bool h_first = false;
-    if (!h_local && n_constraints) {
+    bool h_first = hook ? hook->inputs_on_device : false;
+    if (own_h && n_constraints) {
         cudaPointerAttributes pa;
         if (cudaPointerGetAttributes(&pa, a) == cudaSuccess) h_first = pa.type == cudaMemoryTypeDevice;
         else cudaGetLastError();
@@ -327,7 +336,8 @@ int groth16_prove_core(b200_ctx* ctx, const b200_groth16_pk* pk, const uint64_t*
     auto run_h = [&]() -> int {
         B2_CUDA(ctx, cudaStreamWaitEvent(st, ev_abc, 0));
         B2_CUDA(ctx, cudaEventRecord(ev[6], st));
-        B2_TRY(ntt_compute_h(ctx, pk->dom, d_a, d_b, d_c));
+        if (hook) B2_TRY(hook->compute_h());
+        else B2_TRY(ntt_compute_h(ctx, pk->dom, d_a, d_b, d_c));
         B2_CUDA(ctx, cudaEventRecord(ev[7], st));
         B2_CUDA(ctx, cudaEventRecord(ev_h, st));
         return B200_OK;
@@ -336,7 +346,7 @@ int groth16_prove_core(b200_ctx* ctx, const b200_groth16_pk* pk, const uint64_t*
     // slots 0: A, K, Z;  1: B1, B2 -- so K waits for A, B2 for B1, Z for K
     auto run_sort = [&](int k) -> int {
         if (k < 4) B2_CUDA(ctx, cudaStreamWaitEvent(sx, ev_w, 0));
-        else if (!h_local) B2_CUDA(ctx, cudaStreamWaitEvent(sx, ev_h, 0));
+        else if (own_h || hook) B2_CUDA(ctx, cudaStreamWaitEvent(sx, ev_h, 0));
         if (k == 0 && h_first) B2_CUDA(ctx, cudaStreamWaitEvent(sx, ev_h, 0));  // the transforms and a sort only slow each other down
         if (k == 2) B2_CUDA(ctx, cudaStreamWaitEvent(sx, ev_acc[0], 0));
         if (k == 3) B2_CUDA(ctx, cudaStreamWaitEvent(sx, ev_acc[1], 0));
@@ -359,7 +369,7 @@ int groth16_prove_core(b200_ctx* ctx, const b200_groth16_pk* pk, const uint64_t*
         B2_TRY(run_sort(0));
         B2_TRY(run_sort(1));
         B2_TRY(run_acc(0));
-        if (!h_local && !h_first) B2_TRY(run_h());
+        if ((own_h || hook) && !h_first) B2_TRY(run_h());
         B2_TRY(run_sort(2));
         B2_TRY(run_acc(1));
         B2_TRY(run_sort(3));
@@ -369,7 +379,7 @@ int groth16_prove_core(b200_ctx* ctx, const b200_groth16_pk* pk, const uint64_t*
         B2_TRY(run_acc(4));
     } else {   // one stream, one sort group: strictly sort, accumulate, sort, ...
         for (int k = 0; k < 5; ++k) {
-            if (k == 1 && !h_local && !h_first) B2_TRY(run_h());
+            if (k == 1 && (own_h || hook) && !h_first) B2_TRY(run_h());
             B2_TRY(run_sort(k));
             B2_TRY(run_acc(k));
         }
@@ -399,7 +409,7 @@ int groth16_prove_core(b200_ctx* ctx, const b200_groth16_pk* pk, const uint64_t*
         tm->compute_h_ms = ev_ms(ev[6], ev[7]);
         const cudaEvent_t a_start = h_first ? ev[7] : ev[0];
         tm->msm_a_ms = ev_ms(a_start, ev_acc[0]);
-        tm->msm_b1_ms = ev_ms((!h_local && !h_first) ? ev[7] : ev_acc[0], ev_acc[1]);
+        tm->msm_b1_ms = ev_ms(((own_h || hook) && !h_first) ? ev[7] : ev_acc[0], ev_acc[1]);
         tm->msm_k_ms = ev_ms(ev_acc[1], ev_acc[2]);
         tm->msm_b2_ms = ev_ms(ev_acc[2], ev_acc[3]);
         tm->msm_z_ms = ev_ms(ev_acc[3], ev_acc[4]);

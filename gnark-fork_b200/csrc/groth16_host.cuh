@@ -1,5 +1,6 @@
 // Resident Groth16 proving key and the host entry points of groth16.cu / host_group.cu.
 #pragma once
+#include <functional>
 #include "ntt_host.cuh"
 #include "msm_host.cuh"
 
@@ -31,7 +32,17 @@ struct PkScalarSource {
 int groth16_pk_upload(b200_ctx* ctx, const b200_groth16_pk_desc* d, b200_groth16_pk** out, const PkScalarSource* gen_src = nullptr);
 // setup.cu
 int groth16_setup(b200_ctx* ctx, const b200_groth16_setup_desc* d, b200_groth16_pk** pk_out, b200_groth16_setup_out* out);
+// computeH supplied by the caller and enqueued at the point of the schedule where the prove core runs its own
+// (the group's distributed computeH, group.cu): copy_abc enqueues this rank's share of a, b, c on the copy stream `cp`
+// (after W's copy); compute_h enqueues the transforms on ctx->stream; h_out will hold this shard's range of h.
+struct ProveHHook {
+    std::function<int(cudaStream_t)> copy_abc;
+    std::function<int()> compute_h;
+    const Fr* h_out = nullptr;
+    bool inputs_on_device = false;     // computeH first (nothing to wait for), as for device-resident a, b, c
+};
 int groth16_prove_core(b200_ctx* ctx, const b200_groth16_pk* pk, const uint64_t* a, const uint64_t* b,
                        const uint64_t* c, size_t n_constraints, const uint64_t* w, const uint32_t* k_remove,
-                       size_t n_remove, const uint64_t* h_local, b200_groth16_out* out, b200_timings* tm);
+                       size_t n_remove, const uint64_t* h_local, b200_groth16_out* out, b200_timings* tm,
+                       const ProveHHook* hook = nullptr);
 }  // namespace b200

@@ -11,15 +11,15 @@ using namespace b200::hostgrp;
 
 extern "C" {
 
-int b200_g1_jac_add(const uint64_t* p, const uint64_t* q, uint64_t* out) { return jac_add<Fp>(p, q, out); }
-int b200_g2_jac_add(const uint64_t* p, const uint64_t* q, uint64_t* out) { return jac_add<Fp2>(p, q, out); }
-int b200_g1_jac_to_affine(const uint64_t* p, uint64_t* out) { return jac_aff<Fp>(p, out); }
-int b200_g2_jac_to_affine(const uint64_t* p, uint64_t* out) { return jac_aff<Fp2>(p, out); }
+int b200_g1_jac_add(const uint64_t* p, const uint64_t* q, uint64_t* out) try { return jac_add<Fp>(p, q, out); } B2_ABI_CATCH_INT
+int b200_g2_jac_add(const uint64_t* p, const uint64_t* q, uint64_t* out) try { return jac_add<Fp2>(p, q, out); } B2_ABI_CATCH_INT
+int b200_g1_jac_to_affine(const uint64_t* p, uint64_t* out) try { return jac_aff<Fp>(p, out); } B2_ABI_CATCH_INT
+int b200_g2_jac_to_affine(const uint64_t* p, uint64_t* out) try { return jac_aff<Fp2>(p, out); } B2_ABI_CATCH_INT
 
 int b200_groth16_finalize(const b200_groth16_out* msm, const uint64_t* r, const uint64_t* s,
                           const uint64_t* g1_alpha, const uint64_t* g1_beta, const uint64_t* g1_delta,
                           const uint64_t* g2_beta, const uint64_t* g2_delta, uint64_t* ar_affine,
-                          uint64_t* bs_affine, uint64_t* krs_affine) {
+                          uint64_t* bs_affine, uint64_t* krs_affine) try {
     if (!msm || !r || !s || !g1_alpha || !g1_beta || !g1_delta || !g2_beta || !g2_delta || !ar_affine ||
         !bs_affine || !krs_affine)
         return B200_ERR_ARG;
@@ -61,10 +61,10 @@ int b200_groth16_finalize(const b200_groth16_out* msm, const uint64_t* r, const 
     memcpy(bs_affine, &b_aff, sizeof b_aff);
     memcpy(krs_affine, &k_aff, sizeof k_aff);
     return B200_OK;
-}
+} B2_ABI_CATCH_INT
 
 int b200_groth16_proof_bytes(const uint64_t* ar_affine, const uint64_t* bs_affine, const uint64_t* krs_affine,
-                             uint8_t* out, size_t out_cap) {
+                             uint8_t* out, size_t out_cap) try {
     if (!ar_affine || !bs_affine || !krs_affine || !out) return B200_ERR_ARG;
     const size_t FB = FP_BYTES, total = 5 * FB + 4;   // 164 bytes on BN254, 244 on BLS12-377
     if (out_cap < total) return B200_ERR_ARG;
@@ -79,6 +79,6 @@ int b200_groth16_proof_bytes(const uint64_t* ar_affine, const uint64_t* bs_affin
     memset(out + 4 * FB, 0, 4);       // u32 len(Commitments) = 0, marshal.go:58
     g1_compress(G1Affine::inf(), out + 4 * FB + 4);  // CommitmentPok, marshal.go:61
     return (int)total;
-}
+} B2_ABI_CATCH_INT
 
 }  // extern "C"

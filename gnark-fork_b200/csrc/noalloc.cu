@@ -120,7 +120,7 @@ int na_prefix_rec(b200_ctx* ctx, const Fr* in, Fr* out, size_t n, Fr* scratch) {
 
 using namespace b200;
 
-extern "C" int b200_fr_prefix_product_static(b200_ctx* ctx, int curve, const void* in_dev, void* out_dev, size_t n) {
+extern "C" int b200_fr_prefix_product_static(b200_ctx* ctx, int curve, const void* in_dev, void* out_dev, size_t n) try {
     if (!ctx) return B200_ERR_ARG;
 #if defined(B2_CURVE_BLS12_377)
     if (curve != B200_BLS12_377) return ctx->fail(B200_ERR_UNSUPPORTED, "this library is the BLS12-377 build");
@@ -139,4 +139,4 @@ extern "C" int b200_fr_prefix_product_static(b200_ctx* ctx, int curve, const voi
     Fr* scratch = nullptr;
     B2_TRY(na_scratch_address(ctx, &scratch));
     return na_prefix_rec(ctx, (const Fr*)in_dev, (Fr*)out_dev, n, scratch);
-}
+} B2_ABI_CATCH_CTX(ctx)

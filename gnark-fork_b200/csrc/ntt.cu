@@ -55,6 +55,16 @@ __device__ __forceinline__ void st_fr(Fr* p, const Fr& f) {
     q[1] = make_uint4(f.l[4], f.l[5], f.l[6], f.l[7]);
 }
 
+// Pull mode of a cross phase (multi-GPU in one process, group.cu): the pass does not read a received buffer but loads
+// straight from the ranks' send buffers through peer-mapped pointers (NVLink P2P loads; the same device for virtual
+// ranks).  Buffer index bi = (source rank r << shift) | j is read from src[r] + off + j, off = this rank's chunk in r's
+// send buffer: the all-to-all is fused into the first load of the cross pass, 2^(TL - lg) * 32 B contiguous per row.
+struct NttPeerPull {
+    const Fr* src[NTT_MAX_RANKS];
+    uint32_t shift, off;
+    int on;
+};
+
 struct NttPassArgs {
     const Fr* src;   // loads   (== dst for an in-place pass)
     Fr* dst;         // stores, at smap(buffer index)
@@ -66,6 +76,7 @@ struct NttPassArgs {
     uint32_t glog_n, s_off;   // global transform size and stage offset (distributed phases)
     int has_post_scalar;
     Fr post_scalar;
+    NttPeerPull pull;
 };
 
 constexpr int NTT_THREADS = 1024;
@@ -80,7 +91,7 @@ __global__ void __launch_bounds__(NTT_THREADS) ntt_pass_kernel(const NttPassArgs
 
     for (uint32_t loc = threadIdx.x; loc < tile_n; loc += blockDim.x) {
         const uint32_t bi = ntt_gidx(g, tile, loc);
-        Fr v = ld_fr(a.src + bi);
+        Fr v = a.pull.on ? ld_fr(a.pull.src[bi >> a.pull.shift] + a.pull.off + (bi & ((1u << a.pull.shift) - 1u))) : ld_fr(a.src + bi);
         if (a.pre) v = v * ldg_fr(a.pre + ntt_map(a.gmap, bi));
         sm.put(loc, v);
     }
@@ -138,6 +149,19 @@ __global__ void permute_kernel(const Fr* __restrict__ src, Fr* __restrict__ dst,
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     st_fr(dst + ntt_map(smap, i), ld_fr(src + i));
+}
+
+// PACK fused with its all-to-all (multi-GPU in one process): element i of this rank's natural-order block goes to rank
+// q = i mod R, slot (rank << m) | (i >> lg) of q's buffer -- written straight into the peer's memory.  blockIdx.y = q;
+// consecutive threads take consecutive slots: 1 KiB contiguous peer stores per warp, the strided local reads of the R
+// blocks of one row share their cache lines in L2.
+struct NttPeerPush {
+    Fr* dst[NTT_MAX_RANKS];
+};
+__global__ void pack_push_kernel(const Fr* __restrict__ src, const NttPeerPush peers, uint32_t lg, uint32_t m, uint32_t rank) {
+    const uint32_t off = blockIdx.x * blockDim.x + threadIdx.x, q = blockIdx.y;
+    if (off >> m) return;
+    st_fr(peers.dst[q] + ((size_t)rank << m) + off, ld_fr(src + (((size_t)off << lg) | q)));
 }
 
 __global__ void mul_sub_kernel(Fr* a, const Fr* b, const Fr* c, size_t n) {
@@ -256,6 +280,7 @@ int ntt_run(b200_ctx* ctx, NttDomain* d, Fr* data, int inverse, int dit, const F
         a.s_off = 0;
         a.has_post_scalar = (i == np - 1 && post_scalar) ? 1 : 0;
         a.post_scalar = post_scalar ? *post_scalar : Fr::one();
+        a.pull.on = 0;
         B2_TRY(ntt_launch_pass(ctx, a, dit, d->n()));
     }
     return B200_OK;
@@ -264,8 +289,10 @@ int ntt_run(b200_ctx* ctx, NttDomain* d, Fr* data, int inverse, int dit, const F
 // One phase of a transform distributed over 2^lg ranks (ntt.cuh).  `data` and `tmp` are this
 // rank's two buffers of n >> lg elements; see NttDistPhase for which one a phase reads and writes.
 int ntt_dist_phase(b200_ctx* ctx, NttDomain* d, Fr* data, Fr* tmp, uint32_t lg, uint32_t rank, int kind, int inverse,
-                   const Fr* post, const Fr* post_scalar) {
+                   const Fr* post, const Fr* post_scalar, const Fr* const* peer_src) {
     B2_TRY(ntt_prepare(ctx));
+    if (peer_src && (kind != NTT_DIST_DIF_CROSS && kind != NTT_DIST_DIT_CROSS)) return ctx->fail(B200_ERR_ARG, "peer pull applies to a cross phase");
+    if (peer_src && lg > 4) return ctx->fail(B200_ERR_UNSUPPORTED, "more than 16 ranks");
     if (lg == 0 || 2 * lg > d->log_n) return ctx->fail(B200_ERR_ARG, "distributed NTT needs 1 <= log2(ranks) <= log_n / 2");
     if (rank >> lg) return ctx->fail(B200_ERR_ARG, "rank out of range");
     const uint32_t log_loc = d->log_n - lg;
@@ -305,8 +332,29 @@ int ntt_dist_phase(b200_ctx* ctx, NttDomain* d, Fr* data, Fr* tmp, uint32_t lg, 
         a.s_off = ph.s_off;
         a.has_post_scalar = (last && post_scalar) ? 1 : 0;
         a.post_scalar = post_scalar ? *post_scalar : Fr::one();
+        a.pull.on = 0;
+        if (peer_src) {     // cross phase fused with its exchange: load from the ranks' send buffers, store to `data`
+            a.pull.on = 1;
+            a.pull.shift = d->log_n - 2u * lg;
+            a.pull.off = rank << a.pull.shift;
+            for (uint32_t r = 0; r < (1u << lg); ++r) a.pull.src[r] = peer_src[r];
+            a.src = nullptr;
+            a.dst = data;
+        }
         B2_TRY(ntt_launch_pass(ctx, a, ph.dit, n_loc));
     }
+    return B200_OK;
+}
+
+int ntt_dist_pack_push(b200_ctx* ctx, NttDomain* d, const Fr* block, Fr* const* peer_dst, uint32_t lg, uint32_t rank) {
+    if (lg == 0 || lg > 4 || 2 * lg > d->log_n) return ctx->fail(B200_ERR_ARG, "distributed NTT needs 1 <= log2(ranks) <= min(4, log_n / 2)");
+    const uint32_t m = d->log_n - 2u * lg;
+    NttPeerPush peers;
+    for (uint32_t r = 0; r < (1u << lg); ++r) peers.dst[r] = peer_dst[r];
+    const uint32_t bs = 256, chunk = 1u << m;
+    pack_push_kernel<<<dim3((chunk + bs - 1) / bs, 1u << lg), bs, 0, ctx->stream>>>(block, peers, lg, m, rank);
+    ctx->n_launches += 1;
+    B2_CUDA(ctx, cudaGetLastError());
     return B200_OK;
 }
 

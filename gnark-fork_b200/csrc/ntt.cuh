@@ -115,6 +115,8 @@ B2_HD uint32_t ntt_map(const NttIndexMap& p, uint32_t i) {
     return ((i >> p.m) << p.sh_hi) | ((i & ((1u << p.m) - 1u)) << p.sh_lo) | p.add;
 }
 
+constexpr int NTT_MAX_RANKS = 16;   // ranks of a distributed transform whose exchange is fused over peer memory (ntt.cu: NttPeerPull)
+
 enum NttDistPhaseKind { NTT_DIST_PACK = 0, NTT_DIST_DIF_LOCAL, NTT_DIST_DIF_CROSS, NTT_DIST_DIT_LOCAL, NTT_DIST_DIT_CROSS };
 
 struct NttDistPhase {

@@ -36,8 +36,13 @@ void ntt_domain_free_all(b200_ctx* ctx);
 int ntt_run(b200_ctx* ctx, NttDomain* d, Fr* data, int inverse, int dit, const Fr* pre, const Fr* post,
             const Fr* post_scalar);
 // one phase of a transform distributed over 2^lg ranks (ntt.cuh: NttDistPhaseKind)
+// peer_src (cross phases only, optional): the 2^lg ranks' send buffers (peer-mapped device pointers); the phase then
+// LOADS its input from them -- chunk `rank` of each -- instead of reading a received buffer, and stores to `data`.
 int ntt_dist_phase(b200_ctx* ctx, NttDomain* d, Fr* data, Fr* tmp, uint32_t lg, uint32_t rank, int kind, int inverse,
-                   const Fr* post, const Fr* post_scalar);
+                   const Fr* post, const Fr* post_scalar, const Fr* const* peer_src = nullptr);
+// PACK fused with its all-to-all: this rank's natural-order block is scattered into the ranks' buffers peer_dst[q]
+// (slot (rank << m) | (i >> lg) for element i, q = i mod 2^lg).
+int ntt_dist_pack_push(b200_ctx* ctx, NttDomain* d, const Fr* block, Fr* const* peer_dst, uint32_t lg, uint32_t rank);
 // gnark-crypto semantics (Domain.FFT / FFTInverse with optional OnCoset)
 int ntt_gnark(b200_ctx* ctx, NttDomain* d, Fr* data, int inverse, int dit, int on_coset);
 // a[i] = a[i]*b[i] - c[i]

@@ -332,7 +332,7 @@ static void plonk_pk_delete(b200_ctx* ctx, b200_plonk_pk* pk) {
 
 extern "C" {
 
-int b200_plonk_pk_upload(b200_ctx* ctx, int curve, const b200_plonk_pk_desc* d, b200_plonk_pk** out) {
+int b200_plonk_pk_upload(b200_ctx* ctx, int curve, const b200_plonk_pk_desc* d, b200_plonk_pk** out) try {
     if (!ctx) return B200_ERR_ARG;
 #if defined(B2_CURVE_BLS12_377)
     return ctx->fail(B200_ERR_UNSUPPORTED, "the PlonK prover is built for BN254 only (libb200prover.so)");
@@ -434,15 +434,15 @@ int b200_plonk_pk_upload(b200_ctx* ctx, int curve, const b200_plonk_pk_desc* d, 
     if (st != B200_OK) { plonk_pk_delete(ctx, pk); return st; }
     *out = pk;
     return B200_OK;
-}
+} B2_ABI_CATCH_CTX(ctx)
 
-int b200_plonk_pk_free(b200_ctx* ctx, b200_plonk_pk* pk) {
+int b200_plonk_pk_free(b200_ctx* ctx, b200_plonk_pk* pk) try {
     if (!ctx) return B200_ERR_ARG;
     if (cudaSetDevice(ctx->device) != cudaSuccess) return ctx->fail(B200_ERR_CUDA, "cudaSetDevice");
     B2_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     plonk_pk_delete(ctx, pk);
     return B200_OK;
-}
+} B2_ABI_CATCH_CTX(ctx)
 
 }  // extern "C"
 
@@ -848,7 +848,7 @@ extern "C" {
 
 int b200_plonk_session_begin(b200_ctx* ctx, const b200_plonk_pk* pk, const uint64_t* l, const uint64_t* r, const uint64_t* o,
                              const uint64_t* public_witness, const uint64_t* blinding, const b200_plonk_bsb22* bsb,
-                             b200_plonk_session** out, uint64_t* partials) {
+                             b200_plonk_session** out, uint64_t* partials) try {
     if (!ctx) return B200_ERR_ARG;
     if (cudaSetDevice(ctx->device) != cudaSuccess) return ctx->fail(B200_ERR_CUDA, "cudaSetDevice");
     if (!pk || !l || !r || !o || !out || !partials || (pk->nb_public && !public_witness)) return ctx->fail(B200_ERR_ARG, "null argument");
@@ -892,9 +892,9 @@ int b200_plonk_session_begin(b200_ctx* ctx, const b200_plonk_pk* pk, const uint6
     S->next_phase = 1;
     *out = S.release();
     return B200_OK;
-}
+} B2_ABI_CATCH_CTX(ctx)
 
-int b200_plonk_session_step(b200_ctx* ctx, b200_plonk_session* S, int phase, const uint64_t* totals, uint64_t* partials) {
+int b200_plonk_session_step(b200_ctx* ctx, b200_plonk_session* S, int phase, const uint64_t* totals, uint64_t* partials) try {
     if (!ctx) return B200_ERR_ARG;
     if (cudaSetDevice(ctx->device) != cudaSuccess) return ctx->fail(B200_ERR_CUDA, "cudaSetDevice");
     if (!S || phase != S->next_phase || phase < 1 || phase > 5) return ctx->fail(B200_ERR_ARG, "phases run in order 1..5 after begin");
@@ -910,18 +910,18 @@ int b200_plonk_session_step(b200_ctx* ctx, b200_plonk_session* S, int phase, con
     }
     if (st == B200_OK) S->next_phase = phase + 1;
     return st;
-}
+} B2_ABI_CATCH_CTX(ctx)
 
-int b200_plonk_session_numerator(b200_ctx* ctx, b200_plonk_session* S, void** cres_dev, size_t* block_elems, unsigned* log_blocks) {
+int b200_plonk_session_numerator(b200_ctx* ctx, b200_plonk_session* S, void** cres_dev, size_t* block_elems, unsigned* log_blocks) try {
     if (!ctx) return B200_ERR_ARG;
     if (!S || !cres_dev || !block_elems || !log_blocks) return ctx->fail(B200_ERR_ARG, "null argument");
     *cres_dev = S->cres;
     *block_elems = S->pk->n;
     *log_blocks = S->pk->log_big - S->pk->log_n;
     return B200_OK;
-}
+} B2_ABI_CATCH_CTX(ctx)
 
-int b200_plonk_session_finish(b200_ctx* ctx, b200_plonk_session* S, const uint64_t* totals, b200_plonk_proof* out, b200_plonk_timings* tm) {
+int b200_plonk_session_finish(b200_ctx* ctx, b200_plonk_session* S, const uint64_t* totals, b200_plonk_proof* out, b200_plonk_timings* tm) try {
     if (!ctx) return B200_ERR_ARG;
     if (!S) return ctx->fail(B200_ERR_ARG, "null session");
     std::unique_ptr<b200_plonk_session> guard(S);
@@ -932,16 +932,16 @@ int b200_plonk_session_finish(b200_ctx* ctx, b200_plonk_session* S, const uint64
         if (tm) *tm = S->T;
     }
     return B200_OK;
-}
+} B2_ABI_CATCH_CTX(ctx)
 
 int b200_plonk_prove(b200_ctx* ctx, const b200_plonk_pk* pk, const uint64_t* l, const uint64_t* r, const uint64_t* o,
-                     const uint64_t* public_witness, const uint64_t* blinding, b200_plonk_proof* out, b200_plonk_timings* tm) {
+                     const uint64_t* public_witness, const uint64_t* blinding, b200_plonk_proof* out, b200_plonk_timings* tm) try {
     return b200_plonk_prove_bsb22(ctx, pk, l, r, o, public_witness, blinding, nullptr, out, tm);
-}
+} B2_ABI_CATCH_CTX(ctx)
 
 int b200_plonk_prove_bsb22(b200_ctx* ctx, const b200_plonk_pk* pk, const uint64_t* l, const uint64_t* r, const uint64_t* o,
                            const uint64_t* public_witness, const uint64_t* blinding, const b200_plonk_bsb22* bsb,
-                           b200_plonk_proof* out, b200_plonk_timings* tm) {
+                           b200_plonk_proof* out, b200_plonk_timings* tm) try {
     if (!ctx) return B200_ERR_ARG;
     if (!out) return ctx->fail(B200_ERR_ARG, "null argument");
     if (pk && pk->shard_count > 1) return ctx->fail(B200_ERR_ARG, "a sharded key proves through the session phases (b200_plonk_session_*)");
@@ -956,10 +956,10 @@ int b200_plonk_prove_bsb22(b200_ctx* ctx, const b200_plonk_pk* pk, const uint64_
     if (st == B200_OK) st = b200_plonk_session_step(ctx, S, 5, b, a);
     if (st != B200_OK) { b200_plonk_session_finish(ctx, S, nullptr, nullptr, nullptr); return st; }
     return b200_plonk_session_finish(ctx, S, a, out, tm);
-}
+} B2_ABI_CATCH_CTX(ctx)
 
 int b200_plonk_derive_challenges(const uint64_t* vk_commitments, const uint64_t* vk_qcp, const uint64_t* public_witness, size_t nb_public,
-                                 const b200_plonk_proof* p, uint64_t* out) {
+                                 const b200_plonk_proof* p, uint64_t* out) try {
     if (!vk_commitments || !p || !out || (nb_public && !public_witness)) return B200_ERR_ARG;
     if (p->nb_bsb22 > B200_PLONK_MAX_BSB22 || (p->nb_bsb22 && !vk_qcp)) return B200_ERR_ARG;
     auto pt = [](const uint64_t* src) { G1Affine a; memcpy(&a, src, sizeof a); return a; };
@@ -976,9 +976,9 @@ int b200_plonk_derive_challenges(const uint64_t* vk_commitments, const uint64_t*
     for (int k = 0; k < 3; ++k) bind_point(fs, "zeta", pt(p->h[k]));
     put_fr(out + 12, derive(fs, "zeta"));
     return B200_OK;
-}
+} B2_ABI_CATCH_INT
 
-int b200_plonk_proof_bytes(const b200_plonk_proof* p, uint8_t* out, size_t cap) {
+int b200_plonk_proof_bytes(const b200_plonk_proof* p, uint8_t* out, size_t cap) try {
     if (!p || !out || p->nb_bsb22 > B200_PLONK_MAX_BSB22) return B200_ERR_ARG;
     const uint32_t nb = (uint32_t)p->nb_bsb22;
     if (cap < 552 + 64 * (size_t)nb) return B200_ERR_ARG;
@@ -998,6 +998,6 @@ int b200_plonk_proof_bytes(const b200_plonk_proof* p, uint8_t* out, size_t cap) 
     be32(q, nb); q += 4;                                                    // Bsb22Commitments
     for (uint32_t k = 0; k < nb; ++k) { g1_compress(pt(p->bsb22[k]), q); q += 32; }
     return (int)(q - out);
-}
+} B2_ABI_CATCH_INT
 
 }  // extern "C"

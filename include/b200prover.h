@@ -24,8 +24,9 @@
  *   - The caller owns host buffers for the duration of the call only.  Handles (ctx, domain,
  *     bases, pk) own device memory and are freed explicitly.
  *   - A ctx is bound to ONE device and is not re-entrant (serialise calls per ctx); distinct
- *     ctx are independent.  Multi-GPU = one ctx per device/rank, shards selected with
- *     (shard_index, shard_count); partial sums are combined by the host (b200_g1_jac_add ...).
+ *     ctx are independent.  Multi-GPU: a b200_group (one process, one call per proof over all devices; below), or
+ *     one ctx per device/rank with shards selected by (shard_index, shard_count) and the partial sums combined by
+ *     the caller (b200_g1_jac_add ...).
  *   - There is no CPU fallback: without a CUDA device b200_init fails with B200_ERR_CUDA.
  *   - Zero-length MSM returns the point at infinity; infinity bases (0,0) and zero scalars are
  *     legal inputs.
@@ -45,6 +46,92 @@ extern "C" {
 #pragma GCC visibility push(default)
 #endif
 
+/* BEGIN per-curve symbol names (generated: scripts/gen_symbol_renames.py) */
+#if defined(B200_CURVE_BLS12_377) || defined(B2_CURVE_BLS12_377)
+#define b200_bases_free b200_bls12377_bases_free
+#define b200_bases_info b200_bls12377_bases_info
+#define b200_bases_upload b200_bls12377_bases_upload
+#define b200_bases_upload_raw b200_bls12377_bases_upload_raw
+#define b200_batch_scalar_mul b200_bls12377_batch_scalar_mul
+#define b200_build_curve b200_bls12377_build_curve
+#define b200_build_fp_words b200_bls12377_build_fp_words
+#define b200_d2h b200_bls12377_d2h
+#define b200_destroy b200_bls12377_destroy
+#define b200_dev_alloc b200_bls12377_dev_alloc
+#define b200_dev_free b200_bls12377_dev_free
+#define b200_device_count b200_bls12377_device_count
+#define b200_fp_vec_mul b200_bls12377_fp_vec_mul
+#define b200_fr_batch_inverse_dev b200_bls12377_fr_batch_inverse_dev
+#define b200_fr_mul_sub_dev b200_bls12377_fr_mul_sub_dev
+#define b200_fr_poly_div_linear_dev b200_bls12377_fr_poly_div_linear_dev
+#define b200_fr_poly_eval_dev b200_bls12377_fr_poly_eval_dev
+#define b200_fr_prefix_product_dev b200_bls12377_fr_prefix_product_dev
+#define b200_fr_prefix_product_static b200_bls12377_fr_prefix_product_static
+#define b200_fr_vec_mul b200_bls12377_fr_vec_mul
+#define b200_g1_jac_add b200_bls12377_g1_jac_add
+#define b200_g1_jac_to_affine b200_bls12377_g1_jac_to_affine
+#define b200_g2_jac_add b200_bls12377_g2_jac_add
+#define b200_g2_jac_to_affine b200_bls12377_g2_jac_to_affine
+#define b200_groth16_compute_h b200_bls12377_groth16_compute_h
+#define b200_groth16_finalize b200_bls12377_groth16_finalize
+#define b200_groth16_msms_dev b200_bls12377_groth16_msms_dev
+#define b200_groth16_pk_free b200_bls12377_groth16_pk_free
+#define b200_groth16_pk_info b200_bls12377_groth16_pk_info
+#define b200_groth16_pk_upload b200_bls12377_groth16_pk_upload
+#define b200_groth16_pk_wire_range b200_bls12377_groth16_pk_wire_range
+#define b200_groth16_proof_bytes b200_bls12377_groth16_proof_bytes
+#define b200_groth16_prove_core b200_bls12377_groth16_prove_core
+#define b200_groth16_prove_core_dev b200_bls12377_groth16_prove_core_dev
+#define b200_groth16_setup b200_bls12377_groth16_setup
+#define b200_group_ctx b200_bls12377_group_ctx
+#define b200_group_destroy b200_bls12377_group_destroy
+#define b200_group_groth16_pk_free b200_bls12377_group_groth16_pk_free
+#define b200_group_groth16_pk_info b200_bls12377_group_groth16_pk_info
+#define b200_group_groth16_pk_upload b200_bls12377_group_groth16_pk_upload
+#define b200_group_groth16_prove_core b200_bls12377_group_groth16_prove_core
+#define b200_group_groth16_prove_core_dev b200_bls12377_group_groth16_prove_core_dev
+#define b200_group_groth16_setup b200_bls12377_group_groth16_setup
+#define b200_group_init b200_bls12377_group_init
+#define b200_group_last_error b200_bls12377_group_last_error
+#define b200_group_set_option b200_bls12377_group_set_option
+#define b200_group_size b200_bls12377_group_size
+#define b200_h2d b200_bls12377_h2d
+#define b200_host_alloc b200_bls12377_host_alloc
+#define b200_host_free b200_bls12377_host_free
+#define b200_imad_peak b200_bls12377_imad_peak
+#define b200_init b200_bls12377_init
+#define b200_kzg_commit_dev b200_bls12377_kzg_commit_dev
+#define b200_last_error b200_bls12377_last_error
+#define b200_msm_dev b200_bls12377_msm_dev
+#define b200_msm_g1 b200_bls12377_msm_g1
+#define b200_msm_g2 b200_bls12377_msm_g2
+#define b200_msm_resident b200_bls12377_msm_resident
+#define b200_ntt b200_bls12377_ntt
+#define b200_ntt_dev b200_bls12377_ntt_dev
+#define b200_ntt_dist_phase b200_bls12377_ntt_dist_phase
+#define b200_plonk_build_ratio_dev b200_bls12377_plonk_build_ratio_dev
+#define b200_plonk_derive_challenges b200_bls12377_plonk_derive_challenges
+#define b200_plonk_divide_by_xn_minus_one_dev b200_bls12377_plonk_divide_by_xn_minus_one_dev
+#define b200_plonk_pk_free b200_bls12377_plonk_pk_free
+#define b200_plonk_pk_upload b200_bls12377_plonk_pk_upload
+#define b200_plonk_proof_bytes b200_bls12377_plonk_proof_bytes
+#define b200_plonk_prove b200_bls12377_plonk_prove
+#define b200_plonk_prove_bsb22 b200_bls12377_plonk_prove_bsb22
+#define b200_plonk_quotient_rows_dev b200_bls12377_plonk_quotient_rows_dev
+#define b200_plonk_session_begin b200_bls12377_plonk_session_begin
+#define b200_plonk_session_finish b200_bls12377_plonk_session_finish
+#define b200_plonk_session_numerator b200_bls12377_plonk_session_numerator
+#define b200_plonk_session_step b200_bls12377_plonk_session_step
+#define b200_points_from_raw b200_bls12377_points_from_raw
+#define b200_profile_read b200_bls12377_profile_read
+#define b200_profile_start b200_bls12377_profile_start
+#define b200_set_option b200_bls12377_set_option
+#define b200_sync b200_bls12377_sync
+#define b200_use_stream b200_bls12377_use_stream
+#define b200_version b200_bls12377_version
+#endif
+/* END per-curve symbol names */
+
 typedef struct b200_ctx b200_ctx;
 typedef struct b200_bases b200_bases;             /* resident MSM base set (G1 or G2)         */
 typedef struct b200_groth16_pk b200_groth16_pk;   /* resident Groth16 proving key (or shard)  */
@@ -54,7 +141,8 @@ enum b200_status {
     B200_ERR_CUDA = -1,        /* CUDA runtime error (message in b200_last_error)              */
     B200_ERR_ARG = -2,         /* invalid argument                                             */
     B200_ERR_NOMEM = -3,       /* device or pinned-host allocation failed                      */
-    B200_ERR_UNSUPPORTED = -4  /* curve / size not supported by this build                     */
+    B200_ERR_UNSUPPORTED = -4, /* curve / size not supported by this build                     */
+    B200_ERR_INTERNAL = -5     /* a C++ exception was stopped at the boundary (message kept)   */
 };
 
 enum b200_curve { B200_BN254 = 0, B200_BLS12_377 = 1 };
@@ -422,6 +510,47 @@ int b200_groth16_prove_core_dev(b200_ctx *ctx, const b200_groth16_pk *pk, const 
  * shard's range of h (len = the shard's G1.Z count). */
 int b200_groth16_msms_dev(b200_ctx *ctx, const b200_groth16_pk *pk, const void *w_dev, const void *h_dev,
                           b200_groth16_out *out, b200_timings *timings);
+
+/* ---- multi-GPU in ONE process: the device group ------------------------------------------------------------
+ * What groth16.Prove calls to prove on every GPU of the box with one call (the reference's drop-in shape is one Go
+ * process making one call per proof: backend/groth16/groth16.go:178-182 -> icicle/icicle.go:133; option plumbing
+ * backend/backend.go:132-137 -- the b200 option carries the device list).  A group owns one b200_ctx per device and
+ * runs them from its own host threads; no MPI / NCCL / torchrun around the caller.
+ *   - the five MultiExp run on point-range shards (one per device); partial sums are added on the host inside the call;
+ *   - computeH is distributed with one exchange per transform, fused into the kernels over peer-mapped memory
+ *     (NVLink P2P stores / loads; csrc/group.cu) when the group has a power-of-two number >= 2 of devices with peer
+ *     access and 2 log2(devices) <= log_n; otherwise every device runs the whole computeH (replicated);
+ *   - `devices` may name one device several times (virtual ranks; what the tests do on a single GPU).
+ * A group is not re-entrant (one call at a time), like a ctx.  Errors: negative b200_status, message in
+ * b200_group_last_error. */
+typedef struct b200_group b200_group;
+typedef struct b200_group_groth16_pk b200_group_groth16_pk;
+int b200_group_init(const int *devices, int ndev, b200_group **out);
+void b200_group_destroy(b200_group *group);
+const char *b200_group_last_error(const b200_group *group);
+int b200_group_size(const b200_group *group);
+/* The context of one rank (options, profiling, single-device calls); owned by the group. */
+b200_ctx *b200_group_ctx(b200_group *group, int rank);
+int b200_group_set_option(b200_group *group, const char *key, long value);
+/* b200_groth16_pk_upload / b200_groth16_setup for the whole group: the descriptor's shard_index / shard_count /
+ * presliced are ignored -- rank r keeps the point range r of every base array on its device. */
+int b200_group_groth16_pk_upload(b200_group *group, int curve, const b200_groth16_pk_desc *desc, b200_group_groth16_pk **out);
+int b200_group_groth16_setup(b200_group *group, int curve, const b200_groth16_setup_desc *desc, b200_group_groth16_pk **out,
+                             b200_groth16_setup_out *setup_out);
+int b200_group_groth16_pk_free(b200_group *group, b200_group_groth16_pk *pk);
+/* out[0..4] of one rank's shard; *distributed_h = 1 when computeH runs distributed over the group. */
+int b200_group_groth16_pk_info(b200_group *group, const b200_group_groth16_pk *pk, int rank, b200_msm_set_info out[5],
+                               int *distributed_h);
+/* b200_groth16_prove_core on the group: host a, b, c (n_constraints each), host W; `out` = the five MultiExp results
+ * of the WHOLE proof (partial sums already combined); timings = per-stage maximum over the ranks. */
+int b200_group_groth16_prove_core(b200_group *group, const b200_group_groth16_pk *pk, const uint64_t *a, const uint64_t *b,
+                                  const uint64_t *c, size_t n_constraints, const uint64_t *w, const uint32_t *k_remove,
+                                  size_t n_remove, b200_groth16_out *out, b200_timings *timings);
+/* The same with inputs resident on the devices (distributed computeH only): a_dev[r], b_dev[r], c_dev[r] = rank r's
+ * block [r n / R, (r+1) n / R) of the zero-padded vectors on device r, w_dev[r] = the full W on device r. */
+int b200_group_groth16_prove_core_dev(b200_group *group, const b200_group_groth16_pk *pk, const void *const *a_dev,
+                                      const void *const *b_dev, const void *const *c_dev, const void *const *w_dev,
+                                      b200_groth16_out *out, b200_timings *timings);
 
 /* Host mirror of groth16_bn254.Prove's tail (prove.go:178-321) for callers without Go: applies
  * the fix-ups to the five MSM results with the given blinding scalars r, s (Montgomery Fr) and

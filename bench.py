@@ -410,12 +410,26 @@ def reference_arm(args):
 # ------------------------------------------------------------------------------------------
 # GPU arm
 # ------------------------------------------------------------------------------------------
+def _max_over_ranks(dist, local, x):
+    import torch
+    t = torch.tensor([float(x)], dtype=torch.float64, device=f"cuda:{local}")
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    return float(t.item())
+
+
 def gpu_arm(args):
+    """N = 1: one context.  N > 1: ONE process proves on all N GPUs through the device group (b200_group_*: host thread
+    per rank inside the library, sharded MSMs combined in C, computeH's exchanges fused into the kernels over NVLink peer
+    memory).  Under torchrun (how the driver launches N > 1) rank 0 is that process; the other ranks join the NCCL
+    communicator, then wait on a CPU (gloo) barrier so that no spinning collective kernel sits on the GPUs rank 0 is
+    timing, and take part again in the sharded PlonK proof (--plonk-dist, torch.distributed path)."""
     rank = int(os.environ.get("RANK", "0"))
-    world = int(os.environ.get("WORLD_SIZE", "1"))
+    launched = int(os.environ.get("WORLD_SIZE", "1"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
-    dist = None
-    if world > 1:
+    world = launched if launched > 1 else max(1, args.gpus)       # plain `python bench.py --gpus N` also works: one process
+    dist = gloo = None
+    if launched > 1:
+        import datetime
         import torch
         import torch.distributed as dist
         torch.cuda.set_device(local)
@@ -425,45 +439,49 @@ def gpu_arm(args):
         saved = os.dup(1)
         os.dup2(2, 1)
         try:
-            dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+            dist.init_process_group("nccl", device_id=torch.device("cuda", local), timeout=datetime.timedelta(hours=2))
             dist.barrier()
             torch.cuda.synchronize()
+            gloo = dist.new_group(backend="gloo", timeout=datetime.timedelta(hours=2))
         finally:
             sys.stdout.flush()
             os.dup2(saved, 1)
             os.close(saved)
     pkg = load_pkg()
-    ctx = pkg.Context(local)          # raises without the CUDA library / device: no fallback
+    plonk_all_ranks = bool(args.plonk_log_n and launched > 1 and args.plonk_dist and (world & (world - 1)) == 0)
+    if launched > 1 and rank != 0:
+        dist.barrier(group=gloo)          # rank 0 has finished the Groth16 part (and freed its group)
+        if plonk_all_ranks:
+            ctx = pkg.Context(local)
+            plonk_section(pkg, ctx, args.plonk_log_n, args.steps, args.warmup, dist, rank, world, f"cuda:{local}",
+                          lambda: (ctx.sync(), dist.barrier()), lambda x: _max_over_ranks(dist, local, x))
+            ctx.close()
+        dist.barrier(group=gloo)
+        dist.destroy_process_group()
+        return 0
 
-    def barrier():
-        ctx.sync()
-        if dist is not None:
-            dist.barrier()
-
-    def max_over_ranks(x):
-        if dist is None:
-            return float(x)
-        import torch
-        t = torch.tensor([float(x)], dtype=torch.float64, device=f"cuda:{local}")
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        return float(t.item())
-
+    grp = None
+    if world == 1:
+        ctx = pkg.Context(local)          # raises without the CUDA library / device: no fallback
+    else:
+        grp = pkg.Group([int(x) for x in args.devices.split(",")] if args.devices else list(range(world)))
+        ctx = grp.ctx(0)
     peak = ctx.imad_peak()
     for kv in args.opt:
         k, v = kv.split("=")
-        ctx.set_option(k, int(v))
-    inst = Instance(pkg, args.log_n, rank, world)
+        (grp or ctx).set_option(k, int(v))
+    inst = Instance(pkg, args.log_n, 0, 1)
     t_setup = time.perf_counter()
-    pk = inst.build_key(ctx)
+    pk = inst.build_key(grp or ctx)
     t_key = time.perf_counter() - t_setup
     inst.witness(ctx, pkg)
     t_setup = time.perf_counter() - t_setup
     n, nw = inst.n, inst.n_wires
-    distributed = world > 1 and (world & (world - 1)) == 0 and not args.replicate_h
     rs = rand_field(np.random.default_rng(3), 2)
     vkp = inst.vk_points()
 
-    if not distributed:
+    if grp is None:
+        distributed = False
         dv = {k: pkg.DeviceVector(ctx, getattr(inst, k).nbytes).upload(getattr(inst, k)) for k in ("a", "b", "c", "w")}
 
         def step_dev():
@@ -474,62 +492,46 @@ def gpu_arm(args):
             return ctx.groth16_prove_core(pk, inst.a, inst.b, inst.c, inst.w)[0]
         w_lo, w_hi = pk.wire_range()
         h2d_bytes = int((3 * n + (w_hi - w_lo)) * 32)
+        pk_info = pk.info()
     else:
-        # computeH distributed over the ranks: every rank owns n / world elements of a, b, c; one
-        # all-to-all per transform (NCCL over NVLink); the five MSMs on point-range shards.
-        import torch
-        dev = torch.device("cuda", local)
-        n_loc = n // world
-        blk = slice(rank * n_loc, (rank + 1) * n_loc)
-        host_blk = [torch.from_numpy(getattr(inst, k)[blk].view(np.int64)) for k in ("a", "b", "c")]   # views of the pinned arrays
-        torch.cuda.synchronize(dev)
-        resident = [t.to(dev) for t in host_blk]
-        work = [torch.empty((n_loc, 4), dtype=torch.int64, device=dev) for _ in range(6)]            # a, b, c, 3 x tmp
-        w_host = torch.from_numpy(inst.w.view(np.int64))
-        w_dev = w_host.to(dev)
-        engine = pkg.sharding.DeviceEngine(ctx, inst.log_n, inst.gen, inst.coset, rank, world)
-        exchange = pkg.sharding.torch_exchange(dist, async_op=True)
-        torch.cuda.set_stream(torch.cuda.Stream(dev))                # a real stream (the legacy default one cannot be shared)
-        ctx.use_stream(torch.cuda.current_stream(dev).cuda_stream)   # library kernels and NCCL ordered on one stream
-        ev = [torch.cuda.Event(enable_timing=True) for _ in range(3)]
+        pk_info = pk.info(0)
+        distributed = pk_info.pop("distributed_h")
+        ctxs = [grp.ctx(r) for r in range(world)]
+        h2d_bytes = int((3 * n + nw + 2 * (world - 1)) * 32)      # a, b, c blocks + each rank's wire range of W (ranges overlap by a wire or two)
+        if distributed:
+            n_loc = n // world
+            blocks = [[pkg.DeviceVector(ctxs[r], n_loc * 32).upload(np.ascontiguousarray(getattr(inst, k)[r * n_loc:(r + 1) * n_loc]))
+                       for r in range(world)] for k in ("a", "b", "c")]
+            wv = [pkg.DeviceVector(ctxs[r], inst.w.nbytes).upload(inst.w) for r in range(world)]
 
-        def run(src, w_src):
-            torch.cuda.synchronize(dev)
-            ev[0].record()
-            for dst, s_ in zip(work[:3], src):
-                dst.copy_(s_, non_blocking=True)
-            h = pkg.sharding.compute_h_distributed(engine, exchange, work[0], work[1], work[2], work[3:6])
-            ev[1].record()
-            o, tm = ctx.groth16_msms_dev(pk, w_src, h)     # copies this shard's wire range of W only
-            ev[2].record()
-            ev[2].synchronize()
-            tm = dict(tm, compute_h_ms=ev[0].elapsed_time(ev[1]), h2d_ms=0.0)
-            return o, tm, ev[0].elapsed_time(ev[2])
-
-        def step_dev():
-            return run(resident, w_dev)
+            def step_dev():
+                o, tm = grp.groth16_prove_core_dev(pk, blocks[0], blocks[1], blocks[2], wv)
+                return o, tm, tm["total_ms"]
+        else:       # odd group size: every rank runs the whole computeH from the host buffers
+            def step_dev():
+                o, tm = grp.groth16_prove_core(pk, inst.a, inst.b, inst.c, inst.w)
+                return o, tm, tm["total_ms"]
 
         def step_e2e():
-            return run(host_blk, inst.w)[0]
-        w_lo, w_hi = pk.wire_range()
-        h2d_bytes = int((3 * n_loc + (w_hi - w_lo)) * 32)
+            return grp.groth16_prove_core(pk, inst.a, inst.b, inst.c, inst.w)[0]
+
+    def barrier():
+        for c in ([ctx] if grp is None else ctxs):
+            c.sync()
 
     # correctness first (outside any timed region): the proof of the satisfying witness must verify -- all five MSM
     # results against their discrete logs, the verify equation in the exponent, the host fix-ups (Instance.check)
     out, _, _ = step_dev()
-    verified = None
-    if not args.no_check:
-        total = out.as_dict() if dist is None else pkg.sharding.gather_combine(dist, out.as_dict(), device=f"cuda:{local}")
-        verified = inst.check(ctx, pkg, total, out if dist is None else None) if rank == 0 else True
-    if dist is not None:
-        dist.barrier()
+    verified = None if args.no_check else inst.check(ctx, pkg, out.as_dict(), out)
+    if not args.no_check and grp is not None:       # and the host-buffer path of the group
+        inst.check(ctx, pkg, step_e2e().as_dict())
 
     clocks = ClockSampler(local)
     clocks.start()                      # nvidia-smi needs a moment to come up: start it under the warm-up
     for _ in range(max(0, args.warmup - 1)):
         step_dev()
 
-    # ---- device-resident timed region: K steps, CUDA events --------------------------------
+    # ---- device-resident timed region: K steps, CUDA events (max over the ranks, taken inside the library) ----
     barrier()
     clocks.mark()
     ctx.profile_start()
@@ -544,39 +546,34 @@ def gpu_arm(args):
     barrier()
     wall_dev = time.perf_counter() - t0
     extra = 0
-    while extra < 200:
-        need = clocks.lines() - clocks.skip < 3 and time.perf_counter() - t0 < 5.0
-        if max_over_ranks(1.0 if need else 0.0) == 0.0:      # a collective decision: the steps contain collectives
-            break
+    while extra < 200 and clocks.lines() - clocks.skip < 3 and time.perf_counter() - t0 < 5.0:
         step_dev()                      # region shorter than the 100 ms sampling period: same load, untimed
         extra += 1
     clk = clocks.stop()
     clk["window"] = "timed region" if not extra else f"timed region + {extra} identical untimed steps (region shorter than the sampling period)"
-    step_ms = max_over_ranks(float(np.mean(dev_ms)))
-    stage["total_ms"] = float(np.mean(dev_ms))
+    step_ms = float(np.mean(dev_ms))
+    stage["total_ms"] = step_ms
 
-    # ---- end to end through the host-buffer path: pinned host -> device, MSM results back,
+    # ---- end to end through the host-buffer path: pinned host -> device(s), MSM results back (combined),
     #      host fix-ups (prove.go:178-321) to the affine proof -------------------------------
     step_e2e()
     barrier()
     t0 = time.perf_counter()
     for _ in range(args.steps):
         o = step_e2e()
-        if world == 1:
-            pkg.groth16_finalize(o, rs[0], rs[1], *vkp)
+        pkg.groth16_finalize(o, rs[0], rs[1], *vkp)
     barrier()
-    e2e_s = max_over_ranks((time.perf_counter() - t0) / args.steps)
-    if dist is not None:
-        # strong scaling: partial sums (576 B per rank) gathered and added on the host of rank 0
-        t1 = time.perf_counter()
-        combined = pkg.sharding.gather_combine(dist, o.as_dict(), device=f"cuda:{local}")
-        e2e_s += max_over_ranks(time.perf_counter() - t1)
+    e2e_s = (time.perf_counter() - t0) / args.steps
 
-    pk_info = pk.info()
     args.plonk_result = None
-    if dist is not None:
-        ctx.use_stream(None)
     pk.free()                           # the folded tables go before the PlonK / BLS12-377 keys come
+    if grp is not None:
+        for v in [x for vs in (blocks if distributed else []) for x in vs] + (wv if distributed else []):
+            v.free()
+        grp.close()
+        ctx = pkg.Context(local)
+    if launched > 1:
+        dist.barrier(group=gloo)
     args.cpu_result = None
     if world == 1 and not args.no_cpu:  # the one leg that runs the oracle: the CPU baseline (and the device against it)
         args.cpu_result = cpu_baseline_leg(ctx, pkg, inst.log_n, min(args.cpu_sample_log, inst.log_n))
@@ -586,18 +583,19 @@ def gpu_arm(args):
             args.bls_result = bls12_377_section(pkg, local, args.bls12_377_log_n, args.steps, args.warmup, peak)
         except Exception as e:          # the headline line must still be printed
             args.bls_result = {"error": repr(e)}
-    if args.plonk_log_n and (world == 1 or (args.plonk_dist and (world & (world - 1)) == 0)):
+    if args.plonk_log_n and (world == 1 or plonk_all_ranks):
         try:
-            args.plonk_result = plonk_section(pkg, ctx, args.plonk_log_n, args.steps, args.warmup, dist, rank, world,
-                                              f"cuda:{local}", barrier, max_over_ranks)
+            args.plonk_result = plonk_section(pkg, ctx, args.plonk_log_n, args.steps, args.warmup, dist if launched > 1 else None, rank,
+                                              world if launched > 1 else 1, f"cuda:{local}",
+                                              (lambda: (ctx.sync(), dist.barrier())) if launched > 1 else None,
+                                              (lambda x: _max_over_ranks(dist, local, x)) if launched > 1 else None)
         except Exception as e:          # the headline line must still be printed
             args.plonk_result = {"error": repr(e)}
-    if dist is not None:
-        dist.barrier()
+            if launched > 1:
+                raise
+    if launched > 1:
+        dist.barrier(group=gloo)
         dist.destroy_process_group()
-    if rank != 0:
-        ctx.close()
-        return 0
     return report(args, world, peak, prof, stage, step_ms, e2e_s, clk, verified, inst, t_setup, wall_dev, pk_info, distributed, h2d_bytes)
 
 
@@ -804,11 +802,11 @@ def main():
     ap.add_argument("--reference-budget", type=float, default=150.0, help="--impl reference: seconds of timed full-size CPU steps")
     ap.add_argument("--plonk-log-n", type=int, default=22, help="also time BN254 PlonK Prove at 2^k gates (config 4; sharded over the ranks at N > 1); 0 = skip")
     ap.add_argument("--bls12-377-log-n", type=int, default=22, help="N = 1: also time BLS12-377 Groth16 Prove at 2^k constraints (config 5) through libb200prover_bls12377.so; 0 = skip")
-    ap.add_argument("--plonk-dist", action="store_true", help="N > 1: run the sharded PlonK proof too (off by default: the scaling run stays the Groth16 line only)")
+    ap.add_argument("--no-plonk-dist", dest="plonk_dist", action="store_false", help="N > 1 under torchrun: skip the sharded PlonK proof (config 4 on N GPUs)")
     ap.add_argument("--opt", action="append", default=[], metavar="KEY=VALUE", help="b200_set_option before the key is built (tuning sweeps only; the default run sets none)")
+    ap.add_argument("--devices", default="", help="N > 1: device ordinals of the group, comma separated (default 0..N-1; a device may repeat: virtual ranks, functional runs on one GPU)")
     ap.add_argument("--no-check", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
-    ap.add_argument("--replicate-h", action="store_true", help="N > 1: every rank runs the whole computeH (no exchange)")
     args = ap.parse_args()
     if args.impl == "reference":
         return reference_arm(args)

@@ -30,7 +30,16 @@ struct PkScalarSource {
     uint64_t *out_a = nullptr, *out_b = nullptr, *out_k = nullptr, *out_z = nullptr, *out_g2b = nullptr;
 };
 int groth16_pk_upload(b200_ctx* ctx, const b200_groth16_pk_desc* d, b200_groth16_pk** out, const PkScalarSource* gen_src = nullptr);
-// setup.cu
+// setup.cu: the scalar side of Setup (host + one device batch inversion), derived once, and the point side per shard
+struct SetupScalars {
+    std::vector<Fr> A, B, pkK, vkK;               // filtered A_i(tau), B_i(tau); K scalars of pk.G1.K and vk.G1.K
+    std::vector<std::vector<Fr>> ckK;             // Pedersen bases' scalars per commitment
+    std::vector<uint8_t> infA, infB;
+    Fr tau, alpha, beta, gamma, delta, z_mult;    // z_mult = (tau^n - 1) / delta
+};
+int groth16_setup_scalars(b200_ctx* ctx, const b200_groth16_setup_desc* d, SetupScalars& S);
+int groth16_setup_points(b200_ctx* ctx, const b200_groth16_setup_desc* d, const SetupScalars& S, int shard_index, int shard_count,
+                         b200_groth16_pk** pk_out, b200_groth16_setup_out* out, bool vk_side);
 int groth16_setup(b200_ctx* ctx, const b200_groth16_setup_desc* d, b200_groth16_pk** pk_out, b200_groth16_setup_out* out);
 // computeH supplied by the caller and enqueued at the point of the schedule where the prove core runs its own
 // (the group's distributed computeH, group.cu): copy_abc enqueues this rank's share of a, b, c on the copy stream `cp`

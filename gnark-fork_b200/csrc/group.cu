@@ -339,21 +339,19 @@ int b200_group_groth16_setup(b200_group* g, int curve, const b200_groth16_setup_
     if (curve != b200_build_curve()) return g->fail(B200_ERR_UNSUPPORTED, "curve not supported by this build");
     b200_group_groth16_pk* gpk = new b200_group_groth16_pk();
     gpk->pk.assign(g->R, nullptr);
-    // every rank derives the scalars (host threads) and generates its own point ranges; rank 0 fills the caller's outputs,
-    // the others only the point arrays (each its own range)
-    int st = run_ranks(g, [&](int r) -> int {
-        b200_groth16_setup_desc d = *desc;
-        d.shard_index = r;
-        d.shard_count = g->R;
-        b200_groth16_setup_out local = *so;
+    // the scalar side once (rank 0's device for the batch inversion, host threads for the matrices), then every rank
+    // generates its own point ranges; rank 0 also makes the verifying-key side
+    SetupScalars S;
+    cudaSetDevice(g->ctx[0]->device);
+    int st = groth16_setup_scalars(g->ctx[0], desc, S);
+    if (st != B200_OK) { delete gpk; return g->fail(st, "setup", g->ctx[0]->err.c_str()); }
+    std::vector<b200_groth16_setup_out> outs(g->R, *so);
+    st = run_ranks(g, [&](int r) -> int {
+        b200_groth16_setup_out& local = outs[r];
         if (r != 0) { local.infinity_a = local.infinity_b = nullptr; local.vk_k = nullptr; local.ck_k = nullptr; }
-        const int s = groth16_setup(g->ctx[r], &d, &gpk->pk[r], &local);
-        if (s == B200_OK && r == 0) {
-            local.g1_a = so->g1_a; local.g1_b = so->g1_b; local.g1_k = so->g1_k; local.g1_z = so->g1_z; local.g2_b = so->g2_b;
-            *so = local;
-        }
-        return s;
+        return groth16_setup_points(g->ctx[r], desc, S, r, g->R, &gpk->pk[r], &local, r == 0);
     });
+    if (st == B200_OK) *so = outs[0];
     if (st == B200_OK) st = finish_pk(g, gpk, desc->log_n);
     if (st != B200_OK) { b200_group_groth16_pk_free(g, gpk); return st; }
     *out = gpk;

@@ -92,8 +92,8 @@ int mul_points(b200_ctx* ctx, const A& base, const std::vector<Fr>& sc, uint64_t
 
 }  // namespace
 
-int groth16_setup(b200_ctx* ctx, const b200_groth16_setup_desc* d, b200_groth16_pk** pk_out, b200_groth16_setup_out* out) {
-    if (!d || !pk_out || !out || !d->generator || !d->coset_gen || !d->g1_gen || !d->g2_gen) return ctx->fail(B200_ERR_ARG, "setup: null argument");
+int groth16_setup_scalars(b200_ctx* ctx, const b200_groth16_setup_desc* d, SetupScalars& S) {
+    if (!d || !d->generator || !d->coset_gen || !d->g1_gen || !d->g2_gen) return ctx->fail(B200_ERR_ARG, "setup: null argument");
     if (d->log_n > 27) return ctx->fail(B200_ERR_UNSUPPORTED, "setup: domain above 2^27");
     const size_t n = (size_t)1 << d->log_n, m = d->nb_constraints, nw = d->nb_wires;
     if (m > n || (d->log_n && m <= n / 2)) return ctx->fail(B200_ERR_ARG, "setup: the domain is not fft.NewDomain(nb_constraints)");
@@ -145,8 +145,11 @@ int groth16_setup(b200_ctx* ctx, const b200_groth16_setup_desc* d, b200_groth16_
             kall[i] = t * (klass(i) == 0 ? delta_inv : gamma_inv);
         }
     });
-    std::vector<Fr> vkK, pkK;
-    std::vector<std::vector<Fr>> ckK(d->nb_commitments);
+    std::vector<Fr>& vkK = S.vkK;
+    std::vector<Fr>& pkK = S.pkK;
+    std::vector<std::vector<Fr>>& ckK = S.ckK;
+    vkK.clear(); pkK.clear();
+    ckK.assign(d->nb_commitments, std::vector<Fr>());
     for (size_t i = 0; i < nw; ++i) {
         const int k = klass(i);
         if (k == -1 || k == 1) vkK.push_back(kall[i]);
@@ -159,7 +162,9 @@ int groth16_setup(b200_ctx* ctx, const b200_groth16_setup_desc* d, b200_groth16_
     if (vkK.size() != d->nb_public + d->nb_commitments) return ctx->fail(B200_ERR_ARG, "setup: the number of commitment wires differs from nb_commitments");
 
     // ---- infinity filters (setup.go:217-243) -------------------------------------------------------------------
-    std::vector<uint8_t> infA(nw), infB(nw);
+    std::vector<uint8_t>& infA = S.infA;
+    std::vector<uint8_t>& infB = S.infB;
+    infA.assign(nw, 0); infB.assign(nw, 0);
     size_t na = 0, nb = 0;
     for (size_t i = 0; i < nw; ++i) {
         infA[i] = A[i].is_zero();
@@ -169,13 +174,30 @@ int groth16_setup(b200_ctx* ctx, const b200_groth16_setup_desc* d, b200_groth16_
     }
     A.resize(na);
     B.resize(nb);
-    if (out->infinity_a) memcpy(out->infinity_a, infA.data(), nw);
-    if (out->infinity_b) memcpy(out->infinity_b, infB.data(), nw);
+    S.A.swap(A);
+    S.B.swap(B);
+    S.z_mult = zt * delta_inv;
+    S.tau = tau; S.alpha = alpha; S.beta = beta; S.gamma = gamma; S.delta = delta;
+    return B200_OK;
+}
+
+// The point side of Setup for one shard: this device's ranges of the key from the scalars, the verifying-key side and the
+// Pedersen bases when `out` asks for them.
+int groth16_setup_points(b200_ctx* ctx, const b200_groth16_setup_desc* d, const SetupScalars& S, int shard_index, int shard_count,
+                         b200_groth16_pk** pk_out, b200_groth16_setup_out* out, bool vk_side) {
+    if (!pk_out || !out) return ctx->fail(B200_ERR_ARG, "setup: null argument");
+    const size_t n = (size_t)1 << d->log_n, nw = d->nb_wires;
+    const std::vector<Fr>&A = S.A, &B = S.B, &pkK = S.pkK, &vkK = S.vkK;
+    const std::vector<std::vector<Fr>>& ckK = S.ckK;
+    const size_t na = A.size(), nb = B.size();
+    const Fr alpha = S.alpha, beta = S.beta, gamma = S.gamma, delta = S.delta;
+    if (out->infinity_a) memcpy(out->infinity_a, S.infA.data(), nw);
+    if (out->infinity_b) memcpy(out->infinity_b, S.infB.data(), nw);
 
     // ---- Z scalars (setup.go:203-214), bit-reversed (:265), on the device ---------------------------------------
     DevBuf d_z;
     B2_CUDA(ctx, d_z.alloc(n * sizeof(Fr)));
-    B2_TRY(gen_powers(ctx, d_z.as<Fr>(), tau, zt * delta_inv, n, d->log_n ? (int)d->log_n : 0));
+    B2_TRY(gen_powers(ctx, d_z.as<Fr>(), S.tau, S.z_mult, n, d->log_n ? (int)d->log_n : 0));
 
     // ---- the resident key: this shard's ranges of [A]1 [B]1 [K]1 [Z]1 [B]2 -----------------------------------
     PkScalarSource src;
@@ -187,15 +209,15 @@ int groth16_setup(b200_ctx* ctx, const b200_groth16_setup_desc* d, b200_groth16_
     memset(&pd, 0, sizeof pd);
     pd.log_n = d->log_n; pd.generator = d->generator; pd.coset_gen = d->coset_gen;
     pd.n_a = na; pd.n_b = nb; pd.n_g2b = nb; pd.n_k = pkK.size(); pd.n_z = n - 1;
-    pd.infinity_a = infA.data(); pd.infinity_b = infB.data();
+    pd.infinity_a = S.infA.data(); pd.infinity_b = S.infB.data();
     pd.n_wires = nw; pd.nb_public = d->nb_public;
-    pd.shard_index = d->shard_index; pd.shard_count = d->shard_count ? d->shard_count : 1;
+    pd.shard_index = shard_index; pd.shard_count = shard_count ? shard_count : 1;
     B2_TRY(groth16_pk_upload(ctx, &pd, pk_out, &src));
     d_z.release();
 
     // ---- verifying-key side and the Pedersen bases -----------------------------------------------------------------
     int st = B200_OK;
-    {
+    if (vk_side) {
         std::vector<Fr> s1 = {alpha, beta, delta}, s2 = {beta, delta, gamma};
         std::vector<uint64_t> p1(3 * sizeof(G1Affine) / 8), p2(3 * sizeof(G2Affine) / 8);
         st = mul_points<G1Affine>(ctx, src.g1, s1, p1.data());
@@ -209,8 +231,8 @@ int groth16_setup(b200_ctx* ctx, const b200_groth16_setup_desc* d, b200_groth16_
             memcpy(out->g2_gamma, p2.data() + 2 * sizeof(G2Affine) / 8, sizeof(G2Affine));
         }
     }
-    if (st == B200_OK) st = mul_points<G1Affine>(ctx, src.g1, vkK, out->vk_k);
-    for (size_t j = 0; j < d->nb_commitments && st == B200_OK; ++j)
+    if (st == B200_OK && vk_side) st = mul_points<G1Affine>(ctx, src.g1, vkK, out->vk_k);
+    for (size_t j = 0; j < d->nb_commitments && st == B200_OK && vk_side; ++j)
         if (out->ck_k && out->ck_k[j]) st = mul_points<G1Affine>(ctx, src.g1, ckK[j], out->ck_k[j]);
     if (st != B200_OK) {
         delete *pk_out;
@@ -219,6 +241,12 @@ int groth16_setup(b200_ctx* ctx, const b200_groth16_setup_desc* d, b200_groth16_
     }
     out->n_a = na; out->n_b = nb; out->n_k = pkK.size(); out->n_z = n - 1; out->n_vk_k = vkK.size();
     return B200_OK;
+}
+
+int groth16_setup(b200_ctx* ctx, const b200_groth16_setup_desc* d, b200_groth16_pk** pk_out, b200_groth16_setup_out* out) {
+    SetupScalars S;
+    B2_TRY(groth16_setup_scalars(ctx, d, S));
+    return groth16_setup_points(ctx, d, S, d->shard_index, d->shard_count, pk_out, out, true);
 }
 
 }  // namespace b200

@@ -572,17 +572,18 @@ def gpu_arm(args):
             v.free()
         grp.close()
         ctx = pkg.Context(local)
+    args.bls_result = None
+    if args.bls12_377_log_n:            # config 5, on the same number of GPUs (its own library and device group)
+        try:
+            devs = ([int(x) for x in args.devices.split(",")] if args.devices else list(range(world))) if world > 1 else None
+            args.bls_result = bls12_377_section(pkg, local, args.bls12_377_log_n, args.steps, args.warmup, peak, devs)
+        except Exception as e:          # the headline line must still be printed
+            args.bls_result = {"error": repr(e)}
     if launched > 1:
         dist.barrier(group=gloo)
     args.cpu_result = None
     if world == 1 and not args.no_cpu:  # the one leg that runs the oracle: the CPU baseline (and the device against it)
         args.cpu_result = cpu_baseline_leg(ctx, pkg, inst.log_n, min(args.cpu_sample_log, inst.log_n))
-    args.bls_result = None
-    if args.bls12_377_log_n and world == 1:
-        try:
-            args.bls_result = bls12_377_section(pkg, local, args.bls12_377_log_n, args.steps, args.warmup, peak)
-        except Exception as e:          # the headline line must still be printed
-            args.bls_result = {"error": repr(e)}
     if args.plonk_log_n and (world == 1 or plonk_all_ranks):
         try:
             args.plonk_result = plonk_section(pkg, ctx, args.plonk_log_n, args.steps, args.warmup, dist if launched > 1 else None, rank,
@@ -599,33 +600,36 @@ def gpu_arm(args):
     return report(args, world, peak, prof, stage, step_ms, e2e_s, clk, verified, inst, t_setup, wall_dev, pk_info, distributed, h2d_bytes)
 
 
-def bls12_377_section(pkg, device_index, log_n, steps, warmup, peak):
+def bls12_377_section(pkg, device_index, log_n, steps, warmup, peak, devices=None):
     """BASELINE.json config 5: BLS12-377 Groth16 prove core at 2^log_n constraints on one GPU through the second
     library (libb200prover_bls12377.so: 12-limb Fp, Fp2 with u^2 = -5; same kernels, same ABI).  Same instance shape
     and the same exact check as the BN254 headline (every MSM result against its known discrete log).  `value` =
     seconds per proof through the host-buffer call (pinned a, b, c, W in; H2D inside) + the host fix-ups."""
-    ctx = pkg.Context(device_index, curve=pkg.BLS12_377)
+    grp = pkg.Group(devices, curve=pkg.BLS12_377) if devices and len(devices) > 1 else None     # N > 1: the device group of the second library
+    ctx = grp.ctx(0) if grp else pkg.Context(device_index, curve=pkg.BLS12_377)
+    prover = grp or ctx
+    world = len(devices) if grp else 1
     try:
         inst = Instance(pkg, log_n, 0, 1, cp=BLS12_377_PARAMS)
         t0 = time.perf_counter()
-        pk = inst.build_key(ctx)
+        pk = inst.build_key(prover)
         inst.witness(ctx, pkg)
         t_setup = time.perf_counter() - t0
         rs = rand_field(np.random.default_rng(3), 2, top_limb=inst.cp.top_limb)
         vkp = inst.vk_points()
         for _ in range(max(1, warmup)):
-            out, tm = ctx.groth16_prove_core(pk, inst.a, inst.b, inst.c, inst.w)
+            out, tm = prover.groth16_prove_core(pk, inst.a, inst.b, inst.c, inst.w)
         ctx.profile_start()
         wall, tms = [], []
         for _ in range(steps):
             t1 = time.perf_counter()
-            out, tm = ctx.groth16_prove_core(pk, inst.a, inst.b, inst.c, inst.w)
+            out, tm = prover.groth16_prove_core(pk, inst.a, inst.b, inst.c, inst.w)
             pkg.groth16_finalize(out, rs[0], rs[1], *vkp, curve=pkg.BLS12_377)
             wall.append(time.perf_counter() - t1)
             tms.append(tm)
         prof = ctx.profile_read()
         ok = inst.check(ctx, pkg, out.as_dict(), out)
-        info = pk.info()
+        info = pk.info(0) if grp else pk.info()
         pk.free()
         n = inst.n
         g1 = prof["msm_acc_g1"]
@@ -636,10 +640,11 @@ def bls12_377_section(pkg, device_index, log_n, steps, warmup, peak):
         mac_madd = 8 * mac_fp + 2 * 144 + 156     # XYZZ mixed addition: 8 products + a*b - c*d as two wide products and ONE reduction
         executed = pts * info["a"]["windows"] * mac_madd / (g1_launch_ms * 1e-3) if g1_launch_ms else 0.0
         stage = {k: float(np.mean([t[k] for t in tms])) for k in tms[0]}
-        return {"metric": "BLS12-377 Groth16 prove s @2^%d constraints" % log_n, "value": float(np.mean(wall)), "unit": "s", "n_gpus": 1,
+        return {"metric": "BLS12-377 Groth16 prove s @2^%d constraints" % log_n, "value": float(np.mean(wall)), "unit": "s", "n_gpus": world,
                 "steps": steps, "workload": "synthetic 2^%d-constraint Mul-chain-shaped R1CS on BLS12-377: computeH (7 transforms of 2^%d) + "
                 "4 G1 MSMs + 1 G2 MSM of ~2^%d points (Fp 377 bits = 12 x 32-bit limbs)" % (log_n, log_n, log_n),
-                "path": "b200_groth16_prove_core of libb200prover_bls12377.so (pinned host a, b, c, W in) + b200_groth16_finalize",
+                "path": ("b200_groth16_prove_core" if not grp else "b200_group_groth16_prove_core over %d GPUs" % world) +
+                        " of libb200prover_bls12377.so (pinned host a, b, c, W in) + b200_groth16_finalize",
                 "device_ms": stage["total_ms"], "stage_ms": stage, "verified": bool(ok),
                 "verifier": "refCircuit with its satisfying witness, key from b200_groth16_setup (known toxic waste): every MSM result equals "
                             "[e]G for the discrete log e the witness implies, the verify equation holds in the exponent, host fix-ups checked",
@@ -651,7 +656,7 @@ def bls12_377_section(pkg, device_index, log_n, steps, warmup, peak):
                 "msm_plan": {k: info["a"][k] for k in ("c", "windows", "folded")},
                 "gpu_launches_per_proof": int(prof["kernel_launches"] // max(1, steps)), "setup_s": t_setup}
     finally:
-        ctx.close()
+        (grp or ctx).close()
 
 
 def plonk_section(pkg, ctx, log_n, steps, warmup, dist=None, rank=0, world=1, device=None, barrier=None, max_over_ranks=None):

@@ -256,6 +256,7 @@ def load_library(curve: int = BN254):
         "b200_ntt_dist_phase": (i, [vp, i, u, vp, vp, vp, vp, u, u, i, i, i]),
         "b200_fr_mul_sub_dev": (i, [vp, i, vp, vp, vp, sz]),
         "b200_use_stream": (i, [vp, vp]),
+        "b200_domain_cache_trim": (i, [vp, C.POINTER(sz)]),
         "b200_fr_batch_inverse_dev": (i, [vp, i, vp, vp, sz]),
         "b200_fr_prefix_product_dev": (i, [vp, i, vp, vp, sz]),
         "b200_fr_prefix_product_static": (i, [vp, i, vp, vp, sz]),
@@ -558,6 +559,12 @@ class Context:
 
     def sync(self):
         self._check(self.lib.b200_sync(self.h))
+
+    def domain_cache_trim(self) -> int:
+        """Free the cached NTT domains no resident key refers to; returns the bytes released."""
+        n = C.c_size_t()
+        self._check(self.lib.b200_domain_cache_trim(self.h, C.byref(n)))
+        return int(n.value)
 
     def use_stream(self, cuda_stream: int | None):
         """Order all further work of this context on the caller's CUDA stream (an integer
@@ -876,21 +883,34 @@ class Context:
             d.qcp, d.vk_qcp, d.commitment_index = C.addressof(ptrs), vq.ctypes.data, ci.ctypes.data
         h = C.c_void_p()
         self._check(self.lib.b200_plonk_pk_upload(self.h, self.curve, C.byref(d), C.byref(h)))
-        return PlonkProvingKey(self, h, nb_public, len(qcp), shard_index, shard_count)
+        key = PlonkProvingKey(self, h, nb_public, len(qcp), shard_index, shard_count)
+        key.n = n          # the C ABI takes no lengths: the binding checks them (out-of-bounds host reads otherwise)
+        return key
 
     def _plonk_bsb(self, pk, bsb):
         if not pk.nb_bsb22:
             return None, None
         cols = [_u64(c, (-1, 4)) for c in bsb["pi2"]]
         assert len(cols) == pk.nb_bsb22
+        if any(c.shape[0] != getattr(pk, "n", c.shape[0]) for c in cols):
+            raise B200Error("every Pi2 column must hold n rows")
         ptrs = (C.c_void_p * len(cols))(*[c.ctypes.data for c in cols])
         com, val = _u64(bsb["commitments"], (len(cols), 8)), _u64(bsb["values"], (len(cols), 4))
         return _PlonkBsb22(C.addressof(ptrs), com.ctypes.data, val.ctypes.data), (cols, ptrs, com, val)
+
+    @staticmethod
+    def _plonk_check_lengths(pk, l, r, o, pw):
+        n = getattr(pk, "n", l.shape[0])
+        if not (l.shape[0] == r.shape[0] == o.shape[0] == n):
+            raise B200Error(f"l, r, o must hold n = {n} rows each (got {l.shape[0]}, {r.shape[0]}, {o.shape[0]})")
+        if pw.shape[0] != pk.nb_public:
+            raise B200Error(f"public_witness must hold nb_public = {pk.nb_public} elements (got {pw.shape[0]})")
 
     def plonk_session(self, pk: PlonkProvingKey, l, r, o, public_witness, blinding, bsb=None) -> "PlonkSession":
         """Phase 0 of a (possibly sharded) proof; see PlonkSession."""
         l, r, o = _u64(l, (-1, 4)), _u64(r, (-1, 4)), _u64(o, (-1, 4))
         pw = _u64(public_witness, (-1, 4))
+        self._plonk_check_lengths(pk, l, r, o, pw)
         bl = None if blinding is None else _u64(blinding, (9, 4))
         cb, keep = self._plonk_bsb(pk, bsb)
         h = C.c_void_p()
@@ -906,7 +926,7 @@ class Context:
         bsb22Hint (prove.go:303-352).  Returns (PlonkProof, timings dict)."""
         l, r, o = _u64(l, (-1, 4)), _u64(r, (-1, 4)), _u64(o, (-1, 4))
         pw = _u64(public_witness, (-1, 4))
-        assert pw.shape[0] == pk.nb_public
+        self._plonk_check_lengths(pk, l, r, o, pw)
         bl = None if blinding is None else _u64(blinding, (9, 4))
         proof, tm = PlonkProof(), _PlonkTimings()
         cb, keep = self._plonk_bsb(pk, bsb)

@@ -479,6 +479,15 @@ int b200_fr_mul_sub_dev(b200_ctx* ctx, int curve, void* a_dev, const void* b_dev
     return ntt_mul_sub(ctx, (Fr*)a_dev, (const Fr*)b_dev, (const Fr*)c_dev, n);
 } B2_ABI_CATCH_CTX(ctx)
 
+int b200_domain_cache_trim(b200_ctx* ctx, size_t* bytes_freed) try {
+    if (!ctx) return B200_ERR_ARG;
+    if (set_device(ctx) != B200_OK) return B200_ERR_CUDA;
+    B2_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    const size_t f = ntt_domain_trim(ctx);
+    if (bytes_freed) *bytes_freed = f;
+    return B200_OK;
+} B2_ABI_CATCH_CTX(ctx)
+
 int b200_use_stream(b200_ctx* ctx, void* cuda_stream) try {
     if (!ctx) return B200_ERR_ARG;
     if (set_device(ctx) != B200_OK) return B200_ERR_CUDA;
@@ -606,6 +615,7 @@ int b200_set_option(b200_ctx* ctx, const char* key, long value) try {
     else if (k == "msm_overlap") { ctx->msm_overlap = value ? 1 : 0; }
     else if (k == "msm_precompute") { ctx->msm_precompute = value ? 1 : 0; }
     else if (k == "msm_fold_c") { if (value != 0 && (value < 8 || value > 24)) return ctx->fail(B200_ERR_ARG, "msm_fold_c out of range"); ctx->msm_fold_c = (int)value; }
+    else if (k == "ntt_tma") ctx->ntt_tma = value ? 1 : 0;
     else if (k == "ntt_threads") { if (value < 32 || value > 1024 || (value & (value - 1))) return ctx->fail(B200_ERR_ARG, "ntt_threads must be a power of two in 32..1024"); ctx->ntt_threads = (int)value; }
     else return ctx->fail(B200_ERR_ARG, "unknown option", key);
     return B200_OK;

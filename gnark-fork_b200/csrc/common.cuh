@@ -40,6 +40,7 @@ struct b200_ctx {
     int msm_mode() const { return (msm_c_override & 0xff) | ((msm_ba & 0xf) << 8) | (msm_ba_force ? 0x1000 : 0); }   // what MsmLayout decodes
     int msm_precompute = 1;                 // build folded-window tables for resident base sets
     int msm_fold_c = 0;                     // 0 = automatic (msm_fold_window)
+    int ntt_tma = 1;                        // 1: passes whose tile is a tensor box are staged by TMA (ntt_pass_tma_kernel); A/B in DESIGN.md
     int ntt_tile_log = 9, ntt_strided_stages = 8, ntt_threads = 128;   // measured best (scripts/ntt_sweep.py): many small CTAs overlap load, butterflies and store
 
     // optional per-kernel-class timing (b200_profile_*): CUDA event pairs on `stream`

@@ -123,6 +123,7 @@ int groth16_pk_upload(b200_ctx* ctx, const b200_groth16_pk_desc* d, b200_groth16
     memcpy(gen.l, d->generator, 32);
     memcpy(coset.l, d->coset_gen, 32);
     int st = ntt_domain_get(ctx, d->log_n, gen, coset, &pk->dom);
+    if (st == B200_OK) ++pk->dom->refs;
     const int si = d->shard_index, sc = d->shard_count;
     const bool ps = d->presliced != 0;
     size_t lo, hi;

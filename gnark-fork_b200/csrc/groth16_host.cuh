@@ -17,6 +17,7 @@ struct b200_groth16_pk {
     size_t k_lo = 0, z_lo = 0;       // first K / Z index of this shard
     size_t full_n_k = 0;             // len(pk.G1.K)
     size_t w_lo = 0, w_hi = 0;       // wire range the A / B maps of this shard reference (maps are relative to w_lo)
+    ~b200_groth16_pk() { if (dom) --dom->refs; }
 };
 
 namespace b200 {

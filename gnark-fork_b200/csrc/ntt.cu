@@ -3,6 +3,7 @@
 // /root/reference/backend/groth16/bn254/prove.go:369-375,393 (replaces iciclegnark.NttOnDevice /
 // INttOnDevice, /root/reference/backend/groth16/bn254/icicle/icicle.go:489-502).
 #include <cstdlib>
+#include <cuda.h>
 #include "ntt_host.cuh"
 
 namespace b200 {
@@ -128,6 +129,111 @@ __global__ void __launch_bounds__(NTT_THREADS) ntt_pass_kernel(const NttPassArgs
     }
 }
 
+// ---------------------------------------------------------------------------------------
+// TMA-staged variant of the pass (north_star: "TMA-staged shared-memory butterflies").  The tile of a pass is a box
+// of a tensor view of the vector -- [top][2^S coupled rows, stride 2^L elements][2^LB contiguous elements] for a
+// strided pass, [rows of 64 elements] for the contiguous one -- so ONE cp.async.bulk.tensor (UTMALDG) brings it into
+// shared memory, signalled on an mbarrier, and one UTMASTG writes it back: no per-element index arithmetic, no LSU
+// instructions and no registers on the load / store path; the butterflies are the same radix-2 network on the dense
+// tile.  Used for passes whose store index is the buffer index (all single-GPU passes and the in-place passes of the
+// distributed local phases); option "ntt_tma" (b200_set_option), A/B numbers in DESIGN.md.
+// ---------------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+struct DenseTile {
+    uint4* base;
+    __device__ __forceinline__ Fr get(uint32_t i) const {
+        const uint4 a = base[2 * i], b = base[2 * i + 1];
+        Fr f;
+        f.l[0] = a.x; f.l[1] = a.y; f.l[2] = a.z; f.l[3] = a.w;
+        f.l[4] = b.x; f.l[5] = b.y; f.l[6] = b.z; f.l[7] = b.w;
+        return f;
+    }
+    __device__ __forceinline__ void put(uint32_t i, const Fr& f) {
+        base[2 * i] = make_uint4(f.l[0], f.l[1], f.l[2], f.l[3]);
+        base[2 * i + 1] = make_uint4(f.l[4], f.l[5], f.l[6], f.l[7]);
+    }
+};
+
+template <int DIT>
+__global__ void __launch_bounds__(NTT_THREADS) ntt_pass_tma_kernel(const __grid_constant__ CUtensorMap tmap, const NttPassArgs a,
+                                                                   const int contiguous) {
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    __shared__ __align__(8) uint64_t mbar;
+    DenseTile sm{reinterpret_cast<uint4*>(smem_raw)};
+    const NttPassGeom g = a.g;
+    const uint32_t tile = blockIdx.x;
+    const uint32_t tile_n = 1u << g.TL;
+    // box coordinates (u64 units along dim 0)
+    int32_t c0, c1, c2;
+    if (contiguous) { c0 = 0; c1 = (int32_t)(tile << (g.TL - 6u)); c2 = 0; }
+    else {
+        const uint32_t midbits = g.L - g.LB;
+        c0 = (int32_t)((tile & ((1u << midbits) - 1u)) << (g.LB + 2u)); c1 = 0; c2 = (int32_t)(tile >> midbits);
+    }
+    const uint32_t bar = smem_u32(&mbar), dst = smem_u32(smem_raw);
+    if (threadIdx.x == 0) {
+        asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar));
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(tile_n * 32u) : "memory");
+        asm volatile("cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];"
+                     ::"r"(dst), "l"(reinterpret_cast<uint64_t>(&tmap)), "r"(bar), "r"(c0), "r"(c1), "r"(c2) : "memory");
+    }
+    __syncthreads();     // the barrier is initialised for everybody
+    {
+        uint32_t done = 0;
+        while (!done) {
+            asm volatile("{ .reg .pred p; mbarrier.try_wait.parity.shared::cta.b64 p, [%1], 0; selp.u32 %0, 1, 0, p; }"
+                         : "=r"(done) : "r"(bar) : "memory");
+        }
+    }
+    if (a.pre) {         // coset scaling fused in the first pass: one sweep over the tile as it sits in shared memory
+        for (uint32_t loc = threadIdx.x; loc < tile_n; loc += blockDim.x)
+            sm.put(loc, sm.get(loc) * ldg_fr(a.pre + ntt_map(a.gmap, ntt_gidx(g, tile, loc))));
+        __syncthreads();
+    }
+    const uint32_t n_bf = tile_n >> 1;
+    for (uint32_t k = 0; k < g.S; ++k) {
+        const uint32_t bit = ntt_stage_bit(g, DIT, k);
+        const uint32_t s = a.s_off + g.s0 + k;
+        const bool last = (k + 1 == g.S) && (a.post || a.has_post_scalar);
+        for (uint32_t bf = threadIdx.x; bf < n_bf; bf += blockDim.x) {
+            const uint32_t i0 = ntt_bf_lower(bf, bit), i1 = i0 | (1u << bit);
+            const uint32_t b0 = ntt_gidx(g, tile, i0);
+            const uint32_t g0 = ntt_map(a.gmap, b0);
+            const uint32_t e = ntt_twiddle_exp(a.glog_n, DIT, s, g0);
+            const Fr u = sm.get(i0), v = sm.get(i1);
+            Fr x, y;
+            if (DIT) {
+                const Fr t = (e == 0) ? v : v * ldg_fr(a.tw + e);
+                x = u + t; y = u - t;
+            } else {
+                const Fr d = u - v;
+                x = u + v; y = (e == 0) ? d : d * ldg_fr(a.tw + e);
+            }
+            if (last) {      // scaling fused in the last stage of the last pass (1/n, coset, den tables)
+                if (a.post) {
+                    x = x * ldg_fr(a.post + g0);
+                    y = y * ldg_fr(a.post + ntt_map(a.gmap, ntt_gidx(g, tile, i1)));
+                }
+                if (a.has_post_scalar) { x = x * a.post_scalar; y = y * a.post_scalar; }
+            }
+            sm.put(i0, x);
+            sm.put(i1, y);
+        }
+        __syncthreads();
+    }
+    // generic-proxy writes to shared memory must be visible to the async proxy before the bulk store reads them
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        asm volatile("cp.async.bulk.tensor.3d.global.shared::cta.bulk_group [%0, {%2, %3, %4}], [%1];"
+                     ::"l"(reinterpret_cast<uint64_t>(&tmap)), "r"(dst), "r"(c0), "r"(c1), "r"(c2) : "memory");
+        asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+        asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");     // the tile must outlive the read of the store
+    }
+}
+
 // out[pos(k)] = mult * base^k for k < count; pos = k or bitrev_{log_n}(k).  Each thread owns a
 // run of 16 consecutive exponents: one square-and-multiply, then 15 products.
 constexpr int POW_RUN = 16;
@@ -229,9 +335,73 @@ int ntt_domain_table(b200_ctx* ctx, NttDomain* d, NttDomain::Table t, const Fr**
     return B200_OK;
 }
 
+size_t ntt_domain_trim(b200_ctx* ctx) {
+    size_t freed = 0;
+    std::vector<NttDomain*> keep;
+    for (NttDomain* d : ctx->domains) {
+        if (d->refs > 0) { keep.push_back(d); continue; }
+        freed += d->tw_fwd.bytes + d->tw_inv.bytes;
+        for (auto& t : d->tab) freed += t.bytes;
+        delete d;
+    }
+    ctx->domains.swap(keep);
+    return freed;
+}
+
 void ntt_domain_free_all(b200_ctx* ctx) {
     for (NttDomain* d : ctx->domains) delete d;
     ctx->domains.clear();
+}
+
+// ---- host side of the TMA variant ------------------------------------------------------------------------
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+static EncodeTiledFn tma_encoder() {     // the driver entry point through the runtime: no link-time dependency on libcuda
+    static EncodeTiledFn fn = [] {
+        void* p = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) != cudaSuccess || q != cudaDriverEntryPointSuccess) p = nullptr;
+        cudaGetLastError();
+        return reinterpret_cast<EncodeTiledFn>(p);
+    }();
+    return fn;
+}
+
+// can this pass run as one tensor box per tile?  (box dimensions are at most 256 elements each)
+static bool ntt_tma_ok(const NttPassArgs& a, size_t n_buf, int* contiguous) {
+    const NttPassGeom& g = a.g;
+    if (a.pull.on || a.src != a.dst) return false;
+    if (a.smap.m != 31u || a.smap.sh_hi || a.smap.sh_lo || a.smap.add) return false;     // store index = buffer index
+    if (n_buf < ((size_t)1 << g.TL) || g.TL < 6 || g.TL > 12) return false;
+    *contiguous = (g.L == 0 && g.LB == 0) ? 1 : 0;
+    if (*contiguous) return g.S == g.TL && g.TL - 6u <= 8u && g.log_n >= g.TL;
+    return g.LB <= 6 && g.S <= 8 && g.L >= g.LB && g.L + g.S <= g.log_n;
+}
+
+static int ntt_tma_map(b200_ctx* ctx, const NttPassArgs& a, size_t n_buf, int contiguous, CUtensorMap* out) {
+    EncodeTiledFn enc = tma_encoder();
+    if (!enc) return ctx->fail(B200_ERR_UNSUPPORTED, "cuTensorMapEncodeTiled is not available in this driver");
+    const NttPassGeom& g = a.g;
+    cuuint64_t dim[3], stride[2];
+    cuuint32_t box[3], est[3] = {1, 1, 1};
+    if (contiguous) {          // rows of 64 elements (256 u64); a tile is 2^(TL-6) consecutive rows
+        dim[0] = 256; dim[1] = n_buf >> 6; dim[2] = 1;
+        stride[0] = 2048; stride[1] = (cuuint64_t)n_buf * 32;
+        box[0] = 256; box[1] = 1u << (g.TL - 6u); box[2] = 1;
+    } else {                   // [top][2^S rows, stride 2^L elements][2^L elements]; a tile takes 2^LB of the inner ones
+        dim[0] = (cuuint64_t)4 << g.L; dim[1] = (cuuint64_t)1 << g.S; dim[2] = n_buf >> (g.L + g.S);
+        stride[0] = (cuuint64_t)32 << g.L; stride[1] = (cuuint64_t)32 << (g.L + g.S);
+        box[0] = 4u << g.LB; box[1] = 1u << g.S; box[2] = 1;
+    }
+    const CUresult r = enc(out, CU_TENSOR_MAP_DATA_TYPE_UINT64, 3, const_cast<Fr*>(a.src), dim, stride, box, est, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                           CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) {
+        char msg[64];
+        snprintf(msg, sizeof msg, "CUresult %d", (int)r);
+        return ctx->fail(B200_ERR_CUDA, "cuTensorMapEncodeTiled", msg);
+    }
+    return B200_OK;
 }
 
 static int ntt_launch_pass(b200_ctx* ctx, const NttPassArgs& a, int dit, size_t n_buf) {
@@ -241,8 +411,16 @@ static int ntt_launch_pass(b200_ctx* ctx, const NttPassArgs& a, int dit, size_t 
     if (threads > NTT_THREADS) threads = NTT_THREADS;
     if (threads < 32) threads = 32;
     const size_t smem = smem_tile_bytes(a.g.TL);
+    int contiguous = 0;
+    CUtensorMap tmap;
+    const bool tma = ctx->ntt_tma && tma_encoder() && ntt_tma_ok(a, n_buf, &contiguous);   // else the per-thread-load pass (same GPU path)
+    if (tma) B2_TRY(ntt_tma_map(ctx, a, n_buf, contiguous, &tmap));
     const int span = ctx->prof_begin(B200_PROF_NTT_PASS, (double)n_buf * a.g.S * 0.5);
-    if (dit) ntt_pass_kernel<1><<<tiles, threads, smem, ctx->stream>>>(a);
+    if (tma) {
+        const size_t dense = (size_t)32 << a.g.TL;
+        if (dit) ntt_pass_tma_kernel<1><<<tiles, threads, dense, ctx->stream>>>(tmap, a, contiguous);
+        else ntt_pass_tma_kernel<0><<<tiles, threads, dense, ctx->stream>>>(tmap, a, contiguous);
+    } else if (dit) ntt_pass_kernel<1><<<tiles, threads, smem, ctx->stream>>>(a);
     else ntt_pass_kernel<0><<<tiles, threads, smem, ctx->stream>>>(a);
     ctx->prof_end(span);
     ctx->n_launches += 1;
@@ -253,6 +431,8 @@ static int ntt_launch_pass(b200_ctx* ctx, const NttPassArgs& a, int dit, size_t 
 static int ntt_prepare(b200_ctx* ctx) {
     B2_CUDA(ctx, cudaFuncSetAttribute(ntt_pass_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_tile_bytes(12)));
     B2_CUDA(ctx, cudaFuncSetAttribute(ntt_pass_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_tile_bytes(12)));
+    B2_CUDA(ctx, cudaFuncSetAttribute(ntt_pass_tma_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 32 << 12));
+    B2_CUDA(ctx, cudaFuncSetAttribute(ntt_pass_tma_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 32 << 12));
     return B200_OK;
 }
 

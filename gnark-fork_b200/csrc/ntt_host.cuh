@@ -18,6 +18,7 @@ struct NttDomain {
         NUM_TABLES
     };
     unsigned log_n = 0;
+    int refs = 0;           // resident keys that point at this domain (b200_domain_cache_trim frees the unreferenced ones)
     Fr gen, coset, gen_inv, coset_inv, ninv, den;
     DevBuf tw_fwd, tw_inv;  // w^j, w^-j for j < n/2
     DevBuf tab[NUM_TABLES];
@@ -30,6 +31,8 @@ int gen_powers(b200_ctx* ctx, Fr* out, const Fr& base, const Fr& mult, size_t co
 int ntt_domain_get(b200_ctx* ctx, unsigned log_n, const Fr& gen, const Fr& coset, NttDomain** out);
 int ntt_domain_table(b200_ctx* ctx, NttDomain* d, NttDomain::Table t, const Fr** out);
 void ntt_domain_free_all(b200_ctx* ctx);
+// frees every cached domain no resident key refers to; returns the bytes released
+size_t ntt_domain_trim(b200_ctx* ctx);
 // one transform on a device-resident vector.  pre / post: optional per-element scale tables
 // (indexed by memory position) applied when loading the first pass / storing the last pass;
 // post_scalar: optional single factor applied with the last store.

@@ -14,6 +14,7 @@
 //   * commitments are the folded-window G1 MSM against two resident SRS tables.
 // Fiat-Shamir (SHA-256) and the O(1) group arithmetic (blinding commitments, folded digests) run on the host,
 // as in the reference.
+#include <atomic>
 #include <chrono>
 #include <future>
 #include <vector>
@@ -40,6 +41,7 @@ struct b200_plonk_pk {
     b200_bases *srs = nullptr, *srs_lag = nullptr;
     G1Affine srs_lo[3], srs_hi[3];   // pk.Kzg.G1[0..2], [n..n+2]  (commitBlindingFactor, prove.go:1159-1172)
     G1Affine vk_pts[8];              // S1 S2 S3 Ql Qr Qm Qo Qk
+    mutable std::atomic<bool> in_flight{false};     // the per-proof workspace below is per KEY: one proof at a time
     uint32_t shard_index = 0, shard_count = 1;      // MSM point ranges and quotient cosets of this rank
     size_t srs_lo_idx = 0, srs_hi_idx = 0, lag_lo = 0, lag_hi = 0;
     // BSB22 (api.Commit circuits)
@@ -327,6 +329,8 @@ static void plonk_pk_delete(b200_ctx* ctx, b200_plonk_pk* pk) {
     if (!pk) return;
     if (pk->srs) b200_bases_free(ctx, pk->srs);
     if (pk->srs_lag) b200_bases_free(ctx, pk->srs_lag);
+    if (pk->d0) --pk->d0->refs;
+    if (pk->d1) --pk->d1->refs;
     delete pk;
 }
 
@@ -369,7 +373,9 @@ int b200_plonk_pk_upload(b200_ctx* ctx, int curve, const b200_plonk_pk_desc* d, 
     Fr gen, gen_big, cg;
     memcpy(gen.l, d->generator, 32); memcpy(gen_big.l, d->generator_big, 32); memcpy(cg.l, d->coset_gen, 32);
     int st = ntt_domain_get(ctx, d->log_n, gen, cg, &pk->d0);
+    if (st == B200_OK) ++pk->d0->refs;
     if (st == B200_OK) st = ntt_domain_get(ctx, d->log_big, gen_big, cg, &pk->d1);
+    if (st == B200_OK) ++pk->d1->refs;
     if (st != B200_OK) { plonk_pk_delete(ctx, pk); return st; }
     cudaStream_t s = ctx->stream;
     auto fail_cuda = [&](cudaError_t e, const char* what) {
@@ -487,6 +493,7 @@ struct b200_plonk_session {
         if (fh_digest_task.valid()) fh_digest_task.wait();
         for (auto e : ev_cp) if (e) cudaEventDestroy(e);
         for (auto e : ev_t) if (e) cudaEventDestroy(e);
+        if (pk) pk->in_flight.store(false);     // the key's workspace is free for the next proof
     }
     void lap(float& slot) { const double t = now_ms(); slot += (float)(t - t0); t0 = t; }
     const Fr* bl() const { return bp; }
@@ -856,8 +863,11 @@ int b200_plonk_session_begin(b200_ctx* ctx, const b200_plonk_pk* pk, const uint6
     if (nb && (!bsb || !bsb->pi2 || !bsb->commitments || !bsb->values)) return ctx->fail(B200_ERR_ARG, "the key has BSB22 commitments: bsb is required");
     if (pk->shard_count > 1 && !blinding) return ctx->fail(B200_ERR_ARG, "a sharded proof needs the same blinding on every rank: pass it");
     if (3 * (pk->n + 2) > pk->big) return ctx->fail(B200_ERR_ARG, "big domain below 3(n+2)");
+    // the workspace of a proof lives in the key (and in the ctx): a second session on the same key before the first one
+    // finished would silently corrupt both proofs -- refuse it
+    if (pk->in_flight.exchange(true)) return ctx->fail(B200_ERR_ARG, "a proof is already in flight on this proving key (a key and a ctx prove one proof at a time)");
     std::unique_ptr<b200_plonk_session> S(new b200_plonk_session());
-    S->pk = pk;
+    S->pk = pk;          // ~b200_plonk_session releases the key
     S->nb = nb;
     const size_t n = pk->n, N4 = n + 4;
     for (uint32_t k = 0; k < nb; ++k) {

@@ -38,6 +38,8 @@ class RawProvingKey:
     infinity_a: np.ndarray | None = None
     infinity_b: np.ndarray | None = None
     size: int = 0
+    commitment_keys: list = field(default_factory=list)   # per Pedersen key: ((basis offset, n), (basisExpSigma offset, n))
+    domain_header_bytes: int = 168                        # which fft.Domain layout matched (168, or 169 with a trailing flag byte)
 
 
 _R_MOD = {api.BN254: 0x30644E72E131A029B85045B68181585D2833E84879B9709143E1F593F0000001,
@@ -49,7 +51,23 @@ def fr_limbs(x: int, curve: int) -> np.ndarray:
 
 
 def parse(buf, curve: int = api.BN254) -> RawProvingKey:
-    """Offsets and lengths of every section of a WriteRawTo file; raises PkFormatError on truncation or inconsistency."""
+    """Offsets and lengths of every section of a WriteRawTo file; raises PkFormatError on truncation or inconsistency.
+    The fft.Domain header is the 168 bytes gnark-crypto v0.12 writes; later versions append one `withPrecompute` byte:
+    when the 168-byte layout does not validate the 169-byte one is tried and `domain_header_bytes` says which matched
+    (the layout is recalled, not pinned against the module -- a wrong guess is a loud PkFormatError, never a misparse:
+    every section length is cross-checked against the infinity bitmaps)."""
+    first = None
+    for extra in (0, 1):
+        try:
+            pk = _parse(buf, curve, extra)
+            pk.domain_header_bytes = 168 + extra
+            return pk
+        except PkFormatError as e:
+            first = first or e
+    raise first
+
+
+def _parse(buf, curve: int, domain_extra: int) -> RawProvingKey:
     mv = memoryview(buf)
     fb = 8 * api.fp_words(curve)
     g1, g2 = 2 * fb, 4 * fb
@@ -73,6 +91,7 @@ def parse(buf, curve: int = api.BN254) -> RawProvingKey:
     r = _R_MOD[curve]
     if pow(gen, card, r) != 1 or (card > 1 and pow(gen, card // 2, r) != r - 1):
         raise PkFormatError("Domain.Generator is not a primitive root of unity of order Cardinality (wrong curve?)")
+    take(domain_extra)
     pk = RawProvingKey(curve, card, gen, coset)
     for name in ("alpha", "beta", "delta"):
         pk.points[name] = (take(g1), 1)
@@ -92,8 +111,20 @@ def parse(buf, curve: int = api.BN254) -> RawProvingKey:
     if pk.slices["a"][1] != pk.nb_wires - pk.nb_infinity_a or pk.slices["b"][1] != pk.nb_wires - pk.nb_infinity_b \
             or pk.slices["g2b"][1] != pk.slices["b"][1]:
         raise PkFormatError("len(G1.A), len(G1.B), len(G2.B) disagree with the infinity bitmaps (setup.go:231-262)")
-    if u(4) != 0:
-        raise PkFormatError("proving keys with Pedersen commitment keys are not supported by this loader")
+    # pk.CommitmentKeys (marshal.go:276-293,364): per key the Pedersen basis and basisExpSigma as two raw G1 slices.
+    # They stay host-side data (prove.go:95,134: Commit / BatchProve run on the CPU in the reference and here); the
+    # loader records where they are so the glue can hand them to pedersen without decoding the rest of the file.
+    nb_keys = u(4)
+    if nb_keys > 4096:
+        raise PkFormatError(f"implausible number of commitment keys: {nb_keys}")
+    pk.commitment_keys = []
+    for _ in range(nb_keys):
+        nb = u(4)
+        basis = (take(nb * g1), nb)
+        ns = u(4)
+        if ns != nb:
+            raise PkFormatError("a Pedersen key's basis and basisExpSigma differ in length")
+        pk.commitment_keys.append((basis, (take(ns * g1), ns)))
     pk.size = pos
     return pk
 

@@ -60,6 +60,7 @@ extern "C" {
 #define b200_dev_alloc b200_bls12377_dev_alloc
 #define b200_dev_free b200_bls12377_dev_free
 #define b200_device_count b200_bls12377_device_count
+#define b200_domain_cache_trim b200_bls12377_domain_cache_trim
 #define b200_fp_vec_mul b200_bls12377_fp_vec_mul
 #define b200_fr_batch_inverse_dev b200_bls12377_fr_batch_inverse_dev
 #define b200_fr_mul_sub_dev b200_bls12377_fr_mul_sub_dev
@@ -178,7 +179,8 @@ const char *b200_version(void);
  * bit 1: G1 / G2 bucket accumulation keeps its running sum in shared memory; default G2 only on BN254, off on
  * BLS12-377), "msm_ba" (batched-affine pre-reduction rounds, default 0), "ntt_tile_log" (log2 of the
  * shared-memory tile, 6..12), "ntt_strided_stages" (max stages of a strided NTT pass, 1..12),
- * "ntt_threads" (threads per NTT CTA, power of two). */
+ * "ntt_threads" (threads per NTT CTA, power of two), "ntt_tma" (1 = NTT passes staged by TMA: one cp.async.bulk.tensor
+ * per tile in, one out; 0 = per-thread vector loads). */
 int b200_set_option(b200_ctx *ctx, const char *key, long value);
 /* Run all subsequent work of the context on the caller's CUDA stream (a cudaStream_t of the
  * context's device; NULL: back to the context's own stream).  Drains the previous stream first. */
@@ -238,10 +240,15 @@ int b200_profile_read(b200_ctx *ctx, b200_profile *out); /* synchronises, return
  *   generator  Domain.Generator (primitive 2^log_n-th root), coset_gen = Domain.FrMultiplicativeGen;
  *              both are INPUTS taken from pk.Domain so the device never recomputes a convention.
  * Twiddle and coset tables are built on the device once per (log_n, generator, coset_gen) and
- * cached in the ctx. */
+ * cached in the ctx.
+ * (see b200_domain_cache_trim below) */
 int b200_ntt(b200_ctx *ctx, int curve, uint64_t *host_inout, unsigned log_n, int inverse, int decimation,
              int on_coset, const uint64_t *generator, const uint64_t *coset_gen);
-/* Same on a device-resident vector; kernel_ms (optional) receives the CUDA-event time. */
+/* The domain cache only grows by itself (a 2^24 domain with its computeH tables is ~2 GiB): a long-lived prover that has
+ * freed the keys of a size calls b200_domain_cache_trim, which releases every cached domain no resident key refers
+ * to (bytes_freed optional). */
+int b200_domain_cache_trim(b200_ctx *ctx, size_t *bytes_freed);
+/* Same as b200_ntt on a device-resident vector; kernel_ms (optional) receives the CUDA-event time. */
 int b200_ntt_dev(b200_ctx *ctx, int curve, void *dev_inout, unsigned log_n, int inverse, int decimation,
                  int on_coset, const uint64_t *generator, const uint64_t *coset_gen, float *kernel_ms);
 
@@ -664,6 +671,10 @@ int b200_plonk_prove_bsb22(b200_ctx *ctx, const b200_plonk_pk *pk, const uint64_
  *   step 5  (2 totals) -> 1 partial [batch opening quotient]
  *   finish  (1 total)  -> the proof (identical on every rank); frees the session.
  * b200_plonk_prove_bsb22 is exactly this sequence with totals = partials.  A sharded proof requires `blinding`. */
+/* Re-entrancy: the per-proof workspace lives in the proving key and in the ctx, so a key (and a ctx) proves ONE proof
+ * at a time.  b200_plonk_session_begin (and therefore b200_plonk_prove*) returns B200_ERR_ARG while another session on
+ * the same key is open; a Go glue serialises Prove calls per key with a mutex or uploads the key once
+ * per concurrent prover. */
 typedef struct b200_plonk_session b200_plonk_session;
 int b200_plonk_session_begin(b200_ctx *ctx, const b200_plonk_pk *pk, const uint64_t *l, const uint64_t *r, const uint64_t *o,
                              const uint64_t *public_witness, const uint64_t *blinding, const b200_plonk_bsb22 *bsb,

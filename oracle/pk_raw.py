@@ -46,10 +46,13 @@ def domain_bytes(d, r_mod: int) -> bytes:
         fr(d.coset_gen) + fr(d.coset_gen_inv)
 
 
-def write_raw(pk, curve) -> bytes:
-    """pk: oracle groth16.ProvingKey with points (setup(..., points=True)); curve: the oracle curve module."""
+def write_raw(pk, curve, commitment_keys=(), domain_trailer: bytes = b"") -> bytes:
+    """pk: oracle groth16.ProvingKey with points (setup(..., points=True)); curve: the oracle curve module.
+    commitment_keys: [(basis points, basisExpSigma points)] -- pedersen.ProvingKey.WriteRawTo (marshal.go:276-293) writes
+    the two point slices of a key one after the other (gnark-crypto fr/pedersen, recalled).  domain_trailer: bytes a
+    later gnark-crypto appends to Domain.WriteTo (a one-byte `withPrecompute` flag); the pinned commit writes none."""
     fb = (curve.P.bit_length() + 7) // 8
-    out = [domain_bytes(pk.domain, curve.R)]
+    out = [domain_bytes(pk.domain, curve.R) + domain_trailer]
     out += [g1_raw(p, fb) for p in (pk.g1_alpha, pk.g1_beta, pk.g1_delta)]
     out += [slice_raw(s, g1_raw, fb) for s in (pk.g1_A, pk.g1_B, pk.g1_Z, pk.g1_K)]
     out += [g2_raw(p, fb) for p in (pk.g2_beta, pk.g2_delta)]
@@ -57,5 +60,7 @@ def write_raw(pk, curve) -> bytes:
     nb_wires = len(pk.infinity_A)
     out += [nb_wires.to_bytes(8, "big"), int(pk.nb_infinity_A).to_bytes(8, "big"), int(pk.nb_infinity_B).to_bytes(8, "big")]
     out += [bytes(1 if b else 0 for b in pk.infinity_A), bytes(1 if b else 0 for b in pk.infinity_B)]
-    out.append((0).to_bytes(4, "big"))      # no commitment keys
+    out.append(len(commitment_keys).to_bytes(4, "big"))
+    for basis, sigma in commitment_keys:
+        out += [slice_raw(basis, g1_raw, fb), slice_raw(sigma, g1_raw, fb)]
     return b"".join(out)

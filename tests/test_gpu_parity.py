@@ -218,3 +218,50 @@ def test_msm_resident_witness_like_scalars(ctx, cref, group, n):
     want = (cref.msm_g1 if group == 1 else cref.msm_g2)(scalars, bases)
     to_aff = cref.g1_jac_to_aff if group == 1 else cref.g2_jac_to_aff
     assert np.array_equal(to_aff(got), to_aff(want))
+
+
+def test_domain_cache_trim_keeps_domains_of_resident_keys(ctx, pkg, cref):
+    """b200_domain_cache_trim frees the cached NTT domains no key refers to; a resident key's domain survives and the
+    key still proves afterwards."""
+    from tests.test_gpu_groth16 import build_trapdoor_key
+    nb_mul = (1 << 9) - 1
+    r1cs, td, pk, vk, pkh, vkpts = build_trapdoor_key(ctx, cref, nb_mul)
+    w, a, b, c = G.mul_chain_witness(nb_mul, 2)
+    args = [util.fr_arr(x) for x in (a, b, c, w)]
+    before = ctx.groth16_prove_core(pkh, *args)[0].as_dict()
+    x = rand_field(np.random.default_rng(1), 1 << 11)
+    d = N.Domain(1 << 11)
+    ctx.ntt(x, 11, 0, 0, 0, cref.fr(d.generator), cref.fr(d.coset_gen))      # caches a 2^11 domain nobody owns
+    assert ctx.domain_cache_trim() >= (1 << 10) * 32 * 2
+    after = ctx.groth16_prove_core(pkh, *args)[0].as_dict()
+    for k in ("ar", "bs1", "krs", "krs2"):      # Jacobian representatives depend on the accumulation order: compare the points
+        assert np.array_equal(pkg.g1_jac_to_affine(before[k]), pkg.g1_jac_to_affine(after[k])), k
+    assert np.array_equal(pkg.g2_jac_to_affine(before["bs2"]), pkg.g2_jac_to_affine(after["bs2"]))
+    assert np.array_equal(ctx.ntt(x, 11, 0, 0, 0, cref.fr(d.generator), cref.fr(d.coset_gen)), cref.ntt(x, 11, 0, 0, 0, cref.fr(d.generator), cref.fr(d.coset_gen)))
+    pkh.free()
+    ctx.domain_cache_trim()
+
+
+@pytest.mark.parametrize("log_n,tile_log", [(6, 9), (9, 9), (10, 9), (13, 9), (16, 9), (18, 9), (20, 9), (22, 9), (20, 10), (22, 11), (20, 12), (14, 6)])
+def test_ntt_tma_staged_passes_vs_oracle(ctx, cref, log_n, tile_log):
+    """Option ntt_tma: tiles staged by cp.async.bulk.tensor (ntt_pass_tma_kernel) -- every variant bit-exact vs the
+    oracle, for several tile sizes (the box shapes change with the tile), and computeH with its fused scale tables."""
+    rng = np.random.default_rng(500 + log_n + tile_log)
+    n = 1 << log_n
+    x = rand_field(rng, n)
+    d = N.Domain(n)
+    gen, cg = cref.fr(d.generator), cref.fr(d.coset_gen)
+    ctx.set_option("ntt_tma", 1)
+    ctx.set_option("ntt_tile_log", tile_log)
+    try:
+        for inverse in (0, 1):
+            for dec in (0, 1):
+                for coset in (0, 1):
+                    got = ctx.ntt(x, log_n, inverse, dec, coset, gen, cg)
+                    assert np.array_equal(got, cref.ntt(x, log_n, inverse, dec, coset, gen, cg)), (log_n, tile_log, inverse, dec, coset)
+        if log_n <= 20:
+            a, b, c = rand_field(rng, n - 3), rand_field(rng, n - 3), rand_field(rng, n - 3)
+            assert np.array_equal(ctx.compute_h(a, b, c, log_n, gen, cg), cref.compute_h(a, b, c, log_n, gen, cg))
+    finally:
+        ctx.set_option("ntt_tma", 0)
+        ctx.set_option("ntt_tile_log", 9)

@@ -139,11 +139,11 @@ def test_device_setup_mirror_matches_oracle_setup(ctx, pkg, log_n):
     assert pkg.plonk_proof_bytes(got) == PP.proof_bytes(want)
 
 
-def test_large_proof_verifies(ctx, pkg):
-    """A proof at B200_PLONK_LOG_N rows (default 2^16; run with 22 for BASELINE.json config 4) made from a key
-    the device built, checked by the oracle's plonk.Verify restatement (O(1) work: it only needs vk and tau)."""
+@pytest.mark.parametrize("log_n", [16, 22])
+def test_large_proof_verifies(ctx, pkg, log_n):
+    """A proof at 2^16 and at 2^22 rows (BASELINE.json config 4's size) made from a key the device built, checked by
+    the oracle's plonk.Verify restatement (O(1) work: it only needs vk and tau)."""
     H = _host_mod()
-    log_n = int(os.environ.get("B200_PLONK_LOG_N", "16"))
     n = 1 << log_n
     tau = random.Random(99).randrange(1, R)
     trace, lro, nb_vars, nb_pub, L, Rr, O, pub = H.mul_chain(log_n, 7)
@@ -256,3 +256,30 @@ def test_sharded_proof_on_virtual_ranks(ctx, pkg, world, nb_mul, nb_commit):
             k.free()
     for p in proofs:
         assert pkg.plonk_proof_bytes(p) == PP.proof_bytes(want)
+
+
+def test_second_session_on_a_key_in_flight_is_refused(ctx, pkg):
+    """The per-proof workspace lives in the key: a second session before the first one ends would corrupt both proofs,
+    so b200_plonk_session_begin refuses it (and the binding refuses short l, r, o: the C ABI takes no lengths)."""
+    rng = random.Random(77)
+    spr = PP.mul_chain_scs(30)
+    pk = PP.setup(spr, rng.randrange(1, R))
+    sol = PP.mul_chain_solution(30, 5)
+    L, Rr, O = (util.fr_arr(v) for v in PP.evaluate_lro(spr, sol))
+    pub = util.fr_arr(sol[:1])
+    bl = PU.blinding_array(([1, 2], [3, 4], [5, 6], [7, 8, 9]))
+    dpk = PU.upload_pk(ctx, pk)
+    try:
+        s1 = ctx.plonk_session(dpk, L, Rr, O, pub, bl)
+        with pytest.raises(pkg.B200Error, match="already in flight"):
+            ctx.plonk_session(dpk, L, Rr, O, pub, bl)
+        with pytest.raises(pkg.B200Error, match="already in flight"):
+            ctx.plonk_prove(dpk, L, Rr, O, pub, bl)
+        s1.abandon()
+        with pytest.raises(pkg.B200Error, match="rows"):
+            ctx.plonk_prove(dpk, L[:-1], Rr, O, pub, bl)
+        got, _ = ctx.plonk_prove(dpk, L, Rr, O, pub, bl)          # the key is free again
+        want, _ = PP.prove(spr, pk, sol, ([1, 2], [3, 4], [5, 6], [7, 8, 9]))
+        assert pkg.plonk_proof_bytes(got) == PP.proof_bytes(want)
+    finally:
+        dpk.free()

@@ -59,7 +59,7 @@ def test_parser_rejects_damaged_files(pkg, small_key):
     bad = bytearray(raw); bad[7] = 3                          # cardinality not a power of two
     with pytest.raises(F.PkFormatError):
         F.parse(bytes(bad), pkg.BN254)
-    bad = bytearray(raw); bad[-1] = 1                         # a commitment key follows: unsupported
+    bad = bytearray(raw); bad[-1] = 1                         # says a commitment key follows, and none does: truncated
     with pytest.raises(F.PkFormatError):
         F.parse(bytes(bad), pkg.BN254)
     p = F.parse(bytes(raw), pkg.BN254)
@@ -68,6 +68,28 @@ def test_parser_rejects_damaged_files(pkg, small_key):
         F.parse(bytes(bad), pkg.BN254)
     with pytest.raises(F.PkFormatError):                      # a BN254 file read as BLS12-377
         F.parse(bytes(raw), pkg.BLS12_377)
+
+
+def test_parser_commitment_keys_and_domain_header_variants(pkg, small_key):
+    """pk.CommitmentKeys (marshal.go:276-293,364): the Pedersen keys' two point slices are located, not refused; and the
+    fft.Domain header is accepted with or without the one-byte flag later gnark-crypto versions append."""
+    _, _, pk, _ = small_key
+    F = _fmt(pkg)
+    basis = [B.g1_mul(B.G1_GEN, k) for k in (3, 5, 7)]
+    sigma = [B.g1_mul(B.G1_GEN, 11 * k) for k in (3, 5, 7)]
+    keys = [(basis, sigma), (basis[:1], sigma[:1])]
+    for trailer in (b"", b"\x01"):
+        raw = pk_raw.write_raw(pk, B, commitment_keys=keys, domain_trailer=trailer)
+        p = F.parse(raw, pkg.BN254)
+        assert p.size == len(raw) and p.domain_header_bytes == 168 + len(trailer)
+        assert [(b[1], s[1]) for b, s in p.commitment_keys] == [(3, 3), (1, 1)]
+        (boff, _), (soff, _) = p.commitment_keys[0]
+        assert raw[boff:boff + 64] == pk_raw.g1_raw(basis[0], 32) and raw[soff + 128: soff + 192] == pk_raw.g1_raw(sigma[2], 32)
+        assert p.slices["a"][1] == len(pk.g1_A)
+    bad = bytearray(pk_raw.write_raw(pk, B, commitment_keys=keys))
+    bad[p.commitment_keys[0][1][0] - 1 - len(b"\x01")] ^= 2     # basisExpSigma length differs from the basis length
+    with pytest.raises(F.PkFormatError):
+        F.parse(bytes(bad), pkg.BN254)
 
 
 @pytest.mark.gpu

@@ -76,20 +76,30 @@ class _PlonkBsb22(C.Structure):
     _fields_ = [("pi2", C.c_void_p), ("commitments", C.c_void_p), ("values", C.c_void_p)]
 
 
-class PlonkProof(C.Structure):
-    """b200_plonk_proof: plonk_bn254.Proof (prove.go:96-114), points affine, scalars Montgomery."""
-    _fields_ = [("lro", (C.c_uint64 * 8) * 3), ("z", C.c_uint64 * 8), ("h", (C.c_uint64 * 8) * 3),
-                ("batched_h", C.c_uint64 * 8), ("claimed", (C.c_uint64 * 4) * 7), ("zshift_h", C.c_uint64 * 8),
-                ("zshift_value", C.c_uint64 * 4), ("challenges", (C.c_uint64 * 4) * 5), ("nb_bsb22", C.c_uint64),
-                ("claimed_qcp", (C.c_uint64 * 4) * 8), ("bsb22", (C.c_uint64 * 8) * 8)]
+def _plonk_proof_struct(fw):
+    pw = 2 * fw        # u64 words of an affine G1 point
 
-    def as_dict(self):
-        return {k: np.array(getattr(self, k), dtype=np.uint64) for k, _ in self._fields_}
+    class _Proof(C.Structure):
+        """b200_plonk_proof: plonk.Proof (prove.go:96-114), points affine, scalars Montgomery."""
+        _fields_ = [("lro", (C.c_uint64 * pw) * 3), ("z", C.c_uint64 * pw), ("h", (C.c_uint64 * pw) * 3),
+                    ("batched_h", C.c_uint64 * pw), ("claimed", (C.c_uint64 * 4) * 7), ("zshift_h", C.c_uint64 * pw),
+                    ("zshift_value", C.c_uint64 * 4), ("challenges", (C.c_uint64 * 4) * 5), ("nb_bsb22", C.c_uint64),
+                    ("claimed_qcp", (C.c_uint64 * 4) * 8), ("bsb22", (C.c_uint64 * pw) * 8)]
+        FP_WORDS = fw
 
-    def all_claimed(self) -> np.ndarray:
-        """BatchedProof.ClaimedValues: the 7 fixed ones then Qcp_i(zeta), (7 + nb_bsb22, 4)."""
-        d = self.as_dict()
-        return np.concatenate([d["claimed"], d["claimed_qcp"][:int(self.nb_bsb22)]])
+        def as_dict(self):
+            return {k: np.array(getattr(self, k), dtype=np.uint64) for k, _ in self._fields_}
+
+        def all_claimed(self) -> np.ndarray:
+            """BatchedProof.ClaimedValues: the 7 fixed ones then Qcp_i(zeta), (7 + nb_bsb22, 4)."""
+            d = self.as_dict()
+            return np.concatenate([d["claimed"], d["claimed_qcp"][:int(self.nb_bsb22)]])
+    return _Proof
+
+
+PlonkProof = _plonk_proof_struct(4)             # BN254
+PlonkProof377 = _plonk_proof_struct(6)          # the struct of libb200prover_bls12377.so
+_PLONK_PROOF = {BN254: PlonkProof, BLS12_377: PlonkProof377}
 
 
 class _PlonkTimings(C.Structure):
@@ -194,7 +204,8 @@ def load_library(curve: int = BN254):
                         f"{' CURVE=bls12_377' if curve == BLS12_377 else ''}` "
                         "(or __graft_entry__.build()); there is no CPU fallback")
     lib = _Lib(C.CDLL(path), _SYM_PREFIX[curve])
-    Groth16MsmOut = _MSM_OUT[curve]     # the struct of THIS library's B200_FP_WORDS
+    Groth16MsmOut = _MSM_OUT[curve]     # the structs of THIS library's B200_FP_WORDS
+    PlonkProof = _PLONK_PROOF[curve]
     vp, sz, u, i = C.c_void_p, C.c_size_t, C.c_uint, C.c_int
     sig = {
         "b200_device_count": (i, []),
@@ -370,10 +381,14 @@ def groth16_proof_bytes(ar, bs, krs, curve=BN254) -> bytes:
     return out[:n].tobytes()
 
 
+def _proof_curve(proof) -> int:
+    return BLS12_377 if getattr(proof, "FP_WORDS", 4) == 6 else BN254
+
+
 def plonk_proof_bytes(proof: PlonkProof) -> bytes:
-    """Proof.WriteTo (plonk/bn254/marshal.go:41-66), 552 bytes for a proof without BSB22 commitments."""
-    lib = load_library()
-    out = np.zeros(552 + 64 * 8, dtype=np.uint8)
+    """Proof.WriteTo (plonk/bn254/marshal.go:41-66), 552 bytes for a BN254 proof without BSB22 commitments."""
+    lib = load_library(_proof_curve(proof))
+    out = np.zeros(9 * 48 + 8 + 32 * 16 + 48 * 8, dtype=np.uint8)
     n = lib.b200_plonk_proof_bytes(C.byref(proof), _ptr(out), out.shape[0])
     if n < 0:
         raise B200Error(f"b200_plonk_proof_bytes failed with status {n}")
@@ -382,10 +397,11 @@ def plonk_proof_bytes(proof: PlonkProof) -> bytes:
 
 def plonk_derive_challenges(vk_commitments, public_witness, proof: PlonkProof, vk_qcp=None) -> np.ndarray:
     """gamma, beta, alpha, zeta (4 x 4 u64 Montgomery) of the proof's commitments (verify.go:296-360)."""
-    lib = load_library()
-    vk = _u64(vk_commitments, (8, 8))
+    curve = _proof_curve(proof)
+    lib = load_library(curve)
+    vk = _u64(vk_commitments, (8, 2 * fp_words(curve)))
     pw = _u64(public_witness, (-1, 4))
-    qcp = None if vk_qcp is None else _u64(vk_qcp, (-1, 8))
+    qcp = None if vk_qcp is None else _u64(vk_qcp, (-1, 2 * fp_words(curve)))
     out = np.zeros((4, 4), dtype=np.uint64)
     st = lib.b200_plonk_derive_challenges(_ptr(vk), _ptr(qcp), _ptr(pw) if pw.shape[0] else None, pw.shape[0], C.byref(proof), _ptr(out))
     if st != 0:
@@ -500,8 +516,9 @@ class PlonkSession:
         self.ctx, self.h, self.partials = ctx, handle, partials
 
     def step(self, phase: int, totals=None) -> np.ndarray:
-        t = None if totals is None else _u64(totals, (-1, 12))
-        out = np.zeros((max(1, self.N_OUT[phase]), 12), dtype=np.uint64)
+        jw = 3 * self.ctx.fw
+        t = None if totals is None else _u64(totals, (-1, jw))
+        out = np.zeros((max(1, self.N_OUT[phase]), jw), dtype=np.uint64)
         self.ctx._check(self.ctx.lib.b200_plonk_session_step(self.ctx.h, self.h, phase, _ptr(t), _ptr(out) if self.N_OUT[phase] else None))
         self.partials = out[:self.N_OUT[phase]]
         return self.partials
@@ -513,8 +530,8 @@ class PlonkSession:
         return int(p.value), int(be.value), int(lb.value)
 
     def finish(self, totals):
-        proof, tm = PlonkProof(), _PlonkTimings()
-        t = _u64(totals, (-1, 12))
+        proof, tm = _PLONK_PROOF[self.ctx.curve](), _PlonkTimings()
+        t = _u64(totals, (-1, 3 * self.ctx.fw))
         h, self.h = self.h, None
         self.ctx._check(self.ctx.lib.b200_plonk_session_finish(self.ctx.h, h, _ptr(t), C.byref(proof), C.byref(tm)))
         return proof, {k: getattr(tm, k) for k, _ in tm._fields_}
@@ -867,9 +884,9 @@ class Context:
         keep = {k: _u64(v, (n, 4)) for k, v in dict(ql=ql, qr=qr, qm=qm, qo=qo, qk=qk, s1=s1, s2=s2, s3=s3).items()}
         keep["generator"], keep["generator_big"], keep["coset_gen"] = _u64(generator), _u64(generator_big), _u64(coset_gen)
         keep["perm"] = np.ascontiguousarray(perm, dtype=np.int64).reshape(3 * n)
-        keep["kzg_g1"] = _u64(kzg_g1, (n + 3, 8))
-        keep["kzg_lagrange_g1"] = _u64(kzg_lagrange_g1, (n, 8))
-        keep["vk_commitments"] = _u64(vk_commitments, (8, 8))
+        keep["kzg_g1"] = _u64(kzg_g1, (n + 3, 2 * self.fw))
+        keep["kzg_lagrange_g1"] = _u64(kzg_lagrange_g1, (n, 2 * self.fw))
+        keep["vk_commitments"] = _u64(vk_commitments, (8, 2 * self.fw))
         d = _PlonkPkDesc()
         d.log_n, d.log_big, d.nb_public, d.nb_bsb22 = log_n, log_big, nb_public, len(qcp)
         d.shard_index, d.shard_count = shard_index, shard_count
@@ -878,7 +895,7 @@ class Context:
         if len(qcp):
             cols = [_u64(q, (n, 4)) for q in qcp]
             ptrs = (C.c_void_p * len(cols))(*[c.ctypes.data for c in cols])
-            vq = _u64(vk_qcp, (len(cols), 8))
+            vq = _u64(vk_qcp, (len(cols), 2 * self.fw))
             ci = np.ascontiguousarray(commitment_index, dtype=np.uint64)
             d.qcp, d.vk_qcp, d.commitment_index = C.addressof(ptrs), vq.ctypes.data, ci.ctypes.data
         h = C.c_void_p()
@@ -895,7 +912,7 @@ class Context:
         if any(c.shape[0] != getattr(pk, "n", c.shape[0]) for c in cols):
             raise B200Error("every Pi2 column must hold n rows")
         ptrs = (C.c_void_p * len(cols))(*[c.ctypes.data for c in cols])
-        com, val = _u64(bsb["commitments"], (len(cols), 8)), _u64(bsb["values"], (len(cols), 4))
+        com, val = _u64(bsb["commitments"], (len(cols), 2 * self.fw)), _u64(bsb["values"], (len(cols), 4))
         return _PlonkBsb22(C.addressof(ptrs), com.ctypes.data, val.ctypes.data), (cols, ptrs, com, val)
 
     @staticmethod
@@ -914,7 +931,7 @@ class Context:
         bl = None if blinding is None else _u64(blinding, (9, 4))
         cb, keep = self._plonk_bsb(pk, bsb)
         h = C.c_void_p()
-        partials = np.zeros((3, 12), dtype=np.uint64)
+        partials = np.zeros((3, 3 * self.fw), dtype=np.uint64)
         self._check(self.lib.b200_plonk_session_begin(self.h, pk.h, _ptr(l), _ptr(r), _ptr(o), _ptr(pw) if pw.shape[0] else None,
                                                       _ptr(bl), None if cb is None else C.byref(cb), C.byref(h), _ptr(partials)))
         return PlonkSession(self, h, partials)
@@ -928,7 +945,7 @@ class Context:
         pw = _u64(public_witness, (-1, 4))
         self._plonk_check_lengths(pk, l, r, o, pw)
         bl = None if blinding is None else _u64(blinding, (9, 4))
-        proof, tm = PlonkProof(), _PlonkTimings()
+        proof, tm = _PLONK_PROOF[self.curve](), _PlonkTimings()
         cb, keep = self._plonk_bsb(pk, bsb)
         self._check(self.lib.b200_plonk_prove_bsb22(self.h, pk.h, _ptr(l), _ptr(r), _ptr(o), _ptr(pw) if pw.shape[0] else None,
                                                     _ptr(bl), None if cb is None else C.byref(cb), C.byref(proof), C.byref(tm)))

@@ -178,6 +178,7 @@ void fr_be(const Fr& m, uint8_t out[32]) {
 }
 // G1Affine.RawBytes / Marshal: X || Y big-endian; infinity = 0x40 then zeros
 constexpr int G1_RAW = 2 * FP_BYTES;   // 64 on BN254
+constexpr size_t AFF_WORDS = sizeof(G1Affine) / 8;   // u64 words of an affine G1 point at the ABI: 8 on BN254, 12 on BLS12-377
 void g1_raw(const G1Affine& p, uint8_t* out) {
     if (p.is_inf()) { memset(out, 0, G1_RAW); out[0] = 0x40; return; }
     fp_be(p.x, out);
@@ -338,10 +339,7 @@ extern "C" {
 
 int b200_plonk_pk_upload(b200_ctx* ctx, int curve, const b200_plonk_pk_desc* d, b200_plonk_pk** out) try {
     if (!ctx) return B200_ERR_ARG;
-#if defined(B2_CURVE_BLS12_377)
-    return ctx->fail(B200_ERR_UNSUPPORTED, "the PlonK prover is built for BN254 only (libb200prover.so)");
-#endif
-    if (curve != B200_BN254) return ctx->fail(B200_ERR_UNSUPPORTED, "only BN254 is built into this library");
+    if (curve != b200_build_curve()) return ctx->fail(B200_ERR_UNSUPPORTED, "curve not supported by this build (one library per curve)");
     if (cudaSetDevice(ctx->device) != cudaSuccess) return ctx->fail(B200_ERR_CUDA, "cudaSetDevice");
     if (!d || !out || !d->generator || !d->generator_big || !d->coset_gen || !d->ql || !d->qr || !d->qm || !d->qo || !d->qk || !d->s1 ||
         !d->s2 || !d->s3 || !d->perm || !d->kzg_g1 || !d->kzg_lagrange_g1 || !d->vk_commitments)
@@ -402,7 +400,7 @@ int b200_plonk_pk_upload(b200_ctx* ctx, int curve, const b200_plonk_pk_desc* d, 
     if (e == cudaSuccess) e = cudaMemcpyAsync(pk->perm.p, d->perm, 3 * n * sizeof(int64_t), cudaMemcpyHostToDevice, s);
     if (e != cudaSuccess) return fail_cuda(e, "PlonK key upload");
     memcpy(pk->srs_lo, d->kzg_g1, 3 * sizeof(G1Affine));
-    memcpy(pk->srs_hi, d->kzg_g1 + 8 * n, 3 * sizeof(G1Affine));
+    memcpy(pk->srs_hi, d->kzg_g1 + AFF_WORDS * n, 3 * sizeof(G1Affine));
     memcpy(pk->vk_pts, d->vk_commitments, 8 * sizeof(G1Affine));
     // coset scaling tables: shift_k = g * w_big^k  (shifters, prove.go:903-907)
     Fr shift = cg;
@@ -435,8 +433,8 @@ int b200_plonk_pk_upload(b200_ctx* ctx, int curve, const b200_plonk_pk_desc* d, 
     if (st == B200_OK) st = ntt_run(ctx, pk->d0, pk->qk_lag.as<Fr>(), 0, 1, nullptr, nullptr, nullptr);
     if (st == B200_OK && cudaStreamSynchronize(s) != cudaSuccess) st = ctx->fail(B200_ERR_CUDA, "PlonK key precomputation");
     // each rank keeps its point range of both SRS (the whole of them on one GPU)
-    if (st == B200_OK) st = b200_bases_upload(ctx, curve, 1, d->kzg_g1 + 8 * pk->srs_lo_idx, pk->srs_hi_idx - pk->srs_lo_idx, &pk->srs);
-    if (st == B200_OK) st = b200_bases_upload(ctx, curve, 1, d->kzg_lagrange_g1 + 8 * pk->lag_lo, pk->lag_hi - pk->lag_lo, &pk->srs_lag);
+    if (st == B200_OK) st = b200_bases_upload(ctx, curve, 1, d->kzg_g1 + AFF_WORDS * pk->srs_lo_idx, pk->srs_hi_idx - pk->srs_lo_idx, &pk->srs);
+    if (st == B200_OK) st = b200_bases_upload(ctx, curve, 1, d->kzg_lagrange_g1 + AFF_WORDS * pk->lag_lo, pk->lag_hi - pk->lag_lo, &pk->srs_lag);
     if (st != B200_OK) { plonk_pk_delete(ctx, pk); return st; }
     *out = pk;
     return B200_OK;
@@ -527,6 +525,7 @@ int commit_shard(b200_ctx* ctx, const b200_bases* srs, size_t lo, size_t hi, con
     for (int k = 0; k < live; ++k) out[idx[k]] = res[k];
     return B200_OK;
 }
+constexpr int JAC_WORDS = (int)(sizeof(G1Jac) / 8);   // 12 u64 on BN254, 18 on BLS12-377
 void put_jac(uint64_t* dst, const G1XYZZ& p) { const G1Jac j = p.to_jac(); memcpy(dst, &j, sizeof j); }
 G1XYZZ get_jac(const uint64_t* src) { G1Jac j; memcpy(&j, src, sizeof j); return xyzz_from_jac(j); }
 
@@ -560,7 +559,7 @@ int phase0(b200_ctx* ctx, b200_plonk_session& S, const uint64_t* l, const uint64
     }
     for (int k = 0; k < 3; ++k) B2_CUDA(ctx, cudaStreamWaitEvent(s, S.ev_cp[k], 0));
     B2_CUDA(ctx, cudaStreamWaitEvent(s, S.ev_t[1], 0));
-    for (int k = 0; k < 3; ++k) put_jac(partials + 12 * k, c[k]);
+    for (int k = 0; k < 3; ++k) put_jac(partials + JAC_WORDS * k, c[k]);
     S.lap(S.T.commit_lro_ms);
     B2_CUDA(ctx, cudaEventSynchronize(S.ev_t[1]));
     cudaEventElapsedTime(&S.T.h2d_ms, S.ev_t[0], S.ev_t[1]);   // on the copy stream, under the [L] [R] [O] commitments: not a summand of total_ms
@@ -572,7 +571,7 @@ int phase1(b200_ctx* ctx, b200_plonk_session& S, const uint64_t* totals, uint64_
     const size_t n = pk->n;
     const Fr* bps[3] = {S.bl(), S.br(), S.bo()};
     for (int k = 0; k < 3; ++k) {
-        G1XYZZ c = get_jac(totals + 12 * k);
+        G1XYZZ c = get_jac(totals + JAC_WORDS * k);
         c.add(S.blind_com[k].valid() ? S.blind_com[k].get() : commit_blinding(pk, bps[k], 2));
         S.lro[k] = c.to_affine();
     }
@@ -685,7 +684,7 @@ int phase3(b200_ctx* ctx, b200_plonk_session& S, uint64_t* partials) {
     const size_t cnt[3] = {n + 2, n + 2, n + 2};
     G1XYZZ c[3];
     B2_TRY(commit_shard(ctx, pk->srs, pk->srs_lo_idx, pk->srs_hi_idx, sc, cnt, 3, c));   // commitToQuotient, prove.go:1198-1218
-    for (int k = 0; k < 3; ++k) put_jac(partials + 12 * k, c[k]);
+    for (int k = 0; k < 3; ++k) put_jac(partials + JAC_WORDS * k, c[k]);
     S.lap(S.T.commit_h_ms);
     return B200_OK;
 }
@@ -695,7 +694,7 @@ int phase4(b200_ctx* ctx, b200_plonk_session& S, const uint64_t* totals, uint64_
     const size_t n = pk->n;
     NttDomain* d0 = pk->d0;
     for (int k = 0; k < 3; ++k) {
-        S.hx[k] = get_jac(totals + 12 * k);
+        S.hx[k] = get_jac(totals + JAC_WORDS * k);
         S.h_com[k] = S.hx[k].to_affine();
         bind_point(S.fs, "zeta", S.h_com[k]);
     }
@@ -783,7 +782,7 @@ int phase4(b200_ctx* ctx, b200_plonk_session& S, const uint64_t* totals, uint64_
     for (auto& f : terms) lin_digest.add(f.get());                // joined before any early return
     B2_TRY(st_commit);
     put_jac(partials, c[0]);
-    put_jac(partials + 12, pk->shard_index == 0 ? lin_digest : G1XYZZ::inf());
+    put_jac(partials + JAC_WORDS, pk->shard_index == 0 ? lin_digest : G1XYZZ::inf());
     S.lap(S.T.linearize_ms);
     return B200_OK;
 }
@@ -793,7 +792,7 @@ int phase5(b200_ctx* ctx, b200_plonk_session& S, const uint64_t* totals, uint64_
     const size_t n = pk->n;
     const uint32_t nb = S.nb;
     S.zs_h = get_jac(totals).to_affine();
-    S.lin_digest = get_jac(totals + 12).to_affine();
+    S.lin_digest = get_jac(totals + JAC_WORDS).to_affine();
     if (S.fh_digest_task.valid()) S.fh_digest = S.fh_digest_task.get();
     // ---- batch opening at zeta (batchOpening, prove.go:779-833; kzg.BatchOpenSinglePoint) --------------------
     B2_TRY(fr_poly_eval(ctx, S.fh, n + 2, S.zeta, &S.claimed[0]));
@@ -872,7 +871,7 @@ int b200_plonk_session_begin(b200_ctx* ctx, const b200_plonk_pk* pk, const uint6
     const size_t n = pk->n, N4 = n + 4;
     for (uint32_t k = 0; k < nb; ++k) {
         if (!bsb->pi2[k]) return ctx->fail(B200_ERR_ARG, "null Pi2 column");
-        memcpy(&S->bsb_com[k], bsb->commitments + 8 * k, sizeof(G1Affine));
+        memcpy(&S->bsb_com[k], bsb->commitments + AFF_WORDS * k, sizeof(G1Affine));
         memcpy(S->bsb_val[k].l, bsb->values + 4 * k, 32);
         S->pi2_br[k] = pk->bsb_work.as<Fr>() + (size_t)(3 * k) * n;
         S->pi2_cn[k] = S->pi2_br[k] + n;
@@ -974,8 +973,8 @@ int b200_plonk_derive_challenges(const uint64_t* vk_commitments, const uint64_t*
     if (p->nb_bsb22 > B200_PLONK_MAX_BSB22 || (p->nb_bsb22 && !vk_qcp)) return B200_ERR_ARG;
     auto pt = [](const uint64_t* src) { G1Affine a; memcpy(&a, src, sizeof a); return a; };
     Transcript fs({"gamma", "beta", "alpha", "zeta"});
-    for (int k = 0; k < 8; ++k) bind_point(fs, "gamma", pt(vk_commitments + 8 * k));
-    for (uint64_t k = 0; k < p->nb_bsb22; ++k) bind_point(fs, "gamma", pt(vk_qcp + 8 * k));
+    for (int k = 0; k < 8; ++k) bind_point(fs, "gamma", pt(vk_commitments + AFF_WORDS * k));
+    for (uint64_t k = 0; k < p->nb_bsb22; ++k) bind_point(fs, "gamma", pt(vk_qcp + AFF_WORDS * k));
     for (size_t k = 0; k < nb_public; ++k) { Fr x; memcpy(x.l, public_witness + 4 * k, 32); bind_fr(fs, "gamma", x); }
     for (int k = 0; k < 3; ++k) bind_point(fs, "gamma", pt(p->lro[k]));
     put_fr(out, derive(fs, "gamma"));
@@ -991,22 +990,23 @@ int b200_plonk_derive_challenges(const uint64_t* vk_commitments, const uint64_t*
 int b200_plonk_proof_bytes(const b200_plonk_proof* p, uint8_t* out, size_t cap) try {
     if (!p || !out || p->nb_bsb22 > B200_PLONK_MAX_BSB22) return B200_ERR_ARG;
     const uint32_t nb = (uint32_t)p->nb_bsb22;
-    if (cap < 552 + 64 * (size_t)nb) return B200_ERR_ARG;
+    const size_t FB = FP_BYTES;                       // a compressed G1 point: 32 bytes on BN254, 48 on BLS12-377
+    if (cap < 9 * FB + 8 + 32 * (8 + (size_t)nb) + FB * (size_t)nb) return B200_ERR_ARG;
     auto pt = [](const uint64_t* src) { G1Affine a; memcpy(&a, src, sizeof a); return a; };
     auto fr = [](const uint64_t* src) { Fr a; memcpy(a.l, src, 32); return a; };
     auto be32 = [](uint8_t* q, uint32_t v) { q[0] = (uint8_t)(v >> 24); q[1] = (uint8_t)(v >> 16); q[2] = (uint8_t)(v >> 8); q[3] = (uint8_t)v; };
     uint8_t* q = out;
-    for (int k = 0; k < 3; ++k) { g1_compress(pt(p->lro[k]), q); q += 32; }
-    g1_compress(pt(p->z), q); q += 32;
-    for (int k = 0; k < 3; ++k) { g1_compress(pt(p->h[k]), q); q += 32; }
-    g1_compress(pt(p->batched_h), q); q += 32;
+    for (int k = 0; k < 3; ++k) { g1_compress(pt(p->lro[k]), q); q += FB; }
+    g1_compress(pt(p->z), q); q += FB;
+    for (int k = 0; k < 3; ++k) { g1_compress(pt(p->h[k]), q); q += FB; }
+    g1_compress(pt(p->batched_h), q); q += FB;
     be32(q, 7 + nb); q += 4;                                                // []fr.Element: u32 BE length
     for (int k = 0; k < 7; ++k) { fr_be(fr(p->claimed[k]), q); q += 32; }
     for (uint32_t k = 0; k < nb; ++k) { fr_be(fr(p->claimed_qcp[k]), q); q += 32; }
-    g1_compress(pt(p->zshift_h), q); q += 32;
+    g1_compress(pt(p->zshift_h), q); q += FB;
     fr_be(fr(p->zshift_value), q); q += 32;
     be32(q, nb); q += 4;                                                    // Bsb22Commitments
-    for (uint32_t k = 0; k < nb; ++k) { g1_compress(pt(p->bsb22[k]), q); q += 32; }
+    for (uint32_t k = 0; k < nb; ++k) { g1_compress(pt(p->bsb22[k]), q); q += FB; }
     return (int)(q - out);
 } B2_ABI_CATCH_INT
 

@@ -16,7 +16,7 @@
  *     libb200prover_bls12377.so (make CURVE=bls12_377; bind it with -DB200_CURVE_BLS12_377): same entry
  *     points, curve argument B200_BLS12_377, Fr still 4 u64 but Fp = 6 u64 (R = 2^384), so G1Affine = 12,
  *     G1Jac = 18, G2Affine = 24, G2Jac = 36 u64 -- B200_FP_WORDS below sizes the structs.  Each library
- *     rejects the other curve's id with B200_ERR_UNSUPPORTED.  The PlonK entry points are BN254-only.
+ *     rejects the other curve's id with B200_ERR_UNSUPPORTED.  Both libraries hold the Groth16 and the PlonK prover.
  *   - Jacobian results are SOME representative of the point (not gnark-crypto's particular
  *     one); equality with MultiExp is defined on the affine-normalised point (FromJacobian).
  *   - Return value: 0 on success, a negative b200_status otherwise; b200_last_error(ctx) holds a
@@ -575,7 +575,8 @@ int b200_groth16_finalize(const b200_groth16_out *msm, const uint64_t *r, const 
 int b200_groth16_proof_bytes(const uint64_t *ar_affine, const uint64_t *bs_affine, const uint64_t *krs_affine,
                              uint8_t *out, size_t out_cap);
 
-/* ---- PlonK prover (BN254) ---------------------------------------------------------------------
+/* ---- PlonK prover (BN254; the BLS12-377 library runs the same code on its own field sizes:
+ * /root/reference/backend/plonk/bls12-377/prove.go is the same template) ------------------------
  * plonk_bn254.Prove (/root/reference/backend/plonk/bn254/prove.go:116-180) behind one call, with or
  * without BSB22 commitments (api.Commit circuits, at most B200_PLONK_MAX_BSB22 of them).  The solver stays
  * with the caller (prove.go:365-392 gives L, R, O); everything after it
@@ -615,19 +616,20 @@ typedef struct b200_plonk_pk_desc {
 int b200_plonk_pk_upload(b200_ctx *ctx, int curve, const b200_plonk_pk_desc *desc, b200_plonk_pk **out);
 int b200_plonk_pk_free(b200_ctx *ctx, b200_plonk_pk *pk);
 
-/* plonk_bn254.Proof (prove.go:96-114) with points affine (8 u64) and scalars Montgomery (4 u64). */
+/* plonk_bn254.Proof (prove.go:96-114) with points affine (2 * B200_FP_WORDS u64: 8 on BN254, 12 on BLS12-377) and
+ * scalars Montgomery (4 u64). */
 typedef struct b200_plonk_proof {
-    uint64_t lro[3][8];
-    uint64_t z[8];
-    uint64_t h[3][8];
-    uint64_t batched_h[8];          /* BatchedProof.H                                                       */
+    uint64_t lro[3][2 * B200_FP_WORDS];
+    uint64_t z[2 * B200_FP_WORDS];
+    uint64_t h[3][2 * B200_FP_WORDS];
+    uint64_t batched_h[2 * B200_FP_WORDS];      /* BatchedProof.H                                           */
     uint64_t claimed[7][4];         /* BatchedProof.ClaimedValues: folded H, linearised, l, r, o, s1, s2     */
-    uint64_t zshift_h[8];           /* ZShiftedOpening.H                                                    */
+    uint64_t zshift_h[2 * B200_FP_WORDS];       /* ZShiftedOpening.H                                        */
     uint64_t zshift_value[4];       /* ZShiftedOpening.ClaimedValue                                         */
     uint64_t challenges[5][4];      /* gamma, beta, alpha, zeta, KZG folding gamma (for tests; not serialised) */
     uint64_t nb_bsb22;              /* len(Bsb22Commitments)                                                */
     uint64_t claimed_qcp[B200_PLONK_MAX_BSB22][4];   /* BatchedProof.ClaimedValues[7:]: Qcp_i(zeta)          */
-    uint64_t bsb22[B200_PLONK_MAX_BSB22][8];         /* Bsb22Commitments                                     */
+    uint64_t bsb22[B200_PLONK_MAX_BSB22][2 * B200_FP_WORDS];         /* Bsb22Commitments                     */
 } b200_plonk_proof;
 
 /* What the solver's bsb22Hint (prove.go:303-352) produced for an api.Commit circuit: for each commitment the
@@ -659,8 +661,8 @@ int b200_plonk_prove_bsb22(b200_ctx *ctx, const b200_plonk_pk *pk, const uint64_
 
 /* ---- the same proof as a session of phases: multi-GPU (PlonK P1 range-sharded MSMs, P4 coset-
  * parallel quotient).  One process per GPU, each with its shard of the key; every rank runs the same phases on the
- * same inputs and blinding; a phase returns this rank's PARTIAL commitments (G1Jac, 12 u64 each) and the next phase
- * takes the TOTALS (the caller adds the ranks' partials: b200_g1_jac_add after an all-gather of 96-byte points --
+ * same inputs and blinding; a phase returns this rank's PARTIAL commitments (G1Jac, 3 * B200_FP_WORDS u64 each) and the next phase
+ * takes the TOTALS (the caller adds the ranks' partials: b200_g1_jac_add after an all-gather of the 96-byte (144 on BLS12-377) points --
  * no data-path collective for the MSMs).  After phase 2 the caller all-gathers the numerator's coset blocks in
  * place (b200_plonk_session_numerator: coset k lives in block bitrev(k) of 2^log_blocks blocks of block_elems Fr).
  *   begin   -> 3 partials [L] [R] [O]
@@ -693,7 +695,7 @@ int b200_plonk_derive_challenges(const uint64_t *vk_commitments, const uint64_t 
                                  size_t nb_public, const b200_plonk_proof *proof, uint64_t *out);
 
 /* Proof.WriteTo (plonk/bn254/marshal.go:41-66): 8 compressed G1 | u32 7+k | (7+k) Fr | G1 | Fr | u32 k | k G1
- * = 552 + 64 k bytes for k BSB22 commitments.  Returns the number of bytes written or a negative status. */
+ * = 552 + 64 k bytes for k BSB22 commitments on BN254 (9 x 48 + 8 + 32 (8 + k) + 48 k on BLS12-377).  Returns the number of bytes written or a negative status. */
 int b200_plonk_proof_bytes(const b200_plonk_proof *proof, uint8_t *out, size_t out_cap);
 
 #if defined(__GNUC__)

@@ -297,9 +297,10 @@ def srs_scalars(pk: ProvingKey):
 # ---------------------------------------------------------------------------------------------
 def g1_raw(p) -> bytes:
     """G1Affine.RawBytes / Marshal: X || Y big-endian, infinity = 0x40 then zeros."""
+    fb = (B.P.bit_length() + 7) // 8       # 32 on BN254, 48 on BLS12-377 (oracle/suite377.py runs this file on that curve)
     if p is None:
-        return bytes([0x40]) + bytes(63)
-    return p[0].to_bytes(32, "big") + p[1].to_bytes(32, "big")
+        return bytes([0x40]) + bytes(2 * fb - 1)
+    return p[0].to_bytes(fb, "big") + p[1].to_bytes(fb, "big")
 
 
 def fr_bytes(x: int) -> bytes:

@@ -42,3 +42,8 @@ if _PKG not in sys.modules:
 ntt = _instantiate("ntt")
 sys.modules[_PKG].ntt = ntt
 groth16 = _instantiate("groth16")
+sys.modules[_PKG].groth16 = groth16
+# PlonK (backend/plonk/bls12-377/prove.go is the bn254 template with the curve swapped): the same two oracle files
+plonk = _instantiate("plonk")
+sys.modules[_PKG].plonk = plonk
+plonk_prove = _instantiate("plonk_prove")

@@ -196,3 +196,62 @@ def test_sharded_partial_sums_combine(ctx377, pkg, shards):
         for p in parts[1:]:
             acc = add(acc, p[k], curve=c)
         assert np.array_equal(aff(acc, curve=c), aff(full[k], curve=c)), k
+
+
+# ---- PlonK on BLS12-377 (backend/plonk/bls12-377/prove.go: the bn254 template with the curve swapped) -------------
+def _plonk377_upload(ctx377, PP, pk):
+    mono, lag = PP.srs_scalars(pk)
+    gen = U.g1_arr([B.G1_GEN])[0]
+    kzg = ctx377.batch_scalar_mul(gen, U.fr_arr(mono), 1)          # [tau^i]G1 and [L_i(tau)]G1 from the fixed-base kernel
+    kzg_lag = ctx377.batch_scalar_mul(gen, U.fr_arr(lag), 1)
+    vk = pk.vk
+    vkp = [vk["S"][0], vk["S"][1], vk["S"][2], vk["Ql"], vk["Qr"], vk["Qm"], vk["Qo"], vk["Qk"]]
+    f = U.fr_arr
+    return ctx377.plonk_pk_upload(
+        log_n=pk.d0.log_n, log_big=pk.d1.log_n, generator=U.fr(pk.d0.generator), generator_big=U.fr(pk.d1.generator),
+        coset_gen=U.fr(pk.d0.coset_gen), ql=f(pk.ql), qr=f(pk.qr), qm=f(pk.qm), qo=f(pk.qo), qk=f(pk.qk),
+        s1=f(pk.s1), s2=f(pk.s2), s3=f(pk.s3), perm=np.array(pk.perm, dtype=np.int64), kzg_g1=kzg, kzg_lagrange_g1=kzg_lag,
+        vk_commitments=U.g1_arr(vkp), nb_public=pk.nb_public, qcp=[f(q) for q in pk.qcp],
+        vk_qcp=U.g1_arr(pk.vk["Qcp"]) if pk.qcp else None, commitment_index=[c["index"] for c in pk.commitments])
+
+
+def _plonk377_struct_to_proof(PP, s):
+    d = s.as_dict()
+    nb = int(s.nb_bsb22)
+    return PP.Proof([U.g1_aff(d["lro"][k]) for k in range(3)], U.g1_aff(d["z"]), [U.g1_aff(d["h"][k]) for k in range(3)],
+                    U.g1_aff(d["batched_h"]), U.fr_ints(s.all_claimed()), U.g1_aff(d["zshift_h"]),
+                    U.fr_ints(d["zshift_value"].reshape(1, 4))[0], [U.g1_aff(d["bsb22"][k]) for k in range(nb)])
+
+
+@pytest.mark.parametrize("nb_mul,nb_commit", [(6, 0), (300, 0), (4000, 0), (40, 2)])
+def test_plonk_proof_bytes_identical_to_oracle(pkg, ctx377, nb_mul, nb_commit):
+    """plonk.Prove of the second library against oracle/plonk_prove.py run on BLS12-377 (oracle/suite377.py): proof bytes
+    identical under fixed blinding (696 bytes + 80 per BSB22 commitment), fresh-randomness proofs accepted by the verifier
+    restatement, with and without api.Commit columns."""
+    from oracle.suite377 import plonk_prove as PP
+    rng = random.Random(377 + nb_mul)
+    if nb_commit:
+        spr = PP.commit_chain_scs(nb_mul, nb_commit)
+        pk = PP.setup(spr, rng.randrange(1, B.R))
+        sol, bsb = PP.commit_chain_solution(spr, pk, rng.randrange(2, B.R), [(rng.randrange(B.R), rng.randrange(B.R)) for _ in range(nb_commit)])
+        bsb_arr = {"pi2": [U.fr_arr(c) for c in bsb["pi2"]], "commitments": U.g1_arr(bsb["commitments"]), "values": U.fr_arr(bsb["values"])}
+    else:
+        spr = PP.mul_chain_scs(nb_mul)
+        pk = PP.setup(spr, rng.randrange(1, B.R))
+        sol, bsb, bsb_arr = PP.mul_chain_solution(nb_mul, 5), None, None
+    blinding = tuple([rng.randrange(B.R) for _ in range(k)] for k in (2, 2, 2, 3))
+    want, ch = PP.prove(spr, pk, sol, blinding, bsb) if bsb else PP.prove(spr, pk, sol, blinding)
+    L, Rr, O = (U.fr_arr(v) for v in PP.evaluate_lro(spr, sol))
+    pub = U.fr_arr(sol[:1])
+    bl = U.fr_arr([x for part in blinding for x in part])
+    dpk = _plonk377_upload(ctx377, PP, pk)
+    try:
+        got, tm = ctx377.plonk_prove(dpk, L, Rr, O, pub, bl, bsb_arr)
+        fresh, _ = ctx377.plonk_prove(dpk, L, Rr, O, pub, None, bsb_arr)
+    finally:
+        dpk.free()
+    assert U.fr_ints(got.as_dict()["challenges"]) == [ch["gamma"], ch["beta"], ch["alpha"], ch["zeta"], ch["gamma_kzg"]]
+    raw = pkg.plonk_proof_bytes(got)
+    assert raw == PP.proof_bytes(want) and len(raw) == 696 + 80 * nb_commit
+    assert PP.verify(_plonk377_struct_to_proof(PP, fresh), pk.vk, sol[:1], pk.tau)
+    assert pkg.plonk_proof_bytes(fresh) != raw

@@ -208,3 +208,20 @@ def test_groth16_commitment_circuit_trapdoor_identity(two):
     com = G.commitment_dlogs(pk, vk, w)
     assert G.trapdoor_check(vk, w[:2], dl["ar"], dl["bs"], dl["krs"], [w[i] for i in vk["commit_wires"]], com)
     assert not G.trapdoor_check(vk, w[:2], dl["ar"], dl["bs"], dl["krs"])       # without the commitments it must fail
+
+
+def test_plonk_oracle_on_bls12_377_proves_and_verifies():
+    """oracle/plonk_prove.py executed on BLS12-377 (oracle/suite377.py): a proof of the SCS Mul chain is accepted by the
+    verifier restatement, a wrong public input is not, and Proof.WriteTo has the 48-byte-coordinate size."""
+    import random
+
+    from oracle.suite377 import curve as B3
+    from oracle.suite377 import plonk_prove as PP3
+    rng = random.Random(1)
+    spr = PP3.mul_chain_scs(6)
+    pk = PP3.setup(spr, rng.randrange(1, B3.R))
+    sol = PP3.mul_chain_solution(6, 5)
+    proof, _ = PP3.prove(spr, pk, sol, ([1, 2], [3, 4], [5, 6], [7, 8, 9]))
+    assert PP3.verify(proof, pk.vk, sol[:1], pk.tau)
+    assert not PP3.verify(proof, pk.vk, [(sol[0] + 1) % B3.R], pk.tau)
+    assert len(PP3.proof_bytes(proof)) == 9 * 48 + 8 + 32 * 8

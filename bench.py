@@ -422,7 +422,7 @@ def gpu_arm(args):
     per rank inside the library, sharded MSMs combined in C, computeH's exchanges fused into the kernels over NVLink peer
     memory).  Under torchrun (how the driver launches N > 1) rank 0 is that process; the other ranks join the NCCL
     communicator, then wait on a CPU (gloo) barrier so that no spinning collective kernel sits on the GPUs rank 0 is
-    timing, and take part again in the sharded PlonK proof (--plonk-dist, torch.distributed path)."""
+    timing.  The PlonK (config 4) and BLS12-377 (config 5) sections run on the same N GPUs through their own groups."""
     rank = int(os.environ.get("RANK", "0"))
     launched = int(os.environ.get("WORLD_SIZE", "1"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
@@ -448,15 +448,8 @@ def gpu_arm(args):
             os.dup2(saved, 1)
             os.close(saved)
     pkg = load_pkg()
-    plonk_all_ranks = bool(args.plonk_log_n and launched > 1 and args.plonk_dist and (world & (world - 1)) == 0)
     if launched > 1 and rank != 0:
-        dist.barrier(group=gloo)          # rank 0 has finished the Groth16 part (and freed its group)
-        if plonk_all_ranks:
-            ctx = pkg.Context(local)
-            plonk_section(pkg, ctx, args.plonk_log_n, args.steps, args.warmup, dist, rank, world, f"cuda:{local}",
-                          lambda: (ctx.sync(), dist.barrier()), lambda x: _max_over_ranks(dist, local, x))
-            ctx.close()
-        dist.barrier(group=gloo)
+        dist.barrier(group=gloo)          # rank 0 has finished: every section runs from its one process
         dist.destroy_process_group()
         return 0
 
@@ -579,21 +572,15 @@ def gpu_arm(args):
             args.bls_result = bls12_377_section(pkg, local, args.bls12_377_log_n, args.steps, args.warmup, peak, devs)
         except Exception as e:          # the headline line must still be printed
             args.bls_result = {"error": repr(e)}
-    if launched > 1:
-        dist.barrier(group=gloo)
     args.cpu_result = None
     if world == 1 and not args.no_cpu:  # the one leg that runs the oracle: the CPU baseline (and the device against it)
         args.cpu_result = cpu_baseline_leg(ctx, pkg, inst.log_n, min(args.cpu_sample_log, inst.log_n))
-    if args.plonk_log_n and (world == 1 or plonk_all_ranks):
+    if args.plonk_log_n and (world == 1 or args.plonk_dist):     # config 4 on the same number of GPUs
         try:
-            args.plonk_result = plonk_section(pkg, ctx, args.plonk_log_n, args.steps, args.warmup, dist if launched > 1 else None, rank,
-                                              world if launched > 1 else 1, f"cuda:{local}",
-                                              (lambda: (ctx.sync(), dist.barrier())) if launched > 1 else None,
-                                              (lambda x: _max_over_ranks(dist, local, x)) if launched > 1 else None)
+            devs = ([int(x) for x in args.devices.split(",")] if args.devices else list(range(world))) if world > 1 else None
+            args.plonk_result = plonk_section(pkg, ctx, args.plonk_log_n, args.steps, args.warmup, devs)
         except Exception as e:          # the headline line must still be printed
             args.plonk_result = {"error": repr(e)}
-            if launched > 1:
-                raise
     if launched > 1:
         dist.barrier(group=gloo)
         dist.destroy_process_group()
@@ -659,63 +646,60 @@ def bls12_377_section(pkg, device_index, log_n, steps, warmup, peak, devices=Non
         (grp or ctx).close()
 
 
-def plonk_section(pkg, ctx, log_n, steps, warmup, dist=None, rank=0, world=1, device=None, barrier=None, max_over_ranks=None):
+def plonk_section(pkg, ctx, log_n, steps, warmup, devices=None):
     """BASELINE.json config 4: BN254 PlonK Prove at 2^log_n gates (SCS Mul chain, backend/plonk/plonk_test.go:248-260
     shape) with page-locked host L, R, O; every timed proof is checked with the trapdoor form of plonk.Verify
     (verify.go:45-294; plonk_host.verify_with_trapdoor).  Wall time per proof, host buffers in, proof out.
-    N = 1: b200_plonk_prove.  N > 1: the phase ABI with the key sharded over the ranks (commitments by SRS point
-    range, quotient by coset; sharding.plonk_prove_distributed), max over ranks."""
+    N = 1: b200_plonk_prove.  N > 1: b200_group_plonk_prove from this one process -- the key sharded over the group
+    (commitments by SRS point range, quotient by coset), the exchanges inside the library."""
     import importlib
     H = importlib.import_module("gnark_fork_b200.plonk_host")
     n = 1 << log_n
+    world = len(devices) if devices else 1
     tau = 0x1234567890ABCDEF1234567890ABCDEF % H.R_MOD
     t0 = time.perf_counter()
     trace, lro, nb_vars, nb_pub, L, Rr, O, pub = H.mul_chain(log_n, 3)
     d = H.Domains(n)
     kw = H.setup(ctx, d, trace, lro, nb_vars, nb_pub, tau)
-    dpk = ctx.plonk_pk_upload(**kw, shard_index=rank, shard_count=world)
+    grp = pkg.Group(devices) if world > 1 else None
+    prover = grp or ctx
+    dpk = prover.plonk_pk_upload(**kw)
     t_setup = time.perf_counter() - t0
     bufs = []
     for a in (L, Rr, O):
         b = pkg.pinned_empty(a.shape)
         b[:] = a
         bufs.append(b)
-    rng = np.random.default_rng(777)            # the same blinding on every rank (a sharded proof needs it)
+    c0 = grp.ctx(0) if grp else ctx
 
     def one():
-        if world == 1:
-            return ctx.plonk_prove(dpk, *bufs, pub, None)
-        return pkg.sharding.plonk_prove_distributed(dist, ctx, dpk, *bufs, pub, rand_field(rng, 9), None, device)
+        return prover.plonk_prove(dpk, *bufs, pub, None)
 
-    ctx.profile_start()
+    c0.profile_start()
     for _ in range(max(1, warmup)):
         one()
-    launches = ctx.profile_read()["kernel_launches"] // max(1, warmup)
+    launches = c0.profile_read()["kernel_launches"] // max(1, warmup)
     wall, stages = [], []
     for _ in range(steps):
-        if barrier:
-            barrier()
         t1 = time.perf_counter()
         proof, tm = one()
-        if barrier:
-            barrier()
         wall.append((time.perf_counter() - t1) * 1e3)
         stages.append(tm)
     ms = float(np.mean(wall))
-    if max_over_ranks:
-        ms = max_over_ranks(ms)
-    ok = H.verify_with_trapdoor(proof, kw["vk_commitments"], H.from_mont_array(pub), d, tau) if rank == 0 else True
+    ok = H.verify_with_trapdoor(proof, kw["vk_commitments"], H.from_mont_array(pub), d, tau)
     dpk.free()
+    if grp:
+        grp.close()
     mean_stage = {k: float(np.mean([s[k] for s in stages])) for k in stages[0]}
     msm_ms = sum(mean_stage[k] for k in ("commit_lro_ms", "commit_z_ms", "commit_h_ms", "batch_open_ms")) + mean_stage["linearize_ms"]
     return {"metric": "BN254 PlonK prove ms @2^%d gates" % log_n, "value": ms, "unit": "ms", "n_gpus": world, "steps": steps,
             "workload": "SCS Mul chain filling 2^%d rows, big domain 2^%d; 9 KZG commitments as G1 MSMs of ~2^%d against 2 resident SRS (+ the linearised digest as a 7-point host combination), "
                         "%d transforms of 2^%d + 1 of 2^%d, fresh blinding per proof" % (log_n, d.log_big, log_n, 5 + 5 * (d.big // n), log_n, d.log_big),
             "path": "b200_plonk_prove (page-locked host L, R, O in; proof out; Fiat-Shamir on the host)" if world == 1 else
-                    "b200_plonk_session_* phases on %d ranks: commitments sharded by SRS point range (96-byte partial sums all-gathered, host add), "
-                    "quotient sharded by coset (numerator blocks all-gathered over NCCL)" % world,
-            "h2d_bytes_per_step": int(3 * n * 32 + 32), "d2h_bytes_per_step": 552,
-            "stage_ms": mean_stage, "stage_ms_note": "rank 0, library time only (exchanges between phases are in value, not in stage_ms)",
+                    "b200_group_plonk_prove, one process, %d ranks: commitments sharded by SRS point range (partial sums added on the host inside the call), "
+                    "quotient sharded by coset (numerator blocks by peer copies)" % world,
+            "h2d_bytes_per_step": int(3 * n * 32 + 32) * world, "d2h_bytes_per_step": 552,
+            "stage_ms": mean_stage, "stage_ms_note": "rank 0, library time only",
             "commit_ms_share": msm_ms / mean_stage["total_ms"],
             "gpu_launches_per_proof": int(launches), "verified": bool(ok), "verifier": "plonk.Verify with the KZG pairing checks done in G1 through the known tau of the test SRS",
             "setup_s": t_setup}

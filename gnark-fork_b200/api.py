@@ -256,6 +256,9 @@ def load_library(curve: int = BN254):
         "b200_group_groth16_setup": (i, [vp, i, C.POINTER(_SETUP[curve][0]), C.POINTER(vp), C.POINTER(_SETUP[curve][1])]),
         "b200_group_groth16_pk_free": (i, [vp, vp]),
         "b200_group_groth16_pk_info": (i, [vp, vp, i, C.POINTER(_MsmSetInfo), C.POINTER(i)]),
+        "b200_group_plonk_pk_upload": (i, [vp, i, C.POINTER(_PlonkPkDesc), C.POINTER(vp)]),
+        "b200_group_plonk_pk_free": (i, [vp, vp]),
+        "b200_group_plonk_prove": (i, [vp, vp, vp, vp, vp, vp, vp, C.POINTER(_PlonkBsb22), C.POINTER(PlonkProof), C.POINTER(_PlonkTimings)]),
         "b200_group_groth16_prove_core": (i, [vp, vp, vp, vp, vp, sz, vp, vp, sz, C.POINTER(Groth16MsmOut), C.POINTER(_Timings)]),
         "b200_group_groth16_prove_core_dev": (i, [vp, vp, C.POINTER(vp), C.POINTER(vp), C.POINTER(vp), C.POINTER(vp),
                                                   C.POINTER(Groth16MsmOut), C.POINTER(_Timings)]),
@@ -878,7 +881,7 @@ class Context:
     # -- PlonK prover
     def plonk_pk_upload(self, *, log_n, log_big, generator, generator_big, coset_gen, ql, qr, qm, qo, qk, s1, s2, s3, perm,
                         kzg_g1, kzg_lagrange_g1, vk_commitments, nb_public, qcp=(), vk_qcp=None, commitment_index=(),
-                        shard_index=0, shard_count=1) -> PlonkProvingKey:
+                        shard_index=0, shard_count=1, _invoke=None) -> PlonkProvingKey:
         """qcp: list of pk.trace.Qcp columns (canonical), vk_qcp: their commitments, commitment_index: CommitmentInfo[i].CommitmentIndex."""
         n = 1 << log_n
         keep = {k: _u64(v, (n, 4)) for k, v in dict(ql=ql, qr=qr, qm=qm, qo=qo, qk=qk, s1=s1, s2=s2, s3=s3).items()}
@@ -899,6 +902,10 @@ class Context:
             ci = np.ascontiguousarray(commitment_index, dtype=np.uint64)
             d.qcp, d.vk_qcp, d.commitment_index = C.addressof(ptrs), vq.ctypes.data, ci.ctypes.data
         h = C.c_void_p()
+        if _invoke is not None:
+            key = _invoke(d, h, nb_public, len(qcp))
+            key.n = n
+            return key
         self._check(self.lib.b200_plonk_pk_upload(self.h, self.curve, C.byref(d), C.byref(h)))
         key = PlonkProvingKey(self, h, nb_public, len(qcp), shard_index, shard_count)
         key.n = n          # the C ABI takes no lengths: the binding checks them (out-of-bounds host reads otherwise)
@@ -1059,3 +1066,39 @@ class Group:
         self._check(self.lib.b200_group_groth16_prove_core_dev(self.h, pk.h, *[C.cast(x, C.POINTER(C.c_void_p)) for x in arrs],
                                                                C.byref(out), C.byref(tm)))
         return out, {k: getattr(tm, k) for k, _ in _Timings._fields_}
+
+
+class GroupPlonkProvingKey:
+    def __init__(self, group, handle, nb_public, nb_bsb22):
+        self.group, self.h, self.nb_public, self.nb_bsb22 = group, handle, nb_public, nb_bsb22
+
+    def free(self):
+        if self.h:
+            self.group.lib.b200_group_plonk_pk_free(self.group.h, self.h)
+            self.h = None
+
+
+def _group_plonk_pk_upload(self, **kw) -> GroupPlonkProvingKey:
+    """b200_group_plonk_pk_upload: every rank keeps its shard of the key (SRS point ranges, its cosets)."""
+    def invoke(d, h, nb_public, nb_bsb):
+        self._check(self.lib.b200_group_plonk_pk_upload(self.h, self.curve, C.byref(d), C.byref(h)))
+        return GroupPlonkProvingKey(self, h, nb_public, nb_bsb)
+    return Context.plonk_pk_upload(self.ctx(0), _invoke=invoke, **kw)
+
+
+def _group_plonk_prove(self, pk: GroupPlonkProvingKey, l, r, o, public_witness, blinding=None, bsb=None):
+    """b200_group_plonk_prove: one proof over the whole group; (PlonkProof, rank 0's timings)."""
+    c0 = self.ctx(0)
+    l, r, o = _u64(l, (-1, 4)), _u64(r, (-1, 4)), _u64(o, (-1, 4))
+    pw = _u64(public_witness, (-1, 4))
+    Context._plonk_check_lengths(pk, l, r, o, pw)
+    bl = None if blinding is None else _u64(blinding, (9, 4))
+    proof, tm = _PLONK_PROOF[self.curve](), _PlonkTimings()
+    cb, keep = c0._plonk_bsb(pk, bsb)
+    self._check(self.lib.b200_group_plonk_prove(self.h, pk.h, _ptr(l), _ptr(r), _ptr(o), _ptr(pw) if pw.shape[0] else None,
+                                                _ptr(bl), None if cb is None else C.byref(cb), C.byref(proof), C.byref(tm)))
+    return proof, {k: getattr(tm, k) for k, _ in tm._fields_}
+
+
+Group.plonk_pk_upload = _group_plonk_pk_upload
+Group.plonk_prove = _group_plonk_prove

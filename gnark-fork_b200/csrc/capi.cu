@@ -61,9 +61,12 @@ int b200_init(int device, b200_ctx** out) try {
     cudaDeviceProp prop;
     if (cudaGetDeviceProperties(&prop, device) != cudaSuccess) { delete ctx; return B200_ERR_CUDA; }
     ctx->sm_count = prop.multiProcessorCount;
+    int prio_lo = 0, prio_hi = 0;      // the reduction tail of an MSM is a few small kernels: its blocks go first when SMs free up
+    cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi);
     if (cudaStreamCreateWithFlags(&ctx->own_stream, cudaStreamNonBlocking) != cudaSuccess ||
         cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking) != cudaSuccess ||
         cudaStreamCreateWithFlags(&ctx->aux_stream, cudaStreamNonBlocking) != cudaSuccess ||
+        cudaStreamCreateWithPriority(&ctx->post_stream, cudaStreamNonBlocking, prio_hi) != cudaSuccess ||
         cudaEventCreate(&ctx->ev0) != cudaSuccess || cudaEventCreate(&ctx->ev1) != cudaSuccess) {
         delete ctx;
         return B200_ERR_CUDA;
@@ -89,6 +92,7 @@ void b200_destroy(b200_ctx* ctx) try {
     cudaStreamDestroy(ctx->own_stream);
     if (ctx->copy_stream) cudaStreamDestroy(ctx->copy_stream);
     if (ctx->aux_stream) cudaStreamDestroy(ctx->aux_stream);
+    if (ctx->post_stream) cudaStreamDestroy(ctx->post_stream);
     if (ctx->h_stage) cudaFreeHost(ctx->h_stage);
     for (cudaEvent_t e : ctx->core_events) cudaEventDestroy(e);
     delete ctx;
@@ -616,6 +620,7 @@ int b200_set_option(b200_ctx* ctx, const char* key, long value) try {
     else if (k == "msm_precompute") { ctx->msm_precompute = value ? 1 : 0; }
     else if (k == "msm_fold_c") { if (value != 0 && (value < 8 || value > 24)) return ctx->fail(B200_ERR_ARG, "msm_fold_c out of range"); ctx->msm_fold_c = (int)value; }
     else if (k == "ntt_tma") ctx->ntt_tma = value ? 1 : 0;
+    else if (k == "h_sort_overlap") ctx->h_sort_overlap = value ? 1 : 0;
     else if (k == "ntt_threads") { if (value < 32 || value > 1024 || (value & (value - 1))) return ctx->fail(B200_ERR_ARG, "ntt_threads must be a power of two in 32..1024"); ctx->ntt_threads = (int)value; }
     else return ctx->fail(B200_ERR_ARG, "unknown option", key);
     return B200_OK;

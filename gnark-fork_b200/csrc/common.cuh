@@ -22,8 +22,10 @@ struct b200_ctx {
     cudaStream_t own_stream = nullptr;
     cudaStream_t copy_stream = nullptr;     // per-proof input copies, overlapped with the witness MSMs
     cudaStream_t aux_stream = nullptr;      // sort of the next MSM, overlapped with the current accumulation
+    cudaStream_t post_stream = nullptr;     // bucket reduction of the previous MSM, overlapped with the current accumulation
     void* h_stage = nullptr;                // page-locked staging of MSM result points
     size_t h_stage_bytes = 0;
+    int h_sort_overlap = 0;                 // 1: with device-resident inputs the first MSM's sort runs under computeH instead of after it
     int msm_overlap = 1;                    // 0: the prove core runs its MSMs strictly one after the other
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     std::string err;

@@ -250,6 +250,7 @@ int groth16_prove_core(b200_ctx* ctx, const b200_groth16_pk* pk, const uint64_t*
     const size_t o_sort0 = ar.off; ar.take(sort_max);
     const size_t o_sort1 = overlap ? ar.off : o_sort0; if (overlap) ar.take(sort_max);
     const size_t o_acc = ar.off; ar.take(acc_max);
+    const size_t o_acc1 = overlap ? ar.off : o_acc; if (overlap) ar.take(acc_max);   // second accumulation group: the reduction of MSM k runs beside the accumulation of k+1
     B2_TRY(ctx_reserve(ctx, ar.off));
     if (ctx->h_stage_bytes < res_off[5]) {   // page-locked staging of the few result points per MSM
         if (ctx->h_stage) cudaFreeHost(ctx->h_stage);
@@ -262,12 +263,13 @@ int groth16_prove_core(b200_ctx* ctx, const b200_groth16_pk* pk, const uint64_t*
     Fr* d_w = (Fr*)(base + o_w);
     uint32_t* d_kmap = n_remove ? (uint32_t*)(base + o_kmap) : nullptr;
     char* sort_ws[2] = {base + o_sort0, base + o_sort1};
-    char* acc_ws = base + o_acc;
+    char* acc_ws[2] = {base + o_acc, base + o_acc1};
     cudaStream_t st = ctx->stream;
     cudaStream_t sx = overlap ? ctx->aux_stream : st;
     cudaStream_t cp = ctx->copy_stream;
+    cudaStream_t sp = overlap ? ctx->post_stream : nullptr;
 
-    constexpr int NEV = 24;     // created once per ctx, reused by every proof (freed by b200_destroy)
+    constexpr int NEV = 34;     // created once per ctx, reused by every proof (freed by b200_destroy)
     while (ctx->core_events.size() < NEV) {
         cudaEvent_t e;
         B2_CUDA(ctx, cudaEventCreate(&e));
@@ -276,7 +278,9 @@ int groth16_prove_core(b200_ctx* ctx, const b200_groth16_pk* pk, const uint64_t*
     cudaEvent_t* ev = ctx->core_events.data();
     cudaEvent_t ev_w = ev[9], ev_abc = ev[10], ev_h = ev[11];
     cudaEvent_t* ev_sort = ev + 12;   // [5]
-    cudaEvent_t* ev_acc = ev + 17;    // [5]
+    cudaEvent_t* ev_acc = ev + 17;    // [5]  accumulation + split-bucket merges done: the sort group is free
+    cudaEvent_t* ev_split = ev + 22;  // [5]
+    cudaEvent_t* ev_post = ev + 27;   // [5]  reduction + result copy done: the accumulation group is free
 
     // Copies run on their own stream: W first (the four witness MSMs need only W), then a, b, c,
     // which computeH picks up later -- the PCIe traffic hides behind the first MSM.
@@ -331,8 +335,9 @@ int groth16_prove_core(b200_ctx* ctx, const b200_groth16_pk* pk, const uint64_t*
     for (int k = 0; k < 5; ++k) {
         void* stage = (char*)ctx->h_stage + res_off[k];
         char* sw = sort_ws[overlap ? sort_slot[k] : 0];
-        jobs[k] = groups[k] == 2 ? msm_g2_job_new(ctx, (const G2Affine*)bases[k], scal[k], maps[k], counts[k], folds[k], sw, acc_ws, stage)
-                                 : msm_g1_job_new(ctx, (const G1Affine*)bases[k], scal[k], maps[k], counts[k], folds[k], sw, acc_ws, stage);
+        char* aw = acc_ws[overlap ? (k & 1) : 0];
+        jobs[k] = groups[k] == 2 ? msm_g2_job_new(ctx, (const G2Affine*)bases[k], scal[k], maps[k], counts[k], folds[k], sw, aw, stage)
+                                 : msm_g1_job_new(ctx, (const G1Affine*)bases[k], scal[k], maps[k], counts[k], folds[k], sw, aw, stage);
     }
     auto run_h = [&]() -> int {
         B2_CUDA(ctx, cudaStreamWaitEvent(st, ev_abc, 0));
@@ -348,7 +353,7 @@ int groth16_prove_core(b200_ctx* ctx, const b200_groth16_pk* pk, const uint64_t*
     auto run_sort = [&](int k) -> int {
         if (k < 4) B2_CUDA(ctx, cudaStreamWaitEvent(sx, ev_w, 0));
         else if (own_h || hook) B2_CUDA(ctx, cudaStreamWaitEvent(sx, ev_h, 0));
-        if (k == 0 && h_first) B2_CUDA(ctx, cudaStreamWaitEvent(sx, ev_h, 0));  // the transforms and a sort only slow each other down
+        if (k == 0 && h_first && !ctx->h_sort_overlap) B2_CUDA(ctx, cudaStreamWaitEvent(sx, ev_h, 0));  // the transforms and a sort only slow each other down
         if (k == 2) B2_CUDA(ctx, cudaStreamWaitEvent(sx, ev_acc[0], 0));
         if (k == 3) B2_CUDA(ctx, cudaStreamWaitEvent(sx, ev_acc[1], 0));
         if (k == 4) B2_CUDA(ctx, cudaStreamWaitEvent(sx, ev_acc[2], 0));
@@ -359,8 +364,10 @@ int groth16_prove_core(b200_ctx* ctx, const b200_groth16_pk* pk, const uint64_t*
     };
     auto run_acc = [&](int k) -> int {
         B2_CUDA(ctx, cudaStreamWaitEvent(st, ev_sort[k], 0));
-        B2_TRY(groups[k] == 2 ? msm_g2_job_acc(ctx, jobs[k], st) : msm_g1_job_acc(ctx, jobs[k], st));
+        if (sp && k >= 2) B2_CUDA(ctx, cudaStreamWaitEvent(st, ev_post[k - 2], 0));   // the accumulation group of MSM k-2
+        B2_TRY(groups[k] == 2 ? msm_g2_job_acc(ctx, jobs[k], st, sp, ev_split[k]) : msm_g1_job_acc(ctx, jobs[k], st, sp, ev_split[k]));
         B2_CUDA(ctx, cudaEventRecord(ev_acc[k], st));
+        if (sp) B2_CUDA(ctx, cudaEventRecord(ev_post[k], sp));
         return B200_OK;
     };
     B2_CUDA(ctx, cudaEventRecord(ev[6], st));   // placeholders when computeH is skipped (h supplied)
@@ -385,8 +392,13 @@ int groth16_prove_core(b200_ctx* ctx, const b200_groth16_pk* pk, const uint64_t*
             B2_TRY(run_acc(k));
         }
     }
+    if (sp) {    // the step ends when the last reductions have delivered their results
+        B2_CUDA(ctx, cudaStreamWaitEvent(st, ev_post[3], 0));
+        B2_CUDA(ctx, cudaStreamWaitEvent(st, ev_post[4], 0));
+    }
     B2_CUDA(ctx, cudaEventRecord(ev[8], st));
     B2_CUDA(ctx, cudaStreamSynchronize(st));
+    if (sp) B2_CUDA(ctx, cudaStreamSynchronize(sp));
     B2_CUDA(ctx, cudaStreamSynchronize(cp));
     if (overlap) B2_CUDA(ctx, cudaStreamSynchronize(sx));
 

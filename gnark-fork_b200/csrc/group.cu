@@ -26,6 +26,8 @@
 #include "groth16_host.cuh"
 #include "host_group.cuh"
 
+namespace b200 { int plonk_draw_blinding(uint64_t out[36]); }   // plonk.cu
+
 using namespace b200;
 
 namespace {
@@ -389,6 +391,115 @@ int b200_group_groth16_prove_core_dev(b200_group* g, const b200_group_groth16_pk
                                       b200_groth16_out* out, b200_timings* timings) try {
     if (!g || !gpk || !out || !a_dev || !b_dev || !c_dev || !w_dev) return B200_ERR_ARG;
     return prove(g, gpk, nullptr, nullptr, nullptr, 0, nullptr, a_dev, b_dev, c_dev, w_dev, nullptr, 0, out, timings);
+} B2_ABI_CATCH_INT
+
+
+// ---- PlonK over the group (P1 range-sharded commitments, P4 coset-parallel quotient) ------------------
+// The session phases of plonk.cu, one session per rank, driven from the rank's host thread.  Between phases the partial
+// commitments (one Jacobian point each) are added on the host by every thread from a shared table; after phase 2 every
+// rank pulls the numerator's coset blocks it does not own from the owners' buffers (peer copies on its own stream).
+struct b200_group_plonk_pk {
+    std::vector<b200_plonk_pk*> pk;
+};
+
+int b200_group_plonk_pk_upload(b200_group* g, int curve, const b200_plonk_pk_desc* desc, b200_group_plonk_pk** out) try {
+    if (!g || !desc || !out) return B200_ERR_ARG;
+    *out = nullptr;
+    b200_group_plonk_pk* gpk = new b200_group_plonk_pk();
+    gpk->pk.assign(g->R, nullptr);
+    const int st = run_ranks(g, [&](int r) -> int {
+        b200_plonk_pk_desc d = *desc;
+        d.shard_index = r;
+        d.shard_count = g->R;
+        return b200_plonk_pk_upload(g->ctx[r], curve, &d, &gpk->pk[r]);
+    });
+    if (st != B200_OK) { b200_group_plonk_pk_free(g, gpk); return st; }
+    *out = gpk;
+    return B200_OK;
+} B2_ABI_CATCH_INT
+
+int b200_group_plonk_pk_free(b200_group* g, b200_group_plonk_pk* gpk) try {
+    if (!g) return B200_ERR_ARG;
+    if (!gpk) return B200_OK;
+    for (int r = 0; r < g->R && (size_t)r < gpk->pk.size(); ++r)
+        if (gpk->pk[r]) b200_plonk_pk_free(g->ctx[r], gpk->pk[r]);
+    delete gpk;
+    return B200_OK;
+} B2_ABI_CATCH_INT
+
+int b200_group_plonk_prove(b200_group* g, const b200_group_plonk_pk* gpk, const uint64_t* l, const uint64_t* r_, const uint64_t* o,
+                           const uint64_t* public_witness, const uint64_t* blinding, const b200_plonk_bsb22* bsb,
+                           b200_plonk_proof* out, b200_plonk_timings* timings) try {
+    if (!g || !gpk || !l || !r_ || !o || !out) return B200_ERR_ARG;
+    const int R = g->R;
+    uint64_t drawn[36];
+    if (!blinding) {      // every rank must blind with the same polynomials
+        if (plonk_draw_blinding(drawn) != B200_OK) return g->fail(B200_ERR_ARG, "no entropy source");
+        blinding = drawn;
+    }
+    constexpr int JW = 3 * B200_FP_WORDS;                 // u64 words of a G1Jac
+    std::vector<uint64_t> table((size_t)R * 3 * JW);       // [rank][up to 3 partials]
+    std::vector<void*> num_ptr(R, nullptr);
+    std::vector<b200_plonk_proof> proofs(R);
+    std::vector<b200_plonk_timings> tms(R);
+    size_t block_elems = 0;
+    unsigned log_blocks = 0;
+    auto totals = [&](int count, uint64_t* dst) {          // sum over the ranks, on this thread
+        for (int k = 0; k < count; ++k) {
+            memcpy(dst + JW * k, table.data() + JW * k, JW * 8);
+            for (int q = 1; q < R; ++q) hostgrp::jac_add<Fp>(dst + JW * k, table.data() + ((size_t)q * 3 + k) * JW, dst + JW * k);
+        }
+    };
+    const int st = run_ranks(g, [&](int r) -> int {
+        b200_ctx* ctx = g->ctx[r];
+        b200_plonk_session* S = nullptr;
+        uint64_t part[3 * JW], tot[3 * JW];
+        struct Guard { b200_ctx* c; b200_plonk_session** s; ~Guard() { if (*s) b200_plonk_session_finish(c, *s, nullptr, nullptr, nullptr); } } guard{ctx, &S};
+        auto publish = [&](int count) -> int {             // partials -> table; all ranks; totals
+            memcpy(table.data() + (size_t)r * 3 * JW, part, (size_t)count * JW * 8);
+            if (!g->barrier.wait()) return ctx->fail(B200_ERR_INTERNAL, "another rank failed");
+            totals(count, tot);
+            if (!g->barrier.wait()) return ctx->fail(B200_ERR_INTERNAL, "another rank failed");   // the table may be overwritten again
+            return B200_OK;
+        };
+        B2_TRY(b200_plonk_session_begin(ctx, gpk->pk[r], l, r_, o, public_witness, blinding, bsb, &S, part));
+        B2_TRY(publish(3));
+        B2_TRY(b200_plonk_session_step(ctx, S, 1, tot, part));
+        B2_TRY(publish(1));
+        B2_TRY(b200_plonk_session_step(ctx, S, 2, tot, nullptr));
+        // the numerator: coset k was evaluated by rank k mod R into block bitrev(k) of its buffer
+        size_t be = 0;
+        unsigned lb = 0;
+        B2_TRY(b200_plonk_session_numerator(ctx, S, &num_ptr[r], &be, &lb));
+        B2_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+        if (r == 0) { block_elems = be; log_blocks = lb; }
+        if (!g->barrier.wait()) return ctx->fail(B200_ERR_INTERNAL, "another rank failed");
+        const unsigned rho = 1u << log_blocks;
+        for (unsigned k = 0; k < rho; ++k) {
+            const int owner = (int)(k % (unsigned)R);
+            if (owner == r) continue;
+            unsigned blk = 0;
+            for (unsigned b = 0; b < log_blocks; ++b) blk |= ((k >> b) & 1u) << (log_blocks - 1 - b);
+            const size_t off = (size_t)blk * block_elems * sizeof(Fr);
+            B2_CUDA(ctx, cudaMemcpyPeerAsync((char*)num_ptr[r] + off, ctx->device, (const char*)num_ptr[owner] + off, g->ctx[owner]->device,
+                                             block_elems * sizeof(Fr), ctx->stream));
+        }
+        B2_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+        if (!g->barrier.wait()) return ctx->fail(B200_ERR_INTERNAL, "another rank failed");   // nobody overwrites a block another rank still reads
+        B2_TRY(b200_plonk_session_step(ctx, S, 3, nullptr, part));
+        B2_TRY(publish(3));
+        B2_TRY(b200_plonk_session_step(ctx, S, 4, tot, part));
+        B2_TRY(publish(2));
+        B2_TRY(b200_plonk_session_step(ctx, S, 5, tot, part));
+        B2_TRY(publish(1));
+        b200_plonk_session* fin = S;
+        S = nullptr;                                        // finish frees the session
+        return b200_plonk_session_finish(ctx, fin, tot, &proofs[r], &tms[r]);
+    });
+    if (st != B200_OK) return st;
+    *out = proofs[0];
+    if (timings) *timings = tms[0];
+    return B200_OK;
 } B2_ABI_CATCH_INT
 
 }  // extern "C"

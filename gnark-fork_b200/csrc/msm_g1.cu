@@ -24,7 +24,7 @@ void* msm_g1_job_new(b200_ctx* ctx, const G1Affine* d_bases, const Fr* d_scalars
     return new MsmJob<Fp>(ctx, d_bases, d_scalars, d_idx_map, n, fold, sort_ws, acc_ws, (XYZZ<Fp>*)host_staging);
 }
 int msm_g1_job_sort(b200_ctx* ctx, void* job, cudaStream_t st) { return msm_enqueue_sort(ctx, *(MsmJob<Fp>*)job, st); }
-int msm_g1_job_acc(b200_ctx* ctx, void* job, cudaStream_t st) { return msm_enqueue_acc(ctx, *(MsmJob<Fp>*)job, st); }
+int msm_g1_job_acc(b200_ctx* ctx, void* job, cudaStream_t st, cudaStream_t st_post, cudaEvent_t ev_split) { return msm_enqueue_acc(ctx, *(MsmJob<Fp>*)job, st, st_post, ev_split); }
 void msm_g1_job_finish(void* job, G1Jac* out_host) { msm_finish(*(MsmJob<Fp>*)job, out_host); }
 void msm_g1_job_delete(void* job) { delete (MsmJob<Fp>*)job; }
 }  // namespace b200

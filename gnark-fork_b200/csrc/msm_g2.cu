@@ -13,7 +13,7 @@ void* msm_g2_job_new(b200_ctx* ctx, const G2Affine* d_bases, const Fr* d_scalars
     return new MsmJob<Fp2>(ctx, d_bases, d_scalars, d_idx_map, n, fold, sort_ws, acc_ws, (XYZZ<Fp2>*)host_staging);
 }
 int msm_g2_job_sort(b200_ctx* ctx, void* job, cudaStream_t st) { return msm_enqueue_sort(ctx, *(MsmJob<Fp2>*)job, st); }
-int msm_g2_job_acc(b200_ctx* ctx, void* job, cudaStream_t st) { return msm_enqueue_acc(ctx, *(MsmJob<Fp2>*)job, st); }
+int msm_g2_job_acc(b200_ctx* ctx, void* job, cudaStream_t st, cudaStream_t st_post, cudaEvent_t ev_split) { return msm_enqueue_acc(ctx, *(MsmJob<Fp2>*)job, st, st_post, ev_split); }
 void msm_g2_job_finish(void* job, G2Jac* out_host) { msm_finish(*(MsmJob<Fp2>*)job, out_host); }
 void msm_g2_job_delete(void* job) { delete (MsmJob<Fp2>*)job; }
 }  // namespace b200

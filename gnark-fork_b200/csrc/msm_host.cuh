@@ -29,13 +29,15 @@ MsmSizes msm_sizes(size_t n, int group, int c_override, int fold_c);
 void* msm_g1_job_new(b200_ctx* ctx, const G1Affine* d_bases, const Fr* d_scalars, const uint32_t* d_idx_map, size_t n,
                      const MsmFold* fold, void* sort_ws, void* acc_ws, void* host_staging);
 int msm_g1_job_sort(b200_ctx* ctx, void* job, cudaStream_t st);
-int msm_g1_job_acc(b200_ctx* ctx, void* job, cudaStream_t st);
+// st_post / ev_split (optional): the bucket reduction (leaf sums, trees, result copy) is enqueued on st_post after
+// ev_split, recorded on st behind the accumulation and the split-bucket merges -- it then overlaps whatever st runs next
+int msm_g1_job_acc(b200_ctx* ctx, void* job, cudaStream_t st, cudaStream_t st_post = nullptr, cudaEvent_t ev_split = nullptr);
 void msm_g1_job_finish(void* job, G1Jac* out_host);
 void msm_g1_job_delete(void* job);
 void* msm_g2_job_new(b200_ctx* ctx, const G2Affine* d_bases, const Fr* d_scalars, const uint32_t* d_idx_map, size_t n,
                      const MsmFold* fold, void* sort_ws, void* acc_ws, void* host_staging);
 int msm_g2_job_sort(b200_ctx* ctx, void* job, cudaStream_t st);
-int msm_g2_job_acc(b200_ctx* ctx, void* job, cudaStream_t st);
+int msm_g2_job_acc(b200_ctx* ctx, void* job, cudaStream_t st, cudaStream_t st_post = nullptr, cudaEvent_t ev_split = nullptr);
 void msm_g2_job_finish(void* job, G2Jac* out_host);
 void msm_g2_job_delete(void* job);
 // builds the table for n resident points (device) into `table` ((W x n) affine points); returns
@@ -234,7 +236,7 @@ int msm_enqueue_sort(b200_ctx* ctx, const MsmJob<F>& job, cudaStream_t st) {
 }
 
 template <class F>
-int msm_enqueue_acc(b200_ctx* ctx, const MsmJob<F>& job, cudaStream_t st) {
+int msm_enqueue_acc(b200_ctx* ctx, const MsmJob<F>& job, cudaStream_t st, cudaStream_t st_post = nullptr, cudaEvent_t ev_split = nullptr) {
     if (job.n == 0) return B200_OK;
     const MsmLayout<F>& lay = job.lay;
     const MsmPlan& pl = lay.plan;
@@ -304,7 +306,15 @@ int msm_enqueue_acc(b200_ctx* ctx, const MsmJob<F>& job, cudaStream_t st) {
         msm_combine_big_kernel<F><<<ctx->sm_count * 2, COMBINE_BIG_THREADS, 0, st>>>(big, big + 2 + (M - 1), task_off, ntasks, partials, buckets);
         B2_CUDA(ctx, cudaGetLastError());
     }
-    // reduction: leaf running sums, then binary trees for the Q plain sums of every bucket set
+    // reduction: leaf running sums, then binary trees for the Q plain sums of every bucket set.  It reads the buckets
+    // only (the sort group is free from here): with a post stream it runs beside the next MSM's accumulation.
+    if (st_post && ev_split) {
+        ctx->prof_end(span, st);
+        B2_CUDA(ctx, cudaEventRecord(ev_split, st));
+        B2_CUDA(ctx, cudaStreamWaitEvent(st_post, ev_split, 0));
+        st = st_post;
+        span = ctx->prof_begin(B200_PROF_MSM_REDUCE, 0.0, st);
+    }
     const uint32_t T = lay.T, Q = lay.Q;
     {
         const uint32_t nodes = (uint32_t)pl.WB * T;

@@ -335,6 +335,17 @@ static void plonk_pk_delete(b200_ctx* ctx, b200_plonk_pk* pk) {
     delete pk;
 }
 
+namespace b200 {
+// the nine blinding coefficients of getRandomPolynomial (prove.go:295-301) from the OS entropy source, for the group
+// prover (group.cu): a proof sharded over several ranks needs the same ones on every rank
+int plonk_draw_blinding(uint64_t out[36]) {
+    Fr b[9];
+    const int st = os_random_fr(b, 9);
+    if (st == B200_OK) memcpy(out, b, sizeof b);
+    return st;
+}
+}  // namespace b200
+
 extern "C" {
 
 int b200_plonk_pk_upload(b200_ctx* ctx, int curve, const b200_plonk_pk_desc* d, b200_plonk_pk** out) try {

@@ -94,6 +94,9 @@ extern "C" {
 #define b200_group_groth16_setup b200_bls12377_group_groth16_setup
 #define b200_group_init b200_bls12377_group_init
 #define b200_group_last_error b200_bls12377_group_last_error
+#define b200_group_plonk_pk_free b200_bls12377_group_plonk_pk_free
+#define b200_group_plonk_pk_upload b200_bls12377_group_plonk_pk_upload
+#define b200_group_plonk_prove b200_bls12377_group_plonk_prove
 #define b200_group_set_option b200_bls12377_group_set_option
 #define b200_group_size b200_bls12377_group_size
 #define b200_h2d b200_bls12377_h2d
@@ -687,6 +690,16 @@ int b200_plonk_session_numerator(b200_ctx *ctx, b200_plonk_session *session, voi
 /* totals = proof = NULL abandons a session at any point. */
 int b200_plonk_session_finish(b200_ctx *ctx, b200_plonk_session *session, const uint64_t *totals, b200_plonk_proof *out,
                               b200_plonk_timings *timings);
+
+/* The same proof over a device group (one process, one call): the key is sharded over the ranks as above, every rank
+ * runs the session phases from its own host thread, partial commitments are added on the host inside the call and the
+ * numerator's coset blocks move between the devices by peer copies.  blinding = NULL draws it once for all ranks. */
+typedef struct b200_group_plonk_pk b200_group_plonk_pk;
+int b200_group_plonk_pk_upload(b200_group *group, int curve, const b200_plonk_pk_desc *desc, b200_group_plonk_pk **out);
+int b200_group_plonk_pk_free(b200_group *group, b200_group_plonk_pk *pk);
+int b200_group_plonk_prove(b200_group *group, const b200_group_plonk_pk *pk, const uint64_t *l, const uint64_t *r, const uint64_t *o,
+                           const uint64_t *public_witness, const uint64_t *blinding, const b200_plonk_bsb22 *bsb,
+                           b200_plonk_proof *out, b200_plonk_timings *timings);
 
 /* The four Fiat-Shamir challenges gamma, beta, alpha, zeta (16 u64, Montgomery) of a proof's commitments:
  * bindPublicData + deriveRandomness (plonk/bn254/verify.go:296-360) over SHA-256, gnark-crypto's

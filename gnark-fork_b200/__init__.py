@@ -14,4 +14,5 @@ from .api import (  # noqa: F401
 )
 from . import sharding  # noqa: F401,E402
 from . import groth16_host  # noqa: F401,E402
+from . import pk_format, plonk_pk_format  # noqa: F401,E402
 from . import api  # noqa: F401,E402

@@ -17,6 +17,7 @@ BN254 = 0
 BLS12_377 = 1
 DIF = 0
 DIT = 1
+PLONK_MAX_BSB22 = 8      # B200_PLONK_MAX_BSB22
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 _LIBS: dict = {}
@@ -68,7 +69,7 @@ class _PlonkPkDesc(C.Structure):
                 ("qk", C.c_void_p), ("s1", C.c_void_p), ("s2", C.c_void_p), ("s3", C.c_void_p), ("perm", C.c_void_p),
                 ("kzg_g1", C.c_void_p), ("kzg_lagrange_g1", C.c_void_p), ("vk_commitments", C.c_void_p),
                 ("nb_public", C.c_size_t), ("nb_bsb22", C.c_size_t), ("qcp", C.c_void_p), ("vk_qcp", C.c_void_p),
-                ("commitment_index", C.c_void_p), ("shard_index", C.c_int), ("shard_count", C.c_int)]
+                ("commitment_index", C.c_void_p), ("raw_file", C.c_int), ("shard_index", C.c_int), ("shard_count", C.c_int)]
 
 
 class _PlonkBsb22(C.Structure):
@@ -881,24 +882,36 @@ class Context:
     # -- PlonK prover
     def plonk_pk_upload(self, *, log_n, log_big, generator, generator_big, coset_gen, ql, qr, qm, qo, qk, s1, s2, s3, perm,
                         kzg_g1, kzg_lagrange_g1, vk_commitments, nb_public, qcp=(), vk_qcp=None, commitment_index=(),
-                        shard_index=0, shard_count=1, _invoke=None) -> PlonkProvingKey:
-        """qcp: list of pk.trace.Qcp columns (canonical), vk_qcp: their commitments, commitment_index: CommitmentInfo[i].CommitmentIndex."""
+                        shard_index=0, shard_count=1, raw_file=False, _invoke=None) -> PlonkProvingKey:
+        """qcp: list of pk.trace.Qcp columns (canonical), vk_qcp: their commitments, commitment_index: CommitmentInfo[i].CommitmentIndex.
+        raw_file=True: the arrays are byte sections of a ProvingKey.WriteRawTo file (plonk_pk_format.py), converted on the device."""
         n = 1 << log_n
-        keep = {k: _u64(v, (n, 4)) for k, v in dict(ql=ql, qr=qr, qm=qm, qo=qo, qk=qk, s1=s1, s2=s2, s3=s3).items()}
+        pb = 16 * self.fw      # bytes of a raw / in-memory affine G1 point
+        if raw_file:
+            def sec(x, nbytes):
+                a = np.frombuffer(x, dtype=np.uint8)
+                if a.shape[0] != nbytes:
+                    raise B200Error(f"key file section holds {a.shape[0]} bytes, expected {nbytes}")
+                return a
+            keep = {k: sec(v, 32 * n) for k, v in dict(ql=ql, qr=qr, qm=qm, qo=qo, qk=qk, s1=s1, s2=s2, s3=s3).items()}
+            keep["perm"] = sec(perm, 24 * n)
+            keep["kzg_g1"], keep["kzg_lagrange_g1"], keep["vk_commitments"] = sec(kzg_g1, (n + 3) * pb), sec(kzg_lagrange_g1, n * pb), sec(vk_commitments, 8 * pb)
+        else:
+            keep = {k: _u64(v, (n, 4)) for k, v in dict(ql=ql, qr=qr, qm=qm, qo=qo, qk=qk, s1=s1, s2=s2, s3=s3).items()}
+            keep["perm"] = np.ascontiguousarray(perm, dtype=np.int64).reshape(3 * n)
+            keep["kzg_g1"] = _u64(kzg_g1, (n + 3, 2 * self.fw))
+            keep["kzg_lagrange_g1"] = _u64(kzg_lagrange_g1, (n, 2 * self.fw))
+            keep["vk_commitments"] = _u64(vk_commitments, (8, 2 * self.fw))
         keep["generator"], keep["generator_big"], keep["coset_gen"] = _u64(generator), _u64(generator_big), _u64(coset_gen)
-        keep["perm"] = np.ascontiguousarray(perm, dtype=np.int64).reshape(3 * n)
-        keep["kzg_g1"] = _u64(kzg_g1, (n + 3, 2 * self.fw))
-        keep["kzg_lagrange_g1"] = _u64(kzg_lagrange_g1, (n, 2 * self.fw))
-        keep["vk_commitments"] = _u64(vk_commitments, (8, 2 * self.fw))
         d = _PlonkPkDesc()
         d.log_n, d.log_big, d.nb_public, d.nb_bsb22 = log_n, log_big, nb_public, len(qcp)
-        d.shard_index, d.shard_count = shard_index, shard_count
+        d.shard_index, d.shard_count, d.raw_file = shard_index, shard_count, int(bool(raw_file))
         for k, v in keep.items():
             setattr(d, k, v.ctypes.data)
         if len(qcp):
-            cols = [_u64(q, (n, 4)) for q in qcp]
+            cols = [np.frombuffer(q, dtype=np.uint8) if raw_file else _u64(q, (n, 4)) for q in qcp]
             ptrs = (C.c_void_p * len(cols))(*[c.ctypes.data for c in cols])
-            vq = _u64(vk_qcp, (len(cols), 2 * self.fw))
+            vq = np.frombuffer(vk_qcp, dtype=np.uint8) if raw_file else _u64(vk_qcp, (len(cols), 2 * self.fw))
             ci = np.ascontiguousarray(commitment_index, dtype=np.uint64)
             d.qcp, d.vk_qcp, d.commitment_index = C.addressof(ptrs), vq.ctypes.data, ci.ctypes.data
         h = C.c_void_p()

@@ -248,6 +248,50 @@ __global__ void __launch_bounds__(128) points_from_raw_kernel(uint32_t* __restri
     }
 }
 
+// []fr.Element as curve.Encoder writes it (plonk/bn254/marshal.go:158-176: the trace polynomials of a proving key):
+// 32-byte big-endian CANONICAL integers -> Montgomery limbs, in place.  *bad is set when an element is >= r.
+__global__ void __launch_bounds__(256) fr_from_be_kernel(uint32_t* __restrict__ v, size_t n, uint32_t* __restrict__ bad) {
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    uint4* p = reinterpret_cast<uint4*>(v + i * 8);
+    const uint4 a = p[0], b = p[1];
+    const uint32_t w[8] = {a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w};
+    Fr x;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) x.l[j] = __byte_perm(w[7 - j], 0, 0x0123);
+    bool lt = false, decided = false;
+#pragma unroll
+    for (int j = 7; j >= 0; --j) {
+        const uint32_t rj = FrParams::p(j);
+        if (!decided && x.l[j] != rj) { lt = x.l[j] < rj; decided = true; }
+    }
+    if (!lt) { if (bad) atomicOr(bad, 1u); x = Fr::zero(); }
+    x = x.to_mont();
+    p[0] = make_uint4(x.l[0], x.l[1], x.l[2], x.l[3]);
+    p[1] = make_uint4(x.l[4], x.l[5], x.l[6], x.l[7]);
+}
+// []int64 as encoding/binary writes it (big-endian), in place (pk.trace.S, marshal.go:175)
+__global__ void __launch_bounds__(256) i64_from_be_kernel(uint2* __restrict__ v, size_t n) {
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const uint2 w = v[i];
+    v[i] = make_uint2(__byte_perm(w.y, 0, 0x0123), __byte_perm(w.x, 0, 0x0123));
+}
+int fr_from_be_inplace(b200_ctx* ctx, Fr* d, size_t n, uint32_t* d_bad) {
+    if (n == 0) return B200_OK;
+    fr_from_be_kernel<<<(unsigned)((n + 255) / 256), 256, 0, ctx->stream>>>(reinterpret_cast<uint32_t*>(d), n, d_bad);
+    B2_CUDA(ctx, cudaGetLastError());
+    ctx->n_launches++;
+    return B200_OK;
+}
+int i64_from_be_inplace(b200_ctx* ctx, int64_t* d, size_t n) {
+    if (n == 0) return B200_OK;
+    i64_from_be_kernel<<<(unsigned)((n + 255) / 256), 256, 0, ctx->stream>>>(reinterpret_cast<uint2*>(d), n);
+    B2_CUDA(ctx, cudaGetLastError());
+    ctx->n_launches++;
+    return B200_OK;
+}
+
 int points_from_raw_inplace(b200_ctx* ctx, void* d_points, size_t n, int group, uint32_t* d_bad) {
     if (n == 0) return B200_OK;
     const unsigned blocks = (unsigned)((n + 127) / 128);

@@ -8,5 +8,8 @@ int batch_mul_g1(b200_ctx* ctx, const G1Affine& base, const Fr* d_scalars, size_
 int batch_mul_g2(b200_ctx* ctx, const G2Affine& base, const Fr* d_scalars, size_t n, G2Affine* d_out);
 // gnark-crypto RawEncoding point bytes -> affine Montgomery limbs, in place (both are sizeof(Affine) per point).
 // *bad (device word, may be null) gets 1 if any point carries a compressed-form flag or a coordinate >= p.
+// big-endian canonical fr.Element / big-endian int64 sections of a key file -> device layout, in place
+int fr_from_be_inplace(b200_ctx* ctx, Fr* d, size_t n, uint32_t* d_bad);
+int i64_from_be_inplace(b200_ctx* ctx, int64_t* d, size_t n);
 int points_from_raw_inplace(b200_ctx* ctx, void* d_points, size_t n, int group, uint32_t* d_bad);
 }  // namespace b200

@@ -22,6 +22,7 @@
 #include <cstdio>
 #include "host_group.cuh"
 #include "msm_host.cuh"
+#include "misc_host.cuh"
 #include "poly_host.cuh"
 
 using namespace b200;
@@ -335,6 +336,10 @@ static void plonk_pk_delete(b200_ctx* ctx, b200_plonk_pk* pk) {
     delete pk;
 }
 
+static int b200_bases_upload_raw_words(b200_ctx* ctx, int curve, int group, const uint64_t* raw, size_t n, b200_bases** out) {
+    return b200_bases_upload_raw(ctx, curve, group, reinterpret_cast<const uint8_t*>(raw), n, out);
+}
+
 namespace b200 {
 // the nine blinding coefficients of getRandomPolynomial (prove.go:295-301) from the OS entropy source, for the group
 // prover (group.cu): a proof sharded over several ranks needs the same ones on every rank
@@ -378,7 +383,7 @@ int b200_plonk_pk_upload(b200_ctx* ctx, int curve, const b200_plonk_pk_desc* d, 
         pk->commit_row[k] = d->nb_public + d->commitment_index[k];
         if (pk->commit_row[k] >= n) { delete pk; return ctx->fail(B200_ERR_ARG, "commitment index outside the domain"); }
     }
-    if (pk->nb_bsb) memcpy(pk->vk_qcp, d->vk_qcp, pk->nb_bsb * sizeof(G1Affine));
+    if (pk->nb_bsb && !d->raw_file) memcpy(pk->vk_qcp, d->vk_qcp, pk->nb_bsb * sizeof(G1Affine));
     Fr gen, gen_big, cg;
     memcpy(gen.l, d->generator, 32); memcpy(gen_big.l, d->generator_big, 32); memcpy(cg.l, d->coset_gen, 32);
     int st = ntt_domain_get(ctx, d->log_n, gen, cg, &pk->d0);
@@ -410,9 +415,45 @@ int b200_plonk_pk_upload(b200_ctx* ctx, int curve, const b200_plonk_pk_desc* d, 
         e = cudaMemcpyAsync(pk->trace.as<Fr>() + (size_t)k * n, src[k], n * sizeof(Fr), cudaMemcpyHostToDevice, s);
     if (e == cudaSuccess) e = cudaMemcpyAsync(pk->perm.p, d->perm, 3 * n * sizeof(int64_t), cudaMemcpyHostToDevice, s);
     if (e != cudaSuccess) return fail_cuda(e, "PlonK key upload");
+    const bool raw = d->raw_file != 0;
+    if (raw) {
+        // The arrays are sections of a ProvingKey.WriteRawTo file (plonk/bn254/marshal.go:101-180): scalars big-endian
+        // canonical, the permutation big-endian int64, points raw-encoded.  Converted on the device, in place.
+        DevBuf bad;
+        if (bad.alloc(4) != cudaSuccess || cudaMemsetAsync(bad.p, 0, 4, s) != cudaSuccess) return fail_cuda(cudaErrorMemoryAllocation, "PlonK key upload");
+        st = fr_from_be_inplace(ctx, pk->trace.as<Fr>(), 8 * n, bad.as<uint32_t>());
+        if (st == B200_OK && pk->nb_bsb) st = fr_from_be_inplace(ctx, pk->qcp.as<Fr>(), (size_t)pk->nb_bsb * n, bad.as<uint32_t>());
+        if (st == B200_OK) st = i64_from_be_inplace(ctx, pk->perm.as<int64_t>(), 3 * n);
+        // the few points the host keeps: 3 + 3 SRS points (commitBlindingFactor) and the 8 commitments of the key
+        DevBuf pts;
+        const size_t np = 3 + 3 + 8 + pk->nb_bsb;
+        if (st == B200_OK && pts.alloc(np * sizeof(G1Affine)) != cudaSuccess) st = ctx->fail(B200_ERR_NOMEM, "PlonK key upload");
+        if (st == B200_OK) {
+            char* q = (char*)pts.p;
+            cudaMemcpyAsync(q, d->kzg_g1, 3 * sizeof(G1Affine), cudaMemcpyHostToDevice, s);
+            cudaMemcpyAsync(q + 3 * sizeof(G1Affine), d->kzg_g1 + AFF_WORDS * n, 3 * sizeof(G1Affine), cudaMemcpyHostToDevice, s);
+            cudaMemcpyAsync(q + 6 * sizeof(G1Affine), d->vk_commitments, 8 * sizeof(G1Affine), cudaMemcpyHostToDevice, s);
+            if (pk->nb_bsb) cudaMemcpyAsync(q + 14 * sizeof(G1Affine), d->vk_qcp, pk->nb_bsb * sizeof(G1Affine), cudaMemcpyHostToDevice, s);
+            st = points_from_raw_inplace(ctx, pts.p, np, 1, bad.as<uint32_t>());
+            std::vector<G1Affine> hp(np);
+            uint32_t flag = 0;
+            if (st == B200_OK && (cudaMemcpyAsync(hp.data(), pts.p, np * sizeof(G1Affine), cudaMemcpyDeviceToHost, s) != cudaSuccess ||
+                                  cudaMemcpyAsync(&flag, bad.p, 4, cudaMemcpyDeviceToHost, s) != cudaSuccess || cudaStreamSynchronize(s) != cudaSuccess))
+                st = ctx->fail(B200_ERR_CUDA, "PlonK key upload");
+            if (st == B200_OK && flag) st = ctx->fail(B200_ERR_ARG, "raw_file: an element of the key file is not canonical (scalar >= r, coordinate >= p or compressed-form flag)");
+            if (st == B200_OK) {
+                memcpy(pk->srs_lo, hp.data(), 3 * sizeof(G1Affine));
+                memcpy(pk->srs_hi, hp.data() + 3, 3 * sizeof(G1Affine));
+                memcpy(pk->vk_pts, hp.data() + 6, 8 * sizeof(G1Affine));
+                for (uint32_t k = 0; k < pk->nb_bsb; ++k) pk->vk_qcp[k] = hp[14 + k];
+            }
+        }
+        if (st != B200_OK) { plonk_pk_delete(ctx, pk); return st; }
+    } else {
     memcpy(pk->srs_lo, d->kzg_g1, 3 * sizeof(G1Affine));
     memcpy(pk->srs_hi, d->kzg_g1 + AFF_WORDS * n, 3 * sizeof(G1Affine));
     memcpy(pk->vk_pts, d->vk_commitments, 8 * sizeof(G1Affine));
+    }
     // coset scaling tables: shift_k = g * w_big^k  (shifters, prove.go:903-907)
     Fr shift = cg;
     for (uint32_t k = 0; k < pk->rho && st == B200_OK; ++k) {
@@ -444,8 +485,9 @@ int b200_plonk_pk_upload(b200_ctx* ctx, int curve, const b200_plonk_pk_desc* d, 
     if (st == B200_OK) st = ntt_run(ctx, pk->d0, pk->qk_lag.as<Fr>(), 0, 1, nullptr, nullptr, nullptr);
     if (st == B200_OK && cudaStreamSynchronize(s) != cudaSuccess) st = ctx->fail(B200_ERR_CUDA, "PlonK key precomputation");
     // each rank keeps its point range of both SRS (the whole of them on one GPU)
-    if (st == B200_OK) st = b200_bases_upload(ctx, curve, 1, d->kzg_g1 + AFF_WORDS * pk->srs_lo_idx, pk->srs_hi_idx - pk->srs_lo_idx, &pk->srs);
-    if (st == B200_OK) st = b200_bases_upload(ctx, curve, 1, d->kzg_lagrange_g1 + AFF_WORDS * pk->lag_lo, pk->lag_hi - pk->lag_lo, &pk->srs_lag);
+    auto up = raw ? b200_bases_upload_raw_words : b200_bases_upload;
+    if (st == B200_OK) st = up(ctx, curve, 1, d->kzg_g1 + AFF_WORDS * pk->srs_lo_idx, pk->srs_hi_idx - pk->srs_lo_idx, &pk->srs);
+    if (st == B200_OK) st = up(ctx, curve, 1, d->kzg_lagrange_g1 + AFF_WORDS * pk->lag_lo, pk->lag_hi - pk->lag_lo, &pk->srs_lag);
     if (st != B200_OK) { plonk_pk_delete(ctx, pk); return st; }
     *out = pk;
     return B200_OK;

@@ -608,6 +608,11 @@ typedef struct b200_plonk_pk_desc {
     const uint64_t *const *qcp;     /* pk.trace.Qcp[i]: canonical / regular, n each (NULL when nb_bsb22 = 0)  */
     const uint64_t *vk_qcp;         /* pk.Vk.Qcp: nb_bsb22 affine points                                     */
     const size_t *commitment_index; /* CommitmentInfo[i].CommitmentIndex (constraint index; the row is + nb_public) */
+    int raw_file;                   /* non-zero: the arrays are sections of a ProvingKey.WriteRawTo file
+                                       (plonk/bn254/marshal.go:101-180), converted on the device: ql..s3 and qcp[i] = n
+                                       32-byte big-endian canonical scalars, perm = 3n big-endian int64, kzg_g1 /
+                                       kzg_lagrange_g1 / vk_commitments / vk_qcp = raw-encoded points (see
+                                       b200_points_from_raw); generators and coset_gen stay Montgomery limbs          */
     int shard_index, shard_count;   /* multi-GPU: this rank's share (0, 0 or 0, 1 = the whole key).  The arrays above are
                                        always the full ones; the rank keeps the SRS point range [N k / R, N (k+1) / R) on its
                                        device and evaluates the quotient on the cosets k = shard_index (mod shard_count).      */

@@ -169,3 +169,72 @@ def test_bls12_377_points_from_raw(pkg):
             c.points_from_raw(bytes([0x80]) + bytes(95), 1, 1)
     finally:
         c.close()
+
+
+# ---- PlonK proving key: ProvingKey.WriteRawTo (plonk/bn254/marshal.go:101-180) ---------------------------------------
+def _plonk_key_file(nb_mul, nb_commit, seed, lines_bytes=33280):
+    from oracle import plonk_prove as PP
+    from oracle import plonk_raw
+    rng = random.Random(seed)
+    spr = PP.commit_chain_scs(nb_mul, nb_commit) if nb_commit else PP.mul_chain_scs(nb_mul)
+    pk = PP.setup(spr, rng.randrange(1, B.R))
+    mono, lag = PP.srs_scalars(pk)
+    srs = [B.g1_mul(B.G1_GEN, k) for k in mono]
+    lagp = [B.g1_mul(B.G1_GEN, k) for k in lag]
+    raw = plonk_raw.write_raw(pk, B, srs, lagp, g2_points=(B.G2_GEN, B.g2_mul(B.G2_GEN, pk.tau)), lines_bytes=lines_bytes)
+    return PP, spr, pk, raw, rng
+
+
+@pytest.mark.parametrize("nb_commit,lines_bytes", [(0, 33280), (2, 33280), (0, 1000)])
+def test_plonk_parser_walks_the_writer_layout(pkg, nb_commit, lines_bytes):
+    PP, spr, pk, raw, _ = _plonk_key_file(10, nb_commit, 5, lines_bytes)
+    F = pkg.plonk_pk_format
+    p = F.parse(raw, pkg.BN254)
+    n = pk.d0.cardinality
+    assert p.file_bytes == len(raw) and (p.size, p.size_big, p.nb_public) == (n, pk.d1.cardinality, pk.nb_public)
+    assert (p.generator, p.generator_big, p.coset_shift) == (pk.d0.generator, pk.d1.generator, pk.d0.coset_gen)
+    assert p.lines_bytes == lines_bytes and p.nb_qcp == nb_commit and p.commitment_indexes == [c["index"] for c in pk.commitments]
+    off, ln = p.sections["ql"]
+    assert ln == 32 * n and raw[off:off + 32] == (pk.ql[0] % B.R).to_bytes(32, "big")
+    off, ln = p.sections["perm"]
+    assert off + ln == len(raw) and int.from_bytes(raw[off + 8:off + 16], "big", signed=True) == pk.perm[1]
+    off, ln = p.sections["kzg_lagrange_g1"]
+    assert ln == 64 * n
+    with pytest.raises(pkg.pk_format.PkFormatError):
+        F.parse(raw[:-8], pkg.BN254)
+    bad = bytearray(raw); bad[7] = 3
+    with pytest.raises(pkg.pk_format.PkFormatError):
+        F.parse(bytes(bad), pkg.BN254)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("nb_mul,nb_commit,ranks", [(200, 0, 1), (40, 2, 1), (100, 0, 4)])
+def test_plonk_key_file_to_proof(ctx, pkg, cref, nb_mul, nb_commit, ranks):
+    """A WriteRawTo file goes to the device as it is (scalars, permutation and points converted by kernels) and the key
+    proves: proof bytes == oracle, on one context and sharded over a device group; a damaged scalar is refused."""
+    from tests import plonk_util as PU
+    PP, spr, pk, raw, rng = _plonk_key_file(nb_mul, nb_commit, 77 + nb_mul)
+    if nb_commit:
+        sol, bsb = PP.commit_chain_solution(spr, pk, rng.randrange(2, B.R), [(rng.randrange(B.R), rng.randrange(B.R)) for _ in range(nb_commit)])
+    else:
+        sol, bsb = PP.mul_chain_solution(nb_mul, 5), None
+    blinding = tuple([rng.randrange(B.R) for _ in range(k)] for k in (2, 2, 2, 3))
+    want, _ = PP.prove(spr, pk, sol, blinding, bsb)
+    L, Rr, O = (util.fr_arr(v) for v in PP.evaluate_lro(spr, sol))
+    prover = pkg.Group([0] * ranks) if ranks > 1 else ctx
+    try:
+        dpk, parsed = pkg.plonk_pk_format.upload(prover, raw)
+        try:
+            got, _ = prover.plonk_prove(dpk, L, Rr, O, util.fr_arr(sol[:1]), PU.blinding_array(blinding), PU.bsb_arrays(bsb))
+        finally:
+            dpk.free()
+        assert pkg.plonk_proof_bytes(got) == PP.proof_bytes(want)
+        if ranks == 1:
+            bad = bytearray(raw)
+            off, _ = parsed.sections["qm"]
+            bad[off:off + 32] = b"\xff" * 32                    # a scalar >= r
+            with pytest.raises(pkg.B200Error, match="not canonical"):
+                pkg.plonk_pk_format.upload(prover, bytes(bad))
+    finally:
+        if ranks > 1:
+            prover.close()

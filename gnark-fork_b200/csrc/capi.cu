@@ -613,7 +613,7 @@ int b200_set_option(b200_ctx* ctx, const char* key, long value) try {
     if (k == "msm_c") { if (value != 0 && (value < 4 || value > 24)) return ctx->fail(B200_ERR_ARG, "msm_c out of range"); ctx->msm_c_override = (int)value; }
     else if (k == "ntt_tile_log") { if (value < 6 || value > 12) return ctx->fail(B200_ERR_ARG, "ntt_tile_log out of range"); ctx->ntt_tile_log = (int)value; }
     else if (k == "ntt_strided_stages") { if (value < 1 || value > 12) return ctx->fail(B200_ERR_ARG, "ntt_strided_stages out of range"); ctx->ntt_strided_stages = (int)value; }
-    else if (k == "msm_ba") { if (value < 0 || value > 6) return ctx->fail(B200_ERR_ARG, "msm_ba out of range"); ctx->msm_ba = (int)value; }
+    else if (k == "msm_ba") { if (value < 0 || value > 9) return ctx->fail(B200_ERR_ARG, "msm_ba out of range"); ctx->msm_ba = (int)value; }
     else if (k == "msm_ba_force") { ctx->msm_ba_force = value ? 1 : 0; }
     else if (k == "msm_acc_smem") { ctx->msm_acc_smem = (int)(value & 3); }
     else if (k == "msm_overlap") { ctx->msm_overlap = value ? 1 : 0; }
@@ -621,6 +621,10 @@ int b200_set_option(b200_ctx* ctx, const char* key, long value) try {
     else if (k == "msm_fold_c") { if (value != 0 && (value < 8 || value > 24)) return ctx->fail(B200_ERR_ARG, "msm_fold_c out of range"); ctx->msm_fold_c = (int)value; }
     else if (k == "ntt_tma") ctx->ntt_tma = value ? 1 : 0;
     else if (k == "h_sort_overlap") ctx->h_sort_overlap = value ? 1 : 0;
+    else if (k == "l2_fetch") {   // device-wide hint: bytes DRAM -> L2 fetches at most per miss (32, 64 or 128); experiments on the table gathers
+        if (value != 32 && value != 64 && value != 128) return ctx->fail(B200_ERR_ARG, "l2_fetch must be 32, 64 or 128");
+        B2_CUDA(ctx, cudaDeviceSetLimit(cudaLimitMaxL2FetchGranularity, (size_t)value));
+    }
     else if (k == "ntt_threads") { if (value < 32 || value > 1024 || (value & (value - 1))) return ctx->fail(B200_ERR_ARG, "ntt_threads must be a power of two in 32..1024"); ctx->ntt_threads = (int)value; }
     else return ctx->fail(B200_ERR_ARG, "unknown option", key);
     return B200_OK;

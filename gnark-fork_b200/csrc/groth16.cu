@@ -232,11 +232,12 @@ int groth16_prove_core(b200_ctx* ctx, const b200_groth16_pk* pk, const uint64_t*
     const int groups[5] = {1, 1, 1, 2, 1};
     const MsmFold* folds[5] = {&pk->fA, &pk->fB, &pk->fK, &pk->fG2B, &pk->fZ};
     MsmSizes sz[5];
-    size_t sort_max = 0, acc_max = 0, res_off[6] = {0};
+    size_t sort_max = 0, acc_max = 0, ba_max = 0, res_off[6] = {0};
     for (int k = 0; k < 5; ++k) {
         sz[k] = msm_sizes(counts[k], groups[k], ctx->msm_mode(), folds[k]->c);
         sort_max = std::max(sort_max, sz[k].sort_bytes);
         acc_max = std::max(acc_max, sz[k].acc_bytes);
+        ba_max = std::max(ba_max, sz[k].ba_bytes);
         res_off[k + 1] = res_off[k] + ((sz[k].result_bytes + 255) & ~(size_t)255);
     }
     const bool overlap = ctx->msm_overlap != 0;
@@ -251,6 +252,7 @@ int groth16_prove_core(b200_ctx* ctx, const b200_groth16_pk* pk, const uint64_t*
     const size_t o_sort1 = overlap ? ar.off : o_sort0; if (overlap) ar.take(sort_max);
     const size_t o_acc = ar.off; ar.take(acc_max);
     const size_t o_acc1 = overlap ? ar.off : o_acc; if (overlap) ar.take(acc_max);   // second accumulation group: the reduction of MSM k runs beside the accumulation of k+1
+    const size_t o_ba = ar.off; ar.take(ba_max);   // batched-affine round buffers: the accumulations run one after the other on the main stream
     B2_TRY(ctx_reserve(ctx, ar.off));
     if (ctx->h_stage_bytes < res_off[5]) {   // page-locked staging of the few result points per MSM
         if (ctx->h_stage) cudaFreeHost(ctx->h_stage);
@@ -336,8 +338,8 @@ int groth16_prove_core(b200_ctx* ctx, const b200_groth16_pk* pk, const uint64_t*
         void* stage = (char*)ctx->h_stage + res_off[k];
         char* sw = sort_ws[overlap ? sort_slot[k] : 0];
         char* aw = acc_ws[overlap ? (k & 1) : 0];
-        jobs[k] = groups[k] == 2 ? msm_g2_job_new(ctx, (const G2Affine*)bases[k], scal[k], maps[k], counts[k], folds[k], sw, aw, stage)
-                                 : msm_g1_job_new(ctx, (const G1Affine*)bases[k], scal[k], maps[k], counts[k], folds[k], sw, aw, stage);
+        jobs[k] = groups[k] == 2 ? msm_g2_job_new(ctx, (const G2Affine*)bases[k], scal[k], maps[k], counts[k], folds[k], sw, aw, stage, base + o_ba)
+                                 : msm_g1_job_new(ctx, (const G1Affine*)bases[k], scal[k], maps[k], counts[k], folds[k], sw, aw, stage, base + o_ba);
     }
     auto run_h = [&]() -> int {
         B2_CUDA(ctx, cudaStreamWaitEvent(st, ev_abc, 0));
@@ -357,8 +359,8 @@ int groth16_prove_core(b200_ctx* ctx, const b200_groth16_pk* pk, const uint64_t*
         if (k == 2) B2_CUDA(ctx, cudaStreamWaitEvent(sx, ev_acc[0], 0));
         if (k == 3) B2_CUDA(ctx, cudaStreamWaitEvent(sx, ev_acc[1], 0));
         if (k == 4) B2_CUDA(ctx, cudaStreamWaitEvent(sx, ev_acc[2], 0));
-        if (!(k == 3 && share_b))
-            B2_TRY(groups[k] == 2 ? msm_g2_job_sort(ctx, jobs[k], sx) : msm_g1_job_sort(ctx, jobs[k], sx));
+        if (k == 3 && share_b) B2_TRY(msm_g2_job_prep0(ctx, jobs[k], sx));   // batched-affine rounds: Bs2's own denominator pass over Bs1's entries
+        else B2_TRY(groups[k] == 2 ? msm_g2_job_sort(ctx, jobs[k], sx) : msm_g1_job_sort(ctx, jobs[k], sx));
         B2_CUDA(ctx, cudaEventRecord(ev_sort[k], sx));
         return B200_OK;
     };

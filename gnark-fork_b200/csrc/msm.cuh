@@ -109,6 +109,10 @@ __device__ __forceinline__ T ld_vec(const T* p) {
     for (int i = 0; i < (int)(sizeof(T) / 16); ++i) d[i] = s[i];
     return r;
 }
+// Read-only gather of one record.  A miss of a plain ld.global(.nc) makes L2 fetch the whole 128-byte line from DRAM; with the
+// L2::64B qualifier it fetches the 64-byte half that was asked for (scripts/gather_probe.cu, ncu dram__bytes_read: 2^26 random
+// 64-byte records = 4.31 GB against 8.58 GB; cudaLimitMaxL2FetchGranularity changes nothing).  Records that are not whole
+// lines (a 64-byte G1 point, a 32-byte coordinate, 96-byte BLS12-377 points) take the hint; whole-line records do not.
 template <class T>
 __device__ __forceinline__ T ldg_vec(const T* p) {
     static_assert(sizeof(T) % 16 == 0, "16-byte multiples only");
@@ -116,7 +120,10 @@ __device__ __forceinline__ T ldg_vec(const T* p) {
     const uint4* s = reinterpret_cast<const uint4*>(p);
     uint4* d = reinterpret_cast<uint4*>(&r);
 #pragma unroll
-    for (int i = 0; i < (int)(sizeof(T) / 16); ++i) d[i] = __ldg(s + i);
+    for (int i = 0; i < (int)(sizeof(T) / 16); ++i) {
+        if (sizeof(T) % 128 == 0) d[i] = __ldg(s + i);
+        else asm("ld.global.nc.L2::64B.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(d[i].x), "=r"(d[i].y), "=r"(d[i].z), "=r"(d[i].w) : "l"(s + i));
+    }
     return r;
 }
 template <class T>

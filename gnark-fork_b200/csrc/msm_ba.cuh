@@ -1,8 +1,9 @@
 // Batched-affine pre-reduction of the MSM buckets (an optional stage in front of msm_accumulate_kernel).
 //
-// A mixed XYZZ addition costs 8 products + one a*b - c*d (1288 MAC32).  An AFFINE addition costs one inversion
-// and 3 products; with the inversions of a whole launch shared (Montgomery's trick: prefix products, one inversion
-// per 1024 additions, back-substitution) that is 6 products (816 MAC32) + ~0.6 for the shared inversion.
+// A mixed XYZZ addition costs 8 products + one a*b - c*d (1288 MAC32 in Fp, 3568 in Fp2).  An AFFINE addition costs one
+// inversion and 3 products; with the inversions of a whole launch shared (Montgomery's trick: prefix products, one
+// inversion per BA_K x chunk additions, back-substitution) that is 6 products (816 MAC32 in Fp, 1952 in Fp2: 0.63 / 0.55
+// of the XYZZ addition) + ~0.4 for the shared inversion.
 // The bucket contents are reduced pairwise for R rounds -- after round r every bucket holds ceil(count / 2^r)
 // affine points -- and msm_accumulate_kernel finishes from 1/2^R of the additions.
 //
@@ -10,10 +11,14 @@
 // padded to a multiple of 2^R slots (unused slots keep the 0xffffffff sentinel = the point at infinity), so
 // out[i] = in[2i] + in[2i+1] never mixes two buckets and no per-round offsets exist: offset_r = offset_0 >> r.
 //
-// One round = three launches over n_out additions, BA_K per thread:
-//   ba_prep_kernel     denominators d_i, pref[i] = product of the d before i inside the thread's chunk, cprod[t]
-//   ba_inverse_kernel  cinv[t] = 1 / cprod[t]  (chunks of BA_INV_CHUNK with one Fermat inversion each)
-//   ba_apply_kernel    walks the chunk backwards: 1/d_i = running * pref[i], then lambda, x3, y3
+// One round = three launches over n_out additions, BA_K per thread.  Thread t of T = n_out / BA_K owns the additions
+// t, t + T, t + 2T, ...: neighbouring lanes work on neighbouring pairs, so every load and store of a warp is one
+// contiguous run (the first version gave each thread a contiguous chunk: 2 KB between lanes, L1-bound).
+//   ba_prep_kernel     denominators d_i from the x coordinates alone, pref[i] = product of the thread's earlier d, cprod[t]
+//   ba_inverse_kernel  cinv[t] = 1 / cprod[t]  (strided chunks with one Fermat inversion each)
+//   ba_apply_kernel    walks the thread's additions backwards: 1/d_i = running * pref[i], then lambda, x3, y3
+// Between rounds the points are stored as two planes (all x, then all y): the denominator pass streams the x plane only.
+// The last round writes (x, y) pairs, which msm_accumulate_kernel reads as its bases.
 // Cases: P or Q at infinity (copy), P = Q (doubling: d = 2y, lambda = 3x^2/d; a = 0), P = -Q (infinity), else
 // d = x2 - x1.  d is never zero, so the shared product is invertible.
 #pragma once
@@ -21,86 +26,183 @@
 
 namespace b200 {
 
-constexpr int BA_K = 16;            // additions per thread
-constexpr int BA_INV_CHUNK = 64;    // chunk products per Fermat inversion
+constexpr int BA_K = 32;             // additions per thread
+constexpr int BA_INV_CHUNK = 128;    // at most this many thread products per Fermat inversion
 
 #if defined(__CUDACC__)
 
-template <class F>
-__device__ __forceinline__ F ba_denominator(const Affine<F>& P, const Affine<F>& Q) {
-    if (P.is_inf() || Q.is_inf()) return F::one();
-    if (P.x != Q.x) return Q.x - P.x;
-    if (P.y == Q.y && !P.y.is_zero()) return P.y.dbl();
-    return F::one();
+constexpr uint32_t BA_EMPTY = 0xffffffffu;
+#ifndef BA_APPLY_BLOCKS_FP2
+#define BA_APPLY_BLOCKS_FP2 3
+#endif
+#define BA_APPLY_BLOCKS(F) (sizeof(F) > 48 ? BA_APPLY_BLOCKS_FP2 : 1)   // resident blocks asked of ptxas (Fp2: 222 registers otherwise, 2 blocks)
+
+// One operand pair of a round.  FIRST: gathered from the (folded) base table through the sorted entries (sign bit =
+// negate, 0xffffffff = empty slot); later rounds: elements 2i, 2i+1 of the previous round's planes.
+template <class F, bool FIRST>
+struct BaPair {
+    const Affine<F>* table;
+    const uint32_t* sorted;
+    const F* xs;
+    const F* ys;
+    uint32_t e0, e1;
+    // the pair's entries: FIRST: two sorted entries (one 8-byte load), else the positions 2i, 2i+1
+    static __device__ __forceinline__ uint2 entries(const uint32_t* sorted_, uint32_t i) {
+        if (FIRST) return reinterpret_cast<const uint2*>(sorted_)[i];
+        return make_uint2(2u * i, 2u * i + 1u);
+    }
+    __device__ __forceinline__ BaPair(const Affine<F>* table_, const uint32_t* sorted_, const F* xs_, const F* ys_, uint2 e)
+        : table(table_), sorted(sorted_), xs(xs_), ys(ys_), e0(e.x), e1(e.y) {}
+    __device__ __forceinline__ BaPair(const Affine<F>* table_, const uint32_t* sorted_, const F* xs_, const F* ys_, uint32_t i)
+        : BaPair(table_, sorted_, xs_, ys_, entries(sorted_, i)) {}
+    // start the DRAM -> L2 fetch of the pair's operands (no destination registers): issued one iteration ahead, it turns
+    // the dependent gather of the next addition into an L2 hit.  with_y = false: the denominator pass reads x only.
+    static __device__ __forceinline__ void prefetch_l2(const void* p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
+    static __device__ __forceinline__ void prefetch(const Affine<F>* table_, const F* xs_, const F* ys_, uint2 e, bool with_y) {
+        if (FIRST) {
+            // nothing: prefetch.global.L2 pulls whole 128-byte lines, and the random gathers of the first round sit at the
+            // DRAM's random-access rate (measured: 46 G 64-byte accesses/s with ld.global.nc.L2::64B, 29 G lines/s with the
+            // prefetch in front -- the denominator pass went from 5.0 to 8.8 ms)
+        } else {
+            prefetch_l2(xs_ + e.x);
+            if (sizeof(F) >= 64) prefetch_l2(xs_ + e.y);
+            if (with_y) { prefetch_l2(ys_ + e.x); if (sizeof(F) >= 64) prefetch_l2(ys_ + e.y); }
+        }
+    }
+    __device__ __forceinline__ bool empty() const { return FIRST && (e0 == BA_EMPTY || e1 == BA_EMPTY); }
+    __device__ __forceinline__ F x(int k) const {
+        const uint32_t e = k ? e1 : e0;
+        if (FIRST) return ldg_vec(&table[e & 0x7fffffffu].x);
+        return ld_vec(xs + e);
+    }
+    __device__ __forceinline__ F y(int k) const {
+        const uint32_t e = k ? e1 : e0;
+        if (FIRST) {
+            if (e == BA_EMPTY) return F::zero();
+            const F v = ldg_vec(&table[e & 0x7fffffffu].y);
+            return (e >> 31) ? v.neg() : v;
+        }
+        return ld_vec(ys + e);
+    }
+    __device__ __forceinline__ Affine<F> point(int k) const {
+        const uint32_t e = k ? e1 : e0;
+        if (FIRST) {
+            if (e == BA_EMPTY) return Affine<F>::inf();
+            Affine<F> p = ldg_vec(table + (e & 0x7fffffffu));
+            if (e >> 31) p.y = p.y.neg();
+            return p;
+        }
+        return {ld_vec(xs + e), ld_vec(ys + e)};
+    }
+};
+
+// Kind of an addition: 0 = no division (an operand at infinity, or P = -Q), 1 = chord (d = x2 - x1), 2 = tangent (d = 2y).
+// Decided from x alone whenever the two x differ and neither is zero (the common case); y is read only otherwise.
+template <class F, bool FIRST>
+__device__ __forceinline__ int ba_denominator(const BaPair<F, FIRST>& pr, F* d) {
+    if (pr.empty()) return 0;
+    const F x0 = pr.x(0), x1 = pr.x(1);
+    if (x0.is_zero() || x1.is_zero()) {          // (0, 0) is infinity; x = 0 with y != 0 can be a curve point
+        const F y0 = pr.y(0), y1 = pr.y(1);
+        if ((x0.is_zero() && y0.is_zero()) || (x1.is_zero() && y1.is_zero())) return 0;
+        if (x0 != x1) { *d = x1 - x0; return 1; }
+        if (y0 == y1 && !y0.is_zero()) { *d = y0.dbl(); return 2; }
+        return 0;
+    }
+    if (x0 != x1) { *d = x1 - x0; return 1; }
+    const F y0 = pr.y(0), y1 = pr.y(1);
+    if (y0 == y1 && !y0.is_zero()) { *d = y0.dbl(); return 2; }
+    return 0;
 }
 
-// operand `idx` of a round: the first round gathers through the sorted entries (sign bit = negate,
-// 0xffffffff = empty slot), later rounds read the previous round's points
 template <class F, bool FIRST>
-__device__ __forceinline__ Affine<F> ba_load(const Affine<F>* __restrict__ pts, const uint32_t* __restrict__ sorted, uint32_t idx) {
-    if (!FIRST) return ld_vec(pts + idx);
-    const uint32_t e = sorted[idx];
-    if (e == 0xffffffffu) return Affine<F>::inf();
-    Affine<F> p = ldg_vec(pts + (e & 0x7fffffffu));
-    if (e >> 31) p.y = p.y.neg();
-    return p;
-}
-
-template <class F, bool FIRST>
-__global__ void __launch_bounds__(128) ba_prep_kernel(const Affine<F>* __restrict__ pts, const uint32_t* __restrict__ sorted, uint32_t n_out,
+__global__ void __launch_bounds__(128) ba_prep_kernel(const Affine<F>* __restrict__ table, const uint32_t* __restrict__ sorted,
+                                                      const F* __restrict__ xs, const F* __restrict__ ys, uint32_t T,
                                                       F* __restrict__ pref, F* __restrict__ cprod) {
     const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
-    const uint32_t lo = t * BA_K;
-    if (lo >= n_out) return;
+    if (t >= T) return;
     F acc = F::one();
+    bool have = false;
+    typedef BaPair<F, FIRST> Pair;
+    uint2 e_cur = Pair::entries(sorted, t);
+    uint2 e_nxt = Pair::entries(sorted, T + t);
+    Pair::prefetch(table, xs, ys, e_cur, false);
+#pragma unroll 1
     for (int j = 0; j < BA_K; ++j) {
-        const uint32_t i = lo + j;
-        const Affine<F> P = ba_load<F, FIRST>(pts, sorted, 2 * i), Q = ba_load<F, FIRST>(pts, sorted, 2 * i + 1);
-        st_vec(pref + i, acc);
-        acc = acc * ba_denominator(P, Q);
+        const uint32_t i = (uint32_t)j * T + t;
+        uint2 e_far = e_nxt;
+        if (j + 2 < BA_K) e_far = Pair::entries(sorted, (uint32_t)(j + 2) * T + t);
+        if (j + 1 < BA_K) Pair::prefetch(table, xs, ys, e_nxt, false);
+        if (j) st_vec(pref + i, acc);
+        F d;
+        const Pair pr(table, sorted, xs, ys, e_cur);
+        if (ba_denominator<F, FIRST>(pr, &d)) {
+            acc = have ? acc * d : d;
+            have = true;
+        }
+        e_cur = e_nxt;
+        e_nxt = e_far;
     }
     st_vec(cprod + t, acc);
 }
 
+// thread u inverts the elements u, u + U, u + 2U, ... (at most `chunk` of them) with one Fermat inversion
 template <class F>
-__global__ void __launch_bounds__(64) ba_inverse_kernel(const F* __restrict__ in, F* __restrict__ out, uint32_t m) {
-    const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
-    const uint32_t lo = t * BA_INV_CHUNK;
-    if (lo >= m) return;
-    const int cnt = (int)(m - lo < (uint32_t)BA_INV_CHUNK ? m - lo : (uint32_t)BA_INV_CHUNK);
+__global__ void __launch_bounds__(64) ba_inverse_kernel(const F* __restrict__ in, F* __restrict__ out, uint32_t m, uint32_t U, uint32_t chunk) {
+    const uint32_t u = blockIdx.x * blockDim.x + threadIdx.x;
+    if (u >= U) return;
     F acc = F::one();
-    for (int i = 0; i < cnt; ++i) {
-        st_vec(out + lo + i, acc);
-        acc = acc * ld_vec(in + lo + i);
+    uint32_t cnt = 0;
+    for (uint32_t e = u; e < m && cnt < chunk; e += U, ++cnt) {
+        st_vec(out + e, acc);
+        acc = acc * ld_vec(in + e);
     }
     F inv = acc.inv();
-    for (int i = cnt - 1; i >= 0; --i) {
-        const F pre = ld_vec(out + lo + i);
-        st_vec(out + lo + i, inv * pre);
-        inv = inv * ld_vec(in + lo + i);
+    for (uint32_t k = cnt; k-- > 0;) {
+        const uint32_t e = u + k * U;
+        const F pre = ld_vec(out + e);
+        st_vec(out + e, inv * pre);
+        inv = inv * ld_vec(in + e);
     }
 }
 
-template <class F, bool FIRST>
-__global__ void __launch_bounds__(128) ba_apply_kernel(const Affine<F>* __restrict__ pts, const uint32_t* __restrict__ sorted, uint32_t n_out,
-                                                       const F* __restrict__ pref, const F* __restrict__ cinv, Affine<F>* __restrict__ out) {
+// LAST: the round's output is read by msm_accumulate_kernel: (x, y) pairs; otherwise two planes
+template <class F, bool FIRST, bool LAST>
+__global__ void __launch_bounds__(128, BA_APPLY_BLOCKS(F)) ba_apply_kernel(const Affine<F>* __restrict__ table, const uint32_t* __restrict__ sorted,
+                                                       const F* __restrict__ xs, const F* __restrict__ ys, uint32_t T,
+                                                       const F* __restrict__ pref, const F* __restrict__ cinv,
+                                                       F* __restrict__ out_x, F* __restrict__ out_y, Affine<F>* __restrict__ out_xy) {
     const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
-    const uint32_t lo = t * BA_K;
-    if (lo >= n_out) return;
+    if (t >= T) return;
     F inv = ld_vec(cinv + t);
+    typedef BaPair<F, FIRST> Pair;
+    uint2 e_cur = Pair::entries(sorted, (uint32_t)(BA_K - 1) * T + t);
+    uint2 e_nxt = Pair::entries(sorted, (uint32_t)(BA_K - 2) * T + t);
+    Pair::prefetch(table, xs, ys, e_cur, true);
+#pragma unroll 1
     for (int j = BA_K - 1; j >= 0; --j) {
-        const uint32_t i = lo + j;
-        const Affine<F> P = ba_load<F, FIRST>(pts, sorted, 2 * i), Q = ba_load<F, FIRST>(pts, sorted, 2 * i + 1);
+        const uint32_t i = (uint32_t)j * T + t;
+        uint2 e_far = e_nxt;
+        if (j >= 2) e_far = Pair::entries(sorted, (uint32_t)(j - 2) * T + t);
+        if (j >= 1) {
+            Pair::prefetch(table, xs, ys, e_nxt, true);
+            if (j >= 2) Pair::prefetch_l2(pref + (i - T));
+        }
+        const Pair pr(table, sorted, xs, ys, e_cur);
+        e_cur = e_nxt;
+        e_nxt = e_far;
+        const Affine<F> P = pr.point(0), Q = pr.point(1);
         Affine<F> R;
-        if (P.is_inf()) R = Q;                       // d = 1: the running inverse is unchanged
-        else if (Q.is_inf()) R = P;
+        const bool p_inf = P.is_inf(), q_inf = Q.is_inf();
+        if (p_inf) R = Q;                            // no division: the running inverse is unchanged
+        else if (q_inf) R = P;
         else {
             const bool same_x = P.x == Q.x;
-            if (same_x && !(P.y == Q.y && !P.y.is_zero())) R = Affine<F>::inf();     // P = -Q (or a 2-torsion point): d = 1
+            if (same_x && !(P.y == Q.y && !P.y.is_zero())) R = Affine<F>::inf();     // P = -Q (or a 2-torsion point)
             else {
                 const F d = same_x ? P.y.dbl() : Q.x - P.x;
-                const F dinv = inv * ld_vec(pref + i);
-                inv = inv * d;
+                F dinv = inv;
+                if (j) { dinv = inv * ld_vec(pref + i); inv = inv * d; }
                 F num;
                 if (same_x) { const F xx = P.x.sqr(); num = xx.dbl() + xx; }      // 3 x^2 (a = 0)
                 else num = Q.y - P.y;
@@ -109,7 +211,8 @@ __global__ void __launch_bounds__(128) ba_apply_kernel(const Affine<F>* __restri
                 R.y = lam * (P.x - R.x) - P.y;
             }
         }
-        st_vec(out + i, R);
+        if (LAST) st_vec(out_xy + i, R);
+        else { st_vec(out_x + i, R.x); st_vec(out_y + i, R.y); }
     }
 }
 

@@ -24,10 +24,10 @@ int msm_g2_run(b200_ctx* ctx, const G2Affine* d_bases, const Fr* d_scalars, cons
 // The same pipeline in three steps, for callers that overlap the sort of one MSM with the bucket
 // accumulation of another (groth16.cu): sizes of the two workspace groups and of the host staging,
 // then job_new / job_sort(stream) / job_acc(stream) / [sync] / job_finish / job_delete.
-struct MsmSizes { size_t sort_bytes, acc_bytes, result_bytes; };
+struct MsmSizes { size_t sort_bytes, acc_bytes, result_bytes, ba_bytes; };   // ba_bytes: batched-affine round buffers (one region serves every MSM of a stream: only one accumulates at a time)
 MsmSizes msm_sizes(size_t n, int group, int c_override, int fold_c);
 void* msm_g1_job_new(b200_ctx* ctx, const G1Affine* d_bases, const Fr* d_scalars, const uint32_t* d_idx_map, size_t n,
-                     const MsmFold* fold, void* sort_ws, void* acc_ws, void* host_staging);
+                     const MsmFold* fold, void* sort_ws, void* acc_ws, void* host_staging, void* ba_ws = nullptr);
 int msm_g1_job_sort(b200_ctx* ctx, void* job, cudaStream_t st);
 // st_post / ev_split (optional): the bucket reduction (leaf sums, trees, result copy) is enqueued on st_post after
 // ev_split, recorded on st behind the accumulation and the split-bucket merges -- it then overlaps whatever st runs next
@@ -35,8 +35,10 @@ int msm_g1_job_acc(b200_ctx* ctx, void* job, cudaStream_t st, cudaStream_t st_po
 void msm_g1_job_finish(void* job, G1Jac* out_host);
 void msm_g1_job_delete(void* job);
 void* msm_g2_job_new(b200_ctx* ctx, const G2Affine* d_bases, const Fr* d_scalars, const uint32_t* d_idx_map, size_t n,
-                     const MsmFold* fold, void* sort_ws, void* acc_ws, void* host_staging);
+                     const MsmFold* fold, void* sort_ws, void* acc_ws, void* host_staging, void* ba_ws = nullptr);
 int msm_g2_job_sort(b200_ctx* ctx, void* job, cudaStream_t st);
+// the part of job_sort that depends on the job's own bases: for a job that reuses another job's sorted entries (groth16.cu: Bs2 after Bs1)
+int msm_g2_job_prep0(b200_ctx* ctx, void* job, cudaStream_t st);
 int msm_g2_job_acc(b200_ctx* ctx, void* job, cudaStream_t st, cudaStream_t st_post = nullptr, cudaEvent_t ev_split = nullptr);
 void msm_g2_job_finish(void* job, G2Jac* out_host);
 void msm_g2_job_delete(void* job);
@@ -59,13 +61,15 @@ struct MsmLayout {
     size_t off_digits, off_sorted, off_counts, off_offsets, off_cursor, off_bsums;
     size_t off_ntasks, off_task_off, off_task_bucket, off_order, off_order_hist, off_big, sort_total;
     size_t off_buckets, off_partials, off_S[2], off_W[2], acc_total;
-    size_t total;   // sort_total + acc_total
+    size_t ba_total;   // batched-affine round buffers (offsets off_ba_* are relative to their own base)
+    size_t total;   // sort_total + acc_total + ba_total
     uint32_t scan_blocks, chunk, max_tasks, order_shift, T, logT, Q;
     // batched-affine pre-reduction (msm_ba.cuh): ba rounds, entry slots padded per bucket to 2^ba
     int ba;
     size_t pad_entries;                       // upper bound of the padded slot count (multiple of 2^ba * BA_K)
     size_t off_rcounts, off_roffsets;         // per-bucket counts / offsets after the rounds
-    size_t off_ba_pts[2], off_ba_pref, off_ba_cprod, off_ba_cinv;
+    size_t off_ba_pts[2], off_ba_pref, off_ba_cprod, off_ba_cinv;   // in the batched-affine group
+    size_t off_ba_pref0, off_ba_cprod0;       // in the SORT group: the first round's denominator pass runs with the sort (msm_enqueue_prep0)
     // c_override carries the MSM mode: bits 0-7 the window override, bits 8-11 the batched-affine rounds
     MsmLayout(size_t n_, int c_override, int fold_c) {
         n = n_;
@@ -74,7 +78,7 @@ struct MsmLayout {
         c_override &= 0xff;
         plan = fold_c ? msm_plan_folded(fold_c) : msm_plan(n, c_override);
         M = (size_t)plan.WB * plan.nb;
-        if (!ba_force && ((size_t)plan.W * n < ((size_t)1 << 22) || ((size_t)plan.W * n) / M < ((size_t)8 << ba))) ba = 0;   // too little work per round / per bucket
+        if (!ba_force && ((size_t)plan.W * n < ((size_t)1 << 22) || ((size_t)plan.W * n) / M < ((size_t)2 << ba))) ba = 0;   // too little work per round / per bucket
         pad_entries = (size_t)plan.W * n;
         if (ba) {
             const size_t q = ((size_t)1 << ba) * BA_K;
@@ -108,6 +112,8 @@ struct MsmLayout {
         off_order_hist = a.off; a.take((size_t)ORDER_BINS * 4 * 2);
         off_rcounts = a.off; a.take(ba ? M * 4 : 0);
         off_roffsets = a.off; a.take(ba ? M * 4 : 0);
+        off_ba_pref0 = a.off; a.take(ba ? (pad_entries / 2) * sizeof(F) : 0);
+        off_ba_cprod0 = a.off; a.take(ba ? (pad_entries / 2 / BA_K + 1) * sizeof(F) : 0);
         sort_total = a.off;
         Arena g;
         off_buckets = g.off; g.take(M * sizeof(XYZZ<F>));
@@ -122,13 +128,15 @@ struct MsmLayout {
         // tree ping-pong buffers: WB * Q arrays of T/2 and T/4 points
         off_S[1] = g.off; g.take((size_t)plan.WB * Q * (T / 2 + 1) * sizeof(XYZZ<F>));
         off_W[1] = g.off; g.take((size_t)plan.WB * Q * (T / 4 + 1) * sizeof(XYZZ<F>));
-        off_ba_pts[0] = g.off; g.take(ba ? (pad_entries / 2) * sizeof(Affine<F>) : 0);
-        off_ba_pts[1] = g.off; g.take(ba > 1 ? (pad_entries / 4) * sizeof(Affine<F>) : 0);
-        off_ba_pref = g.off; g.take(ba ? (pad_entries / 2) * sizeof(F) : 0);
-        off_ba_cprod = g.off; g.take(ba ? (pad_entries / 2 / BA_K + 1) * sizeof(F) : 0);
-        off_ba_cinv = g.off; g.take(ba ? (pad_entries / 2 / BA_K + 1) * sizeof(F) : 0);
         acc_total = g.off;
-        total = sort_total + acc_total;
+        Arena q;
+        off_ba_pts[0] = q.off; q.take(ba ? (pad_entries / 2) * sizeof(Affine<F>) : 0);
+        off_ba_pts[1] = q.off; q.take(ba > 1 ? (pad_entries / 4) * sizeof(Affine<F>) : 0);
+        off_ba_pref = q.off; q.take(ba > 1 ? (pad_entries / 4) * sizeof(F) : 0);
+        off_ba_cprod = q.off; q.take(ba > 1 ? (pad_entries / 4 / BA_K + 1) * sizeof(F) : 0);
+        off_ba_cinv = q.off; q.take(ba ? (pad_entries / 2 / BA_K + 1) * sizeof(F) : 0);
+        ba_total = ba ? q.off : 0;
+        total = sort_total + acc_total + ba_total;
     }
     size_t result_points() const { return (size_t)plan.WB * Q; }   // XYZZ values the host finishes from
 };
@@ -145,13 +153,31 @@ struct MsmJob {
     uint32_t stride;
     char* sort_base;
     char* acc_base;
+    char* ba_base;     // batched-affine round buffers (lay.ba_total bytes)
     XYZZ<F>* h_result;   // host staging of lay.result_points() values (page-locked for a truly async copy)
     MsmJob(b200_ctx* ctx, const Affine<F>* bases, const Fr* scalars, const uint32_t* idx_map, size_t n_, const MsmFold* fold,
-           void* sort_ws, void* acc_ws, XYZZ<F>* host_staging)
+           void* sort_ws, void* acc_ws, XYZZ<F>* host_staging, void* ba_ws = nullptr)
         : lay(n_ ? n_ : 1, ctx->msm_mode(), fold ? fold->c : 0), d_bases(bases), d_scalars(scalars), d_idx_map(idx_map), n(n_),
           stride(fold && fold->c ? (uint32_t)fold->stride : 0u), sort_base((char*)sort_ws), acc_base((char*)acc_ws),
-          h_result(host_staging) {}
+          ba_base((char*)ba_ws), h_result(host_staging) {}
 };
+
+// First batched-affine round, denominator pass: needs the sorted entries and the base table only, and is bound by the
+// DRAM's random-access rate with the multiplier idle -- so it is enqueued with the sort (on the stream that runs beside the
+// previous MSM's arithmetic) and leaves pref0 / cprod0 in the sort group.
+template <class F>
+int msm_enqueue_prep0(b200_ctx* ctx, const MsmJob<F>& job, cudaStream_t st) {
+    const MsmLayout<F>& lay = job.lay;
+    if (job.n == 0 || !lay.ba) return B200_OK;
+    char* base = job.sort_base;
+    const uint32_t n_out = (uint32_t)(lay.pad_entries >> 1);
+    const uint32_t threads = n_out / BA_K, blocks = (threads + 127) / 128;
+    ba_prep_kernel<F, true><<<blocks, 128, 0, st>>>(job.d_bases, (const uint32_t*)(base + lay.off_sorted), nullptr, nullptr, threads,
+                                                    (F*)(base + lay.off_ba_pref0), (F*)(base + lay.off_ba_cprod0));
+    B2_CUDA(ctx, cudaGetLastError());
+    ctx->n_launches += 1;
+    return B200_OK;
+}
 
 template <class F>
 int msm_enqueue_sort(b200_ctx* ctx, const MsmJob<F>& job, cudaStream_t st) {
@@ -230,6 +256,7 @@ int msm_enqueue_sort(b200_ctx* ctx, const MsmJob<F>& job, cudaStream_t st) {
         msm_order_fill_kernel<<<ob, ORDER_THREADS, 0, st>>>(task_bucket, task_off, ntasks, rcounts, lay.max_tasks, lay.chunk, lay.order_shift, order_hist, order);
         B2_CUDA(ctx, cudaGetLastError());
     }
+    B2_TRY(msm_enqueue_prep0(ctx, job, st));
     ctx->prof_end(span, st);
     ctx->n_launches += 13;  // digits, 2 x 3 scan, scatter, task count/fill, 3 x order
     return B200_OK;
@@ -265,26 +292,47 @@ int msm_enqueue_acc(b200_ctx* ctx, const MsmJob<F>& job, cudaStream_t st, cudaSt
         const uint32_t *acc_offsets = offsets, *acc_counts = counts;
         if (lay.ba) {
             // pairwise affine rounds: round r turns pad_entries >> r slots into half as many points
-            Affine<F>* pts[2] = {(Affine<F>*)(ab + lay.off_ba_pts[0]), (Affine<F>*)(ab + lay.off_ba_pts[1])};
-            F* pref = (F*)(ab + lay.off_ba_pref);
-            F* cprod = (F*)(ab + lay.off_ba_cprod);
-            F* cinv = (F*)(ab + lay.off_ba_cinv);
+            char* bb = job.ba_base;
+            if (!bb) return ctx->fail(B200_ERR_INTERNAL, "batched-affine rounds without their workspace");
+            Affine<F>* pts[2] = {(Affine<F>*)(bb + lay.off_ba_pts[0]), (Affine<F>*)(bb + lay.off_ba_pts[1])};
+            F *pref = nullptr, *cprod = nullptr;
+            F* cinv = (F*)(bb + lay.off_ba_cinv);
+            // round r reads the base table through the sorted entries (r = 0) or the planes of round r - 1, and writes
+            // planes (x then y) -- the last round (x, y) pairs for msm_accumulate_kernel
+            const F *in_x = nullptr, *in_y = nullptr;
             const Affine<F>* in = job.d_bases;
             for (int r = 0; r < lay.ba; ++r) {
                 const uint32_t n_out = (uint32_t)(lay.pad_entries >> (r + 1));
                 const uint32_t threads = n_out / BA_K, blocks = (threads + 127) / 128;
+                const bool last = r == lay.ba - 1;
                 Affine<F>* out = pts[r & 1];
-                if (r == 0) ba_prep_kernel<F, true><<<blocks, 128, 0, st>>>(in, sorted, n_out, pref, cprod);
-                else ba_prep_kernel<F, false><<<blocks, 128, 0, st>>>(in, nullptr, n_out, pref, cprod);
+                F* out_x = (F*)out;
+                F* out_y = out_x + n_out;
+                if (r == 0) { pref = (F*)(sb + lay.off_ba_pref0); cprod = (F*)(sb + lay.off_ba_cprod0); }   // msm_enqueue_prep0 ran with the sort
+                else {
+                    pref = (F*)(bb + lay.off_ba_pref); cprod = (F*)(bb + lay.off_ba_cprod);
+                    ba_prep_kernel<F, false><<<blocks, 128, 0, st>>>(nullptr, nullptr, in_x, in_y, threads, pref, cprod);
+                    B2_CUDA(ctx, cudaGetLastError());
+                }
+                // thread products per Fermat inversion: as many as keep ~32 K inversion threads busy
+                uint32_t chunk = threads / 32768u;
+                if (chunk < 8u) chunk = 8u;
+                if (chunk > (uint32_t)BA_INV_CHUNK) chunk = (uint32_t)BA_INV_CHUNK;
+                const uint32_t inv_threads = (threads + chunk - 1) / chunk;
+                ba_inverse_kernel<F><<<(inv_threads + 63) / 64, 64, 0, st>>>(cprod, cinv, threads, inv_threads, chunk);
                 B2_CUDA(ctx, cudaGetLastError());
-                const uint32_t inv_threads = (threads + BA_INV_CHUNK - 1) / BA_INV_CHUNK;
-                ba_inverse_kernel<F><<<(inv_threads + 63) / 64, 64, 0, st>>>(cprod, cinv, threads);
-                B2_CUDA(ctx, cudaGetLastError());
-                if (r == 0) ba_apply_kernel<F, true><<<blocks, 128, 0, st>>>(in, sorted, n_out, pref, cinv, out);
-                else ba_apply_kernel<F, false><<<blocks, 128, 0, st>>>(in, nullptr, n_out, pref, cinv, out);
+                if (r == 0) {
+                    if (last) ba_apply_kernel<F, true, true><<<blocks, 128, 0, st>>>(job.d_bases, sorted, nullptr, nullptr, threads, pref, cinv, nullptr, nullptr, out);
+                    else ba_apply_kernel<F, true, false><<<blocks, 128, 0, st>>>(job.d_bases, sorted, nullptr, nullptr, threads, pref, cinv, out_x, out_y, nullptr);
+                } else {
+                    if (last) ba_apply_kernel<F, false, true><<<blocks, 128, 0, st>>>(nullptr, nullptr, in_x, in_y, threads, pref, cinv, nullptr, nullptr, out);
+                    else ba_apply_kernel<F, false, false><<<blocks, 128, 0, st>>>(nullptr, nullptr, in_x, in_y, threads, pref, cinv, out_x, out_y, nullptr);
+                }
                 B2_CUDA(ctx, cudaGetLastError());
                 ctx->n_launches += 3;
                 in = out;
+                in_x = out_x;
+                in_y = out_y;
             }
             acc_bases = in;
             acc_offsets = (const uint32_t*)(sb + lay.off_roffsets);
@@ -387,7 +435,7 @@ int msm_run_impl(b200_ctx* ctx, const Affine<F>* d_bases, const Fr* d_scalars, c
     if (ws) base = (char*)ws;
     else { B2_TRY(ctx_reserve(ctx, lay.total)); base = (char*)ctx->scratch; }
     std::vector<XYZZ<F>> fin(lay.result_points());
-    MsmJob<F> job(ctx, d_bases, d_scalars, d_idx_map, n, fold, base, base + lay.sort_total, fin.data());
+    MsmJob<F> job(ctx, d_bases, d_scalars, d_idx_map, n, fold, base, base + lay.sort_total, fin.data(), base + lay.sort_total + lay.acc_total);
     B2_TRY(msm_enqueue_sort(ctx, job, ctx->stream));
     B2_TRY(msm_enqueue_acc(ctx, job, ctx->stream));
     B2_CUDA(ctx, cudaStreamSynchronize(ctx->stream));

@@ -211,12 +211,13 @@ double now_ms() { return std::chrono::duration<double, std::milli>(std::chrono::
 int commit_many(b200_ctx* ctx, const b200_bases* srs, const Fr* const* coeffs, const size_t* counts, int m, G1XYZZ* out,
                 const cudaEvent_t* wait = nullptr) {
     if (m < 1 || m > 4) return ctx->fail(B200_ERR_ARG, "commit_many: 1..4 polynomials");
-    size_t sort_max = 0, acc_max = 0, res_off[5] = {0};
+    size_t sort_max = 0, acc_max = 0, ba_max = 0, res_off[5] = {0};
     for (int k = 0; k < m; ++k) {
         if (counts[k] > srs->n) return ctx->fail(B200_ERR_ARG, "polynomial longer than the SRS");
         const MsmSizes sz = msm_sizes(counts[k], 1, ctx->msm_mode(), srs->fold.c);
         sort_max = std::max(sort_max, sz.sort_bytes);
         acc_max = std::max(acc_max, sz.acc_bytes);
+        ba_max = std::max(ba_max, sz.ba_bytes);
         res_off[k + 1] = res_off[k] + ((sz.result_bytes + 255) & ~(size_t)255);
     }
     const bool overlap = ctx->msm_overlap != 0 && m > 1;
@@ -224,6 +225,7 @@ int commit_many(b200_ctx* ctx, const b200_bases* srs, const Fr* const* coeffs, c
     const size_t o_sort0 = ar.off; ar.take(sort_max);
     const size_t o_sort1 = overlap ? ar.off : o_sort0; if (overlap) ar.take(sort_max);
     const size_t o_acc = ar.off; ar.take(acc_max);
+    const size_t o_ba = ar.off; ar.take(ba_max);
     B2_TRY(ctx_reserve(ctx, ar.off));
     if (ctx->h_stage_bytes < res_off[m]) {
         if (ctx->h_stage) cudaFreeHost(ctx->h_stage);
@@ -242,7 +244,7 @@ int commit_many(b200_ctx* ctx, const b200_bases* srs, const Fr* const* coeffs, c
     struct JobGuard { void** j; ~JobGuard() { for (int k = 0; k < 4; ++k) if (j[k]) msm_g1_job_delete(j[k]); } } jguard{jobs};
     for (int k = 0; k < m; ++k)
         jobs[k] = msm_g1_job_new(ctx, srs->pts.as<G1Affine>(), coeffs[k], nullptr, counts[k], &srs->fold, sort_ws[overlap ? (k & 1) : 0],
-                                 base + o_acc, (char*)ctx->h_stage + res_off[k]);
+                                 base + o_acc, (char*)ctx->h_stage + res_off[k], base + o_ba);
     B2_CUDA(ctx, cudaEventRecord(ev[0], st));
     if (overlap) B2_CUDA(ctx, cudaStreamWaitEvent(sx, ev[0], 0));
     auto run_sort = [&](int k) -> int {

@@ -1,5 +1,5 @@
 """Batched-affine rounds sweep: device time of one resident-base MSM for msm_ba = 0..5 (results must agree).
-python scripts/ba_sweep.py <group 1|2> <log_n> [per-class profile]"""
+python scripts/ba_sweep.py <group 1|2> <log_n> [rounds, comma separated]"""
 import json, os, sys
 import numpy as np
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
@@ -13,7 +13,8 @@ bh = ctx.upload_bases(ctx.batch_scalar_mul(G1_GEN if group == 1 else G2_GEN, ran
 sv = pkg.DeviceVector(ctx, n * 32).upload(rand_field(rng, n))
 aff = pkg.g1_jac_to_affine if group == 1 else pkg.g2_jac_to_affine
 ref, res = None, {}
-for ba in range(0, 6):
+rounds = [int(x) for x in sys.argv[3].split(",")] if len(sys.argv) > 3 else list(range(0, 6))
+for ba in rounds:
     ctx.set_option("msm_ba", ba)
     ts = []
     for _ in range(4):

@@ -613,8 +613,9 @@ int b200_set_option(b200_ctx* ctx, const char* key, long value) try {
     if (k == "msm_c") { if (value != 0 && (value < 4 || value > 24)) return ctx->fail(B200_ERR_ARG, "msm_c out of range"); ctx->msm_c_override = (int)value; }
     else if (k == "ntt_tile_log") { if (value < 6 || value > 12) return ctx->fail(B200_ERR_ARG, "ntt_tile_log out of range"); ctx->ntt_tile_log = (int)value; }
     else if (k == "ntt_strided_stages") { if (value < 1 || value > 12) return ctx->fail(B200_ERR_ARG, "ntt_strided_stages out of range"); ctx->ntt_strided_stages = (int)value; }
-    else if (k == "msm_ba") { if (value < 0 || value > 9) return ctx->fail(B200_ERR_ARG, "msm_ba out of range"); ctx->msm_ba = (int)value; }
+    else if (k == "msm_ba") { if (value != 15 && (value < 0 || value > 9)) return ctx->fail(B200_ERR_ARG, "msm_ba out of range (0..9 rounds, 15 = automatic)"); ctx->msm_ba = (int)value; }
     else if (k == "msm_ba_force") { ctx->msm_ba_force = value ? 1 : 0; }
+    else if (k == "msm_cap_smem") { if (value < 0 || value > 48 * 1024) return ctx->fail(B200_ERR_ARG, "msm_cap_smem out of range"); ctx->msm_cap_smem = (int)value; }
     else if (k == "msm_acc_smem") { ctx->msm_acc_smem = (int)(value & 3); }
     else if (k == "msm_overlap") { ctx->msm_overlap = value ? 1 : 0; }
     else if (k == "msm_precompute") { ctx->msm_precompute = value ? 1 : 0; }

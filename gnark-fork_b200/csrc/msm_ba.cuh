@@ -32,10 +32,23 @@ constexpr int BA_INV_CHUNK = 128;    // at most this many thread products per Fe
 #if defined(__CUDACC__)
 
 constexpr uint32_t BA_EMPTY = 0xffffffffu;
+#ifndef BA_INLINE_FP2
+#define BA_INLINE_FP2 0   // measured: inlined 15.8 ms per 5.6e7 additions against 13.6 ms with the calls (fma pipe 32 % against 40 %)
+#endif
 #ifndef BA_APPLY_BLOCKS_FP2
 #define BA_APPLY_BLOCKS_FP2 3
 #endif
 #define BA_APPLY_BLOCKS(F) (sizeof(F) > 48 ? BA_APPLY_BLOCKS_FP2 : 1)   // resident blocks asked of ptxas (Fp2: 222 registers otherwise, 2 blocks)
+
+// Products of the round kernels.  Fp2: inlined (Karatsuba with lazy reduction) instead of the out-of-line calls the XYZZ
+// kernels use -- an affine addition has 5 products and a square, its loop body stays inside the instruction cache, and
+// the argument shuffling of a call (IMAD.MOV on the pipe the kernel is bound by) goes away.
+template <class F> __device__ __forceinline__ F ba_mul(const F& a, const F& b) { return a * b; }
+template <class F> __device__ __forceinline__ F ba_sqr(const F& a) { return a.sqr(); }
+#if BA_INLINE_FP2
+template <> __device__ __forceinline__ Fp2 ba_mul<Fp2>(const Fp2& a, const Fp2& b) { return fp2_mul_lazy(a, b); }
+template <> __device__ __forceinline__ Fp2 ba_sqr<Fp2>(const Fp2& a) { return a.sqr_inline(); }
+#endif
 
 // One operand pair of a round.  FIRST: gathered from the (folded) base table through the sorted entries (sign bit =
 // negate, 0xffffffff = empty slot); later rounds: elements 2i, 2i+1 of the previous round's planes.
@@ -137,7 +150,7 @@ __global__ void __launch_bounds__(128) ba_prep_kernel(const Affine<F>* __restric
         F d;
         const Pair pr(table, sorted, xs, ys, e_cur);
         if (ba_denominator<F, FIRST>(pr, &d)) {
-            acc = have ? acc * d : d;
+            acc = have ? ba_mul(acc, d) : d;
             have = true;
         }
         e_cur = e_nxt;
@@ -202,13 +215,13 @@ __global__ void __launch_bounds__(128, BA_APPLY_BLOCKS(F)) ba_apply_kernel(const
             else {
                 const F d = same_x ? P.y.dbl() : Q.x - P.x;
                 F dinv = inv;
-                if (j) { dinv = inv * ld_vec(pref + i); inv = inv * d; }
+                if (j) { dinv = ba_mul(inv, ld_vec(pref + i)); inv = ba_mul(inv, d); }
                 F num;
-                if (same_x) { const F xx = P.x.sqr(); num = xx.dbl() + xx; }      // 3 x^2 (a = 0)
+                if (same_x) { const F xx = ba_sqr(P.x); num = xx.dbl() + xx; }      // 3 x^2 (a = 0)
                 else num = Q.y - P.y;
-                const F lam = num * dinv;
-                R.x = lam.sqr() - P.x - Q.x;
-                R.y = lam * (P.x - R.x) - P.y;
+                const F lam = ba_mul(num, dinv);
+                R.x = ba_sqr(lam) - P.x - Q.x;
+                R.y = ba_mul(lam, P.x - R.x) - P.y;
             }
         }
         if (LAST) st_vec(out_xy + i, R);

@@ -40,6 +40,15 @@ MAC32_PER_G1_POINT = 16 * 11 * 136   # 16 windows x (7M+4S) x 13
 MAC32_PER_G2_POINT = 16 * 29 * 136
 MAC32_PER_G1_MADD = 8 * 136 + 2 * 64 + 72   # executed by XYZZ::add_mixed<Fp> (ec.cuh): 1288
 MAC32_PER_BUTTERFLY = 136
+# batched-affine round (msm_ba.cuh): 5 products + 1 square per addition, + the shared inversion: per 32 additions one thread
+# product that costs 3 products in the inversion kernel and 1/128 of a 380-product Fermat chain
+MAC32_PER_G1_AFFINE_ADD = 6 * 136 + (3 + 380 / 128.0) * 136 / 32.0
+
+
+def g1_executed_mac32_per_point(info):
+    """MAC32 the G1 bucket stage executes per point under the plan of one base set (b200_msm_set_info)."""
+    left = 0.5 ** info.get("ba_rounds", 0)      # share of the additions left for the XYZZ kernel
+    return info["windows"] * ((1.0 - left) * MAC32_PER_G1_AFFINE_ADD + left * MAC32_PER_G1_MADD)
 
 
 def load_pkg():
@@ -625,7 +634,10 @@ def bls12_377_section(pkg, device_index, log_n, steps, warmup, peak, devices=Non
         pts = g1["units"] / max(1, g1["launches"])
         model = pts * 16 * 11 * mac_fp / (g1_launch_ms * 1e-3) if g1_launch_ms else 0.0
         mac_madd = 8 * mac_fp + 2 * 144 + 156     # XYZZ mixed addition: 8 products + a*b - c*d as two wide products and ONE reduction
-        executed = pts * info["a"]["windows"] * mac_madd / (g1_launch_ms * 1e-3) if g1_launch_ms else 0.0
+        ba_r = info["a"].get("ba_rounds", 0)
+        left = 0.5 ** ba_r
+        mac_aff = 6 * mac_fp + (3 + 570 / 128.0) * mac_fp / 32.0      # affine addition with shared inversions (Fermat chain of a 377-bit p: ~570 products)
+        executed = pts * info["a"]["windows"] * ((1 - left) * mac_aff + left * mac_madd) / (g1_launch_ms * 1e-3) if g1_launch_ms else 0.0
         stage = {k: float(np.mean([t[k] for t in tms])) for k in tms[0]}
         return {"metric": "BLS12-377 Groth16 prove s @2^%d constraints" % log_n, "value": float(np.mean(wall)), "unit": "s", "n_gpus": world,
                 "steps": steps, "workload": "synthetic 2^%d-constraint Mul-chain-shaped R1CS on BLS12-377: computeH (7 transforms of 2^%d) + "
@@ -635,12 +647,12 @@ def bls12_377_section(pkg, device_index, log_n, steps, warmup, peak, devices=Non
                 "device_ms": stage["total_ms"], "stage_ms": stage, "verified": bool(ok),
                 "verifier": "refCircuit with its satisfying witness, key from b200_groth16_setup (known toxic waste): every MSM result equals "
                             "[e]G for the discrete log e the witness implies, the verify equation holds in the exponent, host fix-ups checked",
-                "roofline_g1": {"bound": "imad", "kernel": "msm_accumulate_kernel<Fp> (12 limbs)", "launch_ms": g1_launch_ms,
+                "roofline_g1": {"bound": "imad", "kernel": "G1 bucket stage, 12 limbs: %d batched-affine rounds + msm_accumulate_kernel<Fp>" % ba_r, "launch_ms": g1_launch_ms,
                                 "model_mac32_per_s": model, "executed_mac32_per_s": executed, "peak_mac32_per_s": peak["mac32_per_s"],
                                 "frac_model": model / peak["mac32_per_s"], "frac_executed": executed / peak["mac32_per_s"],
                                 "note": "model = points x 16 windows x 11 Fp products x 300 MAC32 (SURVEY.md 8(d)); executed = points x the plan's "
                                         "windows x 2844 MAC32 (XYZZ mixed addition: 8 products x 300 + two 144-MAC32 wide products + one 156-MAC32 reduction)"},
-                "msm_plan": {k: info["a"][k] for k in ("c", "windows", "folded")},
+                "msm_plan": {k: info["a"][k] for k in ("c", "windows", "folded", "ba_rounds")},
                 "gpu_launches_per_proof": int(prof["kernel_launches"] // max(1, steps)), "setup_s": t_setup}
     finally:
         (grp or ctx).close()
@@ -718,21 +730,39 @@ def report(args, world, peak, prof, stage, step_ms, e2e_s, clk, verified, inst, 
     g1_launch_ms = g1["ms"] / max(1, g1["launches"])
     g1_pts = g1["units"] / max(1, g1["launches"])
     g1_mac_s = g1_pts * MAC32_PER_G1_POINT / (g1_launch_ms * 1e-3)
-    roofline = {"kernel": "msm_accumulate_kernel<Fp> (G1 bucket accumulation)", "bound": "imad",
+    ba_rounds = pk_info["a"].get("ba_rounds", 0)
+    exec_pp = g1_executed_mac32_per_point(pk_info["a"])
+    if ba_rounds:
+        kernel = ("G1 bucket stage = %d batched-affine rounds (ba_apply_kernel<Fp> + ba_prep_kernel<Fp> + ba_inverse_kernel<Fp>; the first "
+                  "round's ba_prep_kernel runs with the sort) + msm_accumulate_kernel<Fp> on the 1/%d of the additions that are left" % (ba_rounds, 1 << ba_rounds))
+        # ncu dram__bytes_read.sum + dram__bytes_write.sum over the stage's launches at 2^24 points, 4 rounds (profiles/r02_ba_launches_g1_2p24.csv)
+        traffic = 78.0e9 * g1_pts / 16777216.0 if (ba_rounds == 4 and pk_info["a"]["c"] == 20) else None
+        traffic_source = ("ncu dram__bytes_read.sum + dram__bytes_write.sum summed over the stage's 13 launches at 2^24 points, c = 20, 4 rounds "
+                          "(profiles/r02_ba_launches_g1_2p24.csv: 57.6 GB read + 20.4 GB written), scaled to this launch's points; the table "
+                          "gathers fetch 64-byte halves (ld.global.nc.L2::64B, profiles/r02_gather_probe.txt)")
+        exec_model = (f"{pk_info['a']['windows']} windows of c={pk_info['a']['c']} x [(1 - 1/{1 << ba_rounds}) affine additions with shared inversions "
+                      f"(5 products + 1 square + 0.19 of the inversion kernel = {MAC32_PER_G1_AFFINE_ADD:.0f} MAC32) + 1/{1 << ba_rounds} XYZZ mixed additions (1288 MAC32)]; "
+                      "frac > 1 means fewer field multiplications than the survey's model, not a faster pipe")
+    else:
+        kernel = "msm_accumulate_kernel<Fp> (G1 bucket accumulation)"
+        traffic = (3.77e9 * g1_pts / 4194304.0) if pk_info["a"]["folded"] and pk_info["a"]["c"] == 20 else None
+        traffic_source = ("ncu --set full at 2^22 points (profiles/r01_prof_fold_2p22_raw.csv: 7.54 GB with 128-byte line fetches), halved by the "
+                          "64-byte gather hint of round 2 (profiles/r02_gather_probe.txt), scaled linearly to this launch's points")
+        exec_model = (f"{pk_info['a']['windows']} windows of c={pk_info['a']['c']} "
+                      f"({'folded table' if pk_info['a']['folded'] else 'plain bases'}) x XYZZ mixed add: 8 Montgomery products x 136 "
+                      "+ one a*b - c*d with a shared reduction (2 x 64 + 72) = 1288 MAC32; "
+                      "frac > 1 means fewer field multiplications than the survey's model, not a faster pipe")
+    roofline = {"kernel": kernel, "bound": "imad",
                 "achieved": g1_mac_s / 1e12, "peak": mac_peak / 1e12, "unit": "TMAC32/s", "frac": g1_mac_s / mac_peak,
-                "traffic": (7.536e9 * g1_pts / 4194304.0) if pk_info["a"]["folded"] and pk_info["a"]["c"] == 20 else None,
-                "traffic_source": "ncu --set full at 2^22 points: dram read 7.464 GB + write 0.072 GB per launch "
-                                  "(profiles/r01_prof_fold_2p22_raw.csv), scaled linearly to this launch's points; "
-                                  "2.1x the 64-byte gathers (128-byte lines), at 11 % of DRAM throughput",
+                "traffic": traffic, "traffic_source": traffic_source,
+                "hbm_frac_of_traffic": (traffic / (g1_launch_ms * 1e-3) / 1e9 / hbm_peak) if traffic and g1_launch_ms else None,
                 "launch_ms": g1_launch_ms, "points_per_launch": g1_pts,
+                "launch_ms_note": "CUDA-event span of the stage on the main stream inside the timed region; another MSM's sort runs beside it on the aux stream and stretches it (alone: 24.1 ms at 2^24 points)",
                 "algorithmic_mac32_per_point": MAC32_PER_G1_POINT,
                 "algorithmic_model": "SURVEY 8(d): 16 windows x 11 Fp-mul x 136 MAC32 per point, whatever the kernel executes",
-                "executed_mac32_per_point": pk_info["a"]["windows"] * MAC32_PER_G1_MADD,
-                "executed_frac": g1_pts * pk_info["a"]["windows"] * MAC32_PER_G1_MADD / (g1_launch_ms * 1e-3) / mac_peak,
-                "executed_model": f"{pk_info['a']['windows']} windows of c={pk_info['a']['c']} "
-                                  f"({'folded table' if pk_info['a']['folded'] else 'plain bases'}) x XYZZ mixed add: 8 Montgomery products x 136 "
-                                  "+ one a*b - c*d with a shared reduction (2 x 64 + 72) = 1288 MAC32; "
-                                  "frac > 1 means fewer field multiplications than the survey's model, not a faster pipe",
+                "executed_mac32_per_point": exec_pp,
+                "executed_frac": g1_pts * exec_pp / (g1_launch_ms * 1e-3) / mac_peak,
+                "executed_model": exec_model,
                 "peak_source": "measured in this run: register-resident Montgomery-product chains (b200_imad_peak)"}
     # NTT: north_star's HBM view (64 B per element per pass, 2 passes at <= 2^24) and the IMAD view
     passes_model = 1 if inst.log_n <= 12 else (2 if inst.log_n <= 24 else 3)

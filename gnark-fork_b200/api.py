@@ -47,11 +47,11 @@ class _Timings(C.Structure):
 class _MsmSetInfo(C.Structure):
     """b200_msm_set_info."""
     _fields_ = [("n", C.c_uint64), ("device_bytes", C.c_uint64), ("c", C.c_int32), ("windows", C.c_int32),
-                ("folded", C.c_int32), ("reserved", C.c_int32)]
+                ("folded", C.c_int32), ("ba_rounds", C.c_int32)]
 
     def as_dict(self):
         return {"n": int(self.n), "device_bytes": int(self.device_bytes), "c": int(self.c),
-                "windows": int(self.windows), "folded": int(self.folded)}
+                "windows": int(self.windows), "folded": int(self.folded), "ba_rounds": int(self.ba_rounds)}
 
 
 class _PlonkRowsDesc(C.Structure):

@@ -312,7 +312,8 @@ int b200_bases_free(b200_ctx* ctx, b200_bases* bases) try {
 
 static void fill_set_info(b200_ctx* ctx, size_t n, size_t bytes, const MsmFold& f, b200_msm_set_info* o) {
     const MsmPlan p = f.c ? msm_plan_folded(f.c) : msm_plan(n, ctx->msm_c_override);
-    o->n = n; o->device_bytes = bytes; o->c = p.c; o->windows = p.W; o->folded = p.fold; o->reserved = 0;
+    o->n = n; o->device_bytes = bytes; o->c = p.c; o->windows = p.W; o->folded = p.fold;
+    o->ba_rounds = msm_ba_rounds(n, ctx->msm_mode(), f.c);
 }
 int b200_bases_info(b200_ctx* ctx, const b200_bases* bases, b200_msm_set_info* out) try {
     if (!ctx) return B200_ERR_ARG;

@@ -5,6 +5,7 @@ size_t msm_workspace_bytes(size_t n, int group, int c_override, int fold_c) {
     if (n == 0) return 0;
     return group == 2 ? MsmLayout<Fp2>(n, c_override, fold_c).total : MsmLayout<Fp>(n, c_override, fold_c).total;
 }
+int msm_ba_rounds(size_t n, int c_override, int fold_c) { return n ? MsmLayout<Fp>(n, c_override, fold_c).ba : 0; }
 MsmSizes msm_sizes(size_t n, int group, int c_override, int fold_c) {
     MsmSizes z{0, 0, 0, 0};
     if (n == 0) return z;

@@ -26,6 +26,7 @@ int msm_g2_run(b200_ctx* ctx, const G2Affine* d_bases, const Fr* d_scalars, cons
 // then job_new / job_sort(stream) / job_acc(stream) / [sync] / job_finish / job_delete.
 struct MsmSizes { size_t sort_bytes, acc_bytes, result_bytes, ba_bytes; };   // ba_bytes: batched-affine round buffers (one region serves every MSM of a stream: only one accumulates at a time)
 MsmSizes msm_sizes(size_t n, int group, int c_override, int fold_c);
+int msm_ba_rounds(size_t n, int c_override, int fold_c);   // batched-affine rounds an MSM of n points runs under this mode (the same for G1 and G2)
 void* msm_g1_job_new(b200_ctx* ctx, const G1Affine* d_bases, const Fr* d_scalars, const uint32_t* d_idx_map, size_t n,
                      const MsmFold* fold, void* sort_ws, void* acc_ws, void* host_staging, void* ba_ws = nullptr);
 int msm_g1_job_sort(b200_ctx* ctx, void* job, cudaStream_t st);

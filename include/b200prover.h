@@ -293,7 +293,8 @@ typedef struct b200_msm_set_info {
     int32_t c;             /* window width */
     int32_t windows;       /* signed-digit windows per scalar */
     int32_t folded;        /* 1: precomputed 2^(c w) P table, one shared bucket set */
-    int32_t reserved;
+    int32_t ba_rounds;     /* batched-affine pairwise rounds in front of the XYZZ accumulation (0: none): after them 1/2^rounds of
+                            * the n * windows additions are left for msm_accumulate_kernel */
 } b200_msm_set_info;
 int b200_bases_info(b200_ctx *ctx, const b200_bases *bases, b200_msm_set_info *out);
 /* scalars on the host (copied in) ... */

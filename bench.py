@@ -561,11 +561,15 @@ def gpu_arm(args):
     step_e2e()
     barrier()
     t0 = time.perf_counter()
+    fin_s = 0.0
     for _ in range(args.steps):
         o = step_e2e()
+        t1 = time.perf_counter()
         pkg.groth16_finalize(o, rs[0], rs[1], *vkp)
+        fin_s += time.perf_counter() - t1
     barrier()
     e2e_s = (time.perf_counter() - t0) / args.steps
+    args.finalize_ms = fin_s / args.steps * 1e3
 
     args.plonk_result = None
     pk.free()                           # the folded tables go before the PlonK / BLS12-377 keys come
@@ -797,7 +801,7 @@ def report(args, world, peak, prof, stage, step_ms, e2e_s, clk, verified, inst, 
                               "those spans overlap the others and are stretched by sharing the SMs; they do not add up to the step",
             "g2_acc_frac_of_imad_peak": (g2["units"] * MAC32_PER_G2_POINT / (g2["ms"] * 1e-3) / mac_peak) if g2["ms"] else None,
             "pk_sets": pk_info, "imad_peak": peak, "verified": verified, "verifier": "satisfying witness of the refCircuit; all five MSM results equal [e]G for the discrete logs "
-            "the witness implies under the known toxic waste; verify.go:65-137 holds in the exponent; fix-ups checked (groth16_host)", "setup_s": t_setup, "wall_s_timed_region": wall_dev,
+            "the witness implies under the known toxic waste; verify.go:65-137 holds in the exponent; fix-ups checked (groth16_host)", "setup_s": t_setup, "wall_s_timed_region": wall_dev, "e2e_finalize_ms": getattr(args, "finalize_ms", None),
         },
     }
     if getattr(args, "plonk_result", None):

@@ -23,6 +23,8 @@
 #include <condition_variable>
 #include <mutex>
 #include <thread>
+#include <chrono>
+#include <cstdlib>
 #include "groth16_host.cuh"
 #include "host_group.cuh"
 
@@ -209,8 +211,15 @@ int prove(b200_group* g, const b200_group_groth16_pk* gpk, const uint64_t* a, co
     std::vector<b200_groth16_out> parts(R);
     std::vector<b200_timings> tms(R);
     const bool on_dev = a_dev != nullptr;
+    // B200_TRACE=1: host-side timeline of the call on stderr (thread start, prove core per rank, join, combine)
+    static const bool trace = getenv("B200_TRACE") != nullptr;
+    auto now = [] { return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now().time_since_epoch()).count(); };
+    const double t_enter = now();
+    std::vector<double> t_start(R, 0.0), t_done(R, 0.0);
     int st = run_ranks(g, [&](int r) -> int {
         b200_ctx* ctx = g->ctx[r];
+        t_start[r] = now();
+        struct Done { double* t; decltype(now)* f; ~Done() { *t = (*f)(); } } done{&t_done[r], &now};
         const b200_groth16_pk* pk = gpk->pk[r];
         const uint64_t* wr = on_dev ? (const uint64_t*)w_dev[r] : w;
         if (!gpk->distributed) {      // every rank runs the whole computeH on its own copy of a, b, c
@@ -240,8 +249,14 @@ int prove(b200_group* g, const b200_group_groth16_pk* gpk, const uint64_t* a, co
         return groth16_prove_core(ctx, pk, nullptr, nullptr, nullptr, 0, wr, k_remove, n_remove, nullptr, &parts[r], &tms[r], &hook);
     });
     if (st != B200_OK) return st;
+    const double t_join = now();
     combine(parts, out);
     if (timings) max_timings(tms, timings);
+    if (trace) {
+        fprintf(stderr, "[b200 trace] group prove: join at %.3f ms, combine %.3f ms;", t_join - t_enter, now() - t_join);
+        for (int r = 0; r < R; ++r) fprintf(stderr, " r%d start %.3f core %.3f (device %.3f)", r, t_start[r] - t_enter, t_done[r] - t_start[r], tms[r].total_ms);
+        fprintf(stderr, "\n");
+    }
     return B200_OK;
 }
 

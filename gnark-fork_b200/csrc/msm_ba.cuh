@@ -36,9 +36,16 @@ constexpr uint32_t BA_EMPTY = 0xffffffffu;
 #define BA_INLINE_FP2 0   // measured: inlined 15.8 ms per 5.6e7 additions against 13.6 ms with the calls (fma pipe 32 % against 40 %)
 #endif
 #ifndef BA_APPLY_BLOCKS_FP2
-#define BA_APPLY_BLOCKS_FP2 3
+#define BA_APPLY_BLOCKS_FP2 4
 #endif
-#define BA_APPLY_BLOCKS(F) (sizeof(F) > 48 ? BA_APPLY_BLOCKS_FP2 : 1)   // resident blocks asked of ptxas (Fp2: 222 registers otherwise, 2 blocks)
+#ifndef BA_LOW_LIVENESS_FP2
+#define BA_LOW_LIVENESS_FP2 1
+#endif
+#define BA_LOW_LIVENESS(F) (sizeof(F) > 48 && BA_LOW_LIVENESS_FP2)
+// resident blocks asked of ptxas for ba_apply_kernel.  BN254 Fp2 at 2^24 points (sum of the stage's kernels): 2 blocks (222 registers) 86.9 ms,
+// 3 blocks 76.1, 3 blocks + low-liveness loads 74.9 (no stack), 4 blocks + low-liveness (128 registers, 48 B stack) 72.6, 5 blocks 78.5;
+// 4 blocks WITHOUT the low-liveness loads spill to DRAM: 84.5.  BLS12-377 Fp2 (96-byte elements): 3 blocks.
+#define BA_APPLY_BLOCKS(F) (sizeof(F) == 64 ? BA_APPLY_BLOCKS_FP2 : sizeof(F) > 64 ? 3 : 1)
 
 // Products of the round kernels.  Fp2: inlined (Karatsuba with lazy reduction) instead of the out-of-line calls the XYZZ
 // kernels use -- an affine addition has 5 products and a square, its loop body stays inside the instruction cache, and
@@ -96,6 +103,30 @@ struct BaPair {
             return (e >> 31) ? v.neg() : v;
         }
         return ld_vec(ys + e);
+    }
+    // The same coordinate read AGAIN where the formula uses it (low-liveness path of ba_apply_kernel): volatile, so that the
+    // compiler cannot merge it with the earlier load and keep 16 words live across the out-of-line products.  It hits
+    // L1 / L2 -- the line was fetched a few hundred instructions ago.
+    static __device__ __forceinline__ F reload(const F* p) {
+        F r;
+        const uint4* s = reinterpret_cast<const uint4*>(p);
+        uint4* d = reinterpret_cast<uint4*>(&r);
+#pragma unroll
+        for (int i = 0; i < (int)(sizeof(F) / 16); ++i)
+            asm volatile("ld.global.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(d[i].x), "=r"(d[i].y), "=r"(d[i].z), "=r"(d[i].w) : "l"(s + i) : "memory");
+        return r;
+    }
+    __device__ __forceinline__ F x_again(int k) const {
+        const uint32_t e = k ? e1 : e0;
+        return FIRST ? reload(&table[e & 0x7fffffffu].x) : reload(xs + e);
+    }
+    __device__ __forceinline__ F y_again(int k) const {
+        const uint32_t e = k ? e1 : e0;
+        if (FIRST) {
+            const F v = reload(&table[e & 0x7fffffffu].y);
+            return (e >> 31) ? v.neg() : v;
+        }
+        return reload(ys + e);
     }
     __device__ __forceinline__ Affine<F> point(int k) const {
         const uint32_t e = k ? e1 : e0;
@@ -204,8 +235,30 @@ __global__ void __launch_bounds__(128, BA_APPLY_BLOCKS(F)) ba_apply_kernel(const
         const Pair pr(table, sorted, xs, ys, e_cur);
         e_cur = e_nxt;
         e_nxt = e_far;
-        const Affine<F> P = pr.point(0), Q = pr.point(1);
         Affine<F> R;
+        if (BA_LOW_LIVENESS(F)) {
+            // Fp2: a coordinate is 16 words; holding P and Q through five out-of-line products is what pushed the kernel to
+            // 222 registers (168 + stack at 3 resident blocks).  Here every coordinate is loaded where it is consumed.
+            F d;
+            const int kind = ba_denominator<F, FIRST>(pr, &d);        // the same decision ba_prep_kernel took
+            if (kind == 0) {
+                const Affine<F> P = pr.point(0), Q = pr.point(1);
+                R = P.is_inf() ? Q : (Q.is_inf() ? P : Affine<F>::inf());
+            } else {
+                F dinv = inv;
+                if (j) { dinv = ba_mul(inv, ld_vec(pref + i)); inv = ba_mul(inv, d); }
+                F num;
+                if (kind == 2) { const F xx = ba_sqr(pr.x_again(0)); num = xx.dbl() + xx; }
+                else num = pr.y_again(1) - pr.y_again(0);
+                const F lam = ba_mul(num, dinv);
+                R.x = ba_sqr(lam) - pr.x_again(0) - pr.x_again(1);
+                R.y = ba_mul(lam, pr.x_again(0) - R.x) - pr.y_again(0);
+            }
+            if (LAST) st_vec(out_xy + i, R);
+            else { st_vec(out_x + i, R.x); st_vec(out_y + i, R.y); }
+            continue;
+        }
+        const Affine<F> P = pr.point(0), Q = pr.point(1);
         const bool p_inf = P.is_inf(), q_inf = Q.is_inf();
         if (p_inf) R = Q;                            // no division: the running inverse is unchanged
         else if (q_inf) R = P;

@@ -244,6 +244,7 @@ def load_library(curve: int = BN254):
         "b200_g1_jac_to_affine": (i, [vp, vp]),
         "b200_g2_jac_to_affine": (i, [vp, vp]),
         "b200_batch_scalar_mul": (i, [vp, i, i, vp, vp, sz, vp]),
+        "b200_kzg_to_lagrange_g1": (i, [vp, i, vp, C.c_uint, vp, vp]),
         "b200_groth16_pk_upload": (i, [vp, i, C.POINTER(_PkDesc), C.POINTER(vp)]),
         "b200_groth16_pk_free": (i, [vp, vp]),
         "b200_groth16_setup": (i, [vp, i, C.POINTER(_SETUP[curve][0]), C.POINTER(vp), C.POINTER(_SETUP[curve][1])]),
@@ -692,6 +693,16 @@ class Context:
         w = (2 if group == 1 else 4) * self.fw
         out = np.zeros((s.shape[0], w), dtype=np.uint64)
         self._check(self.lib.b200_batch_scalar_mul(self.h, self.curve, group, _ptr(_u64(base)), _ptr(s), s.shape[0], _ptr(out)))
+        return out
+
+    def kzg_to_lagrange_g1(self, srs_g1, generator):
+        """kzg.ToLagrangeG1 (plonk setup.go:134): [L_i(tau)]G1 from the monomial SRS [tau^j]G1, j < n = 2^k, without tau."""
+        pts = _u64(srs_g1, (-1, 2 * self.fw))
+        n = pts.shape[0]
+        if n == 0 or n & (n - 1):
+            raise B200Error("ToLagrangeG1 takes a power-of-two number of points")
+        out = np.zeros_like(pts)
+        self._check(self.lib.b200_kzg_to_lagrange_g1(self.h, self.curve, _ptr(pts), n.bit_length() - 1, _ptr(_u64(generator)), _ptr(out)))
         return out
 
     # -- Groth16

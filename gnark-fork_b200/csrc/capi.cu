@@ -394,6 +394,15 @@ int b200_batch_scalar_mul(b200_ctx* ctx, int curve, int group, const uint64_t* b
     return B200_OK;
 } B2_ABI_CATCH_CTX(ctx)
 
+int b200_kzg_to_lagrange_g1(b200_ctx* ctx, int curve, const uint64_t* srs_g1_affine, unsigned log_n, const uint64_t* generator,
+                            uint64_t* out_affine) try {
+    B2_ENTER(ctx, curve);
+    if (!srs_g1_affine || !generator || !out_affine) return ctx->fail(B200_ERR_ARG, "null argument");
+    Fr gen;
+    memcpy(gen.l, generator, sizeof gen.l);
+    return kzg_to_lagrange_g1(ctx, srs_g1_affine, log_n, gen, out_affine);
+} B2_ABI_CATCH_CTX(ctx)
+
 // ---- Groth16 -----------------------------------------------------------------------------
 int b200_groth16_pk_upload(b200_ctx* ctx, int curve, const b200_groth16_pk_desc* desc, b200_groth16_pk** out) try {
     B2_ENTER(ctx, curve);
@@ -616,7 +625,6 @@ int b200_set_option(b200_ctx* ctx, const char* key, long value) try {
     else if (k == "ntt_strided_stages") { if (value < 1 || value > 12) return ctx->fail(B200_ERR_ARG, "ntt_strided_stages out of range"); ctx->ntt_strided_stages = (int)value; }
     else if (k == "msm_ba") { if (value != 15 && (value < 0 || value > 9)) return ctx->fail(B200_ERR_ARG, "msm_ba out of range (0..9 rounds, 15 = automatic)"); ctx->msm_ba = (int)value; }
     else if (k == "msm_ba_force") { ctx->msm_ba_force = value ? 1 : 0; }
-    else if (k == "msm_cap_smem") { if (value < 0 || value > 48 * 1024) return ctx->fail(B200_ERR_ARG, "msm_cap_smem out of range"); ctx->msm_cap_smem = (int)value; }
     else if (k == "msm_acc_smem") { ctx->msm_acc_smem = (int)(value & 3); }
     else if (k == "msm_overlap") { ctx->msm_overlap = value ? 1 : 0; }
     else if (k == "msm_precompute") { ctx->msm_precompute = value ? 1 : 0; }

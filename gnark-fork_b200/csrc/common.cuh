@@ -38,8 +38,6 @@ struct b200_ctx {
     std::vector<uint32_t> kmap_host;        // K wire map of the proof in flight (api.Commit circuits, groth16.cu)
     int msm_c_override = 0;                 // tuning knobs (b200_set_option / B200_MSM_C env)
     int msm_ba = 15;                        // batched-affine pre-reduction rounds (msm_ba.cuh); 0 = off, 15 = chosen from the mean bucket load
-    int msm_cap_smem = 0;                   // bytes of dynamic shared memory asked for by the main-stream MSM kernels: caps their resident blocks per SM so that the
-                                            // sort / first denominator pass of the next MSM (aux stream) find room beside them (48 KiB -> at most 4 blocks)
     int msm_ba_force = 0;                   // tests: keep the rounds on MSMs too small to profit
     int msm_mode() const { return (msm_c_override & 0xff) | ((msm_ba & 0xf) << 8) | (msm_ba_force ? 0x1000 : 0); }   // what MsmLayout decodes
     int msm_precompute = 1;                 // build folded-window tables for resident base sets

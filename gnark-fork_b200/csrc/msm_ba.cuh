@@ -33,7 +33,7 @@ constexpr int BA_INV_CHUNK = 128;    // at most this many thread products per Fe
 
 constexpr uint32_t BA_EMPTY = 0xffffffffu;
 #ifndef BA_INLINE_FP2
-#define BA_INLINE_FP2 0   // measured: inlined 15.8 ms per 5.6e7 additions against 13.6 ms with the calls (fma pipe 32 % against 40 %)
+#define BA_INLINE_FP2 0   // measured twice (3 blocks; 4 blocks with the low-liveness loads): inlined 15.6-15.8 ms per 5.6e7 additions against 12.8-13.6 ms with the calls (fma pipe 33 % against 42 %: the loop body leaves the instruction cache)
 #endif
 #ifndef BA_APPLY_BLOCKS_FP2
 #define BA_APPLY_BLOCKS_FP2 4

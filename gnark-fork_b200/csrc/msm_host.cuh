@@ -299,7 +299,6 @@ int msm_enqueue_acc(b200_ctx* ctx, const MsmJob<F>& job, cudaStream_t st, cudaSt
         const int bs = 128;
         span = ctx->prof_begin(ACC_SLOT, (double)n, st);
         const Affine<F>* acc_bases = job.d_bases;
-        const size_t cap = (size_t)ctx->msm_cap_smem;
         const uint32_t *acc_offsets = offsets, *acc_counts = counts;
         if (lay.ba) {
             // pairwise affine rounds: round r turns pad_entries >> r slots into half as many points
@@ -322,7 +321,7 @@ int msm_enqueue_acc(b200_ctx* ctx, const MsmJob<F>& job, cudaStream_t st, cudaSt
                 if (r == 0) { pref = (F*)(sb + lay.off_ba_pref0); cprod = (F*)(sb + lay.off_ba_cprod0); }   // msm_enqueue_prep0 ran with the sort
                 else {
                     pref = (F*)(bb + lay.off_ba_pref); cprod = (F*)(bb + lay.off_ba_cprod);
-                    ba_prep_kernel<F, false><<<blocks, 128, cap, st>>>(nullptr, nullptr, in_x, in_y, threads, pref, cprod);
+                    ba_prep_kernel<F, false><<<blocks, 128, 0, st>>>(nullptr, nullptr, in_x, in_y, threads, pref, cprod);
                     B2_CUDA(ctx, cudaGetLastError());
                 }
                 // thread products per Fermat inversion: as many as keep ~32 K inversion threads busy
@@ -333,11 +332,11 @@ int msm_enqueue_acc(b200_ctx* ctx, const MsmJob<F>& job, cudaStream_t st, cudaSt
                 ba_inverse_kernel<F><<<(inv_threads + 63) / 64, 64, 0, st>>>(cprod, cinv, threads, inv_threads, chunk);
                 B2_CUDA(ctx, cudaGetLastError());
                 if (r == 0) {
-                    if (last) ba_apply_kernel<F, true, true><<<blocks, 128, cap, st>>>(job.d_bases, sorted, nullptr, nullptr, threads, pref, cinv, nullptr, nullptr, out);
-                    else ba_apply_kernel<F, true, false><<<blocks, 128, cap, st>>>(job.d_bases, sorted, nullptr, nullptr, threads, pref, cinv, out_x, out_y, nullptr);
+                    if (last) ba_apply_kernel<F, true, true><<<blocks, 128, 0, st>>>(job.d_bases, sorted, nullptr, nullptr, threads, pref, cinv, nullptr, nullptr, out);
+                    else ba_apply_kernel<F, true, false><<<blocks, 128, 0, st>>>(job.d_bases, sorted, nullptr, nullptr, threads, pref, cinv, out_x, out_y, nullptr);
                 } else {
-                    if (last) ba_apply_kernel<F, false, true><<<blocks, 128, cap, st>>>(nullptr, nullptr, in_x, in_y, threads, pref, cinv, nullptr, nullptr, out);
-                    else ba_apply_kernel<F, false, false><<<blocks, 128, cap, st>>>(nullptr, nullptr, in_x, in_y, threads, pref, cinv, out_x, out_y, nullptr);
+                    if (last) ba_apply_kernel<F, false, true><<<blocks, 128, 0, st>>>(nullptr, nullptr, in_x, in_y, threads, pref, cinv, nullptr, nullptr, out);
+                    else ba_apply_kernel<F, false, false><<<blocks, 128, 0, st>>>(nullptr, nullptr, in_x, in_y, threads, pref, cinv, out_x, out_y, nullptr);
                 }
                 B2_CUDA(ctx, cudaGetLastError());
                 ctx->n_launches += 3;
@@ -353,7 +352,7 @@ int msm_enqueue_acc(b200_ctx* ctx, const MsmJob<F>& job, cudaStream_t st, cudaSt
             msm_accumulate_smem_kernel<F><<<(lay.max_tasks + bs - 1) / bs, bs, 0, st>>>(acc_bases, sorted, acc_offsets, acc_counts, task_bucket, task_off,
                                                                                      ntasks, order, lay.max_tasks, lay.chunk, buckets, partials, lay.ba ? 1u : 0u);
         else
-        msm_accumulate_kernel<F><<<(lay.max_tasks + bs - 1) / bs, bs, cap, st>>>(acc_bases, sorted, acc_offsets, acc_counts, task_bucket, task_off,
+        msm_accumulate_kernel<F><<<(lay.max_tasks + bs - 1) / bs, bs, 0, st>>>(acc_bases, sorted, acc_offsets, acc_counts, task_bucket, task_off,
                                                                             ntasks, order, lay.max_tasks, lay.chunk, buckets, partials, lay.ba ? 1u : 0u);
         ctx->prof_end(span, st);
         B2_CUDA(ctx, cudaGetLastError());

@@ -91,6 +91,9 @@ def _to_regular_canonical(ctx: Context, lagrange: np.ndarray, d: Domains, br: np
     return out[br]
 
 
+LAGRANGE_FROM_POINTS_MAX_LOG = 16      # b200_kzg_to_lagrange_g1: n log n / 2 scalar multiplications (0.06 s at 2^16, ~4.5 s at 2^22)
+
+
 def setup(ctx: Context, d: Domains, trace_lagrange: dict, lro: np.ndarray, nb_variables: int, nb_public: int, tau: int) -> dict:
     """Returns the keyword arguments of Context.plonk_pk_upload plus 'vk' (the 8 commitments, (8, 8) affine)
     and 'perm'.  trace_lagrange: ql qr qm qo qk as (n, 4) Montgomery arrays in Lagrange / regular form."""
@@ -103,9 +106,15 @@ def setup(ctx: Context, d: Domains, trace_lagrange: dict, lro: np.ndarray, nb_va
         pw.append(acc)
         acc = acc * tau % R_MOD
     mono = to_mont_array(pw)
-    lag = ctx.ntt(mono[:n], log_n, True, DIF, False, gen_l, cg_l)[br]
     kzg = ctx.batch_scalar_mul(G1_GEN, mono, 1)
-    kzg_lag = ctx.batch_scalar_mul(G1_GEN, lag, 1)
+    if log_n <= LAGRANGE_FROM_POINTS_MAX_LOG:
+        # setup.go:134 as the reference does it: from the SRS POINTS (kzg.ToLagrangeG1), tau not used
+        kzg_lag = ctx.kzg_to_lagrange_g1(kzg[:n], gen_l)
+    else:
+        # large test keys: L(tau) = F^-1 (tau^j) on the scalar side, then the fixed-base kernel (needs tau; same points --
+        # tests/test_gpu_kzg_lagrange.py compares the two routes)
+        lag = ctx.ntt(mono[:n], log_n, True, DIF, False, gen_l, cg_l)[br]
+        kzg_lag = ctx.batch_scalar_mul(G1_GEN, lag, 1)
     # support of the permutation: w^i | g w^i | g^2 w^i  (getSupportPermutation, setup.go:398-415)
     e1 = np.zeros((n, 4), dtype=np.uint64)
     e1[1] = fr_limbs(1)

@@ -105,6 +105,7 @@ extern "C" {
 #define b200_imad_peak b200_bls12377_imad_peak
 #define b200_init b200_bls12377_init
 #define b200_kzg_commit_dev b200_bls12377_kzg_commit_dev
+#define b200_kzg_to_lagrange_g1 b200_bls12377_kzg_to_lagrange_g1
 #define b200_last_error b200_bls12377_last_error
 #define b200_msm_dev b200_bls12377_msm_dev
 #define b200_msm_g1 b200_bls12377_msm_g1
@@ -316,6 +317,15 @@ int b200_g2_jac_to_affine(const uint64_t *p_jac, uint64_t *out_affine);
  * Used to build large synthetic proving keys without Go. */
 int b200_batch_scalar_mul(b200_ctx *ctx, int curve, int group, const uint64_t *base_affine,
                           const uint64_t *scalars, size_t n, uint64_t *out_affine);
+
+/* kzg.ToLagrangeG1 (gnark-crypto kzg, as called by plonk Setup: /root/reference/backend/plonk/bn254/setup.go:134
+ * `pk.KzgLagrange.G1, err = kzg.ToLagrangeG1(kzgSrs.Pk.G1[:int(vk.Size)])`): the SRS in Lagrange form,
+ * out[i] = [L_i(tau)]G1, from the monomial SRS srs_g1_affine[j] = [tau^j]G1, j < 2^log_n, without knowing tau -- the
+ * inverse DFT of the SRS as a vector of group elements (radix-2 DIF over the group with the inverse twiddles, bit
+ * reversal, scaling by 1/n).  generator: the domain's Generator (fft.NewDomain(2^log_n)), Montgomery form.  Host
+ * pointers, affine points in and out.   */
+int b200_kzg_to_lagrange_g1(b200_ctx *ctx, int curve, const uint64_t *srs_g1_affine, unsigned log_n,
+                            const uint64_t *generator, uint64_t *out_affine);
 
 /* ---- Groth16 ---------------------------------------------------------------------------------
  * One-time residency of the proving key (setupDevicePointers, icicle.go:31-130).  All pointers are

@@ -292,6 +292,31 @@ def srs_scalars(pk: ProvingKey):
     return mono, lag
 
 
+def to_lagrange_g1(points, d: N.Domain, curve=B):
+    """kzg.ToLagrangeG1 as setup.go:134 calls it (gnark-crypto kzg, restated; module absent): copy the monomial SRS
+    [tau^j]G1, radix-2 DIF over the GROUP with the domain's inverse twiddles (a' = a + b, b' = [w^-k](a - b)), bit-reverse,
+    scale every point by 1/n.  Works on points only -- tau is not an input.  points: affine tuples or None (infinity)."""
+    n = len(points)
+    assert n == d.cardinality
+    a = list(points)
+    m, ws = n, d.generator_inv
+    while m >= 2:
+        h = m >> 1
+        tw = [1] * h
+        for j in range(1, h):
+            tw[j] = tw[j - 1] * ws % R
+        for base in range(0, n, m):
+            for j in range(h):
+                u, v = a[base + j], a[base + j + h]
+                a[base + j] = curve.g1_add(u, v)
+                diff = curve.g1_add(u, curve.g1_neg(v))
+                a[base + j + h] = diff if j == 0 else curve.g1_mul(diff, tw[j])
+        ws = ws * ws % R
+        m = h
+    N.bit_reverse(a)
+    return [curve.g1_mul(p, d.cardinality_inv) for p in a]
+
+
 # ---------------------------------------------------------------------------------------------
 # Fiat-Shamir (gnark-crypto fiat-shamir.Transcript; byte layout pinned by solidity.go, see header)
 # ---------------------------------------------------------------------------------------------

@@ -6,6 +6,7 @@
   * computeH itself (prove.go:353-396) at 2^22 and 2^24, with n_constraints < n;
   * G1 MultiExp (prove.go:201-244) at 2^20 and 2^22 and G2 MultiExp (:290) at 2^20 against the oracle's
     Pippenger, one-shot path and resident folded-window path, points compared after affine normalisation;
+  * the top of config 2's transform sweep, 2^26 (two variants);
   * the same on BLS12-377 (config 5): transforms and computeH at 2^22, G1 MSM at 2^20, G2 at 2^18.
 
 The bases are [k_i]G from the device's fixed-base kernel; a slice of them is checked against the oracle's
@@ -34,6 +35,20 @@ def test_ntt_variants_vs_oracle_at_baseline_sizes(ctx, cref, log_n):
         got = ctx.ntt(x, log_n, inverse, dec, coset, gen, cg)
         want = cref.ntt(x, log_n, inverse, dec, coset, gen, cg)
         assert np.array_equal(got, want), (log_n, inverse, dec, coset)
+        del got, want
+
+
+def test_ntt_2p26_vs_oracle(ctx, cref):
+    """The top of config 2's sweep (2^16 ... 2^26): three passes on the device; the two transforms computeH is made of."""
+    log_n = 26
+    rng = np.random.default_rng(26)
+    x = rand_field(rng, 1 << log_n)
+    d = N.Domain(1 << log_n)
+    gen, cg = cref.fr(d.generator), cref.fr(d.coset_gen)
+    for inverse, dec, coset in [(1, 0, 0), (0, 1, 1)]:
+        got = ctx.ntt(x, log_n, inverse, dec, coset, gen, cg)
+        want = cref.ntt(x, log_n, inverse, dec, coset, gen, cg)
+        assert np.array_equal(got, want), (inverse, dec, coset)
         del got, want
 
 

@@ -44,3 +44,20 @@ def test_divide_by_xn_minus_one_is_exact_division():
     N.fft(ev, d_big, N.DIF, on_coset=True)                     # canonical regular -> LagrangeCoset bit-reversed
     got = P.divide_by_xn_minus_one(ev, d_small, d_big)
     assert got == h + [0] * 12
+
+
+def test_to_lagrange_g1_restatement_matches_the_definition():
+    """oracle/plonk_prove.to_lagrange_g1 (kzg.ToLagrangeG1 as setup.go:134 calls it: a DIF over group elements, no tau)
+    against the definition out[i] = [L_i(tau)]G1 with L(tau) = F^-1 (tau^j) from the scalar transform."""
+    from oracle import bn254 as B
+    from oracle import ntt as N
+    from oracle import plonk_prove as PP
+    for n, tau in ((1, 7), (2, 11), (8, 123456789)):
+        d = N.Domain(n)
+        mono = [pow(tau, j, B.R) for j in range(n)]
+        lag = list(mono)
+        N.fft_inverse(lag, d, N.DIF)
+        N.bit_reverse(lag)
+        got = PP.to_lagrange_g1([B.g1_mul(B.G1_GEN, m) for m in mono], d)
+        assert got == [B.g1_mul(B.G1_GEN, x) for x in lag]
+        assert sum(lag) % B.R == 1      # partition of unity

@@ -35,6 +35,9 @@ namespace b200 {
 // R2 = 2^512 mod p.
 // ---------------------------------------------------------------------------------------
 #if defined(B2_CURVE_BLS12_377)
+#if defined(__CUDACC__)
+static __constant__ uint32_t b2_opaque_inv = 0xffffffffu;   // see FpParams::inv_dev
+#endif
 // BLS12-377 (BASELINE.json config 5; p and r pinned in the reference at std/math/emulated/emparams/emparams.go:123,137):
 // Fp has 12 x 32-bit limbs (377 bits, R = 2^384), Fr 8 limbs (253 bits, R = 2^256).  Built as a second library from
 // the same sources with -DB2_CURVE_BLS12_377.
@@ -72,6 +75,16 @@ struct FpParams {
         return v[i];
     }
     static constexpr uint32_t INV = 0xffffffffu;
+    // Device code reads INV through constant memory: with the literal 0xffffffff ptxas rewrites m = t0 * INV as -t0 and
+    // the m * p rows no longer match its mad.lo.cc / madc.hi.cc -> IMAD.WIDE pattern -- every pair became IMAD.X +
+    // IMAD.HI.X (424 multiplier instructions per 12-limb product instead of 303; cuobjdump, profiles/r02_sass_histograms.txt)
+    B2_D static uint32_t inv_dev() {
+#if defined(__CUDA_ARCH__)
+        return b2_opaque_inv;
+#else
+        return INV;
+#endif
+    }
 };
 
 struct FrParams {
@@ -92,6 +105,16 @@ struct FrParams {
         return v[i];
     }
     static constexpr uint32_t INV = 0xffffffffu;
+    // Device code reads INV through constant memory: with the literal 0xffffffff ptxas rewrites m = t0 * INV as -t0 and
+    // the m * p rows no longer match its mad.lo.cc / madc.hi.cc -> IMAD.WIDE pattern -- every pair became IMAD.X +
+    // IMAD.HI.X (424 multiplier instructions per 12-limb product instead of 303; cuobjdump, profiles/r02_sass_histograms.txt)
+    B2_D static uint32_t inv_dev() {
+#if defined(__CUDA_ARCH__)
+        return b2_opaque_inv;
+#else
+        return INV;
+#endif
+    }
 };
 
 #else
@@ -113,6 +136,7 @@ struct FpParams {
         return v[i];
     }
     static constexpr uint32_t INV = 0xe4866389u;
+    B2_D static uint32_t inv_dev() { return INV; }
     // p^2 (16 words): added to a difference of wide products to keep it non-negative (Fp2 lazy reduction)
     B2_HD static constexpr uint32_t p_squared(int i) {
         constexpr uint32_t v[16] = {0x275d69b1u, 0x3b5458a2u, 0x09eac101u, 0xa602072du, 0x6d96cadcu, 0x4a50189cu, 0x7a1242c8u, 0x04689e95u, 0x34c6b38du, 0x26edfa5cu, 0x16375606u, 0xb00b8551u, 0x0348d21cu, 0x599a6f7cu, 0x763cbf9cu, 0x0925c4b8u};
@@ -138,6 +162,7 @@ struct FrParams {
         return v[i];
     }
     static constexpr uint32_t INV = 0xefffffffu;
+    B2_D static uint32_t inv_dev() { return INV; }
 };
 
 #endif
@@ -227,7 +252,7 @@ B2_D void mont_mul_dev(uint32_t* r, const uint32_t* a, const uint32_t* b) {
             asm("mul.lo.u32 %0, %2, %3;\n\tmul.hi.u32 %1, %2, %3;" : "=r"(e[j]), "=r"(e[j + 1]) : "r"(a[j]), "r"(y));
             asm("mul.lo.u32 %0, %2, %3;\n\tmul.hi.u32 %1, %2, %3;" : "=r"(o[j]), "=r"(o[j + 1]) : "r"(a[j + 1]), "r"(y));
         }
-        const uint32_t m = e[0] * PRM::INV;
+        const uint32_t m = e[0] * PRM::inv_dev();
         mad_chain8(o, PRM::p(1), PRM::p(3), PRM::p(5), PRM::p(7), m);
         mad_chain8_top<true>(e, PRM::p(0), PRM::p(2), PRM::p(4), PRM::p(6), m);
     }
@@ -239,7 +264,7 @@ B2_D void mont_mul_dev(uint32_t* r, const uint32_t* a, const uint32_t* b) {
 #pragma unroll
         for (int k = 1; k < 8; ++k) ne[k] = o[k];
         mad_chain8_top<true>(ne, a[0], a[2], a[4], a[6], y);
-        const uint32_t m = ne[0] * PRM::INV;
+        const uint32_t m = ne[0] * PRM::inv_dev();
         mad_chain8(no, PRM::p(1), PRM::p(3), PRM::p(5), PRM::p(7), m);
         mad_chain8_top<false>(ne, PRM::p(0), PRM::p(2), PRM::p(4), PRM::p(6), m);
 #pragma unroll
@@ -386,7 +411,7 @@ B2_D void fold_reduce_shift8(uint32_t& ne0, uint32_t& m, uint32_t* no, const uin
         : "=&r"(ne0), "=&r"(no[0]), "=&r"(no[1]), "=&r"(no[2]), "=&r"(no[3]), "=&r"(no[4]),
           "=&r"(no[5]), "=&r"(no[6]), "=&r"(no[7]), "=&r"(m)
         : "r"(o0), "r"(e[1]), "r"(e[2]), "r"(e[3]), "r"(e[4]), "r"(e[5]), "r"(e[6]), "r"(e[7]),
-          "r"(e[8]), "r"(PRM::p(1)), "r"(PRM::p(3)), "r"(PRM::p(5)), "r"(PRM::p(7)), "r"(PRM::INV));
+          "r"(e[8]), "r"(PRM::p(1)), "r"(PRM::p(3)), "r"(PRM::p(5)), "r"(PRM::p(7)), "r"(PRM::inv_dev()));
 }
 
 // r = t / 2^256 mod p for t = t_lo + 2^256 t_hi < p * 2^256  (r < p)
@@ -396,7 +421,7 @@ B2_D void mont_reduce_dev(uint32_t* r, const uint32_t* t) {
 #pragma unroll
     for (int k = 0; k < 8; ++k) e[k] = t[k];
     {
-        const uint32_t m = e[0] * PRM::INV;
+        const uint32_t m = e[0] * PRM::inv_dev();
 #pragma unroll
         for (int j = 0; j < 8; j += 2)
             asm("mul.lo.u32 %0, %2, %3;\n\tmul.hi.u32 %1, %2, %3;" : "=r"(o[j]), "=r"(o[j + 1]) : "r"(PRM::p(j + 1)), "r"(m));

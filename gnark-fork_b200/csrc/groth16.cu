@@ -3,6 +3,7 @@
 // on /root/reference/backend/groth16/bn254/icicle/icicle.go:31-130,196-393), plus the host-side
 // fix-ups (prove.go:178-321) and Proof.WriteTo (marshal.go:41-66) for callers without Go.
 #include <algorithm>
+#include <cstdlib>
 #include "groth16_host.cuh"
 #include "misc_host.cuh"
 
@@ -375,21 +376,34 @@ int groth16_prove_core(b200_ctx* ctx, const b200_groth16_pk* pk, const uint64_t*
     B2_CUDA(ctx, cudaEventRecord(ev[6], st));   // placeholders when computeH is skipped (h supplied)
     B2_CUDA(ctx, cudaEventRecord(ev[7], st));
     if (h_first) B2_TRY(run_h());
+    // Host-buffer proofs: computeH waits for a, b, c to cross PCIe behind W.  On one GPU the first MSM covers that copy;
+    // in a device group every rank's MSMs are 1/R as long while the ranks share the host's memory system for their
+    // copies, so computeH moves behind more of them (h_pos).  The sort of Z, the only consumer of h, comes after all of them.
+    const bool late_h = (own_h || hook) && !h_first;
+    int h_pos = ctx->h_pos;
+    {
+        static const char* e = getenv("B200_H_POS");
+        if (e && *e) h_pos = atoi(e);
+    }
+    if (h_pos < 0 || h_pos > 2) h_pos = 2;   // measured: e2e 0.2463 -> 0.2445 s on one GPU, 43.5 -> 42.7 ms on eight (positions 1 and 2 equal there)
+    cudaEvent_t stage_start[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};   // != null: the stage starts at the end of computeH
     if (overlap) {
         B2_TRY(run_sort(0));
         B2_TRY(run_sort(1));
         B2_TRY(run_acc(0));
-        if ((own_h || hook) && !h_first) B2_TRY(run_h());
+        if (late_h && h_pos == 0) { B2_TRY(run_h()); stage_start[1] = ev[7]; }
         B2_TRY(run_sort(2));
         B2_TRY(run_acc(1));
+        if (late_h && h_pos == 1) { B2_TRY(run_h()); stage_start[2] = ev[7]; }
         B2_TRY(run_sort(3));
         B2_TRY(run_acc(2));
+        if (late_h && h_pos == 2) { B2_TRY(run_h()); stage_start[3] = ev[7]; }
         B2_TRY(run_sort(4));
         B2_TRY(run_acc(3));
         B2_TRY(run_acc(4));
     } else {   // one stream, one sort group: strictly sort, accumulate, sort, ...
         for (int k = 0; k < 5; ++k) {
-            if (k == 1 && (own_h || hook) && !h_first) B2_TRY(run_h());
+            if (k == 1 && late_h) { B2_TRY(run_h()); stage_start[1] = ev[7]; }
             B2_TRY(run_sort(k));
             B2_TRY(run_acc(k));
         }
@@ -424,9 +438,9 @@ int groth16_prove_core(b200_ctx* ctx, const b200_groth16_pk* pk, const uint64_t*
         tm->compute_h_ms = ev_ms(ev[6], ev[7]);
         const cudaEvent_t a_start = h_first ? ev[7] : ev[0];
         tm->msm_a_ms = ev_ms(a_start, ev_acc[0]);
-        tm->msm_b1_ms = ev_ms(((own_h || hook) && !h_first) ? ev[7] : ev_acc[0], ev_acc[1]);
-        tm->msm_k_ms = ev_ms(ev_acc[1], ev_acc[2]);
-        tm->msm_b2_ms = ev_ms(ev_acc[2], ev_acc[3]);
+        tm->msm_b1_ms = ev_ms(stage_start[1] ? stage_start[1] : ev_acc[0], ev_acc[1]);
+        tm->msm_k_ms = ev_ms(stage_start[2] ? stage_start[2] : ev_acc[1], ev_acc[2]);
+        tm->msm_b2_ms = ev_ms(stage_start[3] ? stage_start[3] : ev_acc[2], ev_acc[3]);
         tm->msm_z_ms = ev_ms(ev_acc[3], ev_acc[4]);
         tm->total_ms = ev_ms(ev[0], ev[8]);
     }

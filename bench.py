@@ -655,7 +655,9 @@ def bls12_377_section(pkg, device_index, log_n, steps, warmup, peak, devices=Non
                                 "model_mac32_per_s": model, "executed_mac32_per_s": executed, "peak_mac32_per_s": peak["mac32_per_s"],
                                 "frac_model": model / peak["mac32_per_s"], "frac_executed": executed / peak["mac32_per_s"],
                                 "note": "model = points x 16 windows x 11 Fp products x 300 MAC32 (SURVEY.md 8(d)); executed = points x the plan's "
-                                        "windows x 2844 MAC32 (XYZZ mixed addition: 8 products x 300 + two 144-MAC32 wide products + one 156-MAC32 reduction)"},
+                                        "windows x [(1 - 2^-rounds) affine additions with shared inversions (6 products x 300 + the inversion share) + 2^-rounds XYZZ mixed "
+                                        "additions (2844 MAC32: 8 products x 300 + two 144-MAC32 wide products + one 156-MAC32 reduction)]; launch_ms is the stage's span "
+                                        "inside the prove core, beside the next MSM's sort"},
                 "msm_plan": {k: info["a"][k] for k in ("c", "windows", "folded", "ba_rounds")},
                 "gpu_launches_per_proof": int(prof["kernel_launches"] // max(1, steps)), "setup_s": t_setup}
     finally:

@@ -219,3 +219,28 @@ def test_prove_core_serial_and_overlapped_agree(ctx, pkg, cref):
     assert np.array_equal(pkg.g2_jac_to_affine(dev["bs2"]), pkg.g2_jac_to_affine(ref["bs2"]))
     [v.free() for v in dv]
     pkh.free()
+
+
+@pytest.mark.parametrize("h_pos", [0, 1, 2])
+def test_prove_core_same_results_wherever_compute_h_is_enqueued(ctx, pkg, cref, h_pos):
+    """Option h_pos (groth16.cu): computeH of a host-buffer proof is enqueued after the accumulation of A, Bs1 or Krs.
+    The five results do not depend on it, and the timings stay consistent (the stages add up to the total)."""
+    nb_mul = 3000
+    w, a, b, c = G.mul_chain_witness(nb_mul, 2)
+    args = [util.fr_arr(x) for x in (a, b, c, w)]
+    _, _, _, _, pkh, _ = build_trapdoor_key(ctx, cref, nb_mul)
+    ref = ctx.groth16_prove_core(pkh, *args)[0].as_dict()
+    ctx.set_option("h_pos", h_pos)
+    try:
+        out, tm = ctx.groth16_prove_core(pkh, *args)
+    finally:
+        ctx.set_option("h_pos", -1)
+    got = out.as_dict()
+    for k in ("ar", "bs1", "krs", "krs2"):
+        assert np.array_equal(pkg.g1_jac_to_affine(got[k]), pkg.g1_jac_to_affine(ref[k])), k
+    assert np.array_equal(pkg.g2_jac_to_affine(got["bs2"]), pkg.g2_jac_to_affine(ref["bs2"]))
+    parts = sum(tm[k] for k in ("compute_h_ms", "msm_a_ms", "msm_b1_ms", "msm_k_ms", "msm_b2_ms", "msm_z_ms"))
+    assert abs(parts - tm["total_ms"]) < 0.25 * tm["total_ms"] + 0.5, (parts, tm)
+    with pytest.raises(pkg.B200Error):
+        ctx.set_option("h_pos", 3)
+    pkh.free()

@@ -776,8 +776,15 @@ def report(args, world, peak, prof, stage, step_ms, e2e_s, clk, verified, inst, 
     ntt_bytes = n_transforms * (n / world if distributed else n) * 64.0 * passes_model   # per rank
     ntt_gbs = ntt_bytes / (ntt["ms"] * 1e-3) / 1e9 if ntt["ms"] else 0.0
     ntt_mac_s = ntt["units"] * MAC32_PER_BUTTERFLY / (ntt["ms"] * 1e-3) if ntt["ms"] else 0.0
-    roofline_ntt = {"kernel": "ntt_pass_kernel", "bound": "hbm", "achieved": ntt_gbs, "peak": hbm_peak, "unit": "GB/s",
-                    "frac": ntt_gbs / hbm_peak, "traffic": None, "peak_source": hbm_src,
+    # measured DRAM traffic of one 2^24 transform (ncu --set full, profiles/r02_final_ntt_2p24_ncu.txt): forward DIF 2.55 GB read +
+    # 1.46 GB written, inverse DIT on the coset (scale table on the last store) 3.11 + 1.47 GB, in 3 pass launches each
+    ntt_traffic_per_transform = 0.5 * (4.01e9 + 4.58e9) * ((n / world if distributed else n) / float(1 << 24))
+    roofline_ntt = {"kernel": "ntt_pass_tma_kernel", "bound": "hbm", "achieved": ntt_gbs, "peak": hbm_peak, "unit": "GB/s",
+                    "frac": ntt_gbs / hbm_peak, "traffic": ntt_traffic_per_transform,
+                    "traffic_source": "ncu dram__bytes_read.sum + dram__bytes_write.sum of the 3 pass launches of one 2^24 transform (mean of a forward DIF, 4.01 GB, "
+                                      "and an inverse coset DIT, 4.58 GB; profiles/r02_final_ntt_2p24_ncu.txt), per transform, scaled linearly to this size; "
+                                      "algorithmic: 64 B per element per pass = %.2f GB per transform at 2 passes" % ((n / world if distributed else n) * 64.0 * passes_model / 1e9),
+                    "peak_source": hbm_src,
                     "imad_frac": ntt_mac_s / mac_peak, "ms_per_transform": ntt["ms"] / max(1, n_transforms),
                     "note": "the transform is IMAD-bound at 254 bits (25 IMAD/B vs a machine balance of ~3): imad_frac is the binding fraction"}
     msm_ms = stage["msm_a_ms"] + stage["msm_b1_ms"] + stage["msm_k_ms"] + stage["msm_z_ms"]

@@ -263,23 +263,42 @@ static __global__ void msm_shift_kernel(const uint32_t* __restrict__ in, uint32_
 }
 
 // 3. scatter (counting sort): cursor starts as a copy of the offsets.
-static __global__ void msm_scatter_kernel(const int32_t* __restrict__ digits, uint32_t n, int c, int W, int fold, uint32_t stride, uint32_t nb,
+// Persistent form: a small grid (a few CTAs per SM) strides over the points, and every thread keeps G cursor atomics in
+// flight (the G digit loads, then the G atomics, then the G stores are issued back to back).  The kernel sits at the L2's
+// request rate for scattered 4-byte accesses, which needs requests in flight, not resident threads: G = 8 in 512 threads
+// per SM holds as many as one atomic in each of 2048 -- and leaves the rest of the SM to the bucket stage of the previous
+// MSM, which runs beside it on the main stream and is bound by the IMAD pipe.
+template <int G>
+static __global__ void __launch_bounds__(256) msm_scatter_kernel(const int32_t* __restrict__ digits, uint32_t n, int c, int W, int fold, uint32_t stride, uint32_t nb,
                                    uint32_t* __restrict__ cursor, uint32_t* __restrict__ sorted) {
-    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-    const bool valid = i < n;
     const int lane = threadIdx.x & 31;
-    for (int w = 0; w < W; ++w) {
-        const int32_t d = valid ? digits[(size_t)w * n + i] : 0;
-        const uint32_t key = d != 0 ? (uint32_t)((d < 0 ? -d : d) - 1) : 0xffffffffu;
-        if (msm_window_is_skewed(w, W, c)) {   // warp-uniform
-            const uint32_t peers = __match_any_sync(0xffffffffu, key);
-            const int leader = __ffs(peers) - 1;
-            uint32_t base = 0;
-            if (key != 0xffffffffu && lane == leader) base = atomicAdd(&cursor[(fold ? 0 : (size_t)w * nb) + key], (uint32_t)__popc(peers));
-            base = __shfl_sync(0xffffffffu, base, leader);
-            if (key != 0xffffffffu) sorted[base + __popc(peers & ((1u << lane) - 1u))] = (fold ? (uint32_t)w * stride + i : i) | (d < 0 ? 0x80000000u : 0u);
-        } else if (key != 0xffffffffu) {
-            sorted[atomicAdd(&cursor[(fold ? 0 : (size_t)w * nb) + key], 1u)] = (fold ? (uint32_t)w * stride + i : i) | (d < 0 ? 0x80000000u : 0u);
+    for (uint32_t base = blockIdx.x * blockDim.x; base < n; base += gridDim.x * blockDim.x) {   // block-uniform trip count
+        const uint32_t i = base + threadIdx.x;
+        const bool valid = i < n;
+        for (int w0 = 0; w0 < W; w0 += G) {
+            int32_t d[G];
+            uint32_t pos[G];
+#pragma unroll
+            for (int k = 0; k < G; ++k) d[k] = (valid && w0 + k < W) ? digits[(size_t)(w0 + k) * n + i] : 0;
+#pragma unroll
+            for (int k = 0; k < G; ++k) {
+                const int w = w0 + k;
+                const uint32_t key = d[k] != 0 ? (uint32_t)((d[k] < 0 ? -d[k] : d[k]) - 1) : 0xffffffffu;
+                pos[k] = 0xffffffffu;
+                if (w < W && msm_window_is_skewed(w, W, c)) {   // warp-uniform
+                    const uint32_t peers = __match_any_sync(0xffffffffu, key);
+                    const int leader = __ffs(peers) - 1;
+                    uint32_t first = 0;
+                    if (key != 0xffffffffu && lane == leader) first = atomicAdd(&cursor[(fold ? 0 : (size_t)w * nb) + key], (uint32_t)__popc(peers));
+                    first = __shfl_sync(0xffffffffu, first, leader);
+                    if (key != 0xffffffffu) pos[k] = first + __popc(peers & ((1u << lane) - 1u));
+                } else if (key != 0xffffffffu) {
+                    pos[k] = atomicAdd(&cursor[(fold ? 0 : (size_t)w * nb) + key], 1u);
+                }
+            }
+#pragma unroll
+            for (int k = 0; k < G; ++k)
+                if (pos[k] != 0xffffffffu) sorted[pos[k]] = (fold ? (uint32_t)(w0 + k) * stride + i : i) | (d[k] < 0 ? 0x80000000u : 0u);
         }
     }
 }

@@ -163,8 +163,9 @@ template <class F, bool FIRST>
 __global__ void __launch_bounds__(128) ba_prep_kernel(const Affine<F>* __restrict__ table, const uint32_t* __restrict__ sorted,
                                                       const F* __restrict__ xs, const F* __restrict__ ys, uint32_t T,
                                                       F* __restrict__ pref, F* __restrict__ cprod) {
-    const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
-    if (t >= T) return;
+    // grid-stride over the chains: the round-0 pass is also launched as a small persistent grid (msm_enqueue_prep0) that
+    // shares the SMs with the bucket stage of the previous MSM
+    for (uint32_t t = blockIdx.x * blockDim.x + threadIdx.x; t < T; t += gridDim.x * blockDim.x) {
     F acc = F::one();
     bool have = false;
     typedef BaPair<F, FIRST> Pair;
@@ -188,6 +189,7 @@ __global__ void __launch_bounds__(128) ba_prep_kernel(const Affine<F>* __restric
         e_nxt = e_far;
     }
     st_vec(cprod + t, acc);
+    }
 }
 
 // thread u inverts the elements u, u + U, u + 2U, ... (at most `chunk` of them) with one Fermat inversion

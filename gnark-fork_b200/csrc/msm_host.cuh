@@ -1,5 +1,7 @@
 // Host driver of the MSM pipeline (template over the coordinate field: Fp for G1, Fp2 for G2).
 #pragma once
+#include <algorithm>
+#include <cstdlib>
 #include <vector>
 #include "msm.cuh"
 #include "msm_ba.cuh"
@@ -175,13 +177,29 @@ struct MsmJob {
 // First batched-affine round, denominator pass: needs the sorted entries and the base table only, and is bound by the
 // DRAM's random-access rate with the multiplier idle -- so it is enqueued with the sort (on the stream that runs beside the
 // previous MSM's arithmetic) and leaves pref0 / cprod0 in the sort group.
+// Small persistent grids for the sort's scatter and the round-0 denominator pass: only where the caller runs them beside
+// another MSM's bucket stage (groth16.cu) and the MSM is large enough that the slower aux chain still ends before that
+// stage does (measured at 2^24 points x 13 windows; not swept below, so the per-rank MSMs of a device group keep full grids).
+template <class F>
+inline bool msm_aux_persistent(const b200_ctx* ctx, const MsmLayout<F>& lay) {
+    return ctx->aux_persist && lay.ba && (size_t)lay.plan.W * lay.n >= ((size_t)3 << 26);
+}
+
 template <class F>
 int msm_enqueue_prep0(b200_ctx* ctx, const MsmJob<F>& job, cudaStream_t st) {
     const MsmLayout<F>& lay = job.lay;
     if (job.n == 0 || !lay.ba) return B200_OK;
     char* base = job.sort_base;
     const uint32_t n_out = (uint32_t)(lay.pad_entries >> 1);
-    const uint32_t threads = n_out / BA_K, blocks = (threads + 127) / 128;
+    const uint32_t threads = n_out / BA_K;
+    uint32_t blocks = (threads + 127) / 128;
+    // Beside the bucket stage of the previous MSM (ctx->aux_persist) the pass runs as 2 CTAs per SM striding over the chains:
+    // it is bound by the DRAM's random-access rate, which 256 threads per SM with two gathers in flight each sustain, and
+    // every CTA it does not occupy stays with the IMAD-bound stage.  Measured on the 2^24 prove core together with the
+    // persistent scatter: 233.8 -> 226.3 ms (profiles/r02_persistent_aux_ab.txt).  B200_PREP0_BPS overrides (0 = full grid).
+    static const int prep0_env = [] { const char* e = getenv("B200_PREP0_BPS"); return e && *e ? atoi(e) : -1; }();
+    const int prep0_bps = prep0_env >= 0 ? prep0_env : (msm_aux_persistent(ctx, lay) ? 2 : 0);
+    if (prep0_bps > 0) blocks = std::min(blocks, (uint32_t)(ctx->sm_count * prep0_bps));
     ba_prep_kernel<F, true><<<blocks, 128, 0, st>>>(job.d_bases, (const uint32_t*)(base + lay.off_sorted), nullptr, nullptr, threads,
                                                     (F*)(base + lay.off_ba_pref0), (F*)(base + lay.off_ba_cprod0));
     B2_CUDA(ctx, cudaGetLastError());
@@ -239,7 +257,19 @@ int msm_enqueue_sort(b200_ctx* ctx, const MsmJob<F>& job, cudaStream_t st) {
     }
     {
         const int bs = 256;
-        msm_scatter_kernel<<<(unsigned)((n + bs - 1) / bs), bs, 0, st>>>(digits, (uint32_t)n, pl.c, pl.W, pl.fold, job.stride, pl.nb, cursor, sorted);
+        // B200_SCATTER_BPS = CTAs per SM of the persistent form (0: one thread per point, one atomic in flight each)
+        static const int scatter_env = [] { const char* e = getenv("B200_SCATTER_BPS"); return e && *e ? atoi(e) : -1; }();
+        const int scatter_bps = scatter_env >= 0 ? scatter_env : (msm_aux_persistent(ctx, lay) ? 1 : 0);
+        const unsigned full = (unsigned)((n + bs - 1) / bs);
+        static const int scatter_bs = [] { const char* e = getenv("B200_SCATTER_BS"); return e && *e ? atoi(e) : 256; }();
+        static const int scatter_g = [] { const char* e = getenv("B200_SCATTER_G"); return e && *e ? atoi(e) : 8; }();
+        if (scatter_bps > 0) {
+            const unsigned grid = std::min((unsigned)((n + scatter_bs - 1) / scatter_bs), (unsigned)(ctx->sm_count * scatter_bps));
+            if (scatter_g >= 16) msm_scatter_kernel<16><<<grid, scatter_bs, 0, st>>>(digits, (uint32_t)n, pl.c, pl.W, pl.fold, job.stride, pl.nb, cursor, sorted);
+            else msm_scatter_kernel<8><<<grid, scatter_bs, 0, st>>>(digits, (uint32_t)n, pl.c, pl.W, pl.fold, job.stride, pl.nb, cursor, sorted);
+        } else {
+            msm_scatter_kernel<1><<<full, bs, 0, st>>>(digits, (uint32_t)n, pl.c, pl.W, pl.fold, job.stride, pl.nb, cursor, sorted);
+        }
         B2_CUDA(ctx, cudaGetLastError());
     }
     {

@@ -362,7 +362,7 @@ int groth16_prove_core(b200_ctx* ctx, const b200_groth16_pk* pk, const uint64_t*
         if (k == 4) B2_CUDA(ctx, cudaStreamWaitEvent(sx, ev_acc[2], 0));
         // every sort but the first runs beside the bucket stage of an earlier MSM: small persistent grids (msm_host.cuh)
         struct Persist { b200_ctx* c; ~Persist() { c->aux_persist = 0; } } persist{ctx};
-        ctx->aux_persist = (overlap && k > 0) ? 1 : 0;
+        ctx->aux_persist = (overlap && (k > 0 || (h_first && ctx->h_sort_overlap))) ? 1 : 0;   // k = 0: beside computeH when the inputs are resident
         if (k == 3 && share_b) B2_TRY(msm_g2_job_prep0(ctx, jobs[k], sx));   // batched-affine rounds: Bs2's own denominator pass over Bs1's entries
         else B2_TRY(groups[k] == 2 ? msm_g2_job_sort(ctx, jobs[k], sx) : msm_g1_job_sort(ctx, jobs[k], sx));
         B2_CUDA(ctx, cudaEventRecord(ev_sort[k], sx));

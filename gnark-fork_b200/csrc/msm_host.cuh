@@ -198,7 +198,9 @@ int msm_enqueue_prep0(b200_ctx* ctx, const MsmJob<F>& job, cudaStream_t st) {
     // every CTA it does not occupy stays with the IMAD-bound stage.  Measured on the 2^24 prove core together with the
     // persistent scatter: 233.8 -> 226.3 ms (profiles/r02_persistent_aux_ab.txt).  B200_PREP0_BPS overrides (0 = full grid).
     static const int prep0_env = [] { const char* e = getenv("B200_PREP0_BPS"); return e && *e ? atoi(e) : -1; }();
-    const int prep0_bps = prep0_env >= 0 ? prep0_env : (msm_aux_persistent(ctx, lay) ? 2 : 0);
+    static const int prep0_env_g2 = [] { const char* e = getenv("B200_PREP0_BPS_G2"); return e && *e ? atoi(e) : -1; }();
+    int prep0_bps = prep0_env >= 0 ? prep0_env : (msm_aux_persistent(ctx, lay) ? 2 : 0);
+    if (sizeof(F) > sizeof(Fp) && prep0_env_g2 >= 0) prep0_bps = prep0_env_g2;
     if (prep0_bps > 0) blocks = std::min(blocks, (uint32_t)(ctx->sm_count * prep0_bps));
     ba_prep_kernel<F, true><<<blocks, 128, 0, st>>>(job.d_bases, (const uint32_t*)(base + lay.off_sorted), nullptr, nullptr, threads,
                                                     (F*)(base + lay.off_ba_pref0), (F*)(base + lay.off_ba_cprod0));

@@ -179,10 +179,13 @@ struct MsmJob {
 // previous MSM's arithmetic) and leaves pref0 / cprod0 in the sort group.
 // Small persistent grids for the sort's scatter and the round-0 denominator pass: only where the caller runs them beside
 // another MSM's bucket stage (groth16.cu) and the MSM is large enough that the slower aux chain still ends before that
-// stage does (measured at 2^24 points x 13 windows; not swept below, so the per-rank MSMs of a device group keep full grids).
+// stage does (measured at 2^24 points x 13 windows: 233.8 -> 226.3 ms per proof, and at 2^22: Groth16 64.2 -> 63.3 ms, PlonK
+// 130.6 -> 128.6 ms, BLS12-377 140.8 -> 139.5 ms; not swept below that, so the 2^21-point MSMs of an 8-GPU group keep full grids).
 template <class F>
 inline bool msm_aux_persistent(const b200_ctx* ctx, const MsmLayout<F>& lay) {
-    return ctx->aux_persist && lay.ba && (size_t)lay.plan.W * lay.n >= ((size_t)3 << 26);
+    static const long long min_env = [] { const char* e = getenv("B200_AUX_MIN_ENTRIES"); return e && *e ? atoll(e) : -1LL; }();
+    const size_t min_entries = min_env >= 0 ? (size_t)min_env : ((size_t)3 << 24);   // 2^22 points x 13 windows and up
+    return ctx->aux_persist && lay.ba && (size_t)lay.plan.W * lay.n >= min_entries;
 }
 
 template <class F>

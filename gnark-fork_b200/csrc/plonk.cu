@@ -250,7 +250,11 @@ int commit_many(b200_ctx* ctx, const b200_bases* srs, const Fr* const* coeffs, c
     auto run_sort = [&](int k) -> int {
         if (wait && wait[k]) B2_CUDA(ctx, cudaStreamWaitEvent(sx, wait[k], 0));
         if (k >= 2) B2_CUDA(ctx, cudaStreamWaitEvent(sx, ev_acc[k - 2], 0));       // its sort group is free again
-        B2_TRY(msm_g1_job_sort(ctx, jobs[k], sx));
+        {   // every sort but the first runs beside the previous commitment's bucket stage (msm_aux_persistent, msm_host.cuh)
+            struct Persist { b200_ctx* c; ~Persist() { c->aux_persist = 0; } } persist{ctx};
+            ctx->aux_persist = (overlap && k > 0) ? 1 : 0;
+            B2_TRY(msm_g1_job_sort(ctx, jobs[k], sx));
+        }
         B2_CUDA(ctx, cudaEventRecord(ev_sort[k], sx));
         return B200_OK;
     };

@@ -631,6 +631,7 @@ int b200_set_option(b200_ctx* ctx, const char* key, long value) try {
     else if (k == "msm_fold_c") { if (value != 0 && (value < 8 || value > 24)) return ctx->fail(B200_ERR_ARG, "msm_fold_c out of range"); ctx->msm_fold_c = (int)value; }
     else if (k == "ntt_tma") ctx->ntt_tma = value ? 1 : 0;
     else if (k == "h_sort_overlap") ctx->h_sort_overlap = value ? 1 : 0;
+    else if (k == "aux_persist_min") ctx->aux_persist_min = value < 0 ? -1 : (long long)value;
     else if (k == "h_pos") { if (value < -1 || value > 2) return ctx->fail(B200_ERR_ARG, "h_pos out of range (-1 automatic, 0..2)"); ctx->h_pos = (int)value; }
     else if (k == "l2_fetch") {   // device-wide hint: bytes DRAM -> L2 fetches at most per miss (32, 64 or 128); experiments on the table gathers
         if (value != 32 && value != 64 && value != 128) return ctx->fail(B200_ERR_ARG, "l2_fetch must be 32, 64 or 128");

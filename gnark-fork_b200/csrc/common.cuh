@@ -25,6 +25,7 @@ struct b200_ctx {
     cudaStream_t post_stream = nullptr;     // bucket reduction of the previous MSM, overlapped with the current accumulation
     void* h_stage = nullptr;                // page-locked staging of MSM result points
     size_t h_stage_bytes = 0;
+    long long aux_persist_min = -1;         // entries (windows x points) from which the persistent aux grids apply; -1 = default (msm_aux_persistent)
     int aux_persist = 0;                    // set by a caller that enqueues an MSM's sort beside another MSM's bucket stage: the sort's scatter and the round-0 denominator pass run as small persistent grids (msm_host.cuh)
     int h_pos = -1;                         // host-buffer proofs: computeH is enqueued after the accumulation of MSM h_pos (0 A, 1 B1, 2 K); -1 = automatic
     int h_sort_overlap = 0;                 // 1: with device-resident inputs the first MSM's sort runs under computeH instead of after it

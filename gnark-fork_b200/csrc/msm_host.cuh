@@ -184,7 +184,7 @@ struct MsmJob {
 template <class F>
 inline bool msm_aux_persistent(const b200_ctx* ctx, const MsmLayout<F>& lay) {
     static const long long min_env = [] { const char* e = getenv("B200_AUX_MIN_ENTRIES"); return e && *e ? atoll(e) : -1LL; }();
-    const size_t min_entries = min_env >= 0 ? (size_t)min_env : ((size_t)3 << 24);   // 2^22 points x 13 windows and up
+    const size_t min_entries = ctx->aux_persist_min >= 0 ? (size_t)ctx->aux_persist_min : min_env >= 0 ? (size_t)min_env : ((size_t)3 << 24);   // default: 2^22 points x 13 windows and up
     return ctx->aux_persist && lay.ba && (size_t)lay.plan.W * lay.n >= min_entries;
 }
 

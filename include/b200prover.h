@@ -181,7 +181,8 @@ const char *b200_version(void);
  * "msm_fold_c" (window width of the folded path, 0 = automatic), "msm_overlap" (1 = the prove core
  * sorts the next MSM on a second stream while the current one accumulates; 0 = strictly serial), "msm_acc_smem" (bit 0 /
  * bit 1: G1 / G2 bucket accumulation keeps its running sum in shared memory; default G2 only on BN254, off on
- * BLS12-377), "msm_ba" (batched-affine pre-reduction rounds, 15 = chosen from the mean bucket load: the default), "h_pos" (proofs from host buffers: computeH is enqueued after the
+ * BLS12-377), "msm_ba" (batched-affine pre-reduction rounds, 15 = chosen from the mean bucket load: the default), "aux_persist_min" (entries = windows x points from which an MSM's sort and round-0 denominator pass, when they run beside
+ * another MSM's bucket stage, are launched as small persistent grids; -1 = the measured default, 5e7), "h_pos" (proofs from host buffers: computeH is enqueued after the
  * accumulation of MSM 0 / 1 / 2 = A / Bs1 / Krs, so that more of the proof covers the copy of a, b, c; -1 = automatic), "ntt_tile_log" (log2 of the
  * shared-memory tile, 6..12), "ntt_strided_stages" (max stages of a strided NTT pass, 1..12),
  * "ntt_threads" (threads per NTT CTA, power of two), "ntt_tma" (1 = NTT passes staged by TMA: one cp.async.bulk.tensor

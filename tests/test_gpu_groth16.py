@@ -244,3 +244,29 @@ def test_prove_core_same_results_wherever_compute_h_is_enqueued(ctx, pkg, cref, 
     with pytest.raises(pkg.B200Error):
         ctx.set_option("h_pos", 3)
     pkh.free()
+
+
+def test_prove_core_with_persistent_aux_grids(ctx, pkg, cref):
+    """The sort's scatter and the round-0 denominator pass as small persistent grids (msm_aux_persistent, msm_host.cuh) --
+    the form the prove core uses from 2^22-point MSMs up -- forced here on a small instance (rounds forced on too):
+    the five results equal those of the full-grid kernels."""
+    nb_mul = (1 << 12) - 1
+    w, a, b, c = G.mul_chain_witness(nb_mul, 2)
+    args = [util.fr_arr(x) for x in (a, b, c, w)]
+    _, _, _, _, pkh, _ = build_trapdoor_key(ctx, cref, nb_mul)
+    ref = ctx.groth16_prove_core(pkh, *args)[0].as_dict()
+    ctx.set_option("msm_ba", 2)
+    ctx.set_option("msm_ba_force", 1)
+    try:
+        rounds = ctx.groth16_prove_core(pkh, *args)[0].as_dict()
+        ctx.set_option("aux_persist_min", 0)
+        persistent = ctx.groth16_prove_core(pkh, *args)[0].as_dict()
+    finally:
+        ctx.set_option("aux_persist_min", -1)
+        ctx.set_option("msm_ba_force", 0)
+        ctx.set_option("msm_ba", 15)
+    for got in (rounds, persistent):
+        for k in ("ar", "bs1", "krs", "krs2"):
+            assert np.array_equal(pkg.g1_jac_to_affine(got[k]), pkg.g1_jac_to_affine(ref[k])), k
+        assert np.array_equal(pkg.g2_jac_to_affine(got["bs2"]), pkg.g2_jac_to_affine(ref["bs2"]))
+    pkh.free()
